@@ -27,7 +27,7 @@ ln -s "$CRL/crl.gui/src" "$INC/crl/gui"
 ln -s "$CRL/crl.algorithm/src" "$INC/crl/alg"
 ln -s "$CRL/crl.loader/src" "$INC/crl/loader"
 
-CXX="${CXX:-g++}"
+CXX="${ORACLE_CXX:-/usr/bin/g++}"   # not $CXX: the image exports a g++ that links libstdc++ statically
 FLAGS="-std=c++17 -O2 -w -fPIC -DSOP_VNS -I$HERE/shim -I$INC -I$SRC -I$HERE"
 TUS=""
 for f in vns_sop_path vns_sop_solver sop_loader dataset_loader_sop dataset_loader_op math_common \
