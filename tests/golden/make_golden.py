@@ -1,0 +1,128 @@
+"""Generates tests/golden/*.npz + golden.json from the reference tree (run HERE, where
+/root/reference exists; the outputs are committed and travel to the GPU box).
+
+  python tests/golden/make_golden.py
+
+Instances are re-encoded (.npz, ids 0-based) from /root/reference/datasets; every expected value
+is produced by the UNMODIFIED reference code in oracle/_ref/liboracle_ref.so (op::VnsSopPath,
+op::VnsSopSolver) or the oracle/_ref/sop_vns_ref binary - never by the repo's own code.
+"""
+import json
+import os
+import subprocess
+import sys
+import tempfile
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+from oracle import binding as ob  # noqa: E402
+from vns_sop_b200 import instances as ins  # noqa: E402
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+from conftest import random_candidates  # noqa: E402
+
+DS = "/root/reference/datasets/"
+INSTANCES = {
+    "berlin52": DS + "sop/11berlin52_T60_p2.sop",
+    "krob200": DS + "sop/40krob200_T80_p2.sop",
+    "opn_s08": DS + "opn_sop_dataset/tsiligirides_problem_2_budget_30_d_50_s_08.sop",
+    "dop_s04": DS + "dop_sop_dataset/tsiligirides_problem_2_budget_30_r_50_s_04.sop",
+    "dop_s08": DS + "dop_sop_dataset/tsiligirides_problem_2_budget_30_r_50_s_08.sop",
+    "dop_s12": DS + "dop_sop_dataset/tsiligirides_problem_2_budget_30_r_50_s_12.sop",
+    "vm1084": DS + "sop/217vm1084_T100_p1.sop",
+}
+FULL_SOLVE = ["berlin52", "opn_s08", "dop_s12", "krob200"]   # seed 1, stock sop.cfg
+N_CANDS = 600
+
+
+def golden_for(name, path):
+    sf = ins.parse_sop(path)
+    ins.save_npz(sf, os.path.join(HERE, name + ".npz"))
+    pb = ins.build_problem(sf)
+    r = ob.RefOracle(path)
+    g = {"C": int(r.C), "N": int(pb.N), "budget": r.budget, "file": os.path.basename(path)}
+    arrays = {"m": r.m, "initial_vns": r.initial_vns()}
+    lo, hi = r.bounds()
+    arrays["dmin"], arrays["dmax"] = lo, hi
+    if pb.N <= 300:
+        arrays["dense"] = r.dense()
+    else:                     # large table: keep a checksum + a few blocks
+        W = r.dense()
+        g["dense_sum"] = float(W.sum())
+        g["dense_wsum"] = float((W * (np.arange(pb.N)[:, None] % 7 + 1) * (np.arange(pb.N)[None, :] % 5 + 1)).sum())
+    # greedy initial solution
+    p = r.path()
+    p.greedy()
+    g["greedy"] = {"T": int(p.T), "length": p.length(), "reward": p.reward()}
+    arrays["greedy_vns"] = p.vns
+    mp = int(r.m.max())
+    F, B, pF, pB = p.layers(mp)
+    arrays.update(greedy_F=F, greedy_B=B, greedy_pF=pF, greedy_pB=pB)
+    cl, nd = p.get_path()
+    arrays.update(greedy_path_cluster=cl, greedy_path_node=nd)
+    g["greedy"]["length_calc"] = p.length_calc()
+    g["greedy"]["length_rear"] = p.length_rear()
+    rs = np.random.RandomState(1234)
+    cands = random_candidates(rs, p.vns, p.T, N_CANDS)
+    ln, lb = p.eval_batch(cands)
+    arrays.update(cands=cands, cand_len=ln, cand_lb=lb)
+    # neighbourhood drivers, seed 7: shake(k) then local search(k), 6 rounds
+    steps = 6 if pb.N <= 300 else 2
+    r.seed(7)
+    seq_vns, seq = [], []
+    for it in range(steps):
+        k = 1 + it % 2
+        p.shake(k)
+        seq.append({"op": "shake", "k": k, "T": int(p.T), "length": p.length(), "reward": p.reward()})
+        seq_vns.append(p.vns)
+        p.local_search(k, len(p.vns) ** 2 if pb.N <= 300 else 4000)
+        seq.append({"op": "ls", "k": k, "T": int(p.T), "length": p.length(), "reward": p.reward()})
+        seq_vns.append(p.vns)
+    g["sequence"] = seq
+    g["sequence_ls_iters"] = "nvns^2" if pb.N <= 300 else 4000
+    g["rand_after_sequence"] = int(r.rand())
+    arrays["sequence_vns"] = np.array(seq_vns, dtype=np.int32)
+    np.savez_compressed(os.path.join(HERE, name + "_golden.npz"), **arrays)
+    return g
+
+
+def full_solve(path, seed=1):
+    with tempfile.TemporaryDirectory() as td:
+        subprocess.check_call([ob.REF_BIN, "--problem=" + path, "--seed=%d" % seed, "--output=" + td],
+                              stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        rec = open(os.path.join(td, "results.log")).read().strip().rstrip(";")
+    d = dict(kv.split(":", 1) for kv in rec.split(";"))
+    impr = [x.split("|") for x in d["SOLUTION_TIME_REWARD_LENGTH_IMPROVEMENTS"].split(",")]
+    return {"seed": seed, "NUM_ITERS": int(d["NUM_ITERS"]), "BUDGET": float(d["BUDGET"]),
+            "REWARDS": float(d["REWARDS"]), "MAX_ACHIEVABLE_REWARDS": float(d["MAX_ACHIEVABLE_REWARDS"]),
+            "LENGTH": float(d["LENGTH"]), "NUM_ITERS_LAST_IMPR": int(d["NUM_ITERS_LAST_IMPR"]),
+            "RESULT_TARGET_IDS": [int(x) for x in d["RESULT_TARGET_IDS"].split(",")],
+            "RESULT_CLUSTER_IDS": [int(x) for x in d["RESULT_CLUSTER_IDS"].split(",")],
+            "IMPROVEMENTS": [[float(x[1]), float(x[2])] for x in impr]}
+
+
+def main():
+    ob.build()
+    out = {}
+    for name, path in INSTANCES.items():
+        print("golden:", name, flush=True)
+        out[name] = golden_for(name, path)
+    for name in FULL_SOLVE:
+        print("full solve:", name, flush=True)
+        out[name]["solve_seed1"] = full_solve(INSTANCES[name])
+    # glibc rand() stream (a16): first 64 outputs for seeds 0,1,2,12345 via the reference process
+    r = ob.RefOracle(INSTANCES["berlin52"])
+    rnd = {}
+    for s in (0, 1, 2, 12345):
+        r.seed(s)
+        rnd[str(s)] = [int(r.rand()) for _ in range(64)]
+    out["_rand"] = rnd
+    with open(os.path.join(HERE, "golden.json"), "w") as fh:
+        json.dump(out, fh, indent=1)
+    print("wrote golden.json")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,92 @@
+"""The C restatement (oracle/vns_oracle.c) against the committed golden vectors, which were
+produced by the reference's own code (tests/golden/make_golden.py).  CPU only."""
+import numpy as np
+import pytest
+
+from conftest import ALL, SMALL, load_arrays, load_problem
+from oracle import binding as ob
+
+
+@pytest.mark.parametrize("name", ALL)
+def test_table_bounds_greedy(name, golden):
+    sf, pb = load_problem(name)
+    g, a = golden[name], load_arrays(name)
+    assert pb.C == g["C"] and pb.N == g["N"] and pb.budget == g["budget"]
+    assert (pb.m == a["m"]).all() and (pb.initial_vns() == a["initial_vns"]).all()
+    o = ob.Oracle(pb)
+    W = o.dense()
+    if "dense" in a:
+        assert (W == a["dense"]).all()
+    else:
+        assert float(W.sum()) == g["dense_sum"]
+        wsum = (W * (np.arange(pb.N)[:, None] % 7 + 1) * (np.arange(pb.N)[None, :] % 5 + 1)).sum()
+        assert float(wsum) == g["dense_wsum"]
+    lo, hi = o.bounds()
+    assert (lo == a["dmin"]).all() and (hi == a["dmax"]).all()
+    p = o.path()
+    p.greedy()
+    assert p.T == g["greedy"]["T"] and (p.vns == a["greedy_vns"]).all()
+    assert p.length() == g["greedy"]["length"] and p.reward() == g["greedy"]["reward"]
+    assert p.length_rear() == g["greedy"]["length_rear"] and p.length_calc() == g["greedy"]["length_calc"]
+    F, B, pF, pB = p.layers()
+    for l in range(p.T + 2):
+        c = pb.start if l == 0 else (pb.goal if l == p.T + 1 else p.vns[l - 1])
+        k = pb.m[c]
+        assert (F[l, :k] == a["greedy_F"][l, :k]).all() and (B[l, :k] == a["greedy_B"][l, :k]).all()
+        assert (pF[l, :k] == a["greedy_pF"][l, :k]).all() and (pB[l, :k] == a["greedy_pB"][l, :k]).all()
+    cl, nd = p.get_path()
+    assert (cl == a["greedy_path_cluster"]).all() and (nd == a["greedy_path_node"]).all()
+    ln, lb = p.eval_batch(a["cands"])
+    assert (ln == a["cand_len"]).all() and (lb == a["cand_lb"]).all()
+
+
+@pytest.mark.parametrize("name", ALL)
+def test_driver_sequence(name, golden):
+    sf, pb = load_problem(name)
+    g, a = golden[name], load_arrays(name)
+    o = ob.Oracle(pb)
+    p = o.path(a["greedy_vns"], g["greedy"]["T"])
+    rng = ob.new_rng(7)
+    for i, st in enumerate(g["sequence"]):
+        if st["op"] == "shake":
+            p.shake(st["k"], rng)
+        else:
+            iters = len(p.vns) ** 2 if g["sequence_ls_iters"] == "nvns^2" else g["sequence_ls_iters"]
+            p.local_search(st["k"], iters, rng)
+        assert p.T == st["T"] and p.length() == st["length"] and p.reward() == st["reward"], (i, st)
+        assert (p.vns == a["sequence_vns"][i]).all()
+    assert ob.rng_next(rng) == g["rand_after_sequence"]
+
+
+def test_glibc_rand_stream(golden):
+    for seed, vals in golden["_rand"].items():
+        rng = ob.new_rng(int(seed))
+        assert [ob.rng_next(rng) for _ in vals] == vals
+
+
+@pytest.mark.parametrize("name", ["berlin52", "opn_s08", "dop_s12"])
+def test_full_solve_seed1(name, golden):
+    sf, pb = load_problem(name)
+    s = golden[name]["solve_seed1"]
+    o = ob.Oracle(pb)
+    p = o.path()
+    res = p.solve(1)
+    assert res.num_iters == s["NUM_ITERS"] and res.num_iters_last_impr == s["NUM_ITERS_LAST_IMPR"]
+    assert res.reward == s["REWARDS"] and res.length == s["LENGTH"]
+    impr = [[res.impr_reward[i], res.impr_length[i]] for i in range(res.n_improvements)]
+    assert impr == s["IMPROVEMENTS"]
+    cl, nd = p.get_path()
+    assert list(pb.node_id[pb.off[cl] + nd]) == s["RESULT_TARGET_IDS"]
+    assert list(pb.orig_cluster_id[cl]) == s["RESULT_CLUSTER_IDS"]
+
+
+@pytest.mark.parametrize("S", [4, 8, 12])
+def test_dubins_known_answers(S):
+    """98 784 known answers: the EXPLICIT matrices shipped with the reference's DOP datasets equal
+    ceil(Dubins length) within the +-1e-9-before-ceil rule."""
+    sf, pb = load_problem("dop_s%02d" % S)
+    o = ob.Oracle(pb, dubins=(S, sf.dubins_radius, 0))
+    L, W = o.dense(), pb.W
+    ok = (np.ceil(L) == W) | (np.ceil(L - 1e-9) == W) | (np.ceil(L + 1e-9) == W)
+    assert ok.all()
+    assert (np.ceil(L) != W).sum() <= 2 + pb.N   # only collinear near-integers and the diagonal

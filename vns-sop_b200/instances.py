@@ -133,14 +133,14 @@ def write_sop(sf: SopFile, path: str) -> None:
         else:
             fh.write("NODE_COORD_SECTION\n")
             for i, (x, y) in enumerate(sf.coords):
-                fh.write(f"{i + 1} {x!r} {y!r}\n")
+                fh.write(f"{i + 1} {float(x)!r} {float(y)!r}\n")
         fh.write("GTSP_SET_SECTION: set_id set_profit id-vertex-list\n")
         for c, nodes in enumerate(sf.set_nodes):
             fh.write(f"{c} {sf.set_profit[c]:g} " + " ".join(str(int(n) + 1) for n in nodes) + "\n")
         if sf.centers is not None:
             fh.write("GTSP_SET_CENTER_COORD_SECTION: set_id x y\n")
             for c, (x, y) in enumerate(sf.centers):
-                fh.write(f"{c} {x!r} {y!r}\n")
+                fh.write(f"{c} {float(x)!r} {float(y)!r}\n")
 
 
 def save_npz(sf: SopFile, path: str) -> None:
