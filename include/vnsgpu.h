@@ -1,0 +1,180 @@
+/* vnsgpu.h - C ABI of the B200 (sm_100a) neighbourhood-evaluation engine for VNS-SOP.
+ *
+ * Drop-in seam: the reference (ctu-mrs/vns-sop) has no plugin/FFI layer; the boundary is the public
+ * interface of op::VnsSopPath (sources/vns_sop_path.h:22-194) + its process-global tables
+ * (setSamplesDistances, vns_sop_path.h:30-31,157-160) and the neighbourhood drivers of
+ * op::VnsSopSolver that call it (sources/vns_sop_solver.cpp:364-385,469-864,931-1155).
+ * Each entry point below names the reference interface it replaces.  INTEGRATION.md shows the
+ * binding a maintainer adds to sources/vns_sop_solver.cpp.
+ *
+ * Conventions: plain pointers and sizes only; every function returns a vnsgpu_status (0 = ok) and
+ * never exits the process (the reference exit(1)s on range errors, e.g. vns_sop_path.cpp:69-72);
+ * host pointers are copied during the call; the context owns all device memory; one host thread
+ * per context.  "_dev" variants take DEVICE pointers and a CUDA stream handle and do not
+ * synchronise.  Clusters are numbered as after the reference loader's renumbering
+ * (sop_loader.cpp:118-156); samples are stored cluster-contiguously.
+ */
+#ifndef VNSGPU_H
+#define VNSGPU_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct vnsgpu_ctx vnsgpu_ctx;
+
+typedef enum {
+   VNSGPU_OK = 0,
+   VNSGPU_E_RANGE = 1,        /* index outside the range the reference exit(1)s on */
+   VNSGPU_E_CUDA = 2,         /* CUDA runtime error, see vnsgpu_last_error */
+   VNSGPU_E_STATE = 3,        /* call order (no table, bad handle, ...) */
+   VNSGPU_E_INCONSISTENT = 4, /* forward/backward length mismatch (vns_sop_path.cpp:80-88) or
+                                 over-budget improved tour (vns_sop_solver.cpp:229-237) */
+   VNSGPU_E_NOMEM = 5
+} vnsgpu_status;
+
+/* edge-weight rules of SOPLoader (sop_loader.cpp:278,360,474-486) */
+enum { VNSGPU_RULE_RAW = 0, VNSGPU_RULE_ROUND = 1, VNSGPU_RULE_CEIL = 2 };
+
+/* candidate operations = the const queries of VnsSopPath */
+enum {
+   VNSGPU_OP_ADD = 0,      /* tryToAdd(a = cluster, b = idx)           vns_sop_path.cpp:245-304  */
+   VNSGPU_OP_REPLACE = 1,  /* tryToReplace(a = cluster, b = idx, 1)    vns_sop_path.cpp:456-513  */
+   VNSGPU_OP_REMOVE = 2,   /* tryToRemove(a = idx)                     vns_sop_path.cpp:515-535  */
+   VNSGPU_OP_MOVE = 3,     /* tryToMove(a = what, b = where)           vns_sop_path.cpp:932-1154 */
+   VNSGPU_OP_EXCHANGE = 4  /* tryToExchange(a = idx1, b = idx2)        vns_sop_path.cpp:635-797  */
+};
+
+typedef struct {
+   int32_t op, a, b;
+   int32_t gain_cluster; /* cluster whose reward is gained (ADD/REPLACE) or -1; used for flags */
+} vnsgpu_cand;
+
+/* per-candidate result flags */
+enum {
+   VNSGPU_F_FEASIBLE = 1, /* len <= budget */
+   VNSGPU_F_ACCEPT = 2,   /* len <= budget && (dReward > 0 || L - len > 1e-5)
+                             (vns_sop_solver.cpp:619,805-806) */
+   VNSGPU_F_LB_SKIP = 4,  /* lower bound > budget: the reference skips the evaluation
+                             (vns_sop_solver.cpp:539,574,749,779) */
+   VNSGPU_F_BAD = 8       /* indices out of range: len = NaN */
+};
+
+/* glibc rand() state (random_r TYPE_3), replayed bit-exactly: math_common.cpp:21-28 */
+typedef struct {
+   int32_t r[31];
+   int32_t f, b;
+   int32_t pad;
+} vnsgpu_rng;
+
+typedef struct {
+   int64_t proposals, lb_skips, evals, accepts, rounds;
+} vnsgpu_ls_stats;
+
+typedef struct {
+   int32_t num_iterations;            /* sop.cfg num-iterations            (vns_sop_solver.cpp:64) */
+   int32_t num_iterations_unimproved; /* sop.cfg num-iterations-unimproved (:65) */
+   int32_t lower_bound_skip;          /* lower-bound-above-budget-then-skip (:68) */
+   int32_t greedy_initial;            /* initial-greedy-solution (:70) */
+   double budget;                     /* TMAX */
+   double max_time_ms;                /* maximal-calculation-time-sec * 1000 (:67); <=0: none */
+   uint32_t seed;                     /* srand(seed) hook (math_common.cpp:9-14) */
+   int32_t max_improvements;          /* capacity of the improvement log arrays */
+} vnsgpu_vns_params;
+
+typedef struct {
+   int32_t num_iters, num_iters_last_impr, n_improvements, status;
+   double reward, length;
+   double time_ms, time_last_impr_ms;
+   int64_t proposals, evals, accepts;
+} vnsgpu_vns_result;
+
+/* ---- context ------------------------------------------------------------------------------ */
+vnsgpu_status vnsgpu_create(vnsgpu_ctx **out, int device);
+void vnsgpu_destroy(vnsgpu_ctx *ctx);
+const char *vnsgpu_last_error(const vnsgpu_ctx *ctx);
+const char *vnsgpu_version(void);
+/* number of kernels this context has launched so far (bench.py's gpu_launches) */
+int64_t vnsgpu_launch_count(const vnsgpu_ctx *ctx);
+/* run everything on this CUDA stream (cudaStream_t as void*); NULL = the context's own stream */
+vnsgpu_status vnsgpu_set_stream(vnsgpu_ctx *ctx, void *stream);
+vnsgpu_status vnsgpu_sync(vnsgpu_ctx *ctx);
+
+/* ---- instance + distance table: replaces VnsSopPath::setSamplesDistances (vns_sop_path.cpp:38-48)
+ *      fed by SOPLoader::getSOPFromNodes / getSOPFromWeightMatrix / getOP / getOPN ---------------- */
+vnsgpu_status vnsgpu_set_clusters(vnsgpu_ctx *ctx, int C, const int *m, const double *reward, int start,
+                                  int goal);
+/* a1/a3: D = rule(sqrt(dx*dx+dy*dy)); xy = N x 2 doubles in sample order (sop_loader.cpp:457-491) */
+vnsgpu_status vnsgpu_build_table_euclid(vnsgpu_ctx *ctx, const double *xy, int rule);
+/* a4 (new; reference ships the result as EXPLICIT matrices): every cluster has S heading samples
+ * theta_k = 2 pi k / S at its centre; D = ceil(Dubins length) or the raw length if !do_ceil */
+vnsgpu_status vnsgpu_build_table_dubins(vnsgpu_ctx *ctx, const double *centers, int S, double rho, int do_ceil);
+/* a2: gather from an explicit N x N row-major matrix in sample order (sop_loader.cpp:413-427) */
+vnsgpu_status vnsgpu_set_table_dense(vnsgpu_ctx *ctx, const double *W);
+vnsgpu_status vnsgpu_get_table_dense(vnsgpu_ctx *ctx, double *W);
+/* a5: calcClusterDistancesBounds (vns_sop_solver.cpp:262-297); C x C each; either may be NULL */
+vnsgpu_status vnsgpu_get_bounds(vnsgpu_ctx *ctx, double *dmin, double *dmax);
+/* bytes of the device-resident table (8 N^2) */
+int64_t vnsgpu_table_bytes(const vnsgpu_ctx *ctx);
+
+/* ---- paths: value-type VnsSopPath objects become handles (copy = device memcpy) -------------- */
+vnsgpu_status vnsgpu_path_create(vnsgpu_ctx *ctx, int *path);
+vnsgpu_status vnsgpu_path_copy(vnsgpu_ctx *ctx, int dst, int src);
+/* targets := vns[0..T) and full update() (vns_sop_path.cpp:1321-1404); vns = the solver's VNS vector */
+vnsgpu_status vnsgpu_path_set(vnsgpu_ctx *ctx, int path, const int *vns, int nvns, int T);
+/* addPoint(c, idx) / removePoint(idx) + updateAfterInsert/Remove (vns_sop_path.cpp:67-103,154-180,
+ * 1406-1540); these touch targets only, like the reference (the VNS vector is the caller's) */
+vnsgpu_status vnsgpu_path_add_point(vnsgpu_ctx *ctx, int path, int cluster, int idx);
+vnsgpu_status vnsgpu_path_remove_point(vnsgpu_ctx *ctx, int path, int idx);
+/* getNumTargets/getAllTargets/getPathLength/getPathLengthRear/getReward (+ the VNS vector);
+ * any output pointer may be NULL */
+vnsgpu_status vnsgpu_path_get(vnsgpu_ctx *ctx, int path, int *T, int *targets, int *nvns, int *vns,
+                              double *length, double *length_rear, double *reward);
+/* getPath (vns_sop_path.cpp:1542-1599) + getPathLengthCalculate (:1700-1741): T+2 entries */
+vnsgpu_status vnsgpu_path_get_solution(vnsgpu_ctx *ctx, int path, int *cluster, int *node, double *length_calc);
+/* shortest / shortest_back as (T+2) x stride doubles (tests; stride >= max cluster size) */
+vnsgpu_status vnsgpu_path_get_dp(vnsgpu_ctx *ctx, int path, double *F, double *B, int stride);
+
+/* ---- batched candidate evaluation (a8-a13): all tryTo* + lower bounds + accept predicate ------ */
+/* host buffers; len/lb/flags may be NULL; first_accept (may be NULL) receives the smallest index
+ * whose ACCEPT flag is set and (when skip != 0) whose LB_SKIP flag is not, or -1 */
+vnsgpu_status vnsgpu_eval_batch(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *cands, double budget,
+                                int skip, double *len, double *lb, uint8_t *flags, int64_t *first_accept);
+/* device buffers, asynchronous on `stream` (NULL = context stream); d_first_accept: one int64,
+ * must be preset to INT64_MAX by the caller (atomicMin target) or NULL */
+vnsgpu_status vnsgpu_eval_batch_dev(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *d_cands,
+                                    double budget, int skip, double *d_len, double *d_lb, uint8_t *d_flags,
+                                    long long *d_first_accept, void *stream);
+/* draws n proposals with the reference's proposal distribution for neighbourhood `kind`
+ * (1 = insertRandom :507-519 -> MOVE / ADD, 2 = exchangeRandom :723-730 -> EXCHANGE / REPLACE) against
+ * the path's current state, advancing *rng exactly as the reference's draws would; HOST buffer */
+vnsgpu_status vnsgpu_gen_proposals(vnsgpu_ctx *ctx, int path, int kind, int64_t n, vnsgpu_rng *rng,
+                                   vnsgpu_cand *cands);
+/* algorithmic bytes of a candidate list: 8*(sum m_src*m_dst + m_first + m_last) + 8 */
+vnsgpu_status vnsgpu_cand_bytes(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *cands, int64_t *bytes);
+
+/* ---- neighbourhood drivers (a15, a16) ---------------------------------------------------------- */
+void vnsgpu_rng_seed(vnsgpu_rng *rng, uint32_t seed); /* srand(seed) */
+int32_t vnsgpu_rng_next(vnsgpu_rng *rng);             /* rand() */
+/* insertRandom (kind 1, vns_sop_solver.cpp:469-684) / exchangeRandom (kind 2, :686-864): the whole
+ * call runs on the device, trajectory-exact; path's targets/VNS vector and *rng are updated */
+vnsgpu_status vnsgpu_local_search(vnsgpu_ctx *ctx, int path, int kind, int num_changes, double budget, int skip,
+                                  vnsgpu_rng *rng, vnsgpu_ls_stats *stats);
+/* pathInsert (kind 1, :931-999) / pathExchange (kind 2, :1001-1089) incl. fitDOPtoBudget */
+vnsgpu_status vnsgpu_shake(vnsgpu_ctx *ctx, int path, int kind, double budget, vnsgpu_rng *rng);
+/* fitDOPtoBudget (:364-385) */
+vnsgpu_status vnsgpu_fit_to_budget(vnsgpu_ctx *ctx, int path, double budget);
+/* greedy_insertion (:1091-1155) */
+vnsgpu_status vnsgpu_greedy(vnsgpu_ctx *ctx, int path, double budget);
+/* VnsSopSolver::iterate (:82-260) as ONE persistent device chain; `path` enters as any state with the
+ * VNS vector set (normally T = 0) and leaves as the best tour.  impr_* receive the improvement log
+ * (reward, length, ms) up to params->max_improvements entries; may be NULL */
+vnsgpu_status vnsgpu_vns_run(vnsgpu_ctx *ctx, int path, const vnsgpu_vns_params *params,
+                             vnsgpu_vns_result *result, double *impr_reward, double *impr_length,
+                             double *impr_time_ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VNSGPU_H */

@@ -1,0 +1,251 @@
+"""GPU parity (run on the B200 box): every row of SURVEY.md 8a through the C ABI (ctypes ->
+libvnsgpu.so -> CUDA kernels) against (1) golden vectors produced by the reference's own code and
+(2) the CPU oracle on the same seeded inputs.  Integer tables: bit-exact.  Real-valued tables:
+bit-exact as well (same association, no FMA), asserted with == ; Dubins lengths: 1e-9 relative
+(device libm differs from glibc)."""
+import numpy as np
+import pytest
+
+from conftest import ALL, SMALL, load_arrays, load_problem, random_candidates
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def eng_cache():
+    from vns_sop_b200 import engine
+    cache = {}
+
+    def get(name):
+        if name not in cache:
+            sf, pb = load_problem(name)
+            cache[name] = (engine.Engine(0).load_problem(pb), sf, pb)
+        return cache[name]
+    yield get
+    for e, _, _ in cache.values():
+        e.close()
+
+
+def layer_cluster(pb, vns, T, l):
+    return pb.start if l == 0 else (pb.goal if l == T + 1 else vns[l - 1])
+
+
+@pytest.mark.parametrize("name", ALL)
+def test_table_and_bounds(name, golden, eng_cache):
+    e, sf, pb = eng_cache(name)
+    g, a = golden[name], load_arrays(name)
+    W = e.table_dense()
+    if "dense" in a:
+        assert (W == a["dense"]).all()
+    else:
+        assert float(W.sum()) == g["dense_sum"]
+        wsum = (W * (np.arange(pb.N)[:, None] % 7 + 1) * (np.arange(pb.N)[None, :] % 5 + 1)).sum()
+        assert float(wsum) == g["dense_wsum"]
+    lo, hi = e.bounds()
+    assert (lo == a["dmin"]).all() and (hi == a["dmax"]).all()
+
+
+@pytest.mark.parametrize("name", ALL)
+def test_update_and_queries_on_greedy_path(name, golden, eng_cache):
+    e, sf, pb = eng_cache(name)
+    g, a = golden[name], load_arrays(name)
+    T = g["greedy"]["T"]
+    p = e.path(a["greedy_vns"], T)
+    assert p.getNumTargets() == T and (p.getAllTargets() == a["greedy_vns"][:T]).all()
+    assert p.getPathLength() == g["greedy"]["length"] and p.getPathLengthRear() == g["greedy"]["length_rear"]
+    assert p.getReward() == g["greedy"]["reward"]
+    F, B = p.layers()
+    for l in range(T + 2):
+        k = pb.m[layer_cluster(pb, a["greedy_vns"], T, l)]
+        assert (F[l, :k] == a["greedy_F"][l, :k]).all(), l
+        assert (B[l, :k] == a["greedy_B"][l, :k]).all(), l
+    cl, nd, calc = p.getPath()
+    assert (cl == a["greedy_path_cluster"]).all() and (nd == a["greedy_path_node"]).all()
+    assert calc == g["greedy"]["length_calc"]
+    ln, lb, fl, first = p.eval_batch(a["cands"])
+    assert (ln == a["cand_len"]).all()
+    assert (lb == a["cand_lb"]).all()
+    # flags restated from the reference's predicates (vns_sop_solver.cpp:539,619,784,805)
+    L, budget = g["greedy"]["length"], pb.budget
+    c = a["cands"]
+    dR = np.zeros(len(c))
+    dR[c[:, 0] == 0] = pb.reward[c[c[:, 0] == 0, 1]]
+    rep = c[:, 0] == 1
+    dR[rep] = pb.reward[c[rep, 1]] - pb.reward[a["greedy_vns"][c[rep, 2]]]
+    feas = ln <= budget
+    acc = feas & ((dR > 0) | ((L - ln) > 1e-5))
+    skip = (lb > budget) & (c[:, 0] != 2)
+    assert ((fl & 1) != 0).tolist() == feas.tolist()
+    assert ((fl & 2) != 0).tolist() == acc.tolist()
+    assert ((fl & 4) != 0).tolist() == skip.tolist()
+    ok = np.nonzero(acc & ~skip)[0]
+    assert first == (int(ok[0]) if len(ok) else -1)
+    # single-call mirrors of the reference methods
+    k = int(np.nonzero(c[:, 0] == 3)[0][0])
+    assert p.tryToMove(c[k, 1], c[k, 2]) == a["cand_len"][k]
+    assert p.tryToMoveLowerBound(c[k, 1], c[k, 2]) == a["cand_lb"][k]
+
+
+@pytest.mark.parametrize("name", SMALL)
+def test_add_remove_point_incremental(name, golden, eng_cache):
+    from oracle import binding as ob
+    e, sf, pb = eng_cache(name)
+    a = load_arrays(name)
+    o = ob.Oracle(pb)
+    po, pg = o.path(), e.path()
+    rs = np.random.RandomState(3)
+    inside = []
+    outside = list(a["initial_vns"])
+    for step in range(40):
+        if inside and (rs.rand() < 0.35 or not outside):
+            idx = int(rs.randint(0, len(inside)))
+            outside.append(inside.pop(idx))
+            po.remove_point(idx)
+            pg.removePoint(idx)
+        else:
+            c = outside.pop(int(rs.randint(0, len(outside))))
+            idx = int(rs.randint(0, len(inside) + 1))
+            inside.insert(idx, c)
+            po.add_point(c, idx)
+            pg.addPoint(c, idx)
+        assert pg.getNumTargets() == po.T and (pg.getAllTargets() == po.targets).all()
+        assert pg.getPathLength() == po.length() and pg.getPathLengthRear() == po.length_rear()
+        Fo, Bo, _, _ = po.layers()
+        F, B = pg.layers()
+        for l in range(po.T + 2):
+            k = pb.m[layer_cluster(pb, inside, po.T, l)]
+            assert (F[l, :k] == Fo[l, :k]).all() and (B[l, :k] == Bo[l, :k]).all()
+
+
+@pytest.mark.parametrize("name", ALL)
+def test_greedy_insertion(name, golden, eng_cache):
+    e, sf, pb = eng_cache(name)
+    g, a = golden[name], load_arrays(name)
+    p = e.path()
+    p.greedy_insertion()
+    assert p.getNumTargets() == g["greedy"]["T"] and (p.vns == a["greedy_vns"]).all()
+    assert p.getPathLength() == g["greedy"]["length"] and p.getReward() == g["greedy"]["reward"]
+
+
+@pytest.mark.parametrize("name", ALL)
+def test_shake_and_local_search_sequence(name, golden, eng_cache):
+    """pathInsert/pathExchange + insertRandom/exchangeRandom with seed 7: the device chain must
+    walk the reference's exact state sequence and leave the RNG at the same position."""
+    from vns_sop_b200 import engine
+    e, sf, pb = eng_cache(name)
+    g, a = golden[name], load_arrays(name)
+    p = e.path(a["greedy_vns"], g["greedy"]["T"])
+    rng = engine.seeded_rng(7)
+    for i, st in enumerate(g["sequence"]):
+        if st["op"] == "shake":
+            p.shake(st["k"], rng)
+        else:
+            iters = len(p.vns) ** 2 if g["sequence_ls_iters"] == "nvns^2" else g["sequence_ls_iters"]
+            stats = p._ls(st["k"], iters, rng, None, 1)
+            assert stats.proposals == iters
+        assert p.getNumTargets() == st["T"], (i, st)
+        assert p.getPathLength() == st["length"] and p.getReward() == st["reward"], (i, st)
+        assert (p.vns == a["sequence_vns"][i]).all(), (i, st)
+        assert (p.getAllTargets() == a["sequence_vns"][i][:st["T"]]).all()
+    assert engine.rng_next(rng) == g["rand_after_sequence"]
+
+
+@pytest.mark.parametrize("name", ["berlin52", "opn_s08", "dop_s12", "krob200"])
+def test_full_vns_run_seed1_follows_reference_trajectory(name, golden, eng_cache):
+    e, sf, pb = eng_cache(name)
+    s = golden[name]["solve_seed1"]
+    p = e.path()
+    res, impr = p.vns_run(1)
+    assert res.status == 0
+    assert res.num_iters == s["NUM_ITERS"] and res.num_iters_last_impr == s["NUM_ITERS_LAST_IMPR"]
+    assert res.reward == s["REWARDS"] and res.length == s["LENGTH"]
+    assert [[r, l] for r, l, _ in impr] == s["IMPROVEMENTS"]
+    cl, nd, calc = p.getPath()
+    assert list(pb.node_id[pb.off[cl] + nd]) == s["RESULT_TARGET_IDS"]
+    assert list(pb.orig_cluster_id[cl]) == s["RESULT_CLUSTER_IDS"]
+    assert calc <= pb.budget
+
+
+@pytest.mark.parametrize("S", [4, 8, 12])
+def test_dubins_table_known_answers(S):
+    """a4: the Dubins kernel against the 98 784 entries shipped with the reference's DOP datasets
+    and against the CPU oracle's lengths."""
+    from oracle import binding as ob
+    from vns_sop_b200 import engine
+    sf, pb = load_problem("dop_s%02d" % S)
+    e = engine.Engine(0).load_problem(pb, dubins=(S, sf.dubins_radius, 0))
+    L = e.table_dense()
+    W = pb.W
+    ok = (np.ceil(L) == W) | (np.ceil(L - 1e-9) == W) | (np.ceil(L + 1e-9) == W)
+    assert ok.all()
+    Lo = ob.Oracle(pb, dubins=(S, sf.dubins_radius, 0)).dense()
+    assert np.allclose(L, Lo, rtol=1e-9, atol=1e-9)
+    e2 = engine.Engine(0).load_problem(pb, dubins=(S, sf.dubins_radius, 1))
+    Lc = e2.table_dense()
+    assert (Lc == np.ceil(L)).all()
+    near = np.abs(L - np.round(L)) < 1e-9
+    assert (Lc[~near] == W[~near]).all()
+    e.close()
+    e2.close()
+
+
+@pytest.mark.parametrize("rule", [0, 1])
+def test_real_valued_and_rounded_tables_vs_oracle(rule):
+    """a3 (raw Euclid, real-valued distances: exercises the floating-point association of
+    SURVEY.md App. A.4) and EUC_2D rounding; whole driver sequences against the CPU oracle."""
+    import dataclasses
+    from oracle import binding as ob
+    from vns_sop_b200 import engine
+    sf, pb = load_problem("krob200")
+    rs = np.random.RandomState(11)
+    pb = dataclasses.replace(pb, rule=rule, xy=pb.xy + rs.rand(*pb.xy.shape))
+    e = engine.Engine(0).load_problem(pb)
+    o = ob.Oracle(pb)
+    assert (e.table_dense() == o.dense()).all()
+    lo, hi = e.bounds()
+    olo, ohi = o.bounds()
+    assert (lo == olo).all() and (hi == ohi).all()
+    po, pg = o.path(), e.path()
+    po.greedy()
+    pg.greedy_insertion()
+    assert (pg.vns == po.vns).all() and pg.getPathLength() == po.length()
+    go, gg = ob.new_rng(5), engine.seeded_rng(5)
+    for it in range(6):
+        k = 1 + it % 2
+        po.shake(k, go)
+        pg.shake(k, gg)
+        assert (pg.vns == po.vns).all() and pg.getNumTargets() == po.T and pg.getPathLength() == po.length()
+        if po.T >= 3:
+            cands = random_candidates(rs, po.vns, po.T, 300)
+            ln, lb, fl, _ = pg.eval_batch(cands)
+            oln, olb = po.eval_batch(cands)
+            assert (ln == oln).all() and (lb == olb).all()
+        po.local_search(k, 1600, go)
+        pg._ls(k, 1600, gg, None, 1)
+        assert (pg.vns == po.vns).all() and pg.getNumTargets() == po.T
+        assert pg.getPathLength() == po.length() and pg.getReward() == po.reward()
+    assert engine.rng_next(gg) == ob.rng_next(go)
+    e.close()
+
+
+def test_edge_cases(eng_cache):
+    from vns_sop_b200 import engine
+    e, sf, pb = eng_cache("berlin52")
+    p = e.path()                                   # empty path: start -> goal
+    assert p.getNumTargets() == 0 and p.getPathLength() == 0.0   # start and goal are the same set
+    ln, lb, fl, first = p.eval_batch(np.zeros((0, 3), np.int32))
+    assert len(ln) == 0 and first == -1
+    bad = np.array([[3, 0, 1], [4, 0, 0], [0, 999, 0], [2, 5, 0], [1, 3, 0], [7, 0, 0]], np.int32)
+    ln, lb, fl, first = p.eval_batch(bad)
+    assert (fl == engine.F_BAD).all() and np.isnan(ln).all() and first == -1
+    with pytest.raises(engine.VnsGpuError):
+        p.removePoint(0)                           # reference: exit(1) (vns_sop_path.cpp:158-161)
+    with pytest.raises(engine.VnsGpuError):
+        p.addPoint(3, 2)                           # vns_sop_path.cpp:69-72
+    with pytest.raises(engine.VnsGpuError):
+        p.tryToMove(0, 1)
+    # local search on states where the reference's guards skip the loop (:498, :711)
+    rng = engine.seeded_rng(1)
+    before = engine.rng_next(engine.Rng.from_buffer_copy(rng))
+    st = p.exchangeRandom(100, rng)                # T == 0 -> no proposals, RNG untouched
+    assert st.proposals == 0 and engine.rng_next(rng) == before

@@ -1,0 +1,131 @@
+// C ABI: RNG replay + neighbourhood drivers (included by vnsgpu.cu)
+
+extern "C" {
+
+void vnsgpu_rng_seed(vnsgpu_rng *rng, uint32_t seed) { rng_seed_host(*reinterpret_cast<RngState *>(rng), seed); }
+int32_t vnsgpu_rng_next(vnsgpu_rng *rng) { return rng_next(*reinterpret_cast<RngState *>(rng)); }
+
+vnsgpu_status vnsgpu_gen_proposals(vnsgpu_ctx *ctx, int path, int kind, int64_t n, vnsgpu_rng *rng, vnsgpu_cand *cands)
+{
+   CK(cudaSetDevice(ctx->device));
+   if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
+   if (kind != 1 && kind != 2) return fail(ctx, VNSGPU_E_RANGE, "kind must be 1 (insert) or 2 (exchange)");
+   PathHdr h;
+   vnsgpu_status s = read_hdr(ctx, path, &h);
+   if (s) return s;
+   const int T = h.hdr[HDR_T], nvns = h.hdr[HDR_NVNS];
+   if (kind == 1 ? nvns < 3 : (nvns < 4 || T < 3)) return fail(ctx, VNSGPU_E_STATE, "neighbourhood is empty for this state");
+   std::vector<int> vns(nvns);
+   CK(cudaMemcpyAsync(vns.data(), ctx->paths[path].d.vns, sizeof(int) * nvns, cudaMemcpyDeviceToHost, ctx->stream));
+   CK(cudaStreamSynchronize(ctx->stream));
+   RngState &g = *reinterpret_cast<RngState *>(rng);
+   const int gap = kind == 1 ? 1 : 2, tohi = kind == 1 ? T : T - 1;
+   for (int64_t k = 0; k < n; ++k) {
+      int from = rng_int(g, 0, nvns - 1), to = rng_int(g, 0, tohi);        // vns_sop_solver.cpp:507-508 / 723-724
+      while (std::abs(from - to) <= gap) {                                 // :510-519 / :726-730
+         from = rng_int(g, 0, nvns - 1);
+         to = rng_int(g, 0, tohi);
+      }
+      vnsgpu_cand &c = cands[k];
+      if (from < T) { c.op = kind == 1 ? VNSGPU_OP_MOVE : VNSGPU_OP_EXCHANGE; c.a = from; c.b = to; c.gain_cluster = -1; }
+      else { c.op = kind == 1 ? VNSGPU_OP_ADD : VNSGPU_OP_REPLACE; c.a = vns[from]; c.b = to; c.gain_cluster = vns[from]; }
+   }
+   return VNSGPU_OK;
+}
+
+vnsgpu_status vnsgpu_local_search(vnsgpu_ctx *ctx, int path, int kind, int num_changes, double budget, int skip, vnsgpu_rng *rng,
+                                  vnsgpu_ls_stats *stats)
+{
+   CK(cudaSetDevice(ctx->device));
+   if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
+   if (kind != 1 && kind != 2) return fail(ctx, VNSGPU_E_RANGE, "kind must be 1 (insert) or 2 (exchange)");
+   CK(cudaMemcpyAsync(ctx->d_rng, rng, sizeof(RngState), cudaMemcpyHostToDevice, ctx->stream));
+   k_local_search<<<1, VNS_CHAIN_THREADS, chain_smem(ctx), ctx->stream>>>(ctx->I, ctx->paths[path].d, kind, num_changes, budget, skip,
+                                                                          ctx->d_rng, ctx->d_stats);
+   LAUNCHED(ctx);
+   LsStats st;
+   CK(cudaMemcpyAsync(rng, ctx->d_rng, sizeof(RngState), cudaMemcpyDeviceToHost, ctx->stream));
+   CK(cudaMemcpyAsync(&st, ctx->d_stats, sizeof(st), cudaMemcpyDeviceToHost, ctx->stream));
+   vnsgpu_status s = check_path_err(ctx, path);
+   if (stats) {
+      stats->proposals = st.proposals; stats->lb_skips = st.lb_skips; stats->evals = st.evals;
+      stats->accepts = st.accepts; stats->rounds = st.rounds;
+   }
+   return s;
+}
+
+vnsgpu_status vnsgpu_shake(vnsgpu_ctx *ctx, int path, int kind, double budget, vnsgpu_rng *rng)
+{
+   CK(cudaSetDevice(ctx->device));
+   if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
+   if (kind != 1 && kind != 2) return fail(ctx, VNSGPU_E_RANGE, "kind must be 1 (pathInsert) or 2 (pathExchange)");
+   CK(cudaMemcpyAsync(ctx->d_rng, rng, sizeof(RngState), cudaMemcpyHostToDevice, ctx->stream));
+   k_shake<<<1, VNS_CHAIN_THREADS, chain_smem(ctx), ctx->stream>>>(ctx->I, ctx->paths[path].d, kind, budget, ctx->d_rng, ctx->d_seg);
+   LAUNCHED(ctx);
+   CK(cudaMemcpyAsync(rng, ctx->d_rng, sizeof(RngState), cudaMemcpyDeviceToHost, ctx->stream));
+   return check_path_err(ctx, path);
+}
+
+vnsgpu_status vnsgpu_fit_to_budget(vnsgpu_ctx *ctx, int path, double budget)
+{
+   CK(cudaSetDevice(ctx->device));
+   if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
+   k_fit<<<1, VNS_CHAIN_THREADS, chain_smem(ctx), ctx->stream>>>(ctx->I, ctx->paths[path].d, budget);
+   LAUNCHED(ctx);
+   return check_path_err(ctx, path);
+}
+
+vnsgpu_status vnsgpu_greedy(vnsgpu_ctx *ctx, int path, double budget)
+{
+   CK(cudaSetDevice(ctx->device));
+   if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
+   k_greedy<<<1, VNS_CHAIN_THREADS, chain_smem(ctx), ctx->stream>>>(ctx->I, ctx->paths[path].d, budget);
+   LAUNCHED(ctx);
+   return check_path_err(ctx, path);
+}
+
+vnsgpu_status vnsgpu_vns_run(vnsgpu_ctx *ctx, int path, const vnsgpu_vns_params *p, vnsgpu_vns_result *result, double *impr_reward,
+                             double *impr_length, double *impr_time_ms)
+{
+   CK(cudaSetDevice(ctx->device));
+   if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
+   int work = -1;
+   vnsgpu_status s = vnsgpu_path_create(ctx, &work);   // actualVNSGOPPath (vns_sop_solver.cpp:195)
+   if (s) return s;
+   const int cap = std::max(1, p->max_improvements);
+   s = need_scratch(ctx, sizeof(double) * 3 * cap);
+   if (s) return s;
+   double *d_ir = (double *)ctx->d_scratch, *d_il = d_ir + cap, *d_it = d_il + cap;
+   RngState g;
+   rng_seed_host(g, p->seed);
+   CK(cudaMemcpyAsync(ctx->d_rng, &g, sizeof(g), cudaMemcpyHostToDevice, ctx->stream));
+   VnsParamsDev prm;
+   prm.num_iterations = p->num_iterations; prm.num_iterations_unimproved = p->num_iterations_unimproved;
+   prm.skip = p->lower_bound_skip; prm.greedy = p->greedy_initial; prm.budget = p->budget;
+   prm.max_time_ms = p->max_time_ms; prm.max_improvements = cap;
+   k_vns_run<<<1, VNS_CHAIN_THREADS, chain_smem(ctx), ctx->stream>>>(ctx->I, ctx->paths[path].d, ctx->paths[work].d, prm, ctx->d_rng,
+                                                                     ctx->d_res, d_ir, d_il, d_it, ctx->d_seg);
+   LAUNCHED(ctx);
+   VnsResultDev r;
+   CK(cudaMemcpyAsync(&r, ctx->d_res, sizeof(r), cudaMemcpyDeviceToHost, ctx->stream));
+   CK(cudaStreamSynchronize(ctx->stream));
+   const int n = std::min(r.n_improvements, cap);
+   if (impr_reward) CK(cudaMemcpy(impr_reward, d_ir, sizeof(double) * n, cudaMemcpyDeviceToHost));
+   if (impr_length) CK(cudaMemcpy(impr_length, d_il, sizeof(double) * n, cudaMemcpyDeviceToHost));
+   if (impr_time_ms) CK(cudaMemcpy(impr_time_ms, d_it, sizeof(double) * n, cudaMemcpyDeviceToHost));
+   if (result) {
+      result->num_iters = r.num_iters; result->num_iters_last_impr = r.num_iters_last_impr;
+      result->n_improvements = r.n_improvements; result->status = r.status;
+      result->reward = r.reward; result->length = r.length; result->time_ms = r.time_ms;
+      result->time_last_impr_ms = r.time_last_impr_ms;
+      result->proposals = r.proposals; result->evals = r.evals; result->accepts = r.accepts;
+   }
+   // release the work path (it is the last handle)
+   cudaFree(ctx->paths[work].block);
+   ctx->paths.pop_back();
+   if (r.status == 4) return fail(ctx, VNSGPU_E_INCONSISTENT, "inconsistent path length in improved tour");
+   if (r.status) return fail(ctx, VNSGPU_E_STATE, "device-side error flag in vns_run");
+   return VNSGPU_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,155 @@
+// __global__ entry points over the device functions of path.cuh / search.cuh.
+#pragma once
+#include <climits>
+
+#include "common.cuh"
+#include "path.cuh"
+#include "search.cuh"
+
+// ---- path maintenance (single CTA per path) -------------------------------------------------------
+// VnsSopPath::update vns_sop_path.cpp:1321-1404
+__global__ void __launch_bounds__(64) k_path_update(InstDev I, PathDev P)
+{
+   cta_update(I, P, P.hdr[HDR_T]);
+}
+
+// addPoint(c, idx) (kind 0) / removePoint(idx) (kind 1) with the incremental re-scan ranges of
+// updateAfterInsert / updateAfterRemove (vns_sop_path.cpp:1406-1540).  Targets only.
+__global__ void __launch_bounds__(256) k_path_edit(InstDev I, PathDev P, int kind, int c, int idx)
+{
+   int T = P.hdr[HDR_T];
+   __syncthreads();
+   if (kind == 0) {
+      cta_shift(P.tg, idx, T - idx, +1);
+      cta_shift_B(I, P, idx + 1, T + 2 - (idx + 1), +1);
+      if (threadIdx.x == 0) P.tg[idx] = c;
+      T += 1;
+      cta_rescan(I, P, T, idx + 1, idx + 1);          // :1426, :1453
+   } else {
+      cta_shift(P.tg, idx + 1, T - idx - 1, -1);
+      cta_shift_B(I, P, idx + 2, T + 2 - (idx + 2), -1);
+      T -= 1;
+      cta_rescan(I, P, T, idx + 1, idx);              // :1488, :1515
+   }
+   if (threadIdx.x == 0) P.hd[HD_REWARD] = path_reward(I, P.tg, T);
+}
+
+__global__ void __launch_bounds__(256) k_path_copy(InstDev I, PathDev dst, PathDev src)
+{
+   cta_copy_path(I, dst, src);
+}
+
+// getPath + getPathLengthCalculate (vns_sop_path.cpp:1542-1599, 1700-1741)
+__global__ void k_path_solution(InstDev I, PathDev P, int *cluster, int *node, double *calc)
+{
+   if (threadIdx.x == 0 && blockIdx.x == 0) *calc = path_walk_back(I, P, P.hdr[HDR_T], cluster, node);
+}
+
+// ---- batched candidate evaluation (a8-a13): one warp per candidate, grid-stride ---------------------
+// len = tryTo*(...), lb = tryTo*LowerBound(...), flags = feasibility / accept predicate / LB skip;
+// d_first receives the smallest accepted (and not LB-skipped when skip != 0) candidate index.
+#define VNS_EVAL_THREADS 256
+__global__ void __launch_bounds__(VNS_EVAL_THREADS) k_eval_batch(InstDev I, PathDev P, long long n, const vnsgpu_cand *__restrict__ cands,
+                                                                 double budget, int skipflag, double *__restrict__ len,
+                                                                 double *__restrict__ lb, uint8_t *__restrict__ flags, long long *d_first)
+{
+   extern __shared__ double smem_v[];
+   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+   double *vbuf = smem_v + (size_t)warp * 2 * I.mp;
+   const int T = P.hdr[HDR_T];
+   const double L = P.hd[HD_LEN];
+   const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+   long long best = LLONG_MAX;
+   for (long long k = (((long long)blockIdx.x * blockDim.x) >> 5) + warp; k < n; k += nwarps) {
+      const int4 cd = __ldg(reinterpret_cast<const int4 *>(cands) + k);   // op, a, b, gain_cluster
+      const CandPlan pl = make_plan(T, cd.x, cd.y, cd.z, I.C);
+      double l, bound;
+      unsigned f = 0;
+      if (pl.bad) {
+         l = CUDART_NAN; bound = CUDART_NAN; f = VNSGPU_F_BAD;
+      } else {
+         l = warp_eval(I, P, T, pl, vbuf, lane);
+         bound = pl.kind == 2 ? l : plan_lower_bound(I, P, T, pl);
+         double dR = 0.0, lm = l;                               // lm = lengthAfterMove of the drivers
+         if (cd.x == 0) {                                        // insertRandom, outside -> path
+            dR = cd.w >= 0 ? __ldg(I.reward + cd.w) : 0.0;       // vns_sop_solver.cpp:581
+            lm = (L - 0.0) + (l - L);                            // :580,:583 (lengthRemoved = L - L)
+         } else if (cd.x == 1) {                                 // exchangeRandom, outside replaces b
+            const int ct = P.tg[cd.z];
+            dR = cd.w >= 0 ? 0.0 + (__ldg(I.reward + cd.w) - __ldg(I.reward + ct)) : 0.0;  // :784
+         }
+         if (lm <= budget) f |= VNSGPU_F_FEASIBLE;
+         if (lm <= budget && (dR > 0 || (L - lm) > VNS_MIN_CHANGE_EPS)) f |= VNSGPU_F_ACCEPT; // :619,:805
+         if (bound > budget && pl.kind != 2) f |= VNSGPU_F_LB_SKIP;                          // :539,...
+      }
+      if (lane == 0) {
+         if (len) len[k] = l;
+         if (lb) lb[k] = bound;
+         if (flags) flags[k] = (uint8_t)f;
+         if ((f & VNSGPU_F_ACCEPT) && !(skipflag && (f & VNSGPU_F_LB_SKIP)) && k < best) best = k;
+      }
+   }
+   if (d_first && lane == 0 && best != LLONG_MAX) atomicMin(d_first, best);
+}
+
+__global__ void __launch_bounds__(256) k_cand_bytes(InstDev I, PathDev P, long long n, const vnsgpu_cand *__restrict__ cands,
+                                                    unsigned long long *total)
+{
+   const int T = P.hdr[HDR_T];
+   long long acc = 0;
+   for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (long long)gridDim.x * blockDim.x) {
+      const int4 cd = __ldg(reinterpret_cast<const int4 *>(cands) + k);
+      const CandPlan pl = make_plan(T, cd.x, cd.y, cd.z, I.C);
+      if (!pl.bad) acc += plan_bytes(I, P, T, pl);
+   }
+   for (int s = 16; s > 0; s >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s);
+   if ((threadIdx.x & 31) == 0) atomicAdd(total, (unsigned long long)acc);
+}
+
+// ---- chain kernels: exactly one CTA of VNS_CHAIN_THREADS; dynamic smem = 2*mp*warps doubles -----------
+__global__ void __launch_bounds__(VNS_CHAIN_THREADS) k_local_search(InstDev I, PathDev P, int kind, int num_changes, double budget,
+                                                                    int skipflag, RngState *rng, LsStats *stats)
+{
+   extern __shared__ double smem_v[];
+   __shared__ LsShared sh;
+   if (threadIdx.x == 0) { sh.rng = *rng; sh.err = 0; sh.st = LsStats{0, 0, 0, 0, 0}; }
+   __syncthreads();
+   cta_local_search(I, P, kind, num_changes, budget, skipflag, sh, smem_v);
+   if (threadIdx.x == 0) { *rng = sh.rng; *stats = sh.st; }
+}
+
+__global__ void __launch_bounds__(VNS_CHAIN_THREADS) k_shake(InstDev I, PathDev P, int kind, double budget, RngState *rng, int *seg)
+{
+   extern __shared__ double smem_v[];
+   __shared__ RngState g;
+   if (threadIdx.x == 0) g = *rng;
+   __syncthreads();
+   cta_shake(I, P, kind, budget, g, seg, smem_v);
+   if (threadIdx.x == 0) *rng = g;
+}
+
+__global__ void __launch_bounds__(VNS_CHAIN_THREADS) k_fit(InstDev I, PathDev P, double budget)
+{
+   extern __shared__ double smem_v[];
+   int T = P.hdr[HDR_T];
+   cta_fit(I, P, T, budget, smem_v);
+   if (threadIdx.x == 0) P.hd[HD_REWARD] = path_reward(I, P.tg, T);
+}
+
+__global__ void __launch_bounds__(VNS_CHAIN_THREADS) k_greedy(InstDev I, PathDev P, double budget)
+{
+   extern __shared__ double smem_v[];
+   cta_greedy(I, P, budget, smem_v);
+}
+
+__global__ void __launch_bounds__(VNS_CHAIN_THREADS) k_vns_run(InstDev I, PathDev tour, PathDev act, VnsParamsDev prm, RngState *rng,
+                                                               VnsResultDev *res, double *impr_reward, double *impr_length,
+                                                               double *impr_ms, int *seg)
+{
+   extern __shared__ double smem_v[];
+   __shared__ LsShared sh;
+   if (threadIdx.x == 0) { sh.rng = *rng; sh.err = 0; sh.st = LsStats{0, 0, 0, 0, 0}; }
+   __syncthreads();
+   cta_vns_run(I, tour, act, prm, res, impr_reward, impr_length, impr_ms, sh, seg, smem_v);
+   if (threadIdx.x == 0) *rng = sh.rng;
+}

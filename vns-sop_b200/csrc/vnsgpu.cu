@@ -1,0 +1,286 @@
+// libvnsgpu.so: C ABI (include/vnsgpu.h) over the sm_100a kernels.  No CPU fallback exists: every
+// entry point either runs its CUDA kernels or returns an error.
+#include <math_constants.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/vnsgpu.h"
+#include "common.cuh"
+#include "table.cuh"
+#include "path.cuh"
+#include "search.cuh"
+#include "kernels.cuh"
+
+static_assert(sizeof(vnsgpu_rng) == sizeof(RngState), "rng layout");
+static_assert(sizeof(vnsgpu_cand) == 16, "cand layout");
+
+struct PathHost {
+   void *block = nullptr;
+   PathDev d{};
+};
+
+struct vnsgpu_ctx {
+   int device = 0;
+   cudaStream_t own = nullptr, stream = nullptr;
+   InstDev I{};
+   bool have_clusters = false, have_table = false;
+   std::vector<int> m, off;
+   std::vector<double> reward;
+   int *d_m = nullptr, *d_off = nullptr, *d_clof = nullptr;
+   double *d_reward = nullptr, *d_D = nullptr, *d_dmin = nullptr, *d_dmax = nullptr;
+   unsigned long long *d_info = nullptr;
+   std::vector<PathHost> paths;
+   // scratch
+   void *d_scratch = nullptr;
+   size_t scratch_bytes = 0;
+   int *d_seg = nullptr;
+   RngState *d_rng = nullptr;
+   LsStats *d_stats = nullptr;
+   long long *d_first = nullptr;
+   VnsResultDev *d_res = nullptr;
+   std::string err;
+   int64_t launches = 0;
+   int num_sms = 148;
+};
+
+#define CK(call)                                                                                   \
+   do {                                                                                            \
+      cudaError_t e__ = (call);                                                                    \
+      if (e__ != cudaSuccess) {                                                                    \
+         ctx->err = std::string(#call) + ": " + cudaGetErrorString(e__);                           \
+         return VNSGPU_E_CUDA;                                                                     \
+      }                                                                                            \
+   } while (0)
+
+#define LAUNCHED(ctx)                                                                              \
+   do {                                                                                            \
+      (ctx)->launches++;                                                                           \
+      cudaError_t e__ = cudaGetLastError();                                                        \
+      if (e__ != cudaSuccess) {                                                                    \
+         (ctx)->err = std::string("kernel launch: ") + cudaGetErrorString(e__);                   \
+         return VNSGPU_E_CUDA;                                                                     \
+      }                                                                                            \
+   } while (0)
+
+static vnsgpu_status fail(vnsgpu_ctx *ctx, vnsgpu_status s, const char *msg)
+{
+   ctx->err = msg;
+   return s;
+}
+
+static vnsgpu_status need_scratch(vnsgpu_ctx *ctx, size_t bytes)
+{
+   if (bytes <= ctx->scratch_bytes) return VNSGPU_OK;
+   if (ctx->d_scratch) CK(cudaFree(ctx->d_scratch));
+   ctx->d_scratch = nullptr;
+   ctx->scratch_bytes = 0;
+   CK(cudaMalloc(&ctx->d_scratch, bytes));
+   ctx->scratch_bytes = bytes;
+   return VNSGPU_OK;
+}
+
+extern "C" {
+
+const char *vnsgpu_version(void) { return "vnsgpu 0.1 (sm_100a)"; }
+
+vnsgpu_status vnsgpu_create(vnsgpu_ctx **out, int device)
+{
+   *out = nullptr;
+   int n = 0;
+   if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0 || device >= n) return VNSGPU_E_CUDA;
+   vnsgpu_ctx *ctx = new vnsgpu_ctx();
+   ctx->device = device;
+   *out = ctx;
+   CK(cudaSetDevice(device));
+   CK(cudaStreamCreateWithFlags(&ctx->own, cudaStreamNonBlocking));
+   ctx->stream = ctx->own;
+   CK(cudaDeviceGetAttribute(&ctx->num_sms, cudaDevAttrMultiProcessorCount, device));
+   CK(cudaMalloc(&ctx->d_rng, sizeof(RngState)));
+   CK(cudaMalloc(&ctx->d_stats, sizeof(LsStats)));
+   CK(cudaMalloc(&ctx->d_first, sizeof(long long)));
+   CK(cudaMalloc(&ctx->d_res, sizeof(VnsResultDev)));
+   CK(cudaMalloc(&ctx->d_info, 2 * sizeof(unsigned long long)));
+   return VNSGPU_OK;
+}
+
+static void free_instance(vnsgpu_ctx *ctx)
+{
+   for (PathHost &p : ctx->paths) cudaFree(p.block);
+   ctx->paths.clear();
+   cudaFree(ctx->d_m); cudaFree(ctx->d_off); cudaFree(ctx->d_clof); cudaFree(ctx->d_reward);
+   cudaFree(ctx->d_D); cudaFree(ctx->d_dmin); cudaFree(ctx->d_dmax); cudaFree(ctx->d_seg);
+   ctx->d_m = ctx->d_off = ctx->d_clof = ctx->d_seg = nullptr;
+   ctx->d_reward = ctx->d_D = ctx->d_dmin = ctx->d_dmax = nullptr;
+   ctx->have_clusters = ctx->have_table = false;
+}
+
+void vnsgpu_destroy(vnsgpu_ctx *ctx)
+{
+   if (!ctx) return;
+   cudaSetDevice(ctx->device);
+   cudaStreamSynchronize(ctx->stream);
+   free_instance(ctx);
+   cudaFree(ctx->d_scratch); cudaFree(ctx->d_rng); cudaFree(ctx->d_stats); cudaFree(ctx->d_first);
+   cudaFree(ctx->d_res); cudaFree(ctx->d_info);
+   if (ctx->own) cudaStreamDestroy(ctx->own);
+   delete ctx;
+}
+
+const char *vnsgpu_last_error(const vnsgpu_ctx *ctx) { return ctx ? ctx->err.c_str() : "no context"; }
+int64_t vnsgpu_launch_count(const vnsgpu_ctx *ctx) { return ctx->launches; }
+int64_t vnsgpu_table_bytes(const vnsgpu_ctx *ctx) { return 8ll * ctx->I.N * ctx->I.N; }
+
+vnsgpu_status vnsgpu_set_stream(vnsgpu_ctx *ctx, void *stream)
+{
+   ctx->stream = stream ? (cudaStream_t)stream : ctx->own;
+   return VNSGPU_OK;
+}
+
+vnsgpu_status vnsgpu_sync(vnsgpu_ctx *ctx)
+{
+   CK(cudaStreamSynchronize(ctx->stream));
+   return VNSGPU_OK;
+}
+
+vnsgpu_status vnsgpu_set_clusters(vnsgpu_ctx *ctx, int C, const int *m, const double *reward, int start, int goal)
+{
+   CK(cudaSetDevice(ctx->device));
+   if (C < 2 || start < 0 || start >= C || goal < 0 || goal >= C) return fail(ctx, VNSGPU_E_RANGE, "bad cluster description");
+   CK(cudaStreamSynchronize(ctx->stream));
+   free_instance(ctx);
+   ctx->m.assign(m, m + C);
+   ctx->reward.assign(reward, reward + C);
+   ctx->off.assign(C + 1, 0);
+   int mp = 0;
+   for (int c = 0; c < C; ++c) {
+      if (m[c] < 1) return fail(ctx, VNSGPU_E_RANGE, "empty cluster");
+      ctx->off[c + 1] = ctx->off[c] + m[c];
+      mp = std::max(mp, m[c]);
+   }
+   const int N = ctx->off[C];
+   if ((long long)mp * N >= (1ll << 31)) return fail(ctx, VNSGPU_E_RANGE, "row band exceeds 2^31 entries");
+   std::vector<int> clof(N);
+   for (int c = 0; c < C; ++c)
+      for (int s = ctx->off[c]; s < ctx->off[c + 1]; ++s) clof[s] = c;
+   CK(cudaMalloc(&ctx->d_m, sizeof(int) * C));
+   CK(cudaMalloc(&ctx->d_off, sizeof(int) * (C + 1)));
+   CK(cudaMalloc(&ctx->d_clof, sizeof(int) * N));
+   CK(cudaMalloc(&ctx->d_reward, sizeof(double) * C));
+   CK(cudaMalloc(&ctx->d_D, sizeof(double) * (size_t)N * N + 64));
+   CK(cudaMalloc(&ctx->d_dmin, sizeof(double) * (size_t)C * C));
+   CK(cudaMalloc(&ctx->d_dmax, sizeof(double) * (size_t)C * C));
+   CK(cudaMemcpyAsync(ctx->d_m, m, sizeof(int) * C, cudaMemcpyHostToDevice, ctx->stream));
+   CK(cudaMemcpyAsync(ctx->d_off, ctx->off.data(), sizeof(int) * (C + 1), cudaMemcpyHostToDevice, ctx->stream));
+   CK(cudaMemcpyAsync(ctx->d_clof, clof.data(), sizeof(int) * N, cudaMemcpyHostToDevice, ctx->stream));
+   CK(cudaMemcpyAsync(ctx->d_reward, reward, sizeof(double) * C, cudaMemcpyHostToDevice, ctx->stream));
+   CK(cudaStreamSynchronize(ctx->stream));
+   InstDev &I = ctx->I;
+   I.C = C; I.N = N; I.mp = mp; I.start = start; I.goal = goal; I.rows = 2 * C + 2; I.exact_int = 0;
+   I.m = ctx->d_m; I.off = ctx->d_off; I.clof = ctx->d_clof; I.reward = ctx->d_reward;
+   I.D = ctx->d_D; I.dmin = ctx->d_dmin;
+   CK(cudaMalloc(&ctx->d_seg, sizeof(int) * 2 * I.rows));
+   ctx->have_clusters = true;
+   return VNSGPU_OK;
+}
+
+static dim3 band_grid(const vnsgpu_ctx *ctx)
+{
+   const long long band = (long long)ctx->I.mp * ctx->I.N;
+   const int gx = (int)std::min<long long>((band + 255) / 256, 4096);
+   return dim3(gx, ctx->I.C);
+}
+
+// bounds + table classification after any table (re)build
+static vnsgpu_status finish_table(vnsgpu_ctx *ctx)
+{
+   CK(cudaMemsetAsync(ctx->d_info, 0, 2 * sizeof(unsigned long long), ctx->stream));
+   const long long npairs = (long long)ctx->I.C * ctx->I.C;
+   const int blocks = (int)((npairs * 32 + 255) / 256);
+   k_bounds<<<blocks, 256, 0, ctx->stream>>>(ctx->I, ctx->d_dmin, ctx->d_dmax, ctx->d_info);
+   LAUNCHED(ctx);
+   unsigned long long info[2];
+   CK(cudaMemcpyAsync(info, ctx->d_info, sizeof(info), cudaMemcpyDeviceToHost, ctx->stream));
+   CK(cudaStreamSynchronize(ctx->stream));
+   double mx;
+   memcpy(&mx, &info[1], sizeof(double));
+   // integers below 2^53 / (layers+1): every partial path sum is exact in double
+   ctx->I.exact_int = (info[0] == 0 && mx * (double)(ctx->I.rows + 1) < 9007199254740992.0) ? 1 : 0;
+   ctx->have_table = true;
+   return VNSGPU_OK;
+}
+
+vnsgpu_status vnsgpu_build_table_euclid(vnsgpu_ctx *ctx, const double *xy, int rule)
+{
+   CK(cudaSetDevice(ctx->device));
+   if (!ctx->have_clusters) return fail(ctx, VNSGPU_E_STATE, "set_clusters first");
+   if (rule < 0 || rule > 2) return fail(ctx, VNSGPU_E_RANGE, "unknown edge weight rule");
+   const size_t bytes = sizeof(double) * 2 * ctx->I.N;
+   vnsgpu_status s = need_scratch(ctx, bytes);
+   if (s) return s;
+   CK(cudaMemcpyAsync(ctx->d_scratch, xy, bytes, cudaMemcpyHostToDevice, ctx->stream));
+   k_table_euclid<<<band_grid(ctx), 256, 0, ctx->stream>>>(ctx->I, (const double2 *)ctx->d_scratch, rule, ctx->d_D);
+   LAUNCHED(ctx);
+   return finish_table(ctx);
+}
+
+vnsgpu_status vnsgpu_build_table_dubins(vnsgpu_ctx *ctx, const double *centers, int S, double rho, int do_ceil)
+{
+   CK(cudaSetDevice(ctx->device));
+   if (!ctx->have_clusters) return fail(ctx, VNSGPU_E_STATE, "set_clusters first");
+   if (S < 1 || !(rho > 0)) return fail(ctx, VNSGPU_E_RANGE, "bad Dubins parameters");
+   const size_t bytes = sizeof(double) * 2 * ctx->I.C;
+   vnsgpu_status s = need_scratch(ctx, bytes);
+   if (s) return s;
+   CK(cudaMemcpyAsync(ctx->d_scratch, centers, bytes, cudaMemcpyHostToDevice, ctx->stream));
+   k_table_dubins<<<band_grid(ctx), 256, 0, ctx->stream>>>(ctx->I, (const double2 *)ctx->d_scratch, S, rho, do_ceil, ctx->d_D);
+   LAUNCHED(ctx);
+   return finish_table(ctx);
+}
+
+vnsgpu_status vnsgpu_set_table_dense(vnsgpu_ctx *ctx, const double *W)
+{
+   CK(cudaSetDevice(ctx->device));
+   if (!ctx->have_clusters) return fail(ctx, VNSGPU_E_STATE, "set_clusters first");
+   const size_t bytes = sizeof(double) * (size_t)ctx->I.N * ctx->I.N;
+   vnsgpu_status s = need_scratch(ctx, bytes);
+   if (s) return s;
+   CK(cudaMemcpyAsync(ctx->d_scratch, W, bytes, cudaMemcpyHostToDevice, ctx->stream));
+   k_table_gather<<<band_grid(ctx), 256, 0, ctx->stream>>>(ctx->I, ctx->d_D, (double *)ctx->d_scratch, 0);
+   LAUNCHED(ctx);
+   return finish_table(ctx);
+}
+
+vnsgpu_status vnsgpu_get_table_dense(vnsgpu_ctx *ctx, double *W)
+{
+   CK(cudaSetDevice(ctx->device));
+   if (!ctx->have_table) return fail(ctx, VNSGPU_E_STATE, "no table");
+   const size_t bytes = sizeof(double) * (size_t)ctx->I.N * ctx->I.N;
+   vnsgpu_status s = need_scratch(ctx, bytes);
+   if (s) return s;
+   k_table_gather<<<band_grid(ctx), 256, 0, ctx->stream>>>(ctx->I, ctx->d_D, (double *)ctx->d_scratch, 1);
+   LAUNCHED(ctx);
+   CK(cudaMemcpyAsync(W, ctx->d_scratch, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+   CK(cudaStreamSynchronize(ctx->stream));
+   return VNSGPU_OK;
+}
+
+vnsgpu_status vnsgpu_get_bounds(vnsgpu_ctx *ctx, double *dmin, double *dmax)
+{
+   CK(cudaSetDevice(ctx->device));
+   if (!ctx->have_table) return fail(ctx, VNSGPU_E_STATE, "no table");
+   const size_t bytes = sizeof(double) * (size_t)ctx->I.C * ctx->I.C;
+   if (dmin) CK(cudaMemcpyAsync(dmin, ctx->d_dmin, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+   if (dmax) CK(cudaMemcpyAsync(dmax, ctx->d_dmax, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+   CK(cudaStreamSynchronize(ctx->stream));
+   return VNSGPU_OK;
+}
+
+} // extern "C"
+
+#include "api_path.inl"
+#include "api_search.inl"
