@@ -1,0 +1,473 @@
+#!/usr/bin/env python
+"""bench.py - candidate move evaluations per second (BASELINE.json `metric`) on B200.
+
+One STEP = one pass of the hot path over one batch: `--batch` candidate moves (MOVE / ADD drawn with
+insertRandom's proposal distribution, EXCHANGE / REPLACE with exchangeRandom's,
+sources/vns_sop_solver.cpp:507-519,723-730) evaluated against one fixed search state by ONE launch
+of the batched layered min-plus kernel (length = tryTo*, lower bound, budget-feasibility / accept
+flags, first accepted index).  Workload = BASELINE.json configs[1]: 40krob200_T80_p2.
+
+  value         evals/s, candidates and results resident in HBM (vnsgpu_eval_batch_dev), CUDA events
+  e2e           evals/s through the host-buffer C-ABI call vnsgpu_eval_batch: pinned host
+                candidates -> device, kernel, lengths + flags -> host, all inside the timed region
+  roofline      algorithmic bytes of the batch / kernel time, against the measured
+                HBM copy bandwidth of MEASURED_PEAKS.json
+  cpu_baseline  the reference's own op::VnsSopPath::tryTo* (oracle/_ref, compiled unmodified) or
+                the C port, on a bounded sample of the same candidates, on this box's host cores
+  --impl reference   the CPU arm alone: all host cores, same candidates, same metric
+
+N > 1 (torchrun): the batch shards by rank - every rank evaluates its own `--batch` candidates
+against its replica of the table (weak scaling, no data-path collective); the time is the max over
+ranks.  No CPU fallback: without libvnsgpu.so or a GPU the own arm raises.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    "krob200": ("40krob200_T80_p2", os.path.join(ROOT, "tests", "golden", "krob200.npz")),
+    "vm1084": ("217vm1084_T100_p1", os.path.join(ROOT, "tests", "golden", "vm1084.npz")),
+    "berlin52": ("11berlin52_T60_p2", os.path.join(ROOT, "tests", "golden", "berlin52.npz")),
+    "opn_s08": ("tsiligirides_problem_2_budget_30_d_50_s_08", os.path.join(ROOT, "tests", "golden", "opn_s08.npz")),
+    "dop_s12": ("tsiligirides_problem_2_budget_30_r_50_s_12", os.path.join(ROOT, "tests", "golden", "dop_s12.npz")),
+}
+STATE_SEED = 7          # the search state is greedy + one seeded VNS step of each neighbourhood
+FALLBACK_HBM_GBS = 6650.0   # /opt/skills/guides/B200_PROFILING.md "FALLBACK"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="krob200", choices=sorted(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=1 << 22, help="candidates per step per GPU")
+    ap.add_argument("--ref-batch", type=int, default=1 << 20, help="candidates per step of the reference arm")
+    ap.add_argument("--cpu-sample", type=int, default=1 << 22, help="candidates of the cpu_baseline leg")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-solve", action="store_true", help="skip the time-to-reward leg")
+    return ap.parse_args()
+
+
+# ---- workload: state + candidates (shared by both arms) ----------------------------------------------
+def draw_proposals(kind, n, vns, T, rs):
+    """n proposals of insertRandom (kind 1) / exchangeRandom (kind 2) against (vns, T):
+    from ~ U[0,|VNS|-1], to ~ U[0,T] resp. U[0,T-1], both redrawn while |from-to| <= 1 resp. 2
+    (vns_sop_solver.cpp:507-519, 723-730) -> (op, a, b) rows."""
+    nv = len(vns)
+    gap, tohi = (1, T) if kind == 1 else (2, T - 1)
+    fr = np.empty(n, np.int64)
+    to = np.empty(n, np.int64)
+    todo = np.arange(n)
+    while len(todo):
+        f = rs.randint(0, nv, len(todo))
+        t = rs.randint(0, tohi + 1, len(todo))
+        fr[todo], to[todo] = f, t
+        todo = todo[np.abs(f - t) <= gap]
+    inside = fr < T
+    op = np.where(inside, 3 if kind == 1 else 4, 0 if kind == 1 else 1)
+    a = np.where(inside, fr, np.asarray(vns)[fr])
+    return np.stack([op, a, to], 1).astype(np.int32)
+
+
+def make_candidates(n, vns, T, seed):
+    rs = np.random.RandomState(seed)
+    h = n // 2
+    c = np.concatenate([draw_proposals(1, h, vns, T, rs), draw_proposals(2, n - h, vns, T, rs)])
+    return c[rs.permutation(n)]
+
+
+def load_workload(name):
+    from vns_sop_b200 import instances as ins
+    sf = ins.load_npz(WORKLOADS[name][1])
+    return sf, ins.build_problem(sf)
+
+
+def state_steps(nvns):
+    return [("shake", 1), ("ls", 1, nvns * nvns), ("shake", 2), ("ls", 2, nvns * nvns)]
+
+
+class CpuEvaluator:
+    """The CPU side: the reference's own code when oracle/_ref was built (kind "reference"), else the
+    C port (kind "port").  TEST/BASELINE infrastructure - never on the product path."""
+
+    def __init__(self, sf, pb):
+        from oracle import binding as ob
+        self.kind = "reference" if ob.RefOracle.available() else "port"
+        if self.kind == "reference":
+            from vns_sop_b200 import instances as ins
+            self.tmp = tempfile.NamedTemporaryFile(suffix=".sop", delete=False)
+            self.tmp.close()
+            ins.write_sop(sf, self.tmp.name)            # /root/reference does not exist on the GPU box
+            self.o = ob.RefOracle(self.tmp.name)
+            self.p = self.o.path()
+            self.p.greedy()
+            self.o.seed(STATE_SEED)
+            for st in state_steps(len(self.p.vns)):
+                if st[0] == "shake":
+                    self.p.shake(st[1])
+                else:
+                    self.p.local_search(st[1], st[2])
+        else:
+            self.o = ob.Oracle(pb)
+            self.p = self.o.path()
+            self.p.greedy()
+            g = ob.new_rng(STATE_SEED)
+            for st in state_steps(len(self.p.vns)):
+                if st[0] == "shake":
+                    self.p.shake(st[1], g)
+                else:
+                    self.p.local_search(st[1], st[2], g)
+        self.vns, self.T = self.p.vns, self.p.T
+
+    def eval(self, cands):
+        return self.p.eval_batch(cands)
+
+
+# ---- reference arm: persistent worker processes, one per host core ---------------------------------------
+_W = {}
+
+
+def _worker_init(workload):
+    sf, pb = load_workload(workload)
+    _W["ev"] = CpuEvaluator(sf, pb)
+
+
+def _worker_eval(cands):
+    ln, lb = _W["ev"].eval(cands)
+    return float(ln.sum())
+
+
+def _worker_state(_):
+    ev = _W["ev"]
+    return ev.kind, ev.vns, ev.T
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import multiprocessing as mp
+    cores = host_cores()
+    name = WORKLOADS[args.workload][0]
+    with mp.get_context("fork").Pool(cores, initializer=_worker_init, initargs=(args.workload,)) as pool:
+        kind, vns, T = pool.map(_worker_state, [0])[0]
+        n = args.ref_batch
+        cands = make_candidates(n, vns, T, 1000)
+        chunks = np.array_split(cands, cores * 4)
+        for _ in range(max(args.warmup, 1)):
+            pool.map(_worker_eval, chunks)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            pool.map(_worker_eval, chunks)
+        dt = time.perf_counter() - t0
+    v = n * args.steps / dt
+    sample = "%d candidates/step (same proposal mix and state as the b200 arm) split over %d processes" % (n, cores)
+    line = {
+        "impl": "reference", "metric": "candidate_move_evals_per_sec", "value": v, "unit": "evals/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": name, "candidates_per_step": n, "state": "greedy + 1 seeded VNS step per neighbourhood",
+                   "outputs": "length + lower bound per candidate"},
+        "cpu_baseline": {"value": v, "unit": "evals/s", "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": v, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---- clocks during the timed region (B200_PROFILING.md "clocks DURING the timed region") ----------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+
+    def __init__(self, index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.perf_counter(), [x.strip() for x in line.split(",")]))
+
+    def window(self, t0, t1):
+        rows = [r for t, r in self.rows if t0 <= t <= t1 + 0.15] or [r for _, r in self.rows[-3:]]
+        sm, mx, reasons = [], 0.0, set()
+        for r in rows:
+            try:
+                sm.append(float(r[0]))
+                mx = max(mx, float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for k, nm in enumerate(self.NAMES):
+                if len(r) > 3 + k and r[3 + k].lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+
+
+def measured_hbm_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except (OSError, KeyError, ValueError):
+        return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+def prepare_gpu_state(eng):
+    from vns_sop_b200 import engine
+    p = eng.path()
+    p.greedy_insertion()
+    rng = engine.seeded_rng(STATE_SEED)
+    for st in state_steps(len(p.vns)):
+        if st[0] == "shake":
+            p.shake(st[1], rng)
+        else:
+            p._ls(st[1], st[2], rng, None, 1)
+    return p
+
+
+def run_b200(args):
+    import ctypes as C
+
+    import torch
+    import torch.distributed as dist
+
+    from vns_sop_b200 import engine
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py (b200 arm) needs a CUDA device; there is no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    sf, pb = load_workload(args.workload)
+    eng = engine.Engine(local).load_problem(pb)
+    lib = eng.lib
+    p = prepare_gpu_state(eng)
+    vns, T = p.vns, p.getNumTargets()
+    n, K, W = args.batch, args.steps, args.warmup
+    rows = make_candidates(n, vns, T, 1000 + rank)          # each rank owns its shard of the candidates
+    cands = p.make_cands(rows)
+    alg_bytes = p.cand_bytes(cands)
+
+    # ---- value: everything resident in HBM -----------------------------------------------------------
+    stream = torch.cuda.Stream(device=dev)
+    h_c = torch.empty(n * 16, dtype=torch.uint8).pin_memory()
+    h_c.numpy()[:] = cands.view(np.uint8)
+    d_c = h_c.to(dev)
+    d_len = torch.empty(n, dtype=torch.float64, device=dev)
+    d_lb = torch.empty(n, dtype=torch.float64, device=dev)
+    d_fl = torch.empty(n, dtype=torch.uint8, device=dev)
+    d_first = torch.zeros(1, dtype=torch.int64, device=dev)
+    torch.cuda.synchronize()
+    sp = C.c_void_p(stream.cuda_stream)
+
+    def step():
+        st = lib.vnsgpu_eval_batch_dev(eng.h, p.h, n, C.c_void_p(d_c.data_ptr()), pb.budget, 1,
+                                       C.c_void_p(d_len.data_ptr()), C.c_void_p(d_lb.data_ptr()),
+                                       C.c_void_p(d_fl.data_ptr()), C.c_void_p(d_first.data_ptr()), sp)
+        eng._ck(st)
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    with torch.cuda.stream(stream):
+        for _ in range(W):
+            step()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        l0 = eng.launches
+        t_host0 = time.perf_counter()
+        e0.record(stream)
+        for a, b in ev:
+            a.record(stream)
+            step()
+            b.record(stream)
+        e1.record(stream)
+        barrier()
+        t_host1 = time.perf_counter()
+        launches = eng.launches - l0
+    total_ms = max_over_ranks(e0.elapsed_time(e1))
+    kern_ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
+    clocks = sampler.window(t_host0, t_host1) if sampler else None
+    value = world * n * K / (total_ms * 1e-3)
+    first_dev = int(d_first.item())
+    ok_flags = int(((d_fl & 2) != 0).sum().item())
+
+    # ---- e2e: the host-buffer C-ABI call (H2D of the candidates + kernel + D2H of lengths and flags) --
+    e2e = None
+    if not args.no_e2e:
+        h_len = torch.empty(n, dtype=torch.float64).pin_memory()
+        h_fl = torch.empty(n, dtype=torch.uint8).pin_memory()
+        first = C.c_int64(-1)
+        eng.set_stream(None)
+
+        def host_step():
+            eng._ck(lib.vnsgpu_eval_batch(eng.h, p.h, n, C.c_void_p(h_c.data_ptr()), pb.budget, 1,
+                                          C.cast(h_len.data_ptr(), C.POINTER(C.c_double)), None,
+                                          C.c_void_p(h_fl.data_ptr()), C.byref(first)))
+
+        for _ in range(W):
+            host_step()
+        barrier()
+        l0 = eng.launches
+        t0 = time.perf_counter()
+        for _ in range(K):
+            host_step()
+        barrier()
+        dt = max_over_ranks(time.perf_counter() - t0)
+        launches += eng.launches - l0
+        e2e = {"value": world * n * K / dt, "unit": "evals/s", "h2d_bytes_per_step": world * n * 16,
+               "d2h_bytes_per_step": world * (n * 9 + 8), "ms_per_step": 1e3 * dt / K,
+               "call": "vnsgpu_eval_batch (pinned host candidates in; lengths + flags + first accepted index out)"}
+        assert first.value == first_dev, "host and device entry points disagree on the first accepted candidate"
+        assert torch.equal(h_len[:4096], d_len[:4096].cpu()), "host and device entry points disagree"
+
+    peak, peak_src = measured_hbm_peak()
+    achieved = alg_bytes / (kern_ms * 1e-3) / 1e9
+    line = {
+        "metric": "candidate_move_evals_per_sec", "value": value, "unit": "evals/s", "n_gpus": world,
+        "steps": K, "warmup": W, "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": WORKLOADS[args.workload][0], "clusters": int(pb.C), "samples": int(pb.N),
+                   "candidates_per_step_per_gpu": n, "targets_in_path": int(T),
+                   "state": "greedy + 1 seeded VNS step per neighbourhood",
+                   "mix": "50% insertRandom proposals (MOVE/ADD), 50% exchangeRandom (EXCHANGE/REPLACE)",
+                   "outputs": "length + lower bound + flags per candidate, first accepted index",
+                   "l2": "candidates + results = %.0f MB per step > 126 MB L2 (streamed); the %.2f MB distance "
+                         "table is cache-resident by design" % (n * 33 / 1e6, eng.table_bytes / 1e6),
+                   "sharding": "candidates split by rank, table replicated, no collective in the data path"},
+        "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": None, "peak_source": peak_src, "kernel": "k_eval_batch",
+                     "kernel_ms": kern_ms, "algorithmic_bytes_per_launch": int(alg_bytes),
+                     "algorithmic_bytes_per_candidate": alg_bytes / n,
+                     "stream_bytes_per_candidate": 33,
+                     "note": "algorithmic bytes = SURVEY.md 8d (every distance-block entry once + first F row + last B row "
+                             "+ result); the table is L1/L2-resident on this instance, so the HBM traffic is the 16 B "
+                             "descriptor + 17 B of results per candidate"},
+        "accepted_in_batch": ok_flags, "first_accept": first_dev,
+    }
+    if rank == 0 and world == 1 and not args.no_cpu:
+        line["cpu_baseline"] = cpu_baseline_leg(args, sf, pb, vns, T, rows, d_len, d_lb)
+    if rank == 0 and world == 1 and not args.no_solve:
+        line["time_to_reward"] = solve_leg(args, eng, sf, pb)
+    if sampler:
+        sampler.stop()
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def cpu_baseline_leg(args, sf, pb, vns, T, rows, d_len, d_lb):
+    """The CPU checker timed on ONE host core on a bounded sample of the batch the GPU just evaluated;
+    its lengths and lower bounds must equal the GPU's bit for bit."""
+    ev = CpuEvaluator(sf, pb)
+    assert ev.T == T and (ev.vns == vns).all(), "CPU and GPU search states differ"
+    ns = min(args.cpu_sample, len(rows))
+    sample = np.ascontiguousarray(rows[:ns])
+    ev.eval(sample[:4096])
+    t0 = time.perf_counter()
+    ln, lb = ev.eval(sample)
+    dt = time.perf_counter() - t0
+    g_len, g_lb = d_len[:ns].cpu().numpy(), d_lb[:ns].cpu().numpy()
+    return {"value": ns / dt, "unit": "evals/s", "cores": 1, "kind": ev.kind,
+            "sample": "first %d candidates of rank 0's batch, %.1f s" % (ns, dt),
+            "bit_identical_to_gpu": bool((ln == g_len).all() and (lb == g_lb).all())}
+
+
+def solve_leg(args, eng, sf, pb):
+    """Second half of the metric: wall time of the whole seeded VNS (stock sop.cfg stopping rule) to the
+    reference's final reward - the device chain walks the reference's exact trajectory."""
+    from oracle import binding as ob
+    p = eng.path()
+    t0 = time.perf_counter()
+    res, impr = p.vns_run(1)
+    gpu_wall = time.perf_counter() - t0
+    out = {"seed": 1, "gpu_wall_s": gpu_wall, "gpu_device_ms": res.time_ms, "reward": res.reward, "length": res.length,
+           "num_iters": res.num_iters, "proposals": res.proposals, "evals": res.evals, "accepts": res.accepts,
+           "chain_evals_per_s": res.evals / gpu_wall}
+    if os.path.exists(ob.REF_BIN):
+        from vns_sop_b200 import instances as ins
+        with tempfile.TemporaryDirectory() as td:
+            f = os.path.join(td, "w.sop")
+            ins.write_sop(sf, f)
+            t0 = time.perf_counter()
+            subprocess.check_call([ob.REF_BIN, "--problem=" + f, "--seed=1", "--output=" + td],
+                                  stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            cpu_wall = time.perf_counter() - t0
+            rec = open(os.path.join(td, "results.log")).read().strip().rstrip(";")
+        d = dict(kv.split(":", 1) for kv in rec.split(";"))
+        out.update({"cpu_reference_wall_s": cpu_wall, "cpu_reward": float(d["REWARDS"]), "cpu_length": float(d["LENGTH"]),
+                    "cpu_num_iters": int(d["NUM_ITERS"]),
+                    "same_result": float(d["REWARDS"]) == res.reward and float(d["LENGTH"]) == res.length
+                    and int(d["NUM_ITERS"]) == res.num_iters})
+    return out
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -141,8 +141,8 @@ vnsgpu_status vnsgpu_path_get_dp(vnsgpu_ctx *ctx, int path, double *F, double *B
  * whose ACCEPT flag is set and (when skip != 0) whose LB_SKIP flag is not, or -1 */
 vnsgpu_status vnsgpu_eval_batch(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *cands, double budget,
                                 int skip, double *len, double *lb, uint8_t *flags, int64_t *first_accept);
-/* device buffers, asynchronous on `stream` (NULL = context stream); d_first_accept: one int64,
- * must be preset to INT64_MAX by the caller (atomicMin target) or NULL */
+/* device buffers, asynchronous on `stream` (NULL = context stream); d_first_accept: one int64 that
+ * the call resets and fills like first_accept above (-1 = none), or NULL */
 vnsgpu_status vnsgpu_eval_batch_dev(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *d_cands,
                                     double budget, int skip, double *d_len, double *d_lb, uint8_t *d_flags,
                                     long long *d_first_accept, void *stream);

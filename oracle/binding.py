@@ -105,8 +105,9 @@ class Oracle:
         m = np.ascontiguousarray(pb.m, dtype=np.int32)
         rw = np.ascontiguousarray(pb.reward, dtype=np.float64)
         self.I = lib.vo_inst_new(pb.C, _ip(m), _dp(rw), pb.start, pb.goal)
-        if dubins is not None:                       # (S, rho, do_ceil)
+        if dubins is not None:                       # (S, rho, do_ceil[, eps])
             ctr = np.ascontiguousarray(pb.centers, dtype=np.float64)
+            C.c_double.in_dll(lib, "vo_dubins_eps").value = dubins[3] if len(dubins) > 3 else 1e-9
             lib.vo_table_dubins(self.I, _dp(ctr), C.c_int(dubins[0]), C.c_double(dubins[1]), C.c_int(dubins[2]))
         elif pb.xy is not None:
             xy = np.ascontiguousarray(pb.xy, dtype=np.float64)

@@ -6,6 +6,10 @@
 #include <string.h>
 
 #define TWO_PI 6.283185307179586476925286766559
+/* a CSC word whose straight segment has length 0 is feasible; rounding in sin/cos can push p^2 a few
+ * ulps below 0 there (any libm), so p^2 in [-eps, 0) is clamped to 0 instead of dropping the word */
+#define VNS_DUBINS_EPS vo_dubins_eps
+double vo_dubins_eps = 1e-9; /* tests set -1e-9 to get the "word dropped" alternative of knife-edge entries */
 
 /* ------------------------------------------------------------------ instance + tables ---- */
 
@@ -97,21 +101,24 @@ double vo_dubins_length(double x0, double y0, double th0, double x1, double y1, 
    double best = INFINITY, psq, p, tau, u, t;
    /* LSL */
    psq = 2 + d * d - 2 * cab + 2 * d * (sa - sb);
-   if (psq >= 0) {
+   if (psq >= -VNS_DUBINS_EPS) {
+      psq = psq > 0 ? psq : 0;
       tau = atan2(cb - ca, d + sa - sb);
       t = mod2pi(tau - al) + sqrt(psq) + mod2pi(be - tau);
       if (t < best) best = t;
    }
    /* RSR */
    psq = 2 + d * d - 2 * cab + 2 * d * (sb - sa);
-   if (psq >= 0) {
+   if (psq >= -VNS_DUBINS_EPS) {
+      psq = psq > 0 ? psq : 0;
       tau = atan2(ca - cb, d - sa + sb);
       t = mod2pi(al - tau) + sqrt(psq) + mod2pi(tau - be);
       if (t < best) best = t;
    }
    /* LSR */
    psq = -2 + d * d + 2 * cab + 2 * d * (sa + sb);
-   if (psq >= 0) {
+   if (psq >= -VNS_DUBINS_EPS) {
+      psq = psq > 0 ? psq : 0;
       p = sqrt(psq);
       tau = atan2(-ca - cb, d + sa + sb) - atan2(-2.0, p);
       t = mod2pi(tau - al) + p + mod2pi(tau - mod2pi(be));
@@ -119,7 +126,8 @@ double vo_dubins_length(double x0, double y0, double th0, double x1, double y1, 
    }
    /* RSL */
    psq = -2 + d * d + 2 * cab - 2 * d * (sa + sb);
-   if (psq >= 0) {
+   if (psq >= -VNS_DUBINS_EPS) {
+      psq = psq > 0 ? psq : 0;
       p = sqrt(psq);
       tau = atan2(ca + cb, d - sa - sb) - atan2(2.0, p);
       t = mod2pi(al - tau) + p + mod2pi(be - tau);

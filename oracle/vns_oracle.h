@@ -61,6 +61,7 @@ static inline long vo_block(const vo_inst *I, int c1, int c2)
 void vo_table_euclid(vo_inst *I, const double *xy, int rule);
 void vo_table_dense(vo_inst *I, const double *W);
 void vo_table_dubins(vo_inst *I, const double *centers, int S, double rho, int do_ceil);
+extern double vo_dubins_eps; /* CSC words with p^2 >= -eps are kept (p^2 clamped to 0); default 1e-9 */
 double vo_dubins_length(double x0, double y0, double th0, double x1, double y1, double th1, double rho);
 void vo_bounds(vo_inst *I);
 void vo_get_dense(const vo_inst *I, double *W);

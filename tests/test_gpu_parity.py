@@ -176,14 +176,32 @@ def test_dubins_table_known_answers(S):
     e = engine.Engine(0).load_problem(pb, dubins=(S, sf.dubins_radius, 0))
     L = e.table_dense()
     W = pb.W
-    ok = (np.ceil(L) == W) | (np.ceil(L - 1e-9) == W) | (np.ceil(L + 1e-9) == W)
-    assert ok.all()
+    # identical start and end state (the diagonal): the true length is 0, but LSR/RSL evaluate
+    # mod2pi(tau - alpha) at tau - alpha = +-1 ulp, so any libm returns 0 or one full circle
+    # (the shipped s_12 file itself holds 315 = ceil(2 pi rho) in 21 of its 252 diagonal
+    # entries).  No solver path reads a same-cluster block.
+    diag = np.eye(pb.N, dtype=bool)
+    full = 2 * np.pi * sf.dubins_radius
+    dl = L[diag]
+    assert (np.minimum(np.abs(dl), np.abs(dl - full)) < 1e-9).all()
+    # knife-edge entries (a CSC word with a zero-length straight segment, kept by the kernel and the
+    # oracle, kept or dropped by the files' generator): see tests/test_oracle_golden.py
     Lo = ob.Oracle(pb, dubins=(S, sf.dubins_radius, 0)).dense()
-    assert np.allclose(L, Lo, rtol=1e-9, atol=1e-9)
+    Ls = ob.Oracle(pb, dubins=(S, sf.dubins_radius, 0, -1e-9)).dense()
+    knife = (Lo != Ls) & ~diag
+
+    def kat(X):
+        return (np.ceil(X) == W) | (np.ceil(X - 1e-9) == W) | (np.ceil(X + 1e-9) == W)
+    ok = kat(L) | (knife & kat(Ls)) | diag
+    bad = np.argwhere(~ok)
+    assert len(bad) == 0, [(int(i), int(j), float(L[i, j]), float(W[i, j])) for i, j in bad[:8]]
+    close = np.isclose(L, Lo, rtol=1e-9, atol=1e-9) | diag
+    bad = np.argwhere(~close)
+    assert len(bad) == 0, [(int(i), int(j), float(L[i, j]), float(Lo[i, j])) for i, j in bad[:8]]
     e2 = engine.Engine(0).load_problem(pb, dubins=(S, sf.dubins_radius, 1))
     Lc = e2.table_dense()
     assert (Lc == np.ceil(L)).all()
-    near = np.abs(L - np.round(L)) < 1e-9
+    near = (np.abs(L - np.round(L)) < 1e-9) | diag | knife
     assert (Lc[~near] == W[~near]).all()
     e.close()
     e2.close()

