@@ -42,7 +42,7 @@ WORKLOADS = {
     "opn_s08": ("tsiligirides_problem_2_budget_30_d_50_s_08", os.path.join(ROOT, "tests", "golden", "opn_s08.npz")),
     "dop_s12": ("tsiligirides_problem_2_budget_30_r_50_s_12", os.path.join(ROOT, "tests", "golden", "dop_s12.npz")),
 }
-STATE_SEED = 7          # the search state is greedy + one seeded VNS step of each neighbourhood
+STATE = "the greedy initial tour (greedy_insertion, vns_sop_solver.cpp:1091-1155; SURVEY.md 8d)"
 FALLBACK_HBM_GBS = 6650.0   # /opt/skills/guides/B200_PROFILING.md "FALLBACK"
 
 
@@ -96,10 +96,6 @@ def load_workload(name):
     return sf, ins.build_problem(sf)
 
 
-def state_steps(nvns):
-    return [("shake", 1), ("ls", 1, nvns * nvns), ("shake", 2), ("ls", 2, nvns * nvns)]
-
-
 class CpuEvaluator:
     """The CPU side: the reference's own code when oracle/_ref was built (kind "reference"), else the
     C port (kind "port").  TEST/BASELINE infrastructure - never on the product path."""
@@ -115,22 +111,10 @@ class CpuEvaluator:
             self.o = ob.RefOracle(self.tmp.name)
             self.p = self.o.path()
             self.p.greedy()
-            self.o.seed(STATE_SEED)
-            for st in state_steps(len(self.p.vns)):
-                if st[0] == "shake":
-                    self.p.shake(st[1])
-                else:
-                    self.p.local_search(st[1], st[2])
         else:
             self.o = ob.Oracle(pb)
             self.p = self.o.path()
             self.p.greedy()
-            g = ob.new_rng(STATE_SEED)
-            for st in state_steps(len(self.p.vns)):
-                if st[0] == "shake":
-                    self.p.shake(st[1], g)
-                else:
-                    self.p.local_search(st[1], st[2], g)
         self.vns, self.T = self.p.vns, self.p.T
 
     def eval(self, cands):
@@ -187,7 +171,7 @@ def run_reference(args):
         "impl": "reference", "metric": "candidate_move_evals_per_sec", "value": v, "unit": "evals/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": name, "candidates_per_step": n, "state": "greedy + 1 seeded VNS step per neighbourhood",
+        "config": {"workload": name, "candidates_per_step": n, "state": STATE,
                    "outputs": "length + lower bound per candidate"},
         "cpu_baseline": {"value": v, "unit": "evals/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": v, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -249,12 +233,6 @@ def prepare_gpu_state(eng):
     from vns_sop_b200 import engine
     p = eng.path()
     p.greedy_insertion()
-    rng = engine.seeded_rng(STATE_SEED)
-    for st in state_steps(len(p.vns)):
-        if st[0] == "shake":
-            p.shake(st[1], rng)
-        else:
-            p._ls(st[1], st[2], rng, None, 1)
     return p
 
 
@@ -385,7 +363,7 @@ def run_b200(args):
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": WORKLOADS[args.workload][0], "clusters": int(pb.C), "samples": int(pb.N),
                    "candidates_per_step_per_gpu": n, "targets_in_path": int(T),
-                   "state": "greedy + 1 seeded VNS step per neighbourhood",
+                   "state": STATE,
                    "mix": "50% insertRandom proposals (MOVE/ADD), 50% exchangeRandom (EXCHANGE/REPLACE)",
                    "outputs": "length + lower bound + flags per candidate, first accepted index",
                    "l2": "candidates + results = %.0f MB per step > 126 MB L2 (streamed); the %.2f MB distance "

@@ -100,6 +100,14 @@ int64_t vnsgpu_launch_count(const vnsgpu_ctx *ctx);
 /* run everything on this CUDA stream (cudaStream_t as void*); NULL = the context's own stream */
 vnsgpu_status vnsgpu_set_stream(vnsgpu_ctx *ctx, void *stream);
 vnsgpu_status vnsgpu_sync(vnsgpu_ctx *ctx);
+/* Tables whose entries are all integers (every shipped dataset: CEIL_2D / EUC_2D / integer EXPLICIT)
+ * are evaluated in exact int32 arithmetic on a 4-byte copy of the table (bit-identical results);
+ * enable = 0 forces the IEEE double path.  Default: enabled. */
+vnsgpu_status vnsgpu_set_int_path(vnsgpu_ctx *ctx, int enable);
+int vnsgpu_int_path_active(const vnsgpu_ctx *ctx);
+/* Batches of >= 8192 candidates are evaluated in chain-length order (a device-side counting sort of the
+ * descriptors; results still land at the caller's indices).  enable = 0 keeps the caller's order. */
+vnsgpu_status vnsgpu_set_batch_sort(vnsgpu_ctx *ctx, int enable);
 
 /* ---- instance + distance table: replaces VnsSopPath::setSamplesDistances (vns_sop_path.cpp:38-48)
  *      fed by SOPLoader::getSOPFromNodes / getSOPFromWeightMatrix / getOP / getOPN ---------------- */
@@ -151,7 +159,8 @@ vnsgpu_status vnsgpu_eval_batch_dev(vnsgpu_ctx *ctx, int path, int64_t n, const 
  * the path's current state, advancing *rng exactly as the reference's draws would; HOST buffer */
 vnsgpu_status vnsgpu_gen_proposals(vnsgpu_ctx *ctx, int path, int kind, int64_t n, vnsgpu_rng *rng,
                                    vnsgpu_cand *cands);
-/* algorithmic bytes of a candidate list: 8*(sum m_src*m_dst + m_first + m_last) + 8 */
+/* algorithmic bytes of a candidate list: w*sum m_src*m_dst + 8*(m_first + m_last) + 8,
+ * w = bytes per table entry the active evaluation path reads (8 double, 4 exact-int32) */
 vnsgpu_status vnsgpu_cand_bytes(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *cands, int64_t *bytes);
 
 /* ---- neighbourhood drivers (a15, a16) ---------------------------------------------------------- */

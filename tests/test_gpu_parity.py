@@ -166,6 +166,62 @@ def test_full_vns_run_seed1_follows_reference_trajectory(name, golden, eng_cache
     assert calc <= pb.budget
 
 
+@pytest.mark.parametrize("int_path", [True, False])
+@pytest.mark.parametrize("name", ALL)
+def test_eval_batch_both_arithmetic_paths_vs_oracle(name, int_path, golden, eng_cache):
+    """The sub-warp group kernel in exact int32 (DPX) and in IEEE double arithmetic: lengths, lower
+    bounds and the first accepted index against the CPU oracle on several search states, with
+    out-of-range candidates mixed in and a batch size that leaves groups and warps ragged."""
+    from oracle import binding as ob
+    from vns_sop_b200 import engine
+    e, sf, pb = eng_cache(name)
+    g, a = golden[name], load_arrays(name)
+    e.set_int_path(int_path)
+    try:
+        assert e.int_path_active == int_path        # every shipped instance has an all-integer table
+        o = ob.Oracle(pb)
+        po, pg = o.path(a["greedy_vns"], g["greedy"]["T"]), e.path(a["greedy_vns"], g["greedy"]["T"])
+        go, gg = ob.new_rng(21), engine.seeded_rng(21)
+        rs = np.random.RandomState(5)
+        for it in range(4):
+            T = po.T
+            if T >= 3:
+                cands = random_candidates(rs, po.vns, T, 2999)
+                cands[::97] = [3, 0, 1]                 # |what - where| < 2: the reference exit(1)s
+                ln, lb, fl, first = pg.eval_batch(cands)
+                oln, olb = po.eval_batch(cands)
+                bad = (fl & engine.F_BAD) != 0
+                assert bad[::97].all() and bad.sum() == len(cands[::97])
+                assert (ln[~bad] == oln[~bad]).all() and (lb[~bad] == olb[~bad]).all()
+                ok = np.nonzero(((fl & 2) != 0) & ((fl & 4) == 0))[0]
+                assert first == (int(ok[0]) if len(ok) else -1)
+            k = 1 + it % 2
+            po.shake(k, go)
+            pg.shake(k, gg)
+            po.local_search(k, 400, go)
+            pg._ls(k, 400, gg, None, 1)
+            assert (pg.vns == po.vns).all() and pg.getNumTargets() == po.T
+        # a batch large enough for the chain-length counting sort (and, through the host-buffer
+        # call, for several pipeline chunks); same answers with the sort switched off
+        T = po.T
+        if T >= 3:
+            big = random_candidates(rs, po.vns, T, 150001 if name == "krob200" else 20011)
+            big[::1013] = [4, 0, 0]
+            ln, lb, fl, first = pg.eval_batch(big)
+            oln, olb = po.eval_batch(big)
+            bad = (fl & engine.F_BAD) != 0
+            assert bad.sum() == len(big[::1013])
+            assert (ln[~bad] == oln[~bad]).all() and (lb[~bad] == olb[~bad]).all()
+            ok = np.nonzero(((fl & 2) != 0) & ((fl & 4) == 0))[0]
+            assert first == (int(ok[0]) if len(ok) else -1)
+            e.set_batch_sort(False)
+            ln2, lb2, fl2, first2 = pg.eval_batch(big)
+            assert (ln2[~bad] == ln[~bad]).all() and (lb2[~bad] == lb[~bad]).all() and (fl2 == fl).all() and first2 == first
+    finally:
+        e.set_int_path(True)
+        e.set_batch_sort(True)
+
+
 @pytest.mark.parametrize("S", [4, 8, 12])
 def test_dubins_table_known_answers(S):
     """a4: the Dubins kernel against the 98 784 entries shipped with the reference's DOP datasets

@@ -190,20 +190,79 @@ static int eval_grid(const vnsgpu_ctx *ctx, int64_t n)
    return (int)std::max<int64_t>(1, std::min(need, cap));
 }
 
+// one evaluation of n candidates on `st`; idx0 = index of cands[0] in the caller's batch (first-accept
+// key); slot = which of the VNS_PIPE_EVENTS sort-scratch regions to use (chunks in flight concurrently)
+#define VNS_SORT_MIN 8192
+static vnsgpu_status launch_eval(vnsgpu_ctx *ctx, int path, int64_t n, int64_t idx0, const vnsgpu_cand *d_cands, double budget,
+                                 int skip, double *d_len, double *d_lb, uint8_t *d_flags, unsigned long long *d_first, cudaStream_t st,
+                                 int slot, int64_t perm_off)
+{
+   const InstDev &I = ctx->I;
+   const PathDev &P = ctx->paths[path].d;
+   if (group_kernel_ok(ctx)) {
+      const unsigned *d_perm = nullptr;
+      if (ctx->sort_batches && n >= VNS_SORT_MIN && n < (1ll << 32)) {
+         const int nb = I.rows + 1;
+         if (!ctx->d_hist) CK(cudaMalloc(&ctx->d_hist, sizeof(unsigned) * 2 * nb * VNS_PIPE_EVENTS));
+         if ((int64_t)ctx->perm_cap < perm_off + n) {
+            if (ctx->d_perm) { CK(cudaDeviceSynchronize()); CK(cudaFree(ctx->d_perm)); }
+            ctx->d_perm = nullptr; ctx->perm_cap = 0;
+            CK(cudaMalloc(&ctx->d_perm, sizeof(unsigned) * (size_t)(perm_off + n)));
+            ctx->perm_cap = (size_t)(perm_off + n);
+         }
+         unsigned *hist = ctx->d_hist + (size_t)slot * 2 * nb, *cursor = hist + nb, *perm = ctx->d_perm + perm_off;
+         const int sgrid = (int)std::min<int64_t>((n + 2047) / 2048, (int64_t)ctx->num_sms * 8);
+         CK(cudaMemsetAsync(hist, 0, sizeof(unsigned) * nb, st));
+         k_sort_hist<<<sgrid, 256, sizeof(unsigned) * nb, st>>>(I, P, n, d_cands, nb, hist);
+         LAUNCHED(ctx);
+         k_sort_scan<<<1, 32, 0, st>>>(nb, hist, cursor);
+         LAUNCHED(ctx);
+         k_sort_scatter<<<sgrid, 256, sizeof(unsigned) * 2 * nb, st>>>(I, P, n, d_cands, nb, cursor, perm);
+         LAUNCHED(ctx);
+         d_perm = perm;
+      }
+      // T is only known on the device; size the layer map for the row capacity
+      const size_t smem = eval_smem_bytes(I.rows, I.C);
+      const int G = ctx->group_lanes, NR = (I.mp + G - 1) / G <= 1 ? 1 : ((I.mp + G - 1) / G <= 2 ? 2 : 4);
+      const int64_t per_cta = (VNS_EVAL_THREADS / 32) * (32 / G);
+      const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n + per_cta - 1) / per_cta, (int64_t)ctx->num_sms * 8));
+#define VNS_LAUNCH_EVAL(V, GG, RR, TAB)                                                                              \
+   k_eval_groups<V, GG, RR><<<grid, VNS_EVAL_THREADS, smem, st>>>(I, TAB, P, n, idx0, d_cands, d_perm, budget, skip, d_len, d_lb, \
+                                                                   d_flags, d_first)
+#define VNS_LAUNCH_EVAL_V(V, TAB)                                                                                    \
+   do {                                                                                                              \
+      if (G == 8 && NR == 1) VNS_LAUNCH_EVAL(V, 8, 1, TAB);                                                           \
+      else if (G == 8 && NR == 2) VNS_LAUNCH_EVAL(V, 8, 2, TAB);                                                      \
+      else if (G == 8) VNS_LAUNCH_EVAL(V, 8, 4, TAB);                                                                 \
+      else if (G == 16 && NR == 1) VNS_LAUNCH_EVAL(V, 16, 1, TAB);                                                    \
+      else if (G == 16) VNS_LAUNCH_EVAL(V, 16, 2, TAB);                                                               \
+      else VNS_LAUNCH_EVAL(V, 32, 1, TAB);                                                                            \
+   } while (0)
+      if (ctx->use_int && ctx->d_D32) VNS_LAUNCH_EVAL_V(int, ctx->d_D32);
+      else VNS_LAUNCH_EVAL_V(double, ctx->d_D);
+#undef VNS_LAUNCH_EVAL_V
+#undef VNS_LAUNCH_EVAL
+   } else {
+      const size_t smem = sizeof(double) * 2 * I.mp * (VNS_EVAL_THREADS / 32);
+      k_eval_batch<<<eval_grid(ctx, n), VNS_EVAL_THREADS, smem, st>>>(I, P, n, idx0, d_cands, budget, skip, d_len, d_lb, d_flags, d_first);
+   }
+   LAUNCHED(ctx);
+   return VNSGPU_OK;
+}
+
 vnsgpu_status vnsgpu_eval_batch_dev(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *d_cands, double budget, int skip,
                                     double *d_len, double *d_lb, uint8_t *d_flags, long long *d_first_accept, void *stream)
 {
    if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
    if (n <= 0) return VNSGPU_OK;
    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
-   const size_t smem = sizeof(double) * 2 * ctx->I.mp * (VNS_EVAL_THREADS / 32);
    if (d_first_accept) CK(cudaMemsetAsync(d_first_accept, 0xFF, sizeof(long long), st));   // -1 = none
-   k_eval_batch<<<eval_grid(ctx, n), VNS_EVAL_THREADS, smem, st>>>(ctx->I, ctx->paths[path].d, n, d_cands, budget, skip, d_len, d_lb,
-                                                                    d_flags, (unsigned long long *)d_first_accept);
-   LAUNCHED(ctx);
-   return VNSGPU_OK;
+   return launch_eval(ctx, path, n, 0, d_cands, budget, skip, d_len, d_lb, d_flags, (unsigned long long *)d_first_accept, st, 0, 0);
 }
 
+// Host buffers.  The batch is cut into chunks that flow through three streams - H2D of chunk c+1, the
+// kernel on chunk c and D2H of chunk c-1 overlap - so the call runs at PCIe speed when the caller's
+// buffers are pinned (pageable buffers work, the copies then serialise inside the driver).
 vnsgpu_status vnsgpu_eval_batch(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *cands, double budget, int skip, double *len,
                                 double *lb, uint8_t *flags, int64_t *first_accept)
 {
@@ -219,16 +278,42 @@ vnsgpu_status vnsgpu_eval_batch(vnsgpu_ctx *ctx, int path, int64_t n, const vnsg
    vnsgpu_cand *d_c = (vnsgpu_cand *)b;
    double *d_len = (double *)(b + o_len), *d_lb = (double *)(b + o_lb);
    uint8_t *d_fl = (uint8_t *)(b + o_fl);
-   CK(cudaMemcpyAsync(d_c, cands, sizeof(vnsgpu_cand) * n, cudaMemcpyHostToDevice, ctx->stream));
-   s = vnsgpu_eval_batch_dev(ctx, path, n, d_c, budget, skip, len ? d_len : nullptr, lb ? d_lb : nullptr, flags ? d_fl : nullptr,
-                             ctx->d_first, ctx->stream);
-   if (s) return s;
-   long long first = 0;
-   if (len) CK(cudaMemcpyAsync(len, d_len, sizeof(double) * n, cudaMemcpyDeviceToHost, ctx->stream));
-   if (lb) CK(cudaMemcpyAsync(lb, d_lb, sizeof(double) * n, cudaMemcpyDeviceToHost, ctx->stream));
-   if (flags) CK(cudaMemcpyAsync(flags, d_fl, n, cudaMemcpyDeviceToHost, ctx->stream));
-   CK(cudaMemcpyAsync(&first, ctx->d_first, sizeof(first), cudaMemcpyDeviceToHost, ctx->stream));
-   CK(cudaStreamSynchronize(ctx->stream));
+   if (!ctx->s_in) {
+      CK(cudaStreamCreateWithFlags(&ctx->s_in, cudaStreamNonBlocking));
+      CK(cudaStreamCreateWithFlags(&ctx->s_out, cudaStreamNonBlocking));
+      for (int k = 0; k < VNS_PIPE_EVENTS; ++k) {
+         CK(cudaEventCreateWithFlags(&ctx->ev_in[k], cudaEventDisableTiming));
+         CK(cudaEventCreateWithFlags(&ctx->ev_k[k], cudaEventDisableTiming));
+      }
+      CK(cudaEventCreateWithFlags(&ctx->ev_start, cudaEventDisableTiming));
+   }
+   // chunks: at most VNS_PIPE_EVENTS, at least 64 Ki candidates each
+   int64_t chunk = std::max<int64_t>(65536, (n + VNS_PIPE_EVENTS - 1) / VNS_PIPE_EVENTS);
+   chunk = (chunk + 255) & ~(int64_t)255;
+   cudaStream_t sk = ctx->stream;
+   CK(cudaMemsetAsync(ctx->d_first, 0xFF, sizeof(long long), sk));
+   CK(cudaEventRecord(ctx->ev_start, sk));          // order behind whatever the caller queued before
+   CK(cudaStreamWaitEvent(ctx->s_in, ctx->ev_start, 0));
+   CK(cudaStreamWaitEvent(ctx->s_out, ctx->ev_start, 0));
+   int c = 0;
+   for (int64_t lo = 0; lo < n; lo += chunk, ++c) {
+      const int64_t cn = std::min(chunk, n - lo);
+      CK(cudaMemcpyAsync(d_c + lo, cands + lo, sizeof(vnsgpu_cand) * cn, cudaMemcpyHostToDevice, ctx->s_in));
+      CK(cudaEventRecord(ctx->ev_in[c], ctx->s_in));
+      CK(cudaStreamWaitEvent(sk, ctx->ev_in[c], 0));
+      s = launch_eval(ctx, path, cn, lo, d_c + lo, budget, skip, len ? d_len + lo : nullptr, lb ? d_lb + lo : nullptr,
+                      flags ? d_fl + lo : nullptr, (unsigned long long *)ctx->d_first, sk, c, lo);
+      if (s) return s;
+      CK(cudaEventRecord(ctx->ev_k[c], sk));
+      CK(cudaStreamWaitEvent(ctx->s_out, ctx->ev_k[c], 0));
+      if (len) CK(cudaMemcpyAsync(len + lo, d_len + lo, sizeof(double) * cn, cudaMemcpyDeviceToHost, ctx->s_out));
+      if (lb) CK(cudaMemcpyAsync(lb + lo, d_lb + lo, sizeof(double) * cn, cudaMemcpyDeviceToHost, ctx->s_out));
+      if (flags) CK(cudaMemcpyAsync(flags + lo, d_fl + lo, cn, cudaMemcpyDeviceToHost, ctx->s_out));
+   }
+   long long first = -1;
+   CK(cudaMemcpyAsync(&first, ctx->d_first, sizeof(first), cudaMemcpyDeviceToHost, sk));
+   CK(cudaStreamSynchronize(sk));
+   CK(cudaStreamSynchronize(ctx->s_out));
    if (first_accept) *first_accept = (int64_t)first;
    return VNSGPU_OK;
 }
@@ -246,7 +331,7 @@ vnsgpu_status vnsgpu_cand_bytes(vnsgpu_ctx *ctx, int path, int64_t n, const vnsg
    CK(cudaMemsetAsync(d_tot, 0, 8, ctx->stream));
    CK(cudaMemcpyAsync(d_c, cands, sizeof(vnsgpu_cand) * n, cudaMemcpyHostToDevice, ctx->stream));
    const int grid = (int)std::min<int64_t>((n + 255) / 256, 1184);
-   k_cand_bytes<<<grid, 256, 0, ctx->stream>>>(ctx->I, ctx->paths[path].d, n, d_c, d_tot);
+   k_cand_bytes<<<grid, 256, 0, ctx->stream>>>(ctx->I, ctx->paths[path].d, n, d_c, d_tot, vnsgpu_int_path_active(ctx) ? 4 : 8);
    LAUNCHED(ctx);
    unsigned long long tot = 0;
    CK(cudaMemcpyAsync(&tot, d_tot, 8, cudaMemcpyDeviceToHost, ctx->stream));

@@ -45,11 +45,11 @@ __global__ void k_path_solution(InstDev I, PathDev P, int *cluster, int *node, d
    if (threadIdx.x == 0 && blockIdx.x == 0) *calc = path_walk_back(I, P, P.hdr[HDR_T], cluster, node);
 }
 
-// ---- batched candidate evaluation (a8-a13): one warp per candidate, grid-stride ---------------------
+// ---- batched candidate evaluation (a8-a13), wide-cluster fallback: one warp per candidate -----------
 // len = tryTo*(...), lb = tryTo*LowerBound(...), flags = feasibility / accept predicate / LB skip;
 // d_first receives the smallest accepted (and not LB-skipped when skip != 0) candidate index.
-#define VNS_EVAL_THREADS 256
-__global__ void __launch_bounds__(VNS_EVAL_THREADS) k_eval_batch(InstDev I, PathDev P, long long n, const vnsgpu_cand *__restrict__ cands,
+// generic fallback for clusters with more than 32 samples (the group kernel of eval.cuh covers the rest)
+__global__ void __launch_bounds__(VNS_EVAL_THREADS) k_eval_batch(InstDev I, PathDev P, long long n, long long idx0, const vnsgpu_cand *__restrict__ cands,
                                                                  double budget, int skipflag, double *__restrict__ len,
                                                                  double *__restrict__ lb, uint8_t *__restrict__ flags, unsigned long long *d_first)
 {
@@ -86,21 +86,21 @@ __global__ void __launch_bounds__(VNS_EVAL_THREADS) k_eval_batch(InstDev I, Path
          if (len) len[k] = l;
          if (lb) lb[k] = bound;
          if (flags) flags[k] = (uint8_t)f;
-         if ((f & VNSGPU_F_ACCEPT) && !(skipflag && (f & VNSGPU_F_LB_SKIP)) && (unsigned long long)k < best) best = (unsigned long long)k;
+         if ((f & VNSGPU_F_ACCEPT) && !(skipflag && (f & VNSGPU_F_LB_SKIP)) && (unsigned long long)(k + idx0) < best) best = (unsigned long long)(k + idx0);
       }
    }
    if (d_first && lane == 0 && best != ULLONG_MAX) atomicMin(d_first, best);
 }
 
 __global__ void __launch_bounds__(256) k_cand_bytes(InstDev I, PathDev P, long long n, const vnsgpu_cand *__restrict__ cands,
-                                                    unsigned long long *total)
+                                                    unsigned long long *total, int w)
 {
    const int T = P.hdr[HDR_T];
    long long acc = 0;
    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (long long)gridDim.x * blockDim.x) {
       const int4 cd = __ldg(reinterpret_cast<const int4 *>(cands) + k);
       const CandPlan pl = make_plan(T, cd.x, cd.y, cd.z, I.C);
-      if (!pl.bad) acc += plan_bytes(I, P, T, pl);
+      if (!pl.bad) acc += plan_bytes(I, P, T, pl, w);
    }
    for (int s = 16; s > 0; s >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s);
    if ((threadIdx.x & 31) == 0) atomicAdd(total, (unsigned long long)acc);

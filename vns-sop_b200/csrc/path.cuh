@@ -242,7 +242,7 @@ __device__ double warp_eval(const InstDev &I, const PathDev &P, int T, const Can
 
 // algorithmic bytes of one candidate: every block entry once + first F row + last B
 // row + the result
-__device__ long long plan_bytes(const InstDev &I, const PathDev &P, int T, const CandPlan &p)
+__device__ long long plan_bytes(const InstDev &I, const PathDev &P, int T, const CandPlan &p, int w)
 {
    long long e = 0;
    int ca = plan_cluster(I, P, T, p, 0);
@@ -254,5 +254,5 @@ __device__ long long plan_bytes(const InstDev &I, const PathDev &P, int T, const
       e += (long long)ma * mb;
       ma = mb;
    }
-   return 8 * (e + m0 + ma) + 8;
+   return w * e + 8 * (m0 + ma) + 8;   // w = bytes per table entry read (8 double, 4 int32 path)
 }

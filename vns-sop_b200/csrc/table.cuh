@@ -40,7 +40,7 @@ __global__ void __launch_bounds__(256) k_table_euclid(InstDev I, const double2 *
 
 #define VNS_TWO_PI 6.283185307179586476925286766559
 // a CSC word whose straight segment has length 0 is feasible; rounding in sin/cos can push p^2 a few
-// ulps below 0 there, so p^2 in [-eps, 0) is clamped to 0 instead of dropping the word (as the oracle)
+// ulps below 0 there, so p^2 in [-eps, 0) is clamped to 0 instead of dropping the word
 #define VNS_DUBINS_EPS 1e-9
 
 __device__ __forceinline__ double mod2pi(double t) { return t - VNS_TWO_PI * floor(t / VNS_TWO_PI); }

@@ -14,10 +14,13 @@
 #include "table.cuh"
 #include "path.cuh"
 #include "search.cuh"
+#include "eval.cuh"
 #include "kernels.cuh"
 
 static_assert(sizeof(vnsgpu_rng) == sizeof(RngState), "rng layout");
 static_assert(sizeof(vnsgpu_cand) == 16, "cand layout");
+
+#define VNS_PIPE_EVENTS 16
 
 struct PathHost {
    void *block = nullptr;
@@ -27,12 +30,20 @@ struct PathHost {
 struct vnsgpu_ctx {
    int device = 0;
    cudaStream_t own = nullptr, stream = nullptr;
+   cudaStream_t s_in = nullptr, s_out = nullptr;                 // copy streams of the host-buffer pipeline
+   cudaEvent_t ev_in[VNS_PIPE_EVENTS] = {}, ev_k[VNS_PIPE_EVENTS] = {}, ev_start = nullptr;
    InstDev I{};
    bool have_clusters = false, have_table = false;
    std::vector<int> m, off;
    std::vector<double> reward;
    int *d_m = nullptr, *d_off = nullptr, *d_clof = nullptr;
    double *d_reward = nullptr, *d_D = nullptr, *d_dmin = nullptr, *d_dmax = nullptr;
+   int *d_D32 = nullptr;     // int32 copy of an all-integer table (DPX evaluation path), else null
+   bool use_int = true;      // vnsgpu_set_int_path
+   bool sort_batches = true; // evaluate batches in chain-length order (vnsgpu_set_batch_sort)
+   int group_lanes = 8;      // lanes per candidate of k_eval_groups, from the mean cluster size
+   unsigned *d_hist = nullptr, *d_perm = nullptr;
+   size_t perm_cap = 0;
    unsigned long long *d_info = nullptr;
    std::vector<PathHost> paths;
    // scratch
@@ -113,7 +124,9 @@ static void free_instance(vnsgpu_ctx *ctx)
    for (PathHost &p : ctx->paths) cudaFree(p.block);
    ctx->paths.clear();
    cudaFree(ctx->d_m); cudaFree(ctx->d_off); cudaFree(ctx->d_clof); cudaFree(ctx->d_reward);
-   cudaFree(ctx->d_D); cudaFree(ctx->d_dmin); cudaFree(ctx->d_dmax); cudaFree(ctx->d_seg);
+   cudaFree(ctx->d_D); cudaFree(ctx->d_dmin); cudaFree(ctx->d_dmax); cudaFree(ctx->d_seg); cudaFree(ctx->d_D32);
+   cudaFree(ctx->d_hist); cudaFree(ctx->d_perm);
+   ctx->d_D32 = nullptr; ctx->d_hist = ctx->d_perm = nullptr; ctx->perm_cap = 0;
    ctx->d_m = ctx->d_off = ctx->d_clof = ctx->d_seg = nullptr;
    ctx->d_reward = ctx->d_D = ctx->d_dmin = ctx->d_dmax = nullptr;
    ctx->have_clusters = ctx->have_table = false;
@@ -127,6 +140,10 @@ void vnsgpu_destroy(vnsgpu_ctx *ctx)
    free_instance(ctx);
    cudaFree(ctx->d_scratch); cudaFree(ctx->d_rng); cudaFree(ctx->d_stats); cudaFree(ctx->d_first);
    cudaFree(ctx->d_res); cudaFree(ctx->d_info);
+   if (ctx->s_in) {
+      cudaStreamDestroy(ctx->s_in); cudaStreamDestroy(ctx->s_out); cudaEventDestroy(ctx->ev_start);
+      for (int k = 0; k < VNS_PIPE_EVENTS; ++k) { cudaEventDestroy(ctx->ev_in[k]); cudaEventDestroy(ctx->ev_k[k]); }
+   }
    if (ctx->own) cudaStreamDestroy(ctx->own);
    delete ctx;
 }
@@ -140,6 +157,25 @@ vnsgpu_status vnsgpu_set_stream(vnsgpu_ctx *ctx, void *stream)
    ctx->stream = stream ? (cudaStream_t)stream : ctx->own;
    return VNSGPU_OK;
 }
+
+vnsgpu_status vnsgpu_set_batch_sort(vnsgpu_ctx *ctx, int enable)
+{
+   ctx->sort_batches = enable != 0;
+   return VNSGPU_OK;
+}
+
+vnsgpu_status vnsgpu_set_int_path(vnsgpu_ctx *ctx, int enable)
+{
+   ctx->use_int = enable != 0;
+   return VNSGPU_OK;
+}
+
+static bool group_kernel_ok(const vnsgpu_ctx *ctx)
+{
+   const int G = ctx->group_lanes, nr = (ctx->I.mp + G - 1) / G;
+   return nr <= (G == 8 ? 4 : (G == 16 ? 2 : 1)) && (long long)ctx->I.N * ctx->I.N < (1ll << 32);
+}
+int vnsgpu_int_path_active(const vnsgpu_ctx *ctx) { return ctx->use_int && ctx->d_D32 != nullptr && group_kernel_ok(ctx); }
 
 vnsgpu_status vnsgpu_sync(vnsgpu_ctx *ctx)
 {
@@ -184,6 +220,14 @@ vnsgpu_status vnsgpu_set_clusters(vnsgpu_ctx *ctx, int C, const int *m, const do
    I.m = ctx->d_m; I.off = ctx->d_off; I.clof = ctx->d_clof; I.reward = ctx->d_reward;
    I.D = ctx->d_D; I.dmin = ctx->d_dmin;
    CK(cudaMalloc(&ctx->d_seg, sizeof(int) * 2 * I.rows));
+   // lanes per candidate: the smallest power of two >= the mean cluster size (>= 8); larger clusters
+   // take up to 4 registers per lane
+   {
+      const double mean = (double)N / C;
+      int G = mean <= 8 ? 8 : (mean <= 16 ? 16 : 32);
+      while (G < 32 && (mp + G - 1) / G > 4) G *= 2;
+      ctx->group_lanes = G;
+   }
    ctx->have_clusters = true;
    return VNSGPU_OK;
 }
@@ -210,6 +254,15 @@ static vnsgpu_status finish_table(vnsgpu_ctx *ctx)
    memcpy(&mx, &info[1], sizeof(double));
    // integers below 2^53 / (layers+1): every partial path sum is exact in double
    ctx->I.exact_int = (info[0] == 0 && mx * (double)(ctx->I.rows + 1) < 9007199254740992.0) ? 1 : 0;
+   // int32 copy for the DPX path: INF + INF and every partial path sum must stay below 2^31
+   if (ctx->d_D32) { CK(cudaFree(ctx->d_D32)); ctx->d_D32 = nullptr; }
+   if (ctx->I.exact_int && mx * (double)(ctx->I.rows + 1) < 536870912.0) {
+      const long long nn = (long long)ctx->I.N * ctx->I.N;
+      CK(cudaMalloc(&ctx->d_D32, sizeof(int) * (size_t)nn + 64));
+      k_table_to_int<<<(int)std::min<long long>((nn + 255) / 256, 148 * 16), 256, 0, ctx->stream>>>(ctx->d_D, ctx->d_D32, nn);
+      LAUNCHED(ctx);
+      CK(cudaStreamSynchronize(ctx->stream));
+   }
    ctx->have_table = true;
    return VNSGPU_OK;
 }

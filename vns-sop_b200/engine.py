@@ -53,6 +53,9 @@ _SIGS = {
     "vnsgpu_create": [C.POINTER(vp), C.c_int],
     "vnsgpu_set_stream": [vp, vp],
     "vnsgpu_sync": [vp],
+    "vnsgpu_set_int_path": [vp, C.c_int],
+    "vnsgpu_set_batch_sort": [vp, C.c_int],
+    "vnsgpu_int_path_active": [vp],
     "vnsgpu_set_clusters": [vp, C.c_int, ip, dp, C.c_int, C.c_int],
     "vnsgpu_build_table_euclid": [vp, dp, C.c_int],
     "vnsgpu_build_table_dubins": [vp, dp, C.c_int, C.c_double, C.c_int],
@@ -166,6 +169,17 @@ class Engine:
 
     def sync(self):
         self._ck(self.lib.vnsgpu_sync(self.h))
+
+    def set_int_path(self, enable):
+        """False forces IEEE double evaluation even on all-integer tables (tests run both)."""
+        self._ck(self.lib.vnsgpu_set_int_path(self.h, int(enable)))
+
+    def set_batch_sort(self, enable):
+        self._ck(self.lib.vnsgpu_set_batch_sort(self.h, int(enable)))
+
+    @property
+    def int_path_active(self):
+        return bool(self.lib.vnsgpu_int_path_active(self.h))
 
     # ---- setSamplesDistances -----------------------------------------------------------------------
     def set_clusters(self, m, reward, start, goal):
