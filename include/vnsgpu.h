@@ -108,6 +108,13 @@ int vnsgpu_int_path_active(const vnsgpu_ctx *ctx);
 /* Batches of >= 8192 candidates are evaluated in chain-length order (a device-side counting sort of the
  * descriptors; results still land at the caller's indices).  enable = 0 keeps the caller's order. */
 vnsgpu_status vnsgpu_set_batch_sort(vnsgpu_ctx *ctx, int enable);
+/* Integer tables, batches of >= 16384: the min-plus product of every run of consecutive path layers is
+ * built once per call and shared by all candidates (exactly associative on integers: bit-identical
+ * lengths); a MOVE / EXCHANGE chain of `span` blocks then costs at most 5.  enable = 0: block by block. */
+vnsgpu_status vnsgpu_set_segment_cache(vnsgpu_ctx *ctx, int enable);
+/* vnsgpu_local_search keeps the whole search state in one SM's shared memory when it fits (clusters <=
+ * 510, samples per cluster <= 32); enable = 0 forces the global-memory chain (tests run both). */
+vnsgpu_status vnsgpu_set_smem_chain(vnsgpu_ctx *ctx, int enable);
 
 /* ---- instance + distance table: replaces VnsSopPath::setSamplesDistances (vns_sop_path.cpp:38-48)
  *      fed by SOPLoader::getSOPFromNodes / getSOPFromWeightMatrix / getOP / getOPN ---------------- */

@@ -127,13 +127,26 @@ def test_greedy_insertion(name, golden, eng_cache):
     assert p.getPathLength() == g["greedy"]["length"] and p.getReward() == g["greedy"]["reward"]
 
 
+@pytest.mark.parametrize("mode", ["smem-int", "smem-double", "global"])
 @pytest.mark.parametrize("name", ALL)
-def test_shake_and_local_search_sequence(name, golden, eng_cache):
+def test_shake_and_local_search_sequence(name, mode, golden, eng_cache):
     """pathInsert/pathExchange + insertRandom/exchangeRandom with seed 7: the device chain must
-    walk the reference's exact state sequence and leave the RNG at the same position."""
+    walk the reference's exact state sequence and leave the RNG at the same position.  Three
+    implementations: shared-memory chain in exact int32 and in double arithmetic, global-memory chain."""
     from vns_sop_b200 import engine
     e, sf, pb = eng_cache(name)
     g, a = golden[name], load_arrays(name)
+    e.set_smem_chain(mode != "global")
+    e.set_int_path(mode != "smem-double")
+    try:
+        _run_sequence(e, pb, g, a)
+    finally:
+        e.set_smem_chain(True)
+        e.set_int_path(True)
+
+
+def _run_sequence(e, pb, g, a):
+    from vns_sop_b200 import engine
     p = e.path(a["greedy_vns"], g["greedy"]["T"])
     rng = engine.seeded_rng(7)
     for i, st in enumerate(g["sequence"]):
@@ -214,12 +227,17 @@ def test_eval_batch_both_arithmetic_paths_vs_oracle(name, int_path, golden, eng_
             assert (ln[~bad] == oln[~bad]).all() and (lb[~bad] == olb[~bad]).all()
             ok = np.nonzero(((fl & 2) != 0) & ((fl & 4) == 0))[0]
             assert first == (int(ok[0]) if len(ok) else -1)
-            e.set_batch_sort(False)
-            ln2, lb2, fl2, first2 = pg.eval_batch(big)
-            assert (ln2[~bad] == ln[~bad]).all() and (lb2[~bad] == lb[~bad]).all() and (fl2 == fl).all() and first2 == first
+            # (the integer path has just used the exact segment products: batch >= 16384)
+            for sort, seg in ((False, True), (True, False), (False, False)):
+                e.set_batch_sort(sort)
+                e.set_segment_cache(seg)
+                ln2, lb2, fl2, first2 = pg.eval_batch(big)
+                assert (ln2[~bad] == ln[~bad]).all() and (lb2[~bad] == lb[~bad]).all() and (fl2 == fl).all()
+                assert first2 == first
     finally:
         e.set_int_path(True)
         e.set_batch_sort(True)
+        e.set_segment_cache(True)
 
 
 @pytest.mark.parametrize("S", [4, 8, 12])

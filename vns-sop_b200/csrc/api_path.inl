@@ -193,9 +193,28 @@ static int eval_grid(const vnsgpu_ctx *ctx, int64_t n)
 // one evaluation of n candidates on `st`; idx0 = index of cands[0] in the caller's batch (first-accept
 // key); slot = which of the VNS_PIPE_EVENTS sort-scratch regions to use (chunks in flight concurrently)
 #define VNS_SORT_MIN 8192
+#define VNS_SEG_MIN 16384
+// integer tables: build the segment products of the path's current state (exact, see eval.cuh SegCache)
+static bool seg_wanted(const vnsgpu_ctx *ctx, int64_t n)
+{
+   return ctx->use_seg && vnsgpu_int_path_active(ctx) && ctx->seg_ok && n >= VNS_SEG_MIN;
+}
+
+static vnsgpu_status prepare_seg(vnsgpu_ctx *ctx, int path, cudaStream_t st)
+{
+   const InstDev &I = ctx->I;
+   const int R = I.rows + 3;
+   if (!ctx->d_segmeta) CK(cudaMalloc(&ctx->d_segmeta, sizeof(int) * 3 * R));
+   k_seg_offsets<<<1, 256, sizeof(int) * 2 * R, st>>>(I, ctx->paths[path].d, ctx->d_segmeta);
+   LAUNCHED(ctx);
+   k_seg_build<<<I.rows, 128, 0, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta);
+   LAUNCHED(ctx);
+   return VNSGPU_OK;
+}
+
 static vnsgpu_status launch_eval(vnsgpu_ctx *ctx, int path, int64_t n, int64_t idx0, const vnsgpu_cand *d_cands, double budget,
                                  int skip, double *d_len, double *d_lb, uint8_t *d_flags, unsigned long long *d_first, cudaStream_t st,
-                                 int slot, int64_t perm_off)
+                                 int slot, int64_t perm_off, bool useseg)
 {
    const InstDev &I = ctx->I;
    const PathDev &P = ctx->paths[path].d;
@@ -213,11 +232,11 @@ static vnsgpu_status launch_eval(vnsgpu_ctx *ctx, int path, int64_t n, int64_t i
          unsigned *hist = ctx->d_hist + (size_t)slot * 2 * nb, *cursor = hist + nb, *perm = ctx->d_perm + perm_off;
          const int sgrid = (int)std::min<int64_t>((n + 2047) / 2048, (int64_t)ctx->num_sms * 8);
          CK(cudaMemsetAsync(hist, 0, sizeof(unsigned) * nb, st));
-         k_sort_hist<<<sgrid, 256, sizeof(unsigned) * nb, st>>>(I, P, n, d_cands, nb, hist);
+         k_sort_hist<<<sgrid, 256, sizeof(unsigned) * nb, st>>>(I, P, n, d_cands, nb, hist, useseg);
          LAUNCHED(ctx);
          k_sort_scan<<<1, 32, 0, st>>>(nb, hist, cursor);
          LAUNCHED(ctx);
-         k_sort_scatter<<<sgrid, 256, sizeof(unsigned) * 2 * nb, st>>>(I, P, n, d_cands, nb, cursor, perm);
+         k_sort_scatter<<<sgrid, 256, sizeof(unsigned) * 2 * nb, st>>>(I, P, n, d_cands, nb, cursor, perm, useseg);
          LAUNCHED(ctx);
          d_perm = perm;
       }
@@ -226,20 +245,28 @@ static vnsgpu_status launch_eval(vnsgpu_ctx *ctx, int path, int64_t n, int64_t i
       const int G = ctx->group_lanes, NR = (I.mp + G - 1) / G <= 1 ? 1 : ((I.mp + G - 1) / G <= 2 ? 2 : 4);
       const int64_t per_cta = (VNS_EVAL_THREADS / 32) * (32 / G);
       const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n + per_cta - 1) / per_cta, (int64_t)ctx->num_sms * 8));
-#define VNS_LAUNCH_EVAL(V, GG, RR, TAB)                                                                              \
-   k_eval_groups<V, GG, RR><<<grid, VNS_EVAL_THREADS, smem, st>>>(I, TAB, P, n, idx0, d_cands, d_perm, budget, skip, d_len, d_lb, \
-                                                                   d_flags, d_first)
-#define VNS_LAUNCH_EVAL_V(V, TAB)                                                                                    \
+      SegCache seg{};
+      if (useseg) {
+         const int R = I.rows + 3;
+         seg.cum = ctx->d_segmeta; seg.pd = ctx->d_segmeta + R;
+         seg.rowoff = reinterpret_cast<const unsigned *>(ctx->d_segmeta + 2 * R);
+      }
+#define VNS_LAUNCH_EVAL(V, GG, RR, SS, TAB)                                                                          \
+   k_eval_groups<V, GG, RR, SS><<<grid, VNS_EVAL_THREADS, smem, st>>>(I, TAB, P, seg, n, idx0, d_cands, d_perm, budget, skip, d_len, \
+                                                                       d_lb, d_flags, d_first)
+#define VNS_LAUNCH_EVAL_V(V, SS, TAB)                                                                                \
    do {                                                                                                              \
-      if (G == 8 && NR == 1) VNS_LAUNCH_EVAL(V, 8, 1, TAB);                                                           \
-      else if (G == 8 && NR == 2) VNS_LAUNCH_EVAL(V, 8, 2, TAB);                                                      \
-      else if (G == 8) VNS_LAUNCH_EVAL(V, 8, 4, TAB);                                                                 \
-      else if (G == 16 && NR == 1) VNS_LAUNCH_EVAL(V, 16, 1, TAB);                                                    \
-      else if (G == 16) VNS_LAUNCH_EVAL(V, 16, 2, TAB);                                                               \
-      else VNS_LAUNCH_EVAL(V, 32, 1, TAB);                                                                            \
+      if (G == 8 && NR == 1) VNS_LAUNCH_EVAL(V, 8, 1, SS, TAB);                                                       \
+      else if (G == 8 && NR == 2) VNS_LAUNCH_EVAL(V, 8, 2, SS, TAB);                                                  \
+      else if (G == 8) VNS_LAUNCH_EVAL(V, 8, 4, SS, TAB);                                                             \
+      else if (G == 16 && NR == 1) VNS_LAUNCH_EVAL(V, 16, 1, SS, TAB);                                                \
+      else if (G == 16) VNS_LAUNCH_EVAL(V, 16, 2, SS, TAB);                                                           \
+      else VNS_LAUNCH_EVAL(V, 32, 1, SS, TAB);                                                                        \
    } while (0)
-      if (ctx->use_int && ctx->d_D32) VNS_LAUNCH_EVAL_V(int, ctx->d_D32);
-      else VNS_LAUNCH_EVAL_V(double, ctx->d_D);
+      if (ctx->use_int && ctx->d_D32) {
+         if (useseg) VNS_LAUNCH_EVAL_V(int, true, ctx->d_D32);
+         else VNS_LAUNCH_EVAL_V(int, false, ctx->d_D32);
+      } else VNS_LAUNCH_EVAL_V(double, false, ctx->d_D);
 #undef VNS_LAUNCH_EVAL_V
 #undef VNS_LAUNCH_EVAL
    } else {
@@ -257,7 +284,13 @@ vnsgpu_status vnsgpu_eval_batch_dev(vnsgpu_ctx *ctx, int path, int64_t n, const 
    if (n <= 0) return VNSGPU_OK;
    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
    if (d_first_accept) CK(cudaMemsetAsync(d_first_accept, 0xFF, sizeof(long long), st));   // -1 = none
-   return launch_eval(ctx, path, n, 0, d_cands, budget, skip, d_len, d_lb, d_flags, (unsigned long long *)d_first_accept, st, 0, 0);
+   const bool useseg = seg_wanted(ctx, n);
+   if (useseg) {
+      vnsgpu_status s = prepare_seg(ctx, path, st);
+      if (s) return s;
+   }
+   return launch_eval(ctx, path, n, 0, d_cands, budget, skip, d_len, d_lb, d_flags, (unsigned long long *)d_first_accept, st, 0, 0,
+                      useseg);
 }
 
 // Host buffers.  The batch is cut into chunks that flow through three streams - H2D of chunk c+1, the
@@ -291,6 +324,11 @@ vnsgpu_status vnsgpu_eval_batch(vnsgpu_ctx *ctx, int path, int64_t n, const vnsg
    int64_t chunk = std::max<int64_t>(65536, (n + VNS_PIPE_EVENTS - 1) / VNS_PIPE_EVENTS);
    chunk = (chunk + 255) & ~(int64_t)255;
    cudaStream_t sk = ctx->stream;
+   const bool useseg = seg_wanted(ctx, n);
+   if (useseg) {
+      s = prepare_seg(ctx, path, sk);
+      if (s) return s;
+   }
    CK(cudaMemsetAsync(ctx->d_first, 0xFF, sizeof(long long), sk));
    CK(cudaEventRecord(ctx->ev_start, sk));          // order behind whatever the caller queued before
    CK(cudaStreamWaitEvent(ctx->s_in, ctx->ev_start, 0));
@@ -302,7 +340,7 @@ vnsgpu_status vnsgpu_eval_batch(vnsgpu_ctx *ctx, int path, int64_t n, const vnsg
       CK(cudaEventRecord(ctx->ev_in[c], ctx->s_in));
       CK(cudaStreamWaitEvent(sk, ctx->ev_in[c], 0));
       s = launch_eval(ctx, path, cn, lo, d_c + lo, budget, skip, len ? d_len + lo : nullptr, lb ? d_lb + lo : nullptr,
-                      flags ? d_fl + lo : nullptr, (unsigned long long *)ctx->d_first, sk, c, lo);
+                      flags ? d_fl + lo : nullptr, (unsigned long long *)ctx->d_first, sk, c, lo, useseg);
       if (s) return s;
       CK(cudaEventRecord(ctx->ev_k[c], sk));
       CK(cudaStreamWaitEvent(ctx->s_out, ctx->ev_k[c], 0));

@@ -1,5 +1,49 @@
 // C ABI: RNG replay + neighbourhood drivers (included by vnsgpu.cu)
 
+// insertRandom / exchangeRandom: the shared-memory chain (chain.cuh) when the state fits one SM's shared
+// memory, else the global-memory chain of search.cuh
+template <typename V>
+static bool chain_fits(const vnsgpu_ctx *ctx, size_t *bytes)
+{
+   *bytes = chain_smem_bytes<V>(ctx->I.C, ctx->I.mp);
+   return ctx->use_smem_chain && group_kernel_ok(ctx) && ctx->I.mp <= 32 && ctx->I.C + 2 <= VNS_CH_THREADS &&
+          *bytes + sizeof(ChainCtl) + 1024 <= (size_t)ctx->max_smem;
+}
+
+template <typename V, int G, int NR>
+static vnsgpu_status launch_chain(vnsgpu_ctx *ctx, const V *tab, int path, int kind, int num_changes, double budget, int skip, size_t smem)
+{
+   CK(cudaFuncSetAttribute(k_chain_ls<V, G, NR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+   k_chain_ls<V, G, NR><<<1, VNS_CH_THREADS, smem, ctx->stream>>>(ctx->I, tab, ctx->paths[path].d, kind, num_changes, budget, skip,
+                                                                    ctx->d_rng, ctx->d_stats);
+   LAUNCHED(ctx);
+   return VNSGPU_OK;
+}
+
+template <typename V>
+static vnsgpu_status launch_chain_v(vnsgpu_ctx *ctx, const V *tab, int path, int kind, int num_changes, double budget, int skip, size_t smem)
+{
+   const int G = ctx->group_lanes, nr = (ctx->I.mp + G - 1) / G;
+   if (G == 8 && nr <= 1) return launch_chain<V, 8, 1>(ctx, tab, path, kind, num_changes, budget, skip, smem);
+   if (G == 8 && nr <= 2) return launch_chain<V, 8, 2>(ctx, tab, path, kind, num_changes, budget, skip, smem);
+   if (G == 8) return launch_chain<V, 8, 4>(ctx, tab, path, kind, num_changes, budget, skip, smem);
+   if (G == 16 && nr <= 1) return launch_chain<V, 16, 1>(ctx, tab, path, kind, num_changes, budget, skip, smem);
+   if (G == 16) return launch_chain<V, 16, 2>(ctx, tab, path, kind, num_changes, budget, skip, smem);
+   return launch_chain<V, 32, 1>(ctx, tab, path, kind, num_changes, budget, skip, smem);
+}
+
+static vnsgpu_status launch_local_search(vnsgpu_ctx *ctx, int path, int kind, int num_changes, double budget, int skip)
+{
+   size_t smem = 0;
+   if (vnsgpu_int_path_active(ctx) && chain_fits<int>(ctx, &smem))
+      return launch_chain_v<int>(ctx, ctx->d_D32, path, kind, num_changes, budget, skip, smem);
+   if (chain_fits<double>(ctx, &smem)) return launch_chain_v<double>(ctx, ctx->d_D, path, kind, num_changes, budget, skip, smem);
+   k_local_search<<<1, VNS_CHAIN_THREADS, chain_smem(ctx), ctx->stream>>>(ctx->I, ctx->paths[path].d, kind, num_changes, budget, skip,
+                                                                          ctx->d_rng, ctx->d_stats);
+   LAUNCHED(ctx);
+   return VNSGPU_OK;
+}
+
 extern "C" {
 
 void vnsgpu_rng_seed(vnsgpu_rng *rng, uint32_t seed) { rng_seed_host(*reinterpret_cast<RngState *>(rng), seed); }
@@ -40,9 +84,8 @@ vnsgpu_status vnsgpu_local_search(vnsgpu_ctx *ctx, int path, int kind, int num_c
    if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
    if (kind != 1 && kind != 2) return fail(ctx, VNSGPU_E_RANGE, "kind must be 1 (insert) or 2 (exchange)");
    CK(cudaMemcpyAsync(ctx->d_rng, rng, sizeof(RngState), cudaMemcpyHostToDevice, ctx->stream));
-   k_local_search<<<1, VNS_CHAIN_THREADS, chain_smem(ctx), ctx->stream>>>(ctx->I, ctx->paths[path].d, kind, num_changes, budget, skip,
-                                                                          ctx->d_rng, ctx->d_stats);
-   LAUNCHED(ctx);
+   vnsgpu_status ls = launch_local_search(ctx, path, kind, num_changes, budget, skip);
+   if (ls) return ls;
    LsStats st;
    CK(cudaMemcpyAsync(rng, ctx->d_rng, sizeof(RngState), cudaMemcpyDeviceToHost, ctx->stream));
    CK(cudaMemcpyAsync(&st, ctx->d_stats, sizeof(st), cudaMemcpyDeviceToHost, ctx->stream));

@@ -79,7 +79,10 @@ __device__ __forceinline__ CandCode decode_cand(int T, int C, int op, int a, int
 #define VNS_EVAL_THREADS 256
 
 // shared memory: layer -> cluster map of the path (T+2 ints, padded to even) + per-cluster {offset, size}
-__host__ __device__ inline size_t eval_smem_bytes(int T, int C) { return sizeof(int) * (size_t)(((T + 2 + 1) & ~1) + 2 * C); }
+__host__ __device__ inline size_t eval_smem_bytes(int T, int C)
+{
+   return sizeof(int) * (size_t)(((T + 2 + 1) & ~1) + 2 * C + 3 * (T + 3));   // + cum, pd, rowoff of the segment cache
+}
 
 // layer of chain node k (see CandCode)
 __device__ __forceinline__ int cand_layer(const CandCode &cc, int k)
@@ -92,14 +95,196 @@ __device__ __forceinline__ int cand_layer(const CandCode &cc, int k)
    return l;
 }
 
+// One lock-step evaluation of the warp's 32/G candidates (cc = this lane's group's candidate, K = 0:
+// idle).  rowF(l, j) / rowB(l, j) return F[l][j] / B[l][j] as V.  Must be called by all 32 lanes.
+// Out: fin = tryTo*(...) of the group's candidate (valid in every lane of the group), between =
+// dist_between of its lower bound.
+//
+// Per round of G edges every lane first DESCRIBES one edge of its group's chain (block offset, block
+// shape, dmin, and - by xor-shuffles across the groups - the warp-wide loop bounds); the edge loop
+// then gets everything it needs from two broadcasts per edge.
+struct EdgeDesc {
+   unsigned rb;   // element offset of the block (row-major ma x mb) from Dv
+   int ma, mb;
+   double dm;     // its contribution to dist_between of the lower bound
+};
+
+// chain = K blocks; edge(k), 1 <= k <= K, describes block k; the chain starts from the vector
+// row0(j), j < m0, and closes against rowK(j), j < mK; tr = closing association (d + B) + v;
+// ps, pe = the pair of edges the reference pre-sums in its lower bound (-1: none).
+template <typename V, int G, int NR, typename Edge, typename Row0, typename RowK>
+__device__ __forceinline__ void groups_eval(const V *__restrict__ Dv, int K, int tr, int ps, int pe, int m0, int mK, int gl, Edge edge,
+                                            Row0 row0, RowK rowK, V &fin_out, double &between_out)
+{
+   typedef ValOps<V> Ops;
+   constexpr bool EXACT = sizeof(V) == 4;   // integer tables: the lower bound's summation order is free
+   constexpr unsigned FULL = 0xffffffffu;
+   const V INF = Ops::inf();
+   // chain start: v = F[s0], closing row B[sK]
+   V v[NR], breg[NR];
+#pragma unroll
+   for (int r = 0; r < NR; ++r) {
+      const int j = gl + r * G;
+      v[r] = j < m0 ? row0(j) : INF;
+      breg[r] = j < mK ? rowK(j) : INF;
+   }
+   double between = 0.0, pend = 0.0;   // ordered accumulation (double tables)
+   double lane_dm = 0.0;               // per-lane partial sum (integer tables)
+   V fin = INF;
+   const int Kmax = __reduce_max_sync(FULL, K);
+   for (int e0 = 0; e0 < Kmax; e0 += G) {
+      // ---- describe edge k = e0 + gl + 1 ------------------------------------------------------
+      unsigned e_rb = 0, e_w;
+      double e_dm = 0.0;
+      {
+         const int k = e0 + gl + 1;
+         int ma = 1, mb = 1, trn = 0;
+         if (k <= K) {
+            const EdgeDesc ed = edge(k);
+            e_rb = ed.rb; ma = ed.ma; mb = ed.mb; e_dm = ed.dm;
+            trn = (k == K) & tr;
+         }
+         int tmax = trn ? mb : ma, nvmax = trn ? ma : mb;       // warp-wide loop bounds of this edge slot
+#pragma unroll
+         for (int s = G; s < 32; s <<= 1) {
+            tmax = max(tmax, __shfl_xor_sync(FULL, tmax, s));
+            nvmax = max(nvmax, __shfl_xor_sync(FULL, nvmax, s));
+         }
+         e_w = (unsigned)ma | ((unsigned)mb << 8) | ((unsigned)(tmax | (trn << 6)) << 16) | ((unsigned)nvmax << 24);
+         if (EXACT) lane_dm += e_dm;
+      }
+      const int kend = min(G, Kmax - e0);
+      for (int kk = 0; kk < kend; ++kk) {
+         const int k = e0 + kk + 1;
+         const unsigned rb = __shfl_sync(FULL, e_rb, kk, G);
+         const unsigned w = __shfl_sync(FULL, e_w, kk, G);
+         const int ma = w & 0xff, mb = (w >> 8) & 0xff, tmaxAll = (w >> 16) & 0x3f, nvmax = w >> 24;
+         const bool trn = (w >> 22) & 1;
+         if (!EXACT) {   // lower bound in the source order of tryTo*LowerBound (path.cuh plan_lower_bound)
+            const double dm = __shfl_sync(FULL, e_dm, kk, G);
+            const bool is_ps = k == ps, is_pe = k == pe;
+            const double add = is_pe ? pend + dm : dm;
+            pend = is_ps ? dm : pend;
+            between = (k <= K && !is_ps) ? between + add : between;
+         }
+         // Loads are never predicated: idle groups, exhausted groups and lanes beyond the block width
+         // re-read a valid entry of their block and pair it with a value that cannot win (min is
+         // idempotent), so the loop body is branch-free and the loads pipeline.
+         const int trip = trn ? mb : ma, nvalid = trn ? ma : mb;
+         const int sl = trn ? 1 : mb, sn = trn ? mb : 1;
+         V acc[NR];
+#pragma unroll
+         for (int rd = 0; rd < NR; ++rd) {
+            acc[rd] = INF;
+            if (rd == 0 || nvmax > rd * G) {                 // warp-uniform
+               const unsigned cbase = rb + (unsigned)(min(gl + rd * G, nvalid - 1) * sn);
+#pragma unroll
+               for (int rs = 0; rs < NR; ++rs) {
+                  if (rs == 0 || tmaxAll > rs * G) {         // warp-uniform
+                     const int tlim = max(min(trip - rs * G, G) - 1, 0);
+                     const unsigned sb = cbase + (unsigned)(min(rs * G, trip - 1) * sl);
+                     const int tm = min(tmaxAll - rs * G, G);
+                     const V opnd = trn ? breg[rs] : v[rs];
+#pragma unroll 2
+                     for (int t = 0; t < tm; ++t) {
+                        const int tt = min(t, tlim);
+                        const V x = __shfl_sync(FULL, opnd, tt, G);
+                        const V dd = __ldg(Dv + (sb + (unsigned)(tt * sl)));
+                        acc[rd] = Ops::add_min(acc[rd], x, dd);
+                     }
+                  }
+               }
+            }
+         }
+         const bool isK = k == K, mid = k < K;
+#pragma unroll
+         for (int r = 0; r < NR; ++r) {
+            const bool lv = gl + r * G < nvalid;
+            const V f = trn ? acc[r] + v[r] : acc[r] + breg[r];
+            fin = (isK && lv) ? Ops::vmin(fin, f) : fin;
+            v[r] = mid ? (lv ? acc[r] : INF) : v[r];
+         }
+      }
+   }
+   if (EXACT) {
+#pragma unroll
+      for (int s = G / 2; s > 0; s >>= 1) lane_dm += __shfl_xor_sync(FULL, lane_dm, s, G);
+      between = lane_dm;
+   }
+#pragma unroll
+   for (int s = G / 2; s > 0; s >>= 1) fin = Ops::vmin(fin, __shfl_xor_sync(FULL, fin, s, G));
+   fin_out = fin;
+   between_out = between;
+}
+
+// ---- exact segment products (integer tables only) -------------------------------------------------
+// MOVE and EXCHANGE chains contain a run of consecutive path layers a -> a+1 -> ... -> b.  Its min-plus
+// product M(a,b) = D(a,a+1) (x) ... (x) D(b-1,b) does not depend on the candidate, and with integer
+// entries min-plus products are exactly associative, so one pre-pass per path state builds every
+// M(a,b), b >= a+2 (k_seg_build) and a chain of `span` blocks shrinks to at most 5 blocks with
+// bit-identical results.  (The double path never uses this: floating-point sums do not reassociate.)
+// M(a,b) is row-major m_a x m_b at element offset rowoff[a] + m_a * (cum[b] - cum[a+2]) from the table.
+struct SegCache {
+   const int *cum;          // cum[l] = samples in layers < l, l = 0 .. S+1
+   const unsigned *rowoff;  // per layer a
+   const int *pd;           // pd[l] = sum_{l' < l} dmin(layer l', layer l'+1): dist_between of a run
+};
+
+struct SegCode {
+   int K, n0, n1, n2, n3, n4, n5, kseg, foreign, tr, nolb;
+};
+
+__device__ __forceinline__ SegCode decode_cand_seg(int T, int C, int op, int a, int b)
+{
+   SegCode c;
+   c.K = 0; c.n0 = c.n1 = c.n2 = c.n3 = c.n4 = c.n5 = 0; c.kseg = -1; c.foreign = 0; c.tr = 0; c.nolb = 0;
+   if (op == VNSGPU_OP_ADD) {
+      if (b < 0 || b > T || a < 0 || a >= C) return c;
+      c.K = 2; c.n0 = b; c.n1 = -1; c.n2 = b + 1; c.foreign = a; c.tr = 1;
+   } else if (op == VNSGPU_OP_REPLACE) {
+      if (b < 0 || b >= T || a < 0 || a >= C) return c;
+      c.K = 2; c.n0 = b; c.n1 = -1; c.n2 = b + 2; c.foreign = a; c.tr = 1;
+   } else if (op == VNSGPU_OP_REMOVE) {
+      if (a < 0 || a >= T) return c;
+      c.K = 1; c.n0 = a; c.n1 = a + 2; c.tr = 1; c.nolb = 1;
+   } else if (op == VNSGPU_OP_MOVE) {
+      if (a >= T || a < 0 || b > T || b < 0 || abs(b - a) < 2) return c;
+      const int i = min(a, b) + 1, j = max(a, b) + 1;
+      if (b > a) {   // up: i-1, [i+1 .. j-1], i, j
+         if (j - i == 2) { c.K = 3; c.n0 = i - 1; c.n1 = i + 1; c.n2 = i; c.n3 = j; }
+         else { c.K = 4; c.n0 = i - 1; c.n1 = i + 1; c.n2 = j - 1; c.n3 = i; c.n4 = j; c.kseg = 2; }
+      } else {       // down: i-1, j, [i .. j-1], j+1
+         c.K = 4; c.n0 = i - 1; c.n1 = j; c.n2 = i; c.n3 = j - 1; c.n4 = j + 1; c.kseg = 3;
+      }
+   } else if (op == VNSGPU_OP_EXCHANGE) {   // i, j, [i+2 .. j-1], i+1, j+1
+      if (a >= T || a < 0 || b >= T || b < 0 || abs(a - b) < 2) return c;
+      const int i = min(a, b), j = max(a, b) + 1;
+      if (j - i == 3) { c.K = 4; c.n0 = i; c.n1 = j; c.n2 = i + 2; c.n3 = i + 1; c.n4 = j + 1; }
+      else { c.K = 5; c.n0 = i; c.n1 = j; c.n2 = i + 2; c.n3 = j - 1; c.n4 = i + 1; c.n5 = j + 1; c.kseg = 3; }
+   }
+   return c;
+}
+
+__device__ __forceinline__ int seg_node(const SegCode &c, int k)
+{
+   int l = c.n0;
+   l = k == 1 ? c.n1 : l;
+   l = k == 2 ? c.n2 : l;
+   l = k == 3 ? c.n3 : l;
+   l = k == 4 ? c.n4 : l;
+   l = k == 5 ? c.n5 : l;
+   return l;
+}
+
 // G lanes x NR registers hold one vector (sample j lives in lane j % G, register j / G); G * NR >= mp.
 // perm (may be null): evaluation order = candidates sorted by chain length, so the 32/G candidates a
 // warp advances in lock step have (almost always) the same number of blocks.
-template <typename V, int G, int NR>
+// SEG: chains compressed with the segment products (seg valid; V = int only).
+template <typename V, int G, int NR, bool SEG>
 __global__ void __launch_bounds__(VNS_EVAL_THREADS)
-k_eval_groups(InstDev I, const V *__restrict__ Dv, PathDev P, long long n, long long idx0, const vnsgpu_cand *__restrict__ cands,
-              const unsigned *__restrict__ perm, double budget, int skipflag, double *__restrict__ len, double *__restrict__ lb,
-              uint8_t *__restrict__ flags, unsigned long long *d_first)
+k_eval_groups(InstDev I, const V *__restrict__ Dv, PathDev P, SegCache seg, long long n, long long idx0,
+              const vnsgpu_cand *__restrict__ cands, const unsigned *__restrict__ perm, double budget, int skipflag,
+              double *__restrict__ len, double *__restrict__ lb, uint8_t *__restrict__ flags, unsigned long long *d_first)
 {
    typedef ValOps<V> Ops;
    extern __shared__ int smem_i[];
@@ -108,10 +293,15 @@ k_eval_groups(InstDev I, const V *__restrict__ Dv, PathDev P, long long n, long 
    int2 *cinfo = reinterpret_cast<int2 *>(smem_i + ((T + 2 + 1) & ~1));
    for (int l = threadIdx.x; l < T + 2; l += blockDim.x) lcl[l] = layer_cluster(I, P.tg, T, l);
    for (int c = threadIdx.x; c < I.C; c += blockDim.x) cinfo[c] = make_int2(I.off[c], I.m[c]);
+   int *s_cum = reinterpret_cast<int *>(cinfo + I.C), *s_pd = s_cum + (T + 3);
+   unsigned *s_rowoff = reinterpret_cast<unsigned *>(s_pd + (T + 2));
+   if (SEG) {
+      for (int l = threadIdx.x; l < T + 3; l += blockDim.x) s_cum[l] = seg.cum[l];
+      for (int l = threadIdx.x; l < T + 2; l += blockDim.x) { s_pd[l] = seg.pd[l]; s_rowoff[l] = seg.rowoff[l]; }
+   }
    __syncthreads();
 
    constexpr int NG = 32 / G;
-   constexpr unsigned FULL = 0xffffffffu;
    const int lane = threadIdx.x & 31, gl = lane % G, g = lane / G;
    const double L = P.hd[HD_LEN];
    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
@@ -125,101 +315,45 @@ k_eval_groups(InstDev I, const V *__restrict__ Dv, PathDev P, long long n, long 
       if (perm && slot < n) kidx = __ldg(perm + slot);
       int4 cd = make_int4(-1, 0, 0, -1);
       if (slot < n) cd = __ldg(reinterpret_cast<const int4 *>(cands) + kidx);
-      const CandCode cc = decode_cand(T, I.C, cd.x, cd.y, cd.z);
-      const int K = cc.K;                         // 0: out of range -> flags BAD
-      // chain start: v = F[s0], closing row B[sK]
-      V v[NR], breg[NR];
-      {
-         const int m0 = K ? cinfo[lcl[cc.s0]].y : 0, mK = K ? cinfo[lcl[cc.sK]].y : 0;
-#pragma unroll
-         for (int r = 0; r < NR; ++r) {
-            const int j = gl + r * G;
-            v[r] = j < m0 ? (V)P.F[(size_t)cc.s0 * I.mp + j] : INF;
-            breg[r] = j < mK ? (V)P.B[(size_t)cc.sK * I.mp + j] : INF;
-         }
-      }
-      double between = 0.0, pend = 0.0;
-      V fin = INF;
-      const int Kmax = __reduce_max_sync(FULL, K);
-      for (int e0 = 0; e0 < Kmax; e0 += G) {
-         // lane gl describes edge k = e0 + gl + 1 of its group's chain: block offset, sizes, dmin
-         unsigned e_rb = 0, e_mm = 1 | (1 << 8);
-         double e_dm = 0.0;
-         {
-            const int k = e0 + gl + 1;
-            if (k <= K) {
+      int K, s0, sK, nolb;                        // K = 0: out of range -> flags BAD
+      V fin;
+      double between;
+      auto table_edge = [&](int ca, int cb) {
+         const int2 cia = cinfo[ca], cib = cinfo[cb];
+         EdgeDesc e;
+         e.rb = (unsigned)cia.x * (unsigned)I.N + (unsigned)cia.y * (unsigned)cib.x;
+         e.ma = cia.y; e.mb = cib.y;
+         e.dm = __ldg(I.dmin + (size_t)ca * I.C + cb);
+         return e;
+      };
+      if (SEG) {
+         const SegCode sc = decode_cand_seg(T, I.C, cd.x, cd.y, cd.z);
+         K = sc.K; s0 = sc.n0; sK = seg_node(sc, sc.K); nolb = sc.nolb;
+         const int m0 = K ? cinfo[lcl[s0]].y : 0, mK = K ? cinfo[lcl[sK]].y : 0;
+         groups_eval<V, G, NR>(Dv, K, sc.tr, -1, -1, m0, mK, gl,
+            [&](int k) {
+               const int la = seg_node(sc, k - 1), lb_ = seg_node(sc, k);
+               if (k == sc.kseg && lb_ > la + 1) {          // run of path layers la .. lb_: one product
+                  EdgeDesc e;
+                  e.ma = s_cum[la + 1] - s_cum[la]; e.mb = s_cum[lb_ + 1] - s_cum[lb_];
+                  e.rb = s_rowoff[la] + (unsigned)(e.ma * (s_cum[lb_] - s_cum[la + 2]));
+                  e.dm = (double)(s_pd[lb_] - s_pd[la]);
+                  return e;
+               }
+               return table_edge(la < 0 ? sc.foreign : lcl[la], lb_ < 0 ? sc.foreign : lcl[lb_]);
+            },
+            [&](int j) { return (V)P.F[(size_t)s0 * I.mp + j]; }, [&](int j) { return (V)P.B[(size_t)sK * I.mp + j]; }, fin, between);
+      } else {
+         const CandCode cc = decode_cand(T, I.C, cd.x, cd.y, cd.z);
+         K = cc.K; s0 = cc.s0; sK = cc.sK; nolb = cc.nolb;
+         const int m0 = K ? cinfo[lcl[s0]].y : 0, mK = K ? cinfo[lcl[sK]].y : 0;
+         groups_eval<V, G, NR>(Dv, K, cc.tr, cc.ps, cc.pe, m0, mK, gl,
+            [&](int k) {
                const int la = cand_layer(cc, k - 1), lb_ = cand_layer(cc, k);
-               const int ca = la < 0 ? cc.foreign : lcl[la], cb = lb_ < 0 ? cc.foreign : lcl[lb_];
-               const int2 cia = cinfo[ca], cib = cinfo[cb];
-               e_rb = (unsigned)cia.x * (unsigned)I.N + (unsigned)cia.y * (unsigned)cib.x;
-               e_mm = (unsigned)cia.y | ((unsigned)cib.y << 8);
-               e_dm = __ldg(I.dmin + (size_t)ca * I.C + cb);
-            }
-         }
-         const int kend = min(G, Kmax - e0);
-         for (int kk = 0; kk < kend; ++kk) {
-            const int k = e0 + kk + 1;
-            const bool act = k <= K;
-            const unsigned rb = __shfl_sync(FULL, e_rb, kk, G);
-            const unsigned mm = __shfl_sync(FULL, e_mm, kk, G);
-            const double dm = __shfl_sync(FULL, e_dm, kk, G);
-            const int ma = mm & 0xff, mb = mm >> 8;
-            // lower bound: dist_between in the source order of tryTo*LowerBound (path.cuh plan_lower_bound)
-            {
-               const bool is_ps = k == cc.ps, is_pe = k == cc.pe;
-               const double add = is_pe ? pend + dm : dm;
-               pend = is_ps ? dm : pend;
-               between = (act && !is_ps) ? between + add : between;
-            }
-            const bool trn = k == K && cc.tr;
-            // Loads are never predicated: idle groups, exhausted groups and lanes beyond the block width
-            // re-read a valid entry of their block and pair it with a value that cannot win (min is
-            // idempotent), so the loop body is branch-free and the loads pipeline.
-            const int trip = trn ? mb : ma, nvalid = trn ? ma : mb;
-            const int sl = trn ? 1 : mb, sn = trn ? mb : 1;
-            const int nvmax = NR > 1 ? __reduce_max_sync(FULL, nvalid) : 0;
-            unsigned cbase[NR];
-            V acc[NR];
-#pragma unroll
-            for (int r = 0; r < NR; ++r) {
-               cbase[r] = rb + (unsigned)(min(gl + r * G, nvalid - 1) * sn);
-               acc[r] = INF;
-            }
-#pragma unroll
-            for (int rs = 0; rs < NR; ++rs) {
-               const int trip_r = min(max(trip - rs * G, 0), G);
-               const int tmax = __reduce_max_sync(FULL, trip_r);
-               const V opnd = trn ? breg[rs] : v[rs];
-#pragma unroll 2
-               for (int t = 0; t < tmax; ++t) {
-                  const int tt = max(min(t, trip_r - 1), 0);
-                  const V x = __shfl_sync(FULL, opnd, tt, G);
-                  const unsigned so = (unsigned)(min(rs * G + tt, trip - 1) * sl);
-#pragma unroll
-                  for (int rd = 0; rd < NR; ++rd) {
-                     if (rd == 0 || nvmax > rd * G) {           // warp-uniform
-                        const V dd = __ldg(Dv + (cbase[rd] + so));
-                        acc[rd] = Ops::add_min(acc[rd], x, dd);
-                     }
-                  }
-               }
-            }
-            if (act) {
-               if (k == K) {
-#pragma unroll
-                  for (int r = 0; r < NR; ++r) {
-                     const V f = trn ? acc[r] + v[r] : acc[r] + breg[r];
-                     if (gl + r * G < nvalid) fin = Ops::vmin(fin, f);
-                  }
-               } else {
-#pragma unroll
-                  for (int r = 0; r < NR; ++r) v[r] = gl + r * G < nvalid ? acc[r] : INF;
-               }
-            }
-         }
+               return table_edge(la < 0 ? cc.foreign : lcl[la], lb_ < 0 ? cc.foreign : lcl[lb_]);
+            },
+            [&](int j) { return (V)P.F[(size_t)s0 * I.mp + j]; }, [&](int j) { return (V)P.B[(size_t)sK * I.mp + j]; }, fin, between);
       }
-#pragma unroll
-      for (int s = G / 2; s > 0; s >>= 1) fin = Ops::vmin(fin, __shfl_xor_sync(FULL, fin, s, G));
       if (gl == 0 && slot < n) {
          double l, bound;
          unsigned f = 0;
@@ -227,7 +361,7 @@ k_eval_groups(InstDev I, const V *__restrict__ Dv, PathDev P, long long n, long 
             l = CUDART_NAN; bound = CUDART_NAN; f = VNSGPU_F_BAD;
          } else {
             l = (double)fin;
-            bound = cc.nolb ? l : P.minF[cc.s0] + between + P.minB[cc.sK];
+            bound = nolb ? l : P.minF[s0] + between + P.minB[sK];
             double dR = 0.0, lm = l;                               // lm = lengthAfterMove of the drivers
             if (cd.x == VNSGPU_OP_ADD) {                           // insertRandom, outside -> path
                dR = cd.w >= 0 ? __ldg(I.reward + cd.w) : 0.0;      // vns_sop_solver.cpp:581
@@ -237,7 +371,7 @@ k_eval_groups(InstDev I, const V *__restrict__ Dv, PathDev P, long long n, long 
             }
             if (lm <= budget) f |= VNSGPU_F_FEASIBLE;
             if (lm <= budget && (dR > 0 || (L - lm) > VNS_MIN_CHANGE_EPS)) f |= VNSGPU_F_ACCEPT;          // :619,:805
-            if (bound > budget && !cc.nolb) f |= VNSGPU_F_LB_SKIP;                                      // :539,...
+            if (bound > budget && !nolb) f |= VNSGPU_F_LB_SKIP;                                      // :539,...
          }
          if (len) len[kidx] = l;
          if (lb) lb[kidx] = bound;
@@ -255,10 +389,15 @@ __global__ void __launch_bounds__(256) k_table_to_int(const double *__restrict__
    for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < n; q += (long long)gridDim.x * blockDim.x) Di[q] = (int)D[q];
 }
 
+__device__ __forceinline__ int sort_key(int T, int C, const int4 &cd, int useseg)
+{
+   return useseg ? decode_cand_seg(T, C, cd.x, cd.y, cd.z).K : decode_cand(T, C, cd.x, cd.y, cd.z).K;
+}
+
 // ---- counting sort of a batch by chain length (descending): three light passes over the descriptors ----
 // hist / cursor: nb = rows + 1 counters each (chain lengths are < rows); perm: n indices.
 __global__ void __launch_bounds__(256) k_sort_hist(InstDev I, PathDev P, long long n, const vnsgpu_cand *__restrict__ cands, int nb,
-                                                   unsigned *__restrict__ hist)
+                                                   unsigned *__restrict__ hist, int useseg)
 {
    extern __shared__ unsigned smem_u[];
    for (int k = threadIdx.x; k < nb; k += blockDim.x) smem_u[k] = 0;
@@ -266,7 +405,7 @@ __global__ void __launch_bounds__(256) k_sort_hist(InstDev I, PathDev P, long lo
    const int T = P.hdr[HDR_T];
    for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < n; q += (long long)gridDim.x * blockDim.x) {
       const int4 cd = __ldg(reinterpret_cast<const int4 *>(cands) + q);
-      atomicAdd(&smem_u[decode_cand(T, I.C, cd.x, cd.y, cd.z).K], 1u);
+      atomicAdd(&smem_u[sort_key(T, I.C, cd, useseg)], 1u);
    }
    __syncthreads();
    for (int k = threadIdx.x; k < nb; k += blockDim.x)
@@ -282,7 +421,7 @@ __global__ void k_sort_scan(int nb, const unsigned *__restrict__ hist, unsigned 
 }
 
 __global__ void __launch_bounds__(256) k_sort_scatter(InstDev I, PathDev P, long long n, const vnsgpu_cand *__restrict__ cands, int nb,
-                                                      unsigned *__restrict__ cursor, unsigned *__restrict__ perm)
+                                                      unsigned *__restrict__ cursor, unsigned *__restrict__ perm, int useseg)
 {
    extern __shared__ unsigned smem_u[];
    unsigned *cnt = smem_u, *base = smem_u + nb;
@@ -293,7 +432,7 @@ __global__ void __launch_bounds__(256) k_sort_scatter(InstDev I, PathDev P, long
    const long long lo = per * blockIdx.x, hi = min(n, lo + per);
    for (long long q = lo + threadIdx.x; q < hi; q += blockDim.x) {
       const int4 cd = __ldg(reinterpret_cast<const int4 *>(cands) + q);
-      atomicAdd(&cnt[decode_cand(T, I.C, cd.x, cd.y, cd.z).K], 1u);
+      atomicAdd(&cnt[sort_key(T, I.C, cd, useseg)], 1u);
    }
    __syncthreads();
    for (int k = threadIdx.x; k < nb; k += blockDim.x) {
@@ -303,7 +442,63 @@ __global__ void __launch_bounds__(256) k_sort_scatter(InstDev I, PathDev P, long
    __syncthreads();
    for (long long q = lo + threadIdx.x; q < hi; q += blockDim.x) {
       const int4 cd = __ldg(reinterpret_cast<const int4 *>(cands) + q);
-      const int K = decode_cand(T, I.C, cd.x, cd.y, cd.z).K;
+      const int K = sort_key(T, I.C, cd, useseg);
       perm[base[K] + atomicAdd(&cnt[K], 1u)] = (unsigned)q;
+   }
+}
+
+// ---- segment-product cache (see SegCache) ------------------------------------------------------------
+// meta (ints): cum[R], pd[R], rowoff[R] with R = I.rows + 3.  One block.
+__global__ void __launch_bounds__(256) k_seg_offsets(InstDev I, PathDev P, int *__restrict__ meta)
+{
+   extern __shared__ int smem_i[];
+   const int T = P.hdr[HDR_T], S = T + 1, R = I.rows + 3;
+   int *m_l = smem_i, *dm_l = smem_i + R;
+   for (int l = threadIdx.x; l <= S; l += blockDim.x) {
+      const int c = layer_cluster(I, P.tg, T, l);
+      m_l[l] = I.m[c];
+      dm_l[l] = l < S ? (int)I.dmin[(size_t)c * I.C + layer_cluster(I, P.tg, T, l + 1)] : 0;
+   }
+   __syncthreads();
+   if (threadIdx.x == 0) {
+      int *cum = meta, *pd = meta + R;
+      unsigned *rowoff = reinterpret_cast<unsigned *>(meta + 2 * R);
+      int c = 0, d = 0;
+      for (int l = 0; l <= S; ++l) { cum[l] = c; pd[l] = d; c += m_l[l]; d += dm_l[l]; }
+      cum[S + 1] = c;
+      unsigned off = (unsigned)I.N * (unsigned)I.N;      // the products follow the table
+      for (int a = 0; a <= S; ++a) {
+         rowoff[a] = off;
+         off += (unsigned)(m_l[a] * (c - cum[min(a + 2, S + 1)]));
+      }
+   }
+}
+
+// block a builds M(a,b) for b = a+2 .. S by M(a,b) = M(a,b-1) (x) D(b-1,b), M(a,a+1) = D(a,a+1)
+__global__ void __launch_bounds__(128) k_seg_build(InstDev I, PathDev P, int *Dv, const int *meta)
+{
+   const int T = P.hdr[HDR_T], S = T + 1, R = I.rows + 3;
+   const int a = blockIdx.x;
+   if (a + 2 > S) return;
+   const int *cum = meta;
+   const unsigned *rowoff = reinterpret_cast<const unsigned *>(meta + 2 * R);
+   const int ca = layer_cluster(I, P.tg, T, a);
+   const int ma = I.m[ca];
+   const int *prev = Dv + ((long long)I.off[ca] * I.N + (long long)ma * I.off[layer_cluster(I, P.tg, T, a + 1)]);
+   int mk = I.m[layer_cluster(I, P.tg, T, a + 1)];
+   for (int b = a + 2; b <= S; ++b) {
+      const int ck = layer_cluster(I, P.tg, T, b - 1), cb = layer_cluster(I, P.tg, T, b);
+      const int mb = I.m[cb];
+      const int *d = Dv + ((long long)I.off[ck] * I.N + (long long)mk * I.off[cb]);
+      int *out = Dv + (rowoff[a] + (unsigned)(ma * (cum[b] - cum[a + 2])));
+      for (int e = threadIdx.x; e < ma * mb; e += blockDim.x) {
+         const int i = e / mb, j = e - i * mb;
+         int acc = VNS_INT_INF;
+         for (int k = 0; k < mk; ++k) acc = __viaddmin_s32(prev[i * mk + k], d[k * mb + j], acc);
+         out[e] = acc;
+      }
+      __syncthreads();
+      prev = out;
+      mk = mb;
    }
 }

@@ -15,6 +15,7 @@
 #include "path.cuh"
 #include "search.cuh"
 #include "eval.cuh"
+#include "chain.cuh"
 #include "kernels.cuh"
 
 static_assert(sizeof(vnsgpu_rng) == sizeof(RngState), "rng layout");
@@ -41,6 +42,9 @@ struct vnsgpu_ctx {
    int *d_D32 = nullptr;     // int32 copy of an all-integer table (DPX evaluation path), else null
    bool use_int = true;      // vnsgpu_set_int_path
    bool sort_batches = true; // evaluate batches in chain-length order (vnsgpu_set_batch_sort)
+   bool use_seg = true;      // exact segment products on integer tables (vnsgpu_set_segment_cache)
+   bool seg_ok = false;      // the int32 buffer has room for them and offsets fit 32 bits
+   int *d_segmeta = nullptr;
    int group_lanes = 8;      // lanes per candidate of k_eval_groups, from the mean cluster size
    unsigned *d_hist = nullptr, *d_perm = nullptr;
    size_t perm_cap = 0;
@@ -57,6 +61,8 @@ struct vnsgpu_ctx {
    std::string err;
    int64_t launches = 0;
    int num_sms = 148;
+   int max_smem = 48 * 1024;      // opt-in shared memory per block
+   bool use_smem_chain = true;    // vnsgpu_set_smem_chain
 };
 
 #define CK(call)                                                                                   \
@@ -111,6 +117,7 @@ vnsgpu_status vnsgpu_create(vnsgpu_ctx **out, int device)
    CK(cudaStreamCreateWithFlags(&ctx->own, cudaStreamNonBlocking));
    ctx->stream = ctx->own;
    CK(cudaDeviceGetAttribute(&ctx->num_sms, cudaDevAttrMultiProcessorCount, device));
+   CK(cudaDeviceGetAttribute(&ctx->max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
    CK(cudaMalloc(&ctx->d_rng, sizeof(RngState)));
    CK(cudaMalloc(&ctx->d_stats, sizeof(LsStats)));
    CK(cudaMalloc(&ctx->d_first, sizeof(long long)));
@@ -125,7 +132,8 @@ static void free_instance(vnsgpu_ctx *ctx)
    ctx->paths.clear();
    cudaFree(ctx->d_m); cudaFree(ctx->d_off); cudaFree(ctx->d_clof); cudaFree(ctx->d_reward);
    cudaFree(ctx->d_D); cudaFree(ctx->d_dmin); cudaFree(ctx->d_dmax); cudaFree(ctx->d_seg); cudaFree(ctx->d_D32);
-   cudaFree(ctx->d_hist); cudaFree(ctx->d_perm);
+   cudaFree(ctx->d_hist); cudaFree(ctx->d_perm); cudaFree(ctx->d_segmeta);
+   ctx->d_segmeta = nullptr; ctx->seg_ok = false;
    ctx->d_D32 = nullptr; ctx->d_hist = ctx->d_perm = nullptr; ctx->perm_cap = 0;
    ctx->d_m = ctx->d_off = ctx->d_clof = ctx->d_seg = nullptr;
    ctx->d_reward = ctx->d_D = ctx->d_dmin = ctx->d_dmax = nullptr;
@@ -155,6 +163,18 @@ int64_t vnsgpu_table_bytes(const vnsgpu_ctx *ctx) { return 8ll * ctx->I.N * ctx-
 vnsgpu_status vnsgpu_set_stream(vnsgpu_ctx *ctx, void *stream)
 {
    ctx->stream = stream ? (cudaStream_t)stream : ctx->own;
+   return VNSGPU_OK;
+}
+
+vnsgpu_status vnsgpu_set_smem_chain(vnsgpu_ctx *ctx, int enable)
+{
+   ctx->use_smem_chain = enable != 0;
+   return VNSGPU_OK;
+}
+
+vnsgpu_status vnsgpu_set_segment_cache(vnsgpu_ctx *ctx, int enable)
+{
+   ctx->use_seg = enable != 0;
    return VNSGPU_OK;
 }
 
@@ -258,7 +278,10 @@ static vnsgpu_status finish_table(vnsgpu_ctx *ctx)
    if (ctx->d_D32) { CK(cudaFree(ctx->d_D32)); ctx->d_D32 = nullptr; }
    if (ctx->I.exact_int && mx * (double)(ctx->I.rows + 1) < 536870912.0) {
       const long long nn = (long long)ctx->I.N * ctx->I.N;
-      CK(cudaMalloc(&ctx->d_D32, sizeof(int) * (size_t)nn + 64));
+      // room behind the table for the segment products of any path: <= (N + mp)^2 / 2 entries
+      const long long segcap = ((long long)ctx->I.N + ctx->I.mp + 1) * ((long long)ctx->I.N + ctx->I.mp + 1) / 2;
+      ctx->seg_ok = nn + segcap < (1ll << 32);
+      CK(cudaMalloc(&ctx->d_D32, sizeof(int) * (size_t)(nn + (ctx->seg_ok ? segcap : 0)) + 64));
       k_table_to_int<<<(int)std::min<long long>((nn + 255) / 256, 148 * 16), 256, 0, ctx->stream>>>(ctx->d_D, ctx->d_D32, nn);
       LAUNCHED(ctx);
       CK(cudaStreamSynchronize(ctx->stream));

@@ -55,6 +55,8 @@ _SIGS = {
     "vnsgpu_sync": [vp],
     "vnsgpu_set_int_path": [vp, C.c_int],
     "vnsgpu_set_batch_sort": [vp, C.c_int],
+    "vnsgpu_set_segment_cache": [vp, C.c_int],
+    "vnsgpu_set_smem_chain": [vp, C.c_int],
     "vnsgpu_int_path_active": [vp],
     "vnsgpu_set_clusters": [vp, C.c_int, ip, dp, C.c_int, C.c_int],
     "vnsgpu_build_table_euclid": [vp, dp, C.c_int],
@@ -173,6 +175,12 @@ class Engine:
     def set_int_path(self, enable):
         """False forces IEEE double evaluation even on all-integer tables (tests run both)."""
         self._ck(self.lib.vnsgpu_set_int_path(self.h, int(enable)))
+
+    def set_segment_cache(self, enable):
+        self._ck(self.lib.vnsgpu_set_segment_cache(self.h, int(enable)))
+
+    def set_smem_chain(self, enable):
+        self._ck(self.lib.vnsgpu_set_smem_chain(self.h, int(enable)))
 
     def set_batch_sort(self, enable):
         self._ck(self.lib.vnsgpu_set_batch_sort(self.h, int(enable)))
