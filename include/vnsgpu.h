@@ -177,6 +177,9 @@ int32_t vnsgpu_rng_next(vnsgpu_rng *rng);             /* rand() */
  * call runs on the device, trajectory-exact; path's targets/VNS vector and *rng are updated */
 vnsgpu_status vnsgpu_local_search(vnsgpu_ctx *ctx, int path, int kind, int num_changes, double budget, int skip,
                                   vnsgpu_rng *rng, vnsgpu_ls_stats *stats);
+/* SM cycles the shared-memory chain spent per phase since the last reset: drawing proposals, evaluating
+ * them, selecting the first accepted one, applying it (move + DP re-scan).  Profiling aid. */
+vnsgpu_status vnsgpu_chain_cycles(vnsgpu_ctx *ctx, int64_t *cycles4, int reset);
 /* pathInsert (kind 1, :931-999) / pathExchange (kind 2, :1001-1089) incl. fitDOPtoBudget */
 vnsgpu_status vnsgpu_shake(vnsgpu_ctx *ctx, int path, int kind, double budget, vnsgpu_rng *rng);
 /* fitDOPtoBudget (:364-385) */

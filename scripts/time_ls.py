@@ -20,4 +20,5 @@ for mode in ("smem-int", "smem-double", "global"):
         t = tot[k]
         print("%s %-11s kind %d: %8d proposals %6d accepts %7d rounds  %.3f s  %.2f us/proposal  %.2f us/round"
               % (name, mode, k, t[0], t[1], t[2], t[3], 1e6 * t[3] / t[0], 1e6 * t[3] / max(t[2], 1)))
+    print("   cycles", e.chain_cycles())
     print("   final T=%d length=%g reward=%g" % (p.getNumTargets(), p.getPathLength(), p.getReward()))

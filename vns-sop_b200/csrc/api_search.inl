@@ -15,7 +15,7 @@ static vnsgpu_status launch_chain(vnsgpu_ctx *ctx, const V *tab, int path, int k
 {
    CK(cudaFuncSetAttribute(k_chain_ls<V, G, NR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
    k_chain_ls<V, G, NR><<<1, VNS_CH_THREADS, smem, ctx->stream>>>(ctx->I, tab, ctx->paths[path].d, kind, num_changes, budget, skip,
-                                                                    ctx->d_rng, ctx->d_stats);
+                                                                    ctx->d_rng, ctx->d_stats, ctx->d_prof);
    LAUNCHED(ctx);
    return VNSGPU_OK;
 }
@@ -44,7 +44,40 @@ static vnsgpu_status launch_local_search(vnsgpu_ctx *ctx, int path, int kind, in
    return VNSGPU_OK;
 }
 
+template <typename V, int G, int NR>
+static vnsgpu_status launch_chain_vns(vnsgpu_ctx *ctx, const V *tab, int path, int work, const VnsParamsDev &prm, double *d_ir, double *d_il,
+                                      double *d_it, size_t smem)
+{
+   CK(cudaFuncSetAttribute(k_chain_vns_run<V, G, NR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+   k_chain_vns_run<V, G, NR><<<1, VNS_CH_THREADS, smem, ctx->stream>>>(ctx->I, tab, ctx->paths[path].d, ctx->paths[work].d, prm, ctx->d_rng,
+                                                                         ctx->d_res, d_ir, d_il, d_it, ctx->d_seg, ctx->d_prof);
+   LAUNCHED(ctx);
+   return VNSGPU_OK;
+}
+
+template <typename V>
+static vnsgpu_status launch_chain_vns_v(vnsgpu_ctx *ctx, const V *tab, int path, int work, const VnsParamsDev &prm, double *d_ir,
+                                        double *d_il, double *d_it, size_t smem)
+{
+   const int G = ctx->group_lanes, nr = (ctx->I.mp + G - 1) / G;
+   if (G == 8 && nr <= 1) return launch_chain_vns<V, 8, 1>(ctx, tab, path, work, prm, d_ir, d_il, d_it, smem);
+   if (G == 8 && nr <= 2) return launch_chain_vns<V, 8, 2>(ctx, tab, path, work, prm, d_ir, d_il, d_it, smem);
+   if (G == 8) return launch_chain_vns<V, 8, 4>(ctx, tab, path, work, prm, d_ir, d_il, d_it, smem);
+   if (G == 16 && nr <= 1) return launch_chain_vns<V, 16, 1>(ctx, tab, path, work, prm, d_ir, d_il, d_it, smem);
+   if (G == 16) return launch_chain_vns<V, 16, 2>(ctx, tab, path, work, prm, d_ir, d_il, d_it, smem);
+   return launch_chain_vns<V, 32, 1>(ctx, tab, path, work, prm, d_ir, d_il, d_it, smem);
+}
+
 extern "C" {
+
+vnsgpu_status vnsgpu_chain_cycles(vnsgpu_ctx *ctx, int64_t *cycles4, int reset)
+{
+   CK(cudaSetDevice(ctx->device));
+   CK(cudaMemcpyAsync(cycles4, ctx->d_prof, 4 * sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream));
+   if (reset) CK(cudaMemsetAsync(ctx->d_prof, 0, 4 * sizeof(long long), ctx->stream));
+   CK(cudaStreamSynchronize(ctx->stream));
+   return VNSGPU_OK;
+}
 
 void vnsgpu_rng_seed(vnsgpu_rng *rng, uint32_t seed) { rng_seed_host(*reinterpret_cast<RngState *>(rng), seed); }
 int32_t vnsgpu_rng_next(vnsgpu_rng *rng) { return rng_next(*reinterpret_cast<RngState *>(rng)); }
@@ -146,9 +179,20 @@ vnsgpu_status vnsgpu_vns_run(vnsgpu_ctx *ctx, int path, const vnsgpu_vns_params 
    prm.num_iterations = p->num_iterations; prm.num_iterations_unimproved = p->num_iterations_unimproved;
    prm.skip = p->lower_bound_skip; prm.greedy = p->greedy_initial; prm.budget = p->budget;
    prm.max_time_ms = p->max_time_ms; prm.max_improvements = cap;
-   k_vns_run<<<1, VNS_CHAIN_THREADS, chain_smem(ctx), ctx->stream>>>(ctx->I, ctx->paths[path].d, ctx->paths[work].d, prm, ctx->d_rng,
-                                                                     ctx->d_res, d_ir, d_il, d_it, ctx->d_seg);
-   LAUNCHED(ctx);
+   {
+      size_t smem = 0;
+      const size_t extra = chain_smem(ctx) + sizeof(RngState) + 64;   // shake / fit / greedy scratch + statics
+      if (vnsgpu_int_path_active(ctx) && chain_fits<int>(ctx, &smem) && smem + extra + sizeof(ChainCtl) + 1024 <= (size_t)ctx->max_smem)
+         s = launch_chain_vns_v<int>(ctx, ctx->d_D32, path, work, prm, d_ir, d_il, d_it, smem + chain_smem(ctx));
+      else if (chain_fits<double>(ctx, &smem) && smem + extra + sizeof(ChainCtl) + 1024 <= (size_t)ctx->max_smem)
+         s = launch_chain_vns_v<double>(ctx, ctx->d_D, path, work, prm, d_ir, d_il, d_it, smem + chain_smem(ctx));
+      else {
+         k_vns_run<<<1, VNS_CHAIN_THREADS, chain_smem(ctx), ctx->stream>>>(ctx->I, ctx->paths[path].d, ctx->paths[work].d, prm, ctx->d_rng,
+                                                                           ctx->d_res, d_ir, d_il, d_it, ctx->d_seg);
+         LAUNCHED(ctx);
+      }
+      if (s) return s;
+   }
    VnsResultDev r;
    CK(cudaMemcpyAsync(&r, ctx->d_res, sizeof(r), cudaMemcpyDeviceToHost, ctx->stream));
    CK(cudaStreamSynchronize(ctx->stream));

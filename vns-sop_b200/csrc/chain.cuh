@@ -33,6 +33,7 @@ struct ChainCtl {
    int pfrom[VNS_CH_MAXPROP], pto[VNS_CH_MAXPROP], pdraws[VNS_CH_MAXPROP], pskip[VNS_CH_MAXPROP];
    unsigned ring[VNS_CH_RING];
    LsStats st;
+   long long prof[4];   // cycles of thread 0: proposals, evaluation, selection, apply (vnsgpu_chain_cycles)
 };
 
 template <typename V> struct ChainSm {
@@ -81,7 +82,13 @@ __device__ void chain_rescan(const InstDev &I, const V *__restrict__ Dv, const C
          const int2 cib = s.cinfo[s.lcl[l]];
          const unsigned base = (unsigned)cia.x * (unsigned)I.N + (unsigned)cia.y * (unsigned)cib.x + (unsigned)min(lane, cib.y - 1);
          V acc = INF;
-         for (int i = 0; i < cia.y; ++i) acc = Ops::add_min(acc, __shfl_sync(FULL, v, i), __ldg(Dv + (base + (unsigned)(i * cib.y))));
+         for (int i0 = 0; i0 < cia.y; i0 += 8) {          // all 8 loads in flight before the first min
+            V dd[8];
+#pragma unroll
+            for (int t = 0; t < 8; ++t) dd[t] = __ldg(Dv + (base + (unsigned)(min(i0 + t, cia.y - 1) * cib.y)));
+#pragma unroll
+            for (int t = 0; t < 8; ++t) acc = Ops::add_min(acc, __shfl_sync(FULL, v, min(i0 + t, cia.y - 1)), dd[t]);
+         }
          v = lane < cib.y ? acc : INF;
          if (lane < cib.y) s.F[l * mp + lane] = acc;
          cia = cib;
@@ -93,7 +100,13 @@ __device__ void chain_rescan(const InstDev &I, const V *__restrict__ Dv, const C
          const int2 cia = s.cinfo[s.lcl[l]];
          const unsigned base = (unsigned)cia.x * (unsigned)I.N + (unsigned)cia.y * (unsigned)cib.x + (unsigned)(min(lane, cia.y - 1) * cib.y);
          V acc = INF;
-         for (int j = 0; j < cib.y; ++j) acc = Ops::add_min(acc, __shfl_sync(FULL, v, j), __ldg(Dv + (base + (unsigned)j)));
+         for (int j0 = 0; j0 < cib.y; j0 += 8) {
+            V dd[8];
+#pragma unroll
+            for (int t = 0; t < 8; ++t) dd[t] = __ldg(Dv + (base + (unsigned)min(j0 + t, cib.y - 1)));
+#pragma unroll
+            for (int t = 0; t < 8; ++t) acc = Ops::add_min(acc, __shfl_sync(FULL, v, min(j0 + t, cib.y - 1)), dd[t]);
+         }
          v = lane < cia.y ? acc : INF;
          if (lane < cia.y) s.Brev[(S - l) * mp + lane] = acc;
          cib = cia;
@@ -237,6 +250,7 @@ __device__ void chain_local_search(const InstDev &I, const V *__restrict__ Dv, c
    int var = 0, empty_rounds = 0;
    while (enabled && var < num_changes) {
       int T = ctl.T;
+      const long long t0 = clock64();
       // ---- 1. proposals in draw order -------------------------------------------------------------
       if (warp == 0) {
          chain_ring_fill(ctl, ctl.pos + 64, lane);
@@ -254,6 +268,7 @@ __device__ void chain_local_search(const InstDev &I, const V *__restrict__ Dv, c
       }
       __syncthreads();
       const int W = ctl.W;
+      const long long t1 = clock64();
       // ---- 2. one group per proposal ---------------------------------------------------------------
       if (warp * NG < W) {
          const int gidx = warp * NG + g;
@@ -271,7 +286,7 @@ __device__ void chain_local_search(const InstDev &I, const V *__restrict__ Dv, c
          const int m0 = K ? s.cinfo[s.lcl[cc.s0]].y : 0, mK = K ? s.cinfo[s.lcl[cc.sK]].y : 0;
          V fin;
          double between;
-         groups_eval<V, G, NR>(Dv, K, cc.tr, cc.ps, cc.pe, m0, mK, gl,
+         groups_eval<V, G, NR, true>(Dv, K, cc.tr, cc.ps, cc.pe, m0, mK, gl,
             [&](int k) {
                const int la = cand_layer(cc, k - 1), lb_ = cand_layer(cc, k);
                const int ca = la < 0 ? cc.foreign : s.lcl[la], cb = lb_ < 0 ? cc.foreign : s.lcl[lb_];
@@ -300,16 +315,21 @@ __device__ void chain_local_search(const InstDev &I, const V *__restrict__ Dv, c
       }
       __syncthreads();
       // ---- 3. first accepted in draw order ---------------------------------------------------------
+      const long long t2 = clock64();
       const int first = ctl.first;
       const int used = first < W ? first + 1 : W;                    // proposals the reference consumed
-      if (threadIdx.x == 0) {
-         int sk = 0;
-         for (int w = 0; w < used; ++w) sk += ctl.pskip[w];
+      if (threadIdx.x < 32) {
+         const int l2 = threadIdx.x + 32;
+         const int sk = __popc(__ballot_sync(0xffffffffu, (int)threadIdx.x < used && ctl.pskip[threadIdx.x])) +
+                        __popc(__ballot_sync(0xffffffffu, l2 < used && ctl.pskip[l2]));
+         if (threadIdx.x == 0) {
          ctl.st.proposals += used; ctl.st.lb_skips += sk; ctl.st.evals += used - sk; ctl.st.rounds += 1;
          if (first < W) ctl.st.accepts += 1;
          ctl.pos += used ? (unsigned)ctl.pdraws[used - 1] : 64u;     // no valid pair among 32: all 64 draws consumed
+         }
       }
       var += used;
+      const long long t3 = clock64();
       empty_rounds = used ? 0 : empty_rounds + 1;
       if (empty_rounds > VNS_MAX_DRAWS / 64) { if (threadIdx.x == 0) ctl.err = 3; }
       if (first < W) {
@@ -318,6 +338,9 @@ __device__ void chain_local_search(const InstDev &I, const V *__restrict__ Dv, c
          else chain_apply_exchange(I, Dv, s, ctl, from, to);
       }
       __syncthreads();
+      if (threadIdx.x == 0) {
+         ctl.prof[0] += t1 - t0; ctl.prof[1] += t2 - t1; ctl.prof[2] += t3 - t2; ctl.prof[3] += clock64() - t3;
+      }
       if (ctl.err) break;
    }
    __syncthreads();
@@ -376,7 +399,7 @@ __device__ void chain_store(const InstDev &I, const PathDev &P, const ChainSm<V>
 
 template <typename V, int G, int NR>
 __global__ void __launch_bounds__(VNS_CH_THREADS) k_chain_ls(InstDev I, const V *__restrict__ Dv, PathDev P, int kind, int num_changes,
-                                                             double budget, int skipflag, RngState *rng, LsStats *stats)
+                                                             double budget, int skipflag, RngState *rng, LsStats *stats, long long *prof)
 {
    extern __shared__ __align__(16) unsigned char smem_c[];
    __shared__ ChainCtl ctl;
@@ -384,7 +407,7 @@ __global__ void __launch_bounds__(VNS_CH_THREADS) k_chain_ls(InstDev I, const V 
    if (threadIdx.x < 32) {
       RngState g = *rng;
       chain_ring_init(ctl, g, threadIdx.x);
-      if (threadIdx.x == 0) ctl.st = LsStats{0, 0, 0, 0, 0};
+      if (threadIdx.x == 0) { ctl.st = LsStats{0, 0, 0, 0, 0}; ctl.prof[0] = ctl.prof[1] = ctl.prof[2] = ctl.prof[3] = 0; }
    }
    chain_load<V>(I, P, s, ctl);
    chain_local_search<V, G, NR>(I, Dv, s, ctl, kind, num_changes, budget, skipflag);
@@ -392,6 +415,98 @@ __global__ void __launch_bounds__(VNS_CH_THREADS) k_chain_ls(InstDev I, const V 
    if (threadIdx.x < 32) {
       __shared__ RngState gout;
       chain_ring_export(ctl, gout, threadIdx.x);
-      if (threadIdx.x == 0) { *rng = gout; *stats = ctl.st; }
+      if (threadIdx.x == 0) {
+         *rng = gout; *stats = ctl.st;
+         for (int k = 0; k < 4; ++k) prof[k] += ctl.prof[k];
+      }
    }
+}
+
+// ---- VnsSopSolver::iterate (vns_sop_solver.cpp:82-260) as one persistent chain; the two local searches
+//      run out of shared memory, shake / fit / greedy / path copies are the global-memory routines of
+//      search.cuh (once per VNS step) --------------------------------------------------------------------
+template <typename V, int G, int NR>
+__global__ void __launch_bounds__(VNS_CH_THREADS) k_chain_vns_run(InstDev I, const V *__restrict__ Dv, PathDev tour, PathDev act,
+                                                                  VnsParamsDev prm, RngState *rng, VnsResultDev *res, double *impr_reward,
+                                                                  double *impr_length, double *impr_ms, int *seg, long long *prof)
+{
+   extern __shared__ __align__(16) unsigned char smem_c[];
+   __shared__ ChainCtl ctl;
+   __shared__ RngState g;
+   __shared__ int s_stop, s_improved;
+   double *vbuf_all = reinterpret_cast<double *>(smem_c);                       // shake / fit / greedy scratch
+   const ChainSm<V> s = chain_carve<V>(smem_c + sizeof(double) * 2 * I.mp * VNS_CH_WARPS, I.C, I.mp);
+   if (threadIdx.x == 0) {
+      g = *rng; s_stop = 0;
+      ctl.st = LsStats{0, 0, 0, 0, 0}; ctl.prof[0] = ctl.prof[1] = ctl.prof[2] = ctl.prof[3] = 0; ctl.err = 0;
+   }
+   __syncthreads();
+   const double t0 = now_ms();
+   cta_update(I, tour, tour.hdr[HDR_T]);
+   if (prm.greedy) cta_greedy(I, tour, prm.budget, vbuf_all);            // :127-129
+   const int num_avail = tour.hdr[HDR_NVNS];                            // :115
+   int last_impr = 1, it = 0, n_impr = 0;                               // :145
+   double t_last = now_ms() - t0;
+   if (threadIdx.x == 0 && impr_reward && n_impr < prm.max_improvements) {   // :150-154
+      impr_reward[n_impr] = tour.hd[HD_REWARD]; impr_length[n_impr] = tour.hd[HD_LEN]; impr_ms[n_impr] = t_last;
+   }
+   n_impr = 1;
+   __syncthreads();
+   bool stop = false;
+   while (!stop) {
+      ++it;
+      if (it >= prm.num_iterations) stop = true;                         // :178
+      if (it - last_impr >= prm.num_iterations_unimproved) stop = true;  // :182
+      int k = 1;
+      while (k <= 2) {
+         if (threadIdx.x == 0 && prm.max_time_ms > 0 && now_ms() - t0 >= prm.max_time_ms) s_stop = 1;  // :189-193
+         cta_copy_path(I, act, tour);                                    // :195-197
+         const double r0 = act.hd[HD_REWARD], l0 = act.hd[HD_LEN];
+         cta_shake(I, act, k, prm.budget, g, seg, vbuf_all);             // :202
+         if (threadIdx.x < 32) chain_ring_init(ctl, g, threadIdx.x);
+         chain_load<V>(I, act, s, ctl);
+         chain_local_search<V, G, NR>(I, Dv, s, ctl, k, num_avail * num_avail, prm.budget, prm.skip);   // :207,:346
+         chain_store<V>(I, act, s, ctl);
+         if (threadIdx.x < 32) chain_ring_export(ctl, g, threadIdx.x);
+         __syncthreads();
+         if (threadIdx.x == 0) {
+            const double r1 = act.hd[HD_REWARD], l1 = act.hd[HD_LEN];
+            s_improved = (r1 > r0 || (r1 == r0 && l1 < l0));             // :213
+         }
+         __syncthreads();
+         if (act.hdr[HDR_ERR]) { stop = true; break; }
+         if (s_improved) {
+            last_impr = it;
+            t_last = now_ms() - t0;
+            if (threadIdx.x == 0) {
+               if (impr_reward && n_impr < prm.max_improvements) {
+                  impr_reward[n_impr] = act.hd[HD_REWARD]; impr_length[n_impr] = act.hd[HD_LEN]; impr_ms[n_impr] = t_last;
+               }
+               // :229-237 sanity check of the improved tour
+               const double calc = path_walk_back(I, act, act.hdr[HDR_T], nullptr, nullptr);
+               const double nl = act.hd[HD_LEN];
+               if (calc > prm.budget || nl > prm.budget || calc - nl > 0.01) act.hdr[HDR_ERR] = 4;
+            }
+            ++n_impr;
+            cta_copy_path(I, tour, act);                                 // :227-228
+            if (tour.hdr[HDR_ERR]) { stop = true; break; }
+            k = 1;                                                       // :241
+         } else {
+            ++k;                                                         // :243
+         }
+      }
+      __syncthreads();
+      if (s_stop) stop = true;
+   }
+   __syncthreads();
+   if (threadIdx.x == 0) {
+      res->num_iters = it; res->num_iters_last_impr = last_impr; res->n_improvements = n_impr;
+      res->status = tour.hdr[HDR_ERR] ? tour.hdr[HDR_ERR] : act.hdr[HDR_ERR];
+      res->reward = tour.hd[HD_REWARD]; res->length = tour.hd[HD_LEN];
+      res->time_ms = now_ms() - t0; res->time_last_impr_ms = t_last;
+      res->proposals = ctl.st.proposals; res->evals = ctl.st.evals; res->accepts = ctl.st.accepts;
+      *rng = g;
+      for (int q = 0; q < 4; ++q) prof[q] += ctl.prof[q];
+   }
+   __syncthreads();
 }

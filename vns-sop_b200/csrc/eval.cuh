@@ -112,7 +112,9 @@ struct EdgeDesc {
 // chain = K blocks; edge(k), 1 <= k <= K, describes block k; the chain starts from the vector
 // row0(j), j < m0, and closes against rowK(j), j < mK; tr = closing association (d + B) + v;
 // ps, pe = the pair of edges the reference pre-sums in its lower bound (-1: none).
-template <typename V, int G, int NR, typename Edge, typename Row0, typename RowK>
+// LAT: latency mode for the single-CTA chains (nothing else hides the L1 latency there): every block
+// step runs G fully unrolled iterations so that all its loads are in flight before the first min.
+template <typename V, int G, int NR, bool LAT = false, typename Edge, typename Row0, typename RowK>
 __device__ __forceinline__ void groups_eval(const V *__restrict__ Dv, int K, int tr, int ps, int pe, int m0, int mK, int gl, Edge edge,
                                             Row0 row0, RowK rowK, V &fin_out, double &between_out)
 {
@@ -185,12 +187,20 @@ __device__ __forceinline__ void groups_eval(const V *__restrict__ Dv, int K, int
                      const unsigned sb = cbase + (unsigned)(min(rs * G, trip - 1) * sl);
                      const int tm = min(tmaxAll - rs * G, G);
                      const V opnd = trn ? breg[rs] : v[rs];
+                     if (LAT) {
+                        V dd[G];
+#pragma unroll
+                        for (int t = 0; t < G; ++t) dd[t] = __ldg(Dv + (sb + (unsigned)(min(t, tlim) * sl)));
+#pragma unroll
+                        for (int t = 0; t < G; ++t) acc[rd] = Ops::add_min(acc[rd], __shfl_sync(FULL, opnd, min(t, tlim), G), dd[t]);
+                     } else {
 #pragma unroll 2
-                     for (int t = 0; t < tm; ++t) {
-                        const int tt = min(t, tlim);
-                        const V x = __shfl_sync(FULL, opnd, tt, G);
-                        const V dd = __ldg(Dv + (sb + (unsigned)(tt * sl)));
-                        acc[rd] = Ops::add_min(acc[rd], x, dd);
+                        for (int t = 0; t < tm; ++t) {
+                           const int tt = min(t, tlim);
+                           const V x = __shfl_sync(FULL, opnd, tt, G);
+                           const V dd = __ldg(Dv + (sb + (unsigned)(tt * sl)));
+                           acc[rd] = Ops::add_min(acc[rd], x, dd);
+                        }
                      }
                   }
                }

@@ -58,6 +58,7 @@ struct vnsgpu_ctx {
    LsStats *d_stats = nullptr;
    long long *d_first = nullptr;
    VnsResultDev *d_res = nullptr;
+   long long *d_prof = nullptr;   // phase cycles of the shared-memory chain
    std::string err;
    int64_t launches = 0;
    int num_sms = 148;
@@ -122,6 +123,8 @@ vnsgpu_status vnsgpu_create(vnsgpu_ctx **out, int device)
    CK(cudaMalloc(&ctx->d_stats, sizeof(LsStats)));
    CK(cudaMalloc(&ctx->d_first, sizeof(long long)));
    CK(cudaMalloc(&ctx->d_res, sizeof(VnsResultDev)));
+   CK(cudaMalloc(&ctx->d_prof, 4 * sizeof(long long)));
+   CK(cudaMemset(ctx->d_prof, 0, 4 * sizeof(long long)));
    CK(cudaMalloc(&ctx->d_info, 2 * sizeof(unsigned long long)));
    return VNSGPU_OK;
 }
@@ -147,7 +150,7 @@ void vnsgpu_destroy(vnsgpu_ctx *ctx)
    cudaStreamSynchronize(ctx->stream);
    free_instance(ctx);
    cudaFree(ctx->d_scratch); cudaFree(ctx->d_rng); cudaFree(ctx->d_stats); cudaFree(ctx->d_first);
-   cudaFree(ctx->d_res); cudaFree(ctx->d_info);
+   cudaFree(ctx->d_res); cudaFree(ctx->d_info); cudaFree(ctx->d_prof);
    if (ctx->s_in) {
       cudaStreamDestroy(ctx->s_in); cudaStreamDestroy(ctx->s_out); cudaEventDestroy(ctx->ev_start);
       for (int k = 0; k < VNS_PIPE_EVENTS; ++k) { cudaEventDestroy(ctx->ev_in[k]); cudaEventDestroy(ctx->ev_k[k]); }

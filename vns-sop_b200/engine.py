@@ -57,6 +57,7 @@ _SIGS = {
     "vnsgpu_set_batch_sort": [vp, C.c_int],
     "vnsgpu_set_segment_cache": [vp, C.c_int],
     "vnsgpu_set_smem_chain": [vp, C.c_int],
+    "vnsgpu_chain_cycles": [vp, C.POINTER(C.c_int64), C.c_int],
     "vnsgpu_int_path_active": [vp],
     "vnsgpu_set_clusters": [vp, C.c_int, ip, dp, C.c_int, C.c_int],
     "vnsgpu_build_table_euclid": [vp, dp, C.c_int],
@@ -178,6 +179,11 @@ class Engine:
 
     def set_segment_cache(self, enable):
         self._ck(self.lib.vnsgpu_set_segment_cache(self.h, int(enable)))
+
+    def chain_cycles(self, reset=True):
+        out = (C.c_int64 * 4)()
+        self._ck(self.lib.vnsgpu_chain_cycles(self.h, out, int(reset)))
+        return dict(zip(("propose", "evaluate", "select", "apply"), out))
 
     def set_smem_chain(self, enable):
         self._ck(self.lib.vnsgpu_set_smem_chain(self.h, int(enable)))
