@@ -242,7 +242,7 @@ def run_b200(args):
     import torch
     import torch.distributed as dist
 
-    from vns_sop_b200 import engine
+    from vns_sop_b200 import engine, sharding
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -281,7 +281,11 @@ def run_b200(args):
     n, K, W = args.batch, args.steps, args.warmup
     rows = make_candidates(n, vns, T, 1000 + rank)          # each rank owns its shard of the candidates
     cands = p.make_cands(rows)
-    alg_bytes = p.cand_bytes(cands)
+    alg_bytes = p.cand_bytes(cands)                        # w = 4 B / table entry on the exact int32 path
+    int_path = eng.int_path_active
+    eng.set_int_path(False)
+    alg_bytes_f64 = p.cand_bytes(cands)                    # SURVEY.md 8d's figure: 8 B / entry
+    eng.set_int_path(True)
 
     # ---- value: everything resident in HBM -----------------------------------------------------------
     stream = torch.cuda.Stream(device=dev)
@@ -300,6 +304,8 @@ def run_b200(args):
                                        C.c_void_p(d_len.data_ptr()), C.c_void_p(d_lb.data_ptr()),
                                        C.c_void_p(d_fl.data_ptr()), C.c_void_p(d_first.data_ptr()), sp)
         eng._ck(st)
+        if world > 1:      # the path's one exchange step: reduce the chosen move (8 bytes, all-reduce MIN)
+            sharding.reduce_first_accept_(d_first, rank * n)
 
     sampler = ClockSampler(local) if rank == 0 else None
     with torch.cuda.stream(stream):
@@ -338,6 +344,8 @@ def run_b200(args):
             eng._ck(lib.vnsgpu_eval_batch(eng.h, p.h, n, C.c_void_p(h_c.data_ptr()), pb.budget, 1,
                                           C.cast(h_len.data_ptr(), C.POINTER(C.c_double)), None,
                                           C.c_void_p(h_fl.data_ptr()), C.byref(first)))
+            if world > 1:
+                sharding.reduce_first_accept(first.value, rank * n, device=dev)
 
         for _ in range(W):
             host_step()
@@ -352,7 +360,8 @@ def run_b200(args):
         e2e = {"value": world * n * K / dt, "unit": "evals/s", "h2d_bytes_per_step": world * n * 16,
                "d2h_bytes_per_step": world * (n * 9 + 8), "ms_per_step": 1e3 * dt / K,
                "call": "vnsgpu_eval_batch (pinned host candidates in; lengths + flags + first accepted index out)"}
-        assert first.value == first_dev, "host and device entry points disagree on the first accepted candidate"
+        if world == 1:
+            assert first.value == first_dev, "host and device entry points disagree on the first accepted candidate"
         assert torch.equal(h_len[:4096], d_len[:4096].cpu()), "host and device entry points disagree"
 
     peak, peak_src = measured_hbm_peak()
@@ -360,7 +369,8 @@ def run_b200(args):
     line = {
         "metric": "candidate_move_evals_per_sec", "value": value, "unit": "evals/s", "n_gpus": world,
         "steps": K, "warmup": W, "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "vs_baseline": None, "dtype": "i32 (exact on this all-integer table; results bit-identical to the f64 reference)" if int_path else "f64",
+        "data": "synthetic",
         "config": {"workload": WORKLOADS[args.workload][0], "clusters": int(pb.C), "samples": int(pb.N),
                    "candidates_per_step_per_gpu": n, "targets_in_path": int(T),
                    "state": STATE,
@@ -368,16 +378,24 @@ def run_b200(args):
                    "outputs": "length + lower bound + flags per candidate, first accepted index",
                    "l2": "candidates + results = %.0f MB per step > 126 MB L2 (streamed); the %.2f MB distance "
                          "table is cache-resident by design" % (n * 33 / 1e6, eng.table_bytes / 1e6),
-                   "sharding": "candidates split by rank, table replicated, no collective in the data path"},
+                   "evaluation": "sub-warp groups, batch sorted by chain length on the device, %s" %
+                                 ("exact int32 DPX arithmetic + exact segment products (rebuilt every step)" if int_path
+                                  else "IEEE double, block by block"),
+                   "sharding": "candidates split by rank (global batch = n_gpus x per-GPU batch), table and path replicated; "
+                               "N > 1 adds one 8-byte all-reduce(MIN) per step for the chosen move"},
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_src, "kernel": "k_eval_batch",
+                     "traffic": None, "peak_source": peak_src, "kernel": "k_eval_groups",
                      "kernel_ms": kern_ms, "algorithmic_bytes_per_launch": int(alg_bytes),
                      "algorithmic_bytes_per_candidate": alg_bytes / n,
+                     "algorithmic_bytes_per_candidate_at_8B_per_entry": alg_bytes_f64 / n,
                      "stream_bytes_per_candidate": 33,
-                     "note": "algorithmic bytes = SURVEY.md 8d (every distance-block entry once + first F row + last B row "
-                             "+ result); the table is L1/L2-resident on this instance, so the HBM traffic is the 16 B "
-                             "descriptor + 17 B of results per candidate"},
+                     "working_set": "L1/L2-resident table (%.2f MB): the HBM traffic is the 16 B descriptor + 17 B of "
+                                    "results per candidate, so this fraction is NOT an HBM-bandwidth claim" % (eng.table_bytes / 1e6),
+                     "note": "achieved = algorithmic bytes (SURVEY.md 8d: every distance-block entry of the reference's chain "
+                             "once at the width the kernel reads, + first F row + last B row + result) / time of one step "
+                             "(sort + segment products + evaluation kernels, CUDA events).  With the segment products the "
+                             "kernel reads FEWER table bytes than this reference-chain figure; see DESIGN.md 5"},
         "accepted_in_batch": ok_flags, "first_accept": first_dev,
     }
     if rank == 0 and world == 1 and not args.no_cpu:
