@@ -182,41 +182,71 @@ def run_reference(args):
 
 # ---- clocks during the timed region (B200_PROFILING.md "clocks DURING the timed region") ----------------
 class ClockSampler:
+    """SM clock + throttle reasons sampled every 5 ms through NVML (nvidia-ml-py) in a background thread;
+    falls back to `nvidia-smi -lms 100` (B200_PROFILING.md) when NVML cannot be loaded."""
+    NAMES = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
-    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
     def __init__(self, index):
-        self.rows, self.proc = [], None
+        self.rows, self.proc, self.stop_flag, self.max_mhz = [], None, False, None
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.th = threading.Thread(target=self._read, daemon=True)
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[index]) if vis and vis.split(",")[index].isdigit() else index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.th = threading.Thread(target=self._poll, daemon=True)
             self.th.start()
-        except OSError:
-            self.proc = None
+        except Exception:
+            self.nv = None
+            try:
+                self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                              "--format=csv,noheader,nounits", "-lms", "100"],
+                                             stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                self.th = threading.Thread(target=self._read, daemon=True)
+                self.th.start()
+            except OSError:
+                self.proc = None
+
+    def _poll(self):
+        nv = self.nv
+        while not self.stop_flag:
+            try:
+                mhz = float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    mask = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                except Exception:
+                    mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                self.rows.append((time.perf_counter(), mhz, {k for k, bit in self.NAMES.items() if mask & bit}))
+            except Exception:
+                pass
+            time.sleep(0.005)
 
     def _read(self):
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for line in self.proc.stdout:
-            self.rows.append((time.perf_counter(), [x.strip() for x in line.split(",")]))
-
-    def window(self, t0, t1):
-        rows = [r for t, r in self.rows if t0 <= t <= t1 + 0.15] or [r for _, r in self.rows[-3:]]
-        sm, mx, reasons = [], 0.0, set()
-        for r in rows:
+            r = [x.strip() for x in line.split(",")]
             try:
-                sm.append(float(r[0]))
-                mx = max(mx, float(r[1]))
+                self.max_mhz = float(r[1])
+                act = {nm for k, nm in enumerate(names) if len(r) > 3 + k and r[3 + k].lower().startswith("active")}
+                self.rows.append((time.perf_counter(), float(r[0]), act))
             except (ValueError, IndexError):
                 continue
-            for k, nm in enumerate(self.NAMES):
-                if len(r) > 3 + k and r[3 + k].lower().startswith("active"):
-                    reasons.add(nm)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+
+    def window(self, t0, t1):
+        rows = [r for r in self.rows if t0 <= r[0] <= t1] or [r for r in self.rows if t0 - 0.2 <= r[0] <= t1 + 0.2]
+        reasons = set()
+        for r in rows:
+            reasons |= r[2]
+        return {"sm_mhz": float(np.median([r[1] for r in rows])) if rows else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(reasons), "samples": len(rows),
+                "source": "nvml, 5 ms period" if self.nv else "nvidia-smi -lms 100"}
 
     def stop(self):
+        self.stop_flag = True
         if self.proc:
             self.proc.terminate()
 
@@ -432,6 +462,7 @@ def solve_leg(args, eng, sf, pb):
     """Second half of the metric: wall time of the whole seeded VNS (stock sop.cfg stopping rule) to the
     reference's final reward - the device chain walks the reference's exact trajectory."""
     from oracle import binding as ob
+    from vns_sop_b200 import instances as ins
     p = eng.path()
     t0 = time.perf_counter()
     res, impr = p.vns_run(1)
@@ -454,6 +485,39 @@ def solve_leg(args, eng, sf, pb):
                     "cpu_num_iters": int(d["NUM_ITERS"]),
                     "same_result": float(d["REWARDS"]) == res.reward and float(d["LENGTH"]) == res.length
                     and int(d["NUM_ITERS"]) == res.num_iters})
+    # multi-start: the reference's --batch=N (N seeds) - one thread block per seed in ONE launch vs one
+    # reference process per host core
+    nruns = 148
+    p2 = eng.path()
+    t0 = time.perf_counter()
+    res_b, best = p2.vns_run_batch(list(range(1, nruns + 1)))
+    gpu_multi = time.perf_counter() - t0
+    out["multi_start"] = {"gpu_runs": nruns, "gpu_wall_s": gpu_multi, "gpu_runs_per_s": nruns / gpu_multi,
+                          "best_reward": res_b[best].reward, "best_length": res_b[best].length, "best_seed": best + 1,
+                          "seed1_same_as_single_run": res_b[0].reward == res.reward and res_b[0].length == res.length}
+    if os.path.exists(ob.REF_BIN):
+        cores = host_cores()
+        with tempfile.TemporaryDirectory() as td:
+            f = os.path.join(td, "w.sop")
+            ins.write_sop(sf, f)
+            t0 = time.perf_counter()
+            procs = []
+            for sd in range(1, cores + 1):
+                od = os.path.join(td, "o%d" % sd)
+                os.makedirs(od)
+                procs.append(subprocess.Popen([ob.REF_BIN, "--problem=" + f, "--seed=%d" % sd, "--output=" + od],
+                                              stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL))
+            for q in procs:
+                q.wait()
+            cpu_multi = time.perf_counter() - t0
+            rewards = []
+            for sd in range(1, cores + 1):
+                rec = open(os.path.join(td, "o%d" % sd, "results.log")).read().strip().rstrip(";")
+                d = dict(kv.split(":", 1) for kv in rec.split(";"))
+                rewards.append((float(d["REWARDS"]), float(d["LENGTH"])))
+        same = all(rewards[k] == (res_b[k].reward, res_b[k].length) for k in range(cores))
+        out["multi_start"].update({"cpu_runs": cores, "cpu_cores": cores, "cpu_wall_s": cpu_multi, "cpu_runs_per_s": cores / cpu_multi,
+                                   "first_%d_seeds_same_results" % cores: same})
     return out
 
 

@@ -193,6 +193,13 @@ vnsgpu_status vnsgpu_vns_run(vnsgpu_ctx *ctx, int path, const vnsgpu_vns_params 
                              vnsgpu_vns_result *result, double *impr_reward, double *impr_length,
                              double *impr_time_ms);
 
+/* Multi-start = the reference's --batch=N (N independent solves with different seeds, crl
+ * algorithm.cc:120-161) as ONE launch: one thread block per run, each a trajectory-exact replica of a
+ * seeded reference run.  Every run starts from `path`'s state; results[r] belongs to seeds[r]; the best
+ * tour (max reward, then min length) is copied into `path` and its index returned in *best_run. */
+vnsgpu_status vnsgpu_vns_run_batch(vnsgpu_ctx *ctx, int path, int nruns, const uint32_t *seeds, const vnsgpu_vns_params *params,
+                                   vnsgpu_vns_result *results, int *best_run);
+
 #ifdef __cplusplus
 }
 #endif

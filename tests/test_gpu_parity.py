@@ -190,6 +190,28 @@ def test_full_vns_run_seed1_follows_reference_trajectory(name, mode, golden, eng
     assert calc <= pb.budget
 
 
+def test_multi_start_batch_equals_single_seeded_runs(golden, eng_cache):
+    """vnsgpu_vns_run_batch (the reference's --batch=N as one launch, one thread block per seed): every run
+    is the same trajectory as the single-seed call, seed 1 is the reference's results.log, and the best
+    tour lands in the path."""
+    for name in ("berlin52", "opn_s08"):
+        e, sf, pb = eng_cache(name)
+        seeds = [1, 2, 3, 4, 5, 6, 7]
+        p = e.path()
+        res, best = p.vns_run_batch(seeds)
+        s = golden[name]["solve_seed1"]
+        assert res[0].reward == s["REWARDS"] and res[0].length == s["LENGTH"] and res[0].num_iters == s["NUM_ITERS"]
+        for k, sd in enumerate(seeds):
+            q = e.path()
+            r1, _ = q.vns_run(sd)
+            assert (res[k].reward, res[k].length, res[k].num_iters, res[k].num_iters_last_impr, res[k].proposals, res[k].accepts) == \
+                   (r1.reward, r1.length, r1.num_iters, r1.num_iters_last_impr, r1.proposals, r1.accepts), (name, sd)
+        key = [(-r.reward, r.length) for r in res]
+        assert best == key.index(min(key))
+        assert p.getReward() == res[best].reward and p.getPathLength() == res[best].length
+        assert p.getPathLengthCalculate() <= pb.budget
+
+
 @pytest.mark.parametrize("int_path", [True, False])
 @pytest.mark.parametrize("name", ALL)
 def test_eval_batch_both_arithmetic_paths_vs_oracle(name, int_path, golden, eng_cache):

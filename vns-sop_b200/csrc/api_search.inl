@@ -68,6 +68,27 @@ static vnsgpu_status launch_chain_vns_v(vnsgpu_ctx *ctx, const V *tab, int path,
    return launch_chain_vns<V, 32, 1>(ctx, tab, path, work, prm, d_ir, d_il, d_it, smem);
 }
 
+template <typename V, int G, int NR>
+static vnsgpu_status launch_chain_multi(vnsgpu_ctx *ctx, const V *tab, int nruns, VnsRunSlot *d_slots, const VnsParamsDev &prm, size_t smem)
+{
+   CK(cudaFuncSetAttribute(k_chain_vns_multi<V, G, NR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+   k_chain_vns_multi<V, G, NR><<<nruns, VNS_CH_THREADS, smem, ctx->stream>>>(ctx->I, tab, d_slots, prm);
+   LAUNCHED(ctx);
+   return VNSGPU_OK;
+}
+
+template <typename V>
+static vnsgpu_status launch_chain_multi_v(vnsgpu_ctx *ctx, const V *tab, int nruns, VnsRunSlot *d_slots, const VnsParamsDev &prm, size_t smem)
+{
+   const int G = ctx->group_lanes, nr = (ctx->I.mp + G - 1) / G;
+   if (G == 8 && nr <= 1) return launch_chain_multi<V, 8, 1>(ctx, tab, nruns, d_slots, prm, smem);
+   if (G == 8 && nr <= 2) return launch_chain_multi<V, 8, 2>(ctx, tab, nruns, d_slots, prm, smem);
+   if (G == 8) return launch_chain_multi<V, 8, 4>(ctx, tab, nruns, d_slots, prm, smem);
+   if (G == 16 && nr <= 1) return launch_chain_multi<V, 16, 1>(ctx, tab, nruns, d_slots, prm, smem);
+   if (G == 16) return launch_chain_multi<V, 16, 2>(ctx, tab, nruns, d_slots, prm, smem);
+   return launch_chain_multi<V, 32, 1>(ctx, tab, nruns, d_slots, prm, smem);
+}
+
 extern "C" {
 
 vnsgpu_status vnsgpu_chain_cycles(vnsgpu_ctx *ctx, int64_t *cycles4, int reset)
@@ -213,6 +234,72 @@ vnsgpu_status vnsgpu_vns_run(vnsgpu_ctx *ctx, int path, const vnsgpu_vns_params 
    if (r.status == 4) return fail(ctx, VNSGPU_E_INCONSISTENT, "inconsistent path length in improved tour");
    if (r.status) return fail(ctx, VNSGPU_E_STATE, "device-side error flag in vns_run");
    return VNSGPU_OK;
+}
+
+vnsgpu_status vnsgpu_vns_run_batch(vnsgpu_ctx *ctx, int path, int nruns, const uint32_t *seeds, const vnsgpu_vns_params *p,
+                                   vnsgpu_vns_result *results, int *best_run)
+{
+   CK(cudaSetDevice(ctx->device));
+   if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
+   if (nruns < 1) return fail(ctx, VNSGPU_E_RANGE, "nruns < 1");
+   size_t smem = 0;
+   const size_t extra = chain_smem(ctx) + sizeof(RngState) + 64;
+   const bool as_int = vnsgpu_int_path_active(ctx) && chain_fits<int>(ctx, &smem) && smem + extra + sizeof(ChainCtl) + 1024 <= (size_t)ctx->max_smem;
+   if (!as_int && !(chain_fits<double>(ctx, &smem) && smem + extra + sizeof(ChainCtl) + 1024 <= (size_t)ctx->max_smem))
+      return fail(ctx, VNSGPU_E_STATE, "instance too large for the shared-memory chain: use vnsgpu_vns_run per seed");
+   // two paths per run (tourVNSGOPPath, actualVNSGOPPath), every tour a copy of `path`
+   const int first = (int)ctx->paths.size();
+   std::vector<VnsRunSlot> slots(nruns);
+   int *d_segs = nullptr;
+   VnsRunSlot *d_slots = nullptr;
+   vnsgpu_status s = VNSGPU_OK;
+   CK(cudaMalloc(&d_segs, sizeof(int) * 2 * ctx->I.rows * (size_t)nruns));
+   CK(cudaMalloc(&d_slots, sizeof(VnsRunSlot) * (size_t)nruns));
+   for (int r = 0; r < nruns && !s; ++r) {
+      int a = -1, b = -1;
+      s = vnsgpu_path_create(ctx, &a);
+      if (!s) s = vnsgpu_path_create(ctx, &b);
+      if (!s) s = vnsgpu_path_copy(ctx, a, path);
+      if (s) break;
+      slots[r].tour = ctx->paths[a].d; slots[r].act = ctx->paths[b].d;
+      rng_seed_host(slots[r].rng, seeds[r]);
+      memset(&slots[r].res, 0, sizeof(VnsResultDev));
+      slots[r].seg = d_segs + (size_t)r * 2 * ctx->I.rows;
+   }
+   if (!s) {
+      CK(cudaMemcpyAsync(d_slots, slots.data(), sizeof(VnsRunSlot) * nruns, cudaMemcpyHostToDevice, ctx->stream));
+      VnsParamsDev prm;
+      prm.num_iterations = p->num_iterations; prm.num_iterations_unimproved = p->num_iterations_unimproved;
+      prm.skip = p->lower_bound_skip; prm.greedy = p->greedy_initial; prm.budget = p->budget;
+      prm.max_time_ms = p->max_time_ms; prm.max_improvements = 0;
+      s = as_int ? launch_chain_multi_v<int>(ctx, ctx->d_D32, nruns, d_slots, prm, smem + chain_smem(ctx))
+                 : launch_chain_multi_v<double>(ctx, ctx->d_D, nruns, d_slots, prm, smem + chain_smem(ctx));
+   }
+   if (!s) {
+      CK(cudaMemcpyAsync(slots.data(), d_slots, sizeof(VnsRunSlot) * nruns, cudaMemcpyDeviceToHost, ctx->stream));
+      CK(cudaStreamSynchronize(ctx->stream));
+      int best = 0, bad = 0;
+      for (int r = 0; r < nruns; ++r) {
+         const VnsResultDev &q = slots[r].res;
+         if (q.status) bad = q.status;
+         if (results) {
+            vnsgpu_vns_result &o = results[r];
+            o.num_iters = q.num_iters; o.num_iters_last_impr = q.num_iters_last_impr; o.n_improvements = q.n_improvements;
+            o.status = q.status; o.reward = q.reward; o.length = q.length; o.time_ms = q.time_ms;
+            o.time_last_impr_ms = q.time_last_impr_ms; o.proposals = q.proposals; o.evals = q.evals; o.accepts = q.accepts;
+         }
+         const VnsResultDev &bq = slots[best].res;
+         if (q.reward > bq.reward || (q.reward == bq.reward && q.length < bq.length)) best = r;
+      }
+      if (best_run) *best_run = best;
+      s = vnsgpu_path_copy(ctx, path, first + 2 * best);      // the best tour replaces `path`
+      if (!s) CK(cudaStreamSynchronize(ctx->stream));
+      if (!s && bad) s = fail(ctx, bad == 4 ? VNSGPU_E_INCONSISTENT : VNSGPU_E_STATE, "device-side error flag in vns_run_batch");
+   }
+   cudaStreamSynchronize(ctx->stream);
+   while ((int)ctx->paths.size() > first) { cudaFree(ctx->paths.back().block); ctx->paths.pop_back(); }
+   cudaFree(d_segs); cudaFree(d_slots);
+   return s;
 }
 
 } // extern "C"

@@ -426,9 +426,9 @@ __global__ void __launch_bounds__(VNS_CH_THREADS) k_chain_ls(InstDev I, const V 
 //      run out of shared memory, shake / fit / greedy / path copies are the global-memory routines of
 //      search.cuh (once per VNS step) --------------------------------------------------------------------
 template <typename V, int G, int NR>
-__global__ void __launch_bounds__(VNS_CH_THREADS) k_chain_vns_run(InstDev I, const V *__restrict__ Dv, PathDev tour, PathDev act,
-                                                                  VnsParamsDev prm, RngState *rng, VnsResultDev *res, double *impr_reward,
-                                                                  double *impr_length, double *impr_ms, int *seg, long long *prof)
+__device__ void chain_vns_body(const InstDev &I, const V *__restrict__ Dv, const PathDev &tour, const PathDev &act, const VnsParamsDev &prm,
+                               RngState *rng, VnsResultDev *res, double *impr_reward, double *impr_length, double *impr_ms, int *seg,
+                               long long *prof)
 {
    extern __shared__ __align__(16) unsigned char smem_c[];
    __shared__ ChainCtl ctl;
@@ -506,7 +506,32 @@ __global__ void __launch_bounds__(VNS_CH_THREADS) k_chain_vns_run(InstDev I, con
       res->time_ms = now_ms() - t0; res->time_last_impr_ms = t_last;
       res->proposals = ctl.st.proposals; res->evals = ctl.st.evals; res->accepts = ctl.st.accepts;
       *rng = g;
-      for (int q = 0; q < 4; ++q) prof[q] += ctl.prof[q];
+      if (prof)
+         for (int q = 0; q < 4; ++q) prof[q] += ctl.prof[q];
    }
    __syncthreads();
+}
+
+template <typename V, int G, int NR>
+__global__ void __launch_bounds__(VNS_CH_THREADS) k_chain_vns_run(InstDev I, const V *__restrict__ Dv, PathDev tour, PathDev act,
+                                                                  VnsParamsDev prm, RngState *rng, VnsResultDev *res, double *impr_reward,
+                                                                  double *impr_length, double *impr_ms, int *seg, long long *prof)
+{
+   chain_vns_body<V, G, NR>(I, Dv, tour, act, prm, rng, res, impr_reward, impr_length, impr_ms, seg, prof);
+}
+
+// Multi-start (the reference's --batch=N: N independent solves, algorithm.cc:120-161): one CTA per run,
+// each with its own seed, paths and scratch; no communication between runs.
+struct VnsRunSlot {
+   PathDev tour, act;
+   RngState rng;
+   VnsResultDev res;
+   int *seg;
+};
+
+template <typename V, int G, int NR>
+__global__ void __launch_bounds__(VNS_CH_THREADS) k_chain_vns_multi(InstDev I, const V *__restrict__ Dv, VnsRunSlot *slots, VnsParamsDev prm)
+{
+   VnsRunSlot &sl = slots[blockIdx.x];
+   chain_vns_body<V, G, NR>(I, Dv, sl.tour, sl.act, prm, &sl.rng, &sl.res, nullptr, nullptr, nullptr, sl.seg, nullptr);
 }

@@ -82,6 +82,7 @@ _SIGS = {
     "vnsgpu_fit_to_budget": [vp, C.c_int, C.c_double],
     "vnsgpu_greedy": [vp, C.c_int, C.c_double],
     "vnsgpu_vns_run": [vp, C.c_int, C.POINTER(VnsParams), C.POINTER(VnsResult), dp, dp, dp],
+    "vnsgpu_vns_run_batch": [vp, C.c_int, C.c_int, C.POINTER(C.c_uint32), C.POINTER(VnsParams), C.POINTER(VnsResult), ip],
 }
 EXPORTS = sorted(list(_SIGS) + ["vnsgpu_destroy", "vnsgpu_last_error", "vnsgpu_version", "vnsgpu_launch_count",
                                 "vnsgpu_table_bytes", "vnsgpu_rng_seed", "vnsgpu_rng_next"])
@@ -417,3 +418,16 @@ class VnsSopPath:
         self.e._ck(self.lib.vnsgpu_vns_run(self.e.h, self.h, C.byref(prm), C.byref(res), _d(ir), _d(il), _d(it)))
         n = min(res.n_improvements, max_improvements)
         return res, list(zip(ir[:n], il[:n], it[:n]))
+
+    def vns_run_batch(self, seeds, num_iterations=2000, num_iterations_unimproved=1000, skip=1, greedy=1, budget=None,
+                      max_time_ms=0.0):
+        """Multi-start (the reference's --batch=N): one device chain per seed in ONE launch ->
+        (list of VnsResult, index of the best run); the best tour replaces this path."""
+        budget = self.e.pb.budget if budget is None else budget
+        prm = VnsParams(num_iterations, num_iterations_unimproved, skip, greedy, budget, max_time_ms, 0, 0)
+        n = len(seeds)
+        sd = (C.c_uint32 * n)(*[int(x) for x in seeds])
+        res = (VnsResult * n)()
+        best = C.c_int(-1)
+        self.e._ck(self.lib.vnsgpu_vns_run_batch(self.e.h, self.h, n, sd, C.byref(prm), res, C.byref(best)))
+        return list(res), best.value
