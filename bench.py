@@ -251,6 +251,19 @@ class ClockSampler:
             self.proc.terminate()
 
 
+def ncu_traffic(workload, batch):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel for one launch of this batch size,
+    from the committed ncu --set full capture (profiles/ncu_traffic.json, written by scripts/ncu_extract.py)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as fh:
+            t = json.load(fh)
+        if t.get("workload") == workload and int(t.get("batch", -1)) == batch:
+            return float(t["dram_bytes_per_launch"])
+    except (OSError, ValueError, KeyError):
+        pass
+    return None
+
+
 def measured_hbm_peak():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
@@ -390,6 +403,24 @@ def run_b200(args):
         e2e = {"value": world * n * K / dt, "unit": "evals/s", "h2d_bytes_per_step": world * n * 16,
                "d2h_bytes_per_step": world * (n * 9 + 8), "ms_per_step": 1e3 * dt / K,
                "call": "vnsgpu_eval_batch (pinned host candidates in; lengths + flags + first accepted index out)"}
+        # what the link alone allows: the same buffers copied with nothing else running (explains e2e vs value)
+        d_tmp = torch.empty(n * 16, dtype=torch.uint8, device=dev)
+        h_tmp = h_c
+        evs = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        d_tmp.copy_(h_tmp, non_blocking=True)
+        torch.cuda.synchronize()
+        evs[0].record()
+        for _ in range(4):
+            d_tmp.copy_(h_tmp, non_blocking=True)
+        evs[1].record()
+        for _ in range(4):
+            h_len.copy_(d_len, non_blocking=True)
+        evs[2].record()
+        torch.cuda.synchronize()
+        e2e["pcie_h2d_gbs"] = 4 * n * 16 / (evs[0].elapsed_time(evs[1]) * 1e-3) / 1e9
+        e2e["pcie_d2h_gbs"] = 4 * n * 8 / (evs[1].elapsed_time(evs[2]) * 1e-3) / 1e9
+        e2e["copy_bound_ms_per_step"] = max(n * 16 / e2e["pcie_h2d_gbs"], (n * 9 + 8) / e2e["pcie_d2h_gbs"]) * 1e-6
+        del d_tmp
         if world == 1:
             assert first.value == first_dev, "host and device entry points disagree on the first accepted candidate"
         assert torch.equal(h_len[:4096], d_len[:4096].cpu()), "host and device entry points disagree"
@@ -415,7 +446,7 @@ def run_b200(args):
                                "N > 1 adds one 8-byte all-reduce(MIN) per step for the chosen move"},
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_src, "kernel": "k_eval_groups",
+                     "traffic": ncu_traffic(args.workload, n), "peak_source": peak_src, "kernel": "k_eval_groups",
                      "kernel_ms": kern_ms, "algorithmic_bytes_per_launch": int(alg_bytes),
                      "algorithmic_bytes_per_candidate": alg_bytes / n,
                      "algorithmic_bytes_per_candidate_at_8B_per_entry": alg_bytes_f64 / n,

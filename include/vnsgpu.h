@@ -135,6 +135,8 @@ int64_t vnsgpu_table_bytes(const vnsgpu_ctx *ctx);
 
 /* ---- paths: value-type VnsSopPath objects become handles (copy = device memcpy) -------------- */
 vnsgpu_status vnsgpu_path_create(vnsgpu_ctx *ctx, int *path);
+/* ~VnsSopPath: frees the handle's device memory; the handle value may be handed out again */
+vnsgpu_status vnsgpu_path_destroy(vnsgpu_ctx *ctx, int path);
 vnsgpu_status vnsgpu_path_copy(vnsgpu_ctx *ctx, int dst, int src);
 /* targets := vns[0..T) and full update() (vns_sop_path.cpp:1321-1404); vns = the solver's VNS vector */
 vnsgpu_status vnsgpu_path_set(vnsgpu_ctx *ctx, int path, const int *vns, int nvns, int T);
@@ -196,9 +198,10 @@ vnsgpu_status vnsgpu_vns_run(vnsgpu_ctx *ctx, int path, const vnsgpu_vns_params 
 /* Multi-start = the reference's --batch=N (N independent solves with different seeds, crl
  * algorithm.cc:120-161) as ONE launch: one thread block per run, each a trajectory-exact replica of a
  * seeded reference run.  Every run starts from `path`'s state; results[r] belongs to seeds[r]; the best
- * tour (max reward, then min length) is copied into `path` and its index returned in *best_run. */
+ * tour (max reward, then min length) is copied into `path` and its index returned in *best_run.
+ * tour_paths (may be NULL): nruns handles that receive every run's final tour; the caller destroys them. */
 vnsgpu_status vnsgpu_vns_run_batch(vnsgpu_ctx *ctx, int path, int nruns, const uint32_t *seeds, const vnsgpu_vns_params *params,
-                                   vnsgpu_vns_result *results, int *best_run);
+                                   vnsgpu_vns_result *results, int *best_run, int *tour_paths);
 
 #ifdef __cplusplus
 }

@@ -7,4 +7,6 @@ timeout 600 python bench.py --workload vm1084 --no-solve --cpu-sample 262144 > g
 timeout 300 python bench.py --workload vm1084 --impl reference --ref-batch 65536 --steps 5 > gpurun_out/bench_ref_vm1084_$TAG.json 2> gpurun_out/bench_ref_vm1084_$TAG.err
 BC="python bench.py --steps 2 --warmup 1 --no-cpu --no-solve --no-e2e --batch 1048576"
 timeout 300 $BC > gpurun_out/plain.log 2>&1 && timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_$TAG.csv $BC > gpurun_out/ncu1.log 2>&1
-timeout 300 $BC > gpurun_out/plain2.log 2>&1 && timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_eval_ -s 1 -c 2 -o gpurun_out/prof_eval_$TAG $BC > gpurun_out/ncu2.log 2>&1
+# full capture of the dominant kernel at bench.py's DEFAULT batch (roofline.traffic is per launch of that size)
+BF="python bench.py --steps 2 --warmup 1 --no-cpu --no-solve --no-e2e"
+timeout 300 $BF > gpurun_out/plain2.log 2>&1 && timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_eval_groups -s 1 -c 1 -o gpurun_out/prof_eval_$TAG $BF > gpurun_out/ncu2.log 2>&1

@@ -34,5 +34,22 @@ def build(force=False, verbose=False):
     return LIB
 
 
+HOST = os.path.join(HERE, "host")
+CLI = os.path.join(HERE, "sop_vns_b200")
+
+
+def build_cli(force=False):
+    """The reference-compatible command line (host/sop_vns_b200.cpp) linked against libvnsgpu.so."""
+    srcs = [os.path.join(HOST, f) for f in sorted(os.listdir(HOST))] + [os.path.join(HERE, "..", "include", f) for f in ("vnsgpu.h", "vnsgpu_path.hpp")]
+    if not force and os.path.exists(CLI) and all(os.path.getmtime(s) <= os.path.getmtime(CLI) for s in srcs + [LIB]):
+        return CLI
+    cxx = os.environ.get("VNSGPU_CXX", "/usr/bin/g++")
+    cmd = [cxx, "-O2", "-std=c++17", "-Wall", "-I", os.path.join(HERE, "..", "include"), "-I", HOST,
+           os.path.join(HOST, "sop_vns_b200.cpp"), "-o", CLI, "-L", HERE, "-lvnsgpu", "-Wl,-rpath,$ORIGIN"]
+    subprocess.check_call(cmd)
+    return CLI
+
+
 if __name__ == "__main__":
     print(build(force=True, verbose=True))
+    print(build_cli(force=True))

@@ -3,7 +3,7 @@
 static bool path_ok(vnsgpu_ctx *ctx, int path)
 {
    if (!ctx->have_table) { ctx->err = "no distance table"; return false; }
-   if (path < 0 || path >= (int)ctx->paths.size()) { ctx->err = "bad path handle"; return false; }
+   if (path < 0 || path >= (int)ctx->paths.size() || !ctx->paths[path].block) { ctx->err = "bad path handle"; return false; }
    return true;
 }
 
@@ -62,11 +62,28 @@ vnsgpu_status vnsgpu_path_create(vnsgpu_ctx *ctx, int *path)
    ph.d.tg = (int *)(b + o_tg); ph.d.vns = (int *)(b + o_vns);
    ph.d.F = (double *)(b + o_F); ph.d.B = (double *)(b + o_B);
    ph.d.minF = (double *)(b + o_minF); ph.d.minB = (double *)(b + o_minB);
-   ctx->paths.push_back(ph);
-   *path = (int)ctx->paths.size() - 1;
+   int slot = -1;   // reuse a destroyed handle's slot
+   for (size_t k = 0; k < ctx->paths.size() && slot < 0; ++k)
+      if (!ctx->paths[k].block) slot = (int)k;
+   if (slot < 0) {
+      ctx->paths.push_back(ph);
+      slot = (int)ctx->paths.size() - 1;
+   } else
+      ctx->paths[slot] = ph;
+   *path = slot;
    k_path_update<<<1, 64, 0, ctx->stream>>>(ctx->I, ph.d);   // empty path start -> goal
    LAUNCHED(ctx);
    CK(cudaStreamSynchronize(ctx->stream));
+   return VNSGPU_OK;
+}
+
+vnsgpu_status vnsgpu_path_destroy(vnsgpu_ctx *ctx, int path)
+{
+   CK(cudaSetDevice(ctx->device));
+   if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
+   CK(cudaStreamSynchronize(ctx->stream));
+   CK(cudaFree(ctx->paths[path].block));
+   ctx->paths[path] = PathHost();
    return VNSGPU_OK;
 }
 

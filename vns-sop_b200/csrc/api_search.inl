@@ -228,16 +228,14 @@ vnsgpu_status vnsgpu_vns_run(vnsgpu_ctx *ctx, int path, const vnsgpu_vns_params 
       result->time_last_impr_ms = r.time_last_impr_ms;
       result->proposals = r.proposals; result->evals = r.evals; result->accepts = r.accepts;
    }
-   // release the work path (it is the last handle)
-   cudaFree(ctx->paths[work].block);
-   ctx->paths.pop_back();
+   vnsgpu_path_destroy(ctx, work);
    if (r.status == 4) return fail(ctx, VNSGPU_E_INCONSISTENT, "inconsistent path length in improved tour");
    if (r.status) return fail(ctx, VNSGPU_E_STATE, "device-side error flag in vns_run");
    return VNSGPU_OK;
 }
 
 vnsgpu_status vnsgpu_vns_run_batch(vnsgpu_ctx *ctx, int path, int nruns, const uint32_t *seeds, const vnsgpu_vns_params *p,
-                                   vnsgpu_vns_result *results, int *best_run)
+                                   vnsgpu_vns_result *results, int *best_run, int *tour_paths)
 {
    CK(cudaSetDevice(ctx->device));
    if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
@@ -248,7 +246,7 @@ vnsgpu_status vnsgpu_vns_run_batch(vnsgpu_ctx *ctx, int path, int nruns, const u
    if (!as_int && !(chain_fits<double>(ctx, &smem) && smem + extra + sizeof(ChainCtl) + 1024 <= (size_t)ctx->max_smem))
       return fail(ctx, VNSGPU_E_STATE, "instance too large for the shared-memory chain: use vnsgpu_vns_run per seed");
    // two paths per run (tourVNSGOPPath, actualVNSGOPPath), every tour a copy of `path`
-   const int first = (int)ctx->paths.size();
+   std::vector<int> tours(nruns, -1), acts(nruns, -1);
    std::vector<VnsRunSlot> slots(nruns);
    int *d_segs = nullptr;
    VnsRunSlot *d_slots = nullptr;
@@ -260,6 +258,7 @@ vnsgpu_status vnsgpu_vns_run_batch(vnsgpu_ctx *ctx, int path, int nruns, const u
       s = vnsgpu_path_create(ctx, &a);
       if (!s) s = vnsgpu_path_create(ctx, &b);
       if (!s) s = vnsgpu_path_copy(ctx, a, path);
+      tours[r] = a; acts[r] = b;
       if (s) break;
       slots[r].tour = ctx->paths[a].d; slots[r].act = ctx->paths[b].d;
       rng_seed_host(slots[r].rng, seeds[r]);
@@ -292,12 +291,16 @@ vnsgpu_status vnsgpu_vns_run_batch(vnsgpu_ctx *ctx, int path, int nruns, const u
          if (q.reward > bq.reward || (q.reward == bq.reward && q.length < bq.length)) best = r;
       }
       if (best_run) *best_run = best;
-      s = vnsgpu_path_copy(ctx, path, first + 2 * best);      // the best tour replaces `path`
+      s = vnsgpu_path_copy(ctx, path, tours[best]);      // the best tour replaces `path`
       if (!s) CK(cudaStreamSynchronize(ctx->stream));
       if (!s && bad) s = fail(ctx, bad == 4 ? VNSGPU_E_INCONSISTENT : VNSGPU_E_STATE, "device-side error flag in vns_run_batch");
    }
    cudaStreamSynchronize(ctx->stream);
-   while ((int)ctx->paths.size() > first) { cudaFree(ctx->paths.back().block); ctx->paths.pop_back(); }
+   for (int r = 0; r < nruns; ++r) {
+      if (acts[r] >= 0) vnsgpu_path_destroy(ctx, acts[r]);
+      if (tours[r] >= 0 && (s || !tour_paths)) vnsgpu_path_destroy(ctx, tours[r]);
+      if (tour_paths) tour_paths[r] = s ? -1 : tours[r];
+   }
    cudaFree(d_segs); cudaFree(d_slots);
    return s;
 }

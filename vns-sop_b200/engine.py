@@ -82,7 +82,8 @@ _SIGS = {
     "vnsgpu_fit_to_budget": [vp, C.c_int, C.c_double],
     "vnsgpu_greedy": [vp, C.c_int, C.c_double],
     "vnsgpu_vns_run": [vp, C.c_int, C.POINTER(VnsParams), C.POINTER(VnsResult), dp, dp, dp],
-    "vnsgpu_vns_run_batch": [vp, C.c_int, C.c_int, C.POINTER(C.c_uint32), C.POINTER(VnsParams), C.POINTER(VnsResult), ip],
+    "vnsgpu_vns_run_batch": [vp, C.c_int, C.c_int, C.POINTER(C.c_uint32), C.POINTER(VnsParams), C.POINTER(VnsResult), ip, ip],
+    "vnsgpu_path_destroy": [vp, C.c_int],
 }
 EXPORTS = sorted(list(_SIGS) + ["vnsgpu_destroy", "vnsgpu_last_error", "vnsgpu_version", "vnsgpu_launch_count",
                                 "vnsgpu_table_bytes", "vnsgpu_rng_seed", "vnsgpu_rng_next"])
@@ -429,5 +430,5 @@ class VnsSopPath:
         sd = (C.c_uint32 * n)(*[int(x) for x in seeds])
         res = (VnsResult * n)()
         best = C.c_int(-1)
-        self.e._ck(self.lib.vnsgpu_vns_run_batch(self.e.h, self.h, n, sd, C.byref(prm), res, C.byref(best)))
+        self.e._ck(self.lib.vnsgpu_vns_run_batch(self.e.h, self.h, n, sd, C.byref(prm), res, C.byref(best), None))
         return list(res), best.value
