@@ -41,8 +41,13 @@ WORKLOADS = {
     "berlin52": ("11berlin52_T60_p2", os.path.join(ROOT, "tests", "golden", "berlin52.npz")),
     "opn_s08": ("tsiligirides_problem_2_budget_30_d_50_s_08", os.path.join(ROOT, "tests", "golden", "opn_s08.npz")),
     "dop_s12": ("tsiligirides_problem_2_budget_30_r_50_s_12", os.path.join(ROOT, "tests", "golden", "dop_s12.npz")),
+    # BASELINE.json config 5: generated (vns-sop_b200/synthetic.py), table far beyond L2 - the HBM regime
+    "synth20k": ("synthetic scaled SOP: 20000 nodes / 2000 clusters of 10, CEIL_2D (generated, seed 20190147)", None, {"n_points": 20000}),
+    "synth2k": ("synthetic scaled SOP: 2000 nodes / 200 clusters of 10, CEIL_2D (generated, seed 20190147)", None, {"n_points": 2000}),
 }
 STATE = "the greedy initial tour (greedy_insertion, vns_sop_solver.cpp:1091-1155; SURVEY.md 8d)"
+STATE_SYNTH = ("nearest-neighbour tour over the cluster centroids cut at 85% of the budget (greedy_insertion is "
+               "O(C^3) evaluations at this size; synthetic.centroid_tour_state)")
 FALLBACK_HBM_GBS = 6650.0   # /opt/skills/guides/B200_PROFILING.md "FALLBACK"
 
 
@@ -92,30 +97,48 @@ def make_candidates(n, vns, T, seed):
 
 def load_workload(name):
     from vns_sop_b200 import instances as ins
-    sf = ins.load_npz(WORKLOADS[name][1])
+    if WORKLOADS[name][1] is None:
+        from vns_sop_b200 import synthetic
+        sf = synthetic.generate(**WORKLOADS[name][2])
+    else:
+        sf = ins.load_npz(WORKLOADS[name][1])
     return sf, ins.build_problem(sf)
+
+
+def workload_state(name, pb):
+    """(vns, T) the candidates are drawn against, or None = run greedy_insertion (dataset instances)."""
+    if WORKLOADS[name][1] is None:
+        from vns_sop_b200 import synthetic
+        return synthetic.centroid_tour_state(pb)
+    return None
+
+
+def state_text(name):
+    return STATE_SYNTH if WORKLOADS[name][1] is None else STATE
 
 
 class CpuEvaluator:
     """The CPU side: the reference's own code when oracle/_ref was built (kind "reference"), else the
     C port (kind "port").  TEST/BASELINE infrastructure - never on the product path."""
 
-    def __init__(self, sf, pb):
+    def __init__(self, sf, pb, state=None):
         from oracle import binding as ob
-        self.kind = "reference" if ob.RefOracle.available() else "port"
+        # the reference's 4-deep vector table (x4 by-value copies) needs tens of GB beyond ~5000 samples
+        self.kind = "reference" if ob.RefOracle.available() and pb.N <= 5000 else "port"
         if self.kind == "reference":
             from vns_sop_b200 import instances as ins
             self.tmp = tempfile.NamedTemporaryFile(suffix=".sop", delete=False)
             self.tmp.close()
             ins.write_sop(sf, self.tmp.name)            # /root/reference does not exist on the GPU box
             self.o = ob.RefOracle(self.tmp.name)
+        else:
+            self.o = ob.Oracle(pb)
+        if state is None:
             self.p = self.o.path()
             self.p.greedy()
         else:
-            self.o = ob.Oracle(pb)
-            self.p = self.o.path()
-            self.p.greedy()
-        self.vns, self.T = self.p.vns, self.p.T
+            self.p = self.o.path(np.ascontiguousarray(state[0], np.int32), int(state[1]))
+        self.vns, self.T = np.asarray(self.p.vns), int(self.p.T)
 
     def eval(self, cands):
         return self.p.eval_batch(cands)
@@ -126,8 +149,9 @@ _W = {}
 
 
 def _worker_init(workload):
-    sf, pb = load_workload(workload)
-    _W["ev"] = CpuEvaluator(sf, pb)
+    if "ev" not in _W:          # normally inherited from the parent through fork (one table, shared pages)
+        sf, pb = load_workload(workload)
+        _W["ev"] = CpuEvaluator(sf, pb, workload_state(workload, pb))
 
 
 def _worker_eval(cands):
@@ -154,6 +178,7 @@ def run_reference(args):
     import multiprocessing as mp
     cores = host_cores()
     name = WORKLOADS[args.workload][0]
+    _worker_init(args.workload)
     with mp.get_context("fork").Pool(cores, initializer=_worker_init, initargs=(args.workload,)) as pool:
         kind, vns, T = pool.map(_worker_state, [0])[0]
         n = args.ref_batch
@@ -171,7 +196,7 @@ def run_reference(args):
         "impl": "reference", "metric": "candidate_move_evals_per_sec", "value": v, "unit": "evals/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": name, "candidates_per_step": n, "state": STATE,
+        "config": {"workload": name, "candidates_per_step": n, "state": state_text(args.workload),
                    "outputs": "length + lower bound per candidate"},
         "cpu_baseline": {"value": v, "unit": "evals/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": v, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -272,8 +297,9 @@ def measured_hbm_peak():
         return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
 
 
-def prepare_gpu_state(eng):
-    from vns_sop_b200 import engine
+def prepare_gpu_state(eng, state=None):
+    if state is not None:
+        return eng.path(np.ascontiguousarray(state[0], np.int32), int(state[1]))
     p = eng.path()
     p.greedy_insertion()
     return p
@@ -319,8 +345,21 @@ def run_b200(args):
     sf, pb = load_workload(args.workload)
     eng = engine.Engine(local).load_problem(pb)
     lib = eng.lib
-    p = prepare_gpu_state(eng)
+    state = workload_state(args.workload, pb)
+    p = prepare_gpu_state(eng, state)
     vns, T = p.vns, p.getNumTargets()
+    table_build = None
+    if pb.xy is not None:       # a1: the pairwise table kernel + bounds (+ int32 copy), buffers already allocated
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        eng.build_table_euclid(pb.xy, pb.rule)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        p = prepare_gpu_state(eng, (vns, T))
+        table_build = {"ms": 1e3 * dt, "entries": int(pb.N) ** 2, "table_bytes": int(eng.table_bytes),
+                       "written_gbs": eng.table_bytes / dt / 1e9,
+                       "what": "vnsgpu_build_table_euclid: H2D of the coordinates, pairwise kernel (8 B/entry written), "
+                               "bounds pass (8 B/entry read), int32 copy (8 B read + 4 B written); wall clock of the call"}
     n, K, W = args.batch, args.steps, args.warmup
     rows = make_candidates(n, vns, T, 1000 + rank)          # each rank owns its shard of the candidates
     cands = p.make_cands(rows)
@@ -425,6 +464,7 @@ def run_b200(args):
             assert first.value == first_dev, "host and device entry points disagree on the first accepted candidate"
         assert torch.equal(h_len[:4096], d_len[:4096].cpu()), "host and device entry points disagree"
 
+    hbm_regime = eng.table_bytes / 2 > 126e6
     peak, peak_src = measured_hbm_peak()
     achieved = alg_bytes / (kern_ms * 1e-3) / 1e9
     line = {
@@ -434,11 +474,13 @@ def run_b200(args):
         "data": "synthetic",
         "config": {"workload": WORKLOADS[args.workload][0], "clusters": int(pb.C), "samples": int(pb.N),
                    "candidates_per_step_per_gpu": n, "targets_in_path": int(T),
-                   "state": STATE,
+                   "state": state_text(args.workload),
                    "mix": "50% insertRandom proposals (MOVE/ADD), 50% exchangeRandom (EXCHANGE/REPLACE)",
                    "outputs": "length + lower bound + flags per candidate, first accepted index",
-                   "l2": "candidates + results = %.0f MB per step > 126 MB L2 (streamed); the %.2f MB distance "
-                         "table is cache-resident by design" % (n * 33 / 1e6, eng.table_bytes / 1e6),
+                   "l2": ("candidates + results = %.0f MB per step > 126 MB L2 (streamed); the %.2f MB distance "
+                          "table is cache-resident by design" % (n * 33 / 1e6, eng.table_bytes / 1e6)) if not hbm_regime else
+                         ("the table read by the kernel (%.0f MB at %d B/entry, plus the segment products) is far beyond the "
+                          "126 MB L2: blocks are gathered from HBM" % (eng.table_bytes / 8 * (4 if int_path else 8) / 1e6, 4 if int_path else 8)),
                    "evaluation": "sub-warp groups, batch sorted by chain length on the device, %s" %
                                  ("exact int32 DPX arithmetic + exact segment products (rebuilt every step)" if int_path
                                   else "IEEE double, block by block"),
@@ -451,17 +493,20 @@ def run_b200(args):
                      "algorithmic_bytes_per_candidate": alg_bytes / n,
                      "algorithmic_bytes_per_candidate_at_8B_per_entry": alg_bytes_f64 / n,
                      "stream_bytes_per_candidate": 33,
-                     "working_set": "L1/L2-resident table (%.2f MB): the HBM traffic is the 16 B descriptor + 17 B of "
-                                    "results per candidate, so this fraction is NOT an HBM-bandwidth claim" % (eng.table_bytes / 1e6),
+                     "working_set": ("L1/L2-resident table (%.2f MB): the HBM traffic is the 16 B descriptor + 17 B of "
+                                     "results per candidate, so this fraction is NOT an HBM-bandwidth claim" % (eng.table_bytes / 1e6))
+                                    if not hbm_regime else "HBM-resident table (%.0f MB as doubles): block gathers miss L2" % (eng.table_bytes / 1e6),
                      "note": "achieved = algorithmic bytes (SURVEY.md 8d: every distance-block entry of the reference's chain "
                              "once at the width the kernel reads, + first F row + last B row + result) / time of one step "
                              "(sort + segment products + evaluation kernels, CUDA events).  With the segment products the "
                              "kernel reads FEWER table bytes than this reference-chain figure; see DESIGN.md 5"},
         "accepted_in_batch": ok_flags, "first_accept": first_dev,
     }
+    if table_build:
+        line["table_build"] = table_build
     if rank == 0 and world == 1 and not args.no_cpu:
-        line["cpu_baseline"] = cpu_baseline_leg(args, sf, pb, vns, T, rows, d_len, d_lb)
-    if rank == 0 and world == 1 and not args.no_solve:
+        line["cpu_baseline"] = cpu_baseline_leg(args, sf, pb, vns, T, rows, d_len, d_lb, state)
+    if rank == 0 and world == 1 and not args.no_solve and state is None:
         line["time_to_reward"] = solve_leg(args, eng, sf, pb)
     if sampler:
         sampler.stop()
@@ -472,10 +517,10 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
-def cpu_baseline_leg(args, sf, pb, vns, T, rows, d_len, d_lb):
+def cpu_baseline_leg(args, sf, pb, vns, T, rows, d_len, d_lb, state=None):
     """The CPU checker timed on ONE host core on a bounded sample of the batch the GPU just evaluated;
     its lengths and lower bounds must equal the GPU's bit for bit."""
-    ev = CpuEvaluator(sf, pb)
+    ev = CpuEvaluator(sf, pb, state)
     assert ev.T == T and (ev.vns == vns).all(), "CPU and GPU search states differ"
     ns = min(args.cpu_sample, len(rows))
     sample = np.ascontiguousarray(rows[:ns])

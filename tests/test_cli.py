@@ -123,7 +123,7 @@ def _solve(cli, f, out, *extra):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name,loop", [("berlin52", 1), ("berlin52", 0), ("opn_s08", 1), ("dop_s08", 1), ("dop_s08", 0), ("krob200", 1)])
+@pytest.mark.parametrize("name,loop", [("berlin52", 1), ("berlin52", 0), ("opn_s08", 1), ("dop_s12", 1), ("dop_s12", 0), ("krob200", 1)])
 def test_seeded_solve_writes_the_reference_record(cli, golden, name, loop, tmp_path):
     sf, f = write_fixture(name, tmp_path)
     out = str(tmp_path / "gpu")

@@ -1,0 +1,145 @@
+"""Synthetic scaled instances (BASELINE.json config 5; vns-sop_b200/synthetic.py).  CPU: the generator is
+deterministic, produces a well-formed .sop and survives a write/parse round trip.  GPU: a 2000-node /
+200-cluster instance (same construction as the 20k-node bench workload, small enough for the CPU oracle)
+against the oracle - table, bounds, DP vectors, every tryTo* / lower bound on long tours, a seeded
+shake + local-search sequence - and size-independent properties of the 20k-node instance itself."""
+import numpy as np
+import pytest
+
+from conftest import random_candidates
+
+
+def test_generator_is_deterministic_and_well_formed(tmp_path):
+    from vns_sop_b200 import instances as ins, synthetic as sy
+    a, b = sy.generate(2000, 10), sy.generate(2000, 10)
+    assert (a.coords == b.coords).all() and a.tmax == b.tmax
+    assert all((x == y).all() for x, y in zip(a.set_nodes, b.set_nodes))
+    assert len(a.set_nodes) == 201 and len(a.set_nodes[0]) == 1 and a.start_set == a.end_set == 0
+    allnodes = np.concatenate(a.set_nodes)
+    assert sorted(allnodes.tolist()) == list(range(2001))          # every node in exactly one set
+    assert (a.set_profit[1:] == 10).all() and a.set_profit[0] == 0  # rule p1: profit = cluster size
+    f = str(tmp_path / "s.sop")
+    ins.write_sop(a, f)
+    c = ins.parse_sop(f)
+    assert (c.coords == a.coords).all() and c.tmax == a.tmax and c.edge_weight_type == "CEIL_2D"
+    pb = ins.build_problem(c)
+    assert pb.C == 202 and pb.N == 2002 and pb.m.max() == 10
+    vns, T = sy.centroid_tour_state(pb)
+    assert sorted(vns.tolist()) == list(range(1, 201)) and 20 < T < 200
+    r = sy.generate(2000, 10, random_clusters=True)
+    assert r.name.endswith("_RND") and not all((x == y).all() for x, y in zip(a.set_nodes, r.set_nodes))
+    # proximity clusters are compact, random ones are not
+    spread = lambda sf: np.mean([sf.coords[s].std(0).sum() for s in sf.set_nodes[1:]])
+    assert spread(a) < 0.25 * spread(r)
+
+
+@pytest.fixture(scope="module")
+def synth():
+    from oracle import binding as ob
+    from vns_sop_b200 import engine, instances as ins, synthetic as sy
+    sf = sy.generate(2000, 10)
+    pb = ins.build_problem(sf)
+    e = engine.Engine(0).load_problem(pb)
+    o = ob.Oracle(pb)
+    yield e, o, pb, sy.centroid_tour_state(pb)
+    e.close()
+
+
+@pytest.mark.gpu
+def test_synthetic_table_bounds_and_dp(synth):
+    e, o, pb, (vns, T) = synth
+    assert (e.table_dense() == o.dense()).all()
+    lo, hi = e.bounds()
+    olo, ohi = o.bounds()
+    assert (lo == olo).all() and (hi == ohi).all()
+    pg, po = e.path(vns, T), o.path(vns, T)
+    assert pg.getPathLength() == po.length() and pg.getPathLengthRear() == po.length_rear() and pg.getReward() == po.reward()
+    F, B = pg.layers()
+    oF, oB = po.layers()
+    for l in range(T + 2):
+        k = 1 if l in (0, T + 1) else 10
+        assert (F[l, :k] == oF[l, :k]).all() and (B[l, :k] == oB[l, :k]).all(), l
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("int_path", [True, False])
+def test_synthetic_long_tour_candidates(synth, int_path):
+    """T = O(100) targets: MOVE / EXCHANGE chains of up to ~T blocks, with and without the segment products."""
+    e, o, pb, (vns, T) = synth
+    pg, po = e.path(vns, T), o.path(vns, T)
+    rs = np.random.RandomState(5)
+    cands = random_candidates(rs, vns, T, 40000)
+    oln, olb = po.eval_batch(cands)
+    e.set_int_path(int_path)
+    try:
+        for seg in (True, False):
+            e.set_segment_cache(seg)
+            ln, lb, fl, first = pg.eval_batch(pg.make_cands(cands))
+            assert (ln == oln).all() and (lb == olb).all(), (int_path, seg)
+    finally:
+        e.set_int_path(True)
+        e.set_segment_cache(True)
+
+
+@pytest.mark.gpu
+def test_synthetic_shake_and_local_search(synth):
+    from oracle import binding as ob
+    from vns_sop_b200 import engine
+    e, o, pb, (vns, T) = synth
+    pg, po = e.path(vns, T), o.path(vns, T)
+    pg.fitDOPtoBudget()
+    po.fit()
+    rg, ro = engine.seeded_rng(11), ob.new_rng(11)
+    for k in (1, 2, 1, 2):
+        pg.shake(k, rg)
+        po.shake(k, ro)
+        assert (pg.vns == po.vns).all() and pg.getNumTargets() == po.T
+        pg._ls(k, 4000, rg, None, 1)
+        po.local_search(k, 4000, ro)
+        assert (pg.vns == po.vns).all() and pg.getNumTargets() == po.T
+        assert pg.getPathLength() == po.length() and pg.getReward() == po.reward()
+    assert engine.rng_next(rg) == ob.rng_next(ro)
+
+
+@pytest.mark.gpu
+def test_20k_instance_properties():
+    """The bench workload itself (3.2 GB table, HBM regime): no oracle at this size inside the test budget, so
+    size-independent properties - the table's block-major gather equals direct evaluation on sampled entries,
+    forward == backward length, REMOVE then ADD-back identities, lower bound <= value, exact-int and double
+    evaluation agree bit for bit, segment products on/off agree."""
+    from vns_sop_b200 import engine, instances as ins, synthetic as sy
+    sf = sy.generate()
+    pb = ins.build_problem(sf)
+    e = engine.Engine(0).load_problem(pb)
+    try:
+        vns, T = sy.centroid_tour_state(pb)
+        p = e.path(vns, T)
+        assert p.getPathLength() == p.getPathLengthRear() > 0
+        cl, nd, calc = p.getPath()
+        assert calc == p.getPathLength()                      # back-pointer walk re-sums to the DP value
+        xy = pb.xy[pb.off[cl] + nd]
+        direct = np.ceil(np.sqrt(((xy[1:] - xy[:-1]) ** 2).sum(1))).sum()
+        assert direct == calc                                  # ... and equals ceil(euclid) on the coordinates
+        rs = np.random.RandomState(3)
+        cands = random_candidates(rs, vns, T, 200000)
+        outs = {}
+        for int_path in (True, False):
+            e.set_int_path(int_path)
+            for seg in ((True, False) if int_path else (False,)):
+                e.set_segment_cache(seg)
+                outs[(int_path, seg)] = p.eval_batch(p.make_cands(cands))
+        e.set_int_path(True)
+        e.set_segment_cache(True)
+        ln, lb, fl, first = outs[(True, True)]
+        for k, (l2, b2, f2, first2) in outs.items():
+            assert (l2 == ln).all() and (b2 == lb).all() and (f2 == fl).all() and first2 == first, k
+        assert (lb <= ln).all()
+        # tryToRemove(i) equals the length after removePoint(i), for a few i
+        rem = cands[cands[:, 0] == 2][:3]
+        for op, i, _ in rem:
+            q = e.path(vns, T)
+            want = ln[np.where((cands == (op, i, 0)).all(1))[0][0]]
+            q.removePoint(int(i))
+            assert q.getPathLength() == want
+    finally:
+        e.close()

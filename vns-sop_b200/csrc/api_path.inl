@@ -337,9 +337,27 @@ vnsgpu_status vnsgpu_eval_batch(vnsgpu_ctx *ctx, int path, int64_t n, const vnsg
       }
       CK(cudaEventCreateWithFlags(&ctx->ev_start, cudaEventDisableTiming));
    }
-   // chunks: at most VNS_PIPE_EVENTS, at least 64 Ki candidates each
-   int64_t chunk = std::max<int64_t>(65536, (n + VNS_PIPE_EVENTS - 1) / VNS_PIPE_EVENTS);
-   chunk = (chunk + 255) & ~(int64_t)255;
+   // Chunk schedule.  The kernel is the slower stage (PCIe moves a candidate's 16 B in and 9-17 B out faster
+   // than it is evaluated), and it is most efficient on large chunks (one sort + launch ramp per chunk): a
+   // small first chunk starts the kernel early, a small last chunk shortens the exposed D2H tail, the
+   // middle is cut large.  VNSGPU_PIPE_CHUNKS=k forces k equal chunks (experiments).
+   std::vector<int64_t> cut;   // chunk sizes
+   if (const char *e = getenv("VNSGPU_PIPE_CHUNKS")) {
+      const int k = std::min(VNS_PIPE_EVENTS, std::max(1, atoi(e)));
+      const int64_t c = (((n + k - 1) / k) + 255) & ~(int64_t)255;
+      for (int64_t lo = 0; lo < n; lo += c) cut.push_back(std::min(c, n - lo));
+   } else if (n < 262144) {
+      cut.push_back(n);
+   } else {
+      static const int w[] = {1, 4, 4, 4, 2, 1};
+      const int64_t unit = ((n / 16) + 255) & ~(int64_t)255;
+      int64_t lo = 0;
+      for (int k = 0; k < 6 && lo < n; ++k) {
+         const int64_t c = k == 5 ? n - lo : std::min<int64_t>(unit * w[k], n - lo);
+         cut.push_back(c);
+         lo += c;
+      }
+   }
    cudaStream_t sk = ctx->stream;
    const bool useseg = seg_wanted(ctx, n);
    if (useseg) {
@@ -350,9 +368,9 @@ vnsgpu_status vnsgpu_eval_batch(vnsgpu_ctx *ctx, int path, int64_t n, const vnsg
    CK(cudaEventRecord(ctx->ev_start, sk));          // order behind whatever the caller queued before
    CK(cudaStreamWaitEvent(ctx->s_in, ctx->ev_start, 0));
    CK(cudaStreamWaitEvent(ctx->s_out, ctx->ev_start, 0));
-   int c = 0;
-   for (int64_t lo = 0; lo < n; lo += chunk, ++c) {
-      const int64_t cn = std::min(chunk, n - lo);
+   int64_t lo = 0;
+   for (int c = 0; c < (int)cut.size(); lo += cut[c], ++c) {
+      const int64_t cn = cut[c];
       CK(cudaMemcpyAsync(d_c + lo, cands + lo, sizeof(vnsgpu_cand) * cn, cudaMemcpyHostToDevice, ctx->s_in));
       CK(cudaEventRecord(ctx->ev_in[c], ctx->s_in));
       CK(cudaStreamWaitEvent(sk, ctx->ev_in[c], 0));
