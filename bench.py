@@ -64,6 +64,8 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-solve", action="store_true", help="skip the time-to-reward leg")
+    ap.add_argument("--no-solve-cpu", action="store_true", help="time-to-reward: skip the reference binary runs (long on vm1084)")
+    ap.add_argument("--multi-start", type=int, default=148, help="seeds of the multi-start leg (0 = skip)")
     return ap.parse_args()
 
 
@@ -281,9 +283,9 @@ def ncu_traffic(workload, batch):
     from the committed ncu --set full capture (profiles/ncu_traffic.json, written by scripts/ncu_extract.py)."""
     try:
         with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as fh:
-            t = json.load(fh)
-        if t.get("workload") == workload and int(t.get("batch", -1)) == batch:
-            return float(t["dram_bytes_per_launch"])
+            for t in json.load(fh)["entries"]:
+                if t.get("workload") == workload and int(t.get("batch", -1)) == batch:
+                    return float(t["dram_bytes_per_launch"])
     except (OSError, ValueError, KeyError):
         pass
     return None
@@ -546,7 +548,7 @@ def solve_leg(args, eng, sf, pb):
     out = {"seed": 1, "gpu_wall_s": gpu_wall, "gpu_device_ms": res.time_ms, "reward": res.reward, "length": res.length,
            "num_iters": res.num_iters, "proposals": res.proposals, "evals": res.evals, "accepts": res.accepts,
            "chain_evals_per_s": res.evals / gpu_wall}
-    if os.path.exists(ob.REF_BIN):
+    if os.path.exists(ob.REF_BIN) and not args.no_solve_cpu:
         from vns_sop_b200 import instances as ins
         with tempfile.TemporaryDirectory() as td:
             f = os.path.join(td, "w.sop")
@@ -563,7 +565,9 @@ def solve_leg(args, eng, sf, pb):
                     and int(d["NUM_ITERS"]) == res.num_iters})
     # multi-start: the reference's --batch=N (N seeds) - one thread block per seed in ONE launch vs one
     # reference process per host core
-    nruns = 148
+    nruns = args.multi_start
+    if nruns <= 0:
+        return out
     p2 = eng.path()
     t0 = time.perf_counter()
     res_b, best = p2.vns_run_batch(list(range(1, nruns + 1)))
@@ -571,7 +575,7 @@ def solve_leg(args, eng, sf, pb):
     out["multi_start"] = {"gpu_runs": nruns, "gpu_wall_s": gpu_multi, "gpu_runs_per_s": nruns / gpu_multi,
                           "best_reward": res_b[best].reward, "best_length": res_b[best].length, "best_seed": best + 1,
                           "seed1_same_as_single_run": res_b[0].reward == res.reward and res_b[0].length == res.length}
-    if os.path.exists(ob.REF_BIN):
+    if os.path.exists(ob.REF_BIN) and not args.no_solve_cpu:
         cores = host_cores()
         with tempfile.TemporaryDirectory() as td:
             f = os.path.join(td, "w.sop")

@@ -18,9 +18,14 @@ keys = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
 out = {k: val(k) for k in keys if k in h}
 out["kernel"] = r[h.index("Kernel Name")]
 dram = out["dram__bytes_read.sum"] + out["dram__bytes_write.sum"]
-json.dump({"workload": workload, "batch": batch, "dram_bytes_per_launch": dram, "kernel": out["kernel"], "capture": rep.split("/")[-1],
-           "note": "one ncu --set full --clock-control none capture; under ncu caches are flushed between replays"},
-          open("profiles/ncu_traffic.json", "w"), indent=1)
+entry = {"workload": workload, "batch": batch, "dram_bytes_per_launch": dram, "kernel": out["kernel"], "capture": rep.split("/")[-1],
+         "note": "one ncu --set full --clock-control none capture; under ncu caches are flushed between replays"}
+try:
+    allent = json.load(open("profiles/ncu_traffic.json"))["entries"]
+except (OSError, KeyError, ValueError):
+    allent = []
+allent = [e for e in allent if not (e["workload"] == workload and e["batch"] == batch)] + [entry]
+json.dump({"entries": allent}, open("profiles/ncu_traffic.json", "w"), indent=1)
 with open("profiles/%s_k_eval_groups_summary.txt" % tag, "w") as fh:
     for k, v in out.items():
         fh.write("%-70s %s\n" % (k, v))

@@ -257,8 +257,8 @@ static vnsgpu_status launch_eval(vnsgpu_ctx *ctx, int path, int64_t n, int64_t i
          LAUNCHED(ctx);
          d_perm = perm;
       }
-      // T is only known on the device; size the layer map for the row capacity
-      const size_t smem = eval_smem_bytes(I.rows, I.C);
+      // T is only known on the device; size the layer map for its bound (a tour visits every cluster at most once)
+      const size_t smem = eval_smem_bytes(std::min(I.rows, I.C), I.C);
       const int G = ctx->group_lanes, NR = (I.mp + G - 1) / G <= 1 ? 1 : ((I.mp + G - 1) / G <= 2 ? 2 : 4);
       const int64_t per_cta = (VNS_EVAL_THREADS / 32) * (32 / G);
       const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n + per_cta - 1) / per_cta, (int64_t)ctx->num_sms * 8));
@@ -269,8 +269,12 @@ static vnsgpu_status launch_eval(vnsgpu_ctx *ctx, int path, int64_t n, int64_t i
          seg.rowoff = reinterpret_cast<const unsigned *>(ctx->d_segmeta + 2 * R);
       }
 #define VNS_LAUNCH_EVAL(V, GG, RR, SS, TAB)                                                                          \
-   k_eval_groups<V, GG, RR, SS><<<grid, VNS_EVAL_THREADS, smem, st>>>(I, TAB, P, seg, n, idx0, d_cands, d_perm, budget, skip, d_len, \
-                                                                       d_lb, d_flags, d_first)
+   do {                                                                                                              \
+      if (smem > 48 * 1024)                                                                                          \
+         CK(cudaFuncSetAttribute(k_eval_groups<V, GG, RR, SS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+      k_eval_groups<V, GG, RR, SS><<<grid, VNS_EVAL_THREADS, smem, st>>>(I, TAB, P, seg, n, idx0, d_cands, d_perm, budget, skip, \
+                                                                          d_len, d_lb, d_flags, d_first);              \
+   } while (0)
 #define VNS_LAUNCH_EVAL_V(V, SS, TAB)                                                                                \
    do {                                                                                                              \
       if (G == 8 && NR == 1) VNS_LAUNCH_EVAL(V, 8, 1, SS, TAB);                                                       \
