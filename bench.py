@@ -64,6 +64,7 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-solve", action="store_true", help="skip the time-to-reward leg")
+    ap.add_argument("--vector-cache", type=int, default=1, help="vnsgpu_set_vector_cache: 0 off, 1 auto (batch >= 4 C^2), 2 always")
     ap.add_argument("--no-solve-cpu", action="store_true", help="time-to-reward: skip the reference binary runs (long on vm1084)")
     ap.add_argument("--multi-start", type=int, default=148, help="seeds of the multi-start leg (0 = skip)")
     return ap.parse_args()
@@ -347,6 +348,7 @@ def run_b200(args):
     sf, pb = load_workload(args.workload)
     eng = engine.Engine(local).load_problem(pb)
     lib = eng.lib
+    eng.set_vector_cache(args.vector_cache)
     state = workload_state(args.workload, pb)
     p = prepare_gpu_state(eng, state)
     vns, T = p.vns, p.getNumTargets()
@@ -467,6 +469,7 @@ def run_b200(args):
         assert torch.equal(h_len[:4096], d_len[:4096].cpu()), "host and device entry points disagree"
 
     hbm_regime = eng.table_bytes / 2 > 126e6
+    vec_mode = bool(int_path and args.vector_cache and pb.m.max() <= 32 and (n >= 4 * pb.C * pb.C or args.vector_cache == 2))
     peak, peak_src = measured_hbm_peak()
     achieved = alg_bytes / (kern_ms * 1e-3) / 1e9
     line = {
@@ -484,13 +487,17 @@ def run_b200(args):
                          ("the table read by the kernel (%.0f MB at %d B/entry, plus the segment products) is far beyond the "
                           "126 MB L2: blocks are gathered from HBM" % (eng.table_bytes / 8 * (4 if int_path else 8) / 1e6, 4 if int_path else 8)),
                    "evaluation": "sub-warp groups, batch sorted by chain length on the device, %s" %
-                                 ("exact int32 DPX arithmetic + exact segment products (rebuilt every step)" if int_path
+                                 (("exact int32 DPX arithmetic; per step the segment products and the endpoint vectors of the path "
+                                   "state are rebuilt (k_seg_build, k_vec_build), then every candidate is one dot-min of two vectors "
+                                   "through at most one block (k_eval_vec)" if vec_mode else
+                                   "exact int32 DPX arithmetic + exact segment products (rebuilt every step)") if int_path
                                   else "IEEE double, block by block"),
                    "sharding": "candidates split by rank (global batch = n_gpus x per-GPU batch), table and path replicated; "
                                "N > 1 adds one 8-byte all-reduce(MIN) per step for the chosen move"},
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": ncu_traffic(args.workload, n), "peak_source": peak_src, "kernel": "k_eval_groups",
+                     "traffic": ncu_traffic(args.workload, n), "peak_source": peak_src,
+                     "kernel": "k_eval_vec" if vec_mode else "k_eval_groups",
                      "kernel_ms": kern_ms, "algorithmic_bytes_per_launch": int(alg_bytes),
                      "algorithmic_bytes_per_candidate": alg_bytes / n,
                      "algorithmic_bytes_per_candidate_at_8B_per_entry": alg_bytes_f64 / n,
@@ -500,8 +507,9 @@ def run_b200(args):
                                     if not hbm_regime else "HBM-resident table (%.0f MB as doubles): block gathers miss L2" % (eng.table_bytes / 1e6),
                      "note": "achieved = algorithmic bytes (SURVEY.md 8d: every distance-block entry of the reference's chain "
                              "once at the width the kernel reads, + first F row + last B row + result) / time of one step "
-                             "(sort + segment products + evaluation kernels, CUDA events).  With the segment products the "
-                             "kernel reads FEWER table bytes than this reference-chain figure; see DESIGN.md 5"},
+                             "(sort + segment products + endpoint vectors + evaluation kernels, CUDA events).  The shared "
+                             "products / vectors make the kernel read FEWER table bytes than this reference-chain figure, so frac can "
+                             "exceed 1: it is a reference-work rate, not a bandwidth; `traffic` is what DRAM really moved.  See DESIGN.md 4-5"},
         "accepted_in_batch": ok_flags, "first_accept": first_dev,
     }
     if table_build:
@@ -548,6 +556,17 @@ def solve_leg(args, eng, sf, pb):
     out = {"seed": 1, "gpu_wall_s": gpu_wall, "gpu_device_ms": res.time_ms, "reward": res.reward, "length": res.length,
            "num_iters": res.num_iters, "proposals": res.proposals, "evals": res.evals, "accepts": res.accepts,
            "chain_evals_per_s": res.evals / gpu_wall}
+    try:     # the compiled reference's own seed-1 record, generated by tests/golden/make_golden.py
+        with open(os.path.join(ROOT, "tests", "golden", "golden.json")) as fh:
+            gold = json.load(fh).get(args.workload, {}).get("solve_seed1")
+    except OSError:
+        gold = None
+    if gold:
+        out["golden"] = {"reward": gold["REWARDS"], "length": gold["LENGTH"], "num_iters": gold["NUM_ITERS"],
+                         "num_iters_last_impr": gold["NUM_ITERS_LAST_IMPR"], "reference_wall_s": gold.get("reference_wall_s"),
+                         "same_trajectory": bool(gold["REWARDS"] == res.reward and gold["LENGTH"] == res.length
+                                                 and gold["NUM_ITERS"] == res.num_iters and gold["NUM_ITERS_LAST_IMPR"] == res.num_iters_last_impr
+                                                 and [[r, l] for r, l, _ in impr] == gold["IMPROVEMENTS"])}
     if os.path.exists(ob.REF_BIN) and not args.no_solve_cpu:
         from vns_sop_b200 import instances as ins
         with tempfile.TemporaryDirectory() as td:

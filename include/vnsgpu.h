@@ -112,6 +112,11 @@ vnsgpu_status vnsgpu_set_batch_sort(vnsgpu_ctx *ctx, int enable);
  * built once per call and shared by all candidates (exactly associative on integers: bit-identical
  * lengths); a MOVE / EXCHANGE chain of `span` blocks then costs at most 5.  enable = 0: block by block. */
 vnsgpu_status vnsgpu_set_segment_cache(vnsgpu_ctx *ctx, int enable);
+/* Integer tables, batches of >= 4 C^2 candidates (on top of the segment products): the two ends of every
+ * candidate's chain depend only on (cluster, layer) - they are built once per call as vectors, and a candidate
+ * costs at most ONE block step (exact: integer min-plus is associative).  enable = 0: segment products only;
+ * 2: also for smaller batches. */
+vnsgpu_status vnsgpu_set_vector_cache(vnsgpu_ctx *ctx, int enable);
 /* vnsgpu_local_search keeps the whole search state in one SM's shared memory when it fits (clusters <=
  * 510, samples per cluster <= 32); enable = 0 forces the global-memory chain (tests run both). */
 vnsgpu_status vnsgpu_set_smem_chain(vnsgpu_ctx *ctx, int enable);

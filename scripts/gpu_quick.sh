@@ -1,5 +1,6 @@
-BF="python bench.py --workload synth20k --steps 2 --warmup 1 --no-cpu --no-solve --no-e2e"
-timeout 600 python bench.py --workload synth20k --steps 10 --cpu-sample 16384 > gpurun_out/bench_q_synth20k.json 2> gpurun_out/bench_q_synth20k.err; echo "exit $?" >> gpurun_out/bench_q_synth20k.err
-timeout 600 python bench.py --workload synth20k --impl reference --ref-batch 16384 --steps 3 --warmup 1 > gpurun_out/bench_q_ref_synth20k.json 2> gpurun_out/bench_q_ref_synth20k.err
-timeout 300 $BF > gpurun_out/plain.log 2>&1 && timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 200 --csv --log-file gpurun_out/launches_synth20k.csv $BF > gpurun_out/ncu1.log 2>&1
-timeout 600 python bench.py --workload vm1084 --steps 3 --no-cpu --no-e2e > gpurun_out/bench_q_vm1084_solve.json 2> gpurun_out/bench_q_vm1084_solve.err; echo "exit $?" >> gpurun_out/bench_q_vm1084_solve.err
+timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/gpu_tests_q.log 2>&1; echo "pytest exit $?" >> gpurun_out/gpu_tests_q.log
+timeout 600 python bench.py --steps 10 --no-solve > gpurun_out/bench_q.json 2> gpurun_out/bench_q.err; echo "exit $?" >> gpurun_out/bench_q.err
+timeout 600 python bench.py --workload vm1084 --steps 10 --no-solve --cpu-sample 262144 > gpurun_out/bench_q_vm1084.json 2> gpurun_out/bench_q_vm1084.err; echo "exit $?" >> gpurun_out/bench_q_vm1084.err
+timeout 600 python bench.py --workload synth2k --steps 10 --cpu-sample 262144 > gpurun_out/bench_q_synth2k.json 2> gpurun_out/bench_q_synth2k.err; echo "exit $?" >> gpurun_out/bench_q_synth2k.err
+timeout 600 python bench.py --workload synth20k --steps 10 --no-cpu > gpurun_out/bench_q_synth20k.json 2> gpurun_out/bench_q_synth20k.err; echo "exit $?" >> gpurun_out/bench_q_synth20k.err
+timeout 900 python bench.py --workload vm1084 --steps 3 --no-cpu --no-e2e --no-solve-cpu --multi-start 0 > gpurun_out/bench_q_vm1084_solve.json 2> gpurun_out/bench_q_vm1084_solve.err; echo "exit $?" >> gpurun_out/bench_q_vm1084_solve.err

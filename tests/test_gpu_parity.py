@@ -251,7 +251,7 @@ def test_eval_batch_both_arithmetic_paths_vs_oracle(name, int_path, golden, eng_
         # call, for several pipeline chunks); same answers with the sort switched off
         T = po.T
         if T >= 3:
-            big = random_candidates(rs, po.vns, T, 150001 if name == "krob200" else 20011)
+            big = random_candidates(rs, po.vns, T, {"krob200": 150001, "vm1084": 200003}.get(name, 20011))
             big[::1013] = [4, 0, 0]
             ln, lb, fl, first = pg.eval_batch(big)
             oln, olb = po.eval_batch(big)
@@ -260,10 +260,12 @@ def test_eval_batch_both_arithmetic_paths_vs_oracle(name, int_path, golden, eng_
             assert (ln[~bad] == oln[~bad]).all() and (lb[~bad] == olb[~bad]).all()
             ok = np.nonzero(((fl & 2) != 0) & ((fl & 4) == 0))[0]
             assert first == (int(ok[0]) if len(ok) else -1)
-            # (the integer path has just used the exact segment products: batch >= 16384)
-            for sort, seg in ((False, True), (True, False), (False, False)):
+            # (the integer path has just used the endpoint vectors + exact segment products: batch >= 16384
+            # and >= 4 C^2); the same batch with the vectors off, the products off, the sort off
+            for sort, seg, vec in ((False, True, True), (True, True, False), (False, True, False), (True, False, False), (False, False, False)):
                 e.set_batch_sort(sort)
                 e.set_segment_cache(seg)
+                e.set_vector_cache(vec)
                 ln2, lb2, fl2, first2 = pg.eval_batch(big)
                 assert (ln2[~bad] == ln[~bad]).all() and (lb2[~bad] == lb[~bad]).all() and (fl2 == fl).all()
                 assert first2 == first
@@ -271,6 +273,7 @@ def test_eval_batch_both_arithmetic_paths_vs_oracle(name, int_path, golden, eng_
         e.set_int_path(True)
         e.set_batch_sort(True)
         e.set_segment_cache(True)
+        e.set_vector_cache(True)
 
 
 @pytest.mark.parametrize("S", [4, 8, 12])

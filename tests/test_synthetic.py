@@ -68,17 +68,19 @@ def test_synthetic_long_tour_candidates(synth, int_path):
     e, o, pb, (vns, T) = synth
     pg, po = e.path(vns, T), o.path(vns, T)
     rs = np.random.RandomState(5)
-    cands = random_candidates(rs, vns, T, 40000)
+    cands = random_candidates(rs, vns, T, 170000)              # >= 4 C^2: the endpoint-vector form engages
     oln, olb = po.eval_batch(cands)
     e.set_int_path(int_path)
     try:
-        for seg in (True, False):
+        for seg, vec in ((True, True), (True, False), (False, False)):
             e.set_segment_cache(seg)
+            e.set_vector_cache(vec)
             ln, lb, fl, first = pg.eval_batch(pg.make_cands(cands))
-            assert (ln == oln).all() and (lb == olb).all(), (int_path, seg)
+            assert (ln == oln).all() and (lb == olb).all(), (int_path, seg, vec)
     finally:
         e.set_int_path(True)
         e.set_segment_cache(True)
+        e.set_vector_cache(True)
 
 
 @pytest.mark.gpu

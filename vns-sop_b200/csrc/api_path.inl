@@ -217,6 +217,16 @@ static bool seg_wanted(const vnsgpu_ctx *ctx, int64_t n)
    return ctx->use_seg && vnsgpu_int_path_active(ctx) && ctx->seg_ok && n >= VNS_SEG_MIN;
 }
 
+// evaluation form of a batch: 0 block by block, 1 segment products, 2 endpoint vectors + segment products.
+// The vectors cost ~8 C (T+2) block steps per path state, so they pay once the batch is a few times C^2.
+static int eval_mode(const vnsgpu_ctx *ctx, int64_t n)
+{
+   if (!seg_wanted(ctx, n)) return 0;
+   const int64_t C = ctx->I.C;
+   if (ctx->use_vec && ctx->I.mp <= 32 && (n >= 4 * C * C || ctx->use_vec == 2) && vec_ints((int)C, (int)C + 2, ctx->I.mp) < (1ull << 31)) return 2;
+   return 1;
+}
+
 static vnsgpu_status prepare_seg(vnsgpu_ctx *ctx, int path, cudaStream_t st)
 {
    const InstDev &I = ctx->I;
@@ -229,9 +239,28 @@ static vnsgpu_status prepare_seg(vnsgpu_ctx *ctx, int path, cudaStream_t st)
    return VNSGPU_OK;
 }
 
+static vnsgpu_status prepare_eval(vnsgpu_ctx *ctx, int path, int mode, cudaStream_t st)
+{
+   if (mode == 0) return VNSGPU_OK;
+   vnsgpu_status s = prepare_seg(ctx, path, st);
+   if (s || mode == 1) return s;
+   const InstDev &I = ctx->I;
+   const int LS = I.C + 2;
+   if (!ctx->d_vec) {
+      CK(cudaMalloc(&ctx->d_vec, sizeof(int) * vec_ints(I.C, LS, I.mp)));
+      CK(cudaMalloc(&ctx->d_veclb, sizeof(int) * vec_lb_ints(I.C, LS)));
+      CK(cudaMemsetAsync(ctx->d_vec, 0, sizeof(int) * vec_ints(I.C, LS, I.mp), st));
+      CK(cudaMemsetAsync(ctx->d_veclb, 0, sizeof(int) * vec_lb_ints(I.C, LS), st));
+   }
+   const long long warps = (long long)(I.C + 1) * LS;   // upper bound of (C + 1) (T + 2)
+   k_vec_build<<<(unsigned)((warps + 7) / 8), 256, 0, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_vec, ctx->d_veclb, LS);
+   LAUNCHED(ctx);
+   return VNSGPU_OK;
+}
+
 static vnsgpu_status launch_eval(vnsgpu_ctx *ctx, int path, int64_t n, int64_t idx0, const vnsgpu_cand *d_cands, double budget,
                                  int skip, double *d_len, double *d_lb, uint8_t *d_flags, unsigned long long *d_first, cudaStream_t st,
-                                 int slot, int64_t perm_off, bool useseg)
+                                 int slot, int64_t perm_off, int useseg)
 {
    const InstDev &I = ctx->I;
    const PathDev &P = ctx->paths[path].d;
@@ -251,7 +280,7 @@ static vnsgpu_status launch_eval(vnsgpu_ctx *ctx, int path, int64_t n, int64_t i
          CK(cudaMemsetAsync(hist, 0, sizeof(unsigned) * nb, st));
          k_sort_hist<<<sgrid, 256, sizeof(unsigned) * nb, st>>>(I, P, n, d_cands, nb, hist, useseg);
          LAUNCHED(ctx);
-         k_sort_scan<<<1, 32, 0, st>>>(nb, hist, cursor);
+         k_sort_scan<<<1, 1024, 0, st>>>(nb, hist, cursor);
          LAUNCHED(ctx);
          k_sort_scatter<<<sgrid, 256, sizeof(unsigned) * 2 * nb, st>>>(I, P, n, d_cands, nb, cursor, perm, useseg);
          LAUNCHED(ctx);
@@ -284,7 +313,22 @@ static vnsgpu_status launch_eval(vnsgpu_ctx *ctx, int path, int64_t n, int64_t i
       else if (G == 16) VNS_LAUNCH_EVAL(V, 16, 2, SS, TAB);                                                           \
       else VNS_LAUNCH_EVAL(V, 32, 1, SS, TAB);                                                                        \
    } while (0)
-      if (ctx->use_int && ctx->d_D32) {
+      if (useseg == 2) {
+         VecCache vc{ctx->d_vec, ctx->d_veclb, I.C + 2};
+#define VNS_LAUNCH_VEC(GG, RR)                                                                                       \
+   do {                                                                                                              \
+      if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k_eval_vec<GG, RR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+      k_eval_vec<GG, RR><<<grid, VNS_EVAL_THREADS, smem, st>>>(I, ctx->d_D32, P, seg, vc, n, idx0, d_cands, d_perm, budget, skip, d_len, \
+                                                               d_lb, d_flags, d_first);                              \
+   } while (0)
+         if (G == 8 && NR == 1) VNS_LAUNCH_VEC(8, 1);
+         else if (G == 8 && NR == 2) VNS_LAUNCH_VEC(8, 2);
+         else if (G == 8) VNS_LAUNCH_VEC(8, 4);
+         else if (G == 16 && NR == 1) VNS_LAUNCH_VEC(16, 1);
+         else if (G == 16) VNS_LAUNCH_VEC(16, 2);
+         else VNS_LAUNCH_VEC(32, 1);
+#undef VNS_LAUNCH_VEC
+      } else if (ctx->use_int && ctx->d_D32) {
          if (useseg) VNS_LAUNCH_EVAL_V(int, true, ctx->d_D32);
          else VNS_LAUNCH_EVAL_V(int, false, ctx->d_D32);
       } else VNS_LAUNCH_EVAL_V(double, false, ctx->d_D);
@@ -305,9 +349,9 @@ vnsgpu_status vnsgpu_eval_batch_dev(vnsgpu_ctx *ctx, int path, int64_t n, const 
    if (n <= 0) return VNSGPU_OK;
    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
    if (d_first_accept) CK(cudaMemsetAsync(d_first_accept, 0xFF, sizeof(long long), st));   // -1 = none
-   const bool useseg = seg_wanted(ctx, n);
-   if (useseg) {
-      vnsgpu_status s = prepare_seg(ctx, path, st);
+   const int useseg = eval_mode(ctx, n);
+   {
+      vnsgpu_status s = prepare_eval(ctx, path, useseg, st);
       if (s) return s;
    }
    return launch_eval(ctx, path, n, 0, d_cands, budget, skip, d_len, d_lb, d_flags, (unsigned long long *)d_first_accept, st, 0, 0,
@@ -363,11 +407,9 @@ vnsgpu_status vnsgpu_eval_batch(vnsgpu_ctx *ctx, int path, int64_t n, const vnsg
       }
    }
    cudaStream_t sk = ctx->stream;
-   const bool useseg = seg_wanted(ctx, n);
-   if (useseg) {
-      s = prepare_seg(ctx, path, sk);
-      if (s) return s;
-   }
+   const int useseg = eval_mode(ctx, n);
+   s = prepare_eval(ctx, path, useseg, sk);
+   if (s) return s;
    CK(cudaMemsetAsync(ctx->d_first, 0xFF, sizeof(long long), sk));
    CK(cudaEventRecord(ctx->ev_start, sk));          // order behind whatever the caller queued before
    CK(cudaStreamWaitEvent(ctx->s_in, ctx->ev_start, 0));

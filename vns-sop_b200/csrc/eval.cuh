@@ -399,8 +399,25 @@ __global__ void __launch_bounds__(256) k_table_to_int(const double *__restrict__
    for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < n; q += (long long)gridDim.x * blockDim.x) Di[q] = (int)D[q];
 }
 
+// sort key of the endpoint-vector kernel: candidates with a block step first
+__device__ __forceinline__ int vec_sort_key(int T, int C, const int4 &cd)
+{
+   const int op = cd.x, a = cd.y, b = cd.z;
+   if (op == VNSGPU_OP_MOVE) {
+      if (a >= T || a < 0 || b > T || b < 0 || abs(b - a) < 2) return 0;
+      return b > a ? (b - a > 2 ? 1 : 0) : 1;     // up: layers i+1 .. j-1 = a+2 .. b;  down: always >= one block
+   }
+   if (op == VNSGPU_OP_EXCHANGE) {
+      if (a >= T || a < 0 || b >= T || b < 0 || abs(a - b) < 2) return 0;
+      return abs(a - b) > 2 ? 1 : 0;              // layers p+1 .. q-1
+   }
+   return 0;
+}
+
+// useseg: 0 block by block, 1 segment products, 2 endpoint vectors (vec.cuh)
 __device__ __forceinline__ int sort_key(int T, int C, const int4 &cd, int useseg)
 {
+   if (useseg == 2) return vec_sort_key(T, C, cd);
    return useseg ? decode_cand_seg(T, C, cd.x, cd.y, cd.z).K : decode_cand(T, C, cd.x, cd.y, cd.z).K;
 }
 
@@ -422,12 +439,25 @@ __global__ void __launch_bounds__(256) k_sort_hist(InstDev I, PathDev P, long lo
       if (smem_u[k]) atomicAdd(&hist[k], smem_u[k]);
 }
 
-__global__ void k_sort_scan(int nb, const unsigned *__restrict__ hist, unsigned *__restrict__ cursor)
+// exclusive scan of the histogram in DESCENDING key order (longest chains first); one block of 1024 threads,
+// thread t owns the t-th chunk of keys counted from the top
+__global__ void __launch_bounds__(1024) k_sort_scan(int nb, const unsigned *__restrict__ hist, unsigned *__restrict__ cursor)
 {
-   if (threadIdx.x == 0 && blockIdx.x == 0) {
-      unsigned pos = 0;
-      for (int k = nb - 1; k >= 0; --k) { cursor[k] = pos; pos += hist[k]; }
+   __shared__ unsigned part[1024];
+   const int chunk = (nb + 1023) / 1024, t = threadIdx.x;
+   const int hi = nb - 1 - t * chunk, lo = max(hi - chunk + 1, 0);   // keys hi, hi-1, .., lo
+   unsigned sum = 0;
+   for (int k = hi; k >= lo; --k) sum += hist[k];
+   part[t] = sum;
+   __syncthreads();
+   for (int d = 1; d < 1024; d <<= 1) {
+      const unsigned add = t >= d ? part[t - d] : 0;
+      __syncthreads();
+      part[t] += add;
+      __syncthreads();
    }
+   unsigned pos = part[t] - sum;   // exclusive prefix of this chunk
+   for (int k = hi; k >= lo; --k) { cursor[k] = pos; pos += hist[k]; }
 }
 
 __global__ void __launch_bounds__(256) k_sort_scatter(InstDev I, PathDev P, long long n, const vnsgpu_cand *__restrict__ cands, int nb,

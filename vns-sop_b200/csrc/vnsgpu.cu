@@ -15,6 +15,7 @@
 #include "path.cuh"
 #include "search.cuh"
 #include "eval.cuh"
+#include "vec.cuh"
 #include "chain.cuh"
 #include "kernels.cuh"
 
@@ -45,6 +46,8 @@ struct vnsgpu_ctx {
    bool use_seg = true;      // exact segment products on integer tables (vnsgpu_set_segment_cache)
    bool seg_ok = false;      // the int32 buffer has room for them and offsets fit 32 bits
    int *d_segmeta = nullptr;
+   int use_vec = 1;          // 0 off, 1 when the batch is large enough, 2 always; endpoint vectors on top of the segment products (vnsgpu_set_vector_cache, vec.cuh)
+   int *d_vec = nullptr, *d_veclb = nullptr;
    int group_lanes = 8;      // lanes per candidate of k_eval_groups, from the mean cluster size
    unsigned *d_hist = nullptr, *d_perm = nullptr;
    size_t perm_cap = 0;
@@ -135,8 +138,8 @@ static void free_instance(vnsgpu_ctx *ctx)
    ctx->paths.clear();
    cudaFree(ctx->d_m); cudaFree(ctx->d_off); cudaFree(ctx->d_clof); cudaFree(ctx->d_reward);
    cudaFree(ctx->d_D); cudaFree(ctx->d_dmin); cudaFree(ctx->d_dmax); cudaFree(ctx->d_seg); cudaFree(ctx->d_D32);
-   cudaFree(ctx->d_hist); cudaFree(ctx->d_perm); cudaFree(ctx->d_segmeta);
-   ctx->d_segmeta = nullptr; ctx->seg_ok = false;
+   cudaFree(ctx->d_hist); cudaFree(ctx->d_perm); cudaFree(ctx->d_segmeta); cudaFree(ctx->d_vec); cudaFree(ctx->d_veclb);
+   ctx->d_segmeta = nullptr; ctx->seg_ok = false; ctx->d_vec = nullptr; ctx->d_veclb = nullptr;
    ctx->d_D32 = nullptr; ctx->d_hist = ctx->d_perm = nullptr; ctx->perm_cap = 0;
    ctx->d_m = ctx->d_off = ctx->d_clof = ctx->d_seg = nullptr;
    ctx->d_reward = ctx->d_D = ctx->d_dmin = ctx->d_dmax = nullptr;
@@ -178,6 +181,12 @@ vnsgpu_status vnsgpu_set_smem_chain(vnsgpu_ctx *ctx, int enable)
 vnsgpu_status vnsgpu_set_segment_cache(vnsgpu_ctx *ctx, int enable)
 {
    ctx->use_seg = enable != 0;
+   return VNSGPU_OK;
+}
+
+vnsgpu_status vnsgpu_set_vector_cache(vnsgpu_ctx *ctx, int enable)
+{
+   ctx->use_vec = enable < 0 ? 0 : (enable > 2 ? 2 : enable);
    return VNSGPU_OK;
 }
 

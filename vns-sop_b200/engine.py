@@ -84,6 +84,7 @@ _SIGS = {
     "vnsgpu_vns_run": [vp, C.c_int, C.POINTER(VnsParams), C.POINTER(VnsResult), dp, dp, dp],
     "vnsgpu_vns_run_batch": [vp, C.c_int, C.c_int, C.POINTER(C.c_uint32), C.POINTER(VnsParams), C.POINTER(VnsResult), ip, ip],
     "vnsgpu_path_destroy": [vp, C.c_int],
+    "vnsgpu_set_vector_cache": [vp, C.c_int],
 }
 EXPORTS = sorted(list(_SIGS) + ["vnsgpu_destroy", "vnsgpu_last_error", "vnsgpu_version", "vnsgpu_launch_count",
                                 "vnsgpu_table_bytes", "vnsgpu_rng_seed", "vnsgpu_rng_next"])
@@ -181,6 +182,9 @@ class Engine:
 
     def set_segment_cache(self, enable):
         self._ck(self.lib.vnsgpu_set_segment_cache(self.h, int(enable)))
+
+    def set_vector_cache(self, enable):
+        self._ck(self.lib.vnsgpu_set_vector_cache(self.h, int(enable)))
 
     def chain_cycles(self, reset=True):
         out = (C.c_int64 * 4)()
