@@ -163,6 +163,14 @@ vnsgpu_status vnsgpu_path_get_dp(vnsgpu_ctx *ctx, int path, double *F, double *B
  * whose ACCEPT flag is set and (when skip != 0) whose LB_SKIP flag is not, or -1 */
 vnsgpu_status vnsgpu_eval_batch(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *cands, double budget,
                                 int skip, double *len, double *lb, uint8_t *flags, int64_t *first_accept);
+/* The same call with 8-byte descriptors (halves the host-to-device bytes; the library expands them on the
+ * device).  Indices must lie in [0, 2^20); gain_cluster in [-1, 2^21 - 2]. */
+static inline uint64_t vnsgpu_pack_cand(int op, int a, int b, int gain_cluster)
+{
+   return (uint64_t)(op & 7) | ((uint64_t)(a & 0xfffff) << 3) | ((uint64_t)(b & 0xfffff) << 23) | ((uint64_t)(gain_cluster + 1) << 43);
+}
+vnsgpu_status vnsgpu_eval_batch_packed(vnsgpu_ctx *ctx, int path, int64_t n, const uint64_t *packed, double budget,
+                                       int skip, double *len, double *lb, uint8_t *flags, int64_t *first_accept);
 /* device buffers, asynchronous on `stream` (NULL = context stream); d_first_accept: one int64 that
  * the call resets and fills like first_accept above (-1 = none), or NULL */
 vnsgpu_status vnsgpu_eval_batch_dev(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *d_cands,

@@ -4,7 +4,9 @@ usage: python scripts/ncu_extract.py gpurun_out/prof_eval_TAG.ncu-rep TAG worklo
 import csv, io, json, subprocess, sys
 rep, tag, workload, batch = sys.argv[1], sys.argv[2], sys.argv[3], int(sys.argv[4])
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
-open("profiles/%s_k_eval_groups_ncu_raw.csv" % tag, "w").write(raw)
+rows0 = list(csv.reader(io.StringIO(raw)))
+kname = rows0[-1][rows0[0].index("Kernel Name")].split("<")[0].split("(")[0].replace("void ", "").strip()
+open("profiles/%s_%s_ncu_raw.csv" % (tag, kname), "w").write(raw)
 rows = list(csv.reader(io.StringIO(raw)))
 h, units, r = rows[0], rows[1], rows[-1]
 def val(name):
@@ -26,8 +28,8 @@ except (OSError, KeyError, ValueError):
     allent = []
 allent = [e for e in allent if not (e["workload"] == workload and e["batch"] == batch)] + [entry]
 json.dump({"entries": allent}, open("profiles/ncu_traffic.json", "w"), indent=1)
-with open("profiles/%s_k_eval_groups_summary.txt" % tag, "w") as fh:
+with open("profiles/%s_%s_summary.txt" % (tag, kname), "w") as fh:
     for k, v in out.items():
         fh.write("%-70s %s\n" % (k, v))
     fh.write("dram bytes per launch %.0f = %.1f B per candidate (batch %d)\n" % (dram, dram / batch, batch))
-print(open("profiles/%s_k_eval_groups_summary.txt" % tag).read())
+print(open("profiles/%s_%s_summary.txt" % (tag, kname)).read())

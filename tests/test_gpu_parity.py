@@ -260,6 +260,8 @@ def test_eval_batch_both_arithmetic_paths_vs_oracle(name, int_path, golden, eng_
             assert (ln[~bad] == oln[~bad]).all() and (lb[~bad] == olb[~bad]).all()
             ok = np.nonzero(((fl & 2) != 0) & ((fl & 4) == 0))[0]
             assert first == (int(ok[0]) if len(ok) else -1)
+            lnp, lbp, flp, firstp = pg.eval_batch_packed(big)          # 8-byte descriptors, same answers
+            assert (lnp[~bad] == ln[~bad]).all() and (lbp[~bad] == lb[~bad]).all() and (flp == fl).all() and firstp == first
             # (the integer path has just used the endpoint vectors + exact segment products: batch >= 16384
             # and >= 4 C^2); the same batch with the vectors off, the products off, the sort off
             for sort, seg, vec in ((False, True, True), (True, True, False), (False, True, False), (True, False, False), (False, False, False)):

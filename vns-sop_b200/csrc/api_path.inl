@@ -361,8 +361,19 @@ vnsgpu_status vnsgpu_eval_batch_dev(vnsgpu_ctx *ctx, int path, int64_t n, const 
 // Host buffers.  The batch is cut into chunks that flow through three streams - H2D of chunk c+1, the
 // kernel on chunk c and D2H of chunk c-1 overlap - so the call runs at PCIe speed when the caller's
 // buffers are pinned (pageable buffers work, the copies then serialise inside the driver).
-vnsgpu_status vnsgpu_eval_batch(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *cands, double budget, int skip, double *len,
-                                double *lb, uint8_t *flags, int64_t *first_accept)
+__global__ void __launch_bounds__(256) k_unpack_cands(long long n, const unsigned long long *__restrict__ src, vnsgpu_cand *__restrict__ dst)
+{
+   for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < n; q += (long long)gridDim.x * blockDim.x) {
+      const unsigned long long w = src[q];
+      int4 c;
+      c.x = (int)(w & 7); c.y = (int)((w >> 3) & 0xfffff); c.z = (int)((w >> 23) & 0xfffff); c.w = (int)(w >> 43) - 1;
+      reinterpret_cast<int4 *>(dst)[q] = c;
+   }
+}
+
+// src: vnsgpu_cand[n] (packed == 0) or uint64_t[n] in the vnsgpu_pack_cand format (packed == 1)
+static vnsgpu_status eval_batch_host(vnsgpu_ctx *ctx, int path, int64_t n, const void *src, int packed, double budget, int skip,
+                                     double *len, double *lb, uint8_t *flags, int64_t *first_accept)
 {
    CK(cudaSetDevice(ctx->device));
    if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
@@ -370,9 +381,11 @@ vnsgpu_status vnsgpu_eval_batch(vnsgpu_ctx *ctx, int path, int64_t n, const vnsg
    if (n <= 0) return VNSGPU_OK;
    const size_t o_len = al16(sizeof(vnsgpu_cand) * n), o_lb = o_len + al16(sizeof(double) * n);
    const size_t o_fl = o_lb + al16(sizeof(double) * n);
-   vnsgpu_status s = need_scratch(ctx, o_fl + al16(n));
+   const size_t o_pk = o_fl + al16(n);
+   vnsgpu_status s = need_scratch(ctx, o_pk + (packed ? al16(sizeof(unsigned long long) * n) : 0));
    if (s) return s;
    char *b = (char *)ctx->d_scratch;
+   unsigned long long *d_pk = (unsigned long long *)(b + o_pk);
    vnsgpu_cand *d_c = (vnsgpu_cand *)b;
    double *d_len = (double *)(b + o_len), *d_lb = (double *)(b + o_lb);
    uint8_t *d_fl = (uint8_t *)(b + o_fl);
@@ -417,9 +430,16 @@ vnsgpu_status vnsgpu_eval_batch(vnsgpu_ctx *ctx, int path, int64_t n, const vnsg
    int64_t lo = 0;
    for (int c = 0; c < (int)cut.size(); lo += cut[c], ++c) {
       const int64_t cn = cut[c];
-      CK(cudaMemcpyAsync(d_c + lo, cands + lo, sizeof(vnsgpu_cand) * cn, cudaMemcpyHostToDevice, ctx->s_in));
+      if (packed)
+         CK(cudaMemcpyAsync(d_pk + lo, (const unsigned long long *)src + lo, sizeof(unsigned long long) * cn, cudaMemcpyHostToDevice, ctx->s_in));
+      else
+         CK(cudaMemcpyAsync(d_c + lo, (const vnsgpu_cand *)src + lo, sizeof(vnsgpu_cand) * cn, cudaMemcpyHostToDevice, ctx->s_in));
       CK(cudaEventRecord(ctx->ev_in[c], ctx->s_in));
       CK(cudaStreamWaitEvent(sk, ctx->ev_in[c], 0));
+      if (packed) {
+         k_unpack_cands<<<(int)std::min<int64_t>((cn + 255) / 256, (int64_t)ctx->num_sms * 8), 256, 0, sk>>>(cn, d_pk + lo, d_c + lo);
+         LAUNCHED(ctx);
+      }
       s = launch_eval(ctx, path, cn, lo, d_c + lo, budget, skip, len ? d_len + lo : nullptr, lb ? d_lb + lo : nullptr,
                       flags ? d_fl + lo : nullptr, (unsigned long long *)ctx->d_first, sk, c, lo, useseg);
       if (s) return s;
@@ -435,6 +455,18 @@ vnsgpu_status vnsgpu_eval_batch(vnsgpu_ctx *ctx, int path, int64_t n, const vnsg
    CK(cudaStreamSynchronize(ctx->s_out));
    if (first_accept) *first_accept = (int64_t)first;
    return VNSGPU_OK;
+}
+
+vnsgpu_status vnsgpu_eval_batch(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *cands, double budget, int skip, double *len,
+                                double *lb, uint8_t *flags, int64_t *first_accept)
+{
+   return eval_batch_host(ctx, path, n, cands, 0, budget, skip, len, lb, flags, first_accept);
+}
+
+vnsgpu_status vnsgpu_eval_batch_packed(vnsgpu_ctx *ctx, int path, int64_t n, const uint64_t *packed, double budget, int skip, double *len,
+                                       double *lb, uint8_t *flags, int64_t *first_accept)
+{
+   return eval_batch_host(ctx, path, n, packed, 1, budget, skip, len, lb, flags, first_accept);
 }
 
 vnsgpu_status vnsgpu_cand_bytes(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *cands, int64_t *bytes)

@@ -176,6 +176,12 @@ k_eval_vec(InstDev I, const int *__restrict__ Dv, PathDev P, SegCache seg, VecCa
    for (int l = threadIdx.x; l < T + 2; l += blockDim.x) { s_pd[l] = seg.pd[l]; s_rowoff[l] = seg.rowoff[l]; }
    __syncthreads();
 
+   // A warp takes 32 candidates at a time.  Phase 1: LANE-parallel - lane L fetches and decodes candidate
+   // base + L (offsets of its two vectors and of its block, sizes, lower-bound sum) and, by xor-shuffles over
+   // its iteration-mates, the warp-wide loop bounds of the iteration it will be evaluated in.  Phase 2: G
+   // iterations; in iteration `it` the NG = 32 / G groups evaluate candidates it * NG + g, fetching their plan
+   // from the lane that decoded it (4 shuffles), and hand the result back to that lane.  Phase 3:
+   // lane-parallel epilogue (bound, flags, stores, first accepted index) for all 32 candidates at once.
    constexpr int NG = 32 / G;
    const int lane = threadIdx.x & 31, gl = lane % G, g = lane / G;
    const double L = P.hd[HD_LEN];
@@ -183,77 +189,95 @@ k_eval_vec(InstDev I, const int *__restrict__ Dv, PathDev P, SegCache seg, VecCa
    const long long warp0 = (((long long)blockIdx.x * blockDim.x) >> 5) + (threadIdx.x >> 5);
    unsigned long long best = ULLONG_MAX;
 
-   for (long long base = warp0 * NG; base < n; base += nwarps * NG) {
-      const long long slot = base + g;
+   for (long long base = warp0 * 32; base < n; base += nwarps * 32) {
+      // ---- phase 1 -----------------------------------------------------------------------------------
+      const long long slot = base + lane;
       long long kidx = slot;
       if (perm && slot < n) kidx = __ldg(perm + slot);
       int4 cd = make_int4(-1, 0, 0, -1);
       if (slot < n) cd = __ldg(reinterpret_cast<const int4 *>(cands) + kidx);
       const VecCode vcd = decode_cand_vec(vc, T, C, mp, lcl, [&](int l) { return s_pd[l]; }, cd.x, cd.y, cd.z);
-      const int mA = vcd.ok ? s_cum[vcd.la + 1] - s_cum[vcd.la] : 0, mB = vcd.ok ? s_cum[vcd.lb + 1] - s_cum[vcd.lb] : 0;
-      int vA[NR], vB[NR];
-#pragma unroll
-      for (int r = 0; r < NR; ++r) {
-         const int j = gl + r * G;
-         vA[r] = j < mA ? __ldg(vc.vec + vcd.offA + j) : INF;
-         vB[r] = j < mB ? __ldg(vc.vec + vcd.offB + j) : INF;
-      }
-      const bool blk = vcd.ok && vcd.lb > vcd.la;
-      if (__any_sync(FULL, blk)) {
-         // block la -> lb: a table block when adjacent, else the segment product M(la, lb)
-         unsigned rb = 0;
-         if (blk) {
+      unsigned p_rb = 0, p_pack;
+      {
+         const int mA = vcd.ok ? s_cum[vcd.la + 1] - s_cum[vcd.la] : 0, mB = vcd.ok ? s_cum[vcd.lb + 1] - s_cum[vcd.lb] : 0;
+         const bool blk = vcd.ok && vcd.lb > vcd.la;
+         if (blk) {   // block la -> lb: a table block when adjacent, else the segment product M(la, lb)
             if (vcd.lb == vcd.la + 1) {
                const int2 cia = cinfo[lcl[vcd.la]], cib = cinfo[lcl[vcd.lb]];
-               rb = (unsigned)cia.x * (unsigned)I.N + (unsigned)cia.y * (unsigned)cib.x;
+               p_rb = (unsigned)cia.x * (unsigned)I.N + (unsigned)cia.y * (unsigned)cib.x;
             } else
-               rb = s_rowoff[vcd.la] + (unsigned)(mA * (s_cum[vcd.lb] - s_cum[vcd.la + 2]));
+               p_rb = s_rowoff[vcd.la] + (unsigned)(mA * (s_cum[vcd.lb] - s_cum[vcd.la + 2]));
          }
-         const int trip = blk ? mA : 1, nvalid = blk ? mB : 1;
-         int tmaxAll = trip, nvmax = nvalid;
+         int tmax = blk ? mA : 1, nvmax = blk ? mB : 1, anyblk = blk;
 #pragma unroll
-         for (int s = G; s < 32; s <<= 1) {
-            tmaxAll = max(tmaxAll, __shfl_xor_sync(FULL, tmaxAll, s));
+         for (int s = 1; s < NG; s <<= 1) {       // iteration-mates = lanes that differ in the low log2(NG) bits
+            tmax = max(tmax, __shfl_xor_sync(FULL, tmax, s));
             nvmax = max(nvmax, __shfl_xor_sync(FULL, nvmax, s));
+            anyblk |= __shfl_xor_sync(FULL, anyblk, s);
          }
-         int acc[NR];
-#pragma unroll
-         for (int rd = 0; rd < NR; ++rd) {
-            acc[rd] = INF;
-            if (rd == 0 || nvmax > rd * G) {                 // warp-uniform
-               const unsigned cbase = rb + (unsigned)min(gl + rd * G, nvalid - 1);
-#pragma unroll
-               for (int rs = 0; rs < NR; ++rs) {
-                  if (rs == 0 || tmaxAll > rs * G) {         // warp-uniform
-                     const int tlim = max(min(trip - rs * G, G) - 1, 0);
-                     const unsigned sb = cbase + (unsigned)(min(rs * G, trip - 1) * nvalid);
-                     const int tm = min(tmaxAll - rs * G, G);
-                     const int opnd = vA[rs];
+         p_pack = (unsigned)mA | ((unsigned)mB << 6) | ((unsigned)tmax << 12) | ((unsigned)nvmax << 18) | ((unsigned)blk << 24) |
+                  ((unsigned)anyblk << 25);
+      }
+      int myfin = INF;
+      // ---- phase 2 -----------------------------------------------------------------------------------
 #pragma unroll 2
-                     for (int t = 0; t < tm; ++t) {
-                        const int tt = min(t, tlim);
-                        acc[rd] = __viaddmin_s32(__shfl_sync(FULL, opnd, tt, G), __ldg(Dv + (sb + (unsigned)(tt * nvalid))), acc[rd]);
+      for (int it = 0; it < G; ++it) {
+         const int c = it * NG + g;
+         const unsigned offA = __shfl_sync(FULL, vcd.offA, c), offB = __shfl_sync(FULL, vcd.offB, c);
+         const unsigned rb = __shfl_sync(FULL, p_rb, c), pk = __shfl_sync(FULL, p_pack, c);
+         const int mA = pk & 63, mB = (pk >> 6) & 63, tmaxAll = (pk >> 12) & 63, nvmax = (pk >> 18) & 63;
+         const bool blk = (pk >> 24) & 1;
+         int vA[NR], vB[NR];
+#pragma unroll
+         for (int r = 0; r < NR; ++r) {
+            const int j = gl + r * G;
+            vA[r] = j < mA ? __ldg(vc.vec + offA + j) : INF;
+            vB[r] = j < mB ? __ldg(vc.vec + offB + j) : INF;
+         }
+         if ((pk >> 25) & 1) {                                 // warp-uniform: some group of this iteration has a block
+            const int trip = blk ? mA : 1, nvalid = blk ? mB : 1;
+            int acc[NR];
+#pragma unroll
+            for (int rd = 0; rd < NR; ++rd) {
+               acc[rd] = INF;
+               if (rd == 0 || nvmax > rd * G) {                 // warp-uniform
+                  const unsigned cbase = rb + (unsigned)min(gl + rd * G, nvalid - 1);
+#pragma unroll
+                  for (int rs = 0; rs < NR; ++rs) {
+                     if (rs == 0 || tmaxAll > rs * G) {         // warp-uniform
+                        const int tlim = max(min(trip - rs * G, G) - 1, 0);
+                        const unsigned sb = cbase + (unsigned)(min(rs * G, trip - 1) * nvalid);
+                        const int tm = min(tmaxAll - rs * G, G);
+                        const int opnd = vA[rs];
+#pragma unroll 2
+                        for (int t = 0; t < tm; ++t) {
+                           const int tt = min(t, tlim);
+                           acc[rd] = __viaddmin_s32(__shfl_sync(FULL, opnd, tt, G), __ldg(Dv + (sb + (unsigned)(tt * nvalid))), acc[rd]);
+                        }
                      }
                   }
                }
             }
+#pragma unroll
+            for (int r = 0; r < NR; ++r) vA[r] = blk ? (gl + r * G < mB ? acc[r] : INF) : vA[r];
          }
+         int fin = INF;
 #pragma unroll
-         for (int r = 0; r < NR; ++r) vA[r] = blk ? (gl + r * G < mB ? acc[r] : INF) : vA[r];
+         for (int r = 0; r < NR; ++r) fin = min(fin, gl + r * G < mB ? vA[r] + vB[r] : INF);
+#pragma unroll
+         for (int s = G / 2; s > 0; s >>= 1) fin = min(fin, __shfl_xor_sync(FULL, fin, s, G));
+         // candidate it * NG + g' was evaluated by group g' = lane % NG: hand it to its owner lane
+         const int got = __shfl_sync(FULL, fin, (lane % NG) * G);
+         myfin = (lane / NG == it) ? got : myfin;
       }
-      int fin = INF;
-#pragma unroll
-      for (int r = 0; r < NR; ++r) fin = min(fin, gl + r * G < mB ? vA[r] + vB[r] : INF);
-#pragma unroll
-      for (int s = G / 2; s > 0; s >>= 1) fin = min(fin, __shfl_xor_sync(FULL, fin, s, G));
-
-      if (gl == 0 && slot < n) {
+      // ---- phase 3 -----------------------------------------------------------------------------------
+      if (slot < n) {
          double l, bound;
          unsigned f = 0;
          if (!vcd.ok) {
             l = CUDART_NAN; bound = CUDART_NAN; f = VNSGPU_F_BAD;
          } else {
-            l = (double)fin;
+            l = (double)myfin;
             bound = vcd.nolb ? l : P.minF[vcd.s0] + (double)vcd.lbsum + P.minB[vcd.sK];
             double dR = 0.0, lm = l;
             if (cd.x == VNSGPU_OP_ADD) {

@@ -74,6 +74,7 @@ _SIGS = {
     "vnsgpu_path_get_solution": [vp, C.c_int, ip, ip, dp],
     "vnsgpu_path_get_dp": [vp, C.c_int, dp, dp, C.c_int],
     "vnsgpu_eval_batch": [vp, C.c_int, C.c_int64, vp, C.c_double, C.c_int, dp, dp, vp, C.POINTER(C.c_int64)],
+    "vnsgpu_eval_batch_packed": [vp, C.c_int, C.c_int64, vp, C.c_double, C.c_int, dp, dp, vp, C.POINTER(C.c_int64)],
     "vnsgpu_eval_batch_dev": [vp, C.c_int, C.c_int64, vp, C.c_double, C.c_int, vp, vp, vp, vp, vp],
     "vnsgpu_gen_proposals": [vp, C.c_int, C.c_int, C.c_int64, C.POINTER(Rng), vp],
     "vnsgpu_cand_bytes": [vp, C.c_int, C.c_int64, vp, C.POINTER(C.c_int64)],
@@ -340,6 +341,25 @@ class VnsSopPath:
         budget = self.e.pb.budget if budget is None else budget
         self.e._ck(self.lib.vnsgpu_eval_batch(self.e.h, self.h, n, c.ctypes.data, budget, skip, _d(ln), _d(lb),
                                               fl.ctypes.data, C.byref(first)))
+        return ln, lb, fl, first.value
+
+    @staticmethod
+    def pack_cands(cands):
+        """CAND_DTYPE array -> uint64 descriptors (vnsgpu_pack_cand in include/vnsgpu.h)."""
+        c = VnsSopPath.make_cands(cands)
+        u = lambda x: x.astype(np.int64).astype(np.uint64)
+        return np.ascontiguousarray((u(c["op"]) & np.uint64(7)) | ((u(c["a"]) & np.uint64(0xfffff)) << np.uint64(3))
+                                    | ((u(c["b"]) & np.uint64(0xfffff)) << np.uint64(23)) | (u(c["gain_cluster"] + 1) << np.uint64(43)))
+
+    def eval_batch_packed(self, cands, budget=None, skip=1):
+        """eval_batch with 8-byte descriptors (half the host-to-device bytes)."""
+        pk = self.pack_cands(cands)
+        n = len(pk)
+        ln, lb, fl = np.empty(n), np.empty(n), np.zeros(n, np.uint8)
+        first = C.c_int64(-1)
+        budget = self.e.pb.budget if budget is None else budget
+        self.e._ck(self.lib.vnsgpu_eval_batch_packed(self.e.h, self.h, n, pk.ctypes.data, budget, skip, _d(ln), _d(lb),
+                                                     fl.ctypes.data, C.byref(first)))
         return ln, lb, fl, first.value
 
     def _one(self, op, a, b):
