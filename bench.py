@@ -41,6 +41,10 @@ WORKLOADS = {
     "berlin52": ("11berlin52_T60_p2", os.path.join(ROOT, "tests", "golden", "berlin52.npz")),
     "opn_s08": ("tsiligirides_problem_2_budget_30_d_50_s_08", os.path.join(ROOT, "tests", "golden", "opn_s08.npz")),
     "dop_s12": ("tsiligirides_problem_2_budget_30_r_50_s_12", os.path.join(ROOT, "tests", "golden", "dop_s12.npz")),
+    # BASELINE.json config 3: the shipped DOP files stop at 12 headings; 16 are generated from the s_08 file's cluster
+    # centres with the Dubins table kernel (vnsgpu_build_table_dubins, ceil rule like the shipped EXPLICIT matrices)
+    "dop_s16": ("tsiligirides_problem_2_budget_30_r_50_s_16 (generated: centres of the shipped s_08 file, 16 headings, Dubins table kernel)",
+                os.path.join(ROOT, "tests", "golden", "dop_s08.npz"), {"dubins_S": 16}),
     # BASELINE.json config 5: generated (vns-sop_b200/synthetic.py), table far beyond L2 - the HBM regime
     "synth20k": ("synthetic scaled SOP: 20000 nodes / 2000 clusters of 10, CEIL_2D (generated, seed 20190147)", None, {"n_points": 20000}),
     "synth2k": ("synthetic scaled SOP: 2000 nodes / 200 clusters of 10, CEIL_2D (generated, seed 20190147)", None, {"n_points": 2000}),
@@ -98,6 +102,11 @@ def make_candidates(n, vns, T, seed):
     return c[rs.permutation(n)]
 
 
+def dubins_S(name):
+    w = WORKLOADS[name]
+    return w[2]["dubins_S"] if len(w) > 2 and "dubins_S" in w[2] else 0
+
+
 def load_workload(name):
     from vns_sop_b200 import instances as ins
     if WORKLOADS[name][1] is None:
@@ -105,12 +114,28 @@ def load_workload(name):
         sf = synthetic.generate(**WORKLOADS[name][2])
     else:
         sf = ins.load_npz(WORKLOADS[name][1])
+    S = dubins_S(name)
+    if S:       # same sets, S heading samples each; the weights are filled in from the device table (fill_dubins_weights)
+        C0 = len(sf.set_nodes)
+        sf.set_nodes = [np.arange(c * S, (c + 1) * S, dtype=np.int32) for c in range(C0)]
+        sf.weights = np.zeros((C0 * S, C0 * S))
+        sf.coords = None
+        sf.edge_weight_type = "EXPLICIT"
+        sf.name = WORKLOADS[name][0].split(" ")[0]
     return sf, ins.build_problem(sf)
+
+
+def fill_dubins_weights(sf, pb, W):
+    """W = the device-built table in sample order -> the file's node order, so that the CPU side can load the
+    instance as the EXPLICIT matrix the reference's DOP files carry."""
+    sf.weights = np.zeros_like(W)
+    sf.weights[np.ix_(pb.node_id, pb.node_id)] = W
+    pb.W = W
 
 
 def workload_state(name, pb):
     """(vns, T) the candidates are drawn against, or None = run greedy_insertion (dataset instances)."""
-    if WORKLOADS[name][1] is None:
+    if WORKLOADS[name][1] is None and pb.xy is not None:
         from vns_sop_b200 import synthetic
         return synthetic.centroid_tour_state(pb)
     return None
@@ -154,6 +179,9 @@ _W = {}
 def _worker_init(workload):
     if "ev" not in _W:          # normally inherited from the parent through fork (one table, shared pages)
         sf, pb = load_workload(workload)
+        if dubins_S(workload):   # no GPU on this arm: the Dubins table from the CPU restatement (oracle/vns_oracle.c)
+            from oracle import binding as ob
+            fill_dubins_weights(sf, pb, ob.Oracle(pb, dubins=(dubins_S(workload), sf.dubins_radius, 1)).dense())
         _W["ev"] = CpuEvaluator(sf, pb, workload_state(workload, pb))
 
 
@@ -346,7 +374,11 @@ def run_b200(args):
         return float(t.item())
 
     sf, pb = load_workload(args.workload)
-    eng = engine.Engine(local).load_problem(pb)
+    if dubins_S(args.workload):
+        eng = engine.Engine(local).load_problem(pb, dubins=(dubins_S(args.workload), sf.dubins_radius, 1))
+        fill_dubins_weights(sf, pb, eng.table_dense())
+    else:
+        eng = engine.Engine(local).load_problem(pb)
     lib = eng.lib
     eng.set_vector_cache(args.vector_cache)
     state = workload_state(args.workload, pb)
