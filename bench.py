@@ -385,17 +385,29 @@ def run_b200(args):
     p = prepare_gpu_state(eng, state)
     vns, T = p.vns, p.getNumTargets()
     table_build = None
-    if pb.xy is not None:       # a1: the pairwise table kernel + bounds (+ int32 copy), buffers already allocated
+    if pb.xy is not None or dubins_S(args.workload):   # a1 / a4 (+ a5): the fused pairwise table kernel, buffers re-allocated inside the call
+        S_ = dubins_S(args.workload)
         torch.cuda.synchronize()
         t0 = time.perf_counter()
-        eng.build_table_euclid(pb.xy, pb.rule)
+        if S_:
+            eng.build_table_dubins(pb.centers, S_, sf.dubins_radius, 1)
+        else:
+            eng.build_table_euclid(pb.xy, pb.rule)
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
+        kms = float(lib.vnsgpu_table_kernel_ms(eng.h))
         p = prepare_gpu_state(eng, (vns, T))
-        table_build = {"ms": 1e3 * dt, "entries": int(pb.N) ** 2, "table_bytes": int(eng.table_bytes),
-                       "written_gbs": eng.table_bytes / dt / 1e9,
-                       "what": "vnsgpu_build_table_euclid: H2D of the coordinates, pairwise kernel (8 B/entry written), "
-                               "bounds pass (8 B/entry read), int32 copy (8 B read + 4 B written); wall clock of the call"}
+        wbytes = int(eng.table_bytes) * (3 if lib.vnsgpu_int_path_active(eng.h) else 2) // 2
+        peak_t = measured_hbm_peak()[0]
+        table_build = {"kernel": "k_table_pairs<%s>" % ("dubins" if S_ else "euclid"), "kernel_ms": kms, "call_ms": 1e3 * dt,
+                       "entries": int(pb.N) ** 2, "bytes_written": wbytes,
+                       "achieved_gbs": wbytes / (kms * 1e-3) / 1e9 if kms > 0 else None,
+                       "frac_of_hbm_peak": wbytes / (kms * 1e-3) / 1e9 / peak_t if kms > 0 else None,
+                       "bound": "fp64 transcendental issue (six Dubins words per entry)" if S_ else "hbm (write)",
+                       "what": "ONE pass: distance per entry, stored as double (8 B) and as int32 (4 B, exact path), cluster-pair "
+                               "min / max (a5) and the integer classification in the epilogue; nothing is read back.  kernel_ms = CUDA "
+                               "events around the launch; call_ms = the whole C-ABI call (H2D of the coordinates, cudaMalloc of the "
+                               "int32 copy, sync)"}
     n, K, W = args.batch, args.steps, args.warmup
     rows = make_candidates(n, vns, T, 1000 + rank)          # each rank owns its shard of the candidates
     cands = p.make_cands(rows)
@@ -599,7 +611,8 @@ def solve_leg(args, eng, sf, pb):
     t0 = time.perf_counter()
     res, impr = p.vns_run(1)
     gpu_wall = time.perf_counter() - t0
-    out = {"seed": 1, "gpu_wall_s": gpu_wall, "gpu_device_ms": res.time_ms, "reward": res.reward, "length": res.length,
+    out = {"seed": 1, "gpu_wall_s": gpu_wall, "gpu_device_ms": res.time_ms, "gpu_time_to_final_reward_s": res.time_last_impr_ms / 1e3,
+           "reward": res.reward, "length": res.length,
            "num_iters": res.num_iters, "proposals": res.proposals, "evals": res.evals, "accepts": res.accepts,
            "chain_evals_per_s": res.evals / gpu_wall}
     try:     # the compiled reference's own seed-1 record, generated by tests/golden/make_golden.py
@@ -624,7 +637,8 @@ def solve_leg(args, eng, sf, pb):
             cpu_wall = time.perf_counter() - t0
             rec = open(os.path.join(td, "results.log")).read().strip().rstrip(";")
         d = dict(kv.split(":", 1) for kv in rec.split(";"))
-        out.update({"cpu_reference_wall_s": cpu_wall, "cpu_reward": float(d["REWARDS"]), "cpu_length": float(d["LENGTH"]),
+        out.update({"cpu_reference_wall_s": cpu_wall, "cpu_time_to_final_reward_s": float(d["CTIME_LAST_IMPR"]) / 1e3,
+                    "cpu_reward": float(d["REWARDS"]), "cpu_length": float(d["LENGTH"]),
                     "cpu_num_iters": int(d["NUM_ITERS"]),
                     "same_result": float(d["REWARDS"]) == res.reward and float(d["LENGTH"]) == res.length
                     and int(d["NUM_ITERS"]) == res.num_iters})
@@ -640,6 +654,18 @@ def solve_leg(args, eng, sf, pb):
     out["multi_start"] = {"gpu_runs": nruns, "gpu_wall_s": gpu_multi, "gpu_runs_per_s": nruns / gpu_multi,
                           "best_reward": res_b[best].reward, "best_length": res_b[best].length, "best_seed": best + 1,
                           "seed1_same_as_single_run": res_b[0].reward == res.reward and res_b[0].length == res.length}
+    # race: the same launch with the reference's seed-1 final reward as target - it ends as soon as ANY seed's tour
+    # reaches it ("wall time to the reference's reward" with one seed per SM); every run stays a prefix of its
+    # seeded reference trajectory
+    p3 = eng.path()
+    t0 = time.perf_counter()
+    res_r, win = p3.vns_run_batch(list(range(1, nruns + 1)), target_reward=res.reward)
+    race_wall = time.perf_counter() - t0
+    eng.set_target_reward(0.0)
+    out["race_to_reference_reward"] = {"target_reward": res.reward, "gpu_runs": nruns, "gpu_wall_s": race_wall,
+                                       "winner_seed": win + 1, "winner_reward": res_r[win].reward, "winner_length": res_r[win].length,
+                                       "winner_device_ms": res_r[win].time_ms, "winner_num_iters": res_r[win].num_iters,
+                                       "vs_single_chain_gpu_s": res.time_last_impr_ms / 1e3}
     if os.path.exists(ob.REF_BIN) and not args.no_solve_cpu:
         cores = host_cores()
         with tempfile.TemporaryDirectory() as td:
@@ -655,14 +681,24 @@ def solve_leg(args, eng, sf, pb):
             for q in procs:
                 q.wait()
             cpu_multi = time.perf_counter() - t0
-            rewards = []
+            rewards, t_hit = [], []
             for sd in range(1, cores + 1):
                 rec = open(os.path.join(td, "o%d" % sd, "results.log")).read().strip().rstrip(";")
                 d = dict(kv.split(":", 1) for kv in rec.split(";"))
                 rewards.append((float(d["REWARDS"]), float(d["LENGTH"])))
+                for rec_i in d.get("SOLUTION_TIME_REWARD_LENGTH_IMPROVEMENTS", "").split(","):     # ms|reward|length
+                    f3 = rec_i.split("|")
+                    if len(f3) == 3 and float(f3[1]) >= res.reward:
+                        t_hit.append(float(f3[0]) / 1e3)
+                        break
         same = all(rewards[k] == (res_b[k].reward, res_b[k].length) for k in range(cores))
         out["multi_start"].update({"cpu_runs": cores, "cpu_cores": cores, "cpu_wall_s": cpu_multi, "cpu_runs_per_s": cores / cpu_multi,
                                    "first_%d_seeds_same_results" % cores: same})
+        out["race_to_reference_reward"].update({
+            "cpu_cores": cores, "cpu_seeds_reaching_target": len(t_hit),
+            "cpu_first_hit_s": min(t_hit) if t_hit else None,
+            "cpu_note": "reference binary, one seed per host core, all started together: the earliest time any run's improvement "
+                        "log (results.log SOLUTION_TIME_REWARD_LENGTH_IMPROVEMENTS) shows reward >= target"})
     return out
 
 

@@ -135,6 +135,9 @@ vnsgpu_status vnsgpu_set_table_dense(vnsgpu_ctx *ctx, const double *W);
 vnsgpu_status vnsgpu_get_table_dense(vnsgpu_ctx *ctx, double *W);
 /* a5: calcClusterDistancesBounds (vns_sop_solver.cpp:262-297); C x C each; either may be NULL */
 vnsgpu_status vnsgpu_get_bounds(vnsgpu_ctx *ctx, double *dmin, double *dmax);
+/* device time (ms, CUDA events) of the last table build kernel: one fused pass writing the table as double (8 N^2 B) and,
+ * for integer-valued rules, as int32 (4 N^2 B), with the a5 bounds and the table classification in its epilogue */
+double vnsgpu_table_kernel_ms(const vnsgpu_ctx *ctx);
 /* bytes of the device-resident table (8 N^2) */
 int64_t vnsgpu_table_bytes(const vnsgpu_ctx *ctx);
 
@@ -215,6 +218,11 @@ vnsgpu_status vnsgpu_vns_run(vnsgpu_ctx *ctx, int path, const vnsgpu_vns_params 
  * tour_paths (may be NULL): nruns handles that receive every run's final tour; the caller destroys them. */
 vnsgpu_status vnsgpu_vns_run_batch(vnsgpu_ctx *ctx, int path, int nruns, const uint32_t *seeds, const vnsgpu_vns_params *params,
                                    vnsgpu_vns_result *results, int *best_run, int *tour_paths);
+/* Race mode of vnsgpu_vns_run_batch ("wall time to a given reward"): with target > 0 the first run whose tour reaches
+ * reward >= target raises a device flag and every run returns at its next shake, so the launch ends as soon as ANY seed
+ * got there (results[r].time_ms of that run = time to the target).  Each run is still a trajectory-exact prefix of the
+ * seeded reference run.  target <= 0 (default): off, only the reference's stopping rules (vns_sop_solver.cpp:178-193). */
+vnsgpu_status vnsgpu_set_target_reward(vnsgpu_ctx *ctx, double target);
 
 #ifdef __cplusplus
 }

@@ -212,6 +212,30 @@ def test_multi_start_batch_equals_single_seeded_runs(golden, eng_cache):
         assert p.getPathLengthCalculate() <= pb.budget
 
 
+def test_multi_start_race_stops_at_target_reward(golden, eng_cache):
+    """vnsgpu_set_target_reward: the launch ends once one seed's tour reaches the target; every run is then a PREFIX
+    of its seeded trajectory (its tour is one of the improvements the full run logs), the winner holds >= target,
+    and with the target switched off again the batch is the full runs."""
+    for name in ("berlin52", "opn_s08"):
+        e, sf, pb = eng_cache(name)
+        seeds = [1, 2, 3, 4, 5, 6, 7, 8]
+        full = {}
+        for sd in seeds:
+            r1, impr = e.path().vns_run(sd)
+            full[sd] = (r1, [(r, l) for r, l, _ in impr])
+        target = sorted(r.reward for r, _ in full.values())[len(seeds) // 2]       # the median final reward
+        p = e.path()
+        res, best = p.vns_run_batch(seeds, target_reward=target)
+        assert res[best].reward >= target and p.getReward() == res[best].reward
+        assert any(r.num_iters < full[sd][0].num_iters for r, sd in zip(res, seeds)), "nobody stopped early"
+        for r, sd in zip(res, seeds):
+            assert r.status == 0 and r.num_iters <= full[sd][0].num_iters
+            assert (r.reward, r.length) in full[sd][1], (name, sd)
+        res2, _ = e.path().vns_run_batch(seeds)                              # target off again (0)
+        for r, sd in zip(res2, seeds):
+            assert (r.reward, r.length, r.num_iters) == (full[sd][0].reward, full[sd][0].length, full[sd][0].num_iters)
+
+
 @pytest.mark.parametrize("int_path", [True, False])
 @pytest.mark.parametrize("name", ALL)
 def test_eval_batch_both_arithmetic_paths_vs_oracle(name, int_path, golden, eng_cache):

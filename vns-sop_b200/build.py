@@ -10,6 +10,7 @@ LIB = os.path.join(HERE, "libvnsgpu.so")
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
     "-fmad=false",          # parity: no FMA contraction (dx*dx+dy*dy in the table build, Dubins terms)
+    "-split-compile", "0",  # NVVM + ptxas of this one translation unit on all host cores
     "-Xcompiler", "-fPIC", "-shared",
 ]
 

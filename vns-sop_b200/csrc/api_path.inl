@@ -234,7 +234,12 @@ static vnsgpu_status prepare_seg(vnsgpu_ctx *ctx, int path, cudaStream_t st)
    if (!ctx->d_segmeta) CK(cudaMalloc(&ctx->d_segmeta, sizeof(int) * 3 * R));
    k_seg_offsets<<<1, 256, sizeof(int) * 2 * R, st>>>(I, ctx->paths[path].d, ctx->d_segmeta);
    LAUNCHED(ctx);
-   k_seg_build<<<I.rows, 128, 0, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta);
+   const size_t smem = seg_build_smem(I.rows, I.mp);
+   if (smem <= (size_t)ctx->max_smem) {
+      if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k_seg_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      k_seg_build<<<I.rows, 128, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta);
+   } else
+      k_seg_build_g<<<I.rows, 128, 0, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta);
    LAUNCHED(ctx);
    return VNSGPU_OK;
 }

@@ -200,6 +200,7 @@ vnsgpu_status vnsgpu_vns_run(vnsgpu_ctx *ctx, int path, const vnsgpu_vns_params 
    prm.num_iterations = p->num_iterations; prm.num_iterations_unimproved = p->num_iterations_unimproved;
    prm.skip = p->lower_bound_skip; prm.greedy = p->greedy_initial; prm.budget = p->budget;
    prm.max_time_ms = p->max_time_ms; prm.max_improvements = cap;
+   prm.target_reward = 0.0; prm.stop_flag = nullptr;
    {
       size_t smem = 0;
       const size_t extra = chain_smem(ctx) + sizeof(RngState) + 64;   // shake / fit / greedy scratch + statics
@@ -271,6 +272,11 @@ vnsgpu_status vnsgpu_vns_run_batch(vnsgpu_ctx *ctx, int path, int nruns, const u
       prm.num_iterations = p->num_iterations; prm.num_iterations_unimproved = p->num_iterations_unimproved;
       prm.skip = p->lower_bound_skip; prm.greedy = p->greedy_initial; prm.budget = p->budget;
       prm.max_time_ms = p->max_time_ms; prm.max_improvements = 0;
+      prm.target_reward = ctx->target_reward; prm.stop_flag = nullptr;
+      if (ctx->target_reward > 0) {
+         CK(cudaMemsetAsync(ctx->d_stop, 0, sizeof(int), ctx->stream));
+         prm.stop_flag = ctx->d_stop;
+      }
       s = as_int ? launch_chain_multi_v<int>(ctx, ctx->d_D32, nruns, d_slots, prm, smem + chain_smem(ctx))
                  : launch_chain_multi_v<double>(ctx, ctx->d_D, nruns, d_slots, prm, smem + chain_smem(ctx));
    }

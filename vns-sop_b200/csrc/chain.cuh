@@ -460,6 +460,14 @@ __device__ void chain_vns_body(const InstDev &I, const V *__restrict__ Dv, const
       int k = 1;
       while (k <= 2) {
          if (threadIdx.x == 0 && prm.max_time_ms > 0 && now_ms() - t0 >= prm.max_time_ms) s_stop = 1;  // :189-193
+         if (prm.stop_flag) {      // multi-start race: not part of the reference's loop
+            if (threadIdx.x == 0) {
+               if (tour.hd[HD_REWARD] >= prm.target_reward) atomicExch(prm.stop_flag, 1);
+               if (*(volatile int *)prm.stop_flag) s_stop = 2;
+            }
+            __syncthreads();
+            if (s_stop == 2) break;
+         }
          cta_copy_path(I, act, tour);                                    // :195-197
          const double r0 = act.hd[HD_REWARD], l0 = act.hd[HD_LEN];
          cta_shake(I, act, k, prm.budget, g, seg, vbuf_all);             // :202

@@ -393,12 +393,6 @@ k_eval_groups(InstDev I, const V *__restrict__ Dv, PathDev P, SegCache seg, long
    if (d_first && best != ULLONG_MAX) atomicMin(d_first, best);
 }
 
-// double -> int32 copy of an all-integer table (same block-major layout)
-__global__ void __launch_bounds__(256) k_table_to_int(const double *__restrict__ D, int *__restrict__ Di, long long n)
-{
-   for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < n; q += (long long)gridDim.x * blockDim.x) Di[q] = (int)D[q];
-}
-
 // sort key of the endpoint-vector kernel: candidates with a block step first
 __device__ __forceinline__ int vec_sort_key(int T, int C, const int4 &cd)
 {
@@ -515,7 +509,8 @@ __global__ void __launch_bounds__(256) k_seg_offsets(InstDev I, PathDev P, int *
 }
 
 // block a builds M(a,b) for b = a+2 .. S by M(a,b) = M(a,b-1) (x) D(b-1,b), M(a,a+1) = D(a,a+1)
-__global__ void __launch_bounds__(128) k_seg_build(InstDev I, PathDev P, int *Dv, const int *meta)
+// (global-memory form: any cluster size; every step is a global round trip)
+__global__ void __launch_bounds__(128) k_seg_build_g(InstDev I, PathDev P, int *Dv, const int *meta)
 {
    const int T = P.hdr[HDR_T], S = T + 1, R = I.rows + 3;
    const int a = blockIdx.x;
@@ -540,5 +535,57 @@ __global__ void __launch_bounds__(128) k_seg_build(InstDev I, PathDev P, int *Dv
       __syncthreads();
       prev = out;
       mk = mb;
+   }
+}
+
+// The same recurrence with the running product in shared memory (double-buffered) and the NEXT table block
+// arriving by cp.async while the current product is computed: a step costs one barrier instead of a global
+// round trip (the chain of block a has S - a - 1 dependent steps; block 0's chain is the kernel's duration).
+// dynamic shared memory: seg_build_smem(S, mp) bytes
+__host__ __device__ inline size_t seg_build_smem(int rows, int mp) { return sizeof(int) * ((size_t)2 * (rows + 3) + (size_t)4 * mp * mp); }
+
+__global__ void __launch_bounds__(128) k_seg_build(InstDev I, PathDev P, int *Dv, const int *meta)
+{
+   extern __shared__ int smem_i[];
+   const int T = P.hdr[HDR_T], S = T + 1, R = I.rows + 3, mp2 = I.mp * I.mp;
+   const int a = blockIdx.x;
+   if (a + 2 > S) return;
+   int *l_m = smem_i, *l_off = smem_i + R;                  // per layer l >= a: cluster size, first sample
+   int *prod = smem_i + 2 * R, *dblk = prod + 2 * mp2;       // two buffers each
+   for (int l = a + threadIdx.x; l <= S; l += blockDim.x) {
+      const int c = layer_cluster(I, P.tg, T, l);
+      l_m[l] = I.m[c]; l_off[l] = I.off[c];
+   }
+   __syncthreads();
+   const int *cum = meta;
+   const unsigned *rowoff = reinterpret_cast<const unsigned *>(meta + 2 * R);
+   const int ma = l_m[a];
+   auto blk = [&](int l) { return Dv + ((long long)l_off[l] * I.N + (long long)l_m[l] * l_off[l + 1]); };   // D(l, l+1)
+   auto fetch = [&](int *dst, const int *src, int n) {
+      for (int e = threadIdx.x; e < n; e += blockDim.x)
+         asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(dst + e)), "l"(src + e));
+      asm volatile("cp.async.commit_group;");
+   };
+   fetch(prod, blk(a), ma * l_m[a + 1]);
+   fetch(dblk, blk(a + 1), l_m[a + 1] * l_m[a + 2]);
+   asm volatile("cp.async.wait_group 0;");
+   __syncthreads();
+   int cur = 0;
+   for (int b = a + 2; b <= S; ++b) {
+      const int mk = l_m[b - 1], mb = l_m[b];
+      if (b < S) fetch(dblk + (cur ^ 1) * mp2, blk(b), mb * l_m[b + 1]);
+      const int *pv = prod + cur * mp2, *d = dblk + cur * mp2;
+      int *nx = prod + (cur ^ 1) * mp2;
+      int *out = Dv + (rowoff[a] + (unsigned)(ma * (cum[b] - cum[a + 2])));
+      for (int e = threadIdx.x; e < ma * mb; e += blockDim.x) {
+         const int i = e / mb, j = e - i * mb;
+         int acc = VNS_INT_INF;
+         for (int k = 0; k < mk; ++k) acc = __viaddmin_s32(pv[i * mk + k], d[k * mb + j], acc);
+         out[e] = acc;
+         nx[e] = acc;
+      }
+      asm volatile("cp.async.wait_group 0;");
+      __syncthreads();
+      cur ^= 1;
    }
 }

@@ -472,6 +472,10 @@ struct VnsParamsDev {
    int num_iterations, num_iterations_unimproved, skip, greedy;
    double budget, max_time_ms;
    int max_improvements;
+   // multi-start race (vnsgpu_set_target_reward): the first run whose tour reaches target_reward raises *stop_flag and
+   // every run leaves at its next shake; null = off (the reference's stopping rules only)
+   double target_reward;
+   int *stop_flag;
 };
 struct VnsResultDev {
    int num_iters, num_iters_last_impr, n_improvements, status;

@@ -62,6 +62,9 @@ struct vnsgpu_ctx {
    long long *d_first = nullptr;
    VnsResultDev *d_res = nullptr;
    long long *d_prof = nullptr;   // phase cycles of the shared-memory chain
+   int *d_stop = nullptr;         // stop flag of the multi-start race
+   double target_reward = 0.0;    // vnsgpu_set_target_reward
+   float table_kernel_ms = 0.f;   // device time of the last k_table_pairs launch
    std::string err;
    int64_t launches = 0;
    int num_sms = 148;
@@ -129,6 +132,7 @@ vnsgpu_status vnsgpu_create(vnsgpu_ctx **out, int device)
    CK(cudaMalloc(&ctx->d_prof, 4 * sizeof(long long)));
    CK(cudaMemset(ctx->d_prof, 0, 4 * sizeof(long long)));
    CK(cudaMalloc(&ctx->d_info, 2 * sizeof(unsigned long long)));
+   CK(cudaMalloc(&ctx->d_stop, sizeof(int)));
    return VNSGPU_OK;
 }
 
@@ -153,7 +157,7 @@ void vnsgpu_destroy(vnsgpu_ctx *ctx)
    cudaStreamSynchronize(ctx->stream);
    free_instance(ctx);
    cudaFree(ctx->d_scratch); cudaFree(ctx->d_rng); cudaFree(ctx->d_stats); cudaFree(ctx->d_first);
-   cudaFree(ctx->d_res); cudaFree(ctx->d_info); cudaFree(ctx->d_prof);
+   cudaFree(ctx->d_res); cudaFree(ctx->d_info); cudaFree(ctx->d_prof); cudaFree(ctx->d_stop);
    if (ctx->s_in) {
       cudaStreamDestroy(ctx->s_in); cudaStreamDestroy(ctx->s_out); cudaEventDestroy(ctx->ev_start);
       for (int k = 0; k < VNS_PIPE_EVENTS; ++k) { cudaEventDestroy(ctx->ev_in[k]); cudaEventDestroy(ctx->ev_k[k]); }
@@ -169,6 +173,12 @@ int64_t vnsgpu_table_bytes(const vnsgpu_ctx *ctx) { return 8ll * ctx->I.N * ctx-
 vnsgpu_status vnsgpu_set_stream(vnsgpu_ctx *ctx, void *stream)
 {
    ctx->stream = stream ? (cudaStream_t)stream : ctx->own;
+   return VNSGPU_OK;
+}
+
+vnsgpu_status vnsgpu_set_target_reward(vnsgpu_ctx *ctx, double target)
+{
+   ctx->target_reward = target;
    return VNSGPU_OK;
 }
 
@@ -271,36 +281,55 @@ static dim3 band_grid(const vnsgpu_ctx *ctx)
    return dim3(gx, ctx->I.C);
 }
 
-// bounds + table classification after any table (re)build
-static vnsgpu_status finish_table(vnsgpu_ctx *ctx)
+} // extern "C"
+
+// The whole table build: ONE fused pass (k_table_pairs: entries as double and as int32, cluster-pair bounds,
+// classification), then the decision whether the exact integer path applies.
+template <int KIND>
+static vnsgpu_status build_table(vnsgpu_ctx *ctx, TableJob J, bool maybe_int)
 {
+   const InstDev &I = ctx->I;
+   const long long nn = (long long)I.N * I.N;
+   // room behind the int32 table for the segment products of any path: <= (N + mp)^2 / 2 entries
+   const long long segcap = ((long long)I.N + I.mp + 1) * ((long long)I.N + I.mp + 1) / 2;
+   if (ctx->d_D32) { CK(cudaFree(ctx->d_D32)); ctx->d_D32 = nullptr; }
+   if (maybe_int) {   // optimistic: the copy is dropped again if the classification says no
+      ctx->seg_ok = nn + segcap < (1ll << 32);
+      if (cudaMalloc(&ctx->d_D32, sizeof(int) * (size_t)(nn + (ctx->seg_ok ? segcap : 0)) + 64) != cudaSuccess) {
+         cudaGetLastError();
+         ctx->d_D32 = nullptr;
+      }
+   }
    CK(cudaMemsetAsync(ctx->d_info, 0, 2 * sizeof(unsigned long long), ctx->stream));
-   const long long npairs = (long long)ctx->I.C * ctx->I.C;
-   const int blocks = (int)((npairs * 32 + 255) / 256);
-   k_bounds<<<blocks, 256, 0, ctx->stream>>>(ctx->I, ctx->d_dmin, ctx->d_dmax, ctx->d_info);
+   J.D = ctx->d_D; J.Di = ctx->d_D32; J.dmin = ctx->d_dmin; J.dmax = ctx->d_dmax; J.info = ctx->d_info;
+   const long long npairs = (long long)I.C * I.C;
+   const int blocks = (int)std::min<long long>((npairs + 7) / 8, (long long)ctx->num_sms * 64);
+   cudaEvent_t e0, e1;
+   CK(cudaEventCreate(&e0));
+   CK(cudaEventCreate(&e1));
+   CK(cudaEventRecord(e0, ctx->stream));
+   k_table_pairs<KIND><<<blocks, 256, 0, ctx->stream>>>(I, J);
    LAUNCHED(ctx);
+   CK(cudaEventRecord(e1, ctx->stream));
    unsigned long long info[2];
    CK(cudaMemcpyAsync(info, ctx->d_info, sizeof(info), cudaMemcpyDeviceToHost, ctx->stream));
    CK(cudaStreamSynchronize(ctx->stream));
+   CK(cudaEventElapsedTime(&ctx->table_kernel_ms, e0, e1));
+   cudaEventDestroy(e0); cudaEventDestroy(e1);
    double mx;
    memcpy(&mx, &info[1], sizeof(double));
    // integers below 2^53 / (layers+1): every partial path sum is exact in double
-   ctx->I.exact_int = (info[0] == 0 && mx * (double)(ctx->I.rows + 1) < 9007199254740992.0) ? 1 : 0;
-   // int32 copy for the DPX path: INF + INF and every partial path sum must stay below 2^31
-   if (ctx->d_D32) { CK(cudaFree(ctx->d_D32)); ctx->d_D32 = nullptr; }
-   if (ctx->I.exact_int && mx * (double)(ctx->I.rows + 1) < 536870912.0) {
-      const long long nn = (long long)ctx->I.N * ctx->I.N;
-      // room behind the table for the segment products of any path: <= (N + mp)^2 / 2 entries
-      const long long segcap = ((long long)ctx->I.N + ctx->I.mp + 1) * ((long long)ctx->I.N + ctx->I.mp + 1) / 2;
-      ctx->seg_ok = nn + segcap < (1ll << 32);
-      CK(cudaMalloc(&ctx->d_D32, sizeof(int) * (size_t)(nn + (ctx->seg_ok ? segcap : 0)) + 64));
-      k_table_to_int<<<(int)std::min<long long>((nn + 255) / 256, 148 * 16), 256, 0, ctx->stream>>>(ctx->d_D, ctx->d_D32, nn);
-      LAUNCHED(ctx);
-      CK(cudaStreamSynchronize(ctx->stream));
+   ctx->I.exact_int = (info[0] == 0 && mx * (double)(I.rows + 1) < 9007199254740992.0) ? 1 : 0;
+   // the int32 copy feeds the DPX path: INF + INF and every partial path sum must stay below 2^31
+   if (ctx->d_D32 && !(ctx->I.exact_int && mx * (double)(I.rows + 1) < 536870912.0)) {
+      CK(cudaFree(ctx->d_D32));
+      ctx->d_D32 = nullptr;
    }
    ctx->have_table = true;
    return VNSGPU_OK;
 }
+
+extern "C" {
 
 vnsgpu_status vnsgpu_build_table_euclid(vnsgpu_ctx *ctx, const double *xy, int rule)
 {
@@ -311,9 +340,9 @@ vnsgpu_status vnsgpu_build_table_euclid(vnsgpu_ctx *ctx, const double *xy, int r
    vnsgpu_status s = need_scratch(ctx, bytes);
    if (s) return s;
    CK(cudaMemcpyAsync(ctx->d_scratch, xy, bytes, cudaMemcpyHostToDevice, ctx->stream));
-   k_table_euclid<<<band_grid(ctx), 256, 0, ctx->stream>>>(ctx->I, (const double2 *)ctx->d_scratch, rule, ctx->d_D);
-   LAUNCHED(ctx);
-   return finish_table(ctx);
+   TableJob J{};
+   J.pts = (const double2 *)ctx->d_scratch; J.rule = rule;
+   return build_table<0>(ctx, J, rule != VNSGPU_RULE_RAW);
 }
 
 vnsgpu_status vnsgpu_build_table_dubins(vnsgpu_ctx *ctx, const double *centers, int S, double rho, int do_ceil)
@@ -325,9 +354,9 @@ vnsgpu_status vnsgpu_build_table_dubins(vnsgpu_ctx *ctx, const double *centers, 
    vnsgpu_status s = need_scratch(ctx, bytes);
    if (s) return s;
    CK(cudaMemcpyAsync(ctx->d_scratch, centers, bytes, cudaMemcpyHostToDevice, ctx->stream));
-   k_table_dubins<<<band_grid(ctx), 256, 0, ctx->stream>>>(ctx->I, (const double2 *)ctx->d_scratch, S, rho, do_ceil, ctx->d_D);
-   LAUNCHED(ctx);
-   return finish_table(ctx);
+   TableJob J{};
+   J.pts = (const double2 *)ctx->d_scratch; J.S = S; J.rho = rho; J.do_ceil = do_ceil;
+   return build_table<1>(ctx, J, do_ceil != 0);
 }
 
 vnsgpu_status vnsgpu_set_table_dense(vnsgpu_ctx *ctx, const double *W)
@@ -338,10 +367,12 @@ vnsgpu_status vnsgpu_set_table_dense(vnsgpu_ctx *ctx, const double *W)
    vnsgpu_status s = need_scratch(ctx, bytes);
    if (s) return s;
    CK(cudaMemcpyAsync(ctx->d_scratch, W, bytes, cudaMemcpyHostToDevice, ctx->stream));
-   k_table_gather<<<band_grid(ctx), 256, 0, ctx->stream>>>(ctx->I, ctx->d_D, (double *)ctx->d_scratch, 0);
-   LAUNCHED(ctx);
-   return finish_table(ctx);
+   TableJob J{};
+   J.W = (const double *)ctx->d_scratch;
+   return build_table<2>(ctx, J, true);
 }
+
+double vnsgpu_table_kernel_ms(const vnsgpu_ctx *ctx) { return (double)ctx->table_kernel_ms; }
 
 vnsgpu_status vnsgpu_get_table_dense(vnsgpu_ctx *ctx, double *W)
 {

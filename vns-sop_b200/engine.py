@@ -57,6 +57,7 @@ _SIGS = {
     "vnsgpu_set_batch_sort": [vp, C.c_int],
     "vnsgpu_set_segment_cache": [vp, C.c_int],
     "vnsgpu_set_smem_chain": [vp, C.c_int],
+    "vnsgpu_set_target_reward": [vp, C.c_double],
     "vnsgpu_chain_cycles": [vp, C.POINTER(C.c_int64), C.c_int],
     "vnsgpu_int_path_active": [vp],
     "vnsgpu_set_clusters": [vp, C.c_int, ip, dp, C.c_int, C.c_int],
@@ -88,7 +89,7 @@ _SIGS = {
     "vnsgpu_set_vector_cache": [vp, C.c_int],
 }
 EXPORTS = sorted(list(_SIGS) + ["vnsgpu_destroy", "vnsgpu_last_error", "vnsgpu_version", "vnsgpu_launch_count",
-                                "vnsgpu_table_bytes", "vnsgpu_rng_seed", "vnsgpu_rng_next"])
+                                "vnsgpu_table_bytes", "vnsgpu_table_kernel_ms", "vnsgpu_rng_seed", "vnsgpu_rng_next"])
 
 
 def load_library(build_if_stale=True):
@@ -110,6 +111,7 @@ def load_library(build_if_stale=True):
     lib.vnsgpu_version.argtypes, lib.vnsgpu_version.restype = [], C.c_char_p
     lib.vnsgpu_launch_count.argtypes, lib.vnsgpu_launch_count.restype = [vp], C.c_int64
     lib.vnsgpu_table_bytes.argtypes, lib.vnsgpu_table_bytes.restype = [vp], C.c_int64
+    lib.vnsgpu_table_kernel_ms.argtypes, lib.vnsgpu_table_kernel_ms.restype = [vp], C.c_double
     lib.vnsgpu_rng_seed.argtypes, lib.vnsgpu_rng_seed.restype = [C.POINTER(Rng), C.c_uint32], None
     lib.vnsgpu_rng_next.argtypes, lib.vnsgpu_rng_next.restype = [C.POINTER(Rng)], C.c_int32
     _lib = lib
@@ -192,6 +194,10 @@ class Engine:
         self._ck(self.lib.vnsgpu_chain_cycles(self.h, out, int(reset)))
         return dict(zip(("propose", "evaluate", "select", "apply"), out))
 
+    def set_target_reward(self, target):
+        """Race mode of vns_run_batch: every run stops once one run's tour reaches `target` (<= 0: off)."""
+        self._ck(self.lib.vnsgpu_set_target_reward(self.h, float(target)))
+
     def set_smem_chain(self, enable):
         self._ck(self.lib.vnsgpu_set_smem_chain(self.h, int(enable)))
 
@@ -229,6 +235,10 @@ class Engine:
     def build_table_euclid(self, xy, rule):
         xy = np.ascontiguousarray(xy, np.float64)
         self._ck(self.lib.vnsgpu_build_table_euclid(self.h, _d(xy), rule))
+
+    def build_table_dubins(self, centers, S, rho, do_ceil=1):
+        ctr = np.ascontiguousarray(centers, np.float64)
+        self._ck(self.lib.vnsgpu_build_table_dubins(self.h, _d(ctr), S, rho, do_ceil))
 
     def table_dense(self):
         W = np.empty((self.N, self.N))
@@ -445,10 +455,12 @@ class VnsSopPath:
         return res, list(zip(ir[:n], il[:n], it[:n]))
 
     def vns_run_batch(self, seeds, num_iterations=2000, num_iterations_unimproved=1000, skip=1, greedy=1, budget=None,
-                      max_time_ms=0.0):
+                      max_time_ms=0.0, target_reward=0.0):
         """Multi-start (the reference's --batch=N): one device chain per seed in ONE launch ->
-        (list of VnsResult, index of the best run); the best tour replaces this path."""
+        (list of VnsResult, index of the best run); the best tour replaces this path.  target_reward > 0: race -
+        the launch ends as soon as one run's tour reaches it (vnsgpu_set_target_reward)."""
         budget = self.e.pb.budget if budget is None else budget
+        self.e.set_target_reward(target_reward)
         prm = VnsParams(num_iterations, num_iterations_unimproved, skip, greedy, budget, max_time_ms, 0, 0)
         n = len(seeds)
         sd = (C.c_uint32 * n)(*[int(x) for x in seeds])
