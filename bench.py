@@ -48,6 +48,12 @@ WORKLOADS = {
     # BASELINE.json config 5: generated (vns-sop_b200/synthetic.py), table far beyond L2 - the HBM regime
     "synth20k": ("synthetic scaled SOP: 20000 nodes / 2000 clusters of 10, CEIL_2D (generated, seed 20190147)", None, {"n_points": 20000}),
     "synth2k": ("synthetic scaled SOP: 2000 nodes / 200 clusters of 10, CEIL_2D (generated, seed 20190147)", None, {"n_points": 2000}),
+    # BASELINE.json config 5, DOP flavour: 2000 locations x 32 heading samples = 64 064 samples; the 32.8 GB table only ever
+    # exists on the device (vnsgpu_build_table_dubins), so this workload has no CPU legs
+    "synth_dop64k": ("synthetic scaled DOP: 2000 locations x 32 heading samples (64064 samples, Dubins table built on the device, "
+                     "rho = 0.5% of the box; generated, seed 20190147)", None, {"dop": {"n_centres": 2000, "headings": 32}}),
+    "synth_dop4k": ("synthetic scaled DOP: 500 locations x 8 heading samples (generated, seed 20190147)", None,
+                    {"dop": {"n_centres": 500, "headings": 8}}),
 }
 STATE = "the greedy initial tour (greedy_insertion, vns_sop_solver.cpp:1091-1155; SURVEY.md 8d)"
 STATE_SYNTH = ("nearest-neighbour tour over the cluster centroids cut at 85% of the budget (greedy_insertion is "
@@ -70,6 +76,7 @@ def parse_args():
     ap.add_argument("--no-solve", action="store_true", help="skip the time-to-reward leg")
     ap.add_argument("--vector-cache", type=int, default=1, help="vnsgpu_set_vector_cache: 0 off, 1 auto (batch >= 4 C^2), 2 always")
     ap.add_argument("--no-solve-cpu", action="store_true", help="time-to-reward: skip the reference binary runs (long on vm1084)")
+    ap.add_argument("--sweep", action="store_true", help="candidate-batch sweep 2^10 .. --batch (x4 steps), device-resident (BASELINE config 5)")
     ap.add_argument("--multi-start", type=int, default=148, help="seeds of the multi-start leg (0 = skip)")
     return ap.parse_args()
 
@@ -104,11 +111,22 @@ def make_candidates(n, vns, T, seed):
 
 def dubins_S(name):
     w = WORKLOADS[name]
+    if len(w) > 2 and "dop" in w[2]:
+        return w[2]["dop"]["headings"]
     return w[2]["dubins_S"] if len(w) > 2 and "dubins_S" in w[2] else 0
+
+
+def device_only(name):
+    """Workloads whose table is never materialised on the host (no CPU legs)."""
+    w = WORKLOADS[name]
+    return len(w) > 2 and "dop" in w[2]
 
 
 def load_workload(name):
     from vns_sop_b200 import instances as ins
+    if WORKLOADS[name][1] is None and "dop" in WORKLOADS[name][2]:
+        from vns_sop_b200 import synthetic
+        return None, synthetic.generate_dop(**WORKLOADS[name][2]["dop"])      # no file form: the table is device-only
     if WORKLOADS[name][1] is None:
         from vns_sop_b200 import synthetic
         sf = synthetic.generate(**WORKLOADS[name][2])
@@ -135,9 +153,9 @@ def fill_dubins_weights(sf, pb, W):
 
 def workload_state(name, pb):
     """(vns, T) the candidates are drawn against, or None = run greedy_insertion (dataset instances)."""
-    if WORKLOADS[name][1] is None and pb.xy is not None:
+    if WORKLOADS[name][1] is None and (pb.xy is not None or device_only(name)):
         from vns_sop_b200 import synthetic
-        return synthetic.centroid_tour_state(pb)
+        return synthetic.centroid_tour_state(pb, 0.6 if device_only(name) else 0.85)
     return None
 
 
@@ -205,6 +223,10 @@ def host_cores():
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
+        return
+    if device_only(args.workload):
+        print(json.dumps({"impl": "reference", "unavailable": "the 33 GB table of this workload only exists on the device; the reference's "
+                          "4-deep vector table (copied by value 4 times) does not fit the host"}), flush=True)
         return
     import multiprocessing as mp
     cores = host_cores()
@@ -374,7 +396,10 @@ def run_b200(args):
         return float(t.item())
 
     sf, pb = load_workload(args.workload)
-    if dubins_S(args.workload):
+    if device_only(args.workload):
+        args.no_cpu = args.no_solve = True
+        eng = engine.Engine(local).load_problem(pb, dubins=(dubins_S(args.workload), pb.dubins_radius, 1))
+    elif dubins_S(args.workload):
         eng = engine.Engine(local).load_problem(pb, dubins=(dubins_S(args.workload), sf.dubins_radius, 1))
         fill_dubins_weights(sf, pb, eng.table_dense())
     else:
@@ -390,7 +415,7 @@ def run_b200(args):
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         if S_:
-            eng.build_table_dubins(pb.centers, S_, sf.dubins_radius, 1)
+            eng.build_table_dubins(pb.centers, S_, pb.dubins_radius, 1)
         else:
             eng.build_table_euclid(pb.xy, pb.rule)
         torch.cuda.synchronize()
@@ -461,6 +486,36 @@ def run_b200(args):
     value = world * n * K / (total_ms * 1e-3)
     first_dev = int(d_first.item())
     ok_flags = int(((d_fl & 2) != 0).sum().item())
+
+    # ---- candidate-batch sweep (BASELINE config 5): the same call on the first b candidates of the batch ---------
+    sweep = None
+    if args.sweep:
+        sweep = []
+        b = 1 << 10
+        sizes = []
+        while b < n:
+            sizes.append(b)
+            b <<= 2
+        sizes.append(n)
+        with torch.cuda.stream(stream):
+            for b in sizes:
+                def sstep():
+                    eng._ck(lib.vnsgpu_eval_batch_dev(eng.h, p.h, b, C.c_void_p(d_c.data_ptr()), pb.budget, 1,
+                                                      C.c_void_p(d_len.data_ptr()), C.c_void_p(d_lb.data_ptr()),
+                                                      C.c_void_p(d_fl.data_ptr()), C.c_void_p(d_first.data_ptr()), sp))
+                    if world > 1:
+                        sharding.reduce_first_accept_(d_first, rank * b)
+                for _ in range(W):
+                    sstep()
+                s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                barrier()
+                s0.record(stream)
+                for _ in range(K):
+                    sstep()
+                s1.record(stream)
+                barrier()
+                ms = max_over_ranks(s0.elapsed_time(s1))
+                sweep.append({"batch_per_gpu": b, "evals_per_s": world * b * K / (ms * 1e-3), "ms_per_step": ms / K})
 
     # ---- e2e: the host-buffer C-ABI call (H2D of the candidates + kernel + D2H of lengths and flags) --
     e2e = None
@@ -572,6 +627,8 @@ def run_b200(args):
     }
     if table_build:
         line["table_build"] = table_build
+    if sweep:
+        line["batch_sweep"] = sweep
     if rank == 0 and world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline_leg(args, sf, pb, vns, T, rows, d_len, d_lb, state)
     if rank == 0 and world == 1 and not args.no_solve and state is None:

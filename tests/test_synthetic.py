@@ -145,3 +145,48 @@ def test_20k_instance_properties():
             assert q.getPathLength() == want
     finally:
         e.close()
+
+
+def test_dop_generator_is_deterministic():
+    from vns_sop_b200 import synthetic as sy
+    a, b = sy.generate_dop(120, 8), sy.generate_dop(120, 8)
+    assert (a.centers == b.centers).all() and a.budget == b.budget
+    assert a.C == 122 and a.N == 122 * 8 and (a.m == 8).all() and a.start == 0 and a.goal == 121
+    assert (a.centers[0] == a.centers[-1]).all()               # goal = the depot again (duplicated end set)
+    assert a.reward[0] == a.reward[-1] == 0 and (a.reward[1:-1] == 1).all()
+    vns, T = sy.centroid_tour_state(a, 0.6)
+    assert sorted(vns.tolist()) == list(range(1, 121)) and 5 < T < 120
+    big = sy.generate_dop()                                    # the bench workload: 2000 x 32, no table on the host
+    assert big.N == 64064 and big.N ** 2 < 2 ** 32 and big.W is None and big.xy is None
+
+
+@pytest.mark.gpu
+def test_synthetic_dop_candidates_vs_oracle():
+    """DOP flavour (asymmetric Dubins table built on the device, every cluster 8 heading samples): the table
+    and all three evaluation forms against the oracle, which computes the same table on the CPU."""
+    from oracle import binding as ob
+    from vns_sop_b200 import engine, synthetic as sy
+    pb = sy.generate_dop(120, 8)
+    e = engine.Engine(0).load_problem(pb, dubins=(8, pb.dubins_radius, 1))
+    try:
+        o = ob.Oracle(pb, dubins=(8, pb.dubins_radius, 1))
+        Wg, Wo = e.table_dense(), o.dense()
+        off_diag = ~np.eye(pb.N, dtype=bool)                   # identical states are ill-conditioned (DESIGN.md 2)
+        assert (Wg[off_diag] == Wo[off_diag]).mean() > 0.9999
+        pb.W = Wg                                              # evaluate both sides on the device-built table
+        o = ob.Oracle(pb)
+        vns, T = sy.centroid_tour_state(pb, 0.6)
+        pg, po = e.path(vns, T), o.path(vns, T)
+        assert pg.getPathLength() == po.length() and pg.getPathLengthRear() == po.length_rear()
+        rs = np.random.RandomState(9)
+        cands = random_candidates(rs, vns, T, 70000)           # >= 4 C^2: the endpoint-vector form engages
+        oln, olb = po.eval_batch(cands)
+        for int_path in (True, False):
+            e.set_int_path(int_path)
+            for seg, vec in ((True, True), (True, False), (False, False)):
+                e.set_segment_cache(seg)
+                e.set_vector_cache(vec)
+                ln, lb, fl, first = pg.eval_batch(pg.make_cands(cands))
+                assert (ln == oln).all() and (lb == olb).all(), (int_path, seg, vec)
+    finally:
+        e.close()

@@ -10,7 +10,6 @@ LIB = os.path.join(HERE, "libvnsgpu.so")
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
     "-fmad=false",          # parity: no FMA contraction (dx*dx+dy*dy in the table build, Dubins terms)
-    "-split-compile", "0",  # NVVM + ptxas of this one translation unit on all host cores
     "-Xcompiler", "-fPIC", "-shared",
 ]
 
@@ -30,7 +29,10 @@ def build(force=False, verbose=False):
     if not force and not stale():
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB, os.path.join(CSRC, "vnsgpu.cu")]
+    # VNSGPU_SPLIT_COMPILE=1: NVVM + ptxas of this one translation unit on all host cores (80 s instead of 4 min) - for
+    # development only: the split changes register allocation (the latency-bound chain kernels lose ~10 %)
+    split = ["-split-compile", "0"] if os.environ.get("VNSGPU_SPLIT_COMPILE") == "1" else []
+    cmd = [nvcc] + NVCC_FLAGS + split + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB, os.path.join(CSRC, "vnsgpu.cu")]
     subprocess.check_call(cmd, cwd=CSRC)
     return LIB
 

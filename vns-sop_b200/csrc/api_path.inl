@@ -231,7 +231,7 @@ static vnsgpu_status prepare_seg(vnsgpu_ctx *ctx, int path, cudaStream_t st)
 {
    const InstDev &I = ctx->I;
    const int R = I.rows + 3;
-   if (!ctx->d_segmeta) CK(cudaMalloc(&ctx->d_segmeta, sizeof(int) * 3 * R));
+   if (!ctx->d_segmeta) CK(cudaMalloc(&ctx->d_segmeta, sizeof(int) * 6 * R));
    k_seg_offsets<<<1, 256, sizeof(int) * 2 * R, st>>>(I, ctx->paths[path].d, ctx->d_segmeta);
    LAUNCHED(ctx);
    const size_t smem = seg_build_smem(I.rows, I.mp);
@@ -257,8 +257,14 @@ static vnsgpu_status prepare_eval(vnsgpu_ctx *ctx, int path, int mode, cudaStrea
       CK(cudaMemsetAsync(ctx->d_vec, 0, sizeof(int) * vec_ints(I.C, LS, I.mp), st));
       CK(cudaMemsetAsync(ctx->d_veclb, 0, sizeof(int) * vec_lb_ints(I.C, LS), st));
    }
-   const long long warps = (long long)(I.C + 1) * LS;   // upper bound of (C + 1) (T + 2)
-   k_vec_build<<<(unsigned)((warps + 7) / 8), 256, 0, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_vec, ctx->d_veclb, LS);
+   // T is only known on the device: grids sized for its bound (T + 2 <= C), surplus warps return at once
+   const int Smax = std::min(I.rows, I.C);
+   const int thr = I.mp <= 22 ? 256 : 128;                      // 2 staged blocks per warp: <= 32 KB per CTA
+   const size_t smem = sizeof(int) * 2 * (size_t)I.mp * I.mp * (thr / 32);
+   const int wpc = thr / 32;
+   k_vec_uw<<<dim3((I.C + wpc - 1) / wpc, Smax), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta, ctx->d_vec, ctx->d_veclb, LS);
+   LAUNCHED(ctx);
+   k_vec_pairs<<<dim3((Smax + 1 + wpc - 1) / wpc, Smax), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta, ctx->d_vec, LS);
    LAUNCHED(ctx);
    return VNSGPU_OK;
 }
@@ -300,7 +306,7 @@ static vnsgpu_status launch_eval(vnsgpu_ctx *ctx, int path, int64_t n, int64_t i
       if (useseg) {
          const int R = I.rows + 3;
          seg.cum = ctx->d_segmeta; seg.pd = ctx->d_segmeta + R;
-         seg.rowoff = reinterpret_cast<const unsigned *>(ctx->d_segmeta + 2 * R);
+         seg.rowoff = reinterpret_cast<const long long *>(ctx->d_segmeta + 2 * R);
       }
 #define VNS_LAUNCH_EVAL(V, GG, RR, SS, TAB)                                                                          \
    do {                                                                                                              \
@@ -320,18 +326,26 @@ static vnsgpu_status launch_eval(vnsgpu_ctx *ctx, int path, int64_t n, int64_t i
    } while (0)
       if (useseg == 2) {
          VecCache vc{ctx->d_vec, ctx->d_veclb, I.C + 2};
+#define VNS_LAUNCH_VEC_L(GG, RR, LL)                                                                                 \
+   do {                                                                                                              \
+      if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k_eval_vec<GG, RR, LL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+      k_eval_vec<GG, RR, LL><<<grid, VNS_EVAL_THREADS, smem, st>>>(I, ctx->d_D32, P, seg, vc, n, idx0, d_cands, d_perm, budget, skip, d_len, \
+                                                                   d_lb, d_flags, d_first);                          \
+   } while (0)
 #define VNS_LAUNCH_VEC(GG, RR)                                                                                       \
    do {                                                                                                              \
-      if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k_eval_vec<GG, RR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-      k_eval_vec<GG, RR><<<grid, VNS_EVAL_THREADS, smem, st>>>(I, ctx->d_D32, P, seg, vc, n, idx0, d_cands, d_perm, budget, skip, d_len, \
-                                                               d_lb, d_flags, d_first);                              \
+      if (lat) VNS_LAUNCH_VEC_L(GG, RR, true);                                                                        \
+      else VNS_LAUNCH_VEC_L(GG, RR, false);                                                                           \
    } while (0)
+         // tables beyond the caches (synthetic scaled instances): latency form of the block step
+         const bool lat = (size_t)I.N * I.N * sizeof(int) > ((size_t)48 << 20);
          if (G == 8 && NR == 1) VNS_LAUNCH_VEC(8, 1);
          else if (G == 8 && NR == 2) VNS_LAUNCH_VEC(8, 2);
          else if (G == 8) VNS_LAUNCH_VEC(8, 4);
          else if (G == 16 && NR == 1) VNS_LAUNCH_VEC(16, 1);
          else if (G == 16) VNS_LAUNCH_VEC(16, 2);
          else VNS_LAUNCH_VEC(32, 1);
+#undef VNS_LAUNCH_VEC_L
 #undef VNS_LAUNCH_VEC
       } else if (ctx->use_int && ctx->d_D32) {
          if (useseg) VNS_LAUNCH_EVAL_V(int, true, ctx->d_D32);

@@ -292,7 +292,7 @@ __device__ void chain_local_search(const InstDev &I, const V *__restrict__ Dv, c
                const int ca = la < 0 ? cc.foreign : s.lcl[la], cb = lb_ < 0 ? cc.foreign : s.lcl[lb_];
                const int2 cia = s.cinfo[ca], cib = s.cinfo[cb];
                EdgeDesc e;
-               e.rb = (unsigned)cia.x * (unsigned)I.N + (unsigned)cia.y * (unsigned)cib.x;
+               e.rb = (long long)cia.x * I.N + (long long)cia.y * cib.x;
                e.ma = cia.y; e.mb = cib.y;
                e.dm = __ldg(I.dmin + (size_t)ca * I.C + cb);
                return e;

@@ -20,6 +20,7 @@ struct InstDev {
    int C, N, mp, start, goal;
    int rows;        // row capacity of a path (2C+2: the shakes add a range before removing one)
    int exact_int;   // every table entry is an integer and all path sums stay < 2^53
+   int symmetric;   // D(c1,c2)[i][j] == D(c2,c1)[j][i] bit for bit (Euclidean builds): a column strip is a row band
    const int *m, *off, *clof;  // clof[s] = cluster of sample s
    const double *reward;
    const double *D;

@@ -81,7 +81,7 @@ __device__ __forceinline__ CandCode decode_cand(int T, int C, int op, int a, int
 // shared memory: layer -> cluster map of the path (T+2 ints, padded to even) + per-cluster {offset, size}
 __host__ __device__ inline size_t eval_smem_bytes(int T, int C)
 {
-   return sizeof(int) * (size_t)(((T + 2 + 1) & ~1) + 2 * C + 3 * (T + 3));   // + cum, pd, rowoff of the segment cache
+   return sizeof(int) * (size_t)(((T + 2 + 1) & ~1) + 2 * C + 4 * (T + 3));   // + rowoff (64-bit), cum, pd of the segment cache
 }
 
 // layer of chain node k (see CandCode)
@@ -104,7 +104,7 @@ __device__ __forceinline__ int cand_layer(const CandCode &cc, int k)
 // shape, dmin, and - by xor-shuffles across the groups - the warp-wide loop bounds); the edge loop
 // then gets everything it needs from two broadcasts per edge.
 struct EdgeDesc {
-   unsigned rb;   // element offset of the block (row-major ma x mb) from Dv
+   long long rb;  // element offset of the block (row-major ma x mb) from Dv (64-bit: tables beyond 2^32 entries)
    int ma, mb;
    double dm;     // its contribution to dist_between of the lower bound
 };
@@ -136,7 +136,8 @@ __device__ __forceinline__ void groups_eval(const V *__restrict__ Dv, int K, int
    const int Kmax = __reduce_max_sync(FULL, K);
    for (int e0 = 0; e0 < Kmax; e0 += G) {
       // ---- describe edge k = e0 + gl + 1 ------------------------------------------------------
-      unsigned e_rb = 0, e_w;
+      long long e_rb = 0;
+      unsigned e_w;
       double e_dm = 0.0;
       {
          const int k = e0 + gl + 1;
@@ -158,7 +159,7 @@ __device__ __forceinline__ void groups_eval(const V *__restrict__ Dv, int K, int
       const int kend = min(G, Kmax - e0);
       for (int kk = 0; kk < kend; ++kk) {
          const int k = e0 + kk + 1;
-         const unsigned rb = __shfl_sync(FULL, e_rb, kk, G);
+         const V *blk = Dv + __shfl_sync(FULL, e_rb, kk, G);
          const unsigned w = __shfl_sync(FULL, e_w, kk, G);
          const int ma = w & 0xff, mb = (w >> 8) & 0xff, tmaxAll = (w >> 16) & 0x3f, nvmax = w >> 24;
          const bool trn = (w >> 22) & 1;
@@ -179,7 +180,7 @@ __device__ __forceinline__ void groups_eval(const V *__restrict__ Dv, int K, int
          for (int rd = 0; rd < NR; ++rd) {
             acc[rd] = INF;
             if (rd == 0 || nvmax > rd * G) {                 // warp-uniform
-               const unsigned cbase = rb + (unsigned)(min(gl + rd * G, nvalid - 1) * sn);
+               const unsigned cbase = (unsigned)(min(gl + rd * G, nvalid - 1) * sn);
 #pragma unroll
                for (int rs = 0; rs < NR; ++rs) {
                   if (rs == 0 || tmaxAll > rs * G) {         // warp-uniform
@@ -190,7 +191,7 @@ __device__ __forceinline__ void groups_eval(const V *__restrict__ Dv, int K, int
                      if (LAT) {
                         V dd[G];
 #pragma unroll
-                        for (int t = 0; t < G; ++t) dd[t] = __ldg(Dv + (sb + (unsigned)(min(t, tlim) * sl)));
+                        for (int t = 0; t < G; ++t) dd[t] = __ldg(blk + (sb + (unsigned)(min(t, tlim) * sl)));
 #pragma unroll
                         for (int t = 0; t < G; ++t) acc[rd] = Ops::add_min(acc[rd], __shfl_sync(FULL, opnd, min(t, tlim), G), dd[t]);
                      } else {
@@ -198,7 +199,7 @@ __device__ __forceinline__ void groups_eval(const V *__restrict__ Dv, int K, int
                         for (int t = 0; t < tm; ++t) {
                            const int tt = min(t, tlim);
                            const V x = __shfl_sync(FULL, opnd, tt, G);
-                           const V dd = __ldg(Dv + (sb + (unsigned)(tt * sl)));
+                           const V dd = __ldg(blk + (sb + (unsigned)(tt * sl)));
                            acc[rd] = Ops::add_min(acc[rd], x, dd);
                         }
                      }
@@ -236,7 +237,7 @@ __device__ __forceinline__ void groups_eval(const V *__restrict__ Dv, int K, int
 // M(a,b) is row-major m_a x m_b at element offset rowoff[a] + m_a * (cum[b] - cum[a+2]) from the table.
 struct SegCache {
    const int *cum;          // cum[l] = samples in layers < l, l = 0 .. S+1
-   const unsigned *rowoff;  // per layer a
+   const long long *rowoff; // per layer a
    const int *pd;           // pd[l] = sum_{l' < l} dmin(layer l', layer l'+1): dist_between of a run
 };
 
@@ -303,8 +304,8 @@ k_eval_groups(InstDev I, const V *__restrict__ Dv, PathDev P, SegCache seg, long
    int2 *cinfo = reinterpret_cast<int2 *>(smem_i + ((T + 2 + 1) & ~1));
    for (int l = threadIdx.x; l < T + 2; l += blockDim.x) lcl[l] = layer_cluster(I, P.tg, T, l);
    for (int c = threadIdx.x; c < I.C; c += blockDim.x) cinfo[c] = make_int2(I.off[c], I.m[c]);
-   int *s_cum = reinterpret_cast<int *>(cinfo + I.C), *s_pd = s_cum + (T + 3);
-   unsigned *s_rowoff = reinterpret_cast<unsigned *>(s_pd + (T + 2));
+   long long *s_rowoff = reinterpret_cast<long long *>(cinfo + I.C);
+   int *s_cum = reinterpret_cast<int *>(s_rowoff + (T + 2)), *s_pd = s_cum + (T + 3);
    if (SEG) {
       for (int l = threadIdx.x; l < T + 3; l += blockDim.x) s_cum[l] = seg.cum[l];
       for (int l = threadIdx.x; l < T + 2; l += blockDim.x) { s_pd[l] = seg.pd[l]; s_rowoff[l] = seg.rowoff[l]; }
@@ -331,7 +332,7 @@ k_eval_groups(InstDev I, const V *__restrict__ Dv, PathDev P, SegCache seg, long
       auto table_edge = [&](int ca, int cb) {
          const int2 cia = cinfo[ca], cib = cinfo[cb];
          EdgeDesc e;
-         e.rb = (unsigned)cia.x * (unsigned)I.N + (unsigned)cia.y * (unsigned)cib.x;
+         e.rb = (long long)cia.x * I.N + (long long)cia.y * cib.x;
          e.ma = cia.y; e.mb = cib.y;
          e.dm = __ldg(I.dmin + (size_t)ca * I.C + cb);
          return e;
@@ -346,7 +347,7 @@ k_eval_groups(InstDev I, const V *__restrict__ Dv, PathDev P, SegCache seg, long
                if (k == sc.kseg && lb_ > la + 1) {          // run of path layers la .. lb_: one product
                   EdgeDesc e;
                   e.ma = s_cum[la + 1] - s_cum[la]; e.mb = s_cum[lb_ + 1] - s_cum[lb_];
-                  e.rb = s_rowoff[la] + (unsigned)(e.ma * (s_cum[lb_] - s_cum[la + 2]));
+                  e.rb = s_rowoff[la] + (long long)e.ma * (s_cum[lb_] - s_cum[la + 2]);
                   e.dm = (double)(s_pd[lb_] - s_pd[la]);
                   return e;
                }
@@ -482,7 +483,8 @@ __global__ void __launch_bounds__(256) k_sort_scatter(InstDev I, PathDev P, long
 }
 
 // ---- segment-product cache (see SegCache) ------------------------------------------------------------
-// meta (ints): cum[R], pd[R], rowoff[R] with R = I.rows + 3.  One block.
+// meta (ints): cum[R], pd[R], rowoff[R] as 64-bit (2R ints), lcl[R] (layer -> cluster), loff[R] (first sample of the
+// layer's cluster) with R = I.rows + 3 (rowoff starts 2R ints in: 8-byte aligned).  One block.
 __global__ void __launch_bounds__(256) k_seg_offsets(InstDev I, PathDev P, int *__restrict__ meta)
 {
    extern __shared__ int smem_i[];
@@ -492,18 +494,20 @@ __global__ void __launch_bounds__(256) k_seg_offsets(InstDev I, PathDev P, int *
       const int c = layer_cluster(I, P.tg, T, l);
       m_l[l] = I.m[c];
       dm_l[l] = l < S ? (int)I.dmin[(size_t)c * I.C + layer_cluster(I, P.tg, T, l + 1)] : 0;
+      meta[4 * R + l] = c;
+      meta[5 * R + l] = I.off[c];
    }
    __syncthreads();
    if (threadIdx.x == 0) {
       int *cum = meta, *pd = meta + R;
-      unsigned *rowoff = reinterpret_cast<unsigned *>(meta + 2 * R);
+      long long *rowoff = reinterpret_cast<long long *>(meta + 2 * R);
       int c = 0, d = 0;
       for (int l = 0; l <= S; ++l) { cum[l] = c; pd[l] = d; c += m_l[l]; d += dm_l[l]; }
       cum[S + 1] = c;
-      unsigned off = (unsigned)I.N * (unsigned)I.N;      // the products follow the table
+      long long off = (long long)I.N * I.N;              // the products follow the table
       for (int a = 0; a <= S; ++a) {
          rowoff[a] = off;
-         off += (unsigned)(m_l[a] * (c - cum[min(a + 2, S + 1)]));
+         off += (long long)m_l[a] * (c - cum[min(a + 2, S + 1)]);
       }
    }
 }
@@ -516,7 +520,7 @@ __global__ void __launch_bounds__(128) k_seg_build_g(InstDev I, PathDev P, int *
    const int a = blockIdx.x;
    if (a + 2 > S) return;
    const int *cum = meta;
-   const unsigned *rowoff = reinterpret_cast<const unsigned *>(meta + 2 * R);
+   const long long *rowoff = reinterpret_cast<const long long *>(meta + 2 * R);
    const int ca = layer_cluster(I, P.tg, T, a);
    const int ma = I.m[ca];
    const int *prev = Dv + ((long long)I.off[ca] * I.N + (long long)ma * I.off[layer_cluster(I, P.tg, T, a + 1)]);
@@ -525,7 +529,7 @@ __global__ void __launch_bounds__(128) k_seg_build_g(InstDev I, PathDev P, int *
       const int ck = layer_cluster(I, P.tg, T, b - 1), cb = layer_cluster(I, P.tg, T, b);
       const int mb = I.m[cb];
       const int *d = Dv + ((long long)I.off[ck] * I.N + (long long)mk * I.off[cb]);
-      int *out = Dv + (rowoff[a] + (unsigned)(ma * (cum[b] - cum[a + 2])));
+      int *out = Dv + (rowoff[a] + (long long)ma * (cum[b] - cum[a + 2]));
       for (int e = threadIdx.x; e < ma * mb; e += blockDim.x) {
          const int i = e / mb, j = e - i * mb;
          int acc = VNS_INT_INF;
@@ -538,11 +542,11 @@ __global__ void __launch_bounds__(128) k_seg_build_g(InstDev I, PathDev P, int *
    }
 }
 
-// The same recurrence with the running product in shared memory (double-buffered) and the NEXT table block
-// arriving by cp.async while the current product is computed: a step costs one barrier instead of a global
-// round trip (the chain of block a has S - a - 1 dependent steps; block 0's chain is the kernel's duration).
-// dynamic shared memory: seg_build_smem(S, mp) bytes
-__host__ __device__ inline size_t seg_build_smem(int rows, int mp) { return sizeof(int) * ((size_t)2 * (rows + 3) + (size_t)4 * mp * mp); }
+// The same recurrence with the running product in shared memory (double-buffered) and the table blocks of the next
+// three steps in flight (cp.async ring of four): a step costs one barrier instead of a global round trip (the chain
+// of block a has S - a - 1 dependent steps; block 0's chain is the kernel's duration).
+// dynamic shared memory: seg_build_smem(rows, mp) bytes
+__host__ __device__ inline size_t seg_build_smem(int rows, int mp) { return sizeof(int) * ((size_t)2 * (rows + 3) + (size_t)6 * mp * mp); }
 
 __global__ void __launch_bounds__(128) k_seg_build(InstDev I, PathDev P, int *Dv, const int *meta)
 {
@@ -551,41 +555,45 @@ __global__ void __launch_bounds__(128) k_seg_build(InstDev I, PathDev P, int *Dv
    const int a = blockIdx.x;
    if (a + 2 > S) return;
    int *l_m = smem_i, *l_off = smem_i + R;                  // per layer l >= a: cluster size, first sample
-   int *prod = smem_i + 2 * R, *dblk = prod + 2 * mp2;       // two buffers each
+   int *prod = smem_i + 2 * R, *dblk = prod + 2 * mp2;       // 2 product buffers, ring of 4 table blocks
    for (int l = a + threadIdx.x; l <= S; l += blockDim.x) {
       const int c = layer_cluster(I, P.tg, T, l);
       l_m[l] = I.m[c]; l_off[l] = I.off[c];
    }
    __syncthreads();
-   const int *cum = meta;
-   const unsigned *rowoff = reinterpret_cast<const unsigned *>(meta + 2 * R);
    const int ma = l_m[a];
-   auto blk = [&](int l) { return Dv + ((long long)l_off[l] * I.N + (long long)l_m[l] * l_off[l + 1]); };   // D(l, l+1)
-   auto fetch = [&](int *dst, const int *src, int n) {
-      for (int e = threadIdx.x; e < n; e += blockDim.x)
-         asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(dst + e)), "l"(src + e));
+   long long ooff = reinterpret_cast<const long long *>(meta + 2 * R)[a];   // M(a,a+2) starts the row; M(a,b+1) follows M(a,b)
+   // D(l, l+1) -> dst (nothing when l >= S); always one commit group so that the group count per step is fixed
+   auto fetch = [&](int *dst, int l) {
+      if (l < S) {
+         const int *src = Dv + ((long long)l_off[l] * I.N + (long long)l_m[l] * l_off[l + 1]);
+         const int n = l_m[l] * l_m[l + 1];
+         for (int e = threadIdx.x; e < n; e += blockDim.x)
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(dst + e)), "l"(src + e));
+      }
       asm volatile("cp.async.commit_group;");
    };
-   fetch(prod, blk(a), ma * l_m[a + 1]);
-   fetch(dblk, blk(a + 1), l_m[a + 1] * l_m[a + 2]);
-   asm volatile("cp.async.wait_group 0;");
-   __syncthreads();
+   fetch(prod, a);                                           // M(a,a+1) = D(a,a+1)
+   for (int b = a + 2; b <= a + 4; ++b) fetch(dblk + (b & 3) * mp2, b - 1);   // step b multiplies by D(b-1,b)
    int cur = 0;
    for (int b = a + 2; b <= S; ++b) {
+      asm volatile("cp.async.wait_group 2;");               // all but the blocks of steps b+1, b+2 have landed
+      __syncthreads();
+      fetch(dblk + ((b + 3) & 3) * mp2, b + 2);              // that buffer was read by step b-1
       const int mk = l_m[b - 1], mb = l_m[b];
-      if (b < S) fetch(dblk + (cur ^ 1) * mp2, blk(b), mb * l_m[b + 1]);
-      const int *pv = prod + cur * mp2, *d = dblk + cur * mp2;
+      const int *pv = prod + cur * mp2, *d = dblk + (b & 3) * mp2;
       int *nx = prod + (cur ^ 1) * mp2;
-      int *out = Dv + (rowoff[a] + (unsigned)(ma * (cum[b] - cum[a + 2])));
+      int *out = Dv + ooff;
       for (int e = threadIdx.x; e < ma * mb; e += blockDim.x) {
          const int i = e / mb, j = e - i * mb;
          int acc = VNS_INT_INF;
+#pragma unroll 4
          for (int k = 0; k < mk; ++k) acc = __viaddmin_s32(pv[i * mk + k], d[k * mb + j], acc);
          out[e] = acc;
          nx[e] = acc;
       }
-      asm volatile("cp.async.wait_group 0;");
-      __syncthreads();
+      ooff += ma * mb;
       cur ^= 1;
    }
+   asm volatile("cp.async.wait_group 0;");
 }

@@ -2,161 +2,262 @@
 //
 // The reference already shares work between candidates through the prefix / suffix vectors F[l], B[l]
 // (vns_sop_path.cpp:1426-1539).  With integer entries min-plus products are exactly associative, so the
-// same idea extends to the two ends of every candidate's chain: they depend only on (cluster, layer), not on
-// the candidate, and there are C x (T+2) of them against millions of candidates per batch.  Per path state
-// one pass (k_vec_build) stores, for every cluster c and layer l (lcl = layer -> cluster, S = T + 1):
-//   InsF(c,l) = F[l-1] (x) D(lcl[l-1],c) (x) D(c,lcl[l])              at layer l      c inserted before l
-//   InsB(c,l) = D(lcl[l-1],c) (x) D(c,lcl[l]) (x) B[l]                at layer l-1
-//   RepF(c,l) = F[l-1] (x) D(lcl[l-1],c) (x) D(c,lcl[l+1])            at layer l+1    layer l replaced by c
-//   RepB(c,l) = D(lcl[l-1],c) (x) D(c,lcl[l+1]) (x) B[l+1]            at layer l-1
-//   RemF(l)   = F[l-1] (x) D(lcl[l-1],lcl[l+1])                       at layer l+1    layer l removed
-//   RemB(l)   = D(lcl[l-1],lcl[l+1]) (x) B[l+1]                       at layer l-1
-// plus int copies FI / BI of F / B and the matching sums of cluster-pair minima for the lower bounds.  Then
-//   tryToAdd(c,idx)      = FI[idx] . InsB(c,idx+1)                    (vns_sop_path.cpp:245-304)
-//   tryToReplace(c,idx)  = FI[idx] . RepB(c,idx+1)                    (:456-513)
-//   tryToRemove(idx)     = FI[idx] . RemB(idx+1)                      (:515-535)
-//   tryToMove up   (i=a+1 -> before j=b+1)  = RemF(i) (x) M(i+1,j-1) . InsB(lcl[i],j)      (:932-1154)
-//   tryToMove down (j=a+1 -> before i=b+1)  = InsF(lcl[j],i) (x) M(i,j-1) . RemB(j)
-//   tryToExchange  (layers p=i+1, q=j)      = RepF(lcl[q],p) (x) M(p+1,q-1) . RepB(lcl[p],q)  (:635-797)
+// same idea extends to the two ends of every candidate's chain: they depend only on (cluster, layer) or on
+// (path layer, layer), not on the candidate.  Per path state two passes store (lcl = layer -> cluster, S = T + 1):
+//   k_vec_uw, one warp per (layer l, cluster c) - one block step each:
+//     U(c,l) = F[l] (x) D(lcl[l],c)          over c's samples: "in c right after layer l"      l = 0 .. S-1
+//     W(c,l) = D(c,lcl[l]) (x) B[l]          over c's samples: "leave c into layer l"          l = 1 .. S
+//     FI[l]  = F[l] as int
+//   k_vec_pairs, one warp per (path layer x, layer l), cx = lcl[x] - one block step each from U / W:
+//     InsF(x,l) = U(cx,l-1) (x) D(cx,lcl[l])        at layer l      cx inserted before l
+//     InsB(x,l) = D(lcl[l-1],cx) (x) W(cx,l)        at layer l-1
+//     RepF(x,l) = U(cx,l-1) (x) D(cx,lcl[l+1])      at layer l+1    layer l replaced by cx
+//     RepB(x,l) = D(lcl[l-1],cx) (x) W(cx,l+1)      at layer l-1
+// plus the matching sums of cluster-pair minima for the lower bounds.  Then
+//   tryToAdd(c,idx)      = U(c,idx) . W(c,idx+1)                      (vns_sop_path.cpp:245-304)   no block at all
+//   tryToReplace(c,idx)  = U(c,idx) . W(c,idx+2)                      (:456-513)
+//   tryToRemove(idx)     = FI[idx] . W(lcl[idx],idx+2)                (:515-535)
+//   tryToMove up   (i=a+1 -> before j=b+1)  = U(lcl[i+1],i-1) (x) M(i+1,j-1) . InsB(i,j)      (:932-1154)
+//   tryToMove down (j=a+1 -> before i=b+1)  = InsF(j,i) (x) M(i,j-1) . W(lcl[j-1],j+1)
+//   tryToExchange  (layers p=i+1, q=j)      = RepF(q,p) (x) M(p+1,q-1) . RepB(p,q)            (:635-797)
 // where "." is min_s x[s] + y[s], M(a,b) is the segment product of eval.cuh (a table block when b == a+1,
 // absent when b == a).  One candidate = at most ONE block step.  Lengths, lower bounds and flags are
 // bit-identical to the block-by-block evaluation (tests/test_gpu_parity.py runs all three forms).
+// Build cost per path state: 2 C (T+2) + 4 T (T+2) block steps (the first version did 8 C (T+2)); the U pass
+// streams whole row bands of the table (consecutive warps read consecutive blocks).
 #pragma once
 #include "eval.cuh"
 
 struct VecCache {
-   const int *vec;   // ((fam * C + c) * LS + l) * mp, fam 0..3 = InsF, InsB, RepF, RepB; then rows RemF, RemB, FI, BI
+   const int *vec;   // U, W: ((k * LS + l) * C + c) * mp, k = 0 / 1; FI: row l; then InsF, InsB, RepF, RepB: ((fam * LS + x) * LS + l) * mp
    const int *lbs;   // insLB[C][LS], repLB[C][LS], remLB[LS]
    int LS;           // layer stride (>= S + 1)
 };
 
-__device__ __forceinline__ unsigned vec_off(const VecCache &vc, int C, int mp, int fam, int c, int l)
-{
-   return (unsigned)(((fam * C + c) * vc.LS + l) * mp);
-}
-__device__ __forceinline__ unsigned vec_row(const VecCache &vc, int C, int mp, int k, int l)   // k: 0 RemF, 1 RemB, 2 FI, 3 BI
-{
-   return (unsigned)(((4 * C + k) * vc.LS + l) * mp);
-}
-__host__ __device__ inline size_t vec_ints(int C, int LS, int mp) { return (size_t)(4 * C + 4) * LS * mp; }
+__host__ __device__ inline size_t vec_uw_ints(int C, int LS, int mp) { return (size_t)2 * LS * C * mp + (size_t)LS * mp; }
+__host__ __device__ inline size_t vec_ints(int C, int LS, int mp) { return vec_uw_ints(C, LS, mp) + (size_t)4 * LS * LS * mp; }
 __host__ __device__ inline size_t vec_lb_ints(int C, int LS) { return (size_t)(2 * C + 1) * LS; }
 
-// lane = output index; v (lane-held, INF beyond the source size) times block (ca -> cb)
-__device__ __forceinline__ int vec_fwd(const InstDev &I, const int *__restrict__ Dv, int v, int ca, int cb, int lane)
+__device__ __forceinline__ unsigned vec_uw(const VecCache &vc, int C, int mp, int k, int c, int l)   // k: 0 U, 1 W
 {
-   const int ma = I.m[ca], mb = I.m[cb];
-   const int *blk = Dv + ((long long)I.off[ca] * I.N + (long long)ma * I.off[cb]);
+   return (unsigned)(((k * vc.LS + l) * C + c) * mp);
+}
+__device__ __forceinline__ unsigned vec_fi(const VecCache &vc, int C, int mp, int l) { return (unsigned)((2 * vc.LS * C + l) * mp); }
+__device__ __forceinline__ unsigned vec_pair(const VecCache &vc, int C, int mp, int fam, int x, int l)   // fam 0..3 = InsF, InsB, RepF, RepB
+{
+   return (unsigned)(2 * vc.LS * C + vc.LS) * (unsigned)mp + (unsigned)(((fam * vc.LS + x) * vc.LS + l) * mp);
+}
+
+// A warp stages a whole table block in its slice of shared memory with cp.async (coalesced 4-byte copies, fire and
+// forget): every block a warp needs is in flight at once and costs ONE memory round trip; the min-plus loops then run
+// out of shared memory.
+__device__ __forceinline__ void warp_stage(int *dst, const int *__restrict__ src, int n, int lane)
+{
+   for (int e = lane; e < n; e += 32)
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(dst + e)), "l"(src + e));
+}
+__device__ __forceinline__ void warp_stage_wait()
+{
+   asm volatile("cp.async.commit_group;");
+   asm volatile("cp.async.wait_group 0;");
+   __syncwarp();
+}
+// lane = output index; v (lane-held, INF beyond the source size) times the staged ma x mb block
+__device__ __forceinline__ int vec_fwd(const int *blk, int ma, int mb, int v, int lane)
+{
    int acc = VNS_INT_INF;
    const int j = min(lane, mb - 1);
-   for (int s = 0; s < ma; ++s) acc = __viaddmin_s32(__shfl_sync(0xffffffffu, v, s), __ldg(blk + s * mb + j), acc);
+#pragma unroll 4
+   for (int s = 0; s < ma; ++s) acc = __viaddmin_s32(__shfl_sync(0xffffffffu, v, s), blk[s * mb + j], acc);
    return lane < mb ? acc : VNS_INT_INF;
 }
-// lane = source index; block (ca -> cb) times v (lane-held over cb's samples)
-__device__ __forceinline__ int vec_bwd(const InstDev &I, const int *__restrict__ Dv, int v, int ca, int cb, int lane)
+// lane = source index; the staged ma x mb block times v (lane-held over the mb destination samples)
+__device__ __forceinline__ int vec_bwd(const int *blk, int ma, int mb, int v, int lane)
 {
-   const int ma = I.m[ca], mb = I.m[cb];
-   const int *blk = Dv + ((long long)I.off[ca] * I.N + (long long)ma * I.off[cb]);
    int acc = VNS_INT_INF;
    const int s = min(lane, ma - 1);
-   for (int j = 0; j < mb; ++j) acc = __viaddmin_s32(__shfl_sync(0xffffffffu, v, j), __ldg(blk + s * mb + j), acc);
+#pragma unroll 4
+   for (int j = 0; j < mb; ++j) acc = __viaddmin_s32(__shfl_sync(0xffffffffu, v, j), blk[s * mb + j], acc);
    return lane < ma ? acc : VNS_INT_INF;
 }
 
-// one warp per (c, l); row c == C holds RemF / RemB / FI / BI.  Needs mp <= 32.
-__global__ void __launch_bounds__(256) k_vec_build(InstDev I, PathDev P, const int *__restrict__ Dv, int *__restrict__ vec,
-                                                   int *__restrict__ lbs, int LS)
+// per-layer description of the path written by k_seg_offsets (eval.cuh): cluster, first sample, size
+struct LayerMeta {
+   const int *cum, *lcl, *loff;
+   __device__ __forceinline__ int cl(int l) const { return __ldg(lcl + l); }
+   __device__ __forceinline__ int off(int l) const { return __ldg(loff + l); }
+   __device__ __forceinline__ int m(int l) const { return __ldg(cum + l + 1) - __ldg(cum + l); }
+};
+__device__ __forceinline__ LayerMeta layer_meta(const InstDev &I, const int *meta)
 {
+   const int R = I.rows + 3;
+   return LayerMeta{meta, meta + 4 * R, meta + 5 * R};
+}
+
+// one warp per (l, c), grid.y = l: consecutive warps read consecutive blocks of row band lcl[l] (U) and write consecutive
+// vectors.  Needs mp <= 32.  Dynamic shared memory: 2 mp^2 ints per warp.
+__global__ void __launch_bounds__(256) k_vec_uw(InstDev I, PathDev P, const int *__restrict__ Dv, const int *__restrict__ meta,
+                                                int *__restrict__ vec, int *__restrict__ lbs, int LS)
+{
+   extern __shared__ int smem_i[];
    const int T = P.hdr[HDR_T], S = T + 1, C = I.C, mp = I.mp;
    const int lane = threadIdx.x & 31;
-   const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-   if (w >= (long long)(C + 1) * (S + 1)) return;
-   const int c = (int)(w / (S + 1)), l = (int)(w % (S + 1));
+   const int l = blockIdx.y, c = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);      // grid.y = layer: no divisions
+   if (l > S || c >= C) return;
+   const LayerMeta lm = layer_meta(I, meta);
    VecCache vc{vec, lbs, LS};
-   auto cl = [&](int x) { return layer_cluster(I, P.tg, T, x); };
-   auto Fv = [&](int x) { return lane < I.m[cl(x)] ? (int)P.F[(size_t)x * mp + lane] : VNS_INT_INF; };
-   auto Bv = [&](int x) { return lane < I.m[cl(x)] ? (int)P.B[(size_t)x * mp + lane] : VNS_INT_INF; };
-   auto dm = [&](int a, int b) { return (int)I.dmin[(size_t)a * C + b]; };
-   auto put = [&](unsigned off, int v) { if (lane < mp) vec[off + lane] = v; };
-   if (c == C) {
-      put(vec_row(vc, C, mp, 2, l), Fv(l));
-      put(vec_row(vc, C, mp, 3, l), Bv(l));
-      if (l >= 1 && l <= S - 1) {
-         const int a = cl(l - 1), b = cl(l + 1);
-         put(vec_row(vc, C, mp, 0, l), vec_fwd(I, Dv, Fv(l - 1), a, b, lane));
-         put(vec_row(vc, C, mp, 1, l), vec_bwd(I, Dv, Bv(l + 1), a, b, lane));
-         if (lane == 0) lbs[(size_t)2 * C * LS + l] = dm(a, b);
+   int *bU = smem_i + (threadIdx.x >> 5) * 2 * mp * mp, *bW = bU + mp * mp;
+   const int cl = lm.cl(l), ml = lm.m(l), ol = lm.off(l);
+   const int mc = __ldg(I.m + c), oc = __ldg(I.off + c);
+   const bool doU = l <= S - 1, doW = l >= 1, sym = I.symmetric != 0;
+   // symmetric tables: D(c, cl) is the transpose of D(cl, c) - the column strip of W comes out of the same row band
+   if (doU || sym) warp_stage(bU, Dv + ((long long)ol * I.N + (long long)ml * oc), ml * mc, lane);     // D(cl, c)
+   if (doW && !sym) warp_stage(bW, Dv + ((long long)oc * I.N + (long long)mc * ol), mc * ml, lane);    // D(c, cl)
+   const int f = (doU && lane < ml) ? (int)P.F[(size_t)l * mp + lane] : VNS_INT_INF;
+   const int bv = (doW && lane < ml) ? (int)P.B[(size_t)l * mp + lane] : VNS_INT_INF;
+   int lb_ins = 0, lb_rep = 0, lb_rem = 0;
+   if (doW && lane == 0) {   // lower-bound sums (integers: order-free)
+      const int a = lm.cl(l - 1), nx = l <= S - 1 ? lm.cl(l + 1) : cl;
+      const int din = (int)I.dmin[(size_t)a * C + c];
+      lb_ins = din + (int)I.dmin[(size_t)c * C + cl];
+      lb_rep = din + (int)I.dmin[(size_t)c * C + nx];
+      lb_rem = (int)I.dmin[(size_t)a * C + nx];
+   }
+   warp_stage_wait();
+   if (doU) {   // U(c,l) = F[l] (x) D(cl, c)
+      const int u = vec_fwd(bU, ml, mc, f, lane);
+      if (lane < mp) vec[vec_uw(vc, C, mp, 0, c, l) + lane] = u;
+      if (c == 0 && lane < mp) vec[vec_fi(vc, C, mp, l) + lane] = f;
+   }
+   if (doW) {   // W(c,l) = D(c, cl) (x) B[l]
+      const int wv = sym ? vec_fwd(bU, ml, mc, bv, lane) : vec_bwd(bW, mc, ml, bv, lane);
+      if (lane < mp) vec[vec_uw(vc, C, mp, 1, c, l) + lane] = wv;
+      if (lane == 0) {
+         lbs[(size_t)c * LS + l] = lb_ins;                                   // insert c before l
+         if (l <= S - 1) lbs[(size_t)(C + c) * LS + l] = lb_rep;             // c replaces l
+         if (c == 0 && l <= S - 1) lbs[(size_t)2 * C * LS + l] = lb_rem;     // l removed
+      }
+   }
+}
+
+// one warp per (x, l), x = 1 .. T (path layer, cluster cx; grid.y), l = 1 .. S.  Two table blocks, four products.
+__global__ void __launch_bounds__(256) k_vec_pairs(InstDev I, PathDev P, const int *__restrict__ Dv, const int *__restrict__ meta,
+                                                   int *__restrict__ vec, int LS)
+{
+   extern __shared__ int smem_i[];
+   const int T = P.hdr[HDR_T], S = T + 1, C = I.C, mp = I.mp;
+   const int lane = threadIdx.x & 31;
+   const int x = blockIdx.y + 1, wl = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);   // grid.y = path layer x
+   if (x > T) return;
+   const LayerMeta lm = layer_meta(I, meta);
+   VecCache vc{vec, nullptr, LS};
+   int *b1 = smem_i + (threadIdx.x >> 5) * 2 * mp * mp, *b2 = b1 + mp * mp;
+   if (I.symmetric) {
+      // one block D(cx, lcl[l]) per warp, l = 0 .. S: it is also D(lcl[l], cx) transposed, so all four products are
+      // forward steps through it:  InsF(x,l), RepF(x,l-1) from U;  InsB(x,l+1), RepB(x,l+1) from W
+      const int l = wl;
+      if (l > S) return;
+      const int cx = lm.cl(x), mx = lm.m(x), ox = lm.off(x), ml = lm.m(l);
+      warp_stage(b1, Dv + ((long long)ox * I.N + (long long)mx * lm.off(l)), mx * ml, lane);
+      auto ld = [&](int k, int ll, bool on) { return (on && lane < mx) ? __ldg(vec + vec_uw(vc, C, mp, k, cx, min(max(ll, 0), S)) + lane) : VNS_INT_INF; };
+      const int u1 = ld(0, l - 1, l >= 1), u2 = ld(0, l - 2, l >= 2), w1 = ld(1, l + 1, l <= S - 1), w2 = ld(1, l + 2, l <= S - 2);
+      warp_stage_wait();
+      int a1 = VNS_INT_INF, a2 = VNS_INT_INF, a3 = VNS_INT_INF, a4 = VNS_INT_INF;
+      const int j = min(lane, ml - 1);
+#pragma unroll 2
+      for (int s = 0; s < mx; ++s) {
+         const int d = b1[s * ml + j];
+         a1 = __viaddmin_s32(__shfl_sync(0xffffffffu, u1, s), d, a1);
+         a2 = __viaddmin_s32(__shfl_sync(0xffffffffu, u2, s), d, a2);
+         a3 = __viaddmin_s32(__shfl_sync(0xffffffffu, w1, s), d, a3);
+         a4 = __viaddmin_s32(__shfl_sync(0xffffffffu, w2, s), d, a4);
+      }
+      if (lane < mp) {
+         const bool in = lane < ml;
+         if (l >= 1) vec[vec_pair(vc, C, mp, 0, x, l) + lane] = in ? a1 : VNS_INT_INF;
+         if (l >= 2) vec[vec_pair(vc, C, mp, 2, x, l - 1) + lane] = in ? a2 : VNS_INT_INF;
+         if (l <= S - 1) vec[vec_pair(vc, C, mp, 1, x, l + 1) + lane] = in ? a3 : VNS_INT_INF;
+         if (l <= S - 2) vec[vec_pair(vc, C, mp, 3, x, l + 1) + lane] = in ? a4 : VNS_INT_INF;
       }
       return;
    }
-   if (l < 1) return;
-   const int a = cl(l - 1);
-   {  // insert c between layers l-1 and l
-      const int b = cl(l);
-      put(vec_off(vc, C, mp, 0, c, l), vec_fwd(I, Dv, vec_fwd(I, Dv, Fv(l - 1), a, c, lane), c, b, lane));
-      put(vec_off(vc, C, mp, 1, c, l), vec_bwd(I, Dv, vec_bwd(I, Dv, Bv(l), c, b, lane), a, c, lane));
-      if (lane == 0) lbs[(size_t)c * LS + l] = dm(a, c) + dm(c, b);
-   }
-   if (l <= S - 1) {   // c replaces layer l
-      const int b = cl(l + 1);
-      put(vec_off(vc, C, mp, 2, c, l), vec_fwd(I, Dv, vec_fwd(I, Dv, Fv(l - 1), a, c, lane), c, b, lane));
-      put(vec_off(vc, C, mp, 3, c, l), vec_bwd(I, Dv, vec_bwd(I, Dv, Bv(l + 1), c, b, lane), a, c, lane));
-      if (lane == 0) lbs[(size_t)(C + c) * LS + l] = dm(a, c) + dm(c, b);
-   }
+   const int l = wl + 1;
+   if (l > S) return;
+   const int cx = lm.cl(x), mx = lm.m(x), ox = lm.off(x);
+   const int ml = lm.m(l), ma = lm.m(l - 1);
+   warp_stage(b1, Dv + ((long long)ox * I.N + (long long)mx * lm.off(l)), mx * ml, lane);          // D(cx, lcl[l])
+   warp_stage(b2, Dv + ((long long)lm.off(l - 1) * I.N + (long long)ma * ox), ma * mx, lane);      // D(lcl[l-1], cx)
+   auto ld = [&](unsigned off, bool on) { return (on && lane < mx) ? __ldg(vec + off + lane) : VNS_INT_INF; };
+   auto put = [&](unsigned off, int v) { if (lane < mp) vec[off + lane] = v; };
+   const int u1 = ld(vec_uw(vc, C, mp, 0, cx, l - 1), true), u2 = ld(vec_uw(vc, C, mp, 0, cx, max(l - 2, 0)), l >= 2);
+   const int w1 = ld(vec_uw(vc, C, mp, 1, cx, l), true), w2 = ld(vec_uw(vc, C, mp, 1, cx, min(l + 1, S)), l <= S - 1);
+   warp_stage_wait();
+   put(vec_pair(vc, C, mp, 0, x, l), vec_fwd(b1, mx, ml, u1, lane));                       // InsF(x,l)   from U(cx,l-1)
+   if (l >= 2) put(vec_pair(vc, C, mp, 2, x, l - 1), vec_fwd(b1, mx, ml, u2, lane));       // RepF(x,l-1) from U(cx,l-2)
+   put(vec_pair(vc, C, mp, 1, x, l), vec_bwd(b2, ma, mx, w1, lane));                       // InsB(x,l)   from W(cx,l)
+   if (l <= S - 1) put(vec_pair(vc, C, mp, 3, x, l), vec_bwd(b2, ma, mx, w2, lane));       // RepB(x,l)   from W(cx,l+1)
 }
 
 // decoded candidate in endpoint-vector form
 struct VecCode {
    int ok;            // 0: indices out of range
    unsigned offA, offB;
-   int la, lb;        // layers of A and B (block la -> lb when lb > la)
+   int mA, mB;        // sizes of A and B
+   int la, lb;        // block la -> lb between them when lb > la (path layers)
    int lbsum;         // dist_between of the lower bound
    int s0, sK;        // layers whose minF / minB enter the lower bound
    int nolb;
 };
 
-template <typename PD>
-__device__ __forceinline__ VecCode decode_cand_vec(const VecCache &vc, int T, int C, int mp, const int *lcl, PD pd, int op, int a, int b)
+// lcl: layer -> cluster, lm(l): size of layer l, cm(c): size of cluster c, pd(l): prefix sums of dmin along the path
+template <typename LM, typename CM, typename PD>
+__device__ __forceinline__ VecCode decode_cand_vec(const VecCache &vc, int T, int C, int mp, const int *lcl, LM lm, CM cm, PD pd, int op,
+                                                   int a, int b)
 {
    VecCode v;
-   v.ok = 0; v.offA = v.offB = 0; v.la = v.lb = 0; v.lbsum = 0; v.s0 = v.sK = 0; v.nolb = 0;
+   v.ok = 0; v.offA = v.offB = 0; v.mA = v.mB = 0; v.la = v.lb = 0; v.lbsum = 0; v.s0 = v.sK = 0; v.nolb = 0;
    const int *insLB = vc.lbs, *repLB = vc.lbs + (size_t)C * vc.LS, *remLB = vc.lbs + (size_t)2 * C * vc.LS;
    if (op == VNSGPU_OP_ADD) {
       if (b < 0 || b > T || a < 0 || a >= C) return v;
-      v.ok = 1; v.la = v.lb = b; v.offA = vec_row(vc, C, mp, 2, b); v.offB = vec_off(vc, C, mp, 1, a, b + 1);
+      v.ok = 1; v.mA = v.mB = cm(a); v.offA = vec_uw(vc, C, mp, 0, a, b); v.offB = vec_uw(vc, C, mp, 1, a, b + 1);
       v.lbsum = __ldg(insLB + (size_t)a * vc.LS + b + 1); v.s0 = b; v.sK = b + 1;
    } else if (op == VNSGPU_OP_REPLACE) {
       if (b < 0 || b >= T || a < 0 || a >= C) return v;
-      v.ok = 1; v.la = v.lb = b; v.offA = vec_row(vc, C, mp, 2, b); v.offB = vec_off(vc, C, mp, 3, a, b + 1);
+      v.ok = 1; v.mA = v.mB = cm(a); v.offA = vec_uw(vc, C, mp, 0, a, b); v.offB = vec_uw(vc, C, mp, 1, a, b + 2);
       v.lbsum = __ldg(repLB + (size_t)a * vc.LS + b + 1); v.s0 = b; v.sK = b + 2;
    } else if (op == VNSGPU_OP_REMOVE) {
       if (a < 0 || a >= T) return v;
-      v.ok = 1; v.la = v.lb = a; v.offA = vec_row(vc, C, mp, 2, a); v.offB = vec_row(vc, C, mp, 1, a + 1);
+      v.ok = 1; v.mA = v.mB = lm(a); v.offA = vec_fi(vc, C, mp, a); v.offB = vec_uw(vc, C, mp, 1, lcl[a], a + 2);
       v.s0 = a; v.sK = a + 2; v.nolb = 1;
    } else if (op == VNSGPU_OP_MOVE) {
       if (a >= T || a < 0 || b > T || b < 0 || abs(b - a) < 2) return v;
       const int i = min(a, b) + 1, j = max(a, b) + 1;
       v.ok = 1;
       if (b > a) {   // layer i moves up, in front of layer j
-         v.la = i + 1; v.lb = j - 1; v.offA = vec_row(vc, C, mp, 0, i); v.offB = vec_off(vc, C, mp, 1, lcl[i], j);
+         v.la = i + 1; v.lb = j - 1; v.offA = vec_uw(vc, C, mp, 0, lcl[i + 1], i - 1); v.offB = vec_pair(vc, C, mp, 1, i, j);
          v.lbsum = __ldg(remLB + i) + (pd(j - 1) - pd(i + 1)) + __ldg(insLB + (size_t)lcl[i] * vc.LS + j);
          v.s0 = i - 1; v.sK = j;
       } else {       // layer j moves down, in front of layer i
-         v.la = i; v.lb = j - 1; v.offA = vec_off(vc, C, mp, 0, lcl[j], i); v.offB = vec_row(vc, C, mp, 1, j);
+         v.la = i; v.lb = j - 1; v.offA = vec_pair(vc, C, mp, 0, j, i); v.offB = vec_uw(vc, C, mp, 1, lcl[j - 1], j + 1);
          v.lbsum = __ldg(insLB + (size_t)lcl[j] * vc.LS + i) + (pd(j - 1) - pd(i)) + __ldg(remLB + j);
          v.s0 = i - 1; v.sK = j + 1;
       }
+      v.mA = lm(v.la); v.mB = lm(v.lb);
    } else if (op == VNSGPU_OP_EXCHANGE) {
       if (a >= T || a < 0 || b >= T || b < 0 || abs(a - b) < 2) return v;
       const int p = min(a, b) + 1, q = max(a, b) + 1;   // the two exchanged layers
       v.ok = 1; v.la = p + 1; v.lb = q - 1;
-      v.offA = vec_off(vc, C, mp, 2, lcl[q], p); v.offB = vec_off(vc, C, mp, 3, lcl[p], q);
+      v.offA = vec_pair(vc, C, mp, 2, q, p); v.offB = vec_pair(vc, C, mp, 3, p, q);
       v.lbsum = __ldg(repLB + (size_t)lcl[q] * vc.LS + p) + (pd(q - 1) - pd(p + 1)) + __ldg(repLB + (size_t)lcl[p] * vc.LS + q);
       v.s0 = p - 1; v.sK = q + 1;
+      v.mA = lm(v.la); v.mB = lm(v.lb);
    }
    return v;
 }
 
-template <int G, int NR>
+// LAT: the table does not fit the caches (synthetic scaled instances) - every block step issues all its G row loads
+// before the first min (one memory round trip per step instead of G / 2); rows beyond the block re-read its last row.
+template <int G, int NR, bool LAT>
 __global__ void __launch_bounds__(VNS_EVAL_THREADS)
 k_eval_vec(InstDev I, const int *__restrict__ Dv, PathDev P, SegCache seg, VecCache vc, long long n, long long idx0,
            const vnsgpu_cand *__restrict__ cands, const unsigned *__restrict__ perm, double budget, int skipflag,
@@ -170,8 +271,8 @@ k_eval_vec(InstDev I, const int *__restrict__ Dv, PathDev P, SegCache seg, VecCa
    int2 *cinfo = reinterpret_cast<int2 *>(smem_i + ((T + 2 + 1) & ~1));
    for (int l = threadIdx.x; l < T + 2; l += blockDim.x) lcl[l] = layer_cluster(I, P.tg, T, l);
    for (int c = threadIdx.x; c < C; c += blockDim.x) cinfo[c] = make_int2(I.off[c], I.m[c]);
-   int *s_cum = reinterpret_cast<int *>(cinfo + C), *s_pd = s_cum + (T + 3);
-   unsigned *s_rowoff = reinterpret_cast<unsigned *>(s_pd + (T + 2));
+   long long *s_rowoff = reinterpret_cast<long long *>(cinfo + C);
+   int *s_cum = reinterpret_cast<int *>(s_rowoff + (T + 2)), *s_pd = s_cum + (T + 3);
    for (int l = threadIdx.x; l < T + 3; l += blockDim.x) s_cum[l] = seg.cum[l];
    for (int l = threadIdx.x; l < T + 2; l += blockDim.x) { s_pd[l] = seg.pd[l]; s_rowoff[l] = seg.rowoff[l]; }
    __syncthreads();
@@ -196,17 +297,19 @@ k_eval_vec(InstDev I, const int *__restrict__ Dv, PathDev P, SegCache seg, VecCa
       if (perm && slot < n) kidx = __ldg(perm + slot);
       int4 cd = make_int4(-1, 0, 0, -1);
       if (slot < n) cd = __ldg(reinterpret_cast<const int4 *>(cands) + kidx);
-      const VecCode vcd = decode_cand_vec(vc, T, C, mp, lcl, [&](int l) { return s_pd[l]; }, cd.x, cd.y, cd.z);
-      unsigned p_rb = 0, p_pack;
+      const VecCode vcd = decode_cand_vec(vc, T, C, mp, lcl, [&](int l) { return s_cum[l + 1] - s_cum[l]; },
+                                          [&](int c) { return cinfo[c].y; }, [&](int l) { return s_pd[l]; }, cd.x, cd.y, cd.z);
+      long long p_rb = 0;
+      unsigned p_pack;
       {
-         const int mA = vcd.ok ? s_cum[vcd.la + 1] - s_cum[vcd.la] : 0, mB = vcd.ok ? s_cum[vcd.lb + 1] - s_cum[vcd.lb] : 0;
+         const int mA = vcd.mA, mB = vcd.mB;
          const bool blk = vcd.ok && vcd.lb > vcd.la;
          if (blk) {   // block la -> lb: a table block when adjacent, else the segment product M(la, lb)
             if (vcd.lb == vcd.la + 1) {
                const int2 cia = cinfo[lcl[vcd.la]], cib = cinfo[lcl[vcd.lb]];
-               p_rb = (unsigned)cia.x * (unsigned)I.N + (unsigned)cia.y * (unsigned)cib.x;
+               p_rb = (long long)cia.x * I.N + (long long)cia.y * cib.x;
             } else
-               p_rb = s_rowoff[vcd.la] + (unsigned)(mA * (s_cum[vcd.lb] - s_cum[vcd.la + 2]));
+               p_rb = s_rowoff[vcd.la] + (long long)mA * (s_cum[vcd.lb] - s_cum[vcd.la + 2]);
          }
          int tmax = blk ? mA : 1, nvmax = blk ? mB : 1, anyblk = blk;
 #pragma unroll
@@ -224,7 +327,8 @@ k_eval_vec(InstDev I, const int *__restrict__ Dv, PathDev P, SegCache seg, VecCa
       for (int it = 0; it < G; ++it) {
          const int c = it * NG + g;
          const unsigned offA = __shfl_sync(FULL, vcd.offA, c), offB = __shfl_sync(FULL, vcd.offB, c);
-         const unsigned rb = __shfl_sync(FULL, p_rb, c), pk = __shfl_sync(FULL, p_pack, c);
+         const int *blkp = Dv + __shfl_sync(FULL, p_rb, c);
+         const unsigned pk = __shfl_sync(FULL, p_pack, c);
          const int mA = pk & 63, mB = (pk >> 6) & 63, tmaxAll = (pk >> 12) & 63, nvmax = (pk >> 18) & 63;
          const bool blk = (pk >> 24) & 1;
          int vA[NR], vB[NR];
@@ -241,7 +345,7 @@ k_eval_vec(InstDev I, const int *__restrict__ Dv, PathDev P, SegCache seg, VecCa
             for (int rd = 0; rd < NR; ++rd) {
                acc[rd] = INF;
                if (rd == 0 || nvmax > rd * G) {                 // warp-uniform
-                  const unsigned cbase = rb + (unsigned)min(gl + rd * G, nvalid - 1);
+                  const unsigned cbase = (unsigned)min(gl + rd * G, nvalid - 1);
 #pragma unroll
                   for (int rs = 0; rs < NR; ++rs) {
                      if (rs == 0 || tmaxAll > rs * G) {         // warp-uniform
@@ -249,10 +353,18 @@ k_eval_vec(InstDev I, const int *__restrict__ Dv, PathDev P, SegCache seg, VecCa
                         const unsigned sb = cbase + (unsigned)(min(rs * G, trip - 1) * nvalid);
                         const int tm = min(tmaxAll - rs * G, G);
                         const int opnd = vA[rs];
+                        if (LAT) {
+                           int dd[G];
+#pragma unroll
+                           for (int t = 0; t < G; ++t) dd[t] = __ldg(blkp + (sb + (unsigned)(min(t, tlim) * nvalid)));
+#pragma unroll
+                           for (int t = 0; t < G; ++t) acc[rd] = __viaddmin_s32(__shfl_sync(FULL, opnd, min(t, tlim), G), dd[t], acc[rd]);
+                        } else {
 #pragma unroll 2
-                        for (int t = 0; t < tm; ++t) {
-                           const int tt = min(t, tlim);
-                           acc[rd] = __viaddmin_s32(__shfl_sync(FULL, opnd, tt, G), __ldg(Dv + (sb + (unsigned)(tt * nvalid))), acc[rd]);
+                           for (int t = 0; t < tm; ++t) {
+                              const int tt = min(t, tlim);
+                              acc[rd] = __viaddmin_s32(__shfl_sync(FULL, opnd, tt, G), __ldg(blkp + (sb + (unsigned)(tt * nvalid))), acc[rd]);
+                           }
                         }
                      }
                   }

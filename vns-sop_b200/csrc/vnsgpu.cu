@@ -258,7 +258,7 @@ vnsgpu_status vnsgpu_set_clusters(vnsgpu_ctx *ctx, int C, const int *m, const do
    CK(cudaMemcpyAsync(ctx->d_reward, reward, sizeof(double) * C, cudaMemcpyHostToDevice, ctx->stream));
    CK(cudaStreamSynchronize(ctx->stream));
    InstDev &I = ctx->I;
-   I.C = C; I.N = N; I.mp = mp; I.start = start; I.goal = goal; I.rows = 2 * C + 2; I.exact_int = 0;
+   I.C = C; I.N = N; I.mp = mp; I.start = start; I.goal = goal; I.rows = 2 * C + 2; I.exact_int = 0; I.symmetric = 0;
    I.m = ctx->d_m; I.off = ctx->d_off; I.clof = ctx->d_clof; I.reward = ctx->d_reward;
    I.D = ctx->d_D; I.dmin = ctx->d_dmin;
    CK(cudaMalloc(&ctx->d_seg, sizeof(int) * 2 * I.rows));
@@ -294,7 +294,7 @@ static vnsgpu_status build_table(vnsgpu_ctx *ctx, TableJob J, bool maybe_int)
    const long long segcap = ((long long)I.N + I.mp + 1) * ((long long)I.N + I.mp + 1) / 2;
    if (ctx->d_D32) { CK(cudaFree(ctx->d_D32)); ctx->d_D32 = nullptr; }
    if (maybe_int) {   // optimistic: the copy is dropped again if the classification says no
-      ctx->seg_ok = nn + segcap < (1ll << 32);
+      ctx->seg_ok = true;                                  // block offsets are 64-bit
       if (cudaMalloc(&ctx->d_D32, sizeof(int) * (size_t)(nn + (ctx->seg_ok ? segcap : 0)) + 64) != cudaSuccess) {
          cudaGetLastError();
          ctx->d_D32 = nullptr;
@@ -325,6 +325,7 @@ static vnsgpu_status build_table(vnsgpu_ctx *ctx, TableJob J, bool maybe_int)
       CK(cudaFree(ctx->d_D32));
       ctx->d_D32 = nullptr;
    }
+   ctx->I.symmetric = KIND == 0 ? 1 : 0;   // sqrt(dx*dx+dy*dy): the same bits in both directions
    ctx->have_table = true;
    return VNSGPU_OK;
 }

@@ -64,11 +64,39 @@ def generate(n_points: int = 20000, cluster_size: int = 10, seed: int = DEFAULT_
     return sf
 
 
+def generate_dop(n_centres: int = 2000, headings: int = 32, seed: int = DEFAULT_SEED, box: float = 1e4,
+                 radius_fraction: float = 0.005, budget_fraction: float = 0.4, name: str | None = None) -> ins.Problem:
+    """DOP flavour of the scaled instance ("2000 centres x 32 headings", rho = 0.5 % of the bounding
+    box): every cluster is one location with `headings` heading samples, cluster 0 = the depot (start and goal, so
+    the goal set is duplicated at the end like SOPLoader does for g == s, sop_loader.cpp:118-156), profit = 1 per
+    location.  The distance table is NOT materialised here (8 N^2 bytes = 33 GB at the default size): the Problem
+    carries the centres and `dubins_radius`, and the engine builds the table on the device
+    (vnsgpu_build_table_dubins).  Returns the flat Problem directly."""
+    rs = np.random.Generator(np.random.MT19937(seed))
+    ctr = np.floor(rs.uniform(0.0, box, size=(n_centres, 2)))
+    depot = np.floor(ctr.mean(0))
+    centers = np.vstack([depot[None, :], ctr, depot[None, :]])            # start, locations, goal (= the depot again)
+    C = n_centres + 2
+    m = np.full(C, headings, dtype=np.int32)
+    off = np.zeros(C + 1, dtype=np.int32)
+    off[1:] = np.cumsum(m)
+    order = nn_tour(centers[:-1], 0)
+    tour_len = float(np.sqrt(((centers[order] - centers[np.roll(order, -1)]) ** 2).sum(1)).sum())
+    reward = np.ones(C)
+    reward[0] = reward[-1] = 0.0
+    node_id = np.arange(C * headings, dtype=np.int32)
+    node_id[-headings:] = node_id[:headings]                               # the goal's samples are the depot's nodes
+    return ins.Problem(name=name or "synth_dop_%d_x%d" % (n_centres, headings), C=C, m=m, off=off, reward=reward, start=0,
+                       goal=C - 1, budget=float(int(budget_fraction * tour_len)), node_id=node_id,
+                       orig_cluster_id=np.concatenate([np.arange(C - 1), [0]]).astype(np.int32), rule=-1,
+                       centers=centers, dubins_radius=radius_fraction * box)
+
+
 def centroid_tour_state(pb: ins.Problem, fraction: float = 0.85):
     """A long feasible-looking tour without running greedy_insertion (which is O(C^3) evaluations at this
     size): the nearest-neighbour order over the cluster centroids, cut where the centroid-to-centroid length
     reaches `fraction` of the budget.  Returns (vns vector, T) for VnsSopPath.set()."""
-    cent = np.vstack([pb.xy[pb.off[c]:pb.off[c + 1]].mean(0) for c in range(pb.C)])
+    cent = pb.centers if pb.xy is None else np.vstack([pb.xy[pb.off[c]:pb.off[c + 1]].mean(0) for c in range(pb.C)])
     inner = [c for c in range(pb.C) if c not in (pb.start, pb.goal)]
     order = nn_tour(cent[[pb.start] + inner], 0)[1:]                    # indices into [start] + inner
     seq = [inner[k - 1] for k in order]
