@@ -74,7 +74,7 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-solve", action="store_true", help="skip the time-to-reward leg")
-    ap.add_argument("--vector-cache", type=int, default=1, help="vnsgpu_set_vector_cache: 0 off, 1 auto (batch >= 4 C^2), 2 always")
+    ap.add_argument("--vector-cache", type=int, default=1, help="vnsgpu_set_vector_cache: 0 off, 1 auto (batch >= C^2), 2 always")
     ap.add_argument("--no-solve-cpu", action="store_true", help="time-to-reward: skip the reference binary runs (long on vm1084)")
     ap.add_argument("--sweep", action="store_true", help="candidate-batch sweep 2^10 .. --batch (x4 steps), device-resident (BASELINE config 5)")
     ap.add_argument("--multi-start", type=int, default=148, help="seeds of the multi-start leg (0 = skip)")
@@ -528,8 +528,17 @@ def run_b200(args):
         h_pk = torch.empty(n, dtype=torch.int64).pin_memory()
         h_pk.numpy()[:] = p.pack_cands(cands).view(np.int64)
 
-        def host_step(packed=True):
-            if packed:      # 8-byte descriptors (vnsgpu_pack_cand): half the host-to-device bytes
+        h_pk32 = h_len32 = None
+        if int_path:   # compact wire format of all-integer tables: 4 B descriptors in, int32 lengths + flags out
+            h_pk32 = torch.empty(n, dtype=torch.int32).pin_memory()
+            h_pk32.numpy()[:] = p.pack_cands32(cands).view(np.int32)
+            h_len32 = torch.empty(n, dtype=torch.int32).pin_memory()
+
+        def host_step(packed=1):
+            if packed == 2:
+                eng._ck(lib.vnsgpu_eval_batch_packed32(eng.h, p.h, n, C.c_void_p(h_pk32.data_ptr()), pb.budget, 1,
+                                                       C.c_void_p(h_len32.data_ptr()), C.c_void_p(h_fl.data_ptr()), C.byref(first)))
+            elif packed:    # 8-byte descriptors (vnsgpu_pack_cand): half the host-to-device bytes
                 eng._ck(lib.vnsgpu_eval_batch_packed(eng.h, p.h, n, C.c_void_p(h_pk.data_ptr()), pb.budget, 1,
                                                      C.cast(h_len.data_ptr(), C.POINTER(C.c_double)), None,
                                                      C.c_void_p(h_fl.data_ptr()), C.byref(first)))
@@ -551,14 +560,30 @@ def run_b200(args):
             barrier()
             return max_over_ranks(time.perf_counter() - t0), eng.launches - l0
 
-        dt16, _ = timed(False)
-        dt, nl = timed(True)
-        launches += nl
-        e2e = {"value": world * n * K / dt, "unit": "evals/s", "h2d_bytes_per_step": world * n * 8,
-               "d2h_bytes_per_step": world * (n * 9 + 8), "ms_per_step": 1e3 * dt / K,
-               "call": "vnsgpu_eval_batch_packed (pinned host buffers: 8 B descriptors in; lengths + flags + first accepted index out)",
-               "with_16B_descriptors": {"value": world * n * K / dt16, "ms_per_step": 1e3 * dt16 / K, "call": "vnsgpu_eval_batch",
-                                        "h2d_bytes_per_step": world * n * 16}}
+        dt16, _ = timed(0)
+        dt8, nl8 = timed(1)
+        first8 = first.value
+        sub16 = {"value": world * n * K / dt16, "ms_per_step": 1e3 * dt16 / K, "call": "vnsgpu_eval_batch",
+                 "h2d_bytes_per_step": world * n * 16, "d2h_bytes_per_step": world * (n * 9 + 8)}
+        sub8 = {"value": world * n * K / dt8, "ms_per_step": 1e3 * dt8 / K, "call": "vnsgpu_eval_batch_packed",
+                "h2d_bytes_per_step": world * n * 8, "d2h_bytes_per_step": world * (n * 9 + 8)}
+        if int_path:
+            dt, nl = timed(2)
+            launches += nl
+            in_b, out_b = 4, 5
+            e2e = {"value": world * n * K / dt, "unit": "evals/s", "h2d_bytes_per_step": world * n * 4,
+                   "d2h_bytes_per_step": world * (n * 5 + 8), "ms_per_step": 1e3 * dt / K,
+                   "call": "vnsgpu_eval_batch_packed32 (pinned host buffers: 4 B descriptors in; int32 lengths - exact on this "
+                           "all-integer table - + flags + first accepted index out)",
+                   "with_8B_descriptors_f64_lengths": sub8, "with_16B_descriptors": sub16}
+            if world == 1:
+                assert first.value == first8, "compact and 8-byte entry points disagree on the first accepted candidate"
+            assert torch.equal(h_len32[:65536].double(), h_len[:65536]), "compact entry point: lengths differ"
+        else:
+            launches += nl8
+            in_b, out_b = 8, 9
+            e2e = dict(sub8, unit="evals/s", with_16B_descriptors=sub16,
+                       call="vnsgpu_eval_batch_packed (pinned host buffers: 8 B descriptors in; lengths + flags + first accepted index out)")
         # what the link alone allows: the same buffers copied with nothing else running (explains e2e vs value)
         d_tmp = torch.empty(n * 16, dtype=torch.uint8, device=dev)
         h_tmp = h_c
@@ -575,14 +600,14 @@ def run_b200(args):
         torch.cuda.synchronize()
         e2e["pcie_h2d_gbs"] = 4 * n * 16 / (evs[0].elapsed_time(evs[1]) * 1e-3) / 1e9
         e2e["pcie_d2h_gbs"] = 4 * n * 8 / (evs[1].elapsed_time(evs[2]) * 1e-3) / 1e9
-        e2e["copy_bound_ms_per_step"] = max(n * 8 / e2e["pcie_h2d_gbs"], (n * 9 + 8) / e2e["pcie_d2h_gbs"]) * 1e-6
+        e2e["copy_bound_ms_per_step"] = max(n * in_b / e2e["pcie_h2d_gbs"], (n * out_b + 8) / e2e["pcie_d2h_gbs"]) * 1e-6
         del d_tmp
         if world == 1:
             assert first.value == first_dev, "host and device entry points disagree on the first accepted candidate"
         assert torch.equal(h_len[:4096], d_len[:4096].cpu()), "host and device entry points disagree"
 
     hbm_regime = eng.table_bytes / 2 > 126e6
-    vec_mode = bool(int_path and args.vector_cache and pb.m.max() <= 32 and (n >= 4 * pb.C * pb.C or args.vector_cache == 2))
+    vec_mode = bool(int_path and args.vector_cache and pb.m.max() <= 32 and (n >= pb.C * pb.C or args.vector_cache == 2))
     peak, peak_src = measured_hbm_peak()
     achieved = alg_bytes / (kern_ms * 1e-3) / 1e9
     line = {

@@ -112,7 +112,7 @@ vnsgpu_status vnsgpu_set_batch_sort(vnsgpu_ctx *ctx, int enable);
  * built once per call and shared by all candidates (exactly associative on integers: bit-identical
  * lengths); a MOVE / EXCHANGE chain of `span` blocks then costs at most 5.  enable = 0: block by block. */
 vnsgpu_status vnsgpu_set_segment_cache(vnsgpu_ctx *ctx, int enable);
-/* Integer tables, batches of >= 4 C^2 candidates (on top of the segment products): the two ends of every
+/* Integer tables, batches of >= C^2 candidates (on top of the segment products): the two ends of every
  * candidate's chain depend only on (cluster, layer) - they are built once per call as vectors, and a candidate
  * costs at most ONE block step (exact: integer min-plus is associative).  enable = 0: segment products only;
  * 2: also for smaller batches. */
@@ -174,6 +174,17 @@ static inline uint64_t vnsgpu_pack_cand(int op, int a, int b, int gain_cluster)
 }
 vnsgpu_status vnsgpu_eval_batch_packed(vnsgpu_ctx *ctx, int path, int64_t n, const uint64_t *packed, double budget,
                                        int skip, double *len, double *lb, uint8_t *flags, int64_t *first_accept);
+/* Compact wire format for link-bound batches on ALL-INTEGER tables (vnsgpu_int_path_active): 4-byte descriptors in,
+ * int32 lengths out - 4 + 5 bytes per candidate over PCIe instead of 8 + 9.  Every length of an integer table is an
+ * integer below 2^31, so (double)len[i] is the reference's tryTo* value exactly; bad indices give INT32_MIN (the
+ * double calls give NaN).  Indices must lie in [0, 16384); gain_is_a != 0: the candidate's gain cluster is a (what
+ * insertRandom / exchangeRandom pass for ADD / REPLACE), else none.  VNSGPU_E_STATE on a real-valued table. */
+static inline uint32_t vnsgpu_pack_cand32(int op, int a, int b, int gain_is_a)
+{
+   return (uint32_t)(op & 7) | ((uint32_t)(a & 0x3fff) << 3) | ((uint32_t)(b & 0x3fff) << 17) | ((uint32_t)(gain_is_a != 0) << 31);
+}
+vnsgpu_status vnsgpu_eval_batch_packed32(vnsgpu_ctx *ctx, int path, int64_t n, const uint32_t *packed, double budget,
+                                         int skip, int32_t *len, uint8_t *flags, int64_t *first_accept);
 /* device buffers, asynchronous on `stream` (NULL = context stream); d_first_accept: one int64 that
  * the call resets and fills like first_accept above (-1 = none), or NULL */
 vnsgpu_status vnsgpu_eval_batch_dev(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *d_cands,

@@ -286,8 +286,15 @@ def test_eval_batch_both_arithmetic_paths_vs_oracle(name, int_path, golden, eng_
             assert first == (int(ok[0]) if len(ok) else -1)
             lnp, lbp, flp, firstp = pg.eval_batch_packed(big)          # 8-byte descriptors, same answers
             assert (lnp[~bad] == ln[~bad]).all() and (lbp[~bad] == lb[~bad]).all() and (flp == fl).all() and firstp == first
+            if int_path:     # compact wire format: 4-byte descriptors in, int32 lengths out (exact on integer tables)
+                ln32, fl32, first32 = pg.eval_batch_packed32(big)
+                assert ln32.dtype == np.int32 and (ln32[~bad] == ln[~bad]).all() and (ln32[bad] == np.iinfo(np.int32).min).all()
+                assert (fl32 == fl).all() and first32 == first
+            else:            # real-valued evaluation path: the int32 call refuses instead of rounding
+                with pytest.raises(engine.VnsGpuError):
+                    pg.eval_batch_packed32(big[:64])
             # (the integer path has just used the endpoint vectors + exact segment products: batch >= 16384
-            # and >= 4 C^2); the same batch with the vectors off, the products off, the sort off
+            # and >= C^2); the same batch with the vectors off, the products off, the sort off
             for sort, seg, vec in ((False, True, True), (True, True, False), (False, True, False), (True, False, False), (False, False, False)):
                 e.set_batch_sort(sort)
                 e.set_segment_cache(seg)

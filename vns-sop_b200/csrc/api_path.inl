@@ -218,12 +218,13 @@ static bool seg_wanted(const vnsgpu_ctx *ctx, int64_t n)
 }
 
 // evaluation form of a batch: 0 block by block, 1 segment products, 2 endpoint vectors + segment products.
-// The vectors cost ~8 C (T+2) block steps per path state, so they pay once the batch is a few times C^2.
+// The vectors cost 2 C (T+2) + 4 T (T+2) <= 6 C^2 block steps per path state and save ~4 block steps per candidate, so
+// they pay once the batch reaches ~C^2 (T is only known on the device: C bounds it).
 static int eval_mode(const vnsgpu_ctx *ctx, int64_t n)
 {
    if (!seg_wanted(ctx, n)) return 0;
    const int64_t C = ctx->I.C;
-   if (ctx->use_vec && ctx->I.mp <= 32 && (n >= 4 * C * C || ctx->use_vec == 2) && vec_ints((int)C, (int)C + 2, ctx->I.mp) < (1ull << 31)) return 2;
+   if (ctx->use_vec && ctx->I.mp <= 32 && (n >= C * C || ctx->use_vec == 2) && vec_ints((int)C, (int)C + 2, ctx->I.mp) < (1ull << 31)) return 2;
    return 1;
 }
 
@@ -237,7 +238,7 @@ static vnsgpu_status prepare_seg(vnsgpu_ctx *ctx, int path, cudaStream_t st)
    const size_t smem = seg_build_smem(I.rows, I.mp);
    if (smem <= (size_t)ctx->max_smem) {
       if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k_seg_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      k_seg_build<<<I.rows, 128, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta);
+      k_seg_build<<<std::min(I.rows, I.C + 2), VNS_SEG_THREADS, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta);
    } else
       k_seg_build_g<<<I.rows, 128, 0, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta);
    LAUNCHED(ctx);
@@ -262,9 +263,14 @@ static vnsgpu_status prepare_eval(vnsgpu_ctx *ctx, int path, int mode, cudaStrea
    const int thr = I.mp <= 22 ? 256 : 128;                      // 2 staged blocks per warp: <= 32 KB per CTA
    const size_t smem = sizeof(int) * 2 * (size_t)I.mp * I.mp * (thr / 32);
    const int wpc = thr / 32;
-   k_vec_uw<<<dim3((I.C + wpc - 1) / wpc, Smax), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta, ctx->d_vec, ctx->d_veclb, LS);
+   // grid.y = layer lanes (the kernels stride over the layers): enough CTAs to fill the device on small instances,
+   // few enough that none is empty on large ones
+   const int gxu = (I.C + wpc - 1) / wpc, gxp = (Smax + 1 + wpc - 1) / wpc;
+   const int gyu = std::min(Smax, std::max(16, (8 * ctx->num_sms + gxu - 1) / gxu));
+   const int gyp = std::min(Smax, std::max(16, (8 * ctx->num_sms + gxp - 1) / gxp));
+   k_vec_uw<<<dim3(gxu, gyu), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta, ctx->d_vec, ctx->d_veclb, LS);
    LAUNCHED(ctx);
-   k_vec_pairs<<<dim3((Smax + 1 + wpc - 1) / wpc, Smax), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta, ctx->d_vec, LS);
+   k_vec_pairs<<<dim3(gxp, gyp), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta, ctx->d_vec, LS);
    LAUNCHED(ctx);
    return VNSGPU_OK;
 }
@@ -390,9 +396,30 @@ __global__ void __launch_bounds__(256) k_unpack_cands(long long n, const unsigne
    }
 }
 
-// src: vnsgpu_cand[n] (packed == 0) or uint64_t[n] in the vnsgpu_pack_cand format (packed == 1)
+// 4-byte descriptors (vnsgpu_pack_cand32): op 3 bits, a 14 bits, b 14 bits, bit 31 = the gain cluster is a
+__global__ void __launch_bounds__(256) k_unpack_cands32(long long n, const unsigned *__restrict__ src, vnsgpu_cand *__restrict__ dst)
+{
+   for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < n; q += (long long)gridDim.x * blockDim.x) {
+      const unsigned w = src[q];
+      int4 c;
+      c.x = (int)(w & 7); c.y = (int)((w >> 3) & 0x3fff); c.z = (int)((w >> 17) & 0x3fff); c.w = (w >> 31) ? c.y : -1;
+      reinterpret_cast<int4 *>(dst)[q] = c;
+   }
+}
+
+// lengths of an all-integer table as int32 (exact: every length is an integer below 2^31); NaN (bad indices) -> INT_MIN
+__global__ void __launch_bounds__(256) k_len_to_i32(long long n, const double *__restrict__ len, int *__restrict__ out)
+{
+   for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < n; q += (long long)gridDim.x * blockDim.x) {
+      const double l = len[q];
+      out[q] = l == l ? (int)l : INT_MIN;
+   }
+}
+
+// src: vnsgpu_cand[n] (packed == 0), uint64_t[n] in the vnsgpu_pack_cand format (packed == 1) or uint32_t[n] in the
+// vnsgpu_pack_cand32 format (packed == 2); len_i32 (integer tables only): lengths as int32 instead of len
 static vnsgpu_status eval_batch_host(vnsgpu_ctx *ctx, int path, int64_t n, const void *src, int packed, double budget, int skip,
-                                     double *len, double *lb, uint8_t *flags, int64_t *first_accept)
+                                     double *len, double *lb, uint8_t *flags, int64_t *first_accept, int32_t *len_i32 = nullptr)
 {
    CK(cudaSetDevice(ctx->device));
    if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
@@ -401,10 +428,13 @@ static vnsgpu_status eval_batch_host(vnsgpu_ctx *ctx, int path, int64_t n, const
    const size_t o_len = al16(sizeof(vnsgpu_cand) * n), o_lb = o_len + al16(sizeof(double) * n);
    const size_t o_fl = o_lb + al16(sizeof(double) * n);
    const size_t o_pk = o_fl + al16(n);
-   vnsgpu_status s = need_scratch(ctx, o_pk + (packed ? al16(sizeof(unsigned long long) * n) : 0));
+   const size_t o_li = o_pk + (packed ? al16(sizeof(unsigned long long) * n) : 0);
+   vnsgpu_status s = need_scratch(ctx, o_li + (len_i32 ? al16(sizeof(int) * n) : 0));
    if (s) return s;
    char *b = (char *)ctx->d_scratch;
    unsigned long long *d_pk = (unsigned long long *)(b + o_pk);
+   unsigned *d_pk32 = (unsigned *)(b + o_pk);
+   int *d_li = (int *)(b + o_li);
    vnsgpu_cand *d_c = (vnsgpu_cand *)b;
    double *d_len = (double *)(b + o_len), *d_lb = (double *)(b + o_lb);
    uint8_t *d_fl = (uint8_t *)(b + o_fl);
@@ -449,21 +479,30 @@ static vnsgpu_status eval_batch_host(vnsgpu_ctx *ctx, int path, int64_t n, const
    int64_t lo = 0;
    for (int c = 0; c < (int)cut.size(); lo += cut[c], ++c) {
       const int64_t cn = cut[c];
-      if (packed)
+      if (packed == 2)
+         CK(cudaMemcpyAsync(d_pk32 + lo, (const unsigned *)src + lo, sizeof(unsigned) * cn, cudaMemcpyHostToDevice, ctx->s_in));
+      else if (packed)
          CK(cudaMemcpyAsync(d_pk + lo, (const unsigned long long *)src + lo, sizeof(unsigned long long) * cn, cudaMemcpyHostToDevice, ctx->s_in));
       else
          CK(cudaMemcpyAsync(d_c + lo, (const vnsgpu_cand *)src + lo, sizeof(vnsgpu_cand) * cn, cudaMemcpyHostToDevice, ctx->s_in));
       CK(cudaEventRecord(ctx->ev_in[c], ctx->s_in));
       CK(cudaStreamWaitEvent(sk, ctx->ev_in[c], 0));
       if (packed) {
-         k_unpack_cands<<<(int)std::min<int64_t>((cn + 255) / 256, (int64_t)ctx->num_sms * 8), 256, 0, sk>>>(cn, d_pk + lo, d_c + lo);
+         const int ug = (int)std::min<int64_t>((cn + 255) / 256, (int64_t)ctx->num_sms * 8);
+         if (packed == 2) k_unpack_cands32<<<ug, 256, 0, sk>>>(cn, d_pk32 + lo, d_c + lo);
+         else k_unpack_cands<<<ug, 256, 0, sk>>>(cn, d_pk + lo, d_c + lo);
          LAUNCHED(ctx);
       }
-      s = launch_eval(ctx, path, cn, lo, d_c + lo, budget, skip, len ? d_len + lo : nullptr, lb ? d_lb + lo : nullptr,
+      s = launch_eval(ctx, path, cn, lo, d_c + lo, budget, skip, (len || len_i32) ? d_len + lo : nullptr, lb ? d_lb + lo : nullptr,
                       flags ? d_fl + lo : nullptr, (unsigned long long *)ctx->d_first, sk, c, lo, useseg);
       if (s) return s;
+      if (len_i32) {
+         k_len_to_i32<<<(int)std::min<int64_t>((cn + 255) / 256, (int64_t)ctx->num_sms * 8), 256, 0, sk>>>(cn, d_len + lo, d_li + lo);
+         LAUNCHED(ctx);
+      }
       CK(cudaEventRecord(ctx->ev_k[c], sk));
       CK(cudaStreamWaitEvent(ctx->s_out, ctx->ev_k[c], 0));
+      if (len_i32) CK(cudaMemcpyAsync(len_i32 + lo, d_li + lo, sizeof(int) * cn, cudaMemcpyDeviceToHost, ctx->s_out));
       if (len) CK(cudaMemcpyAsync(len + lo, d_len + lo, sizeof(double) * cn, cudaMemcpyDeviceToHost, ctx->s_out));
       if (lb) CK(cudaMemcpyAsync(lb + lo, d_lb + lo, sizeof(double) * cn, cudaMemcpyDeviceToHost, ctx->s_out));
       if (flags) CK(cudaMemcpyAsync(flags + lo, d_fl + lo, cn, cudaMemcpyDeviceToHost, ctx->s_out));
@@ -486,6 +525,16 @@ vnsgpu_status vnsgpu_eval_batch_packed(vnsgpu_ctx *ctx, int path, int64_t n, con
                                        double *lb, uint8_t *flags, int64_t *first_accept)
 {
    return eval_batch_host(ctx, path, n, packed, 1, budget, skip, len, lb, flags, first_accept);
+}
+
+vnsgpu_status vnsgpu_eval_batch_packed32(vnsgpu_ctx *ctx, int path, int64_t n, const uint32_t *packed, double budget, int skip,
+                                         int32_t *len, uint8_t *flags, int64_t *first_accept)
+{
+   if (!vnsgpu_int_path_active(ctx)) {
+      ctx->err = "vnsgpu_eval_batch_packed32: int32 lengths need an all-integer table (exact int32 path not active)";
+      return VNSGPU_E_STATE;
+   }
+   return eval_batch_host(ctx, path, n, packed, 2, budget, skip, nullptr, nullptr, flags, first_accept, len);
 }
 
 vnsgpu_status vnsgpu_cand_bytes(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *cands, int64_t *bytes)

@@ -542,25 +542,35 @@ __global__ void __launch_bounds__(128) k_seg_build_g(InstDev I, PathDev P, int *
    }
 }
 
-// The same recurrence with the running product in shared memory (double-buffered) and the table blocks of the next
-// three steps in flight (cp.async ring of four): a step costs one barrier instead of a global round trip (the chain
-// of block a has S - a - 1 dependent steps; block 0's chain is the kernel's duration).
-// dynamic shared memory: seg_build_smem(rows, mp) bytes
-__host__ __device__ inline size_t seg_build_smem(int rows, int mp) { return sizeof(int) * ((size_t)2 * (rows + 3) + (size_t)6 * mp * mp); }
-
-__global__ void __launch_bounds__(128) k_seg_build(InstDev I, PathDev P, int *Dv, const int *meta)
+// The same recurrence with the running product in shared memory and the table blocks of the next three steps in
+// flight (cp.async ring of four).  Row i of M(a,b) depends on row i of M(a,b-1) only, so the rows are independent
+// chains: warp w of the 8 owns rows w, w+8, w+16, w+24 (lane = column), keeps them in its own slice of shared memory
+// (read back as broadcast 16-byte loads: four k per load) and needs no barrier for them; the one barrier per step
+// publishes the staged table block.  The chain of block a has S - a - 1 dependent steps; block 0's chain is the
+// kernel's duration (the first version spread every product over the whole CTA: 6 us per step, this one ~0.5 us).
+// Needs mp <= 32.  dynamic shared memory: seg_build_smem(rows, mp) bytes
+#define VNS_SEG_THREADS 256
+__host__ __device__ inline size_t seg_build_smem(int rows, int mp)
 {
-   extern __shared__ int smem_i[];
-   const int T = P.hdr[HDR_T], S = T + 1, R = I.rows + 3, mp2 = I.mp * I.mp;
+   return sizeof(int) * ((size_t)((2 * (rows + 3) + 3) & ~3) + (size_t)4 * ((mp * mp + 3) & ~3) + (size_t)32 * 32);
+}
+
+__global__ void __launch_bounds__(VNS_SEG_THREADS) k_seg_build(InstDev I, PathDev P, int *Dv, const int *meta)
+{
+   extern __shared__ __align__(16) int smem_i[];
+   constexpr int INF = VNS_INT_INF;
+   const int T = P.hdr[HDR_T], S = T + 1, R = I.rows + 3, mp2 = (I.mp * I.mp + 3) & ~3;
    const int a = blockIdx.x;
    if (a + 2 > S) return;
    int *l_m = smem_i, *l_off = smem_i + R;                  // per layer l >= a: cluster size, first sample
-   int *prod = smem_i + 2 * R, *dblk = prod + 2 * mp2;       // 2 product buffers, ring of 4 table blocks
+   int *dblk = smem_i + ((2 * R + 3) & ~3);                  // ring of 4 table blocks
+   int *prow = dblk + 4 * mp2;                               // 32 rows x 32 of the running product (INF beyond its columns)
    for (int l = a + threadIdx.x; l <= S; l += blockDim.x) {
       const int c = layer_cluster(I, P.tg, T, l);
       l_m[l] = I.m[c]; l_off[l] = I.off[c];
    }
    __syncthreads();
+   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
    const int ma = l_m[a];
    long long ooff = reinterpret_cast<const long long *>(meta + 2 * R)[a];   // M(a,a+2) starts the row; M(a,b+1) follows M(a,b)
    // D(l, l+1) -> dst (nothing when l >= S); always one commit group so that the group count per step is fixed
@@ -573,27 +583,49 @@ __global__ void __launch_bounds__(128) k_seg_build(InstDev I, PathDev P, int *Dv
       }
       asm volatile("cp.async.commit_group;");
    };
-   fetch(prod, a);                                           // M(a,a+1) = D(a,a+1)
    for (int b = a + 2; b <= a + 4; ++b) fetch(dblk + (b & 3) * mp2, b - 1);   // step b multiplies by D(b-1,b)
-   int cur = 0;
+   {   // M(a,a+1) = D(a,a+1): this warp's rows
+      const int m1 = l_m[a + 1];
+      const int *src = Dv + ((long long)l_off[a] * I.N + (long long)ma * l_off[a + 1]);
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+         const int i = w + 8 * r;
+         if (i < ma) prow[i * 32 + lane] = lane < m1 ? __ldg(src + i * m1 + lane) : INF;
+      }
+      __syncwarp();
+   }
    for (int b = a + 2; b <= S; ++b) {
       asm volatile("cp.async.wait_group 2;");               // all but the blocks of steps b+1, b+2 have landed
       __syncthreads();
       fetch(dblk + ((b + 3) & 3) * mp2, b + 2);              // that buffer was read by step b-1
       const int mk = l_m[b - 1], mb = l_m[b];
-      const int *pv = prod + cur * mp2, *d = dblk + (b & 3) * mp2;
-      int *nx = prod + (cur ^ 1) * mp2;
-      int *out = Dv + ooff;
-      for (int e = threadIdx.x; e < ma * mb; e += blockDim.x) {
-         const int i = e / mb, j = e - i * mb;
-         int acc = VNS_INT_INF;
-#pragma unroll 4
-         for (int k = 0; k < mk; ++k) acc = __viaddmin_s32(pv[i * mk + k], d[k * mb + j], acc);
-         out[e] = acc;
-         nx[e] = acc;
+      const int *d = dblk + (b & 3) * mp2 + min(lane, mb - 1);
+      int acc[4] = {INF, INF, INF, INF};
+      for (int k4 = 0; k4 < mk; k4 += 4) {
+         const int d0 = d[k4 * mb], d1 = d[min(k4 + 1, mk - 1) * mb], d2 = d[min(k4 + 2, mk - 1) * mb], d3 = d[min(k4 + 3, mk - 1) * mb];
+#pragma unroll
+         for (int r = 0; r < 4; ++r) {
+            if (w + 8 * r < ma) {                            // warp-uniform
+               const int4 p = *reinterpret_cast<const int4 *>(prow + (w + 8 * r) * 32 + k4);   // INF beyond mk
+               acc[r] = __viaddmin_s32(p.x, d0, acc[r]);
+               acc[r] = __viaddmin_s32(p.y, d1, acc[r]);
+               acc[r] = __viaddmin_s32(p.z, d2, acc[r]);
+               acc[r] = __viaddmin_s32(p.w, d3, acc[r]);
+            }
+         }
       }
+      __syncwarp();
+      int *out = Dv + ooff;
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+         const int i = w + 8 * r;
+         if (i < ma) {
+            if (lane < mb) out[i * mb + lane] = acc[r];
+            prow[i * 32 + lane] = lane < mb ? acc[r] : INF;
+         }
+      }
+      __syncwarp();
       ooff += ma * mb;
-      cur ^= 1;
    }
    asm volatile("cp.async.wait_group 0;");
 }

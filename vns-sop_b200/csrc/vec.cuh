@@ -53,8 +53,12 @@ __device__ __forceinline__ unsigned vec_pair(const VecCache &vc, int C, int mp, 
 // out of shared memory.
 __device__ __forceinline__ void warp_stage(int *dst, const int *__restrict__ src, int n, int lane)
 {
-   for (int e = lane; e < n; e += 32)
-      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(dst + e)), "l"(src + e));
+   const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
+   if ((((unsigned)(size_t)src | d) & 15u) == 0 && (n & 3) == 0) {   // warp-uniform: 16-byte copies (4 x fewer LSU instructions)
+      for (int e = lane * 4; e < n; e += 128) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d + 4u * e), "l"(src + e));
+   } else {
+      for (int e = lane; e < n; e += 32) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + 4u * e), "l"(src + e));
+   }
 }
 __device__ __forceinline__ void warp_stage_wait()
 {
@@ -71,13 +75,20 @@ __device__ __forceinline__ int vec_fwd(const int *blk, int ma, int mb, int v, in
    for (int s = 0; s < ma; ++s) acc = __viaddmin_s32(__shfl_sync(0xffffffffu, v, s), blk[s * mb + j], acc);
    return lane < mb ? acc : VNS_INT_INF;
 }
-// lane = source index; the staged ma x mb block times v (lane-held over the mb destination samples)
+// lane = source index; the staged ma x mb block times v (lane-held over the mb destination samples).  Lane s walks its
+// row DIAGONALLY (column (s + t) mod mb at step t): with mb = 32 the 32 lanes then hit 32 different banks, where the
+// straight order (every lane the same column: stride mb) is a 32-way bank conflict.  min is order-free: same result.
 __device__ __forceinline__ int vec_bwd(const int *blk, int ma, int mb, int v, int lane)
 {
    int acc = VNS_INT_INF;
    const int s = min(lane, ma - 1);
+   const int *row = blk + s * mb;
+   int j = s % mb;
 #pragma unroll 4
-   for (int j = 0; j < mb; ++j) acc = __viaddmin_s32(__shfl_sync(0xffffffffu, v, j), blk[s * mb + j], acc);
+   for (int t = 0; t < mb; ++t) {
+      acc = __viaddmin_s32(__shfl_sync(0xffffffffu, v, j), row[j], acc);
+      j = j + 1 == mb ? 0 : j + 1;
+   }
    return lane < ma ? acc : VNS_INT_INF;
 }
 
@@ -94,61 +105,65 @@ __device__ __forceinline__ LayerMeta layer_meta(const InstDev &I, const int *met
    return LayerMeta{meta, meta + 4 * R, meta + 5 * R};
 }
 
-// one warp per (l, c), grid.y = l: consecutive warps read consecutive blocks of row band lcl[l] (U) and write consecutive
-// vectors.  Needs mp <= 32.  Dynamic shared memory: 2 mp^2 ints per warp.
+// one warp per (l, c), l strided over grid.y: consecutive warps read consecutive blocks of row band lcl[l] (U) and write
+// consecutive vectors.  Needs mp <= 32.  Dynamic shared memory: 2 mp^2 ints per warp.
 __global__ void __launch_bounds__(256) k_vec_uw(InstDev I, PathDev P, const int *__restrict__ Dv, const int *__restrict__ meta,
                                                 int *__restrict__ vec, int *__restrict__ lbs, int LS)
 {
    extern __shared__ int smem_i[];
    const int T = P.hdr[HDR_T], S = T + 1, C = I.C, mp = I.mp;
    const int lane = threadIdx.x & 31;
-   const int l = blockIdx.y, c = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);      // grid.y = layer: no divisions
-   if (l > S || c >= C) return;
+   const int c = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+   if (c >= C) return;
    const LayerMeta lm = layer_meta(I, meta);
    VecCache vc{vec, lbs, LS};
    int *bU = smem_i + (threadIdx.x >> 5) * 2 * mp * mp, *bW = bU + mp * mp;
-   const int cl = lm.cl(l), ml = lm.m(l), ol = lm.off(l);
    const int mc = __ldg(I.m + c), oc = __ldg(I.off + c);
-   const bool doU = l <= S - 1, doW = l >= 1, sym = I.symmetric != 0;
-   // symmetric tables: D(c, cl) is the transpose of D(cl, c) - the column strip of W comes out of the same row band
-   if (doU || sym) warp_stage(bU, Dv + ((long long)ol * I.N + (long long)ml * oc), ml * mc, lane);     // D(cl, c)
-   if (doW && !sym) warp_stage(bW, Dv + ((long long)oc * I.N + (long long)mc * ol), mc * ml, lane);    // D(c, cl)
-   const int f = (doU && lane < ml) ? (int)P.F[(size_t)l * mp + lane] : VNS_INT_INF;
-   const int bv = (doW && lane < ml) ? (int)P.B[(size_t)l * mp + lane] : VNS_INT_INF;
-   int lb_ins = 0, lb_rep = 0, lb_rem = 0;
-   if (doW && lane == 0) {   // lower-bound sums (integers: order-free)
-      const int a = lm.cl(l - 1), nx = l <= S - 1 ? lm.cl(l + 1) : cl;
-      const int din = (int)I.dmin[(size_t)a * C + c];
-      lb_ins = din + (int)I.dmin[(size_t)c * C + cl];
-      lb_rep = din + (int)I.dmin[(size_t)c * C + nx];
-      lb_rem = (int)I.dmin[(size_t)a * C + nx];
-   }
-   warp_stage_wait();
-   if (doU) {   // U(c,l) = F[l] (x) D(cl, c)
-      const int u = vec_fwd(bU, ml, mc, f, lane);
-      if (lane < mp) vec[vec_uw(vc, C, mp, 0, c, l) + lane] = u;
-      if (c == 0 && lane < mp) vec[vec_fi(vc, C, mp, l) + lane] = f;
-   }
-   if (doW) {   // W(c,l) = D(c, cl) (x) B[l]
-      const int wv = sym ? vec_fwd(bU, ml, mc, bv, lane) : vec_bwd(bW, mc, ml, bv, lane);
-      if (lane < mp) vec[vec_uw(vc, C, mp, 1, c, l) + lane] = wv;
-      if (lane == 0) {
-         lbs[(size_t)c * LS + l] = lb_ins;                                   // insert c before l
-         if (l <= S - 1) lbs[(size_t)(C + c) * LS + l] = lb_rep;             // c replaces l
-         if (c == 0 && l <= S - 1) lbs[(size_t)2 * C * LS + l] = lb_rem;     // l removed
+   // T is only known on the device: grid.y is a fixed number of layer lanes, every warp strides over the layers
+   for (int l = blockIdx.y; l <= S; l += gridDim.y) {
+      const int cl = lm.cl(l), ml = lm.m(l), ol = lm.off(l);
+      const bool doU = l <= S - 1, doW = l >= 1, sym = I.symmetric != 0;
+      // symmetric tables: D(c, cl) is the transpose of D(cl, c) - the column strip of W comes out of the same row band
+      if (doU || sym) warp_stage(bU, Dv + ((long long)ol * I.N + (long long)ml * oc), ml * mc, lane);     // D(cl, c)
+      if (doW && !sym) warp_stage(bW, Dv + ((long long)oc * I.N + (long long)mc * ol), mc * ml, lane);    // D(c, cl)
+      const int f = (doU && lane < ml) ? (int)P.F[(size_t)l * mp + lane] : VNS_INT_INF;
+      const int bv = (doW && lane < ml) ? (int)P.B[(size_t)l * mp + lane] : VNS_INT_INF;
+      int lb_ins = 0, lb_rep = 0, lb_rem = 0;
+      if (doW && lane == 0) {   // lower-bound sums (integers: order-free)
+         const int a = lm.cl(l - 1), nx = l <= S - 1 ? lm.cl(l + 1) : cl;
+         const int din = (int)I.dmin[(size_t)a * C + c];
+         lb_ins = din + (int)I.dmin[(size_t)c * C + cl];
+         lb_rep = din + (int)I.dmin[(size_t)c * C + nx];
+         lb_rem = (int)I.dmin[(size_t)a * C + nx];
       }
+      warp_stage_wait();
+      if (doU) {   // U(c,l) = F[l] (x) D(cl, c)
+         const int u = vec_fwd(bU, ml, mc, f, lane);
+         if (lane < mp) vec[vec_uw(vc, C, mp, 0, c, l) + lane] = u;
+         if (c == 0 && lane < mp) vec[vec_fi(vc, C, mp, l) + lane] = f;
+      }
+      if (doW) {   // W(c,l) = D(c, cl) (x) B[l]
+         const int wv = sym ? vec_fwd(bU, ml, mc, bv, lane) : vec_bwd(bW, mc, ml, bv, lane);
+         if (lane < mp) vec[vec_uw(vc, C, mp, 1, c, l) + lane] = wv;
+         if (lane == 0) {
+            lbs[(size_t)c * LS + l] = lb_ins;                                   // insert c before l
+            if (l <= S - 1) lbs[(size_t)(C + c) * LS + l] = lb_rep;             // c replaces l
+            if (c == 0 && l <= S - 1) lbs[(size_t)2 * C * LS + l] = lb_rem;     // l removed
+         }
+      }
+      __syncwarp();   // the staged blocks are overwritten by the next layer
    }
 }
 
-// one warp per (x, l), x = 1 .. T (path layer, cluster cx; grid.y), l = 1 .. S.  Two table blocks, four products.
+// one warp per (x, l), x = 1 .. T (path layer, cluster cx; strided over grid.y), l = 1 .. S.  Two table blocks, four products.
 __global__ void __launch_bounds__(256) k_vec_pairs(InstDev I, PathDev P, const int *__restrict__ Dv, const int *__restrict__ meta,
                                                    int *__restrict__ vec, int LS)
 {
    extern __shared__ int smem_i[];
    const int T = P.hdr[HDR_T], S = T + 1, C = I.C, mp = I.mp;
    const int lane = threadIdx.x & 31;
-   const int x = blockIdx.y + 1, wl = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);   // grid.y = path layer x
-   if (x > T) return;
+   const int wl = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+   if (wl > S) return;
    const LayerMeta lm = layer_meta(I, meta);
    VecCache vc{vec, nullptr, LS};
    int *b1 = smem_i + (threadIdx.x >> 5) * 2 * mp * mp, *b2 = b1 + mp * mp;
@@ -156,46 +171,52 @@ __global__ void __launch_bounds__(256) k_vec_pairs(InstDev I, PathDev P, const i
       // one block D(cx, lcl[l]) per warp, l = 0 .. S: it is also D(lcl[l], cx) transposed, so all four products are
       // forward steps through it:  InsF(x,l), RepF(x,l-1) from U;  InsB(x,l+1), RepB(x,l+1) from W
       const int l = wl;
-      if (l > S) return;
-      const int cx = lm.cl(x), mx = lm.m(x), ox = lm.off(x), ml = lm.m(l);
-      warp_stage(b1, Dv + ((long long)ox * I.N + (long long)mx * lm.off(l)), mx * ml, lane);
-      auto ld = [&](int k, int ll, bool on) { return (on && lane < mx) ? __ldg(vec + vec_uw(vc, C, mp, k, cx, min(max(ll, 0), S)) + lane) : VNS_INT_INF; };
-      const int u1 = ld(0, l - 1, l >= 1), u2 = ld(0, l - 2, l >= 2), w1 = ld(1, l + 1, l <= S - 1), w2 = ld(1, l + 2, l <= S - 2);
-      warp_stage_wait();
-      int a1 = VNS_INT_INF, a2 = VNS_INT_INF, a3 = VNS_INT_INF, a4 = VNS_INT_INF;
-      const int j = min(lane, ml - 1);
+      const int ml = lm.m(l), ofl = lm.off(l);
+      for (int x = blockIdx.y + 1; x <= T; x += gridDim.y) {
+         const int cx = lm.cl(x), mx = lm.m(x), ox = lm.off(x);
+         warp_stage(b1, Dv + ((long long)ox * I.N + (long long)mx * ofl), mx * ml, lane);
+         auto ld = [&](int k, int ll, bool on) { return (on && lane < mx) ? __ldg(vec + vec_uw(vc, C, mp, k, cx, min(max(ll, 0), S)) + lane) : VNS_INT_INF; };
+         const int u1 = ld(0, l - 1, l >= 1), u2 = ld(0, l - 2, l >= 2), w1 = ld(1, l + 1, l <= S - 1), w2 = ld(1, l + 2, l <= S - 2);
+         warp_stage_wait();
+         int a1 = VNS_INT_INF, a2 = VNS_INT_INF, a3 = VNS_INT_INF, a4 = VNS_INT_INF;
+         const int j = min(lane, ml - 1);
 #pragma unroll 2
-      for (int s = 0; s < mx; ++s) {
-         const int d = b1[s * ml + j];
-         a1 = __viaddmin_s32(__shfl_sync(0xffffffffu, u1, s), d, a1);
-         a2 = __viaddmin_s32(__shfl_sync(0xffffffffu, u2, s), d, a2);
-         a3 = __viaddmin_s32(__shfl_sync(0xffffffffu, w1, s), d, a3);
-         a4 = __viaddmin_s32(__shfl_sync(0xffffffffu, w2, s), d, a4);
-      }
-      if (lane < mp) {
-         const bool in = lane < ml;
-         if (l >= 1) vec[vec_pair(vc, C, mp, 0, x, l) + lane] = in ? a1 : VNS_INT_INF;
-         if (l >= 2) vec[vec_pair(vc, C, mp, 2, x, l - 1) + lane] = in ? a2 : VNS_INT_INF;
-         if (l <= S - 1) vec[vec_pair(vc, C, mp, 1, x, l + 1) + lane] = in ? a3 : VNS_INT_INF;
-         if (l <= S - 2) vec[vec_pair(vc, C, mp, 3, x, l + 1) + lane] = in ? a4 : VNS_INT_INF;
+         for (int s = 0; s < mx; ++s) {
+            const int d = b1[s * ml + j];
+            a1 = __viaddmin_s32(__shfl_sync(0xffffffffu, u1, s), d, a1);
+            a2 = __viaddmin_s32(__shfl_sync(0xffffffffu, u2, s), d, a2);
+            a3 = __viaddmin_s32(__shfl_sync(0xffffffffu, w1, s), d, a3);
+            a4 = __viaddmin_s32(__shfl_sync(0xffffffffu, w2, s), d, a4);
+         }
+         if (lane < mp) {
+            const bool in = lane < ml;
+            if (l >= 1) vec[vec_pair(vc, C, mp, 0, x, l) + lane] = in ? a1 : VNS_INT_INF;
+            if (l >= 2) vec[vec_pair(vc, C, mp, 2, x, l - 1) + lane] = in ? a2 : VNS_INT_INF;
+            if (l <= S - 1) vec[vec_pair(vc, C, mp, 1, x, l + 1) + lane] = in ? a3 : VNS_INT_INF;
+            if (l <= S - 2) vec[vec_pair(vc, C, mp, 3, x, l + 1) + lane] = in ? a4 : VNS_INT_INF;
+         }
+         __syncwarp();   // the staged block is overwritten by the next x
       }
       return;
    }
    const int l = wl + 1;
    if (l > S) return;
-   const int cx = lm.cl(x), mx = lm.m(x), ox = lm.off(x);
-   const int ml = lm.m(l), ma = lm.m(l - 1);
-   warp_stage(b1, Dv + ((long long)ox * I.N + (long long)mx * lm.off(l)), mx * ml, lane);          // D(cx, lcl[l])
-   warp_stage(b2, Dv + ((long long)lm.off(l - 1) * I.N + (long long)ma * ox), ma * mx, lane);      // D(lcl[l-1], cx)
-   auto ld = [&](unsigned off, bool on) { return (on && lane < mx) ? __ldg(vec + off + lane) : VNS_INT_INF; };
-   auto put = [&](unsigned off, int v) { if (lane < mp) vec[off + lane] = v; };
-   const int u1 = ld(vec_uw(vc, C, mp, 0, cx, l - 1), true), u2 = ld(vec_uw(vc, C, mp, 0, cx, max(l - 2, 0)), l >= 2);
-   const int w1 = ld(vec_uw(vc, C, mp, 1, cx, l), true), w2 = ld(vec_uw(vc, C, mp, 1, cx, min(l + 1, S)), l <= S - 1);
-   warp_stage_wait();
-   put(vec_pair(vc, C, mp, 0, x, l), vec_fwd(b1, mx, ml, u1, lane));                       // InsF(x,l)   from U(cx,l-1)
-   if (l >= 2) put(vec_pair(vc, C, mp, 2, x, l - 1), vec_fwd(b1, mx, ml, u2, lane));       // RepF(x,l-1) from U(cx,l-2)
-   put(vec_pair(vc, C, mp, 1, x, l), vec_bwd(b2, ma, mx, w1, lane));                       // InsB(x,l)   from W(cx,l)
-   if (l <= S - 1) put(vec_pair(vc, C, mp, 3, x, l), vec_bwd(b2, ma, mx, w2, lane));       // RepB(x,l)   from W(cx,l+1)
+   const int ml = lm.m(l), ma = lm.m(l - 1), ofl = lm.off(l), ofa = lm.off(l - 1);
+   for (int x = blockIdx.y + 1; x <= T; x += gridDim.y) {
+      const int cx = lm.cl(x), mx = lm.m(x), ox = lm.off(x);
+      warp_stage(b1, Dv + ((long long)ox * I.N + (long long)mx * ofl), mx * ml, lane);          // D(cx, lcl[l])
+      warp_stage(b2, Dv + ((long long)ofa * I.N + (long long)ma * ox), ma * mx, lane);          // D(lcl[l-1], cx)
+      auto ld = [&](unsigned off, bool on) { return (on && lane < mx) ? __ldg(vec + off + lane) : VNS_INT_INF; };
+      auto put = [&](unsigned off, int v) { if (lane < mp) vec[off + lane] = v; };
+      const int u1 = ld(vec_uw(vc, C, mp, 0, cx, l - 1), true), u2 = ld(vec_uw(vc, C, mp, 0, cx, max(l - 2, 0)), l >= 2);
+      const int w1 = ld(vec_uw(vc, C, mp, 1, cx, l), true), w2 = ld(vec_uw(vc, C, mp, 1, cx, min(l + 1, S)), l <= S - 1);
+      warp_stage_wait();
+      put(vec_pair(vc, C, mp, 0, x, l), vec_fwd(b1, mx, ml, u1, lane));                       // InsF(x,l)   from U(cx,l-1)
+      if (l >= 2) put(vec_pair(vc, C, mp, 2, x, l - 1), vec_fwd(b1, mx, ml, u2, lane));       // RepF(x,l-1) from U(cx,l-2)
+      put(vec_pair(vc, C, mp, 1, x, l), vec_bwd(b2, ma, mx, w1, lane));                       // InsB(x,l)   from W(cx,l)
+      if (l <= S - 1) put(vec_pair(vc, C, mp, 3, x, l), vec_bwd(b2, ma, mx, w2, lane));       // RepB(x,l)   from W(cx,l+1)
+      __syncwarp();   // the staged blocks are overwritten by the next x
+   }
 }
 
 // decoded candidate in endpoint-vector form

@@ -76,6 +76,7 @@ _SIGS = {
     "vnsgpu_path_get_dp": [vp, C.c_int, dp, dp, C.c_int],
     "vnsgpu_eval_batch": [vp, C.c_int, C.c_int64, vp, C.c_double, C.c_int, dp, dp, vp, C.POINTER(C.c_int64)],
     "vnsgpu_eval_batch_packed": [vp, C.c_int, C.c_int64, vp, C.c_double, C.c_int, dp, dp, vp, C.POINTER(C.c_int64)],
+    "vnsgpu_eval_batch_packed32": [vp, C.c_int, C.c_int64, vp, C.c_double, C.c_int, vp, vp, C.POINTER(C.c_int64)],
     "vnsgpu_eval_batch_dev": [vp, C.c_int, C.c_int64, vp, C.c_double, C.c_int, vp, vp, vp, vp, vp],
     "vnsgpu_gen_proposals": [vp, C.c_int, C.c_int, C.c_int64, C.POINTER(Rng), vp],
     "vnsgpu_cand_bytes": [vp, C.c_int, C.c_int64, vp, C.POINTER(C.c_int64)],
@@ -371,6 +372,29 @@ class VnsSopPath:
         self.e._ck(self.lib.vnsgpu_eval_batch_packed(self.e.h, self.h, n, pk.ctypes.data, budget, skip, _d(ln), _d(lb),
                                                      fl.ctypes.data, C.byref(first)))
         return ln, lb, fl, first.value
+
+    @staticmethod
+    def pack_cands32(cands):
+        """CAND_DTYPE array -> uint32 descriptors (vnsgpu_pack_cand32): indices < 16384, gain cluster either a or none."""
+        c = VnsSopPath.make_cands(cands)
+        g = c["gain_cluster"]
+        if not (((g == -1) | (g == c["a"])).all() and (c["a"] >= 0).all() and (c["b"] >= 0).all()
+                and (c["a"] < 16384).all() and (c["b"] < 16384).all()):
+            raise ValueError("candidates do not fit the 4-byte descriptor format")
+        u = lambda x: x.astype(np.int64).astype(np.uint32)
+        return np.ascontiguousarray((u(c["op"]) & np.uint32(7)) | (u(c["a"]) << np.uint32(3)) | (u(c["b"]) << np.uint32(17))
+                                    | (u(g >= 0) << np.uint32(31)))
+
+    def eval_batch_packed32(self, cands, budget=None, skip=1):
+        """Compact wire format on all-integer tables: 4-byte descriptors in, int32 lengths + flags out."""
+        pk = self.pack_cands32(cands)
+        n = len(pk)
+        ln, fl = np.empty(n, np.int32), np.zeros(n, np.uint8)
+        first = C.c_int64(-1)
+        budget = self.e.pb.budget if budget is None else budget
+        self.e._ck(self.lib.vnsgpu_eval_batch_packed32(self.e.h, self.h, n, pk.ctypes.data, budget, skip, ln.ctypes.data,
+                                                       fl.ctypes.data, C.byref(first)))
+        return ln, fl, first.value
 
     def _one(self, op, a, b):
         ln, lb, fl, _ = self.eval_batch(np.array([[op, a, b]], np.int32), budget=np.inf)
