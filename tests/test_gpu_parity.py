@@ -309,6 +309,58 @@ def test_eval_batch_both_arithmetic_paths_vs_oracle(name, int_path, golden, eng_
         e.set_vector_cache(True)
 
 
+@pytest.mark.parametrize("name", ["krob200", "opn_s08"])
+def test_host_call_graph_replay(name, golden, eng_cache):
+    """The host-buffer call with PINNED buffers becomes one CUDA graph launch from the third identical call on.
+    The graph must stay valid while the path's state changes on the device (the kernels read targets, T, F / B
+    there) and must be dropped when a buffer or the batch size changes: every call is compared with the
+    eager call on pageable buffers (bit-exact) through several local-search steps."""
+    import ctypes as C
+    import torch
+    from vns_sop_b200 import engine
+    e, sf, pb = eng_cache(name)
+    g, a = golden[name], load_arrays(name)
+    pg = e.path(a["greedy_vns"], g["greedy"]["T"])
+    rs = np.random.RandomState(11)
+    T = pg.getNumTargets()
+    base = random_candidates(rs, pg.vns, T, 20000)
+    cands = np.tile(base, (15, 1))                      # 300 000 >= the graph threshold
+    rs.shuffle(cands)
+    n = len(cands)
+    pk = torch.from_numpy(pg.pack_cands32(cands).view(np.int32).copy()).pin_memory()
+    h_len = torch.empty(n, dtype=torch.int32).pin_memory()
+    h_len2 = torch.empty(n, dtype=torch.int32).pin_memory()
+    h_fl = torch.empty(n, dtype=torch.uint8).pin_memory()
+    first = C.c_int64(-1)
+    rng = engine.seeded_rng(5)
+
+    def pinned_call(nn, out):
+        e._ck(e.lib.vnsgpu_eval_batch_packed32(e.h, pg.h, nn, C.c_void_p(pk.data_ptr()), pb.budget, 1,
+                                               C.c_void_p(out.data_ptr()), C.c_void_p(h_fl.data_ptr()), C.byref(first)))
+        return out.numpy()[:nn].copy(), h_fl.numpy()[:nn].copy(), first.value
+
+    l0 = e.launches
+    for it in range(6):
+        ln, fl, f1 = pinned_call(n, h_len)               # calls 0, 1 eager; 2.. replay the graph
+        rln, rlb, rfl, rf = pg.eval_batch(cands)         # pageable buffers: always eager
+        bad = (rfl & engine.F_BAD) != 0
+        assert (ln[~bad] == rln[~bad]).all() and (fl == rfl).all() and f1 == rf, (name, it)
+        assert (ln[bad] == np.iinfo(np.int32).min).all()
+        pg._ls(1 + it % 2, 40, rng, None, 1)             # the search moves on: T, targets, F / B change on the device
+    assert e.launches > l0                               # replays still count their kernels
+    # another output buffer, another batch size: the recorded graph must not be reused
+    ln, fl, f1 = pinned_call(n, h_len2)
+    rln, rlb, rfl, rf = pg.eval_batch(cands)
+    bad = (rfl & engine.F_BAD) != 0
+    assert (ln[~bad] == rln[~bad]).all() and (fl == rfl).all() and f1 == rf
+    m = n - 4099
+    for _ in range(4):
+        ln, fl, f1 = pinned_call(m, h_len2)
+    rln, rlb, rfl, rf = pg.eval_batch(cands[:m])
+    bad = (rfl & engine.F_BAD) != 0
+    assert (ln[~bad] == rln[~bad]).all() and (fl == rfl).all() and f1 == rf
+
+
 @pytest.mark.parametrize("S", [4, 8, 12])
 def test_dubins_table_known_answers(S):
     """a4: the Dubins kernel against the 98 784 entries shipped with the reference's DOP datasets

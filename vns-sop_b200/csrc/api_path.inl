@@ -235,10 +235,17 @@ static vnsgpu_status prepare_seg(vnsgpu_ctx *ctx, int path, cudaStream_t st)
    if (!ctx->d_segmeta) CK(cudaMalloc(&ctx->d_segmeta, sizeof(int) * 6 * R));
    k_seg_offsets<<<1, 256, sizeof(int) * 2 * R, st>>>(I, ctx->paths[path].d, ctx->d_segmeta);
    LAUNCHED(ctx);
-   const size_t smem = seg_build_smem(I.rows, I.mp);
-   if (smem <= (size_t)ctx->max_smem) {
-      if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k_seg_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      k_seg_build<<<std::min(I.rows, I.C + 2), VNS_SEG_THREADS, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta);
+   const int nst = I.mp <= 22 ? 16 : 8;                      // ring depth: <= 32 KB of staged table blocks
+   const size_t smem = seg_build_smem(I.rows, I.mp, nst);
+   if (smem <= (size_t)ctx->max_smem && I.mp <= 32 && I.N < 65536) {
+      const int grid = std::min(I.rows, I.C + 2);
+      if (nst == 16) {
+         if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k_seg_build<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+         k_seg_build<16><<<grid, VNS_SEG_THREADS, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta);
+      } else {
+         if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k_seg_build<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+         k_seg_build<8><<<grid, VNS_SEG_THREADS, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta);
+      }
    } else
       k_seg_build_g<<<I.rows, 128, 0, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta);
    LAUNCHED(ctx);
@@ -295,11 +302,13 @@ static vnsgpu_status launch_eval(vnsgpu_ctx *ctx, int path, int64_t n, int64_t i
          unsigned *hist = ctx->d_hist + (size_t)slot * 2 * nb, *cursor = hist + nb, *perm = ctx->d_perm + perm_off;
          const int sgrid = (int)std::min<int64_t>((n + 2047) / 2048, (int64_t)ctx->num_sms * 8);
          CK(cudaMemsetAsync(hist, 0, sizeof(unsigned) * nb, st));
-         k_sort_hist<<<sgrid, 256, sizeof(unsigned) * nb, st>>>(I, P, n, d_cands, nb, hist, useseg);
+         // endpoint vectors on a table beyond the caches: order the block candidates by product row (vec_sort_key)
+         const int sortmode = (useseg == 2 && (size_t)I.N * I.N * sizeof(int) > ((size_t)48 << 20)) ? 3 : useseg;
+         k_sort_hist<<<sgrid, 256, sizeof(unsigned) * nb, st>>>(I, P, n, d_cands, nb, hist, sortmode);
          LAUNCHED(ctx);
          k_sort_scan<<<1, 1024, 0, st>>>(nb, hist, cursor);
          LAUNCHED(ctx);
-         k_sort_scatter<<<sgrid, 256, sizeof(unsigned) * 2 * nb, st>>>(I, P, n, d_cands, nb, cursor, perm, useseg);
+         k_sort_scatter<<<sgrid, 256, sizeof(unsigned) * 2 * nb, st>>>(I, P, n, d_cands, nb, cursor, perm, sortmode);
          LAUNCHED(ctx);
          d_perm = perm;
       }
@@ -396,6 +405,14 @@ __global__ void __launch_bounds__(256) k_unpack_cands(long long n, const unsigne
    }
 }
 
+static bool host_pinned(const void *p)
+{
+   if (!p) return true;
+   cudaPointerAttributes at;
+   if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+   return at.type == cudaMemoryTypeHost;
+}
+
 // 4-byte descriptors (vnsgpu_pack_cand32): op 3 bits, a 14 bits, b 14 bits, bit 31 = the gain cluster is a
 __global__ void __launch_bounds__(256) k_unpack_cands32(long long n, const unsigned *__restrict__ src, vnsgpu_cand *__restrict__ dst)
 {
@@ -446,6 +463,8 @@ static vnsgpu_status eval_batch_host(vnsgpu_ctx *ctx, int path, int64_t n, const
          CK(cudaEventCreateWithFlags(&ctx->ev_k[k], cudaEventDisableTiming));
       }
       CK(cudaEventCreateWithFlags(&ctx->ev_start, cudaEventDisableTiming));
+      CK(cudaEventCreateWithFlags(&ctx->ev_out, cudaEventDisableTiming));
+      if (const char *e = getenv("VNSGPU_HOST_GRAPH")) ctx->use_graph = atoi(e) != 0;
    }
    // Chunk schedule.  The kernel is the slower stage (PCIe moves a candidate's 16 B in and 9-17 B out faster
    // than it is evaluated), and it is most efficient on large chunks (one sort + launch ramp per chunk): a
@@ -470,49 +489,100 @@ static vnsgpu_status eval_batch_host(vnsgpu_ctx *ctx, int path, int64_t n, const
    }
    cudaStream_t sk = ctx->stream;
    const int useseg = eval_mode(ctx, n);
-   s = prepare_eval(ctx, path, useseg, sk);
-   if (s) return s;
-   CK(cudaMemsetAsync(ctx->d_first, 0xFF, sizeof(long long), sk));
-   CK(cudaEventRecord(ctx->ev_start, sk));          // order behind whatever the caller queued before
-   CK(cudaStreamWaitEvent(ctx->s_in, ctx->ev_start, 0));
-   CK(cudaStreamWaitEvent(ctx->s_out, ctx->ev_start, 0));
-   int64_t lo = 0;
-   for (int c = 0; c < (int)cut.size(); lo += cut[c], ++c) {
-      const int64_t cn = cut[c];
-      if (packed == 2)
-         CK(cudaMemcpyAsync(d_pk32 + lo, (const unsigned *)src + lo, sizeof(unsigned) * cn, cudaMemcpyHostToDevice, ctx->s_in));
-      else if (packed)
-         CK(cudaMemcpyAsync(d_pk + lo, (const unsigned long long *)src + lo, sizeof(unsigned long long) * cn, cudaMemcpyHostToDevice, ctx->s_in));
-      else
-         CK(cudaMemcpyAsync(d_c + lo, (const vnsgpu_cand *)src + lo, sizeof(vnsgpu_cand) * cn, cudaMemcpyHostToDevice, ctx->s_in));
-      CK(cudaEventRecord(ctx->ev_in[c], ctx->s_in));
-      CK(cudaStreamWaitEvent(sk, ctx->ev_in[c], 0));
-      if (packed) {
-         const int ug = (int)std::min<int64_t>((cn + 255) / 256, (int64_t)ctx->num_sms * 8);
-         if (packed == 2) k_unpack_cands32<<<ug, 256, 0, sk>>>(cn, d_pk32 + lo, d_c + lo);
-         else k_unpack_cands<<<ug, 256, 0, sk>>>(cn, d_pk + lo, d_c + lo);
-         LAUNCHED(ctx);
-      }
-      s = launch_eval(ctx, path, cn, lo, d_c + lo, budget, skip, (len || len_i32) ? d_len + lo : nullptr, lb ? d_lb + lo : nullptr,
-                      flags ? d_fl + lo : nullptr, (unsigned long long *)ctx->d_first, sk, c, lo, useseg);
-      if (s) return s;
-      if (len_i32) {
-         k_len_to_i32<<<(int)std::min<int64_t>((cn + 255) / 256, (int64_t)ctx->num_sms * 8), 256, 0, sk>>>(cn, d_len + lo, d_li + lo);
-         LAUNCHED(ctx);
-      }
-      CK(cudaEventRecord(ctx->ev_k[c], sk));
-      CK(cudaStreamWaitEvent(ctx->s_out, ctx->ev_k[c], 0));
-      if (len_i32) CK(cudaMemcpyAsync(len_i32 + lo, d_li + lo, sizeof(int) * cn, cudaMemcpyDeviceToHost, ctx->s_out));
-      if (len) CK(cudaMemcpyAsync(len + lo, d_len + lo, sizeof(double) * cn, cudaMemcpyDeviceToHost, ctx->s_out));
-      if (lb) CK(cudaMemcpyAsync(lb + lo, d_lb + lo, sizeof(double) * cn, cudaMemcpyDeviceToHost, ctx->s_out));
-      if (flags) CK(cudaMemcpyAsync(flags + lo, d_fl + lo, cn, cudaMemcpyDeviceToHost, ctx->s_out));
+   if (!ctx->h_first) CK(cudaMallocHost(&ctx->h_first, sizeof(long long)));
+
+   // The call is ~100 stream operations (6 chunks x copies, events, 8 kernels).  A caller that repeats it with the
+   // same buffers and batch size - a solver evaluating one neighbourhood batch per search state - gets it as ONE
+   // CUDA graph launch from the third identical call on (the second one records it): the key is every pointer and
+   // size the operations bake in.  The path's state (targets, T, F / B) is read by the kernels on the device, so the
+   // graph stays valid while the search moves on.  Pageable host buffers and VNSGPU_HOST_GRAPH=0 keep the eager form.
+   HostGraphKey key;
+   memset(&key, 0, sizeof(key));
+   key.I = ctx->I; key.P = ctx->paths[path].d;
+   key.src = src; key.len = len; key.lb = lb; key.flags = flags; key.leni = len_i32;
+   key.scratch = ctx->d_scratch; key.D32 = ctx->d_D32; key.vec = ctx->d_vec; key.veclb = ctx->d_veclb;
+   key.segmeta = ctx->d_segmeta; key.hist = ctx->d_hist; key.perm = ctx->d_perm; key.sk = sk;
+   key.n = n; key.budget = budget; key.skip = skip; key.packed = packed; key.mode = useseg;
+   key.sort = ctx->sort_batches; key.use_int = ctx->use_int; key.G = ctx->group_lanes; key.perm_cap = ctx->perm_cap;
+   auto finish = [&]() -> vnsgpu_status {
+      CK(cudaStreamSynchronize(sk));
+      if (first_accept) *first_accept = (int64_t)*ctx->h_first;
+      return VNSGPU_OK;
+   };
+   if (ctx->hg_exec && memcmp(&key, &ctx->hg_key, sizeof(key)) == 0) {
+      CK(cudaGraphLaunch(ctx->hg_exec, sk));
+      ctx->launches += ctx->hg_launches;
+      return finish();
    }
-   long long first = -1;
-   CK(cudaMemcpyAsync(&first, ctx->d_first, sizeof(first), cudaMemcpyDeviceToHost, sk));
-   CK(cudaStreamSynchronize(sk));
-   CK(cudaStreamSynchronize(ctx->s_out));
-   if (first_accept) *first_accept = (int64_t)first;
-   return VNSGPU_OK;
+   if (ctx->hg_exec) { cudaGraphExecDestroy(ctx->hg_exec); ctx->hg_exec = nullptr; }
+   bool capture = ctx->use_graph && ctx->hg_seen && memcmp(&key, &ctx->hg_last, sizeof(key)) == 0 && n >= 262144 &&
+                  host_pinned(src) && host_pinned(len) && host_pinned(lb) && host_pinned(flags) && host_pinned(len_i32);
+   ctx->hg_last = key; ctx->hg_seen = true;
+   if (capture && cudaStreamBeginCapture(sk, cudaStreamCaptureModeRelaxed) != cudaSuccess) { cudaGetLastError(); capture = false; }
+   const int64_t launches0 = ctx->launches;
+
+   auto issue = [&]() -> vnsgpu_status {
+      vnsgpu_status s = prepare_eval(ctx, path, useseg, sk);
+      if (s) return s;
+      CK(cudaMemsetAsync(ctx->d_first, 0xFF, sizeof(long long), sk));
+      CK(cudaEventRecord(ctx->ev_start, sk));          // order behind whatever the caller queued before
+      CK(cudaStreamWaitEvent(ctx->s_in, ctx->ev_start, 0));
+      CK(cudaStreamWaitEvent(ctx->s_out, ctx->ev_start, 0));
+      int64_t lo = 0;
+      for (int c = 0; c < (int)cut.size(); lo += cut[c], ++c) {
+         const int64_t cn = cut[c];
+         if (packed == 2)
+            CK(cudaMemcpyAsync(d_pk32 + lo, (const unsigned *)src + lo, sizeof(unsigned) * cn, cudaMemcpyHostToDevice, ctx->s_in));
+         else if (packed)
+            CK(cudaMemcpyAsync(d_pk + lo, (const unsigned long long *)src + lo, sizeof(unsigned long long) * cn, cudaMemcpyHostToDevice, ctx->s_in));
+         else
+            CK(cudaMemcpyAsync(d_c + lo, (const vnsgpu_cand *)src + lo, sizeof(vnsgpu_cand) * cn, cudaMemcpyHostToDevice, ctx->s_in));
+         CK(cudaEventRecord(ctx->ev_in[c], ctx->s_in));
+         CK(cudaStreamWaitEvent(sk, ctx->ev_in[c], 0));
+         if (packed) {
+            const int ug = (int)std::min<int64_t>((cn + 255) / 256, (int64_t)ctx->num_sms * 8);
+            if (packed == 2) k_unpack_cands32<<<ug, 256, 0, sk>>>(cn, d_pk32 + lo, d_c + lo);
+            else k_unpack_cands<<<ug, 256, 0, sk>>>(cn, d_pk + lo, d_c + lo);
+            LAUNCHED(ctx);
+         }
+         s = launch_eval(ctx, path, cn, lo, d_c + lo, budget, skip, (len || len_i32) ? d_len + lo : nullptr, lb ? d_lb + lo : nullptr,
+                         flags ? d_fl + lo : nullptr, (unsigned long long *)ctx->d_first, sk, c, lo, useseg);
+         if (s) return s;
+         if (len_i32) {
+            k_len_to_i32<<<(int)std::min<int64_t>((cn + 255) / 256, (int64_t)ctx->num_sms * 8), 256, 0, sk>>>(cn, d_len + lo, d_li + lo);
+            LAUNCHED(ctx);
+         }
+         CK(cudaEventRecord(ctx->ev_k[c], sk));
+         CK(cudaStreamWaitEvent(ctx->s_out, ctx->ev_k[c], 0));
+         if (len_i32) CK(cudaMemcpyAsync(len_i32 + lo, d_li + lo, sizeof(int) * cn, cudaMemcpyDeviceToHost, ctx->s_out));
+         if (len) CK(cudaMemcpyAsync(len + lo, d_len + lo, sizeof(double) * cn, cudaMemcpyDeviceToHost, ctx->s_out));
+         if (lb) CK(cudaMemcpyAsync(lb + lo, d_lb + lo, sizeof(double) * cn, cudaMemcpyDeviceToHost, ctx->s_out));
+         if (flags) CK(cudaMemcpyAsync(flags + lo, d_fl + lo, cn, cudaMemcpyDeviceToHost, ctx->s_out));
+      }
+      CK(cudaMemcpyAsync(ctx->h_first, ctx->d_first, sizeof(long long), cudaMemcpyDeviceToHost, sk));
+      CK(cudaEventRecord(ctx->ev_out, ctx->s_out));         // join the D2H stream (the H2D stream is joined by ev_in)
+      CK(cudaStreamWaitEvent(sk, ctx->ev_out, 0));
+      return VNSGPU_OK;
+   };
+   s = issue();
+   if (capture) {
+      cudaGraph_t g = nullptr;
+      const cudaError_t e = cudaStreamEndCapture(sk, &g);
+      if (s || e != cudaSuccess || !g) {
+         cudaGetLastError();
+         if (g) cudaGraphDestroy(g);
+         if (!s) { ctx->err = std::string("cudaStreamEndCapture: ") + cudaGetErrorString(e); s = VNSGPU_E_CUDA; }
+         return s;
+      }
+      const cudaError_t ei = cudaGraphInstantiate(&ctx->hg_exec, g, 0);
+      cudaGraphDestroy(g);
+      if (ei != cudaSuccess) { ctx->hg_exec = nullptr; ctx->err = std::string("cudaGraphInstantiate: ") + cudaGetErrorString(ei); return VNSGPU_E_CUDA; }
+      ctx->hg_key = key;
+      ctx->hg_launches = ctx->launches - launches0;
+      CK(cudaGraphLaunch(ctx->hg_exec, sk));
+   } else if (s)
+      return s;
+   return finish();
 }
 
 vnsgpu_status vnsgpu_eval_batch(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *cands, double budget, int skip, double *len,

@@ -394,25 +394,30 @@ k_eval_groups(InstDev I, const V *__restrict__ Dv, PathDev P, SegCache seg, long
    if (d_first && best != ULLONG_MAX) atomicMin(d_first, best);
 }
 
-// sort key of the endpoint-vector kernel: candidates with a block step first
-__device__ __forceinline__ int vec_sort_key(int T, int C, const int4 &cd)
+// sort key of the endpoint-vector kernel: candidates with a block step first.  byrow (tables beyond the caches):
+// block candidates are ordered by the first layer la of their untouched run - the products M(la, .) are one contiguous
+// row of at most (S - la) blocks, so the candidates a wave of CTAs works on share a few L2-resident rows instead of
+// gathering 4 KB blocks from all over HBM (ncu, 33 GB table: 5.8 GB of DRAM reads per 4 Mi candidates before)
+__device__ __forceinline__ int vec_sort_key(int T, int C, const int4 &cd, bool byrow)
 {
    const int op = cd.x, a = cd.y, b = cd.z;
    if (op == VNSGPU_OP_MOVE) {
       if (a >= T || a < 0 || b > T || b < 0 || abs(b - a) < 2) return 0;
-      return b > a ? (b - a > 2 ? 1 : 0) : 1;     // up: layers i+1 .. j-1 = a+2 .. b;  down: always >= one block
+      const int blk = b > a ? (b - a > 2 ? 1 : 0) : 1;     // up: layers i+1 .. j-1 = a+2 .. b;  down: always >= one block
+      return byrow && blk ? 1 + min(a, b) + (b > a ? 2 : 1) : blk;
    }
    if (op == VNSGPU_OP_EXCHANGE) {
       if (a >= T || a < 0 || b >= T || b < 0 || abs(a - b) < 2) return 0;
-      return abs(a - b) > 2 ? 1 : 0;              // layers p+1 .. q-1
+      const int blk = abs(a - b) > 2 ? 1 : 0;              // layers p+1 .. q-1
+      return byrow && blk ? 1 + min(a, b) + 2 : blk;
    }
    return 0;
 }
 
-// useseg: 0 block by block, 1 segment products, 2 endpoint vectors (vec.cuh)
+// useseg: 0 block by block, 1 segment products, 2 endpoint vectors (vec.cuh), 3 endpoint vectors ordered by product row
 __device__ __forceinline__ int sort_key(int T, int C, const int4 &cd, int useseg)
 {
-   if (useseg == 2) return vec_sort_key(T, C, cd);
+   if (useseg >= 2) return vec_sort_key(T, C, cd, useseg == 3);
    return useseg ? decode_cand_seg(T, C, cd.x, cd.y, cd.z).K : decode_cand(T, C, cd.x, cd.y, cd.z).K;
 }
 
@@ -542,19 +547,21 @@ __global__ void __launch_bounds__(128) k_seg_build_g(InstDev I, PathDev P, int *
    }
 }
 
-// The same recurrence with the running product in shared memory and the table blocks of the next three steps in
-// flight (cp.async ring of four).  Row i of M(a,b) depends on row i of M(a,b-1) only, so the rows are independent
+// The same recurrence with the running product in shared memory and the table blocks of the next NST - 1 steps in
+// flight (cp.async ring of NST).  Row i of M(a,b) depends on row i of M(a,b-1) only, so the rows are independent
 // chains: warp w of the 8 owns rows w, w+8, w+16, w+24 (lane = column), keeps them in its own slice of shared memory
 // (read back as broadcast 16-byte loads: four k per load) and needs no barrier for them; the one barrier per step
 // publishes the staged table block.  The chain of block a has S - a - 1 dependent steps; block 0's chain is the
-// kernel's duration (the first version spread every product over the whole CTA: 6 us per step, this one ~0.5 us).
-// Needs mp <= 32.  dynamic shared memory: seg_build_smem(rows, mp) bytes
+// kernel's duration, and a step cannot be shorter than (memory latency) / (NST - 1): on HBM-resident tables the
+// ring of four of the first version (three steps ahead) held every step at ~1-2 us, hence 8 / 16 stages.
+// Needs mp <= 32 and N < 65536 (group_kernel_ok).  dynamic shared memory: seg_build_smem(rows, mp, NST) bytes
 #define VNS_SEG_THREADS 256
-__host__ __device__ inline size_t seg_build_smem(int rows, int mp)
+__host__ __device__ inline size_t seg_build_smem(int rows, int mp, int nst)
 {
-   return sizeof(int) * ((size_t)((2 * (rows + 3) + 3) & ~3) + (size_t)4 * ((mp * mp + 3) & ~3) + (size_t)32 * 32);
+   return sizeof(int) * ((size_t)(((rows + 3) + 3) & ~3) + (size_t)nst * ((mp * mp + 3) & ~3) + (size_t)32 * 32);
 }
 
+template <int NST>
 __global__ void __launch_bounds__(VNS_SEG_THREADS) k_seg_build(InstDev I, PathDev P, int *Dv, const int *meta)
 {
    extern __shared__ __align__(16) int smem_i[];
@@ -562,12 +569,12 @@ __global__ void __launch_bounds__(VNS_SEG_THREADS) k_seg_build(InstDev I, PathDe
    const int T = P.hdr[HDR_T], S = T + 1, R = I.rows + 3, mp2 = (I.mp * I.mp + 3) & ~3;
    const int a = blockIdx.x;
    if (a + 2 > S) return;
-   int *l_m = smem_i, *l_off = smem_i + R;                  // per layer l >= a: cluster size, first sample
-   int *dblk = smem_i + ((2 * R + 3) & ~3);                  // ring of 4 table blocks
-   int *prow = dblk + 4 * mp2;                               // 32 rows x 32 of the running product (INF beyond its columns)
+   unsigned short *l_m = reinterpret_cast<unsigned short *>(smem_i), *l_off = l_m + R;   // per layer l >= a: cluster size, first sample
+   int *dblk = smem_i + ((R + 3) & ~3);                      // ring of NST table blocks
+   int *prow = dblk + NST * mp2;                             // 32 rows x 32 of the running product (INF beyond its columns)
    for (int l = a + threadIdx.x; l <= S; l += blockDim.x) {
       const int c = layer_cluster(I, P.tg, T, l);
-      l_m[l] = I.m[c]; l_off[l] = I.off[c];
+      l_m[l] = (unsigned short)I.m[c]; l_off[l] = (unsigned short)I.off[c];
    }
    __syncthreads();
    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -578,12 +585,18 @@ __global__ void __launch_bounds__(VNS_SEG_THREADS) k_seg_build(InstDev I, PathDe
       if (l < S) {
          const int *src = Dv + ((long long)l_off[l] * I.N + (long long)l_m[l] * l_off[l + 1]);
          const int n = l_m[l] * l_m[l + 1];
-         for (int e = threadIdx.x; e < n; e += blockDim.x)
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(dst + e)), "l"(src + e));
+         const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
+         if ((((unsigned)(size_t)src) & 15u) == 0 && (n & 3) == 0) {     // block-uniform: 16-byte copies
+            for (int e = threadIdx.x * 4; e < n; e += VNS_SEG_THREADS * 4)
+               asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d + 4u * e), "l"(src + e));
+         } else {
+            for (int e = threadIdx.x; e < n; e += VNS_SEG_THREADS)
+               asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + 4u * e), "l"(src + e));
+         }
       }
       asm volatile("cp.async.commit_group;");
    };
-   for (int b = a + 2; b <= a + 4; ++b) fetch(dblk + (b & 3) * mp2, b - 1);   // step b multiplies by D(b-1,b)
+   for (int b = a + 2; b <= a + NST; ++b) fetch(dblk + (b % NST) * mp2, b - 1);   // step b multiplies by D(b-1,b)
    {   // M(a,a+1) = D(a,a+1): this warp's rows
       const int m1 = l_m[a + 1];
       const int *src = Dv + ((long long)l_off[a] * I.N + (long long)ma * l_off[a + 1]);
@@ -595,11 +608,11 @@ __global__ void __launch_bounds__(VNS_SEG_THREADS) k_seg_build(InstDev I, PathDe
       __syncwarp();
    }
    for (int b = a + 2; b <= S; ++b) {
-      asm volatile("cp.async.wait_group 2;");               // all but the blocks of steps b+1, b+2 have landed
+      asm volatile("cp.async.wait_group %0;" ::"n"(NST - 2));   // all but the blocks of the NST - 2 steps ahead have landed
       __syncthreads();
-      fetch(dblk + ((b + 3) & 3) * mp2, b + 2);              // that buffer was read by step b-1
+      fetch(dblk + ((b + NST - 1) % NST) * mp2, b + NST - 2);   // that buffer was read by step b-1
       const int mk = l_m[b - 1], mb = l_m[b];
-      const int *d = dblk + (b & 3) * mp2 + min(lane, mb - 1);
+      const int *d = dblk + (b % NST) * mp2 + min(lane, mb - 1);
       int acc[4] = {INF, INF, INF, INF};
       for (int k4 = 0; k4 < mk; k4 += 4) {
          const int d0 = d[k4 * mb], d1 = d[min(k4 + 1, mk - 1) * mb], d2 = d[min(k4 + 2, mk - 1) * mb], d3 = d[min(k4 + 3, mk - 1) * mb];

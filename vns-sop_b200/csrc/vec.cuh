@@ -356,8 +356,8 @@ k_eval_vec(InstDev I, const int *__restrict__ Dv, PathDev P, SegCache seg, VecCa
 #pragma unroll
          for (int r = 0; r < NR; ++r) {
             const int j = gl + r * G;
-            vA[r] = j < mA ? __ldg(vc.vec + offA + j) : INF;
-            vB[r] = j < mB ? __ldg(vc.vec + offB + j) : INF;
+            vA[r] = j < mA ? __ldg(vc.vec + (offA + (unsigned)j)) : INF;      // one 32-bit add, then base + 4 * index
+            vB[r] = j < mB ? __ldg(vc.vec + (offB + (unsigned)j)) : INF;
          }
          if ((pk >> 25) & 1) {                                 // warp-uniform: some group of this iteration has a block
             const int trip = blk ? mA : 1, nvalid = blk ? mB : 1;
@@ -381,10 +381,22 @@ k_eval_vec(InstDev I, const int *__restrict__ Dv, PathDev P, SegCache seg, VecCa
 #pragma unroll
                            for (int t = 0; t < G; ++t) acc[rd] = __viaddmin_s32(__shfl_sync(FULL, opnd, min(t, tlim), G), dd[t], acc[rd]);
                         } else {
-#pragma unroll 2
-                           for (int t = 0; t < tm; ++t) {
-                              const int tt = min(t, tlim);
-                              acc[rd] = __viaddmin_s32(__shfl_sync(FULL, opnd, tt, G), __ldg(blkp + (sb + (unsigned)(tt * nvalid))), acc[rd]);
+                           // cache-resident tables: eight unrolled steps at a time, rows unclamped - per step one
+                           // IMAD.WIDE (row address), LDG, SHFL with an immediate lane and VIADDMNMX, the eight loads
+                           // in flight together.  Rows beyond this group's block pair a sample that is INF (vA beyond
+                           // mA) with whatever follows the block: table entries, products or the zeroed rest of the
+                           // allocation, all in [0, 2^29), so INF + it neither wraps nor wins the min
+                           const char *prow = reinterpret_cast<const char *>(blkp + (cbase + (unsigned)(rs * G * nvalid)));
+                           const unsigned stride = 4u * (unsigned)nvalid;      // bytes per row
+#pragma unroll
+                           for (int t0 = 0; t0 < G; t0 += 8) {
+                              if (t0 == 0 || t0 < tm) {                // warp-uniform
+                                 int dd[8];
+#pragma unroll
+                                 for (int t = 0; t < 8; ++t) dd[t] = __ldg(reinterpret_cast<const int *>(prow + (unsigned long long)stride * (unsigned)(t0 + t)));
+#pragma unroll
+                                 for (int t = 0; t < 8; ++t) acc[rd] = __viaddmin_s32(__shfl_sync(FULL, opnd, t0 + t, G), dd[t], acc[rd]);
+                              }
                            }
                         }
                      }

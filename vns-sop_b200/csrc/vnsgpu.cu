@@ -29,6 +29,18 @@ struct PathHost {
    PathDev d{};
 };
 
+// everything the stream operations of the host-buffer evaluation call bake in (see eval_batch_host)
+struct HostGraphKey {
+   InstDev I;
+   PathDev P;
+   const void *src, *len, *lb, *flags, *leni, *scratch, *D32, *vec, *veclb, *segmeta, *hist, *perm;
+   cudaStream_t sk;
+   int64_t n;
+   double budget;
+   size_t perm_cap;
+   int skip, packed, mode, sort, use_int, G;
+};
+
 struct vnsgpu_ctx {
    int device = 0;
    cudaStream_t own = nullptr, stream = nullptr;
@@ -70,6 +82,13 @@ struct vnsgpu_ctx {
    int num_sms = 148;
    int max_smem = 48 * 1024;      // opt-in shared memory per block
    bool use_smem_chain = true;    // vnsgpu_set_smem_chain
+   // the host-buffer evaluation call as a CUDA graph (eval_batch_host)
+   bool use_graph = true, hg_seen = false;
+   HostGraphKey hg_key, hg_last;
+   cudaGraphExec_t hg_exec = nullptr;
+   int64_t hg_launches = 0;
+   long long *h_first = nullptr;  // pinned
+   cudaEvent_t ev_out = nullptr;
 };
 
 #define CK(call)                                                                                   \
@@ -159,10 +178,12 @@ void vnsgpu_destroy(vnsgpu_ctx *ctx)
    cudaFree(ctx->d_scratch); cudaFree(ctx->d_rng); cudaFree(ctx->d_stats); cudaFree(ctx->d_first);
    cudaFree(ctx->d_res); cudaFree(ctx->d_info); cudaFree(ctx->d_prof); cudaFree(ctx->d_stop);
    if (ctx->s_in) {
-      cudaStreamDestroy(ctx->s_in); cudaStreamDestroy(ctx->s_out); cudaEventDestroy(ctx->ev_start);
+      cudaStreamDestroy(ctx->s_in); cudaStreamDestroy(ctx->s_out); cudaEventDestroy(ctx->ev_start); cudaEventDestroy(ctx->ev_out);
       for (int k = 0; k < VNS_PIPE_EVENTS; ++k) { cudaEventDestroy(ctx->ev_in[k]); cudaEventDestroy(ctx->ev_k[k]); }
    }
    if (ctx->own) cudaStreamDestroy(ctx->own);
+   if (ctx->hg_exec) cudaGraphExecDestroy(ctx->hg_exec);
+   if (ctx->h_first) cudaFreeHost(ctx->h_first);
    delete ctx;
 }
 
@@ -295,10 +316,14 @@ static vnsgpu_status build_table(vnsgpu_ctx *ctx, TableJob J, bool maybe_int)
    if (ctx->d_D32) { CK(cudaFree(ctx->d_D32)); ctx->d_D32 = nullptr; }
    if (maybe_int) {   // optimistic: the copy is dropped again if the classification says no
       ctx->seg_ok = true;                                  // block offsets are 64-bit
-      if (cudaMalloc(&ctx->d_D32, sizeof(int) * (size_t)(nn + (ctx->seg_ok ? segcap : 0)) + 64) != cudaSuccess) {
+      // + 8 KB: k_eval_vec lets a row pointer run up to 31 rows past a block.  Everything behind the table is zeroed
+      // once, so that such a read always finds a number in [0, 2^29) (zero, or a product of an earlier path state)
+      const size_t extra = sizeof(int) * (size_t)(ctx->seg_ok ? segcap : 0) + 8192;
+      if (cudaMalloc(&ctx->d_D32, sizeof(int) * (size_t)nn + extra) != cudaSuccess) {
          cudaGetLastError();
          ctx->d_D32 = nullptr;
-      }
+      } else
+         CK(cudaMemsetAsync(ctx->d_D32 + nn, 0, extra, ctx->stream));
    }
    CK(cudaMemsetAsync(ctx->d_info, 0, 2 * sizeof(unsigned long long), ctx->stream));
    J.D = ctx->d_D; J.Di = ctx->d_D32; J.dmin = ctx->d_dmin; J.dmax = ctx->d_dmax; J.info = ctx->d_info;
