@@ -74,7 +74,8 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-solve", action="store_true", help="skip the time-to-reward leg")
-    ap.add_argument("--vector-cache", type=int, default=1, help="vnsgpu_set_vector_cache: 0 off, 1 auto (batch >= C^2), 2 always")
+    ap.add_argument("--vector-cache", type=int, default=1, help="vnsgpu_set_vector_cache: 0 off, 1 auto (batch >= C^2 / 4), 2 always")
+    ap.add_argument("--batch-sort", type=int, default=-1, help="vnsgpu_set_batch_sort: 0 off, 1 on, -1 library default (experiments)")
     ap.add_argument("--no-solve-cpu", action="store_true", help="time-to-reward: skip the reference binary runs (long on vm1084)")
     ap.add_argument("--sweep", action="store_true", help="candidate-batch sweep 2^10 .. --batch (x4 steps), device-resident (BASELINE config 5)")
     ap.add_argument("--multi-start", type=int, default=148, help="seeds of the multi-start leg (0 = skip)")
@@ -289,19 +290,26 @@ class ClockSampler:
             except OSError:
                 self.proc = None
 
-    def _poll(self):
+    def sample_now(self):
+        """One NVML sample from the calling thread: bench.py takes them while the timed steps are queued on the
+        device (a 7 ms timed region can fall between two polls of the background thread)."""
         nv = self.nv
-        while not self.stop_flag:
+        if nv is None:
+            return
+        try:
+            mhz = float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
             try:
-                mhz = float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
-                try:
-                    mask = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
-                except Exception:
-                    mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
-                self.rows.append((time.perf_counter(), mhz, {k for k, bit in self.NAMES.items() if mask & bit}))
+                mask = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
             except Exception:
-                pass
-            time.sleep(0.005)
+                mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+            self.rows.append((time.perf_counter(), mhz, {k for k, bit in self.NAMES.items() if mask & bit}))
+        except Exception:
+            pass
+
+    def _poll(self):
+        while not self.stop_flag:
+            self.sample_now()
+            time.sleep(0.002)
 
     def _read(self):
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
@@ -321,12 +329,31 @@ class ClockSampler:
             reasons |= r[2]
         return {"sm_mhz": float(np.median([r[1] for r in rows])) if rows else None, "sm_max_mhz": self.max_mhz,
                 "reasons": sorted(reasons), "samples": len(rows),
-                "source": "nvml, 5 ms period" if self.nv else "nvidia-smi -lms 100"}
+                "source": "nvml, 2 ms period + samples taken while the timed steps are queued" if self.nv else "nvidia-smi -lms 100"}
 
     def stop(self):
         self.stop_flag = True
         if self.proc:
             self.proc.terminate()
+
+
+def ncu_cache_level(workload, batch):
+    """Which memory level the dominant kernel saturates, from the same committed capture (percent of that unit's peak):
+    for a cache-resident table the HBM fraction says nothing - the binding roof is the L1 data pipe (LSU wavefronts)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as fh:
+            for t in json.load(fh)["entries"]:
+                if t.get("workload") == workload and int(t.get("batch", -1)) == batch and t.get("l1tex_throughput_pct") is not None:
+                    lv = {"l1tex": t.get("l1tex_throughput_pct"), "lsu_wavefronts": t.get("lsu_wavefronts_pct"),
+                          "l2": t.get("l2_throughput_pct"), "dram": t.get("dram_throughput_pct"), "issue_active": t.get("issue_active_pct")}
+                    top = max((k for k in ("l1tex", "l2", "dram") if lv[k] is not None), key=lambda k: lv[k])
+                    return {"binding_level": top, "pct_of_peak": lv, "l1_hit_pct": t.get("l1_hit_pct"),
+                            "kernel_us_under_ncu": t.get("kernel_us_under_ncu"), "capture": t.get("capture"),
+                            "what": "ncu --set full: throughput of each memory level as a percentage of its own peak for one launch "
+                                    "of the dominant kernel at this batch size"}
+    except (OSError, ValueError, KeyError):
+        pass
+    return None
 
 
 def ncu_traffic(workload, batch):
@@ -406,6 +433,8 @@ def run_b200(args):
         eng = engine.Engine(local).load_problem(pb)
     lib = eng.lib
     eng.set_vector_cache(args.vector_cache)
+    if args.batch_sort >= 0:
+        eng.set_batch_sort(bool(args.batch_sort))
     state = workload_state(args.workload, pb)
     p = prepare_gpu_state(eng, state)
     vns, T = p.vns, p.getNumTargets()
@@ -472,11 +501,15 @@ def run_b200(args):
         l0 = eng.launches
         t_host0 = time.perf_counter()
         e0.record(stream)
-        for a, b in ev:
+        for i, (a, b) in enumerate(ev):
             a.record(stream)
             step()
             b.record(stream)
+            if sampler and i == K // 2:
+                sampler.sample_now()
         e1.record(stream)
+        if sampler:
+            sampler.sample_now()          # the device is still working through the queued steps
         barrier()
         t_host1 = time.perf_counter()
         launches = eng.launches - l0
@@ -534,8 +567,13 @@ def run_b200(args):
             h_pk32.numpy()[:] = p.pack_cands32(cands).view(np.int32)
             h_len32 = torch.empty(n, dtype=torch.int32).pin_memory()
 
+        h_res = torch.empty(n, dtype=torch.int32).pin_memory() if int_path else None
+
         def host_step(packed=1):
-            if packed == 2:
+            if packed == 3:     # 4 B descriptors in, ONE 4 B result word (length | flags << 29) out
+                eng._ck(lib.vnsgpu_eval_batch_packed32r(eng.h, p.h, n, C.c_void_p(h_pk32.data_ptr()), pb.budget, 1,
+                                                        C.c_void_p(h_res.data_ptr()), C.byref(first)))
+            elif packed == 2:
                 eng._ck(lib.vnsgpu_eval_batch_packed32(eng.h, p.h, n, C.c_void_p(h_pk32.data_ptr()), pb.budget, 1,
                                                        C.c_void_p(h_len32.data_ptr()), C.c_void_p(h_fl.data_ptr()), C.byref(first)))
             elif packed:    # 8-byte descriptors (vnsgpu_pack_cand): half the host-to-device bytes
@@ -568,17 +606,26 @@ def run_b200(args):
         sub8 = {"value": world * n * K / dt8, "ms_per_step": 1e3 * dt8 / K, "call": "vnsgpu_eval_batch_packed",
                 "h2d_bytes_per_step": world * n * 8, "d2h_bytes_per_step": world * (n * 9 + 8)}
         if int_path:
-            dt, nl = timed(2)
+            dt5, _ = timed(2)
+            first5 = first.value
+            sub5 = {"value": world * n * K / dt5, "ms_per_step": 1e3 * dt5 / K, "call": "vnsgpu_eval_batch_packed32",
+                    "h2d_bytes_per_step": world * n * 4, "d2h_bytes_per_step": world * (n * 5 + 8)}
+            dt, nl = timed(3)
             launches += nl
-            in_b, out_b = 4, 5
+            in_b, out_b = 4, 4
             e2e = {"value": world * n * K / dt, "unit": "evals/s", "h2d_bytes_per_step": world * n * 4,
-                   "d2h_bytes_per_step": world * (n * 5 + 8), "ms_per_step": 1e3 * dt / K,
-                   "call": "vnsgpu_eval_batch_packed32 (pinned host buffers: 4 B descriptors in; int32 lengths - exact on this "
-                           "all-integer table - + flags + first accepted index out)",
-                   "with_8B_descriptors_f64_lengths": sub8, "with_16B_descriptors": sub16}
+                   "d2h_bytes_per_step": world * (n * 4 + 8), "ms_per_step": 1e3 * dt / K,
+                   "call": "vnsgpu_eval_batch_packed32r (pinned host buffers: 4 B descriptors in; one 4 B result word per "
+                           "candidate out = int32 length - exact on this all-integer table - | flags << 29, + first accepted "
+                           "index); replayed as one CUDA graph launch",
+                   "with_4B_descriptors_i32_lengths_u8_flags": sub5, "with_8B_descriptors_f64_lengths": sub8,
+                   "with_16B_descriptors": sub16}
             if world == 1:
-                assert first.value == first8, "compact and 8-byte entry points disagree on the first accepted candidate"
+                assert first.value == first8 == first5, "compact and 8-byte entry points disagree on the first accepted candidate"
             assert torch.equal(h_len32[:65536].double(), h_len[:65536]), "compact entry point: lengths differ"
+            w = h_res.numpy().view(np.uint32)[:65536]
+            assert ((w & 0x1fffffff) == h_len32.numpy()[:65536]).all() and ((w >> 29) == h_fl.numpy()[:65536]).all(), \
+                "result words differ from lengths + flags"
         else:
             launches += nl8
             in_b, out_b = 8, 9
@@ -606,8 +653,8 @@ def run_b200(args):
             assert first.value == first_dev, "host and device entry points disagree on the first accepted candidate"
         assert torch.equal(h_len[:4096], d_len[:4096].cpu()), "host and device entry points disagree"
 
-    hbm_regime = eng.table_bytes / 2 > 126e6
-    vec_mode = bool(int_path and args.vector_cache and pb.m.max() <= 32 and (n >= pb.C * pb.C or args.vector_cache == 2))
+    hbm_regime = eng.table_bytes / 2 > (48 << 20)      # the library's own switch (vec_lat): int32 table beyond 48 MiB
+    vec_mode = bool(int_path and args.vector_cache and pb.m.max() <= 32 and (4 * n >= pb.C * pb.C or args.vector_cache == 2))
     peak, peak_src = measured_hbm_peak()
     achieved = alg_bytes / (kern_ms * 1e-3) / 1e9
     line = {
@@ -624,17 +671,20 @@ def run_b200(args):
                           "table is cache-resident by design" % (n * 33 / 1e6, eng.table_bytes / 1e6)) if not hbm_regime else
                          ("the table read by the kernel (%.0f MB at %d B/entry, plus the segment products) is far beyond the "
                           "126 MB L2: blocks are gathered from HBM" % (eng.table_bytes / 8 * (4 if int_path else 8) / 1e6, 4 if int_path else 8)),
-                   "evaluation": "sub-warp groups, batch sorted by chain length on the device, %s" %
+                   "evaluation": "sub-warp groups, %s" %
                                  (("exact int32 DPX arithmetic; per step the segment products and the endpoint vectors of the path "
-                                   "state are rebuilt (k_seg_build, k_vec_build), then every candidate is one dot-min of two vectors "
-                                   "through at most one block (k_eval_vec)" if vec_mode else
-                                   "exact int32 DPX arithmetic + exact segment products (rebuilt every step)") if int_path
-                                  else "IEEE double, block by block"),
+                                   "state are rebuilt (k_seg_build, k_vec_uw, k_vec_pairs), then every candidate is one dot-min of two "
+                                   "vectors through at most one block (k_eval_vec; %s)" %
+                                   ("batch sorted by product row on the device" if hbm_regime else "batch in the caller's order")
+                                   if vec_mode else
+                                   "batch sorted by chain length on the device, exact int32 DPX arithmetic + exact segment products "
+                                   "(rebuilt every step)") if int_path
+                                  else "batch sorted by chain length on the device, IEEE double, block by block"),
                    "sharding": "candidates split by rank (global batch = n_gpus x per-GPU batch), table and path replicated; "
                                "N > 1 adds one 8-byte all-reduce(MIN) per step for the chosen move"},
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": ncu_traffic(args.workload, n), "peak_source": peak_src,
+                     "traffic": ncu_traffic(args.workload, n), "cache_level": ncu_cache_level(args.workload, n), "peak_source": peak_src,
                      "kernel": "k_eval_vec" if vec_mode else "k_eval_groups",
                      "kernel_ms": kern_ms, "algorithmic_bytes_per_launch": int(alg_bytes),
                      "algorithmic_bytes_per_candidate": alg_bytes / n,

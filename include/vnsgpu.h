@@ -112,11 +112,15 @@ vnsgpu_status vnsgpu_set_batch_sort(vnsgpu_ctx *ctx, int enable);
  * built once per call and shared by all candidates (exactly associative on integers: bit-identical
  * lengths); a MOVE / EXCHANGE chain of `span` blocks then costs at most 5.  enable = 0: block by block. */
 vnsgpu_status vnsgpu_set_segment_cache(vnsgpu_ctx *ctx, int enable);
-/* Integer tables, batches of >= C^2 candidates (on top of the segment products): the two ends of every
+/* Integer tables, batches of >= C^2 / 4 candidates (on top of the segment products): the two ends of every
  * candidate's chain depend only on (cluster, layer) - they are built once per call as vectors, and a candidate
  * costs at most ONE block step (exact: integer min-plus is associative).  enable = 0: segment products only;
  * 2: also for smaller batches. */
 vnsgpu_status vnsgpu_set_vector_cache(vnsgpu_ctx *ctx, int enable);
+/* All-integer tables whose entries are below 65535 also get a uint16 copy (2 N^2 bytes); the endpoint-vector builds,
+ * which stream whole row bands of the table, read that copy (half the HBM bytes; the values are the same integers).
+ * enable = 0 makes them read the int32 copy (tests run both).  Default: enabled. */
+vnsgpu_status vnsgpu_set_u16_table(vnsgpu_ctx *ctx, int enable);
 /* vnsgpu_local_search keeps the whole search state in one SM's shared memory when it fits (clusters <=
  * 510, samples per cluster <= 32); enable = 0 forces the global-memory chain (tests run both). */
 vnsgpu_status vnsgpu_set_smem_chain(vnsgpu_ctx *ctx, int enable);
@@ -185,6 +189,19 @@ static inline uint32_t vnsgpu_pack_cand32(int op, int a, int b, int gain_is_a)
 }
 vnsgpu_status vnsgpu_eval_batch_packed32(vnsgpu_ctx *ctx, int path, int64_t n, const uint32_t *packed, double budget,
                                          int skip, int32_t *len, uint8_t *flags, int64_t *first_accept);
+/* The same call with ONE 4-byte result word per candidate: length | flags << 29 (FEASIBLE / ACCEPT / LB_SKIP in bits
+ * 29-31; every length of the exact int32 path is below 2^29), 0xffffffff for bad indices - 4 + 4 bytes per candidate
+ * over the link.  vnsgpu_result_len / vnsgpu_result_flags take a word apart. */
+static inline int32_t vnsgpu_result_len(uint32_t w)
+{
+   return (int32_t)(w & 0x1fffffffu);
+}
+static inline int vnsgpu_result_flags(uint32_t w)
+{
+   return w == 0xffffffffu ? VNSGPU_F_BAD : (int)(w >> 29);
+}
+vnsgpu_status vnsgpu_eval_batch_packed32r(vnsgpu_ctx *ctx, int path, int64_t n, const uint32_t *packed, double budget,
+                                          int skip, uint32_t *result, int64_t *first_accept);
 /* device buffers, asynchronous on `stream` (NULL = context stream); d_first_accept: one int64 that
  * the call resets and fills like first_accept above (-1 = none), or NULL */
 vnsgpu_status vnsgpu_eval_batch_dev(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *d_cands,

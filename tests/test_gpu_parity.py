@@ -290,11 +290,13 @@ def test_eval_batch_both_arithmetic_paths_vs_oracle(name, int_path, golden, eng_
                 ln32, fl32, first32 = pg.eval_batch_packed32(big)
                 assert ln32.dtype == np.int32 and (ln32[~bad] == ln[~bad]).all() and (ln32[bad] == np.iinfo(np.int32).min).all()
                 assert (fl32 == fl).all() and first32 == first
+                lnw, flw, firstw = pg.eval_batch_packed32r(big)      # one result word per candidate: length | flags << 29
+                assert (lnw == ln32).all() and (flw == fl).all() and firstw == first
             else:            # real-valued evaluation path: the int32 call refuses instead of rounding
                 with pytest.raises(engine.VnsGpuError):
                     pg.eval_batch_packed32(big[:64])
             # (the integer path has just used the endpoint vectors + exact segment products: batch >= 16384
-            # and >= C^2); the same batch with the vectors off, the products off, the sort off
+            # and >= C^2 / 4); the same batch with the vectors off, the products off, the sort off
             for sort, seg, vec in ((False, True, True), (True, True, False), (False, True, False), (True, False, False), (False, False, False)):
                 e.set_batch_sort(sort)
                 e.set_segment_cache(seg)
@@ -302,6 +304,14 @@ def test_eval_batch_both_arithmetic_paths_vs_oracle(name, int_path, golden, eng_
                 ln2, lb2, fl2, first2 = pg.eval_batch(big)
                 assert (ln2[~bad] == ln[~bad]).all() and (lb2[~bad] == lb[~bad]).all() and (fl2 == fl).all()
                 assert first2 == first
+                if int_path and vec:         # the endpoint-vector builds from the int32 table instead of the uint16 copy
+                    e.set_u16_table(False)
+                    ln3, lb3, fl3, first3 = pg.eval_batch(big)
+                    e.set_u16_table(True)
+                    assert (ln3[~bad] == ln[~bad]).all() and (lb3[~bad] == lb[~bad]).all() and (fl3 == fl).all() and first3 == first
+                if int_path and not vec:     # result words through the conversion kernel (sorted / block-by-block forms)
+                    lnw, flw, firstw = pg.eval_batch_packed32r(big)
+                    assert (lnw[~bad] == ln[~bad]).all() and (flw == fl).all() and firstw == first
     finally:
         e.set_int_path(True)
         e.set_batch_sort(True)

@@ -68,7 +68,7 @@ def test_synthetic_long_tour_candidates(synth, int_path):
     e, o, pb, (vns, T) = synth
     pg, po = e.path(vns, T), o.path(vns, T)
     rs = np.random.RandomState(5)
-    cands = random_candidates(rs, vns, T, 170000)              # >= C^2: the endpoint-vector form engages
+    cands = random_candidates(rs, vns, T, 170000)              # >= C^2 / 4: the endpoint-vector form engages
     oln, olb = po.eval_batch(cands)
     e.set_int_path(int_path)
     try:
@@ -179,7 +179,7 @@ def test_synthetic_dop_candidates_vs_oracle():
         pg, po = e.path(vns, T), o.path(vns, T)
         assert pg.getPathLength() == po.length() and pg.getPathLengthRear() == po.length_rear()
         rs = np.random.RandomState(9)
-        cands = random_candidates(rs, vns, T, 70000)           # >= C^2: the endpoint-vector form engages
+        cands = random_candidates(rs, vns, T, 70000)           # >= C^2 / 4: the endpoint-vector form engages
         oln, olb = po.eval_batch(cands)
         for int_path in (True, False):
             e.set_int_path(int_path)

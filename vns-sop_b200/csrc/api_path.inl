@@ -214,17 +214,21 @@ static int eval_grid(const vnsgpu_ctx *ctx, int64_t n)
 // integer tables: build the segment products of the path's current state (exact, see eval.cuh SegCache)
 static bool seg_wanted(const vnsgpu_ctx *ctx, int64_t n)
 {
-   return ctx->use_seg && vnsgpu_int_path_active(ctx) && ctx->seg_ok && n >= VNS_SEG_MIN;
+   // block by block a candidate costs ~T/3 block steps, the products ~T^2/2 once per state: they pay from a batch of a
+   // few T on.  Fixed floor for small instances (a handful of launches costs more than it saves there), n C >= 2^20 for
+   // large ones (64 k-sample DOP state, 1024 candidates: 3.3 ms block by block, 1.4 ms with the products)
+   return ctx->use_seg && vnsgpu_int_path_active(ctx) && ctx->seg_ok && (n >= VNS_SEG_MIN || n * (int64_t)ctx->I.C >= (1 << 20));
 }
 
 // evaluation form of a batch: 0 block by block, 1 segment products, 2 endpoint vectors + segment products.
-// The vectors cost 2 C (T+2) + 4 T (T+2) <= 6 C^2 block steps per path state and save ~4 block steps per candidate, so
-// they pay once the batch reaches ~C^2 (T is only known on the device: C bounds it).
+// The vectors cost 2 C (T+2) + 4 T (T+2) block steps per path state (T is only known on the device; typically
+// T ~ C / 3) and save ~4 block steps per candidate.  Measured break-even on the HBM-sized instances (batch sweeps
+// r1t): 0.9 M candidates at C = 2002, m = 10 and 0.35 M at C = 2002, m = 32 - hence batch >= C^2 / 4.
 static int eval_mode(const vnsgpu_ctx *ctx, int64_t n)
 {
    if (!seg_wanted(ctx, n)) return 0;
    const int64_t C = ctx->I.C;
-   if (ctx->use_vec && ctx->I.mp <= 32 && (n >= C * C || ctx->use_vec == 2) && vec_ints((int)C, (int)C + 2, ctx->I.mp) < (1ull << 31)) return 2;
+   if (ctx->use_vec && ctx->I.mp <= 32 && (4 * n >= C * C || ctx->use_vec == 2) && vec_ints((int)C, (int)C + 2, ctx->I.mp) < (1ull << 31)) return 2;
    return 1;
 }
 
@@ -267,30 +271,52 @@ static vnsgpu_status prepare_eval(vnsgpu_ctx *ctx, int path, int mode, cudaStrea
    }
    // T is only known on the device: grids sized for its bound (T + 2 <= C), surplus warps return at once
    const int Smax = std::min(I.rows, I.C);
-   const int thr = I.mp <= 22 ? 256 : 128;                      // 2 staged blocks per warp: <= 32 KB per CTA
-   const size_t smem = sizeof(int) * 2 * (size_t)I.mp * I.mp * (thr / 32);
+   // the builds stream table blocks and nothing else: from the uint16 copy when there is one (half the bytes)
+   const bool u16 = ctx->d_D16 && ctx->use_u16;
+   const size_t slot = vec_slot_bytes(I.mp, u16 ? sizeof(unsigned short) : sizeof(int));
+   const int thr = 2 * slot * 8 <= 40 * 1024 ? 256 : 128;      // 2 staged blocks per warp: <= 40 KB per CTA
    const int wpc = thr / 32;
+   const size_t smem = 2 * slot * wpc;
    // grid.y = layer lanes (the kernels stride over the layers): enough CTAs to fill the device on small instances,
    // few enough that none is empty on large ones
    const int gxu = (I.C + wpc - 1) / wpc, gxp = (Smax + 1 + wpc - 1) / wpc;
    const int gyu = std::min(Smax, std::max(16, (8 * ctx->num_sms + gxu - 1) / gxu));
    const int gyp = std::min(Smax, std::max(16, (8 * ctx->num_sms + gxp - 1) / gxp));
-   k_vec_uw<<<dim3(gxu, gyu), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta, ctx->d_vec, ctx->d_veclb, LS);
+   if (u16) k_vec_uw<unsigned short><<<dim3(gxu, gyu), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D16, ctx->d_segmeta, ctx->d_vec, ctx->d_veclb, LS);
+   else k_vec_uw<int><<<dim3(gxu, gyu), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta, ctx->d_vec, ctx->d_veclb, LS);
    LAUNCHED(ctx);
-   k_vec_pairs<<<dim3(gxp, gyp), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta, ctx->d_vec, LS);
+   if (u16) k_vec_pairs<unsigned short><<<dim3(gxp, gyp), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D16, ctx->d_segmeta, ctx->d_vec, LS);
+   else k_vec_pairs<int><<<dim3(gxp, gyp), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta, ctx->d_vec, LS);
    LAUNCHED(ctx);
    return VNSGPU_OK;
 }
 
+// tables beyond the caches (synthetic scaled instances): latency form of k_eval_vec's block step, batch sorted by product row
+static bool vec_lat(const vnsgpu_ctx *ctx) { return (size_t)ctx->I.N * ctx->I.N * sizeof(int) > ((size_t)48 << 20); }
+
+// Is the batch evaluated in sorted order?  The endpoint-vector kernel on a cache-resident table mostly is not: every
+// candidate is at most one block step there, so all the sort can do is group the candidates without one (a warp
+// iteration skips the block product only if all its 32/G groups do).  With clusters of at most 2 G samples (one pass of
+// the block product) that is worth less than the three sort passes and the scattered descriptor reads / result writes
+// of a permuted batch (krob200, 4 Mi candidates: 11.5 -> 12.5 G evals/s without the sort); with larger clusters (up to
+// 4 x 4 passes per product) the grouping still pays (vm1084: 5.8 G sorted, 5.2 G unsorted).
+static bool eval_sorts(const vnsgpu_ctx *ctx, int64_t n, int useseg)
+{
+   const bool light = useseg == 2 && !vec_lat(ctx) && ctx->I.mp <= 2 * ctx->group_lanes;
+   return group_kernel_ok(ctx) && ctx->sort_batches && n >= VNS_SORT_MIN && n < (1ll << 32) && !light;
+}
+
+// fmt / d_leni: only with useseg == 2 and !eval_sorts(): d_cands are vnsgpu_pack_cand32 words read in place (fmt 2),
+// lengths are written as int32 as well
 static vnsgpu_status launch_eval(vnsgpu_ctx *ctx, int path, int64_t n, int64_t idx0, const vnsgpu_cand *d_cands, double budget,
                                  int skip, double *d_len, double *d_lb, uint8_t *d_flags, unsigned long long *d_first, cudaStream_t st,
-                                 int slot, int64_t perm_off, int useseg)
+                                 int slot, int64_t perm_off, int useseg, int fmt = 0, int *d_leni = nullptr)
 {
    const InstDev &I = ctx->I;
    const PathDev &P = ctx->paths[path].d;
    if (group_kernel_ok(ctx)) {
       const unsigned *d_perm = nullptr;
-      if (ctx->sort_batches && n >= VNS_SORT_MIN && n < (1ll << 32)) {
+      if (eval_sorts(ctx, n, useseg)) {
          const int nb = I.rows + 1;
          if (!ctx->d_hist) CK(cudaMalloc(&ctx->d_hist, sizeof(unsigned) * 2 * nb * VNS_PIPE_EVENTS));
          if ((int64_t)ctx->perm_cap < perm_off + n) {
@@ -303,7 +329,7 @@ static vnsgpu_status launch_eval(vnsgpu_ctx *ctx, int path, int64_t n, int64_t i
          const int sgrid = (int)std::min<int64_t>((n + 2047) / 2048, (int64_t)ctx->num_sms * 8);
          CK(cudaMemsetAsync(hist, 0, sizeof(unsigned) * nb, st));
          // endpoint vectors on a table beyond the caches: order the block candidates by product row (vec_sort_key)
-         const int sortmode = (useseg == 2 && (size_t)I.N * I.N * sizeof(int) > ((size_t)48 << 20)) ? 3 : useseg;
+         const int sortmode = (useseg == 2 && vec_lat(ctx)) ? 3 : useseg;
          k_sort_hist<<<sgrid, 256, sizeof(unsigned) * nb, st>>>(I, P, n, d_cands, nb, hist, sortmode);
          LAUNCHED(ctx);
          k_sort_scan<<<1, 1024, 0, st>>>(nb, hist, cursor);
@@ -345,15 +371,14 @@ static vnsgpu_status launch_eval(vnsgpu_ctx *ctx, int path, int64_t n, int64_t i
    do {                                                                                                              \
       if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k_eval_vec<GG, RR, LL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
       k_eval_vec<GG, RR, LL><<<grid, VNS_EVAL_THREADS, smem, st>>>(I, ctx->d_D32, P, seg, vc, n, idx0, d_cands, d_perm, budget, skip, d_len, \
-                                                                   d_lb, d_flags, d_first);                          \
+                                                                   d_lb, d_flags, d_first, fmt, d_leni);             \
    } while (0)
 #define VNS_LAUNCH_VEC(GG, RR)                                                                                       \
    do {                                                                                                              \
       if (lat) VNS_LAUNCH_VEC_L(GG, RR, true);                                                                        \
       else VNS_LAUNCH_VEC_L(GG, RR, false);                                                                           \
    } while (0)
-         // tables beyond the caches (synthetic scaled instances): latency form of the block step
-         const bool lat = (size_t)I.N * I.N * sizeof(int) > ((size_t)48 << 20);
+         const bool lat = vec_lat(ctx);
          if (G == 8 && NR == 1) VNS_LAUNCH_VEC(8, 1);
          else if (G == 8 && NR == 2) VNS_LAUNCH_VEC(8, 2);
          else if (G == 8) VNS_LAUNCH_VEC(8, 4);
@@ -433,11 +458,25 @@ __global__ void __launch_bounds__(256) k_len_to_i32(long long n, const double *_
    }
 }
 
+// result words of vnsgpu_eval_batch_packed32r: length | flags << 29 (lengths of the exact int32 path are below 2^29), all
+// ones for bad indices
+__global__ void __launch_bounds__(256) k_len_to_word(long long n, const double *__restrict__ len, const uint8_t *__restrict__ flags,
+                                                     unsigned *__restrict__ out)
+{
+   for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < n; q += (long long)gridDim.x * blockDim.x) {
+      const double l = len[q];
+      const unsigned f = flags[q];
+      out[q] = (l == l && !(f & VNSGPU_F_BAD)) ? ((unsigned)(int)l | (f << 29)) : 0xffffffffu;
+   }
+}
+
 // src: vnsgpu_cand[n] (packed == 0), uint64_t[n] in the vnsgpu_pack_cand format (packed == 1) or uint32_t[n] in the
 // vnsgpu_pack_cand32 format (packed == 2); len_i32 (integer tables only): lengths as int32 instead of len
 static vnsgpu_status eval_batch_host(vnsgpu_ctx *ctx, int path, int64_t n, const void *src, int packed, double budget, int skip,
-                                     double *len, double *lb, uint8_t *flags, int64_t *first_accept, int32_t *len_i32 = nullptr)
+                                     double *len, double *lb, uint8_t *flags, int64_t *first_accept, int32_t *len_i32 = nullptr,
+                                     bool resw = false)
 {
+   // resw: len_i32 receives result words (length | flags << 29) and `flags` is not copied out
    CK(cudaSetDevice(ctx->device));
    if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
    if (first_accept) *first_accept = -1;
@@ -500,10 +539,10 @@ static vnsgpu_status eval_batch_host(vnsgpu_ctx *ctx, int path, int64_t n, const
    memset(&key, 0, sizeof(key));
    key.I = ctx->I; key.P = ctx->paths[path].d;
    key.src = src; key.len = len; key.lb = lb; key.flags = flags; key.leni = len_i32;
-   key.scratch = ctx->d_scratch; key.D32 = ctx->d_D32; key.vec = ctx->d_vec; key.veclb = ctx->d_veclb;
+   key.scratch = ctx->d_scratch; key.D32 = ctx->d_D32; key.D16 = (ctx->d_D16 && ctx->use_u16) ? ctx->d_D16 : nullptr; key.vec = ctx->d_vec; key.veclb = ctx->d_veclb;
    key.segmeta = ctx->d_segmeta; key.hist = ctx->d_hist; key.perm = ctx->d_perm; key.sk = sk;
    key.n = n; key.budget = budget; key.skip = skip; key.packed = packed; key.mode = useseg;
-   key.sort = ctx->sort_batches; key.use_int = ctx->use_int; key.G = ctx->group_lanes; key.perm_cap = ctx->perm_cap;
+   key.sort = ctx->sort_batches + 2 * (int)resw; key.use_int = ctx->use_int; key.G = ctx->group_lanes; key.perm_cap = ctx->perm_cap;
    auto finish = [&]() -> vnsgpu_status {
       CK(cudaStreamSynchronize(sk));
       if (first_accept) *first_accept = (int64_t)*ctx->h_first;
@@ -539,17 +578,27 @@ static vnsgpu_status eval_batch_host(vnsgpu_ctx *ctx, int path, int64_t n, const
             CK(cudaMemcpyAsync(d_c + lo, (const vnsgpu_cand *)src + lo, sizeof(vnsgpu_cand) * cn, cudaMemcpyHostToDevice, ctx->s_in));
          CK(cudaEventRecord(ctx->ev_in[c], ctx->s_in));
          CK(cudaStreamWaitEvent(sk, ctx->ev_in[c], 0));
-         if (packed) {
+         // endpoint-vector kernel on an unsorted chunk: it reads the 4-byte descriptors in place and writes int32 lengths
+         // itself (two kernels and 36 B / candidate of HBM traffic less per chunk)
+         const bool direct = packed == 2 && useseg == 2 && !eval_sorts(ctx, cn, useseg);
+         if (packed && !direct) {
             const int ug = (int)std::min<int64_t>((cn + 255) / 256, (int64_t)ctx->num_sms * 8);
             if (packed == 2) k_unpack_cands32<<<ug, 256, 0, sk>>>(cn, d_pk32 + lo, d_c + lo);
             else k_unpack_cands<<<ug, 256, 0, sk>>>(cn, d_pk + lo, d_c + lo);
             LAUNCHED(ctx);
          }
-         s = launch_eval(ctx, path, cn, lo, d_c + lo, budget, skip, (len || len_i32) ? d_len + lo : nullptr, lb ? d_lb + lo : nullptr,
-                         flags ? d_fl + lo : nullptr, (unsigned long long *)ctx->d_first, sk, c, lo, useseg);
+         if (direct)
+            s = launch_eval(ctx, path, cn, lo, reinterpret_cast<const vnsgpu_cand *>(d_pk32 + lo), budget, skip, len ? d_len + lo : nullptr,
+                            lb ? d_lb + lo : nullptr, flags ? d_fl + lo : nullptr, (unsigned long long *)ctx->d_first, sk, c, lo, useseg,
+                            resw ? 6 : 2, len_i32 ? d_li + lo : nullptr);
+         else
+            s = launch_eval(ctx, path, cn, lo, d_c + lo, budget, skip, (len || len_i32) ? d_len + lo : nullptr, lb ? d_lb + lo : nullptr,
+                            (flags || resw) ? d_fl + lo : nullptr, (unsigned long long *)ctx->d_first, sk, c, lo, useseg);
          if (s) return s;
-         if (len_i32) {
-            k_len_to_i32<<<(int)std::min<int64_t>((cn + 255) / 256, (int64_t)ctx->num_sms * 8), 256, 0, sk>>>(cn, d_len + lo, d_li + lo);
+         if (len_i32 && !direct) {
+            const int cg = (int)std::min<int64_t>((cn + 255) / 256, (int64_t)ctx->num_sms * 8);
+            if (resw) k_len_to_word<<<cg, 256, 0, sk>>>(cn, d_len + lo, d_fl + lo, (unsigned *)d_li + lo);
+            else k_len_to_i32<<<cg, 256, 0, sk>>>(cn, d_len + lo, d_li + lo);
             LAUNCHED(ctx);
          }
          CK(cudaEventRecord(ctx->ev_k[c], sk));
@@ -605,6 +654,16 @@ vnsgpu_status vnsgpu_eval_batch_packed32(vnsgpu_ctx *ctx, int path, int64_t n, c
       return VNSGPU_E_STATE;
    }
    return eval_batch_host(ctx, path, n, packed, 2, budget, skip, nullptr, nullptr, flags, first_accept, len);
+}
+
+vnsgpu_status vnsgpu_eval_batch_packed32r(vnsgpu_ctx *ctx, int path, int64_t n, const uint32_t *packed, double budget, int skip,
+                                          uint32_t *result, int64_t *first_accept)
+{
+   if (!vnsgpu_int_path_active(ctx)) {
+      ctx->err = "vnsgpu_eval_batch_packed32r: result words need an all-integer table (exact int32 path not active)";
+      return VNSGPU_E_STATE;
+   }
+   return eval_batch_host(ctx, path, n, packed, 2, budget, skip, nullptr, nullptr, nullptr, first_accept, (int32_t *)result, true);
 }
 
 vnsgpu_status vnsgpu_cand_bytes(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *cands, int64_t *bytes)

@@ -120,6 +120,7 @@ struct TableJob {
    int do_ceil;          // KIND 1
    double *D;            // block-major table (out)
    int *Di;              // its int32 copy (out) or null
+   unsigned short *D16;  // its uint16 copy (out, saturated) or null: halves the bytes the state builds stream (vec.cuh)
    double *dmin, *dmax;  // C x C (out)
    unsigned long long *info;   // [0] += CTAs that saw a non-integer or negative entry, [1] = max over the bit patterns
                                // of the CTAs' largest entries (entries >= 0 order like their bit patterns)
@@ -167,6 +168,7 @@ __global__ void __launch_bounds__(256) k_table_pairs(InstDev I, TableJob J)
          }
          J.D[base + e] = d;
          if (J.Di) J.Di[base + e] = (int)d;
+         if (J.D16) J.D16[base + e] = (unsigned short)(d >= 0.0 && d < 65535.0 ? d : 65535.0);
          lo = d < lo ? d : lo;
          hi = d > hi ? d : hi;
          bad |= (d != floor(d)) || (d < 0);

@@ -48,17 +48,23 @@ __device__ __forceinline__ unsigned vec_pair(const VecCache &vc, int C, int mp, 
    return (unsigned)(2 * vc.LS * C + vc.LS) * (unsigned)mp + (unsigned)(((fam * vc.LS + x) * vc.LS + l) * mp);
 }
 
-// A warp stages a whole table block in its slice of shared memory with cp.async (coalesced 4-byte copies, fire and
-// forget): every block a warp needs is in flight at once and costs ONE memory round trip; the min-plus loops then run
-// out of shared memory.
-__device__ __forceinline__ void warp_stage(int *dst, const int *__restrict__ src, int n, int lane)
+// A warp stages a whole table block in its slice of shared memory with cp.async (fire and forget): every block a warp
+// needs is in flight at once and costs ONE memory round trip; the min-plus loops then run out of shared memory.
+// Always 16-byte copies, whatever the block's alignment: the copy starts at the 16-byte line below the block and the
+// data sits at the same offset inside the (16-byte aligned) slot - up to 15 bytes of neighbouring entries come along on
+// either side (inside the table's allocation: it starts 256-byte aligned and ends with slack).  Returns the block.
+// TT = int (int32 table) or unsigned short (uint16 table: half the bytes).  Slot size: vec_slot_bytes.
+__host__ __device__ inline size_t vec_slot_bytes(int mp, size_t elem) { return (((size_t)mp * mp * elem + 15) & ~(size_t)15) + 32; }
+
+template <typename TT>
+__device__ __forceinline__ const TT *warp_stage(char *slot, const TT *__restrict__ src, int n, int lane)
 {
-   const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
-   if ((((unsigned)(size_t)src | d) & 15u) == 0 && (n & 3) == 0) {   // warp-uniform: 16-byte copies (4 x fewer LSU instructions)
-      for (int e = lane * 4; e < n; e += 128) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d + 4u * e), "l"(src + e));
-   } else {
-      for (int e = lane; e < n; e += 32) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + 4u * e), "l"(src + e));
-   }
+   const unsigned shift = (unsigned)((size_t)src & 15);
+   const char *s0 = reinterpret_cast<const char *>(src) - shift;
+   const unsigned d0 = (unsigned)__cvta_generic_to_shared(slot);
+   const int nb = (int)((shift + (unsigned)n * (unsigned)sizeof(TT) + 15u) & ~15u);
+   for (int e = lane * 16; e < nb; e += 512) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d0 + e), "l"(s0 + e));
+   return reinterpret_cast<const TT *>(slot + shift);
 }
 __device__ __forceinline__ void warp_stage_wait()
 {
@@ -67,26 +73,28 @@ __device__ __forceinline__ void warp_stage_wait()
    __syncwarp();
 }
 // lane = output index; v (lane-held, INF beyond the source size) times the staged ma x mb block
-__device__ __forceinline__ int vec_fwd(const int *blk, int ma, int mb, int v, int lane)
+template <typename TT>
+__device__ __forceinline__ int vec_fwd(const TT *blk, int ma, int mb, int v, int lane)
 {
    int acc = VNS_INT_INF;
    const int j = min(lane, mb - 1);
 #pragma unroll 4
-   for (int s = 0; s < ma; ++s) acc = __viaddmin_s32(__shfl_sync(0xffffffffu, v, s), blk[s * mb + j], acc);
+   for (int s = 0; s < ma; ++s) acc = __viaddmin_s32(__shfl_sync(0xffffffffu, v, s), (int)blk[s * mb + j], acc);
    return lane < mb ? acc : VNS_INT_INF;
 }
 // lane = source index; the staged ma x mb block times v (lane-held over the mb destination samples).  Lane s walks its
 // row DIAGONALLY (column (s + t) mod mb at step t): with mb = 32 the 32 lanes then hit 32 different banks, where the
 // straight order (every lane the same column: stride mb) is a 32-way bank conflict.  min is order-free: same result.
-__device__ __forceinline__ int vec_bwd(const int *blk, int ma, int mb, int v, int lane)
+template <typename TT>
+__device__ __forceinline__ int vec_bwd(const TT *blk, int ma, int mb, int v, int lane)
 {
    int acc = VNS_INT_INF;
    const int s = min(lane, ma - 1);
-   const int *row = blk + s * mb;
+   const TT *row = blk + s * mb;
    int j = s % mb;
 #pragma unroll 4
    for (int t = 0; t < mb; ++t) {
-      acc = __viaddmin_s32(__shfl_sync(0xffffffffu, v, j), row[j], acc);
+      acc = __viaddmin_s32(__shfl_sync(0xffffffffu, v, j), (int)row[j], acc);
       j = j + 1 == mb ? 0 : j + 1;
    }
    return lane < ma ? acc : VNS_INT_INF;
@@ -106,8 +114,9 @@ __device__ __forceinline__ LayerMeta layer_meta(const InstDev &I, const int *met
 }
 
 // one warp per (l, c), l strided over grid.y: consecutive warps read consecutive blocks of row band lcl[l] (U) and write
-// consecutive vectors.  Needs mp <= 32.  Dynamic shared memory: 2 mp^2 ints per warp.
-__global__ void __launch_bounds__(256) k_vec_uw(InstDev I, PathDev P, const int *__restrict__ Dv, const int *__restrict__ meta,
+// consecutive vectors.  Needs mp <= 32.  Dynamic shared memory: 2 slots (vec_slot_bytes) per warp.
+template <typename TT>
+__global__ void __launch_bounds__(256) k_vec_uw(InstDev I, PathDev P, const TT *__restrict__ Dv, const int *__restrict__ meta,
                                                 int *__restrict__ vec, int *__restrict__ lbs, int LS)
 {
    extern __shared__ int smem_i[];
@@ -117,15 +126,17 @@ __global__ void __launch_bounds__(256) k_vec_uw(InstDev I, PathDev P, const int 
    if (c >= C) return;
    const LayerMeta lm = layer_meta(I, meta);
    VecCache vc{vec, lbs, LS};
-   int *bU = smem_i + (threadIdx.x >> 5) * 2 * mp * mp, *bW = bU + mp * mp;
+   const size_t slot = vec_slot_bytes(mp, sizeof(TT));
+   char *sU = reinterpret_cast<char *>(smem_i) + (threadIdx.x >> 5) * 2 * slot, *sW = sU + slot;
    const int mc = __ldg(I.m + c), oc = __ldg(I.off + c);
    // T is only known on the device: grid.y is a fixed number of layer lanes, every warp strides over the layers
    for (int l = blockIdx.y; l <= S; l += gridDim.y) {
       const int cl = lm.cl(l), ml = lm.m(l), ol = lm.off(l);
       const bool doU = l <= S - 1, doW = l >= 1, sym = I.symmetric != 0;
       // symmetric tables: D(c, cl) is the transpose of D(cl, c) - the column strip of W comes out of the same row band
-      if (doU || sym) warp_stage(bU, Dv + ((long long)ol * I.N + (long long)ml * oc), ml * mc, lane);     // D(cl, c)
-      if (doW && !sym) warp_stage(bW, Dv + ((long long)oc * I.N + (long long)mc * ol), mc * ml, lane);    // D(c, cl)
+      const TT *bU = nullptr, *bW = nullptr;
+      if (doU || sym) bU = warp_stage(sU, Dv + ((long long)ol * I.N + (long long)ml * oc), ml * mc, lane);     // D(cl, c)
+      if (doW && !sym) bW = warp_stage(sW, Dv + ((long long)oc * I.N + (long long)mc * ol), mc * ml, lane);    // D(c, cl)
       const int f = (doU && lane < ml) ? (int)P.F[(size_t)l * mp + lane] : VNS_INT_INF;
       const int bv = (doW && lane < ml) ? (int)P.B[(size_t)l * mp + lane] : VNS_INT_INF;
       int lb_ins = 0, lb_rep = 0, lb_rem = 0;
@@ -156,7 +167,8 @@ __global__ void __launch_bounds__(256) k_vec_uw(InstDev I, PathDev P, const int 
 }
 
 // one warp per (x, l), x = 1 .. T (path layer, cluster cx; strided over grid.y), l = 1 .. S.  Two table blocks, four products.
-__global__ void __launch_bounds__(256) k_vec_pairs(InstDev I, PathDev P, const int *__restrict__ Dv, const int *__restrict__ meta,
+template <typename TT>
+__global__ void __launch_bounds__(256) k_vec_pairs(InstDev I, PathDev P, const TT *__restrict__ Dv, const int *__restrict__ meta,
                                                    int *__restrict__ vec, int LS)
 {
    extern __shared__ int smem_i[];
@@ -166,7 +178,8 @@ __global__ void __launch_bounds__(256) k_vec_pairs(InstDev I, PathDev P, const i
    if (wl > S) return;
    const LayerMeta lm = layer_meta(I, meta);
    VecCache vc{vec, nullptr, LS};
-   int *b1 = smem_i + (threadIdx.x >> 5) * 2 * mp * mp, *b2 = b1 + mp * mp;
+   const size_t slot = vec_slot_bytes(mp, sizeof(TT));
+   char *s1 = reinterpret_cast<char *>(smem_i) + (threadIdx.x >> 5) * 2 * slot, *s2 = s1 + slot;
    if (I.symmetric) {
       // one block D(cx, lcl[l]) per warp, l = 0 .. S: it is also D(lcl[l], cx) transposed, so all four products are
       // forward steps through it:  InsF(x,l), RepF(x,l-1) from U;  InsB(x,l+1), RepB(x,l+1) from W
@@ -174,7 +187,7 @@ __global__ void __launch_bounds__(256) k_vec_pairs(InstDev I, PathDev P, const i
       const int ml = lm.m(l), ofl = lm.off(l);
       for (int x = blockIdx.y + 1; x <= T; x += gridDim.y) {
          const int cx = lm.cl(x), mx = lm.m(x), ox = lm.off(x);
-         warp_stage(b1, Dv + ((long long)ox * I.N + (long long)mx * ofl), mx * ml, lane);
+         const TT *b1 = warp_stage(s1, Dv + ((long long)ox * I.N + (long long)mx * ofl), mx * ml, lane);
          auto ld = [&](int k, int ll, bool on) { return (on && lane < mx) ? __ldg(vec + vec_uw(vc, C, mp, k, cx, min(max(ll, 0), S)) + lane) : VNS_INT_INF; };
          const int u1 = ld(0, l - 1, l >= 1), u2 = ld(0, l - 2, l >= 2), w1 = ld(1, l + 1, l <= S - 1), w2 = ld(1, l + 2, l <= S - 2);
          warp_stage_wait();
@@ -182,7 +195,7 @@ __global__ void __launch_bounds__(256) k_vec_pairs(InstDev I, PathDev P, const i
          const int j = min(lane, ml - 1);
 #pragma unroll 2
          for (int s = 0; s < mx; ++s) {
-            const int d = b1[s * ml + j];
+            const int d = (int)b1[s * ml + j];
             a1 = __viaddmin_s32(__shfl_sync(0xffffffffu, u1, s), d, a1);
             a2 = __viaddmin_s32(__shfl_sync(0xffffffffu, u2, s), d, a2);
             a3 = __viaddmin_s32(__shfl_sync(0xffffffffu, w1, s), d, a3);
@@ -204,8 +217,8 @@ __global__ void __launch_bounds__(256) k_vec_pairs(InstDev I, PathDev P, const i
    const int ml = lm.m(l), ma = lm.m(l - 1), ofl = lm.off(l), ofa = lm.off(l - 1);
    for (int x = blockIdx.y + 1; x <= T; x += gridDim.y) {
       const int cx = lm.cl(x), mx = lm.m(x), ox = lm.off(x);
-      warp_stage(b1, Dv + ((long long)ox * I.N + (long long)mx * ofl), mx * ml, lane);          // D(cx, lcl[l])
-      warp_stage(b2, Dv + ((long long)ofa * I.N + (long long)ma * ox), ma * mx, lane);          // D(lcl[l-1], cx)
+      const TT *b1 = warp_stage(s1, Dv + ((long long)ox * I.N + (long long)mx * ofl), mx * ml, lane);          // D(cx, lcl[l])
+      const TT *b2 = warp_stage(s2, Dv + ((long long)ofa * I.N + (long long)ma * ox), ma * mx, lane);          // D(lcl[l-1], cx)
       auto ld = [&](unsigned off, bool on) { return (on && lane < mx) ? __ldg(vec + off + lane) : VNS_INT_INF; };
       auto put = [&](unsigned off, int v) { if (lane < mp) vec[off + lane] = v; };
       const int u1 = ld(vec_uw(vc, C, mp, 0, cx, l - 1), true), u2 = ld(vec_uw(vc, C, mp, 0, cx, max(l - 2, 0)), l >= 2);
@@ -279,11 +292,14 @@ __device__ __forceinline__ VecCode decode_cand_vec(const VecCache &vc, int T, in
 // LAT: the table does not fit the caches (synthetic scaled instances) - every block step issues all its G row loads
 // before the first min (one memory round trip per step instead of G / 2); rows beyond the block re-read its last row.
 template <int G, int NR, bool LAT>
-__global__ void __launch_bounds__(VNS_EVAL_THREADS)
+__global__ void __launch_bounds__(VNS_EVAL_THREADS, LAT ? 2 : (NR > 2 ? 3 : 4))  // CTAs / SM: cache-resident form 4 (64 registers; 3 with four registers per vector), LAT 2 (128)
 k_eval_vec(InstDev I, const int *__restrict__ Dv, PathDev P, SegCache seg, VecCache vc, long long n, long long idx0,
-           const vnsgpu_cand *__restrict__ cands, const unsigned *__restrict__ perm, double budget, int skipflag,
-           double *__restrict__ len, double *__restrict__ lb, uint8_t *__restrict__ flags, unsigned long long *d_first)
+           const void *__restrict__ cands, const unsigned *__restrict__ perm, double budget, int skipflag,
+           double *__restrict__ len, double *__restrict__ lb, uint8_t *__restrict__ flags, unsigned long long *d_first,
+           int fmt, int *__restrict__ leni)
 {
+   // fmt & 3: 0 = vnsgpu_cand (16 B), 2 = vnsgpu_pack_cand32 words (4 B) read in place; leni: lengths as int32 (may be
+   // null), with fmt & 4 as result words: length | flags << 29, all ones for bad indices (vnsgpu_eval_batch_packed32r)
    extern __shared__ int smem_i[];
    constexpr unsigned FULL = 0xffffffffu;
    constexpr int INF = VNS_INT_INF;
@@ -317,7 +333,13 @@ k_eval_vec(InstDev I, const int *__restrict__ Dv, PathDev P, SegCache seg, VecCa
       long long kidx = slot;
       if (perm && slot < n) kidx = __ldg(perm + slot);
       int4 cd = make_int4(-1, 0, 0, -1);
-      if (slot < n) cd = __ldg(reinterpret_cast<const int4 *>(cands) + kidx);
+      if (slot < n) {
+         if ((fmt & 3) == 2) {
+            const unsigned w = __ldg(reinterpret_cast<const unsigned *>(cands) + kidx);
+            cd.x = (int)(w & 7); cd.y = (int)((w >> 3) & 0x3fff); cd.z = (int)((w >> 17) & 0x3fff); cd.w = (w >> 31) ? cd.y : -1;
+         } else
+            cd = __ldg(reinterpret_cast<const int4 *>(cands) + kidx);
+      }
       const VecCode vcd = decode_cand_vec(vc, T, C, mp, lcl, [&](int l) { return s_cum[l + 1] - s_cum[l]; },
                                           [&](int c) { return cinfo[c].y; }, [&](int l) { return s_pd[l]; }, cd.x, cd.y, cd.z);
       long long p_rb = 0;
@@ -436,6 +458,7 @@ k_eval_vec(InstDev I, const int *__restrict__ Dv, PathDev P, SegCache seg, VecCa
             if (bound > budget && !vcd.nolb) f |= VNSGPU_F_LB_SKIP;                                  // :539,...
          }
          if (len) len[kidx] = l;
+         if (leni) leni[kidx] = (fmt & 4) ? (vcd.ok ? (int)((unsigned)myfin | (f << 29)) : -1) : (vcd.ok ? myfin : INT_MIN);
          if (lb) lb[kidx] = bound;
          if (flags) flags[kidx] = (uint8_t)f;
          if ((f & VNSGPU_F_ACCEPT) && !(skipflag && (f & VNSGPU_F_LB_SKIP)) && (unsigned long long)(kidx + idx0) < best)

@@ -33,7 +33,7 @@ struct PathHost {
 struct HostGraphKey {
    InstDev I;
    PathDev P;
-   const void *src, *len, *lb, *flags, *leni, *scratch, *D32, *vec, *veclb, *segmeta, *hist, *perm;
+   const void *src, *len, *lb, *flags, *leni, *scratch, *D32, *D16, *vec, *veclb, *segmeta, *hist, *perm;
    cudaStream_t sk;
    int64_t n;
    double budget;
@@ -53,6 +53,8 @@ struct vnsgpu_ctx {
    int *d_m = nullptr, *d_off = nullptr, *d_clof = nullptr;
    double *d_reward = nullptr, *d_D = nullptr, *d_dmin = nullptr, *d_dmax = nullptr;
    int *d_D32 = nullptr;     // int32 copy of an all-integer table (DPX evaluation path), else null
+   unsigned short *d_D16 = nullptr;   // uint16 copy when every entry is an integer below 65535: the endpoint-vector builds stream it
+   bool use_u16 = true;      // vnsgpu_set_u16_table
    bool use_int = true;      // vnsgpu_set_int_path
    bool sort_batches = true; // evaluate batches in chain-length order (vnsgpu_set_batch_sort)
    bool use_seg = true;      // exact segment products on integer tables (vnsgpu_set_segment_cache)
@@ -160,10 +162,10 @@ static void free_instance(vnsgpu_ctx *ctx)
    for (PathHost &p : ctx->paths) cudaFree(p.block);
    ctx->paths.clear();
    cudaFree(ctx->d_m); cudaFree(ctx->d_off); cudaFree(ctx->d_clof); cudaFree(ctx->d_reward);
-   cudaFree(ctx->d_D); cudaFree(ctx->d_dmin); cudaFree(ctx->d_dmax); cudaFree(ctx->d_seg); cudaFree(ctx->d_D32);
+   cudaFree(ctx->d_D); cudaFree(ctx->d_dmin); cudaFree(ctx->d_dmax); cudaFree(ctx->d_seg); cudaFree(ctx->d_D32); cudaFree(ctx->d_D16);
    cudaFree(ctx->d_hist); cudaFree(ctx->d_perm); cudaFree(ctx->d_segmeta); cudaFree(ctx->d_vec); cudaFree(ctx->d_veclb);
    ctx->d_segmeta = nullptr; ctx->seg_ok = false; ctx->d_vec = nullptr; ctx->d_veclb = nullptr;
-   ctx->d_D32 = nullptr; ctx->d_hist = ctx->d_perm = nullptr; ctx->perm_cap = 0;
+   ctx->d_D32 = nullptr; ctx->d_D16 = nullptr; ctx->d_hist = ctx->d_perm = nullptr; ctx->perm_cap = 0;
    ctx->d_m = ctx->d_off = ctx->d_clof = ctx->d_seg = nullptr;
    ctx->d_reward = ctx->d_D = ctx->d_dmin = ctx->d_dmax = nullptr;
    ctx->have_clusters = ctx->have_table = false;
@@ -218,6 +220,12 @@ vnsgpu_status vnsgpu_set_segment_cache(vnsgpu_ctx *ctx, int enable)
 vnsgpu_status vnsgpu_set_vector_cache(vnsgpu_ctx *ctx, int enable)
 {
    ctx->use_vec = enable < 0 ? 0 : (enable > 2 ? 2 : enable);
+   return VNSGPU_OK;
+}
+
+vnsgpu_status vnsgpu_set_u16_table(vnsgpu_ctx *ctx, int enable)
+{
+   ctx->use_u16 = enable != 0;
    return VNSGPU_OK;
 }
 
@@ -325,6 +333,12 @@ static vnsgpu_status build_table(vnsgpu_ctx *ctx, TableJob J, bool maybe_int)
       } else
          CK(cudaMemsetAsync(ctx->d_D32 + nn, 0, extra, ctx->stream));
    }
+   if (ctx->d_D16) { CK(cudaFree(ctx->d_D16)); ctx->d_D16 = nullptr; }
+   if (ctx->d_D32 && cudaMalloc(&ctx->d_D16, sizeof(unsigned short) * (size_t)nn + 64) != cudaSuccess) {   // optimistic as well
+      cudaGetLastError();
+      ctx->d_D16 = nullptr;
+   }
+   J.D16 = ctx->d_D16;
    CK(cudaMemsetAsync(ctx->d_info, 0, 2 * sizeof(unsigned long long), ctx->stream));
    J.D = ctx->d_D; J.Di = ctx->d_D32; J.dmin = ctx->d_dmin; J.dmax = ctx->d_dmax; J.info = ctx->d_info;
    const long long npairs = (long long)I.C * I.C;
@@ -349,6 +363,10 @@ static vnsgpu_status build_table(vnsgpu_ctx *ctx, TableJob J, bool maybe_int)
    if (ctx->d_D32 && !(ctx->I.exact_int && mx * (double)(I.rows + 1) < 536870912.0)) {
       CK(cudaFree(ctx->d_D32));
       ctx->d_D32 = nullptr;
+   }
+   if (ctx->d_D16 && !(ctx->d_D32 && mx < 65535.0)) {      // the uint16 copy needs every entry below its saturation value
+      CK(cudaFree(ctx->d_D16));
+      ctx->d_D16 = nullptr;
    }
    ctx->I.symmetric = KIND == 0 ? 1 : 0;   // sqrt(dx*dx+dy*dy): the same bits in both directions
    ctx->have_table = true;

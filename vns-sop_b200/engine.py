@@ -55,6 +55,7 @@ _SIGS = {
     "vnsgpu_sync": [vp],
     "vnsgpu_set_int_path": [vp, C.c_int],
     "vnsgpu_set_batch_sort": [vp, C.c_int],
+    "vnsgpu_set_u16_table": [vp, C.c_int],
     "vnsgpu_set_segment_cache": [vp, C.c_int],
     "vnsgpu_set_smem_chain": [vp, C.c_int],
     "vnsgpu_set_target_reward": [vp, C.c_double],
@@ -77,6 +78,7 @@ _SIGS = {
     "vnsgpu_eval_batch": [vp, C.c_int, C.c_int64, vp, C.c_double, C.c_int, dp, dp, vp, C.POINTER(C.c_int64)],
     "vnsgpu_eval_batch_packed": [vp, C.c_int, C.c_int64, vp, C.c_double, C.c_int, dp, dp, vp, C.POINTER(C.c_int64)],
     "vnsgpu_eval_batch_packed32": [vp, C.c_int, C.c_int64, vp, C.c_double, C.c_int, vp, vp, C.POINTER(C.c_int64)],
+    "vnsgpu_eval_batch_packed32r": [vp, C.c_int, C.c_int64, vp, C.c_double, C.c_int, vp, C.POINTER(C.c_int64)],
     "vnsgpu_eval_batch_dev": [vp, C.c_int, C.c_int64, vp, C.c_double, C.c_int, vp, vp, vp, vp, vp],
     "vnsgpu_gen_proposals": [vp, C.c_int, C.c_int, C.c_int64, C.POINTER(Rng), vp],
     "vnsgpu_cand_bytes": [vp, C.c_int, C.c_int64, vp, C.POINTER(C.c_int64)],
@@ -201,6 +203,9 @@ class Engine:
 
     def set_smem_chain(self, enable):
         self._ck(self.lib.vnsgpu_set_smem_chain(self.h, int(enable)))
+
+    def set_u16_table(self, enable):
+        self._ck(self.lib.vnsgpu_set_u16_table(self.h, int(enable)))
 
     def set_batch_sort(self, enable):
         self._ck(self.lib.vnsgpu_set_batch_sort(self.h, int(enable)))
@@ -394,6 +399,21 @@ class VnsSopPath:
         budget = self.e.pb.budget if budget is None else budget
         self.e._ck(self.lib.vnsgpu_eval_batch_packed32(self.e.h, self.h, n, pk.ctypes.data, budget, skip, ln.ctypes.data,
                                                        fl.ctypes.data, C.byref(first)))
+        return ln, fl, first.value
+
+    def eval_batch_packed32r(self, cands, budget=None, skip=1):
+        """One 4-byte result word per candidate (length | flags << 29, all ones = bad indices) -> (int32 lengths with
+        INT32_MIN for bad indices, flags, first accepted index), taken apart like vnsgpu_result_len / _flags."""
+        pk = self.pack_cands32(cands)
+        n = len(pk)
+        w = np.empty(n, np.uint32)
+        first = C.c_int64(-1)
+        budget = self.e.pb.budget if budget is None else budget
+        self.e._ck(self.lib.vnsgpu_eval_batch_packed32r(self.e.h, self.h, n, pk.ctypes.data, budget, skip, w.ctypes.data,
+                                                        C.byref(first)))
+        bad = w == np.uint32(0xffffffff)
+        ln = np.where(bad, np.iinfo(np.int32).min, (w & np.uint32(0x1fffffff)).astype(np.int64)).astype(np.int32)
+        fl = np.where(bad, F_BAD, w >> np.uint32(29)).astype(np.uint8)
         return ln, fl, first.value
 
     def _one(self, op, a, b):
