@@ -381,6 +381,25 @@ k_eval_vec(InstDev I, const int *__restrict__ Dv, PathDev P, SegCache seg, VecCa
             vA[r] = j < mA ? __ldg(vc.vec + (offA + (unsigned)j)) : INF;      // one 32-bit add, then base + 4 * index
             vB[r] = j < mB ? __ldg(vc.vec + (offB + (unsigned)j)) : INF;
          }
+         if (LAT && it + 1 < G) {
+            // tables beyond the caches: while this iteration's loads are in flight, pull the NEXT candidate's block rows
+            // (one prefetch per lane = one row) and its two vectors into L1 - an iteration is otherwise one exposed
+            // memory round trip after the other (ncu r1u: 24 % of the warp slots occupied, DRAM and L2 at 15 %)
+            const int cn = c + NG;
+            const unsigned pkn = __shfl_sync(FULL, p_pack, cn);
+            const long long rbn = __shfl_sync(FULL, p_rb, cn);
+            const unsigned oAn = __shfl_sync(FULL, vcd.offA, cn), oBn = __shfl_sync(FULL, vcd.offB, cn);
+            if ((pkn >> 24) & 1) {
+               const int mAn = pkn & 63, mBn = (pkn >> 6) & 63;
+#pragma unroll
+               for (int r = 0; r < NR; ++r)
+                  if (gl + r * G < mAn) asm volatile("prefetch.global.L1 [%0];" ::"l"(Dv + rbn + (long long)((gl + r * G) * mBn)));
+            }
+            if (gl == 0) {
+               asm volatile("prefetch.global.L1 [%0];" ::"l"(vc.vec + oAn));
+               asm volatile("prefetch.global.L1 [%0];" ::"l"(vc.vec + oBn));
+            }
+         }
          if ((pk >> 25) & 1) {                                 // warp-uniform: some group of this iteration has a block
             const int trip = blk ? mA : 1, nvalid = blk ? mB : 1;
             int acc[NR];
