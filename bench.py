@@ -484,12 +484,17 @@ def run_b200(args):
     sp = C.c_void_p(stream.cuda_stream)
 
     def step():
+        if world > 1:      # sharded form: the key comes out as a global index, ready for the collective
+            st = lib.vnsgpu_eval_batch_dev_shard(eng.h, p.h, n, C.c_void_p(d_c.data_ptr()), pb.budget, 1,
+                                                 C.c_void_p(d_len.data_ptr()), C.c_void_p(d_lb.data_ptr()),
+                                                 C.c_void_p(d_fl.data_ptr()), C.c_void_p(d_first.data_ptr()), rank * n, sp)
+            eng._ck(st)
+            sharding.reduce_key_(d_first)      # the path's one exchange step: the chosen move (8 bytes, all-reduce MIN)
+            return
         st = lib.vnsgpu_eval_batch_dev(eng.h, p.h, n, C.c_void_p(d_c.data_ptr()), pb.budget, 1,
                                        C.c_void_p(d_len.data_ptr()), C.c_void_p(d_lb.data_ptr()),
                                        C.c_void_p(d_fl.data_ptr()), C.c_void_p(d_first.data_ptr()), sp)
         eng._ck(st)
-        if world > 1:      # the path's one exchange step: reduce the chosen move (8 bytes, all-reduce MIN)
-            sharding.reduce_first_accept_(d_first, rank * n)
 
     sampler = ClockSampler(local) if rank == 0 else None
     with torch.cuda.stream(stream):
@@ -518,6 +523,8 @@ def run_b200(args):
     clocks = sampler.window(t_host0, t_host1) if sampler else None
     value = world * n * K / (total_ms * 1e-3)
     first_dev = int(d_first.item())
+    if first_dev >= 0x7f7f7f7f7f7f7f7f:      # VNSGPU_NO_KEY of the sharded form
+        first_dev = -1
     ok_flags = int(((d_fl & 2) != 0).sum().item())
 
     # ---- candidate-batch sweep (BASELINE config 5): the same call on the first b candidates of the batch ---------
@@ -533,11 +540,15 @@ def run_b200(args):
         with torch.cuda.stream(stream):
             for b in sizes:
                 def sstep():
-                    eng._ck(lib.vnsgpu_eval_batch_dev(eng.h, p.h, b, C.c_void_p(d_c.data_ptr()), pb.budget, 1,
-                                                      C.c_void_p(d_len.data_ptr()), C.c_void_p(d_lb.data_ptr()),
-                                                      C.c_void_p(d_fl.data_ptr()), C.c_void_p(d_first.data_ptr()), sp))
                     if world > 1:
-                        sharding.reduce_first_accept_(d_first, rank * b)
+                        eng._ck(lib.vnsgpu_eval_batch_dev_shard(eng.h, p.h, b, C.c_void_p(d_c.data_ptr()), pb.budget, 1,
+                                                                C.c_void_p(d_len.data_ptr()), C.c_void_p(d_lb.data_ptr()),
+                                                                C.c_void_p(d_fl.data_ptr()), C.c_void_p(d_first.data_ptr()), rank * b, sp))
+                        sharding.reduce_key_(d_first)
+                    else:
+                        eng._ck(lib.vnsgpu_eval_batch_dev(eng.h, p.h, b, C.c_void_p(d_c.data_ptr()), pb.budget, 1,
+                                                          C.c_void_p(d_len.data_ptr()), C.c_void_p(d_lb.data_ptr()),
+                                                          C.c_void_p(d_fl.data_ptr()), C.c_void_p(d_first.data_ptr()), sp))
                 for _ in range(W):
                     sstep()
                 s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -207,6 +207,13 @@ vnsgpu_status vnsgpu_eval_batch_packed32r(vnsgpu_ctx *ctx, int path, int64_t n, 
 vnsgpu_status vnsgpu_eval_batch_dev(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *d_cands,
                                     double budget, int skip, double *d_len, double *d_lb, uint8_t *d_flags,
                                     long long *d_first_accept, void *stream);
+/* Multi-GPU form (candidates sharded over ranks, table and path replicated on each): d_first_key receives index_base +
+ * the local index of the shard's first accepted candidate, or VNSGPU_NO_KEY; an all-reduce(MIN) of that one int64 over
+ * the ranks is the index the sequential loop would have applied, identical for any number of GPUs. */
+#define VNSGPU_NO_KEY 0x7f7f7f7f7f7f7f7fLL
+vnsgpu_status vnsgpu_eval_batch_dev_shard(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *d_cands,
+                                          double budget, int skip, double *d_len, double *d_lb, uint8_t *d_flags,
+                                          long long *d_first_key, int64_t index_base, void *stream);
 /* draws n proposals with the reference's proposal distribution for neighbourhood `kind`
  * (1 = insertRandom :507-519 -> MOVE / ADD, 2 = exchangeRandom :723-730 -> EXCHANGE / REPLACE) against
  * the path's current state, advancing *rng exactly as the reference's draws would; HOST buffer */

@@ -56,3 +56,36 @@ def test_product_never_touches_the_oracle():
                 src = open(os.path.join(dirpath, f)).read()
                 src = src.replace("oracle/vns_oracle.c:vo_dubins_length", "")
                 assert "oracle" not in src, os.path.join(dirpath, f)
+
+
+def test_header_is_plain_c_and_packers_match_python(tmp_path):
+    """include/vnsgpu.h must compile as C (the boundary is a C ABI: no C++ or torch types), and its inline helpers
+    (8-byte / 4-byte descriptors, result words) must agree with the Python mirror in engine.py bit for bit."""
+    import subprocess
+    import numpy as np
+    from vns_sop_b200 import engine
+    src = tmp_path / "t.c"
+    src.write_text(r'''
+#include <stdio.h>
+#include "vnsgpu.h"
+int main(void) {
+   static const int c[][3] = {{0, 7, 0}, {1, 41, 29}, {3, 5, 17}, {4, 16383, 2}, {3, 0, 16383}, {0, 200, 1999}};
+   for (unsigned k = 0; k < sizeof(c) / sizeof(c[0]); ++k) {
+      const int gain = c[k][0] <= 1 ? c[k][1] : -1;
+      printf("%llu %u\n", (unsigned long long)vnsgpu_pack_cand(c[k][0], c[k][1], c[k][2], gain),
+             (unsigned)vnsgpu_pack_cand32(c[k][0], c[k][1], c[k][2], gain >= 0));
+   }
+   printf("%d %d %d %d\n", (int)vnsgpu_result_len(0x60002a37u), vnsgpu_result_flags(0x60002a37u),
+          vnsgpu_result_flags(0xffffffffu), (int)sizeof(vnsgpu_cand));
+   return 0;
+}
+''')
+    exe = tmp_path / "t"
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
+    out = subprocess.check_output([str(exe)], text=True).split("\n")
+    rows = np.array([[0, 7, 0], [1, 41, 29], [3, 5, 17], [4, 16383, 2], [3, 0, 16383], [0, 200, 1999]], np.int32)
+    p64, p32 = engine.VnsSopPath.pack_cands(rows), engine.VnsSopPath.pack_cands32(rows)
+    for k in range(len(rows)):
+        a, b = out[k].split()
+        assert int(a) == int(p64[k]) and int(b) == int(p32[k]), (k, out[k], p64[k], p32[k])
+    assert out[len(rows)].split() == [str(0x2a37), "3", str(engine.F_BAD), "16"]

@@ -284,6 +284,15 @@ def test_eval_batch_both_arithmetic_paths_vs_oracle(name, int_path, golden, eng_
             assert (ln[~bad] == oln[~bad]).all() and (lb[~bad] == olb[~bad]).all()
             ok = np.nonzero(((fl & 2) != 0) & ((fl & 4) == 0))[0]
             assert first == (int(ok[0]) if len(ok) else -1)
+            import torch, ctypes as C                                   # sharded device entry point: global key
+            d_c = torch.from_numpy(pg.make_cands(big).view(np.uint8).copy()).cuda()
+            d_key = torch.zeros(1, dtype=torch.int64, device="cuda")
+            for lo_, hi_ in ((0, len(big)), (len(big) // 2, len(big))):
+                e._ck(e.lib.vnsgpu_eval_batch_dev_shard(e.h, pg.h, hi_ - lo_, C.c_void_p(d_c.data_ptr() + 16 * lo_), pb.budget, 1,
+                                                        None, None, None, C.c_void_p(d_key.data_ptr()), 1000 + lo_, None))
+                e.sync()
+                okk = ok[ok >= lo_]
+                assert int(d_key.item()) == (1000 + int(okk[0]) if len(okk) else engine.NO_KEY)
             lnp, lbp, flp, firstp = pg.eval_batch_packed(big)          # 8-byte descriptors, same answers
             assert (lnp[~bad] == ln[~bad]).all() and (lbp[~bad] == lb[~bad]).all() and (flp == fl).all() and firstp == first
             if int_path:     # compact wire format: 4-byte descriptors in, int32 lengths out (exact on integer tables)

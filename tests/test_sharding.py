@@ -55,7 +55,10 @@ def _worker(rank, world, port, name, T, vns, cands, out):
     import torch
     local = fn(cands[lo:hi])[3]
     key = sharding.reduce_first_accept_(torch.tensor([local], dtype=torch.int64), lo)
-    out.put((rank, lo, hi, first, int(key.item()), float(ln.sum())))
+    # the sharded entry point (vnsgpu_eval_batch_dev_shard) writes index_base + local index or NO_KEY itself
+    from vns_sop_b200 import engine
+    key2 = sharding.reduce_key_(torch.tensor([engine.NO_KEY if local < 0 else lo + local], dtype=torch.int64))
+    out.put((rank, lo, hi, first, int(key.item()), float(ln.sum()), int(key2.item())))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -95,3 +98,5 @@ def test_two_rank_first_accept_equals_single_rank(case, golden):
     want_key = sharding.NONE if first1 < 0 else first1
     assert res[0][4] == res[1][4] == want_key
     assert abs(res[0][5] + res[1][5] - float(ln.sum())) < 1e-6
+    from vns_sop_b200 import engine
+    assert res[0][6] == res[1][6] == (engine.NO_KEY if first1 < 0 else first1)

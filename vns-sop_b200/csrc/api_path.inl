@@ -417,6 +417,27 @@ vnsgpu_status vnsgpu_eval_batch_dev(vnsgpu_ctx *ctx, int path, int64_t n, const 
                       useseg);
 }
 
+// One rank's shard of a batch that several GPUs evaluate: the key of the first accepted candidate comes
+// out as index_base + local index, VNSGPU_NO_KEY when the shard has none - the ranks all-reduce(MIN) the 8 bytes as they
+// are (no conversion kernels between the evaluation and the collective).
+vnsgpu_status vnsgpu_eval_batch_dev_shard(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *d_cands, double budget, int skip,
+                                          double *d_len, double *d_lb, uint8_t *d_flags, long long *d_first_key, int64_t index_base,
+                                          void *stream)
+{
+   if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
+   if (!d_first_key || index_base < 0) return VNSGPU_E_RANGE;
+   cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+   CK(cudaMemsetAsync(d_first_key, 0x7F, sizeof(long long), st));     // VNSGPU_NO_KEY: above every index, positive as int64
+   if (n <= 0) return VNSGPU_OK;
+   const int useseg = eval_mode(ctx, n);
+   {
+      vnsgpu_status s = prepare_eval(ctx, path, useseg, st);
+      if (s) return s;
+   }
+   return launch_eval(ctx, path, n, index_base, d_cands, budget, skip, d_len, d_lb, d_flags, (unsigned long long *)d_first_key, st, 0, 0,
+                      useseg);
+}
+
 // Host buffers.  The batch is cut into chunks that flow through three streams - H2D of chunk c+1, the
 // kernel on chunk c and D2H of chunk c-1 overlap - so the call runs at PCIe speed when the caller's
 // buffers are pinned (pageable buffers work, the copies then serialise inside the driver).

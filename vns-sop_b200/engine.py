@@ -13,6 +13,7 @@ from . import build as _build
 
 OP_ADD, OP_REPLACE, OP_REMOVE, OP_MOVE, OP_EXCHANGE = range(5)
 F_FEASIBLE, F_ACCEPT, F_LB_SKIP, F_BAD = 1, 2, 4, 8
+NO_KEY = 0x7f7f7f7f7f7f7f7f      # VNSGPU_NO_KEY
 CAND_DTYPE = np.dtype([("op", np.int32), ("a", np.int32), ("b", np.int32), ("gain_cluster", np.int32)])
 
 _STATUS = {1: "E_RANGE", 2: "E_CUDA", 3: "E_STATE", 4: "E_INCONSISTENT", 5: "E_NOMEM"}
@@ -80,6 +81,7 @@ _SIGS = {
     "vnsgpu_eval_batch_packed32": [vp, C.c_int, C.c_int64, vp, C.c_double, C.c_int, vp, vp, C.POINTER(C.c_int64)],
     "vnsgpu_eval_batch_packed32r": [vp, C.c_int, C.c_int64, vp, C.c_double, C.c_int, vp, C.POINTER(C.c_int64)],
     "vnsgpu_eval_batch_dev": [vp, C.c_int, C.c_int64, vp, C.c_double, C.c_int, vp, vp, vp, vp, vp],
+    "vnsgpu_eval_batch_dev_shard": [vp, C.c_int, C.c_int64, vp, C.c_double, C.c_int, vp, vp, vp, vp, C.c_int64, vp],
     "vnsgpu_gen_proposals": [vp, C.c_int, C.c_int, C.c_int64, C.POINTER(Rng), vp],
     "vnsgpu_cand_bytes": [vp, C.c_int, C.c_int64, vp, C.POINTER(C.c_int64)],
     "vnsgpu_local_search": [vp, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.POINTER(Rng), C.POINTER(LsStats)],

@@ -48,6 +48,15 @@ def reduce_first_accept_(key_tensor, lo: int, group=None):
     return key_tensor
 
 
+def reduce_key_(key_tensor, group=None):
+    """The exchange step of vnsgpu_eval_batch_dev_shard: key_tensor is the one-element int64 tensor the engine wrote
+    (index_base + local index, or NO_KEY); one all-reduce(MIN), nothing else on the stream."""
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(key_tensor, op=dist.ReduceOp.MIN, group=group)
+    return key_tensor
+
+
 def sharded_first_accept(eval_fn, cands: np.ndarray, rank: int, world: int, group=None, device=None):
     """Evaluate rank's shard of `cands` with eval_fn(shard) -> (len, lb, flags, local_first) and
     reduce the chosen move.  Returns (lo, hi, len, lb, flags, global_first)."""
