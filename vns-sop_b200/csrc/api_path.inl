@@ -244,11 +244,11 @@ static vnsgpu_status prepare_seg(vnsgpu_ctx *ctx, int path, cudaStream_t st)
    if (smem <= (size_t)ctx->max_smem && I.mp <= 32 && I.N < 65536) {
       const int grid = std::min(I.rows, I.C + 2);
       if (nst == 16) {
-         if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k_seg_build<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-         k_seg_build<16><<<grid, VNS_SEG_THREADS, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta);
+         if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k_seg_build<16, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+         k_seg_build<16, 4><<<grid, VNS_SEG_THREADS, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta);
       } else {
-         if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k_seg_build<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-         k_seg_build<8><<<grid, VNS_SEG_THREADS, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta);
+         if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k_seg_build<8, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+         k_seg_build<8, 1><<<grid, VNS_SEG_THREADS, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta);
       }
    } else
       k_seg_build_g<<<I.rows, 128, 0, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta);

@@ -561,7 +561,9 @@ __host__ __device__ inline size_t seg_build_smem(int rows, int mp, int nst)
    return sizeof(int) * ((size_t)(((rows + 3) + 3) & ~3) + (size_t)nst * ((mp * mp + 3) & ~3) + (size_t)32 * 32);
 }
 
-template <int NST>
+// U steps per barrier (small clusters: a step is a few hundred cycles of work, the barrier + wait + fetch round costs as
+// much): the U table blocks of a round have landed before its barrier, the rows stay warp-private in between.
+template <int NST, int U>
 __global__ void __launch_bounds__(VNS_SEG_THREADS) k_seg_build(InstDev I, PathDev P, int *Dv, const int *meta)
 {
    extern __shared__ __align__(16) int smem_i[];
@@ -596,7 +598,8 @@ __global__ void __launch_bounds__(VNS_SEG_THREADS) k_seg_build(InstDev I, PathDe
       }
       asm volatile("cp.async.commit_group;");
    };
-   for (int b = a + 2; b <= a + NST; ++b) fetch(dblk + (b % NST) * mp2, b - 1);   // step b multiplies by D(b-1,b)
+   static_assert(NST >= 2 * U && NST % U == 0, "ring of NST blocks, U per round");
+   for (int b = a + 2; b < a + 2 + NST - U; ++b) fetch(dblk + (b % NST) * mp2, b - 1);   // step b multiplies by D(b-1,b)
    {   // M(a,a+1) = D(a,a+1): this warp's rows
       const int m1 = l_m[a + 1];
       const int *src = Dv + ((long long)l_off[a] * I.N + (long long)ma * l_off[a + 1]);
@@ -607,10 +610,14 @@ __global__ void __launch_bounds__(VNS_SEG_THREADS) k_seg_build(InstDev I, PathDe
       }
       __syncwarp();
    }
-   for (int b = a + 2; b <= S; ++b) {
-      asm volatile("cp.async.wait_group %0;" ::"n"(NST - 2));   // all but the blocks of the NST - 2 steps ahead have landed
+   for (int b0 = a + 2; b0 <= S; b0 += U) {
+      // invariant: fetched through step b0 + NST - U - 1; the blocks of steps b0 .. b0 + U - 1 are the oldest U groups
+      asm volatile("cp.async.wait_group %0;" ::"n"(NST - 2 * U));
       __syncthreads();
-      fetch(dblk + ((b + NST - 1) % NST) * mp2, b + NST - 2);   // that buffer was read by step b-1
+#pragma unroll
+      for (int u = 0; u < U; ++u) fetch(dblk + ((b0 + NST - U + u) % NST) * mp2, b0 + NST - U + u - 1);   // slots of the previous round
+#pragma unroll 1
+      for (int b = b0; b < b0 + U && b <= S; ++b) {
       const int mk = l_m[b - 1], mb = l_m[b];
       const int *d = dblk + (b % NST) * mp2 + min(lane, mb - 1);
       int acc[4] = {INF, INF, INF, INF};
@@ -639,6 +646,7 @@ __global__ void __launch_bounds__(VNS_SEG_THREADS) k_seg_build(InstDev I, PathDe
       }
       __syncwarp();
       ooff += ma * mb;
+      }
    }
    asm volatile("cp.async.wait_group 0;");
 }
