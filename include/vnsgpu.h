@@ -106,7 +106,9 @@ vnsgpu_status vnsgpu_sync(vnsgpu_ctx *ctx);
 vnsgpu_status vnsgpu_set_int_path(vnsgpu_ctx *ctx, int enable);
 int vnsgpu_int_path_active(const vnsgpu_ctx *ctx);
 /* Batches of >= 8192 candidates are evaluated in chain-length order (a device-side counting sort of the
- * descriptors; results still land at the caller's indices).  enable = 0 keeps the caller's order. */
+ * descriptors; results still land at the caller's indices).  The endpoint-vector form keeps the caller's order on
+ * cache-resident tables with small clusters (nothing to gain there) and sorts by product row on tables beyond the
+ * caches (L2 locality).  enable = 0 keeps the caller's order everywhere. */
 vnsgpu_status vnsgpu_set_batch_sort(vnsgpu_ctx *ctx, int enable);
 /* Integer tables, batches of >= 16384: the min-plus product of every run of consecutive path layers is
  * built once per call and shared by all candidates (exactly associative on integers: bit-identical
