@@ -665,7 +665,7 @@ def run_b200(args):
         assert torch.equal(h_len[:4096], d_len[:4096].cpu()), "host and device entry points disagree"
 
     hbm_regime = eng.table_bytes / 2 > (48 << 20)      # the library's own switch (vec_lat): int32 table beyond 48 MiB
-    vec_mode = bool(int_path and args.vector_cache and pb.m.max() <= 32 and (4 * n >= pb.C * pb.C or args.vector_cache == 2))
+    vec_mode = bool(int_path and args.vector_cache and pb.m.max() <= 32 and ((16 if pb.m.max() > 16 else 4) * n >= pb.C * pb.C or args.vector_cache == 2))
     peak, peak_src = measured_hbm_peak()
     achieved = alg_bytes / (kern_ms * 1e-3) / 1e9
     line = {

@@ -223,12 +223,13 @@ static bool seg_wanted(const vnsgpu_ctx *ctx, int64_t n)
 // evaluation form of a batch: 0 block by block, 1 segment products, 2 endpoint vectors + segment products.
 // The vectors cost 2 C (T+2) + 4 T (T+2) block steps per path state (T is only known on the device; typically
 // T ~ C / 3) and save ~4 block steps per candidate.  Measured break-even on the HBM-sized instances (batch sweeps
-// r1t): 0.9 M candidates at C = 2002, m = 10 and 0.35 M at C = 2002, m = 32 - hence batch >= C^2 / 4.
+// r1t, r2d): 0.6 M candidates at C = 2002, m = 10 and 0.2 M at C = 2002, m = 32 - hence batch >= C^2 / 4, C^2 / 16 for
+// clusters of more than 16 samples (the 4 KB block gathers of the product form cost more than their bytes).
 static int eval_mode(const vnsgpu_ctx *ctx, int64_t n)
 {
    if (!seg_wanted(ctx, n)) return 0;
    const int64_t C = ctx->I.C;
-   if (ctx->use_vec && ctx->I.mp <= 32 && (4 * n >= C * C || ctx->use_vec == 2) && vec_ints((int)C, (int)C + 2, ctx->I.mp) < (1ull << 31)) return 2;
+   if (ctx->use_vec && ctx->I.mp <= 32 && ((ctx->I.mp > 16 ? 16 : 4) * n >= C * C || ctx->use_vec == 2) && vec_ints((int)C, (int)C + 2, ctx->I.mp) < (1ull << 31)) return 2;
    return 1;
 }
 
@@ -378,7 +379,17 @@ static vnsgpu_status launch_eval(vnsgpu_ctx *ctx, int path, int64_t n, int64_t i
       if (lat) VNS_LAUNCH_VEC_L(GG, RR, true);                                                                        \
       else VNS_LAUNCH_VEC_L(GG, RR, false);                                                                           \
    } while (0)
-         const bool lat = vec_lat(ctx);
+         // tables beyond the caches: the same cache form of the kernel (64 registers, 4 CTAs / SM) with the NEXT candidate's
+         // block and vectors prefetched into L1 one iteration ahead.  The LAT form (all row loads of a block step in
+         // flight, 128 registers) is kept for comparison: VNSGPU_HBM_FORM = pf1 (default) | pf2 | lat1 | lat2 (form and
+         // prefetch distance).  ncu r2c, 4 Mi candidates: 64 k-sample DOP table lat1 1.48 ms, pf1 1.17 ms; 20 k-node
+         // table 0.93 -> 0.74 ms; distance 2 changes nothing.
+         static const char *hbm_form = getenv("VNSGPU_HBM_FORM");
+         const bool hbm = vec_lat(ctx);
+         const bool lat = hbm && hbm_form && hbm_form[0] == 'l';
+         static const char *pf_all = getenv("VNSGPU_PF_ALL");      // experiment: prefetch on cache-resident tables as well
+         if (!hbm && pf_all && pf_all[0] == '1') fmt |= 1 << 4;
+         if (hbm) fmt |= ((hbm_form && hbm_form[0] && hbm_form[strlen(hbm_form) - 1] == '2') ? 2 : 1) << 4;
          if (G == 8 && NR == 1) VNS_LAUNCH_VEC(8, 1);
          else if (G == 8 && NR == 2) VNS_LAUNCH_VEC(8, 2);
          else if (G == 8) VNS_LAUNCH_VEC(8, 4);

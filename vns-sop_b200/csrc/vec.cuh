@@ -298,7 +298,7 @@ k_eval_vec(InstDev I, const int *__restrict__ Dv, PathDev P, SegCache seg, VecCa
            double *__restrict__ len, double *__restrict__ lb, uint8_t *__restrict__ flags, unsigned long long *d_first,
            int fmt, int *__restrict__ leni)
 {
-   // fmt & 3: 0 = vnsgpu_cand (16 B), 2 = vnsgpu_pack_cand32 words (4 B) read in place; leni: lengths as int32 (may be
+   // fmt & 3: 0 = vnsgpu_cand (16 B), 2 = vnsgpu_pack_cand32 words (4 B) read in place; (fmt >> 4) & 3: prefetch distance; leni: lengths as int32 (may be
    // null), with fmt & 4 as result words: length | flags << 29, all ones for bad indices (vnsgpu_eval_batch_packed32r)
    extern __shared__ int smem_i[];
    constexpr unsigned FULL = 0xffffffffu;
@@ -381,11 +381,12 @@ k_eval_vec(InstDev I, const int *__restrict__ Dv, PathDev P, SegCache seg, VecCa
             vA[r] = j < mA ? __ldg(vc.vec + (offA + (unsigned)j)) : INF;      // one 32-bit add, then base + 4 * index
             vB[r] = j < mB ? __ldg(vc.vec + (offB + (unsigned)j)) : INF;
          }
-         if (LAT && it + 1 < G) {
+         const int pd = (fmt >> 4) & 3;                        // prefetch distance in iterations (0: none); kernel-uniform
+         if (pd && it + pd < G) {
             // tables beyond the caches: while this iteration's loads are in flight, pull the NEXT candidate's block rows
             // (one prefetch per lane = one row) and its two vectors into L1 - an iteration is otherwise one exposed
             // memory round trip after the other (ncu r1u: 24 % of the warp slots occupied, DRAM and L2 at 15 %)
-            const int cn = c + NG;
+            const int cn = c + pd * NG;
             const unsigned pkn = __shfl_sync(FULL, p_pack, cn);
             const long long rbn = __shfl_sync(FULL, p_rb, cn);
             const unsigned oAn = __shfl_sync(FULL, vcd.offA, cn), oBn = __shfl_sync(FULL, vcd.offB, cn);
