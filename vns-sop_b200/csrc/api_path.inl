@@ -379,17 +379,8 @@ static vnsgpu_status launch_eval(vnsgpu_ctx *ctx, int path, int64_t n, int64_t i
       if (lat) VNS_LAUNCH_VEC_L(GG, RR, true);                                                                        \
       else VNS_LAUNCH_VEC_L(GG, RR, false);                                                                           \
    } while (0)
-         // tables beyond the caches: the same cache form of the kernel (64 registers, 4 CTAs / SM) with the NEXT candidate's
-         // block and vectors prefetched into L1 one iteration ahead.  The LAT form (all row loads of a block step in
-         // flight, 128 registers) is kept for comparison: VNSGPU_HBM_FORM = pf1 (default) | pf2 | lat1 | lat2 (form and
-         // prefetch distance).  ncu r2c, 4 Mi candidates: 64 k-sample DOP table lat1 1.48 ms, pf1 1.17 ms; 20 k-node
-         // table 0.93 -> 0.74 ms; distance 2 changes nothing.
-         static const char *hbm_form = getenv("VNSGPU_HBM_FORM");
-         const bool hbm = vec_lat(ctx);
-         const bool lat = hbm && hbm_form && hbm_form[0] == 'l';
-         static const char *pf_all = getenv("VNSGPU_PF_ALL");      // experiment: prefetch on cache-resident tables as well
-         if (!hbm && pf_all && pf_all[0] == '1') fmt |= 1 << 4;
-         if (hbm) fmt |= ((hbm_form && hbm_form[0] && hbm_form[strlen(hbm_form) - 1] == '2') ? 2 : 1) << 4;
+         // tables beyond the caches: the same kernel with the NEXT candidate's block and vectors prefetched into L1
+         const bool lat = vec_lat(ctx);
          if (G == 8 && NR == 1) VNS_LAUNCH_VEC(8, 1);
          else if (G == 8 && NR == 2) VNS_LAUNCH_VEC(8, 2);
          else if (G == 8) VNS_LAUNCH_VEC(8, 4);

@@ -289,16 +289,18 @@ __device__ __forceinline__ VecCode decode_cand_vec(const VecCache &vc, int T, in
    return v;
 }
 
-// LAT: the table does not fit the caches (synthetic scaled instances) - every block step issues all its G row loads
-// before the first min (one memory round trip per step instead of G / 2); rows beyond the block re-read its last row.
-template <int G, int NR, bool LAT>
-__global__ void __launch_bounds__(VNS_EVAL_THREADS, LAT ? 2 : (NR > 2 ? 3 : 4))  // CTAs / SM: cache-resident form 4 (64 registers; 3 with four registers per vector), LAT 2 (128)
+// PF: the table does not fit the caches (synthetic scaled instances) - while an iteration's loads are in flight the next
+// candidate's block rows and vectors are prefetched into L1 (compiled in only there: on cache-resident tables the extra
+// registers cost up to 10 %).  An earlier form for these tables issued all G row loads of a block step before the first
+// min (128 registers, 2 CTAs / SM): 1.48 ms against 1.17 ms for this one on the 64 k-sample DOP table (ncu r2c).
+template <int G, int NR, bool PF>
+__global__ void __launch_bounds__(VNS_EVAL_THREADS, NR > 2 ? 3 : 4)  // CTAs / SM: 4 (64 registers), 3 with four registers per vector
 k_eval_vec(InstDev I, const int *__restrict__ Dv, PathDev P, SegCache seg, VecCache vc, long long n, long long idx0,
            const void *__restrict__ cands, const unsigned *__restrict__ perm, double budget, int skipflag,
            double *__restrict__ len, double *__restrict__ lb, uint8_t *__restrict__ flags, unsigned long long *d_first,
            int fmt, int *__restrict__ leni)
 {
-   // fmt & 3: 0 = vnsgpu_cand (16 B), 2 = vnsgpu_pack_cand32 words (4 B) read in place; (fmt >> 4) & 3: prefetch distance; leni: lengths as int32 (may be
+   // fmt & 3: 0 = vnsgpu_cand (16 B), 2 = vnsgpu_pack_cand32 words (4 B) read in place; leni: lengths as int32 (may be
    // null), with fmt & 4 as result words: length | flags << 29, all ones for bad indices (vnsgpu_eval_batch_packed32r)
    extern __shared__ int smem_i[];
    constexpr unsigned FULL = 0xffffffffu;
@@ -381,12 +383,11 @@ k_eval_vec(InstDev I, const int *__restrict__ Dv, PathDev P, SegCache seg, VecCa
             vA[r] = j < mA ? __ldg(vc.vec + (offA + (unsigned)j)) : INF;      // one 32-bit add, then base + 4 * index
             vB[r] = j < mB ? __ldg(vc.vec + (offB + (unsigned)j)) : INF;
          }
-         const int pd = (fmt >> 4) & 3;                        // prefetch distance in iterations (0: none); kernel-uniform
-         if (pd && it + pd < G) {
+         if (PF && it + 1 < G) {
             // tables beyond the caches: while this iteration's loads are in flight, pull the NEXT candidate's block rows
             // (one prefetch per lane = one row) and its two vectors into L1 - an iteration is otherwise one exposed
-            // memory round trip after the other (ncu r1u: 24 % of the warp slots occupied, DRAM and L2 at 15 %)
-            const int cn = c + pd * NG;
+            // memory round trip after the other
+            const int cn = c + NG;
             const unsigned pkn = __shfl_sync(FULL, p_pack, cn);
             const long long rbn = __shfl_sync(FULL, p_rb, cn);
             const unsigned oAn = __shfl_sync(FULL, vcd.offA, cn), oBn = __shfl_sync(FULL, vcd.offB, cn);
@@ -402,7 +403,7 @@ k_eval_vec(InstDev I, const int *__restrict__ Dv, PathDev P, SegCache seg, VecCa
             }
          }
          if ((pk >> 25) & 1) {                                 // warp-uniform: some group of this iteration has a block
-            const int trip = blk ? mA : 1, nvalid = blk ? mB : 1;
+            const int nvalid = blk ? mB : 1;
             int acc[NR];
 #pragma unroll
             for (int rd = 0; rd < NR; ++rd) {
@@ -412,18 +413,10 @@ k_eval_vec(InstDev I, const int *__restrict__ Dv, PathDev P, SegCache seg, VecCa
 #pragma unroll
                   for (int rs = 0; rs < NR; ++rs) {
                      if (rs == 0 || tmaxAll > rs * G) {         // warp-uniform
-                        const int tlim = max(min(trip - rs * G, G) - 1, 0);
-                        const unsigned sb = cbase + (unsigned)(min(rs * G, trip - 1) * nvalid);
                         const int tm = min(tmaxAll - rs * G, G);
                         const int opnd = vA[rs];
-                        if (LAT) {
-                           int dd[G];
-#pragma unroll
-                           for (int t = 0; t < G; ++t) dd[t] = __ldg(blkp + (sb + (unsigned)(min(t, tlim) * nvalid)));
-#pragma unroll
-                           for (int t = 0; t < G; ++t) acc[rd] = __viaddmin_s32(__shfl_sync(FULL, opnd, min(t, tlim), G), dd[t], acc[rd]);
-                        } else {
-                           // cache-resident tables: eight unrolled steps at a time, rows unclamped - per step one
+                        {
+                           // eight unrolled steps at a time, rows unclamped - per step one
                            // IMAD.WIDE (row address), LDG, SHFL with an immediate lane and VIADDMNMX, the eight loads
                            // in flight together.  Rows beyond this group's block pair a sample that is INF (vA beyond
                            // mA) with whatever follows the block: table entries, products or the zeroed rest of the
