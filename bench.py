@@ -581,7 +581,11 @@ def run_b200(args):
         h_res = torch.empty(n, dtype=torch.int32).pin_memory() if int_path else None
 
         def host_step(packed=1):
-            if packed == 3:     # 4 B descriptors in, ONE 4 B result word (length | flags << 29) out
+            if packed == 4:     # 4 B descriptors in, only the chosen move (first accepted index) out: what insertRandom /
+                                # exchangeRandom consume (vns_sop_solver.cpp:619-646, :805-832)
+                eng._ck(lib.vnsgpu_eval_batch_packed32(eng.h, p.h, n, C.c_void_p(h_pk32.data_ptr()), pb.budget, 1,
+                                                       None, None, C.byref(first)))
+            elif packed == 3:   # 4 B descriptors in, ONE 4 B result word (length | flags << 29) out
                 eng._ck(lib.vnsgpu_eval_batch_packed32r(eng.h, p.h, n, C.c_void_p(h_pk32.data_ptr()), pb.budget, 1,
                                                         C.c_void_p(h_res.data_ptr()), C.byref(first)))
             elif packed == 2:
@@ -621,6 +625,12 @@ def run_b200(args):
             first5 = first.value
             sub5 = {"value": world * n * K / dt5, "ms_per_step": 1e3 * dt5 / K, "call": "vnsgpu_eval_batch_packed32",
                     "h2d_bytes_per_step": world * n * 4, "d2h_bytes_per_step": world * (n * 5 + 8)}
+            dt0, _ = timed(4)
+            first0 = first.value
+            sub0 = {"value": world * n * K / dt0, "ms_per_step": 1e3 * dt0 / K, "call": "vnsgpu_eval_batch_packed32 (len = flags = NULL)",
+                    "h2d_bytes_per_step": world * n * 4, "d2h_bytes_per_step": world * 8,
+                    "what": "only the index of the first accepted candidate comes back - the one result the reference's "
+                            "insertRandom / exchangeRandom loops consume"}
             dt, nl = timed(3)
             launches += nl
             in_b, out_b = 4, 4
@@ -629,10 +639,10 @@ def run_b200(args):
                    "call": "vnsgpu_eval_batch_packed32r (pinned host buffers: 4 B descriptors in; one 4 B result word per "
                            "candidate out = int32 length - exact on this all-integer table - | flags << 29, + first accepted "
                            "index); replayed as one CUDA graph launch",
-                   "with_4B_descriptors_i32_lengths_u8_flags": sub5, "with_8B_descriptors_f64_lengths": sub8,
+                   "first_accept_only": sub0, "with_4B_descriptors_i32_lengths_u8_flags": sub5, "with_8B_descriptors_f64_lengths": sub8,
                    "with_16B_descriptors": sub16}
             if world == 1:
-                assert first.value == first8 == first5, "compact and 8-byte entry points disagree on the first accepted candidate"
+                assert first.value == first8 == first5 == first0, "compact and 8-byte entry points disagree on the first accepted candidate"
             assert torch.equal(h_len32[:65536].double(), h_len[:65536]), "compact entry point: lengths differ"
             w = h_res.numpy().view(np.uint32)[:65536]
             assert ((w & 0x1fffffff) == h_len32.numpy()[:65536]).all() and ((w >> 29) == h_fl.numpy()[:65536]).all(), \
