@@ -578,6 +578,9 @@ __global__ void __launch_bounds__(VNS_SEG_THREADS) k_seg_build(InstDev I, PathDe
       const int c = layer_cluster(I, P.tg, T, l);
       l_m[l] = (unsigned short)I.m[c]; l_off[l] = (unsigned short)I.off[c];
    }
+   // ring and rows start as zeros: the product loop reads up to three rows past a staged block (below) and must find
+   // numbers in [0, INF] there - zeros, older blocks, or the rows of the running product that follow the ring
+   for (int e = threadIdx.x; e < NST * mp2 + 32 * 32; e += blockDim.x) dblk[e] = 0;
    __syncthreads();
    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
    const int ma = l_m[a];
@@ -621,8 +624,10 @@ __global__ void __launch_bounds__(VNS_SEG_THREADS) k_seg_build(InstDev I, PathDe
       const int mk = l_m[b - 1], mb = l_m[b];
       const int *d = dblk + (b % NST) * mp2 + min(lane, mb - 1);
       int acc[4] = {INF, INF, INF, INF};
-      for (int k4 = 0; k4 < mk; k4 += 4) {
-         const int d0 = d[k4 * mb], d1 = d[min(k4 + 1, mk - 1) * mb], d2 = d[min(k4 + 2, mk - 1) * mb], d3 = d[min(k4 + 3, mk - 1) * mb];
+      for (int k4 = 0; k4 < mk; k4 += 4, d += 4 * mb) {
+         // rows k >= mk (at most three, when mk is not a multiple of 4) are read UNCLAMPED: they pair whatever follows the
+         // block in shared memory (see above) with the INF the product's row holds beyond column mk - never the minimum
+         const int d0 = d[0], d1 = d[mb], d2 = d[2 * mb], d3 = d[3 * mb];
 #pragma unroll
          for (int r = 0; r < 4; ++r) {
             if (w + 8 * r < ma) {                            // warp-uniform
