@@ -10,8 +10,12 @@ LIB = os.path.join(HERE, "libvnsgpu.so")
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
     "-fmad=false",          # parity: no FMA contraction (dx*dx+dy*dy in the table build, Dubins terms)
-    "-Xcompiler", "-fPIC", "-shared",
+    "-Xcompiler", "-fPIC",
 ]
+# translation units of the library (each compiled on its own core, then linked; no relocatable device code: no kernel
+# calls a device function of another unit)
+UNITS = ["vnsgpu.cu", "api_path.cu", "api_search.cu", "chain2.cu", "comm.cu", "noalloc.cu"]
+OBJ = os.path.join(HERE, "build")
 
 
 def sources():
@@ -25,15 +29,53 @@ def stale():
     return any(os.path.getmtime(s) > t for s in sources())
 
 
+def _unit_deps(unit):
+    """headers a unit includes (transitively, by scanning #include "..." lines)"""
+    seen, todo = set(), [unit]
+    while todo:
+        f = todo.pop()
+        if f in seen:
+            continue
+        seen.add(f)
+        path = os.path.normpath(os.path.join(CSRC, f))
+        if not os.path.exists(path):
+            continue
+        for line in open(path):
+            line = line.strip()
+            if line.startswith('#include "'):
+                todo.append(line.split('"')[1])
+    return [os.path.normpath(os.path.join(CSRC, f)) for f in seen]
+
+
 def build(force=False, verbose=False):
     if not force and not stale():
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    # VNSGPU_SPLIT_COMPILE=1: NVVM + ptxas of this one translation unit on all host cores (80 s instead of 4 min) - for
-    # development only: the split changes register allocation (the latency-bound chain kernels lose ~10 %)
-    split = ["-split-compile", "0"] if os.environ.get("VNSGPU_SPLIT_COMPILE") == "1" else []
-    cmd = [nvcc] + NVCC_FLAGS + split + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB, os.path.join(CSRC, "vnsgpu.cu")]
-    subprocess.check_call(cmd, cwd=CSRC)
+    os.makedirs(OBJ, exist_ok=True)
+    units = [u for u in UNITS if os.path.exists(os.path.join(CSRC, u))]
+    procs, objs = [], []
+    for u in units:
+        o = os.path.join(OBJ, u.replace(".cu", ".o"))
+        objs.append(o)
+        deps = _unit_deps(u)
+        if not force and os.path.exists(o) and all(os.path.getmtime(d) <= os.path.getmtime(o) for d in deps if os.path.exists(d)):
+            continue
+        cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", "-o", o, os.path.join(CSRC, u)]
+        log = open(o + ".log", "w")
+        procs.append((u, subprocess.Popen(cmd, cwd=CSRC, stdout=log, stderr=subprocess.STDOUT), log))
+    failed = []
+    for u, p, log in procs:
+        rc = p.wait()
+        log.close()
+        if rc != 0:
+            failed.append(u)
+    if verbose or failed:
+        for u, p, log in procs:
+            print("---- %s ----" % u)
+            print(open(log.name).read())
+    if failed:
+        raise RuntimeError("nvcc failed on " + ", ".join(failed))
+    subprocess.check_call([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB] + objs, cwd=CSRC)
     return LIB
 
 

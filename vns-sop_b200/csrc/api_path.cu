@@ -1,41 +1,10 @@
-// C ABI: path handles + batched evaluation (included by vnsgpu.cu)
-
-static bool path_ok(vnsgpu_ctx *ctx, int path)
-{
-   if (!ctx->have_table) { ctx->err = "no distance table"; return false; }
-   if (path < 0 || path >= (int)ctx->paths.size() || !ctx->paths[path].block) { ctx->err = "bad path handle"; return false; }
-   return true;
-}
-
-static size_t al16(size_t x) { return (x + 15) & ~(size_t)15; }
-
-// host mirror of the path header (read back after every mutating call)
-struct PathHdr {
-   int hdr[HDR_INTS];
-   double hd[HD_DBLS];
-};
-
-static vnsgpu_status read_hdr(vnsgpu_ctx *ctx, int path, PathHdr *h)
-{
-   const PathDev &d = ctx->paths[path].d;
-   // hdr and hd are adjacent at the start of the block
-   CK(cudaMemcpyAsync(h, d.hdr, sizeof(PathHdr), cudaMemcpyDeviceToHost, ctx->stream));
-   CK(cudaStreamSynchronize(ctx->stream));
-   return VNSGPU_OK;
-}
-
-static vnsgpu_status check_path_err(vnsgpu_ctx *ctx, int path)
-{
-   PathHdr h;
-   vnsgpu_status s = read_hdr(ctx, path, &h);
-   if (s) return s;
-   if (h.hdr[HDR_ERR] == 4) return fail(ctx, VNSGPU_E_INCONSISTENT, "forward/backward path length mismatch");
-   if (h.hdr[HDR_ERR] == 3) return fail(ctx, VNSGPU_E_STATE, "proposal rejection loop did not terminate");
-   if (h.hdr[HDR_ERR]) return fail(ctx, VNSGPU_E_STATE, "device-side error flag");
-   return VNSGPU_OK;
-}
-
-static size_t chain_smem(const vnsgpu_ctx *ctx) { return sizeof(double) * 2 * ctx->I.mp * VNS_CHAIN_WARPS; }
+// C ABI: path handles + batched evaluation
+#include "ctx.hpp"
+#include "path.cuh"
+#include "search.cuh"
+#include "eval.cuh"
+#include "vec.cuh"
+#include "kernels.cuh"
 
 extern "C" {
 

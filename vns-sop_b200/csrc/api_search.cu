@@ -1,4 +1,10 @@
-// C ABI: RNG replay + neighbourhood drivers (included by vnsgpu.cu)
+// C ABI: RNG replay + neighbourhood drivers
+#include "ctx.hpp"
+#include "path.cuh"
+#include "search.cuh"
+#include "eval.cuh"
+#include "chain.cuh"
+#include "kernels_search.cuh"
 
 // insertRandom / exchangeRandom: the shared-memory chain (chain.cuh) when the state fits one SM's shared
 // memory, else the global-memory chain of search.cuh

@@ -15,6 +15,8 @@
 #define VNS_M 1.7976931348623157e308  // numeric_limits<double>::max(), vns_sop_path.cpp:10
 #define VNS_MIN_CHANGE_EPS 0.00001    // vns_sop_solver.cpp:15
 #define VNS_WARP 32
+#define VNS_CHAIN_THREADS 512   // CTA size of the global-memory chain kernels (search.cuh)
+#define VNS_CHAIN_WARPS (VNS_CHAIN_THREADS / 32)
 
 struct InstDev {
    int C, N, mp, start, goal;
@@ -106,3 +108,23 @@ inline void rng_seed_host(RngState &g, uint32_t seed)
    g.pad = 0;
    for (int i = 0; i < 310; ++i) rng_next(g);
 }
+
+// ---- plain structs shared by the host API units and the search kernels ---------------------------
+struct LsStats {
+   long long proposals, lb_skips, evals, accepts, rounds;
+};
+struct VnsParamsDev {
+   int num_iterations, num_iterations_unimproved, skip, greedy;
+   double budget, max_time_ms;
+   int max_improvements;
+   // multi-start race (vnsgpu_set_target_reward): the first run whose tour reaches target_reward raises *stop_flag and
+   // every run leaves at its next shake; null = off (the reference's stopping rules only)
+   double target_reward;
+   int *stop_flag;
+};
+struct VnsResultDev {
+   int num_iters, num_iters_last_impr, n_improvements, status;
+   double reward, length, time_ms, time_last_impr_ms;
+   long long proposals, evals, accepts;
+};
+

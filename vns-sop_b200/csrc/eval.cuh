@@ -423,7 +423,7 @@ __device__ __forceinline__ int sort_key(int T, int C, const int4 &cd, int useseg
 
 // ---- counting sort of a batch by chain length (descending): three light passes over the descriptors ----
 // hist / cursor: nb = rows + 1 counters each (chain lengths are < rows); perm: n indices.
-__global__ void __launch_bounds__(256) k_sort_hist(InstDev I, PathDev P, long long n, const vnsgpu_cand *__restrict__ cands, int nb,
+static __global__ void __launch_bounds__(256) k_sort_hist(InstDev I, PathDev P, long long n, const vnsgpu_cand *__restrict__ cands, int nb,
                                                    unsigned *__restrict__ hist, int useseg)
 {
    extern __shared__ unsigned smem_u[];
@@ -441,7 +441,7 @@ __global__ void __launch_bounds__(256) k_sort_hist(InstDev I, PathDev P, long lo
 
 // exclusive scan of the histogram in DESCENDING key order (longest chains first); one block of 1024 threads,
 // thread t owns the t-th chunk of keys counted from the top
-__global__ void __launch_bounds__(1024) k_sort_scan(int nb, const unsigned *__restrict__ hist, unsigned *__restrict__ cursor)
+static __global__ void __launch_bounds__(1024) k_sort_scan(int nb, const unsigned *__restrict__ hist, unsigned *__restrict__ cursor)
 {
    __shared__ unsigned part[1024];
    const int chunk = (nb + 1023) / 1024, t = threadIdx.x;
@@ -460,7 +460,7 @@ __global__ void __launch_bounds__(1024) k_sort_scan(int nb, const unsigned *__re
    for (int k = hi; k >= lo; --k) { cursor[k] = pos; pos += hist[k]; }
 }
 
-__global__ void __launch_bounds__(256) k_sort_scatter(InstDev I, PathDev P, long long n, const vnsgpu_cand *__restrict__ cands, int nb,
+static __global__ void __launch_bounds__(256) k_sort_scatter(InstDev I, PathDev P, long long n, const vnsgpu_cand *__restrict__ cands, int nb,
                                                       unsigned *__restrict__ cursor, unsigned *__restrict__ perm, int useseg)
 {
    extern __shared__ unsigned smem_u[];
@@ -490,7 +490,7 @@ __global__ void __launch_bounds__(256) k_sort_scatter(InstDev I, PathDev P, long
 // ---- segment-product cache (see SegCache) ------------------------------------------------------------
 // meta (ints): cum[R], pd[R], rowoff[R] as 64-bit (2R ints), lcl[R] (layer -> cluster), loff[R] (first sample of the
 // layer's cluster) with R = I.rows + 3 (rowoff starts 2R ints in: 8-byte aligned).  One block.
-__global__ void __launch_bounds__(256) k_seg_offsets(InstDev I, PathDev P, int *__restrict__ meta)
+static __global__ void __launch_bounds__(256) k_seg_offsets(InstDev I, PathDev P, int *__restrict__ meta)
 {
    extern __shared__ int smem_i[];
    const int T = P.hdr[HDR_T], S = T + 1, R = I.rows + 3;
@@ -519,7 +519,7 @@ __global__ void __launch_bounds__(256) k_seg_offsets(InstDev I, PathDev P, int *
 
 // block a builds M(a,b) for b = a+2 .. S by M(a,b) = M(a,b-1) (x) D(b-1,b), M(a,a+1) = D(a,a+1)
 // (global-memory form: any cluster size; every step is a global round trip)
-__global__ void __launch_bounds__(128) k_seg_build_g(InstDev I, PathDev P, int *Dv, const int *meta)
+static __global__ void __launch_bounds__(128) k_seg_build_g(InstDev I, PathDev P, int *Dv, const int *meta)
 {
    const int T = P.hdr[HDR_T], S = T + 1, R = I.rows + 3;
    const int a = blockIdx.x;

@@ -1,4 +1,5 @@
-// __global__ entry points over the device functions of path.cuh / search.cuh.
+// __global__ entry points over the device functions of path.cuh / search.cuh: path maintenance + the generic
+// batched evaluation (included by api_path.cu only).
 #pragma once
 #include <climits>
 
@@ -8,14 +9,14 @@
 
 // ---- path maintenance (single CTA per path) -------------------------------------------------------
 // VnsSopPath::update vns_sop_path.cpp:1321-1404
-__global__ void __launch_bounds__(64) k_path_update(InstDev I, PathDev P)
+static __global__ void __launch_bounds__(64) k_path_update(InstDev I, PathDev P)
 {
    cta_update(I, P, P.hdr[HDR_T]);
 }
 
 // addPoint(c, idx) (kind 0) / removePoint(idx) (kind 1) with the incremental re-scan ranges of
 // updateAfterInsert / updateAfterRemove (vns_sop_path.cpp:1406-1540).  Targets only.
-__global__ void __launch_bounds__(256) k_path_edit(InstDev I, PathDev P, int kind, int c, int idx)
+static __global__ void __launch_bounds__(256) k_path_edit(InstDev I, PathDev P, int kind, int c, int idx)
 {
    int T = P.hdr[HDR_T];
    __syncthreads();
@@ -34,13 +35,13 @@ __global__ void __launch_bounds__(256) k_path_edit(InstDev I, PathDev P, int kin
    if (threadIdx.x == 0) P.hd[HD_REWARD] = path_reward(I, P.tg, T);
 }
 
-__global__ void __launch_bounds__(256) k_path_copy(InstDev I, PathDev dst, PathDev src)
+static __global__ void __launch_bounds__(256) k_path_copy(InstDev I, PathDev dst, PathDev src)
 {
    cta_copy_path(I, dst, src);
 }
 
 // getPath + getPathLengthCalculate (vns_sop_path.cpp:1542-1599, 1700-1741)
-__global__ void k_path_solution(InstDev I, PathDev P, int *cluster, int *node, double *calc)
+static __global__ void k_path_solution(InstDev I, PathDev P, int *cluster, int *node, double *calc)
 {
    if (threadIdx.x == 0 && blockIdx.x == 0) *calc = path_walk_back(I, P, P.hdr[HDR_T], cluster, node);
 }
@@ -49,7 +50,7 @@ __global__ void k_path_solution(InstDev I, PathDev P, int *cluster, int *node, d
 // len = tryTo*(...), lb = tryTo*LowerBound(...), flags = feasibility / accept predicate / LB skip;
 // d_first receives the smallest accepted (and not LB-skipped when skip != 0) candidate index.
 // generic fallback for clusters with more than 32 samples (the group kernel of eval.cuh covers the rest)
-__global__ void __launch_bounds__(VNS_EVAL_THREADS) k_eval_batch(InstDev I, PathDev P, long long n, long long idx0, const vnsgpu_cand *__restrict__ cands,
+static __global__ void __launch_bounds__(VNS_EVAL_THREADS) k_eval_batch(InstDev I, PathDev P, long long n, long long idx0, const vnsgpu_cand *__restrict__ cands,
                                                                  double budget, int skipflag, double *__restrict__ len,
                                                                  double *__restrict__ lb, uint8_t *__restrict__ flags, unsigned long long *d_first)
 {
@@ -92,7 +93,7 @@ __global__ void __launch_bounds__(VNS_EVAL_THREADS) k_eval_batch(InstDev I, Path
    if (d_first && lane == 0 && best != ULLONG_MAX) atomicMin(d_first, best);
 }
 
-__global__ void __launch_bounds__(256) k_cand_bytes(InstDev I, PathDev P, long long n, const vnsgpu_cand *__restrict__ cands,
+static __global__ void __launch_bounds__(256) k_cand_bytes(InstDev I, PathDev P, long long n, const vnsgpu_cand *__restrict__ cands,
                                                     unsigned long long *total, int w)
 {
    const int T = P.hdr[HDR_T];
@@ -106,50 +107,3 @@ __global__ void __launch_bounds__(256) k_cand_bytes(InstDev I, PathDev P, long l
    if ((threadIdx.x & 31) == 0) atomicAdd(total, (unsigned long long)acc);
 }
 
-// ---- chain kernels: exactly one CTA of VNS_CHAIN_THREADS; dynamic smem = 2*mp*warps doubles -----------
-__global__ void __launch_bounds__(VNS_CHAIN_THREADS) k_local_search(InstDev I, PathDev P, int kind, int num_changes, double budget,
-                                                                    int skipflag, RngState *rng, LsStats *stats)
-{
-   extern __shared__ double smem_v[];
-   __shared__ LsShared sh;
-   if (threadIdx.x == 0) { sh.rng = *rng; sh.err = 0; sh.st = LsStats{0, 0, 0, 0, 0}; }
-   __syncthreads();
-   cta_local_search(I, P, kind, num_changes, budget, skipflag, sh, smem_v);
-   if (threadIdx.x == 0) { *rng = sh.rng; *stats = sh.st; }
-}
-
-__global__ void __launch_bounds__(VNS_CHAIN_THREADS) k_shake(InstDev I, PathDev P, int kind, double budget, RngState *rng, int *seg)
-{
-   extern __shared__ double smem_v[];
-   __shared__ RngState g;
-   if (threadIdx.x == 0) g = *rng;
-   __syncthreads();
-   cta_shake(I, P, kind, budget, g, seg, smem_v);
-   if (threadIdx.x == 0) *rng = g;
-}
-
-__global__ void __launch_bounds__(VNS_CHAIN_THREADS) k_fit(InstDev I, PathDev P, double budget)
-{
-   extern __shared__ double smem_v[];
-   int T = P.hdr[HDR_T];
-   cta_fit(I, P, T, budget, smem_v);
-   if (threadIdx.x == 0) P.hd[HD_REWARD] = path_reward(I, P.tg, T);
-}
-
-__global__ void __launch_bounds__(VNS_CHAIN_THREADS) k_greedy(InstDev I, PathDev P, double budget)
-{
-   extern __shared__ double smem_v[];
-   cta_greedy(I, P, budget, smem_v);
-}
-
-__global__ void __launch_bounds__(VNS_CHAIN_THREADS) k_vns_run(InstDev I, PathDev tour, PathDev act, VnsParamsDev prm, RngState *rng,
-                                                               VnsResultDev *res, double *impr_reward, double *impr_length,
-                                                               double *impr_ms, int *seg)
-{
-   extern __shared__ double smem_v[];
-   __shared__ LsShared sh;
-   if (threadIdx.x == 0) { sh.rng = *rng; sh.err = 0; sh.st = LsStats{0, 0, 0, 0, 0}; }
-   __syncthreads();
-   cta_vns_run(I, tour, act, prm, res, impr_reward, impr_length, impr_ms, sh, seg, smem_v);
-   if (threadIdx.x == 0) *rng = sh.rng;
-}

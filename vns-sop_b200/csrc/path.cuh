@@ -53,7 +53,7 @@ __device__ __forceinline__ void warp_bwd_layer(const InstDev &I, const PathDev &
 }
 
 // forward layers [lfrom, S] by the calling warp (lfrom >= 1; lfrom == 0 also initialises layer 0)
-__device__ void warp_fwd_scan(const InstDev &I, const PathDev &P, int T, int lfrom, int lane)
+static __device__ void warp_fwd_scan(const InstDev &I, const PathDev &P, int T, int lfrom, int lane)
 {
    const int S = T + 1;
    if (lfrom <= 0) {  // F[0][*] = 0: default ClusterNodeDist, heuristic_types.h:184-187
@@ -68,7 +68,7 @@ __device__ void warp_fwd_scan(const InstDev &I, const PathDev &P, int T, int lfr
 }
 
 // backward layers [lfrom, 0] by the calling warp (lfrom >= S initialises layer S)
-__device__ void warp_bwd_scan(const InstDev &I, const PathDev &P, int T, int lfrom, int lane)
+static __device__ void warp_bwd_scan(const InstDev &I, const PathDev &P, int T, int lfrom, int lane)
 {
    const int S = T + 1;
    if (lfrom >= S) {
@@ -83,7 +83,7 @@ __device__ void warp_bwd_scan(const InstDev &I, const PathDev &P, int T, int lfr
 }
 
 // getReward vns_sop_path.cpp:2016-2031 (left-to-right sum in targets order), one thread
-__device__ double path_reward(const InstDev &I, const int *tg, int T)
+static __device__ double path_reward(const InstDev &I, const int *tg, int T)
 {
    double r = 0;
    for (int t = 0; t < T; ++t) r += __ldg(I.reward + tg[t]);
@@ -166,7 +166,7 @@ __device__ __forceinline__ int plan_cluster(const InstDev &I, const PathDev &P, 
 // source order of tryTo*LowerBound (vns_sop_path.cpp:207-243, 423-454, 573-633, 799-930):
 // MOVE-up adds its last two edges as one pre-summed term (:873-874), MOVE-down its first two
 // (:912-913); everything else is left-to-right from 0.0.  Uniform across the warp.
-__device__ double plan_lower_bound(const InstDev &I, const PathDev &P, int T, const CandPlan &p)
+static __device__ double plan_lower_bound(const InstDev &I, const PathDev &P, int T, const CandPlan &p)
 {
    const int K = p.K;
    if (p.kind == 2) return 0.0;  // tryToRemove has no lower bound in the reference
@@ -197,7 +197,7 @@ __device__ double plan_lower_bound(const InstDev &I, const PathDev &P, int T, co
 }
 
 // Full evaluation by one warp.  vbuf: 2*I.mp doubles of shared memory private to the warp.
-__device__ double warp_eval(const InstDev &I, const PathDev &P, int T, const CandPlan &p, double *vbuf, int lane)
+static __device__ double warp_eval(const InstDev &I, const PathDev &P, int T, const CandPlan &p, double *vbuf, int lane)
 {
    double *v = vbuf, *w = vbuf + I.mp;
    int ca = plan_cluster(I, P, T, p, 0);
@@ -242,7 +242,7 @@ __device__ double warp_eval(const InstDev &I, const PathDev &P, int T, const Can
 
 // algorithmic bytes of one candidate: every block entry once + first F row + last B
 // row + the result
-__device__ long long plan_bytes(const InstDev &I, const PathDev &P, int T, const CandPlan &p, int w)
+static __device__ long long plan_bytes(const InstDev &I, const PathDev &P, int T, const CandPlan &p, int w)
 {
    long long e = 0;
    int ca = plan_cluster(I, P, T, p, 0);

@@ -6,8 +6,6 @@
 #include "common.cuh"
 #include "path.cuh"
 
-#define VNS_CHAIN_THREADS 512
-#define VNS_CHAIN_WARPS (VNS_CHAIN_THREADS / 32)
 #define VNS_MAX_DRAWS (1 << 22)  // guard of the rejection loops (:510-519, :726-730) against hangs
 
 // ---- CTA-wide vector helpers (all threads must call) ---------------------------------------------
@@ -39,7 +37,7 @@ __device__ void cta_shift(Tp *arr, int from, int count, int delta)
 }
 
 // rows [from_row, from_row+nrows) of B / minB move by delta rows
-__device__ void cta_shift_B(const InstDev &I, const PathDev &P, int from_row, int nrows, int delta)
+static __device__ void cta_shift_B(const InstDev &I, const PathDev &P, int from_row, int nrows, int delta)
 {
    cta_shift(P.B, from_row * I.mp, nrows * I.mp, delta * I.mp);
    cta_shift(P.minB, from_row, nrows, delta);
@@ -47,7 +45,7 @@ __device__ void cta_shift_B(const InstDev &I, const PathDev &P, int from_row, in
 
 // forward layers [lf, S] on warp 0 and backward layers [lb, 0] on warp 1, concurrently; then the
 // consistency check of VnsSopPath::addPoint (vns_sop_path.cpp:80-88, tolerance 0.01)
-__device__ void cta_rescan(const InstDev &I, const PathDev &P, int T, int lf, int lb)
+static __device__ void cta_rescan(const InstDev &I, const PathDev &P, int T, int lf, int lb)
 {
    __syncthreads();
    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -62,7 +60,7 @@ __device__ void cta_rescan(const InstDev &I, const PathDev &P, int T, int lf, in
 }
 
 // VnsSopPath::update (vns_sop_path.cpp:1321-1404) + getReward
-__device__ void cta_update(const InstDev &I, const PathDev &P, int T)
+static __device__ void cta_update(const InstDev &I, const PathDev &P, int T)
 {
    cta_rescan(I, P, T, 0, T + 1);
    if (threadIdx.x == 0) P.hd[HD_REWARD] = path_reward(I, P.tg, T);
@@ -72,7 +70,7 @@ __device__ void cta_update(const InstDev &I, const PathDev &P, int T)
 // ---- applying an accepted move: only the final state matters -----------------
 // insertRandom accept (vns_sop_solver.cpp:621-646): VNS[from] is re-inserted immediately before the
 // element that was at index `to`.  Returns the new T.
-__device__ int cta_apply_insert(const InstDev &I, const PathDev &P, int T, int nvns, int from, int to)
+static __device__ int cta_apply_insert(const InstDev &I, const PathDev &P, int T, int nvns, int from, int to)
 {
    __shared__ int s_c;
    if (threadIdx.x == 0) s_c = P.vns[from];
@@ -102,7 +100,7 @@ __device__ int cta_apply_insert(const InstDev &I, const PathDev &P, int T, int n
 }
 
 // exchangeRandom accept (vns_sop_solver.cpp:807-832): VNS[from] <-> VNS[to]; `to` is always in the path
-__device__ void cta_apply_exchange(const InstDev &I, const PathDev &P, int T, int from, int to)
+static __device__ void cta_apply_exchange(const InstDev &I, const PathDev &P, int T, int from, int to)
 {
    if (threadIdx.x == 0) {
       const int cf = P.vns[from], ct = P.vns[to];
@@ -116,9 +114,6 @@ __device__ void cta_apply_exchange(const InstDev &I, const PathDev &P, int T, in
 }
 
 // ---- the local-search chain ---------------------------------------------------------------------
-struct LsStats {
-   long long proposals, lb_skips, evals, accepts, rounds;
-};
 
 struct LsShared {
    RngState rng;                    // glibc rand() replay (math_common.cpp:21-28)
@@ -135,7 +130,7 @@ struct LsShared {
 // one warp each; the first accepted one in draw order is applied, the RNG is rewound to just after
 // its draws, and everything behind it is discarded - exactly the state sequence of the reference's
 // sequential loop.  vbuf_all: VNS_CHAIN_WARPS * 2 * I.mp doubles of shared memory.
-__device__ void cta_local_search(const InstDev &I, const PathDev &P, int kind, int num_changes, double budget, int skipflag,
+static __device__ void cta_local_search(const InstDev &I, const PathDev &P, int kind, int num_changes, double budget, int skipflag,
                                  LsShared &sh, double *vbuf_all)
 {
    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -240,20 +235,20 @@ __device__ void cta_local_search(const InstDev &I, const PathDev &P, int kind, i
 }
 
 // ---- shake + fit-to-budget ------------------------------------------------------------------------
-__device__ void vec_insert1(int *v, int &n, int pos, const int *src, int k)
+static __device__ void vec_insert1(int *v, int &n, int pos, const int *src, int k)
 {
    for (int x = n - 1; x >= pos; --x) v[x + k] = v[x];
    for (int x = 0; x < k; ++x) v[pos + x] = src[x];
    n += k;
 }
-__device__ void vec_erase1(int *v, int &n, int a, int b_incl)
+static __device__ void vec_erase1(int *v, int &n, int a, int b_incl)
 {
    const int k = b_incl - a + 1;
    for (int x = b_incl + 1; x < n; ++x) v[x - k] = v[x];
    n -= k;
 }
 // k distinct draws in [0, hi] (unordered_set insert loop :936-939 / :1007-1010), sorted (:945,:1015)
-__device__ void draw_distinct_sorted(RngState &g, int hi, int k, int *out)
+static __device__ void draw_distinct_sorted(RngState &g, int hi, int k, int *out)
 {
    int n = 0, guard = 0;
    while (n < k && guard++ < VNS_MAX_DRAWS) {
@@ -268,7 +263,7 @@ __device__ void draw_distinct_sorted(RngState &g, int hi, int k, int *out)
 
 // fitDOPtoBudget vns_sop_solver.cpp:364-385.  Needs F valid for layers <= T (forward DP) on entry;
 // runs on warp 0 only (other warps wait at the barrier), leaves a fully re-scanned path.
-__device__ void cta_fit(const InstDev &I, const PathDev &P, int &T_io, double budget, double *vbuf)
+static __device__ void cta_fit(const InstDev &I, const PathDev &P, int &T_io, double budget, double *vbuf)
 {
    __shared__ int s_T;
    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -308,7 +303,7 @@ __device__ void cta_fit(const InstDev &I, const PathDev &P, int &T_io, double bu
 // the same vector splices on the VNS vector and (for the parts inside the path) on targets, then
 // fitDOPtoBudget.  The splices are serial on thread 0 (O(|VNS|) integer moves, once per VNS step).
 // seg: scratch of 2*rows ints in global memory.
-__device__ void cta_shake(const InstDev &I, const PathDev &P, int kind, double budget, RngState &rng, int *seg, double *vbuf)
+static __device__ void cta_shake(const InstDev &I, const PathDev &P, int kind, double budget, RngState &rng, int *seg, double *vbuf)
 {
    __shared__ int s_T2, s_first;
    __syncthreads();
@@ -374,7 +369,7 @@ __device__ void cta_shake(const InstDev &I, const PathDev &P, int kind, double b
 // Each round evaluates the full (candidate x position) grid - (|VNS|-T)*(T+1) independent tryToAdd -
 // and inserts the strict minimum of (d - L)/reward among d <= budget; ties keep the first grid index
 // (candidate-major, position-minor: the reference's loop order with strict '<' at :1119).
-__device__ void cta_greedy(const InstDev &I, const PathDev &P, double budget, double *vbuf_all)
+static __device__ void cta_greedy(const InstDev &I, const PathDev &P, double budget, double *vbuf_all)
 {
    __shared__ double s_best[VNS_CHAIN_WARPS];
    __shared__ double s_d[VNS_CHAIN_WARPS];
@@ -419,7 +414,7 @@ __device__ void cta_greedy(const InstDev &I, const PathDev &P, double budget, do
 }
 
 // ---- path copy (VnsSopPath value semantics: vns_sop_solver.cpp:195-197,227-228) ------------------------
-__device__ void cta_copy_path(const InstDev &I, const PathDev &dst, const PathDev &src)
+static __device__ void cta_copy_path(const InstDev &I, const PathDev &dst, const PathDev &src)
 {
    __syncthreads();
    const int T = src.hdr[HDR_T], nvns = src.hdr[HDR_NVNS];
@@ -436,7 +431,7 @@ __device__ void cta_copy_path(const InstDev &I, const PathDev &dst, const PathDe
 // getPathLengthCalculate vns_sop_path.cpp:1700-1741: arg-min at the goal layer (first index on ties),
 // walk the forward back-pointers (smallest predecessor index achieving F[l][j], :1356-1371) and
 // re-sum the raw distances goal -> start.  One thread.  node[] (T+2 ints) may be null.
-__device__ double path_walk_back(const InstDev &I, const PathDev &P, int T, int *cluster, int *node)
+static __device__ double path_walk_back(const InstDev &I, const PathDev &P, int T, int *cluster, int *node)
 {
    const int S = T + 1;
    int cur = 0;
@@ -468,21 +463,6 @@ __device__ double path_walk_back(const InstDev &I, const PathDev &P, int T, int 
 }
 
 // ---- VnsSopSolver::iterate vns_sop_solver.cpp:82-260 as one persistent chain ------------------------
-struct VnsParamsDev {
-   int num_iterations, num_iterations_unimproved, skip, greedy;
-   double budget, max_time_ms;
-   int max_improvements;
-   // multi-start race (vnsgpu_set_target_reward): the first run whose tour reaches target_reward raises *stop_flag and
-   // every run leaves at its next shake; null = off (the reference's stopping rules only)
-   double target_reward;
-   int *stop_flag;
-};
-struct VnsResultDev {
-   int num_iters, num_iters_last_impr, n_improvements, status;
-   double reward, length, time_ms, time_last_impr_ms;
-   long long proposals, evals, accepts;
-};
-
 __device__ __forceinline__ double now_ms()
 {
    unsigned long long t;
@@ -490,7 +470,7 @@ __device__ __forceinline__ double now_ms()
    return (double)t * 1e-6;
 }
 
-__device__ void cta_vns_run(const InstDev &I, const PathDev &tour, const PathDev &act, const VnsParamsDev &prm, VnsResultDev *res,
+static __device__ void cta_vns_run(const InstDev &I, const PathDev &tour, const PathDev &act, const VnsParamsDev &prm, VnsResultDev *res,
                             double *impr_reward, double *impr_length, double *impr_ms, LsShared &sh, int *seg, double *vbuf_all)
 {
    __shared__ int s_stop, s_improved;

@@ -37,7 +37,7 @@ __device__ __forceinline__ double mod2pi(double t) { return t - VNS_TWO_PI * flo
 // Shortest Dubins path (six words, normalised by rho).  No reference code exists;
 // the known answers are the EXPLICIT matrices of datasets/dop_sop_dataset.
 // Operation order mirrors oracle/vns_oracle.c:vo_dubins_length term by term.
-__device__ double dubins_length(double x0, double y0, double th0, double x1, double y1, double th1, double rho)
+static __device__ double dubins_length(double x0, double y0, double th0, double x1, double y1, double th1, double rho)
 {
    double dx = x1 - x0, dy = y1 - y0;
    double d = sqrt(dx * dx + dy * dy) / rho;
@@ -97,7 +97,7 @@ __device__ double dubins_length(double x0, double y0, double th0, double x1, dou
 
 // a2: SOPLoader::getSOPFromWeightMatrix sop_loader.cpp:413-427 (W in sample order); to_dense = 1
 // runs the inverse permutation (download for tests)
-__global__ void __launch_bounds__(256) k_table_gather(InstDev I, double *__restrict__ D, double *__restrict__ W, int to_dense)
+static __global__ void __launch_bounds__(256) k_table_gather(InstDev I, double *__restrict__ D, double *__restrict__ W, int to_dense)
 {
    const int c1 = blockIdx.y;
    const int m1 = I.m[c1], o1 = I.off[c1];

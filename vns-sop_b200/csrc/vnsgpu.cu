@@ -1,133 +1,7 @@
 // libvnsgpu.so: C ABI (include/vnsgpu.h) over the sm_100a kernels.  No CPU fallback exists: every
-// entry point either runs its CUDA kernels or returns an error.
-#include <math_constants.h>
-
-#include <algorithm>
-#include <cstdio>
-#include <cstdlib>
-#include <cstring>
-#include <string>
-#include <vector>
-
-#include "../../include/vnsgpu.h"
-#include "common.cuh"
+// entry point either runs its CUDA kernels or returns an error.  This unit: context + distance table.
+#include "ctx.hpp"
 #include "table.cuh"
-#include "path.cuh"
-#include "search.cuh"
-#include "eval.cuh"
-#include "vec.cuh"
-#include "chain.cuh"
-#include "kernels.cuh"
-
-static_assert(sizeof(vnsgpu_rng) == sizeof(RngState), "rng layout");
-static_assert(sizeof(vnsgpu_cand) == 16, "cand layout");
-
-#define VNS_PIPE_EVENTS 16
-
-struct PathHost {
-   void *block = nullptr;
-   PathDev d{};
-};
-
-// everything the stream operations of the host-buffer evaluation call bake in (see eval_batch_host)
-struct HostGraphKey {
-   InstDev I;
-   PathDev P;
-   const void *src, *len, *lb, *flags, *leni, *scratch, *D32, *D16, *vec, *veclb, *segmeta, *hist, *perm;
-   cudaStream_t sk;
-   int64_t n;
-   double budget;
-   size_t perm_cap;
-   int skip, packed, mode, sort, use_int, G;
-};
-
-struct vnsgpu_ctx {
-   int device = 0;
-   cudaStream_t own = nullptr, stream = nullptr;
-   cudaStream_t s_in = nullptr, s_out = nullptr;                 // copy streams of the host-buffer pipeline
-   cudaEvent_t ev_in[VNS_PIPE_EVENTS] = {}, ev_k[VNS_PIPE_EVENTS] = {}, ev_start = nullptr;
-   InstDev I{};
-   bool have_clusters = false, have_table = false;
-   std::vector<int> m, off;
-   std::vector<double> reward;
-   int *d_m = nullptr, *d_off = nullptr, *d_clof = nullptr;
-   double *d_reward = nullptr, *d_D = nullptr, *d_dmin = nullptr, *d_dmax = nullptr;
-   int *d_D32 = nullptr;     // int32 copy of an all-integer table (DPX evaluation path), else null
-   unsigned short *d_D16 = nullptr;   // uint16 copy when every entry is an integer below 65535: the endpoint-vector builds stream it
-   bool use_u16 = true;      // vnsgpu_set_u16_table
-   bool use_int = true;      // vnsgpu_set_int_path
-   bool sort_batches = true; // evaluate batches in chain-length order (vnsgpu_set_batch_sort)
-   bool use_seg = true;      // exact segment products on integer tables (vnsgpu_set_segment_cache)
-   bool seg_ok = false;      // the int32 buffer has room for them and offsets fit 32 bits
-   int *d_segmeta = nullptr;
-   int use_vec = 1;          // 0 off, 1 when the batch is large enough, 2 always; endpoint vectors on top of the segment products (vnsgpu_set_vector_cache, vec.cuh)
-   int *d_vec = nullptr, *d_veclb = nullptr;
-   int group_lanes = 8;      // lanes per candidate of k_eval_groups, from the mean cluster size
-   unsigned *d_hist = nullptr, *d_perm = nullptr;
-   size_t perm_cap = 0;
-   unsigned long long *d_info = nullptr;
-   std::vector<PathHost> paths;
-   // scratch
-   void *d_scratch = nullptr;
-   size_t scratch_bytes = 0;
-   int *d_seg = nullptr;
-   RngState *d_rng = nullptr;
-   LsStats *d_stats = nullptr;
-   long long *d_first = nullptr;
-   VnsResultDev *d_res = nullptr;
-   long long *d_prof = nullptr;   // phase cycles of the shared-memory chain
-   int *d_stop = nullptr;         // stop flag of the multi-start race
-   double target_reward = 0.0;    // vnsgpu_set_target_reward
-   float table_kernel_ms = 0.f;   // device time of the last k_table_pairs launch
-   std::string err;
-   int64_t launches = 0;
-   int num_sms = 148;
-   int max_smem = 48 * 1024;      // opt-in shared memory per block
-   bool use_smem_chain = true;    // vnsgpu_set_smem_chain
-   // the host-buffer evaluation call as a CUDA graph (eval_batch_host)
-   bool use_graph = true, hg_seen = false;
-   HostGraphKey hg_key, hg_last;
-   cudaGraphExec_t hg_exec = nullptr;
-   int64_t hg_launches = 0;
-   long long *h_first = nullptr;  // pinned
-   cudaEvent_t ev_out = nullptr;
-};
-
-#define CK(call)                                                                                   \
-   do {                                                                                            \
-      cudaError_t e__ = (call);                                                                    \
-      if (e__ != cudaSuccess) {                                                                    \
-         ctx->err = std::string(#call) + ": " + cudaGetErrorString(e__);                           \
-         return VNSGPU_E_CUDA;                                                                     \
-      }                                                                                            \
-   } while (0)
-
-#define LAUNCHED(ctx)                                                                              \
-   do {                                                                                            \
-      (ctx)->launches++;                                                                           \
-      cudaError_t e__ = cudaGetLastError();                                                        \
-      if (e__ != cudaSuccess) {                                                                    \
-         (ctx)->err = std::string("kernel launch: ") + cudaGetErrorString(e__);                   \
-         return VNSGPU_E_CUDA;                                                                     \
-      }                                                                                            \
-   } while (0)
-
-static vnsgpu_status fail(vnsgpu_ctx *ctx, vnsgpu_status s, const char *msg)
-{
-   ctx->err = msg;
-   return s;
-}
-
-static vnsgpu_status need_scratch(vnsgpu_ctx *ctx, size_t bytes)
-{
-   if (bytes <= ctx->scratch_bytes) return VNSGPU_OK;
-   if (ctx->d_scratch) CK(cudaFree(ctx->d_scratch));
-   ctx->d_scratch = nullptr;
-   ctx->scratch_bytes = 0;
-   CK(cudaMalloc(&ctx->d_scratch, bytes));
-   ctx->scratch_bytes = bytes;
-   return VNSGPU_OK;
-}
 
 extern "C" {
 
@@ -241,11 +115,6 @@ vnsgpu_status vnsgpu_set_int_path(vnsgpu_ctx *ctx, int enable)
    return VNSGPU_OK;
 }
 
-static bool group_kernel_ok(const vnsgpu_ctx *ctx)
-{
-   const int G = ctx->group_lanes, nr = (ctx->I.mp + G - 1) / G;
-   return nr <= (G == 8 ? 4 : (G == 16 ? 2 : 1)) && (long long)ctx->I.N * ctx->I.N < (1ll << 32);
-}
 int vnsgpu_int_path_active(const vnsgpu_ctx *ctx) { return ctx->use_int && ctx->d_D32 != nullptr && group_kernel_ok(ctx); }
 
 vnsgpu_status vnsgpu_sync(vnsgpu_ctx *ctx)
@@ -445,5 +314,3 @@ vnsgpu_status vnsgpu_get_bounds(vnsgpu_ctx *ctx, double *dmin, double *dmax)
 
 } // extern "C"
 
-#include "api_path.inl"
-#include "api_search.inl"
