@@ -31,7 +31,10 @@ typedef enum {
    VNSGPU_E_STATE = 3,        /* call order (no table, bad handle, ...) */
    VNSGPU_E_INCONSISTENT = 4, /* forward/backward length mismatch (vns_sop_path.cpp:80-88) or
                                  over-budget improved tour (vns_sop_solver.cpp:229-237) */
-   VNSGPU_E_NOMEM = 5
+   VNSGPU_E_NOMEM = 5,
+   VNSGPU_E_TOO_LARGE = 6,    /* the instance does not fit the requested form (e.g. vnsgpu_vns_run_batch: search state
+                                 beyond one SM's shared memory); the caller may fall back to another entry point */
+   VNSGPU_E_NCCL = 7          /* NCCL error in a vnsgpu_comm_* call, see vnsgpu_last_error */
 } vnsgpu_status;
 
 /* edge-weight rules of SOPLoader (sop_loader.cpp:278,360,474-486) */
@@ -126,6 +129,17 @@ vnsgpu_status vnsgpu_set_u16_table(vnsgpu_ctx *ctx, int enable);
 /* vnsgpu_local_search keeps the whole search state in one SM's shared memory when it fits (clusters <=
  * 510, samples per cluster <= 32); enable = 0 forces the global-memory chain (tests run both). */
 vnsgpu_status vnsgpu_set_smem_chain(vnsgpu_ctx *ctx, int enable);
+/* Form of the shared-memory chain on all-integer tables.  0 (default): the second form - the lower bound of every
+ * proposal first (one thread each, O(1) from prefix sums along the path), only the survivors are evaluated, up to 256
+ * draw pairs per thread block and round, shake + fitDOPtoBudget in shared memory as well.  1: the first form (one
+ * sub-warp group per proposal, 64 proposals per round).  Same trajectory either way (tests run both). */
+vnsgpu_status vnsgpu_set_chain_form(vnsgpu_ctx *ctx, int form);
+/* Thread blocks that cooperate on ONE trajectory-exact chain (second form; cooperative launch).  Every block holds a
+ * replica of the search state and evaluates its own slice of 256 draw pairs of the round's window (it reaches its
+ * slice of the glibc rand() stream with one 31 x 31 jump matrix); one grid barrier per round; the first slice with an
+ * accepted proposal wins, exactly the proposal the reference's sequential loop would have applied.  0 (default): from the
+ * instance size (1 block up to ~128 clusters, then |clusters|^2 / 2048, at most one per SM). */
+vnsgpu_status vnsgpu_set_chain_blocks(vnsgpu_ctx *ctx, int blocks);
 
 /* ---- instance + distance table: replaces VnsSopPath::setSamplesDistances (vns_sop_path.cpp:38-48)
  *      fed by SOPLoader::getSOPFromNodes / getSOPFromWeightMatrix / getOP / getOPN ---------------- */

@@ -127,22 +127,39 @@ def test_greedy_insertion(name, golden, eng_cache):
     assert p.getPathLength() == g["greedy"]["length"] and p.getReward() == g["greedy"]["reward"]
 
 
-@pytest.mark.parametrize("mode", ["smem-int", "smem-double", "global"])
+CHAIN_MODES = ["smem-int", "smem-int-grid3", "smem-int-grid8", "smem-int-v1", "smem-double", "global"]
+
+
+def _set_chain_mode(e, mode):
+    """smem-int: second chain form (lower bound first), one thread block; -gridN: N cooperating thread blocks;
+    -v1: first form; smem-double: first form in IEEE double; global: global-memory chain"""
+    e.set_smem_chain(mode != "global")
+    e.set_int_path(mode != "smem-double")
+    e.set_chain_form(1 if mode == "smem-int-v1" else 0)
+    e.set_chain_blocks(int(mode.split("grid")[1]) if "grid" in mode else 1)
+
+
+def _reset_chain_mode(e):
+    e.set_smem_chain(True)
+    e.set_int_path(True)
+    e.set_chain_form(0)
+    e.set_chain_blocks(0)
+
+
+@pytest.mark.parametrize("mode", CHAIN_MODES)
 @pytest.mark.parametrize("name", ALL)
 def test_shake_and_local_search_sequence(name, mode, golden, eng_cache):
     """pathInsert/pathExchange + insertRandom/exchangeRandom with seed 7: the device chain must
-    walk the reference's exact state sequence and leave the RNG at the same position.  Three
-    implementations: shared-memory chain in exact int32 and in double arithmetic, global-memory chain."""
-    from vns_sop_b200 import engine
+    walk the reference's exact state sequence and leave the RNG at the same position.  Every
+    implementation: second chain form on 1, 3 and 8 cooperating thread blocks, first form in exact int32 and in
+    double arithmetic, global-memory chain."""
     e, sf, pb = eng_cache(name)
     g, a = golden[name], load_arrays(name)
-    e.set_smem_chain(mode != "global")
-    e.set_int_path(mode != "smem-double")
+    _set_chain_mode(e, mode)
     try:
         _run_sequence(e, pb, g, a)
     finally:
-        e.set_smem_chain(True)
-        e.set_int_path(True)
+        _reset_chain_mode(e)
 
 
 def _run_sequence(e, pb, g, a):
@@ -163,23 +180,21 @@ def _run_sequence(e, pb, g, a):
     assert engine.rng_next(rng) == g["rand_after_sequence"]
 
 
-@pytest.mark.parametrize("mode", ["smem-int", "smem-double", "global"])
+@pytest.mark.parametrize("mode", CHAIN_MODES)
 @pytest.mark.parametrize("name", ["berlin52", "opn_s08", "dop_s12", "krob200"])
 def test_full_vns_run_seed1_follows_reference_trajectory(name, mode, golden, eng_cache):
     """VnsSopSolver::iterate with the stock stopping rule and seed 1 as one device chain: iteration
     counts, every improvement (reward, length) and the final tour equal the reference's results.log."""
     e, sf, pb = eng_cache(name)
     s = golden[name]["solve_seed1"]
-    if mode != "smem-int" and name == "krob200":
-        pytest.skip("long run: the integer shared-memory chain covers krob200")
-    e.set_smem_chain(mode != "global")
-    e.set_int_path(mode != "smem-double")
+    if mode not in ("smem-int", "smem-int-grid3") and name == "krob200":
+        pytest.skip("long run: the second chain form (1 and 3 thread blocks) covers krob200")
+    _set_chain_mode(e, mode)
     try:
         p = e.path()
         res, impr = p.vns_run(1)
     finally:
-        e.set_smem_chain(True)
-        e.set_int_path(True)
+        _reset_chain_mode(e)
     assert res.status == 0
     assert res.num_iters == s["NUM_ITERS"] and res.num_iters_last_impr == s["NUM_ITERS_LAST_IMPR"]
     assert res.reward == s["REWARDS"] and res.length == s["LENGTH"]

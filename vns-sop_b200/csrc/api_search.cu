@@ -5,6 +5,7 @@
 #include "eval.cuh"
 #include "chain.cuh"
 #include "kernels_search.cuh"
+#include "chain2_host.hpp"
 
 // insertRandom / exchangeRandom: the shared-memory chain (chain.cuh) when the state fits one SM's shared
 // memory, else the global-memory chain of search.cuh
@@ -41,6 +42,8 @@ static vnsgpu_status launch_chain_v(vnsgpu_ctx *ctx, const V *tab, int path, int
 static vnsgpu_status launch_local_search(vnsgpu_ctx *ctx, int path, int kind, int num_changes, double budget, int skip)
 {
    size_t smem = 0;
+   int cis = 0;
+   if (ctx->use_smem_chain && c2_fits(ctx, &smem, &cis)) return c2_launch_ls(ctx, path, kind, num_changes, budget, skip, smem, cis);
    if (vnsgpu_int_path_active(ctx) && chain_fits<int>(ctx, &smem))
       return launch_chain_v<int>(ctx, ctx->d_D32, path, kind, num_changes, budget, skip, smem);
    if (chain_fits<double>(ctx, &smem)) return launch_chain_v<double>(ctx, ctx->d_D, path, kind, num_changes, budget, skip, smem);
@@ -192,12 +195,17 @@ vnsgpu_status vnsgpu_vns_run(vnsgpu_ctx *ctx, int path, const vnsgpu_vns_params 
 {
    CK(cudaSetDevice(ctx->device));
    if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
-   int work = -1;
-   vnsgpu_status s = vnsgpu_path_create(ctx, &work);   // actualVNSGOPPath (vns_sop_solver.cpp:195)
-   if (s) return s;
    const int cap = std::max(1, p->max_improvements);
-   s = need_scratch(ctx, sizeof(double) * 3 * cap);
+   vnsgpu_status s = need_scratch(ctx, sizeof(double) * 3 * cap);
    if (s) return s;
+   size_t smem2 = 0;
+   int cis = 0;
+   const bool c2 = ctx->use_smem_chain && c2_fits(ctx, &smem2, &cis);
+   int work = -1;
+   if (!c2) {
+      s = vnsgpu_path_create(ctx, &work);   // actualVNSGOPPath (vns_sop_solver.cpp:195); the second chain keeps it in shared memory
+      if (s) return s;
+   }
    double *d_ir = (double *)ctx->d_scratch, *d_il = d_ir + cap, *d_it = d_il + cap;
    RngState g;
    rng_seed_host(g, p->seed);
@@ -207,7 +215,9 @@ vnsgpu_status vnsgpu_vns_run(vnsgpu_ctx *ctx, int path, const vnsgpu_vns_params 
    prm.skip = p->lower_bound_skip; prm.greedy = p->greedy_initial; prm.budget = p->budget;
    prm.max_time_ms = p->max_time_ms; prm.max_improvements = cap;
    prm.target_reward = 0.0; prm.stop_flag = nullptr;
-   {
+   if (c2)
+      s = c2_launch_vns(ctx, path, prm, d_ir, d_il, d_it, smem2, cis);
+   else {
       size_t smem = 0;
       const size_t extra = chain_smem(ctx) + sizeof(RngState) + 64;   // shake / fit / greedy scratch + statics
       if (vnsgpu_int_path_active(ctx) && chain_fits<int>(ctx, &smem) && smem + extra + sizeof(ChainCtl) + 1024 <= (size_t)ctx->max_smem)
@@ -219,8 +229,8 @@ vnsgpu_status vnsgpu_vns_run(vnsgpu_ctx *ctx, int path, const vnsgpu_vns_params 
                                                                            ctx->d_res, d_ir, d_il, d_it, ctx->d_seg);
          LAUNCHED(ctx);
       }
-      if (s) return s;
    }
+   if (s) { if (work >= 0) vnsgpu_path_destroy(ctx, work); return s; }
    VnsResultDev r;
    CK(cudaMemcpyAsync(&r, ctx->d_res, sizeof(r), cudaMemcpyDeviceToHost, ctx->stream));
    CK(cudaStreamSynchronize(ctx->stream));
@@ -235,7 +245,7 @@ vnsgpu_status vnsgpu_vns_run(vnsgpu_ctx *ctx, int path, const vnsgpu_vns_params 
       result->time_last_impr_ms = r.time_last_impr_ms;
       result->proposals = r.proposals; result->evals = r.evals; result->accepts = r.accepts;
    }
-   vnsgpu_path_destroy(ctx, work);
+   if (work >= 0) vnsgpu_path_destroy(ctx, work);
    if (r.status == 4) return fail(ctx, VNSGPU_E_INCONSISTENT, "inconsistent path length in improved tour");
    if (r.status) return fail(ctx, VNSGPU_E_STATE, "device-side error flag in vns_run");
    return VNSGPU_OK;
@@ -248,50 +258,76 @@ vnsgpu_status vnsgpu_vns_run_batch(vnsgpu_ctx *ctx, int path, int nruns, const u
    if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
    if (nruns < 1) return fail(ctx, VNSGPU_E_RANGE, "nruns < 1");
    size_t smem = 0;
+   int cis = 0;
+   const bool c2 = ctx->use_smem_chain && c2_fits(ctx, &smem, &cis);
    const size_t extra = chain_smem(ctx) + sizeof(RngState) + 64;
-   const bool as_int = vnsgpu_int_path_active(ctx) && chain_fits<int>(ctx, &smem) && smem + extra + sizeof(ChainCtl) + 1024 <= (size_t)ctx->max_smem;
-   if (!as_int && !(chain_fits<double>(ctx, &smem) && smem + extra + sizeof(ChainCtl) + 1024 <= (size_t)ctx->max_smem))
-      return fail(ctx, VNSGPU_E_STATE, "instance too large for the shared-memory chain: use vnsgpu_vns_run per seed");
-   // two paths per run (tourVNSGOPPath, actualVNSGOPPath), every tour a copy of `path`
+   bool as_int = false;
+   if (!c2) {
+      as_int = vnsgpu_int_path_active(ctx) && chain_fits<int>(ctx, &smem) && smem + extra + sizeof(ChainCtl) + 1024 <= (size_t)ctx->max_smem;
+      if (!as_int && !(chain_fits<double>(ctx, &smem) && smem + extra + sizeof(ChainCtl) + 1024 <= (size_t)ctx->max_smem))
+         return fail(ctx, VNSGPU_E_TOO_LARGE, "instance too large for the shared-memory chain: use vnsgpu_vns_run per seed");
+   }
+   // first form: two paths per run (tourVNSGOPPath, actualVNSGOPPath); second form: the tour only.  Every tour a copy of `path`
    std::vector<int> tours(nruns, -1), acts(nruns, -1);
-   std::vector<VnsRunSlot> slots(nruns);
+   const size_t slot_bytes = c2 ? c2_run_slot_bytes() : sizeof(VnsRunSlot);
+   std::vector<char> slots(slot_bytes * (size_t)nruns);
    int *d_segs = nullptr;
-   VnsRunSlot *d_slots = nullptr;
+   void *d_slots = nullptr;
    vnsgpu_status s = VNSGPU_OK;
-   CK(cudaMalloc(&d_segs, sizeof(int) * 2 * ctx->I.rows * (size_t)nruns));
-   CK(cudaMalloc(&d_slots, sizeof(VnsRunSlot) * (size_t)nruns));
+   auto cuda_ok = [&](cudaError_t e, const char *what) {
+      if (e == cudaSuccess || s) return;
+      ctx->err = std::string(what) + ": " + cudaGetErrorString(e);
+      s = VNSGPU_E_CUDA;
+   };
+   if (!c2) cuda_ok(cudaMalloc(&d_segs, sizeof(int) * 2 * ctx->I.rows * (size_t)nruns), "cudaMalloc(segs)");
+   cuda_ok(cudaMalloc(&d_slots, slot_bytes * (size_t)nruns), "cudaMalloc(slots)");
    for (int r = 0; r < nruns && !s; ++r) {
       int a = -1, b = -1;
       s = vnsgpu_path_create(ctx, &a);
-      if (!s) s = vnsgpu_path_create(ctx, &b);
+      tours[r] = a;
+      if (!s && !c2) { s = vnsgpu_path_create(ctx, &b); acts[r] = b; }
       if (!s) s = vnsgpu_path_copy(ctx, a, path);
-      tours[r] = a; acts[r] = b;
       if (s) break;
-      slots[r].tour = ctx->paths[a].d; slots[r].act = ctx->paths[b].d;
-      rng_seed_host(slots[r].rng, seeds[r]);
-      memset(&slots[r].res, 0, sizeof(VnsResultDev));
-      slots[r].seg = d_segs + (size_t)r * 2 * ctx->I.rows;
+      RngState g;
+      rng_seed_host(g, seeds[r]);
+      if (c2)
+         c2_run_slot_fill(slots.data() + slot_bytes * r, ctx->paths[a].d, g);
+      else {
+         VnsRunSlot &sl = *reinterpret_cast<VnsRunSlot *>(slots.data() + slot_bytes * r);
+         sl.tour = ctx->paths[a].d; sl.act = ctx->paths[b].d; sl.rng = g;
+         memset(&sl.res, 0, sizeof(VnsResultDev));
+         sl.seg = d_segs + (size_t)r * 2 * ctx->I.rows;
+      }
    }
    if (!s) {
-      CK(cudaMemcpyAsync(d_slots, slots.data(), sizeof(VnsRunSlot) * nruns, cudaMemcpyHostToDevice, ctx->stream));
+      cuda_ok(cudaMemcpyAsync(d_slots, slots.data(), slots.size(), cudaMemcpyHostToDevice, ctx->stream), "cudaMemcpyAsync(slots)");
       VnsParamsDev prm;
       prm.num_iterations = p->num_iterations; prm.num_iterations_unimproved = p->num_iterations_unimproved;
       prm.skip = p->lower_bound_skip; prm.greedy = p->greedy_initial; prm.budget = p->budget;
       prm.max_time_ms = p->max_time_ms; prm.max_improvements = 0;
       prm.target_reward = ctx->target_reward; prm.stop_flag = nullptr;
       if (ctx->target_reward > 0) {
-         CK(cudaMemsetAsync(ctx->d_stop, 0, sizeof(int), ctx->stream));
+         cuda_ok(cudaMemsetAsync(ctx->d_stop, 0, sizeof(int), ctx->stream), "cudaMemsetAsync(stop)");
          prm.stop_flag = ctx->d_stop;
       }
-      s = as_int ? launch_chain_multi_v<int>(ctx, ctx->d_D32, nruns, d_slots, prm, smem + chain_smem(ctx))
-                 : launch_chain_multi_v<double>(ctx, ctx->d_D, nruns, d_slots, prm, smem + chain_smem(ctx));
+      if (!s) {
+         if (c2) s = c2_launch_multi(ctx, nruns, d_slots, prm, smem, cis);
+         else
+            s = as_int ? launch_chain_multi_v<int>(ctx, ctx->d_D32, nruns, (VnsRunSlot *)d_slots, prm, smem + chain_smem(ctx))
+                       : launch_chain_multi_v<double>(ctx, ctx->d_D, nruns, (VnsRunSlot *)d_slots, prm, smem + chain_smem(ctx));
+      }
    }
    if (!s) {
-      CK(cudaMemcpyAsync(slots.data(), d_slots, sizeof(VnsRunSlot) * nruns, cudaMemcpyDeviceToHost, ctx->stream));
-      CK(cudaStreamSynchronize(ctx->stream));
+      cuda_ok(cudaMemcpyAsync(slots.data(), d_slots, slots.size(), cudaMemcpyDeviceToHost, ctx->stream), "cudaMemcpyAsync(results)");
+      cuda_ok(cudaStreamSynchronize(ctx->stream), "cudaStreamSynchronize");
+   }
+   if (!s) {
+      auto result_of = [&](int r) -> const VnsResultDev & {
+         return c2 ? c2_run_slot_result(slots.data() + slot_bytes * r) : reinterpret_cast<const VnsRunSlot *>(slots.data() + slot_bytes * r)->res;
+      };
       int best = 0, bad = 0;
       for (int r = 0; r < nruns; ++r) {
-         const VnsResultDev &q = slots[r].res;
+         const VnsResultDev &q = result_of(r);
          if (q.status) bad = q.status;
          if (results) {
             vnsgpu_vns_result &o = results[r];
@@ -299,21 +335,24 @@ vnsgpu_status vnsgpu_vns_run_batch(vnsgpu_ctx *ctx, int path, int nruns, const u
             o.status = q.status; o.reward = q.reward; o.length = q.length; o.time_ms = q.time_ms;
             o.time_last_impr_ms = q.time_last_impr_ms; o.proposals = q.proposals; o.evals = q.evals; o.accepts = q.accepts;
          }
-         const VnsResultDev &bq = slots[best].res;
+         const VnsResultDev &bq = result_of(best);
          if (q.reward > bq.reward || (q.reward == bq.reward && q.length < bq.length)) best = r;
       }
       if (best_run) *best_run = best;
       s = vnsgpu_path_copy(ctx, path, tours[best]);      // the best tour replaces `path`
-      if (!s) CK(cudaStreamSynchronize(ctx->stream));
+      if (!s) cuda_ok(cudaStreamSynchronize(ctx->stream), "cudaStreamSynchronize");
       if (!s && bad) s = fail(ctx, bad == 4 ? VNSGPU_E_INCONSISTENT : VNSGPU_E_STATE, "device-side error flag in vns_run_batch");
    }
+   // every exit path releases the temporaries
    cudaStreamSynchronize(ctx->stream);
+   const std::string keep = ctx->err;
    for (int r = 0; r < nruns; ++r) {
       if (acts[r] >= 0) vnsgpu_path_destroy(ctx, acts[r]);
       if (tours[r] >= 0 && (s || !tour_paths)) vnsgpu_path_destroy(ctx, tours[r]);
       if (tour_paths) tour_paths[r] = s ? -1 : tours[r];
    }
    cudaFree(d_segs); cudaFree(d_slots);
+   if (s) ctx->err = keep;
    return s;
 }
 

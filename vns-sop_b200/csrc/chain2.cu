@@ -1,0 +1,191 @@
+// Host side of the second search chain (chain2.cuh): fit test, per-context device tables (int32 cluster-pair minima,
+// cluster offsets, RNG jump matrices, grid barrier + slots), cooperative launches.  Called from api_search.cu.
+#include "ctx.hpp"
+#include "path.cuh"
+#include "search.cuh"
+#include "eval.cuh"
+#include "chain2.cuh"
+#include "chain2_host.hpp"
+
+static __global__ void __launch_bounds__(256) k_dmin_to_int(int n, const double *__restrict__ dmin, int *__restrict__ out)
+{
+   const int k = blockIdx.x * blockDim.x + threadIdx.x;
+   if (k < n) out[k] = (int)dmin[k];
+}
+
+// jump[r][j][t]: x_{p + 512 r - 31 + t} = sum_j jump[r][j][t] * x_{p - 31 + j}  (mod 2^32) for the glibc TYPE_3 recurrence
+// x_i = x_{i-31} + x_{i-3}.  Companion matrix M: s'[t] = s[t+1] (t < 30), s'[30] = s[0] + s[28]; jump[r] = M^(512 r).
+static void build_jump(int ncta, std::vector<unsigned> &out)
+{
+   typedef std::vector<unsigned> Mat;   // 31 x 31, row-major: out_state[t] = sum_j A[t][j] * s[j]
+   auto mul = [](const Mat &A, const Mat &B) {
+      Mat Cm(31 * 31, 0u);
+      for (int i = 0; i < 31; ++i)
+         for (int k = 0; k < 31; ++k) {
+            const unsigned a = A[i * 31 + k];
+            if (!a) continue;
+            for (int j = 0; j < 31; ++j) Cm[i * 31 + j] += a * B[k * 31 + j];
+         }
+      return Cm;
+   };
+   Mat M(31 * 31, 0u), P(31 * 31, 0u);
+   for (int t = 0; t < 30; ++t) M[t * 31 + t + 1] = 1u;
+   M[30 * 31 + 0] = 1u; M[30 * 31 + 28] = 1u;
+   Mat step = M;                                  // M^(2 * C2_PAIRS) by squaring (2 * C2_PAIRS is a power of two)
+   for (int d = 1; d < 2 * C2_PAIRS; d <<= 1) step = mul(step, step);
+   for (int t = 0; t < 31; ++t) P[t * 31 + t] = 1u;   // identity
+   out.assign((size_t)ncta * 31 * 32, 0u);
+   for (int r = 0; r < ncta; ++r) {
+      for (int t = 0; t < 31; ++t)
+         for (int j = 0; j < 31; ++j) out[((size_t)r * 31 + j) * 32 + t] = P[t * 31 + j];
+      P = mul(step, P);
+   }
+}
+
+bool c2_fits(const vnsgpu_ctx *ctx, size_t *smem, int *cinfo_in_smem)
+{
+   if (!ctx->use_chain2 || !vnsgpu_int_path_active(ctx) || ctx->I.mp > 32 || !group_kernel_ok(ctx)) return false;
+   // static shared memory of the kernels (control block, slot, RNG, the few words of search.cuh's helpers) + margin
+   const size_t fixed = sizeof(C2Ctl) + sizeof(C2Slot) + sizeof(RngState) + 2048;
+   size_t b = c2_smem_bytes(ctx->I.C, ctx->I.mp, true);
+   *cinfo_in_smem = 1;
+   if (b + fixed > (size_t)ctx->max_smem) {
+      b = c2_smem_bytes(ctx->I.C, ctx->I.mp, false);
+      *cinfo_in_smem = 0;
+   }
+   // the greedy start of vns_run borrows 2 * mp * warps doubles of the same buffer
+   b = std::max(b, sizeof(double) * 2 * ctx->I.mp * VNS_CHAIN_WARPS);
+   *smem = b;
+   return b + fixed <= (size_t)ctx->max_smem;
+}
+
+// blocks that cooperate on one chain: 1 on small instances (a round is a few microseconds there: a grid barrier per
+// round would cost as much), more as the neighbourhood grows (numIters = |VNS|^2 proposals per call, :343-362)
+int c2_blocks(const vnsgpu_ctx *ctx)
+{
+   if (ctx->chain_blocks > 0) return std::min(ctx->chain_blocks, ctx->num_sms);
+   const long long c2 = (long long)ctx->I.C * ctx->I.C;
+   if (c2 < 16384) return 1;
+   return (int)std::min<long long>(ctx->num_sms, std::max<long long>(2, c2 / 2048));
+}
+
+static vnsgpu_status c2_prepare(vnsgpu_ctx *ctx, int ncta, C2Env *E, int cinfo_in_smem)
+{
+   const InstDev &I = ctx->I;
+   if (!ctx->d_dmin32) {
+      CK(cudaMalloc(&ctx->d_dmin32, sizeof(int) * (size_t)I.C * I.C));
+      k_dmin_to_int<<<(I.C * I.C + 255) / 256, 256, 0, ctx->stream>>>(I.C * I.C, ctx->d_dmin, ctx->d_dmin32);
+      LAUNCHED(ctx);
+      std::vector<int2> ci(I.C);
+      for (int c = 0; c < I.C; ++c) ci[c] = make_int2(ctx->off[c], ctx->m[c]);
+      CK(cudaMalloc(&ctx->d_cinfo, sizeof(int2) * I.C));
+      CK(cudaMemcpyAsync(ctx->d_cinfo, ci.data(), sizeof(int2) * I.C, cudaMemcpyHostToDevice, ctx->stream));
+      CK(cudaStreamSynchronize(ctx->stream));
+   }
+   if (ncta > 1 && ctx->c2_ncta < ncta) {
+      if (ctx->d_c2grid) { CK(cudaStreamSynchronize(ctx->stream)); CK(cudaFree(ctx->d_c2grid)); }
+      ctx->d_c2grid = nullptr;
+      ctx->c2_ncta = 0;
+      std::vector<unsigned> J;
+      build_jump(ncta, J);
+      const size_t o_slots = 256, o_jump = o_slots + sizeof(C2Slot) * 2 * ncta, total = o_jump + sizeof(unsigned) * J.size();
+      CK(cudaMalloc(&ctx->d_c2grid, total));
+      CK(cudaMemsetAsync(ctx->d_c2grid, 0, o_jump, ctx->stream));
+      CK(cudaMemcpyAsync((char *)ctx->d_c2grid + o_jump, J.data(), sizeof(unsigned) * J.size(), cudaMemcpyHostToDevice, ctx->stream));
+      CK(cudaStreamSynchronize(ctx->stream));
+      ctx->c2_ncta = ncta;
+      ctx->c2_slots_off = o_slots; ctx->c2_jump_off = o_jump;
+   }
+   E->I = I; E->Dv = ctx->d_D32; E->dmin = ctx->d_dmin32; E->g_cinfo = (const int2 *)ctx->d_cinfo; E->cinfo_in_smem = cinfo_in_smem;
+   E->grid = C2Grid{nullptr, nullptr, nullptr, nullptr, 1};
+   if (ncta > 1) {
+      char *b = (char *)ctx->d_c2grid;
+      CK(cudaMemsetAsync(b, 0, 256, ctx->stream));            // barrier counter + control words
+      E->grid.bar = (unsigned long long *)b;
+      E->grid.gctl = (int *)(b + 64);
+      E->grid.slots = (C2Slot *)(b + ctx->c2_slots_off);
+      E->grid.jump = (const unsigned *)(b + ctx->c2_jump_off);
+      E->grid.ncta = ncta;
+   }
+   return VNSGPU_OK;
+}
+
+static int c2_variant(const vnsgpu_ctx *ctx)
+{
+   int G = ctx->group_lanes;
+   if (const char *e = getenv("VNSGPU_CHAIN_G")) { const int g = atoi(e); if (g == 8 || g == 16 || g == 32) G = g; }
+   while (G < 32 && (ctx->I.mp + G - 1) / G > (G == 8 ? 4 : 2)) G *= 2;
+   const int nr = (ctx->I.mp + G - 1) / G;
+   if (G == 8) return nr <= 1 ? 0 : (nr <= 2 ? 1 : 2);
+   if (G == 16) return nr <= 1 ? 3 : 4;
+   return 5;
+}
+
+template <typename K> static vnsgpu_status c2_launch(vnsgpu_ctx *ctx, K kernel, int nblocks, bool coop, size_t smem, void **args)
+{
+   CK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+   if (coop) CK(cudaLaunchCooperativeKernel((const void *)kernel, dim3(nblocks), dim3(C2_THREADS), args, smem, ctx->stream));
+   else CK(cudaLaunchKernel((const void *)kernel, dim3(nblocks), dim3(C2_THREADS), args, smem, ctx->stream));
+   LAUNCHED(ctx);
+   return VNSGPU_OK;
+}
+
+#define C2_DISPATCH(KERNEL, nblocks_, coop_)                                                            \
+   switch (c2_variant(ctx)) {                                                                           \
+   case 0: return c2_launch(ctx, KERNEL<8, 1>, nblocks_, coop_, smem, args);                            \
+   case 1: return c2_launch(ctx, KERNEL<8, 2>, nblocks_, coop_, smem, args);                            \
+   case 2: return c2_launch(ctx, KERNEL<8, 4>, nblocks_, coop_, smem, args);                            \
+   case 3: return c2_launch(ctx, KERNEL<16, 1>, nblocks_, coop_, smem, args);                           \
+   case 4: return c2_launch(ctx, KERNEL<16, 2>, nblocks_, coop_, smem, args);                           \
+   default: return c2_launch(ctx, KERNEL<32, 1>, nblocks_, coop_, smem, args);                          \
+   }
+
+vnsgpu_status c2_launch_ls(vnsgpu_ctx *ctx, int path, int kind, int num_changes, double budget, int skip, size_t smem, int cinfo_in_smem)
+{
+   const int ncta = c2_blocks(ctx);
+   C2Env E;
+   vnsgpu_status s = c2_prepare(ctx, ncta, &E, cinfo_in_smem);
+   if (s) return s;
+   PathDev P = ctx->paths[path].d;
+   RngState *rng = ctx->d_rng;
+   LsStats *st = ctx->d_stats;
+   long long *prof = ctx->d_prof;
+   void *args[] = {&E, &P, &kind, &num_changes, &budget, &skip, &rng, &st, &prof};
+   C2_DISPATCH(k_chain2_ls, ncta, ncta > 1)
+}
+
+vnsgpu_status c2_launch_vns(vnsgpu_ctx *ctx, int path, const VnsParamsDev &prm_, double *d_ir, double *d_il, double *d_it, size_t smem,
+                            int cinfo_in_smem)
+{
+   const int ncta = c2_blocks(ctx);
+   C2Env E;
+   vnsgpu_status s = c2_prepare(ctx, ncta, &E, cinfo_in_smem);
+   if (s) return s;
+   PathDev P = ctx->paths[path].d;
+   VnsParamsDev prm = prm_;
+   RngState *rng = ctx->d_rng;
+   VnsResultDev *res = ctx->d_res;
+   long long *prof = ctx->d_prof;
+   void *args[] = {&E, &P, &prm, &rng, &res, &d_ir, &d_il, &d_it, &prof};
+   C2_DISPATCH(k_chain2_vns_run, ncta, ncta > 1)
+}
+
+vnsgpu_status c2_launch_multi(vnsgpu_ctx *ctx, int nruns, void *d_slots_, const VnsParamsDev &prm_, size_t smem, int cinfo_in_smem)
+{
+   C2Env E;
+   vnsgpu_status s = c2_prepare(ctx, 1, &E, cinfo_in_smem);
+   if (s) return s;
+   C2RunSlot *d_slots = (C2RunSlot *)d_slots_;
+   VnsParamsDev prm = prm_;
+   void *args[] = {&E, &d_slots, &prm};
+   C2_DISPATCH(k_chain2_vns_multi, nruns, false)
+}
+
+size_t c2_run_slot_bytes() { return sizeof(C2RunSlot); }
+void c2_run_slot_fill(void *slot, const PathDev &tour, const RngState &rng)
+{
+   C2RunSlot *s = (C2RunSlot *)slot;
+   s->tour = tour; s->rng = rng;
+   memset(&s->res, 0, sizeof(VnsResultDev));
+}
+const VnsResultDev &c2_run_slot_result(const void *slot) { return ((const C2RunSlot *)slot)->res; }

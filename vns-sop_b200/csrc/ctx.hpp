@@ -78,6 +78,14 @@ struct vnsgpu_ctx {
    int num_sms = 148;
    int max_smem = 48 * 1024;      // opt-in shared memory per block
    bool use_smem_chain = true;    // vnsgpu_set_smem_chain
+   // second search chain (chain2.cuh): exact-int tables, lower bound first, 1 .. num_sms cooperating thread blocks
+   bool use_chain2 = true;        // vnsgpu_set_chain_form
+   int chain_blocks = 0;          // vnsgpu_set_chain_blocks: 0 = from the instance size
+   int *d_dmin32 = nullptr;       // cluster-pair minima as int32
+   void *d_cinfo = nullptr;       // int2 {first sample, size} per cluster
+   void *d_c2grid = nullptr;      // grid barrier + control words, slots, RNG jump matrices
+   int c2_ncta = 0;
+   size_t c2_slots_off = 0, c2_jump_off = 0;
    // the host-buffer evaluation call as a CUDA graph (eval_batch_host)
    bool use_graph = true, hg_seen = false;
    HostGraphKey hg_key, hg_last;

@@ -38,6 +38,8 @@ static void free_instance(vnsgpu_ctx *ctx)
    cudaFree(ctx->d_m); cudaFree(ctx->d_off); cudaFree(ctx->d_clof); cudaFree(ctx->d_reward);
    cudaFree(ctx->d_D); cudaFree(ctx->d_dmin); cudaFree(ctx->d_dmax); cudaFree(ctx->d_seg); cudaFree(ctx->d_D32); cudaFree(ctx->d_D16);
    cudaFree(ctx->d_hist); cudaFree(ctx->d_perm); cudaFree(ctx->d_segmeta); cudaFree(ctx->d_vec); cudaFree(ctx->d_veclb);
+   cudaFree(ctx->d_dmin32); cudaFree(ctx->d_cinfo);
+   ctx->d_dmin32 = nullptr; ctx->d_cinfo = nullptr;
    ctx->d_segmeta = nullptr; ctx->seg_ok = false; ctx->d_vec = nullptr; ctx->d_veclb = nullptr;
    ctx->d_D32 = nullptr; ctx->d_D16 = nullptr; ctx->d_hist = ctx->d_perm = nullptr; ctx->perm_cap = 0;
    ctx->d_m = ctx->d_off = ctx->d_clof = ctx->d_seg = nullptr;
@@ -52,7 +54,7 @@ void vnsgpu_destroy(vnsgpu_ctx *ctx)
    cudaStreamSynchronize(ctx->stream);
    free_instance(ctx);
    cudaFree(ctx->d_scratch); cudaFree(ctx->d_rng); cudaFree(ctx->d_stats); cudaFree(ctx->d_first);
-   cudaFree(ctx->d_res); cudaFree(ctx->d_info); cudaFree(ctx->d_prof); cudaFree(ctx->d_stop);
+   cudaFree(ctx->d_res); cudaFree(ctx->d_info); cudaFree(ctx->d_prof); cudaFree(ctx->d_stop); cudaFree(ctx->d_c2grid);
    if (ctx->s_in) {
       cudaStreamDestroy(ctx->s_in); cudaStreamDestroy(ctx->s_out); cudaEventDestroy(ctx->ev_start); cudaEventDestroy(ctx->ev_out);
       for (int k = 0; k < VNS_PIPE_EVENTS; ++k) { cudaEventDestroy(ctx->ev_in[k]); cudaEventDestroy(ctx->ev_k[k]); }
@@ -82,6 +84,18 @@ vnsgpu_status vnsgpu_set_target_reward(vnsgpu_ctx *ctx, double target)
 vnsgpu_status vnsgpu_set_smem_chain(vnsgpu_ctx *ctx, int enable)
 {
    ctx->use_smem_chain = enable != 0;
+   return VNSGPU_OK;
+}
+
+vnsgpu_status vnsgpu_set_chain_form(vnsgpu_ctx *ctx, int form)
+{
+   ctx->use_chain2 = form != 1;
+   return VNSGPU_OK;
+}
+
+vnsgpu_status vnsgpu_set_chain_blocks(vnsgpu_ctx *ctx, int blocks)
+{
+   ctx->chain_blocks = blocks < 0 ? 0 : blocks;
    return VNSGPU_OK;
 }
 
@@ -191,6 +205,7 @@ static vnsgpu_status build_table(vnsgpu_ctx *ctx, TableJob J, bool maybe_int)
    // room behind the int32 table for the segment products of any path: <= (N + mp)^2 / 2 entries
    const long long segcap = ((long long)I.N + I.mp + 1) * ((long long)I.N + I.mp + 1) / 2;
    if (ctx->d_D32) { CK(cudaFree(ctx->d_D32)); ctx->d_D32 = nullptr; }
+   if (ctx->d_dmin32) { CK(cudaFree(ctx->d_dmin32)); CK(cudaFree(ctx->d_cinfo)); ctx->d_dmin32 = nullptr; ctx->d_cinfo = nullptr; }
    if (maybe_int) {   // optimistic: the copy is dropped again if the classification says no
       ctx->seg_ok = true;                                  // block offsets are 64-bit
       // + 8 KB: k_eval_vec lets a row pointer run up to 31 rows past a block.  Everything behind the table is zeroed

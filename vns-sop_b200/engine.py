@@ -16,7 +16,7 @@ F_FEASIBLE, F_ACCEPT, F_LB_SKIP, F_BAD = 1, 2, 4, 8
 NO_KEY = 0x7f7f7f7f7f7f7f7f      # VNSGPU_NO_KEY
 CAND_DTYPE = np.dtype([("op", np.int32), ("a", np.int32), ("b", np.int32), ("gain_cluster", np.int32)])
 
-_STATUS = {1: "E_RANGE", 2: "E_CUDA", 3: "E_STATE", 4: "E_INCONSISTENT", 5: "E_NOMEM"}
+_STATUS = {1: "E_RANGE", 2: "E_CUDA", 3: "E_STATE", 4: "E_INCONSISTENT", 5: "E_NOMEM", 6: "E_TOO_LARGE", 7: "E_NCCL"}
 
 
 class VnsGpuError(RuntimeError):
@@ -59,6 +59,8 @@ _SIGS = {
     "vnsgpu_set_u16_table": [vp, C.c_int],
     "vnsgpu_set_segment_cache": [vp, C.c_int],
     "vnsgpu_set_smem_chain": [vp, C.c_int],
+    "vnsgpu_set_chain_form": [vp, C.c_int],
+    "vnsgpu_set_chain_blocks": [vp, C.c_int],
     "vnsgpu_set_target_reward": [vp, C.c_double],
     "vnsgpu_chain_cycles": [vp, C.POINTER(C.c_int64), C.c_int],
     "vnsgpu_int_path_active": [vp],
@@ -205,6 +207,14 @@ class Engine:
 
     def set_smem_chain(self, enable):
         self._ck(self.lib.vnsgpu_set_smem_chain(self.h, int(enable)))
+
+    def set_chain_form(self, form):
+        """0: second form (lower bound first, shake in shared memory, integer tables), 1: first form"""
+        self._ck(self.lib.vnsgpu_set_chain_form(self.h, int(form)))
+
+    def set_chain_blocks(self, blocks):
+        """thread blocks cooperating on one trajectory-exact chain (0: from the instance size)"""
+        self._ck(self.lib.vnsgpu_set_chain_blocks(self.h, int(blocks)))
 
     def set_u16_table(self, enable):
         self._ck(self.lib.vnsgpu_set_u16_table(self.h, int(enable)))

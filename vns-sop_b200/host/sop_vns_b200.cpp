@@ -408,7 +408,7 @@ int run(int argc, char **argv)
       int best = -1;
       const auto t0 = std::chrono::steady_clock::now();
       vnsgpu_status st = vnsgpu_vns_run_batch(eng.ctx(), tour.handle(), nruns, seeds.data(), &prm, res.data(), &best, tours.data());
-      if (st == VNSGPU_E_STATE) {   // instance beyond the one-block-per-run kernel: run the seeds one by one
+      if (st == VNSGPU_E_TOO_LARGE) {   // instance beyond the one-block-per-run kernel: run the seeds one by one (any other status is a real failure)
          for (int i = 0; i < nruns; ++i) recs[i] = iterate_device(eng, cfg, pb, seeds[i], tour);
       } else {
          eng.check(st);
