@@ -218,6 +218,20 @@ static inline int vnsgpu_result_flags(uint32_t w)
 }
 vnsgpu_status vnsgpu_eval_batch_packed32r(vnsgpu_ctx *ctx, int path, int64_t n, const uint32_t *packed, double budget,
                                           int skip, uint32_t *result, int64_t *first_accept);
+/* Allocation-free variant of vnsgpu_eval_batch.  It has no counterpart in the reference and was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments, results and flags as vnsgpu_eval_batch; the staged descriptors and results
+ * live in a file-scope static __device__ array of the library (about 0.5 MB that every GPU which loads the library holds
+ * until exit) instead of context scratch, the candidates are evaluated block by block (no segment products, endpoint
+ * vectors or sort: those caches are allocated on demand by the other entry points), and the call makes no cudaMalloc,
+ * cudaFree or other allocating call.  n > VNSGPU_NOALLOC_MAX_CANDS returns VNSGPU_E_RANGE with a message in
+ * vnsgpu_last_error.  All calls on one device share the array, which keeps the last call's contents: the call clears
+ * what has to start clean, and calls that overlap on the GPU (several contexts or streams on one device) race - keep
+ * them serial. */
+#define VNSGPU_NOALLOC_MAX_CANDS 16384
+vnsgpu_status vnsgpu_eval_batch_noalloc(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *cands, double budget,
+                                        int skip, double *len, double *lb, uint8_t *flags, int64_t *first_accept);
+int64_t vnsgpu_noalloc_max_cands(void);
 /* device buffers, asynchronous on `stream` (NULL = context stream); d_first_accept: one int64 that
  * the call resets and fills like first_accept above (-1 = none), or NULL */
 vnsgpu_status vnsgpu_eval_batch_dev(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *d_cands,

@@ -79,6 +79,7 @@ _SIGS = {
     "vnsgpu_path_get_solution": [vp, C.c_int, ip, ip, dp],
     "vnsgpu_path_get_dp": [vp, C.c_int, dp, dp, C.c_int],
     "vnsgpu_eval_batch": [vp, C.c_int, C.c_int64, vp, C.c_double, C.c_int, dp, dp, vp, C.POINTER(C.c_int64)],
+    "vnsgpu_eval_batch_noalloc": [vp, C.c_int, C.c_int64, vp, C.c_double, C.c_int, dp, dp, vp, C.POINTER(C.c_int64)],
     "vnsgpu_eval_batch_packed": [vp, C.c_int, C.c_int64, vp, C.c_double, C.c_int, dp, dp, vp, C.POINTER(C.c_int64)],
     "vnsgpu_eval_batch_packed32": [vp, C.c_int, C.c_int64, vp, C.c_double, C.c_int, vp, vp, C.POINTER(C.c_int64)],
     "vnsgpu_eval_batch_packed32r": [vp, C.c_int, C.c_int64, vp, C.c_double, C.c_int, vp, C.POINTER(C.c_int64)],
@@ -95,7 +96,7 @@ _SIGS = {
     "vnsgpu_path_destroy": [vp, C.c_int],
     "vnsgpu_set_vector_cache": [vp, C.c_int],
 }
-EXPORTS = sorted(list(_SIGS) + ["vnsgpu_destroy", "vnsgpu_last_error", "vnsgpu_version", "vnsgpu_launch_count",
+EXPORTS = sorted(list(_SIGS) + ["vnsgpu_noalloc_max_cands", "vnsgpu_destroy", "vnsgpu_last_error", "vnsgpu_version", "vnsgpu_launch_count",
                                 "vnsgpu_table_bytes", "vnsgpu_table_kernel_ms", "vnsgpu_rng_seed", "vnsgpu_rng_next"])
 
 
@@ -117,6 +118,7 @@ def load_library(build_if_stale=True):
     lib.vnsgpu_last_error.argtypes, lib.vnsgpu_last_error.restype = [vp], C.c_char_p
     lib.vnsgpu_version.argtypes, lib.vnsgpu_version.restype = [], C.c_char_p
     lib.vnsgpu_launch_count.argtypes, lib.vnsgpu_launch_count.restype = [vp], C.c_int64
+    lib.vnsgpu_noalloc_max_cands.argtypes, lib.vnsgpu_noalloc_max_cands.restype = [], C.c_int64
     lib.vnsgpu_table_bytes.argtypes, lib.vnsgpu_table_bytes.restype = [vp], C.c_int64
     lib.vnsgpu_table_kernel_ms.argtypes, lib.vnsgpu_table_kernel_ms.restype = [vp], C.c_double
     lib.vnsgpu_rng_seed.argtypes, lib.vnsgpu_rng_seed.restype = [C.POINTER(Rng), C.c_uint32], None
@@ -369,6 +371,18 @@ class VnsSopPath:
         budget = self.e.pb.budget if budget is None else budget
         self.e._ck(self.lib.vnsgpu_eval_batch(self.e.h, self.h, n, c.ctypes.data, budget, skip, _d(ln), _d(lb),
                                               fl.ctypes.data, C.byref(first)))
+        return ln, lb, fl, first.value
+
+    def eval_batch_noalloc(self, cands, budget=None, skip=1):
+        """eval_batch through vnsgpu_eval_batch_noalloc: scratch in the library's static device array, no allocation;
+        at most VNSGPU_NOALLOC_MAX_CANDS candidates per call."""
+        c = self.make_cands(cands)
+        n = len(c)
+        ln, lb, fl = np.empty(n), np.empty(n), np.zeros(n, np.uint8)
+        first = C.c_int64(-1)
+        budget = self.e.pb.budget if budget is None else budget
+        self.e._ck(self.lib.vnsgpu_eval_batch_noalloc(self.e.h, self.h, n, c.ctypes.data, budget, skip, _d(ln), _d(lb),
+                                                      fl.ctypes.data, C.byref(first)))
         return ln, lb, fl, first.value
 
     @staticmethod
