@@ -140,6 +140,12 @@ vnsgpu_status vnsgpu_set_chain_form(vnsgpu_ctx *ctx, int form);
  * accepted proposal wins, exactly the proposal the reference's sequential loop would have applied.  0 (default): from the
  * instance size (1 block up to ~128 clusters, then |clusters|^2 / 2048, at most one per SM). */
 vnsgpu_status vnsgpu_set_chain_blocks(vnsgpu_ctx *ctx, int blocks);
+/* Product tree of the second chain form: an aligned segment tree of exact min-plus products over the path's edges.  A run
+ * of consecutive layers inside a tryToMove / tryToExchange chain costs at most 2 log2(T) steps instead of `span`, and
+ * after an accepted move every layer's shortest / shortest_back row is recomputed independently through the tree
+ * (updateAfterInsert / updateAfterRemove, vns_sop_path.cpp:1406-1540, are T dependent steps).  Exact on integer tables
+ * (associativity): same trajectory.  mode -1 (default): on from 96 clusters; 0 off; 1 on (tests run both). */
+vnsgpu_status vnsgpu_set_chain_tree(vnsgpu_ctx *ctx, int mode);
 
 /* ---- instance + distance table: replaces VnsSopPath::setSamplesDistances (vns_sop_path.cpp:38-48)
  *      fed by SOPLoader::getSOPFromNodes / getSOPFromWeightMatrix / getOP / getOPN ---------------- */

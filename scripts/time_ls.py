@@ -9,7 +9,8 @@ sf, pb = load_problem(name)
 e = engine.Engine(0).load_problem(pb)
 for mode in modes:
     e.set_chain_form(1 if mode == "v1" else 0)
-    e.set_chain_blocks(int(mode.split("-")[1]) if mode.startswith("c2-") else 1)
+    e.set_chain_blocks(int(mode.split("-")[1].rstrip("t")) if mode.startswith("c2-") else 1)
+    e.set_chain_tree(1 if mode.endswith("t") and mode != "v1" else 0)
     p = e.path(); p.greedy_insertion(); rng = engine.seeded_rng(7)
     n = len(p.vns) ** 2
     tot = {1: [0, 0, 0, 0.0], 2: [0, 0, 0, 0.0]}

@@ -46,7 +46,7 @@ bool c2_fits(const vnsgpu_ctx *ctx, size_t *smem, int *cinfo_in_smem)
 {
    if (!ctx->use_chain2 || !vnsgpu_int_path_active(ctx) || ctx->I.mp > 32 || !group_kernel_ok(ctx)) return false;
    // static shared memory of the kernels (control block, slot, RNG, the few words of search.cuh's helpers) + margin
-   const size_t fixed = sizeof(C2Ctl) + sizeof(C2Slot) + sizeof(RngState) + 2048;
+   const size_t fixed = sizeof(C2Ctl) + sizeof(C2Slot) + sizeof(RngState) + sizeof(C2Tree) + 2048;
    size_t b = c2_smem_bytes(ctx->I.C, ctx->I.mp, true);
    *cinfo_in_smem = 1;
    if (b + fixed > (size_t)ctx->max_smem) {
@@ -59,17 +59,25 @@ bool c2_fits(const vnsgpu_ctx *ctx, size_t *smem, int *cinfo_in_smem)
    return b + fixed <= (size_t)ctx->max_smem;
 }
 
-// blocks that cooperate on one chain: 1 on small instances (a round is a few microseconds there: a grid barrier per
-// round would cost as much), more as the neighbourhood grows (numIters = |VNS|^2 proposals per call, :343-362)
+// blocks that cooperate on one chain: 1 up to ~256 clusters (with the product tree a round's evaluation is a few
+// microseconds there: a grid barrier per round costs as much as it saves - vm1084, 219 clusters: 0.254 / 0.192 us per
+// proposal on one block, 0.239 / 0.176 on eight), more as the neighbourhood grows (numIters = |VNS|^2, :343-362)
 int c2_blocks(const vnsgpu_ctx *ctx)
 {
    if (ctx->chain_blocks > 0) return std::min(ctx->chain_blocks, ctx->num_sms);
    const long long c2 = (long long)ctx->I.C * ctx->I.C;
-   if (c2 < 16384) return 1;
-   return (int)std::min<long long>(ctx->num_sms, std::max<long long>(2, c2 / 2048));
+   if (c2 < 65536) return 1;
+   return (int)std::min<long long>(ctx->num_sms, std::max<long long>(2, c2 / 32768));
 }
 
-static vnsgpu_status c2_prepare(vnsgpu_ctx *ctx, int ncta, C2Env *E, int cinfo_in_smem)
+// product tree (chain2_tree.cuh): pays once a tour has a few dozen targets; one replica per thread block
+static bool c2_tree_wanted(const vnsgpu_ctx *ctx)
+{
+   if (ctx->chain_tree >= 0) return ctx->chain_tree != 0;
+   return ctx->I.C >= 96;
+}
+
+static vnsgpu_status c2_prepare(vnsgpu_ctx *ctx, int ncta, C2Env *E, int cinfo_in_smem, int nblocks)
 {
    const InstDev &I = ctx->I;
    if (!ctx->d_dmin32) {
@@ -97,6 +105,19 @@ static vnsgpu_status c2_prepare(vnsgpu_ctx *ctx, int ncta, C2Env *E, int cinfo_i
       ctx->c2_slots_off = o_slots; ctx->c2_jump_off = o_jump;
    }
    E->I = I; E->Dv = ctx->d_D32; E->dmin = ctx->d_dmin32; E->g_cinfo = (const int2 *)ctx->d_cinfo; E->cinfo_in_smem = cinfo_in_smem;
+   E->tree_base = nullptr; E->tree_stride = 0;
+   if (c2_tree_wanted(ctx)) {
+      int lvl_off[C2_MAXLEV + 2], nlev = 0;
+      const long long stride = (long long)c2_tree_layout(I.C + 2, lvl_off, &nlev) * I.mp * I.mp;
+      const size_t need = sizeof(int) * (size_t)stride * (size_t)nblocks;
+      if (need > ctx->c2_tree_bytes) {
+         if (ctx->d_c2tree) { CK(cudaStreamSynchronize(ctx->stream)); CK(cudaFree(ctx->d_c2tree)); }
+         ctx->d_c2tree = nullptr; ctx->c2_tree_bytes = 0;
+         CK(cudaMalloc(&ctx->d_c2tree, need));
+         ctx->c2_tree_bytes = need;
+      }
+      E->tree_base = ctx->d_c2tree; E->tree_stride = stride;
+   }
    E->grid = C2Grid{nullptr, nullptr, nullptr, nullptr, 1};
    if (ncta > 1) {
       char *b = (char *)ctx->d_c2grid;
@@ -144,7 +165,7 @@ vnsgpu_status c2_launch_ls(vnsgpu_ctx *ctx, int path, int kind, int num_changes,
 {
    const int ncta = c2_blocks(ctx);
    C2Env E;
-   vnsgpu_status s = c2_prepare(ctx, ncta, &E, cinfo_in_smem);
+   vnsgpu_status s = c2_prepare(ctx, ncta, &E, cinfo_in_smem, ncta);
    if (s) return s;
    PathDev P = ctx->paths[path].d;
    RngState *rng = ctx->d_rng;
@@ -159,7 +180,7 @@ vnsgpu_status c2_launch_vns(vnsgpu_ctx *ctx, int path, const VnsParamsDev &prm_,
 {
    const int ncta = c2_blocks(ctx);
    C2Env E;
-   vnsgpu_status s = c2_prepare(ctx, ncta, &E, cinfo_in_smem);
+   vnsgpu_status s = c2_prepare(ctx, ncta, &E, cinfo_in_smem, ncta);
    if (s) return s;
    PathDev P = ctx->paths[path].d;
    VnsParamsDev prm = prm_;
@@ -173,7 +194,7 @@ vnsgpu_status c2_launch_vns(vnsgpu_ctx *ctx, int path, const VnsParamsDev &prm_,
 vnsgpu_status c2_launch_multi(vnsgpu_ctx *ctx, int nruns, void *d_slots_, const VnsParamsDev &prm_, size_t smem, int cinfo_in_smem)
 {
    C2Env E;
-   vnsgpu_status s = c2_prepare(ctx, 1, &E, cinfo_in_smem);
+   vnsgpu_status s = c2_prepare(ctx, 1, &E, cinfo_in_smem, nruns);
    if (s) return s;
    C2RunSlot *d_slots = (C2RunSlot *)d_slots_;
    VnsParamsDev prm = prm_;

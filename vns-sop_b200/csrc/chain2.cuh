@@ -25,6 +25,7 @@
 #include "common.cuh"
 #include "eval.cuh"
 #include "search.cuh"
+#include "chain2_tree.cuh"
 
 #define C2_THREADS 512
 #define C2_WARPS (C2_THREADS / 32)
@@ -72,6 +73,7 @@ struct C2Sm {
    int *lcl, *vns, *seg;     // 2R, 2R, alias of Brev
    const int2 *cinfo;        // C: {first sample, size}; shared memory when it fits, else global
    int2 *cinfo_sm;
+   const C2Tree *tr;         // product tree of this block (chain2_tree.cuh); nlev = 0: none
 };
 
 // ints: F, Brev R x mpp each (mpp = max(mp, 2): the shake's scratch of 2R ints lives in Brev, which is rebuilt after every
@@ -101,6 +103,7 @@ static __device__ __forceinline__ C2Sm c2_carve(unsigned char *base, int C, int 
    size_t o = (sizeof(int) * c2_state_ints(C, mp) + 15) & ~(size_t)15;
    s.cinfo_sm = cinfo_in_smem ? reinterpret_cast<int2 *>(base + o) : nullptr;
    s.cinfo = cinfo_in_smem ? s.cinfo_sm : g_cinfo;
+   s.tr = nullptr;
    return s;
 }
 
@@ -111,7 +114,19 @@ struct C2Env {             // per-launch constants
    const int2 *g_cinfo;    // C
    C2Grid grid;
    int cinfo_in_smem;
+   int *tree_base;         // product-tree replicas, one per thread block (null: no tree)
+   long long tree_stride;  // ints per replica
 };
+
+// the block's tree descriptor (thread 0 of every kernel fills it before the first barrier)
+static __device__ __forceinline__ void c2_tree_init(C2Tree &tr, const C2Env &E)
+{
+   int nlev = 0;
+   c2_tree_layout(E.I.C + 2, tr.lvl_off, &nlev);
+   tr.pitch = E.I.mp * E.I.mp;
+   tr.nodes = E.tree_base ? E.tree_base + (long long)blockIdx.x * E.tree_stride : nullptr;
+   tr.nlev = tr.nodes ? nlev : 0;
+}
 
 // ---- grid barrier (cooperative launch: all blocks resident) ----------------------------------------------------------
 static __device__ __forceinline__ void c2_grid_sync(const C2Grid &G, unsigned long long &epoch)
@@ -268,15 +283,86 @@ static __device__ void c2_pd_scan(const C2Env &E, const C2Sm &s, int S, int lane
    __syncwarp();
 }
 
-// all threads: forward layers [lf, S] on warp 0, backward [lb, 0] on warp 1, prefix sums on warp 2
-static __device__ void c2_rescan(const C2Env &E, const C2Sm &s, C2Ctl &ctl, int T, int lf, int lb)
+// F / B rows through the product tree: every layer of [lf, S] (forward, from row lf - 1) and of [lb, 0] (backward, from
+// row lb + 1) is an independent chain of at most 2 log2(T) nodes, one sub-warp group each; warps 0 .. W/2-1 take the
+// forward layers, the others the backward ones (the last warp first rebuilds the prefix sums of the cluster-pair minima)
+template <int G, int NR>
+static __device__ void c2_rows_by_tree(const C2Env &E, const C2Sm &s, int S, int lf, int lb)
+{
+   constexpr int NG = 32 / G, HW = C2_WARPS / 2;
+   constexpr unsigned FULL = 0xffffffffu;
+   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, gl = lane % G, gq = lane / G;
+   const int mp = E.I.mp, nlev = s.tr->nlev;
+   if (warp < HW) {
+      const int nF = S - lf + 1;
+      const int m0 = s.cinfo[s.lcl[lf - 1]].y;
+      for (int base = warp * NG; base < nF; base += HW * NG) {
+         const int q = base + gq, l = lf + q;
+         int lv, nd;
+         const int K = q < nF ? c2_decomp(nlev, lf - 1, l, -1, &lv, &nd) : 0;
+         int v[NR], mo = 0;
+#pragma unroll
+         for (int r = 0; r < NR; ++r) v[r] = gl + r * G < m0 ? s.F[(lf - 1) * mp + gl + r * G] : C2_INF;
+         c2_chain<G, NR, false>(K, gl, [&](int k) {
+            int l2 = 0, n2 = 0;
+            c2_decomp(nlev, lf - 1, l, k - 1, &l2, &n2);
+            return c2_tree_mat(*s.tr, E.Dv, E.I.N, s.cinfo, s.lcl, l2, n2);
+         }, v, mo);
+         int mn = C2_INF;
+#pragma unroll
+         for (int r = 0; r < NR; ++r) {
+            const int j = gl + r * G;
+            if (K && j < mo) { s.F[l * mp + j] = v[r]; mn = min(mn, v[r]); }
+         }
+#pragma unroll
+         for (int sft = G / 2; sft > 0; sft >>= 1) mn = min(mn, __shfl_xor_sync(FULL, mn, sft, G));
+         if (K && gl == 0) s.minF[l] = mn;
+      }
+   } else {
+      if (warp == C2_WARPS - 1) c2_pd_scan(E, s, S, lane);
+      const int nB = lb + 1;
+      const int m0 = s.cinfo[s.lcl[lb + 1]].y;
+      for (int base = (warp - HW) * NG; base < nB; base += (C2_WARPS - HW) * NG) {
+         const int q = base + gq, l = lb - q;
+         int lv, nd;
+         const int K = q < nB ? c2_decomp(nlev, l, lb + 1, -1, &lv, &nd) : 0;
+         int v[NR], mo = 0;
+#pragma unroll
+         for (int r = 0; r < NR; ++r) v[r] = gl + r * G < m0 ? s.Brev[(S - (lb + 1)) * mp + gl + r * G] : C2_INF;
+         c2_chain<G, NR, true>(K, gl, [&](int k) {          // nodes from the right: B[l] = M_1 (x) (M_2 (x) ... (M_K (x) B[lb+1]))
+            int l2 = 0, n2 = 0;
+            c2_decomp(nlev, l, lb + 1, K - k, &l2, &n2);
+            return c2_tree_mat(*s.tr, E.Dv, E.I.N, s.cinfo, s.lcl, l2, n2);
+         }, v, mo);
+         int mn = C2_INF;
+#pragma unroll
+         for (int r = 0; r < NR; ++r) {
+            const int j = gl + r * G;
+            if (K && j < mo) { s.Brev[(S - l) * mp + j] = v[r]; mn = min(mn, v[r]); }
+         }
+#pragma unroll
+         for (int sft = G / 2; sft > 0; sft >>= 1) mn = min(mn, __shfl_xor_sync(FULL, mn, sft, G));
+         if (K && gl == 0) s.minBrev[S - l] = mn;
+      }
+   }
+}
+
+// all threads.  Changed edges of the path: [e1lo, e1hi) and [e2lo, e2hi) (product tree).  Without a tree: forward layers
+// [lf, S] on warp 0, backward [lb, 0] on warp 1, prefix sums on warp 2
+template <int G, int NR>
+static __device__ void c2_rescan(const C2Env &E, const C2Sm &s, C2Ctl &ctl, int T, int lf, int lb, int e1lo, int e1hi, int e2lo, int e2hi)
 {
    const int S = T + 1;
    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
    __syncthreads();
-   if (warp == 0) c2_fwd_scan(E, s, S, lf, lane);
-   else if (warp == 1) c2_bwd_scan(E, s, S, lb, lane);
-   else if (warp == 2) c2_pd_scan(E, s, S, lane);
+   if (s.tr->nlev > 0) {
+      c2_tree_rebuild(*s.tr, E.Dv, E.I.N, s.cinfo, s.lcl, S, e1lo, min(e1hi, S), e2lo, min(e2hi, S));
+      c2_rows_by_tree<G, NR>(E, s, S, lf, lb);
+   } else {
+      if (warp == 0) c2_fwd_scan(E, s, S, lf, lane);
+      else if (warp == 1) c2_bwd_scan(E, s, S, lb, lane);
+      else if (warp == 2) c2_pd_scan(E, s, S, lane);
+   }
    __syncthreads();
    if (threadIdx.x == 0) {
       ctl.L = s.minF[S];                                                   // getPathLength :1660-1678
@@ -311,6 +397,7 @@ static __device__ __forceinline__ void c2_shift1(int *arr, int lo, int hi, int d
 
 // insertRandom accept (vns_sop_solver.cpp:621-646): VNS[from] is re-inserted immediately before the element that was
 // at index `to`; only the final state matters.  tg = lcl + 1.
+template <int G, int NR>
 static __device__ void c2_apply_insert(const C2Env &E, const C2Sm &s, C2Ctl &ctl, int from, int to)
 {
    const int T = ctl.T;
@@ -322,23 +409,24 @@ static __device__ void c2_apply_insert(const C2Env &E, const C2Sm &s, C2Ctl &ctl
          c2_shift1(s.vns, from + 1, to - 1, -1);
          c2_shift1(tg, from + 1, to - 1, -1);
          if (threadIdx.x == 0) { s.vns[to - 1] = c; tg[to - 1] = c; }
-         c2_rescan(E, s, ctl, T, from + 1, to);
+         c2_rescan<G, NR>(E, s, ctl, T, from + 1, to, from, to + 1, 0, 0);
       } else {                // travels down to index `to`; layers to+1 .. from+1 change
          c2_shift1(s.vns, to, from - 1, +1);
          c2_shift1(tg, to, from - 1, +1);
          if (threadIdx.x == 0) { s.vns[to] = c; tg[to] = c; }
-         c2_rescan(E, s, ctl, T, to + 1, from + 1);
+         c2_rescan<G, NR>(E, s, ctl, T, to + 1, from + 1, to, from + 2, 0, 0);
       }
    } else {                   // from outside the path (from >= T >= to): one more target at index `to`
       c2_shift1(s.vns, to, from - 1, +1);
       c2_shift1(tg, to, T, +1);               // includes the goal's entry tg[T] = lcl[T+1]
       if (threadIdx.x == 0) { s.vns[to] = c; tg[to] = c; ctl.T = T + 1; }
       // B rows of the old layers to+1 .. S keep their slots (distance from the goal is unchanged)
-      c2_rescan(E, s, ctl, T + 1, to + 1, to + 1);
+      c2_rescan<G, NR>(E, s, ctl, T + 1, to + 1, to + 1, to, T + 2, 0, 0);   // every edge behind the new target moves
    }
 }
 
 // exchangeRandom accept (:807-832): VNS[from] <-> VNS[to]; `to` is always in the path
+template <int G, int NR>
 static __device__ void c2_apply_exchange(const C2Env &E, const C2Sm &s, C2Ctl &ctl, int from, int to)
 {
    const int T = ctl.T;
@@ -352,7 +440,7 @@ static __device__ void c2_apply_exchange(const C2Env &E, const C2Sm &s, C2Ctl &c
    }
    const int lo = (from < T && from < to) ? from : to;
    const int hi = (from < T && from > to) ? from : to;
-   c2_rescan(E, s, ctl, T, lo + 1, hi + 1);
+   c2_rescan<G, NR>(E, s, ctl, T, lo + 1, hi + 1, lo, lo + 2, hi, hi + 2);   // layers lo + 1 and hi + 1 changed
 }
 
 // ---- glibc rand() stream (math_common.cpp:21-28; random_r TYPE_3: x_i = x_{i-3} + x_{i-31}, output >> 1) ----------------
@@ -387,90 +475,68 @@ static __device__ __forceinline__ void c2_ring_jump(C2Ctl &ctl, const RngState &
    __syncwarp();
 }
 
-// ---- evaluation of one survivor by a sub-warp group: forward chain in exact int32 ---------------------------------------
-// Must be called by all 32 lanes; K = 0: idle group.  desc(k) describes block k (1 <= k <= K) of the group's chain.
-// Descriptors are produced one round (G steps) ahead; the describing lane prefetches its block into L1.
-template <int G, int NR, typename Desc>
-static __device__ __forceinline__ int c2_eval(const int *__restrict__ Dv, int K, int m0, int mK, int gl, Desc desc, const int *row0,
-                                              const int *rowK)
+// ---- chain of a proposal: up to two explicit blocks, a run of path edges [ra, rb) walked through the product tree, up to
+//      two explicit blocks; closed against B[sK].  Layers; -1 = the foreign cluster (ADD / REPLACE) ------------------------
+struct C2Code {
+   int K, s0, sK, foreign;
+   int npre, npost, ra, rb, rcnt;
+   int pa0, pb0, pa1, pb1, qa0, qb0, qa1, qb1;
+};
+
+// insertRandom: in-path -> tryToMove(from, to) (vns_sop_path.cpp:932-1154), else tryToAdd(VNS[from], to) (:245-304);
+// exchangeRandom: in-path -> tryToExchange(from, to) (:635-797), else tryToReplace(VNS[from], to) (:456-513)
+static __device__ __forceinline__ C2Code c2_decode(int nlev, int T, int kind, bool in, int from, int to, int cf)
 {
-   constexpr unsigned FULL = 0xffffffffu;
-   int v[NR], breg[NR];
-#pragma unroll
-   for (int r = 0; r < NR; ++r) {
-      const int j = gl + r * G;
-      v[r] = j < m0 ? row0[j] : C2_INF;
-      breg[r] = j < mK ? rowK[j] : C2_INF;
+   C2Code c;
+   c.K = 0; c.s0 = c.sK = 0; c.foreign = cf; c.npre = c.npost = 0; c.ra = c.rb = 0; c.rcnt = 0;
+   c.pa0 = c.pb0 = c.pa1 = c.pb1 = c.qa0 = c.qb0 = c.qa1 = c.qb1 = 0;
+   if (!in) {
+      c.s0 = to; c.sK = kind == 1 ? to + 1 : to + 2;
+      c.npre = 2; c.pa0 = to; c.pb0 = -1; c.pa1 = -1; c.pb1 = c.sK;
+   } else if (kind == 1) {
+      const int i = min(from, to) + 1, j = max(from, to) + 1;
+      if (to > from) {   // up:   i-1, i+1 .. j-1, i, j
+         c.s0 = i - 1; c.sK = j;
+         c.npre = 1; c.pa0 = i - 1; c.pb0 = i + 1;
+         c.ra = i + 1; c.rb = j - 1;
+         c.npost = 2; c.qa0 = j - 1; c.qb0 = i; c.qa1 = i; c.qb1 = j;
+      } else {           // down: i-1, j, i .. j-1, j+1
+         c.s0 = i - 1; c.sK = j + 1;
+         c.npre = 2; c.pa0 = i - 1; c.pb0 = j; c.pa1 = j; c.pb1 = i;
+         c.ra = i; c.rb = j - 1;
+         c.npost = 1; c.qa0 = j - 1; c.qb0 = j + 1;
+      }
+   } else {              // i, j, i+2 .. j-1, i+1, j+1
+      const int i = min(from, to), j = max(from, to) + 1;
+      c.s0 = i; c.sK = j + 1;
+      c.npre = 2; c.pa0 = i; c.pb0 = j; c.pa1 = j; c.pb1 = i + 2;
+      c.ra = i + 2; c.rb = j - 1;
+      c.npost = 2; c.qa0 = j - 1; c.qb0 = i + 1; c.qa1 = i + 1; c.qb1 = j + 1;
    }
-   int fin = C2_INF;
-   const int Kmax = __reduce_max_sync(FULL, K);
-   long long n_rb = 0;
-   int n_ma = 1, n_mb = 1;
-   auto describe = [&](int k) {
-      n_rb = 0; n_ma = 1; n_mb = 1;
-      if (k <= K) {
-         const int4 d = desc(k);      // x, y: block offset (low, high), z: ma, w: mb
-         n_rb = ((long long)d.y << 32) | (unsigned)d.x; n_ma = d.z; n_mb = d.w;
-         const char *p = reinterpret_cast<const char *>(Dv + n_rb);
-         const int bytes = n_ma * n_mb * 4;
-         for (int o = 0; o < bytes; o += 128) asm volatile("prefetch.global.L1 [%0];" ::"l"(p + o));
-      }
-   };
-   describe(gl + 1);
-   for (int e0 = 0; e0 < Kmax; e0 += G) {
-      const long long e_rb = n_rb;
-      int tmax = n_ma, nvmax = n_mb;
-#pragma unroll
-      for (int sft = G; sft < 32; sft <<= 1) {
-         tmax = max(tmax, __shfl_xor_sync(FULL, tmax, sft));
-         nvmax = max(nvmax, __shfl_xor_sync(FULL, nvmax, sft));
-      }
-      const unsigned e_w = (unsigned)n_ma | ((unsigned)n_mb << 8) | ((unsigned)tmax << 16) | ((unsigned)nvmax << 24);
-      if (e0 + G < Kmax) describe(e0 + G + gl + 1);
-      const int kend = min(G, Kmax - e0);
-      for (int kk = 0; kk < kend; ++kk) {
-         const int k = e0 + kk + 1;
-         const int *blk = Dv + __shfl_sync(FULL, e_rb, kk, G);
-         const unsigned w = __shfl_sync(FULL, e_w, kk, G);
-         const int ma = w & 0xff, mb = (w >> 8) & 0xff, tmaxAll = (w >> 16) & 0xff, nvm = w >> 24;
-         int acc[NR];
-#pragma unroll
-         for (int rd = 0; rd < NR; ++rd) {
-            acc[rd] = C2_INF;
-            if (rd == 0 || nvm > rd * G) {                       // warp-uniform
-               const unsigned cbase = (unsigned)min(gl + rd * G, mb - 1);
-#pragma unroll
-               for (int rs = 0; rs < NR; ++rs) {
-                  if (rs == 0 || tmaxAll > rs * G) {              // warp-uniform
-                     const int tlim = max(min(ma - rs * G, G) - 1, 0);
-                     const unsigned sb = cbase + (unsigned)(min(rs * G, ma - 1) * mb);
-                     const int opnd = v[rs];
-                     int dd[G];
-#pragma unroll
-                     for (int t = 0; t < G; ++t) dd[t] = __ldg(blk + (sb + (unsigned)(min(t, tlim) * mb)));
-                     int a0 = C2_INF, a1 = C2_INF;
-#pragma unroll
-                     for (int t = 0; t < G; t += 2) {
-                        a0 = __viaddmin_s32(__shfl_sync(FULL, opnd, min(t, tlim), G), dd[t], a0);
-                        a1 = __viaddmin_s32(__shfl_sync(FULL, opnd, min(t + 1, tlim), G), dd[t + 1], a1);
-                     }
-                     acc[rd] = min(acc[rd], min(a0, a1));
-                  }
-               }
-            }
-         }
-         const bool isK = k == K, mid = k < K;
-#pragma unroll
-         for (int r = 0; r < NR; ++r) {
-            const bool lv = gl + r * G < mb;
-            fin = (isK && lv) ? min(fin, acc[r] + breg[r]) : fin;
-            v[r] = mid ? (lv ? acc[r] : C2_INF) : v[r];
-         }
-      }
+   int l, n;
+   c.rcnt = c.rb > c.ra ? c2_decomp(nlev, c.ra, c.rb, -1, &l, &n) : 0;
+   c.K = c.npre + c.rcnt + c.npost;
+   return c;
+}
+
+// block k (1 <= k <= K) of the chain
+static __device__ __forceinline__ C2Mat c2_code_block(const C2Env &E, const C2Sm &s, const C2Code &c, int k)
+{
+   int la, lb;
+   if (k <= c.npre) { la = k == 1 ? c.pa0 : c.pa1; lb = k == 1 ? c.pb0 : c.pb1; }
+   else if (k <= c.npre + c.rcnt) {
+      int l = 0, n = 0;
+      c2_decomp(s.tr->nlev, c.ra, c.rb, k - c.npre - 1, &l, &n);
+      return c2_tree_mat(*s.tr, E.Dv, E.I.N, s.cinfo, s.lcl, l, n);
+   } else {
+      const int q = k - c.npre - c.rcnt;
+      la = q == 1 ? c.qa0 : c.qa1; lb = q == 1 ? c.qb0 : c.qb1;
    }
-#pragma unroll
-   for (int sft = G / 2; sft > 0; sft >>= 1) fin = min(fin, __shfl_xor_sync(FULL, fin, sft, G));
-   return fin;
+   const int2 cia = s.cinfo[la < 0 ? c.foreign : s.lcl[la]], cib = s.cinfo[lb < 0 ? c.foreign : s.lcl[lb]];
+   C2Mat m;
+   m.p = E.Dv + ((long long)cia.x * E.I.N + (long long)cia.y * cib.x);
+   m.ma = cia.y; m.mb = cib.y;
+   return m;
 }
 
 // ---- lower bound of a proposal in O(1) (one thread): minF(s0) + dist_between + minB(sK) --------------------------------
@@ -594,22 +660,21 @@ static __device__ void c2_local_search(const C2Env &E, const C2Sm &s, C2Ctl &ctl
             const int from = act ? ctl.sfrom[sidx] : 0, to = act ? ctl.sto[sidx] : 0;
             const bool in = from < T;
             const int cf = s.vns[from];
-            int op = -1, a = 0;
-            if (act) {
-               if (kind == 1) { op = in ? VNSGPU_OP_MOVE : VNSGPU_OP_ADD; a = in ? from : cf; }
-               else { op = in ? VNSGPU_OP_EXCHANGE : VNSGPU_OP_REPLACE; a = in ? from : cf; }
-            }
-            const CandCode cc = decode_cand(T, E.I.C, op, a, to);
+            const C2Code cc = act ? c2_decode(s.tr->nlev, T, kind, in, from, to, cf) : C2Code{};
             const int K = cc.K;
-            const int m0 = K ? s.cinfo[s.lcl[cc.s0]].y : 0, mK = K ? s.cinfo[s.lcl[cc.sK]].y : 0;
-            const int fin = c2_eval<G, NR>(E.Dv, K, m0, mK, gl,
-               [&](int k) {
-                  const int la = cand_layer(cc, k - 1), lb_ = cand_layer(cc, k);
-                  const int2 cia = s.cinfo[la < 0 ? cc.foreign : s.lcl[la]], cib = s.cinfo[lb_ < 0 ? cc.foreign : s.lcl[lb_]];
-                  const long long rb = (long long)cia.x * E.I.N + (long long)cia.y * cib.x;
-                  return make_int4((int)(rb & 0xffffffffll), (int)(rb >> 32), cia.y, cib.y);
-               },
-               s.F + cc.s0 * mp, s.Brev + (S - cc.sK) * mp);
+            int v[NR];
+            {
+               const int m0 = K ? s.cinfo[s.lcl[cc.s0]].y : 0;
+#pragma unroll
+               for (int r = 0; r < NR; ++r) v[r] = gl + r * G < m0 ? s.F[cc.s0 * mp + gl + r * G] : C2_INF;
+            }
+            int mK = 0;
+            c2_chain<G, NR, false>(K, gl, [&](int k) { return c2_code_block(E, s, cc, k); }, v, mK);
+            int fin = C2_INF;
+#pragma unroll
+            for (int r = 0; r < NR; ++r) fin = min(fin, (K && gl + r * G < mK) ? v[r] + s.Brev[(S - cc.sK) * mp + gl + r * G] : C2_INF);
+#pragma unroll
+            for (int sft = G / 2; sft > 0; sft >>= 1) fin = min(fin, __shfl_xor_sync(FULL, fin, sft, G));
             if (act && gl == 0) {
                const double L = (double)ctl.L;
                double dR = 0.0;
@@ -703,8 +768,8 @@ static __device__ void c2_local_search(const C2Env &E, const C2Sm &s, C2Ctl &ctl
       empty_rounds = used ? 0 : empty_rounds + 1;
       if (empty_rounds > VNS_MAX_DRAWS / 64 && threadIdx.x == 0) ctl.err = 3;
       if (ctl.win_found) {
-         if (kind == 1) c2_apply_insert(E, s, ctl, ctl.win_from, ctl.win_to);
-         else c2_apply_exchange(E, s, ctl, ctl.win_from, ctl.win_to);
+         if (kind == 1) c2_apply_insert<G, NR>(E, s, ctl, ctl.win_from, ctl.win_to);
+         else c2_apply_exchange<G, NR>(E, s, ctl, ctl.win_from, ctl.win_to);
       }
       __syncthreads();
       if (threadIdx.x == 0) {
@@ -741,6 +806,7 @@ static __device__ void c2_load(const C2Env &E, const PathDev &P, const C2Sm &s, 
    __syncthreads();
    if ((threadIdx.x >> 5) == 2) c2_pd_scan(E, s, S, threadIdx.x & 31);
    __syncthreads();
+   if (s.tr->nlev > 0) c2_tree_rebuild(*s.tr, E.Dv, E.I.N, s.cinfo, s.lcl, S, 0, S, 0, 0);
 }
 
 // entries beyond a layer's cluster size are never read by anyone and are not written back
@@ -892,6 +958,7 @@ static __device__ void c2_shake(const C2Env &E, const C2Sm &s, C2Ctl &ctl, int k
          if (s.minF[S] != s.minBrev[S] && !ctl.err) ctl.err = 4;
       }
       __syncthreads();
+      if (s.tr->nlev > 0) c2_tree_rebuild(*s.tr, E.Dv, E.I.N, s.cinfo, s.lcl, S, 0, S, 0, 0);
    }
 }
 
@@ -903,8 +970,11 @@ __global__ void __launch_bounds__(C2_THREADS) k_chain2_ls(C2Env E, PathDev P, in
    extern __shared__ __align__(16) unsigned char smem_c[];
    __shared__ C2Ctl ctl;
    __shared__ RngState g;
-   const C2Sm s = c2_carve(smem_c, E.I.C, E.I.mp, E.g_cinfo, E.cinfo_in_smem != 0);
+   __shared__ C2Tree tree;
+   C2Sm s = c2_carve(smem_c, E.I.C, E.I.mp, E.g_cinfo, E.cinfo_in_smem != 0);
+   s.tr = &tree;
    if (threadIdx.x == 0) {
+      c2_tree_init(tree, E);
       g = *rng;
       ctl.st = LsStats{0, 0, 0, 0, 0}; ctl.prof[0] = ctl.prof[1] = ctl.prof[2] = ctl.prof[3] = 0; ctl.ema = 16;
    }
@@ -938,10 +1008,13 @@ static __device__ void c2_vns_body(const C2Env &E, const PathDev &tour, const Vn
    const bool multi = E.grid.bar != nullptr;
    const bool lead = !multi || blockIdx.x == 0;
    double *vbuf_all = reinterpret_cast<double *>(smem_c);       // greedy scratch (start of the run only): overlaps the state
-   const C2Sm s = c2_carve(smem_c, I.C, I.mp, E.g_cinfo, E.cinfo_in_smem != 0);
+   __shared__ C2Tree tree;
+   C2Sm s = c2_carve(smem_c, I.C, I.mp, E.g_cinfo, E.cinfo_in_smem != 0);
+   s.tr = &tree;
    unsigned long long epoch = 0;
    unsigned round_no = 0;
    if (threadIdx.x == 0) {
+      c2_tree_init(tree, E);
       g = *rng; s_stop = 0;
       ctl.st = LsStats{0, 0, 0, 0, 0}; ctl.prof[0] = ctl.prof[1] = ctl.prof[2] = ctl.prof[3] = 0; ctl.err = 0; ctl.bad = 0; ctl.ema = 16;
    }

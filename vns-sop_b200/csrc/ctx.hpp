@@ -85,6 +85,9 @@ struct vnsgpu_ctx {
    void *d_cinfo = nullptr;       // int2 {first sample, size} per cluster
    void *d_c2grid = nullptr;      // grid barrier + control words, slots, RNG jump matrices
    int c2_ncta = 0;
+   int chain_tree = -1;           // vnsgpu_set_chain_tree: -1 from the instance size, 0 off, 1 on
+   int *d_c2tree = nullptr;       // product-tree replicas
+   size_t c2_tree_bytes = 0;
    size_t c2_slots_off = 0, c2_jump_off = 0;
    // the host-buffer evaluation call as a CUDA graph (eval_batch_host)
    bool use_graph = true, hg_seen = false;

@@ -61,6 +61,7 @@ _SIGS = {
     "vnsgpu_set_smem_chain": [vp, C.c_int],
     "vnsgpu_set_chain_form": [vp, C.c_int],
     "vnsgpu_set_chain_blocks": [vp, C.c_int],
+    "vnsgpu_set_chain_tree": [vp, C.c_int],
     "vnsgpu_set_target_reward": [vp, C.c_double],
     "vnsgpu_chain_cycles": [vp, C.POINTER(C.c_int64), C.c_int],
     "vnsgpu_int_path_active": [vp],
@@ -213,6 +214,10 @@ class Engine:
     def set_chain_form(self, form):
         """0: second form (lower bound first, shake in shared memory, integer tables), 1: first form"""
         self._ck(self.lib.vnsgpu_set_chain_form(self.h, int(form)))
+
+    def set_chain_tree(self, mode):
+        """product tree of the second chain form: -1 from the instance size, 0 off, 1 on"""
+        self._ck(self.lib.vnsgpu_set_chain_tree(self.h, int(mode)))
 
     def set_chain_blocks(self, blocks):
         """thread blocks cooperating on one trajectory-exact chain (0: from the instance size)"""
