@@ -259,6 +259,17 @@ vnsgpu_status vnsgpu_gen_proposals(vnsgpu_ctx *ctx, int path, int kind, int64_t 
  * w = bytes per table entry the active evaluation path reads (8 double, 4 exact-int32) */
 vnsgpu_status vnsgpu_cand_bytes(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *cands, int64_t *bytes);
 
+/* ---- measurement support (bench.py; SURVEY.md 8d: "report achieved / peak for whichever level holds the working set") ---
+ * Streaming-read bandwidth of the whole device with the data resident in L1 (each thread block re-reads its own 64 KB),
+ * in L2 (all blocks re-read one 32 MB buffer) and in HBM (4 GiB read once): gbs[0..2] in GB/s, best of 5. */
+vnsgpu_status vnsgpu_measure_read_peaks(vnsgpu_ctx *ctx, double *gbs);
+/* Device time of the phases of vnsgpu_eval_batch_dev / _shard (CUDA events on the launching stream): segment products
+ * (k_seg_offsets + k_seg_build), endpoint vectors (k_vec_uw + k_vec_pairs), counting sort, evaluation kernel. */
+enum { VNSGPU_PHASE_SEG = 0, VNSGPU_PHASE_VEC = 1, VNSGPU_PHASE_SORT = 2, VNSGPU_PHASE_EVAL = 3, VNSGPU_PHASES = 4 };
+vnsgpu_status vnsgpu_set_phase_timing(vnsgpu_ctx *ctx, int enable);
+/* ms[VNSGPU_PHASES], count[VNSGPU_PHASES]: totals since the last call; synchronise the stream first */
+vnsgpu_status vnsgpu_phase_times(vnsgpu_ctx *ctx, double *ms, int64_t *count);
+
 /* ---- neighbourhood drivers (a15, a16) ---------------------------------------------------------- */
 void vnsgpu_rng_seed(vnsgpu_rng *rng, uint32_t seed); /* srand(seed) */
 int32_t vnsgpu_rng_next(vnsgpu_rng *rng);             /* rand() */

@@ -147,6 +147,75 @@ def test_20k_instance_properties():
         e.close()
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("place,blocks", [(0, 1), (1, 5), (3, 3)])
+def test_synthetic_local_search_placements(synth, place, blocks, monkeypatch):
+    """The second chain form with its F / B rows in per-block global memory (what instances beyond shared memory use)
+    and in shared memory, on 1, 3 and 5 cooperating thread blocks, product tree on: same states as the oracle."""
+    from oracle import binding as ob
+    from vns_sop_b200 import engine
+    e, o, pb, (vns, T) = synth
+    monkeypatch.setenv("VNSGPU_CHAIN_PLACE", str(place))
+    e.set_chain_blocks(blocks)
+    try:
+        pg, po = e.path(vns, T), o.path(vns, T)
+        pg.fitDOPtoBudget()
+        po.fit()
+        rg, ro = engine.seeded_rng(5), ob.new_rng(5)
+        for k in (1, 2):
+            pg.shake(k, rg)
+            po.shake(k, ro)
+            st = pg._ls(k, 6000, rg, None, 1)
+            po.local_search(k, 6000, ro)
+            assert st.proposals == 6000
+            assert (pg.vns == po.vns).all() and pg.getNumTargets() == po.T
+            assert pg.getPathLength() == po.length() and pg.getReward() == po.reward()
+        assert engine.rng_next(rg) == ob.rng_next(ro)
+    finally:
+        e.set_chain_blocks(0)
+
+
+@pytest.mark.gpu
+def test_20k_instance_local_search_vs_oracle():
+    """Config 5 (20 000 nodes / 2000 clusters, 3.2 GB table): one insertRandom and one exchangeRandom call of 30 000
+    proposals each on the device (cooperating thread blocks, product tree, rows in global memory) against the C port on
+    the same state: same VNS vector, targets, length, reward and RNG position; and 4000 candidates of that state
+    against the port's tryTo*."""
+    import time
+    from oracle import binding as ob
+    from vns_sop_b200 import engine, instances as ins, synthetic as sy
+    sf = sy.generate()
+    pb = ins.build_problem(sf)
+    e = engine.Engine(0).load_problem(pb)
+    try:
+        o = ob.Oracle(pb)
+        vns, T = sy.centroid_tour_state(pb)
+        pg, po = e.path(vns, T), o.path(vns, T)
+        assert pg.getPathLength() == po.length()
+        rs = np.random.RandomState(9)
+        cands = random_candidates(rs, vns, T, 4000)
+        ln, lb, fl, first = pg.eval_batch(pg.make_cands(cands))
+        oln, olb = po.eval_batch(cands)
+        assert (ln == oln).all() and (lb == olb).all()
+        rg, ro = engine.seeded_rng(3), ob.new_rng(3)
+        for k in (1, 2):
+            e.sync()
+            t0 = time.perf_counter()
+            st = pg._ls(k, 30000, rg, None, 1)
+            tg = time.perf_counter() - t0
+            t0 = time.perf_counter()
+            po.local_search(k, 30000, ro)
+            tc = time.perf_counter() - t0
+            print("20k-node local search kind %d: 30000 proposals, %d accepts, %d rounds: GPU %.3f s, C port (1 core) %.3f s"
+                  % (k, st.accepts, st.rounds, tg, tc))
+            assert st.proposals == 30000
+            assert (pg.vns == po.vns).all() and pg.getNumTargets() == po.T
+            assert pg.getPathLength() == po.length() and pg.getReward() == po.reward()
+        assert engine.rng_next(rg) == ob.rng_next(ro)
+    finally:
+        e.close()
+
+
 def test_dop_generator_is_deterministic():
     from vns_sop_b200 import synthetic as sy
     a, b = sy.generate_dop(120, 8), sy.generate_dop(120, 8)

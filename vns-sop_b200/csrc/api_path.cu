@@ -207,6 +207,7 @@ static vnsgpu_status prepare_seg(vnsgpu_ctx *ctx, int path, cudaStream_t st)
    const InstDev &I = ctx->I;
    const int R = I.rows + 3;
    if (!ctx->d_segmeta) CK(cudaMalloc(&ctx->d_segmeta, sizeof(int) * 6 * R));
+   PhaseTimer pt(ctx, VNSGPU_PHASE_SEG, st);
    k_seg_offsets<<<1, 256, sizeof(int) * 2 * R, st>>>(I, ctx->paths[path].d, ctx->d_segmeta);
    LAUNCHED(ctx);
    const int nst = I.mp <= 22 ? 16 : 8;                      // ring depth: <= 32 KB of staged table blocks
@@ -252,6 +253,7 @@ static vnsgpu_status prepare_eval(vnsgpu_ctx *ctx, int path, int mode, cudaStrea
    const int gxu = (I.C + wpc - 1) / wpc, gxp = (Smax + 1 + wpc - 1) / wpc;
    const int gyu = std::min(Smax, std::max(16, (8 * ctx->num_sms + gxu - 1) / gxu));
    const int gyp = std::min(Smax, std::max(16, (8 * ctx->num_sms + gxp - 1) / gxp));
+   PhaseTimer pt(ctx, VNSGPU_PHASE_VEC, st);
    if (u16) k_vec_uw<unsigned short><<<dim3(gxu, gyu), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D16, ctx->d_segmeta, ctx->d_vec, ctx->d_veclb, LS);
    else k_vec_uw<int><<<dim3(gxu, gyu), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta, ctx->d_vec, ctx->d_veclb, LS);
    LAUNCHED(ctx);
@@ -296,6 +298,7 @@ static vnsgpu_status launch_eval(vnsgpu_ctx *ctx, int path, int64_t n, int64_t i
             ctx->perm_cap = (size_t)(perm_off + n);
          }
          unsigned *hist = ctx->d_hist + (size_t)slot * 2 * nb, *cursor = hist + nb, *perm = ctx->d_perm + perm_off;
+         PhaseTimer pt(ctx, VNSGPU_PHASE_SORT, st);
          const int sgrid = (int)std::min<int64_t>((n + 2047) / 2048, (int64_t)ctx->num_sms * 8);
          CK(cudaMemsetAsync(hist, 0, sizeof(unsigned) * nb, st));
          // endpoint vectors on a table beyond the caches: order the block candidates by product row (vec_sort_key)
@@ -308,6 +311,7 @@ static vnsgpu_status launch_eval(vnsgpu_ctx *ctx, int path, int64_t n, int64_t i
          LAUNCHED(ctx);
          d_perm = perm;
       }
+      PhaseTimer pt(ctx, VNSGPU_PHASE_EVAL, st);
       // T is only known on the device; size the layer map for its bound (a tour visits every cluster at most once)
       const size_t smem = eval_smem_bytes(std::min(I.rows, I.C), I.C);
       const int G = ctx->group_lanes, NR = (I.mp + G - 1) / G <= 1 ? 1 : ((I.mp + G - 1) / G <= 2 ? 2 : 4);

@@ -42,21 +42,20 @@ static void build_jump(int ncta, std::vector<unsigned> &out)
    }
 }
 
-bool c2_fits(const vnsgpu_ctx *ctx, size_t *smem, int *cinfo_in_smem)
+// placement: bit 0 = cluster table in shared memory, bit 1 = F / Brev rows in shared memory (else per-block global slices)
+bool c2_fits(const vnsgpu_ctx *ctx, size_t *smem, int *place)
 {
    if (!ctx->use_chain2 || !vnsgpu_int_path_active(ctx) || ctx->I.mp > 32 || !group_kernel_ok(ctx)) return false;
    // static shared memory of the kernels (control block, slot, RNG, the few words of search.cuh's helpers) + margin
    const size_t fixed = sizeof(C2Ctl) + sizeof(C2Slot) + sizeof(RngState) + sizeof(C2Tree) + 2048;
-   size_t b = c2_smem_bytes(ctx->I.C, ctx->I.mp, true);
-   *cinfo_in_smem = 1;
-   if (b + fixed > (size_t)ctx->max_smem) {
-      b = c2_smem_bytes(ctx->I.C, ctx->I.mp, false);
-      *cinfo_in_smem = 0;
+   const size_t greedy = sizeof(double) * 2 * ctx->I.mp * VNS_CHAIN_WARPS;   // the greedy start of vns_run borrows the buffer
+   const int forced = getenv("VNSGPU_CHAIN_PLACE") ? atoi(getenv("VNSGPU_CHAIN_PLACE")) : -1;   // tests: force a placement
+   for (int pl = 3; pl >= 0; --pl) {
+      if (forced >= 0 && pl != (forced & 3)) continue;
+      const size_t b = std::max(c2_smem_bytes(ctx->I.C, ctx->I.mp, (pl & 1) != 0, (pl & 2) != 0), greedy);
+      if (b + fixed <= (size_t)ctx->max_smem) { *smem = b; *place = pl; return true; }
    }
-   // the greedy start of vns_run borrows 2 * mp * warps doubles of the same buffer
-   b = std::max(b, sizeof(double) * 2 * ctx->I.mp * VNS_CHAIN_WARPS);
-   *smem = b;
-   return b + fixed <= (size_t)ctx->max_smem;
+   return false;
 }
 
 // blocks that cooperate on one chain: 1 up to ~256 clusters (with the product tree a round's evaluation is a few
@@ -77,8 +76,9 @@ static bool c2_tree_wanted(const vnsgpu_ctx *ctx)
    return ctx->I.C >= 96;
 }
 
-static vnsgpu_status c2_prepare(vnsgpu_ctx *ctx, int ncta, C2Env *E, int cinfo_in_smem, int nblocks)
+static vnsgpu_status c2_prepare(vnsgpu_ctx *ctx, int ncta, C2Env *E, int place, int nblocks)
 {
+   const int cinfo_in_smem = place & 1;
    const InstDev &I = ctx->I;
    if (!ctx->d_dmin32) {
       CK(cudaMalloc(&ctx->d_dmin32, sizeof(int) * (size_t)I.C * I.C));
@@ -117,6 +117,18 @@ static vnsgpu_status c2_prepare(vnsgpu_ctx *ctx, int ncta, C2Env *E, int cinfo_i
          ctx->c2_tree_bytes = need;
       }
       E->tree_base = ctx->d_c2tree; E->tree_stride = stride;
+   }
+   E->rows_base = nullptr; E->rows_stride = 0;
+   if (!(place & 2)) {
+      const long long stride = ((long long)c2_rows_ints(I.C, I.mp) + 63) & ~63ll;
+      const size_t need = sizeof(int) * (size_t)stride * (size_t)nblocks;
+      if (need > ctx->c2_rows_bytes) {
+         if (ctx->d_c2rows) { CK(cudaStreamSynchronize(ctx->stream)); CK(cudaFree(ctx->d_c2rows)); }
+         ctx->d_c2rows = nullptr; ctx->c2_rows_bytes = 0;
+         CK(cudaMalloc(&ctx->d_c2rows, need));
+         ctx->c2_rows_bytes = need;
+      }
+      E->rows_base = ctx->d_c2rows; E->rows_stride = stride;
    }
    E->grid = C2Grid{nullptr, nullptr, nullptr, nullptr, 1};
    if (ncta > 1) {
@@ -161,11 +173,11 @@ template <typename K> static vnsgpu_status c2_launch(vnsgpu_ctx *ctx, K kernel, 
    default: return c2_launch(ctx, KERNEL<32, 1>, nblocks_, coop_, smem, args);                          \
    }
 
-vnsgpu_status c2_launch_ls(vnsgpu_ctx *ctx, int path, int kind, int num_changes, double budget, int skip, size_t smem, int cinfo_in_smem)
+vnsgpu_status c2_launch_ls(vnsgpu_ctx *ctx, int path, int kind, int num_changes, double budget, int skip, size_t smem, int place)
 {
    const int ncta = c2_blocks(ctx);
    C2Env E;
-   vnsgpu_status s = c2_prepare(ctx, ncta, &E, cinfo_in_smem, ncta);
+   vnsgpu_status s = c2_prepare(ctx, ncta, &E, place, ncta);
    if (s) return s;
    PathDev P = ctx->paths[path].d;
    RngState *rng = ctx->d_rng;
@@ -176,11 +188,11 @@ vnsgpu_status c2_launch_ls(vnsgpu_ctx *ctx, int path, int kind, int num_changes,
 }
 
 vnsgpu_status c2_launch_vns(vnsgpu_ctx *ctx, int path, const VnsParamsDev &prm_, double *d_ir, double *d_il, double *d_it, size_t smem,
-                            int cinfo_in_smem)
+                            int place)
 {
    const int ncta = c2_blocks(ctx);
    C2Env E;
-   vnsgpu_status s = c2_prepare(ctx, ncta, &E, cinfo_in_smem, ncta);
+   vnsgpu_status s = c2_prepare(ctx, ncta, &E, place, ncta);
    if (s) return s;
    PathDev P = ctx->paths[path].d;
    VnsParamsDev prm = prm_;
@@ -191,10 +203,10 @@ vnsgpu_status c2_launch_vns(vnsgpu_ctx *ctx, int path, const VnsParamsDev &prm_,
    C2_DISPATCH(k_chain2_vns_run, ncta, ncta > 1)
 }
 
-vnsgpu_status c2_launch_multi(vnsgpu_ctx *ctx, int nruns, void *d_slots_, const VnsParamsDev &prm_, size_t smem, int cinfo_in_smem)
+vnsgpu_status c2_launch_multi(vnsgpu_ctx *ctx, int nruns, void *d_slots_, const VnsParamsDev &prm_, size_t smem, int place)
 {
    C2Env E;
-   vnsgpu_status s = c2_prepare(ctx, 1, &E, cinfo_in_smem, nruns);
+   vnsgpu_status s = c2_prepare(ctx, 1, &E, place, nruns);
    if (s) return s;
    C2RunSlot *d_slots = (C2RunSlot *)d_slots_;
    VnsParamsDev prm = prm_;

@@ -76,31 +76,37 @@ struct C2Sm {
    const C2Tree *tr;         // product tree of this block (chain2_tree.cuh); nlev = 0: none
 };
 
-// ints: F, Brev R x mpp each (mpp = max(mp, 2): the shake's scratch of 2R ints lives in Brev, which is rebuilt after every
-// shake); minF, minBrev, pd R each; lcl, vns 2R each (the shakes insert a range before erasing one, vns_sop_solver.cpp:958-990)
-__host__ __device__ inline size_t c2_state_ints(int C, int mp)
+// F, Brev: R x mpp ints each (mpp = max(mp, 2): the shake's scratch of 2R ints lives in Brev, which is rebuilt after every
+// shake) - in shared memory when they fit, else in this block's slice of a global buffer (L1 / L2 resident).  Always in
+// shared memory: minF, minBrev, pd R ints each; lcl, vns 2R each (the shakes insert a range before erasing one,
+// vns_sop_solver.cpp:958-990).
+__host__ __device__ inline size_t c2_rows_ints(int C, int mp)
 {
    const size_t R = C + 3, mpp = mp < 2 ? 2 : mp;
-   return 2 * R * mpp + 7 * R;
+   return 2 * R * mpp;
 }
-__host__ __device__ inline size_t c2_smem_bytes(int C, int mp, bool cinfo_in_smem)
+__host__ __device__ inline size_t c2_smem_bytes(int C, int mp, bool cinfo_in_smem, bool rows_in_smem)
 {
-   return ((sizeof(int) * c2_state_ints(C, mp) + 15) & ~(size_t)15) + (cinfo_in_smem ? sizeof(int2) * (size_t)C : 0) + 16;
+   const size_t R = C + 3;
+   return ((sizeof(int) * ((rows_in_smem ? c2_rows_ints(C, mp) : 0) + 7 * R) + 15) & ~(size_t)15) + (cinfo_in_smem ? sizeof(int2) * (size_t)C : 0) + 16;
 }
 
-static __device__ __forceinline__ C2Sm c2_carve(unsigned char *base, int C, int mp, const int2 *g_cinfo, bool cinfo_in_smem)
+// rows: this block's F / Brev in global memory, or null (shared)
+static __device__ __forceinline__ C2Sm c2_carve(unsigned char *base, int C, int mp, const int2 *g_cinfo, bool cinfo_in_smem, int *rows)
 {
    const size_t R = C + 3, mpp = mp < 2 ? 2 : mp;
    C2Sm s;
-   s.F = reinterpret_cast<int *>(base);
+   int *small = reinterpret_cast<int *>(base);
+   if (rows) s.F = rows;
+   else { s.F = small; small += 2 * R * mpp; }
    s.Brev = s.F + R * mpp;
-   s.minF = s.Brev + R * mpp;
+   s.minF = small;
    s.minBrev = s.minF + R;
    s.pd = s.minBrev + R;
    s.lcl = s.pd + R;
    s.vns = s.lcl + 2 * R;
    s.seg = s.Brev;        // 2R ints of shake scratch
-   size_t o = (sizeof(int) * c2_state_ints(C, mp) + 15) & ~(size_t)15;
+   size_t o = (sizeof(int) * ((rows ? 0 : 2 * R * mpp) + 7 * R) + 15) & ~(size_t)15;
    s.cinfo_sm = cinfo_in_smem ? reinterpret_cast<int2 *>(base + o) : nullptr;
    s.cinfo = cinfo_in_smem ? s.cinfo_sm : g_cinfo;
    s.tr = nullptr;
@@ -116,7 +122,14 @@ struct C2Env {             // per-launch constants
    int cinfo_in_smem;
    int *tree_base;         // product-tree replicas, one per thread block (null: no tree)
    long long tree_stride;  // ints per replica
+   int *rows_base;         // F / Brev replicas, one per thread block (null: they live in shared memory)
+   long long rows_stride;
 };
+
+static __device__ __forceinline__ C2Sm c2_carve_env(unsigned char *base, const C2Env &E)
+{
+   return c2_carve(base, E.I.C, E.I.mp, E.g_cinfo, E.cinfo_in_smem != 0, E.rows_base ? E.rows_base + (long long)blockIdx.x * E.rows_stride : nullptr);
+}
 
 // the block's tree descriptor (thread 0 of every kernel fills it before the first barrier)
 static __device__ __forceinline__ void c2_tree_init(C2Tree &tr, const C2Env &E)
@@ -283,67 +296,76 @@ static __device__ void c2_pd_scan(const C2Env &E, const C2Sm &s, int S, int lane
    __syncwarp();
 }
 
-// F / B rows through the product tree: every layer of [lf, S] (forward, from row lf - 1) and of [lb, 0] (backward, from
-// row lb + 1) is an independent chain of at most 2 log2(T) nodes, one sub-warp group each; warps 0 .. W/2-1 take the
-// forward layers, the others the backward ones (the last warp first rebuilds the prefix sums of the cluster-pair minima)
+// F / B rows through the product tree, ONE tree step per layer.  Forward: F[l] = F[l - 2^z] (x) node(z, .), z = ctz(l) -
+// the row it starts from is either below lf (still valid) or has a larger ctz, so the layers are processed in phases
+// z = nlev .. 0, all layers of a phase in parallel (one sub-warp group each).  Backward: B[l] = node(z, l >> z) (x)
+// B[l + 2^z] in the same phases, except for the at most nlev + 1 layers whose aligned node would overhang the goal
+// (l + 2^z > S: the boundaries p_0 = 0 < p_1 < .. of the binary expansion of S); those are a sequential chain
+// B[p_i] = node (x) B[p_{i+1}] done first.  Work: S tree steps instead of S x 2 log2(S); depth nlev + 1 barriers.
+// Warps 0 .. W/2-1 take the forward layers, the others the backward ones (the last warp first rebuilds the prefix sums
+// of the cluster-pair minima).
+template <int G, int NR, bool TR>
+static __device__ __forceinline__ void c2_row_step(const C2Env &E, const C2Sm &s, int S, bool on, int l, int z, int gl)
+{
+   // forward (TR = false): row l from row l - 2^z;  backward (TR = true): row l from row l + 2^z
+   constexpr unsigned FULL = 0xffffffffu;
+   const int mp = E.I.mp;
+   const int src = TR ? l + (1 << z) : l - (1 << z), nd = (TR ? l : src) >> z;
+   int v[NR], mo = 0;
+   const int m0 = on ? s.cinfo[s.lcl[src]].y : 0;
+   const int *row = TR ? s.Brev + (S - src) * mp : s.F + src * mp;
+#pragma unroll
+   for (int r = 0; r < NR; ++r) v[r] = gl + r * G < m0 ? row[gl + r * G] : C2_INF;
+   c2_chain<G, NR, TR>(on ? 1 : 0, gl, [&](int) { return c2_tree_mat(*s.tr, E.Dv, E.I.N, s.cinfo, s.lcl, z, nd); }, v, mo);
+   int mn = C2_INF;
+   int *out = TR ? s.Brev + (S - l) * mp : s.F + l * mp;
+#pragma unroll
+   for (int r = 0; r < NR; ++r) {
+      const int j = gl + r * G;
+      if (on && j < mo) { out[j] = v[r]; mn = min(mn, v[r]); }
+   }
+#pragma unroll
+   for (int sft = G / 2; sft > 0; sft >>= 1) mn = min(mn, __shfl_xor_sync(FULL, mn, sft, G));
+   if (on && gl == 0) { if (TR) s.minBrev[S - l] = mn; else s.minF[l] = mn; }
+}
+
 template <int G, int NR>
 static __device__ void c2_rows_by_tree(const C2Env &E, const C2Sm &s, int S, int lf, int lb)
 {
    constexpr int NG = 32 / G, HW = C2_WARPS / 2;
-   constexpr unsigned FULL = 0xffffffffu;
    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, gl = lane % G, gq = lane / G;
-   const int mp = E.I.mp, nlev = s.tr->nlev;
-   if (warp < HW) {
-      const int nF = S - lf + 1;
-      const int m0 = s.cinfo[s.lcl[lf - 1]].y;
-      for (int base = warp * NG; base < nF; base += HW * NG) {
-         const int q = base + gq, l = lf + q;
-         int lv, nd;
-         const int K = q < nF ? c2_decomp(nlev, lf - 1, l, -1, &lv, &nd) : 0;
-         int v[NR], mo = 0;
-#pragma unroll
-         for (int r = 0; r < NR; ++r) v[r] = gl + r * G < m0 ? s.F[(lf - 1) * mp + gl + r * G] : C2_INF;
-         c2_chain<G, NR, false>(K, gl, [&](int k) {
-            int l2 = 0, n2 = 0;
-            c2_decomp(nlev, lf - 1, l, k - 1, &l2, &n2);
-            return c2_tree_mat(*s.tr, E.Dv, E.I.N, s.cinfo, s.lcl, l2, n2);
-         }, v, mo);
-         int mn = C2_INF;
-#pragma unroll
-         for (int r = 0; r < NR; ++r) {
-            const int j = gl + r * G;
-            if (K && j < mo) { s.F[l * mp + j] = v[r]; mn = min(mn, v[r]); }
-         }
-#pragma unroll
-         for (int sft = G / 2; sft > 0; sft >>= 1) mn = min(mn, __shfl_xor_sync(FULL, mn, sft, G));
-         if (K && gl == 0) s.minF[l] = mn;
+   const int nlev = s.tr->nlev;
+   if (warp == C2_WARPS - 1) c2_pd_scan(E, s, S, lane);
+   if (warp == HW) {
+      // overhanging layers p_i <= lb, nearest to the goal first: p_i = S with its lowest i set bits cleared
+      int hi = S;                                   // p_{i+1}
+      while (hi > 0) {
+         const int z = __ffs(hi) - 1, p = hi - (1 << z);
+         if (p <= lb) { c2_row_step<G, NR, true>(E, s, S, gq == 0, p, z, gl); __syncwarp(); }
+         hi = p;
       }
-   } else {
-      if (warp == C2_WARPS - 1) c2_pd_scan(E, s, S, lane);
-      const int nB = lb + 1;
-      const int m0 = s.cinfo[s.lcl[lb + 1]].y;
-      for (int base = (warp - HW) * NG; base < nB; base += (C2_WARPS - HW) * NG) {
-         const int q = base + gq, l = lb - q;
-         int lv, nd;
-         const int K = q < nB ? c2_decomp(nlev, l, lb + 1, -1, &lv, &nd) : 0;
-         int v[NR], mo = 0;
-#pragma unroll
-         for (int r = 0; r < NR; ++r) v[r] = gl + r * G < m0 ? s.Brev[(S - (lb + 1)) * mp + gl + r * G] : C2_INF;
-         c2_chain<G, NR, true>(K, gl, [&](int k) {          // nodes from the right: B[l] = M_1 (x) (M_2 (x) ... (M_K (x) B[lb+1]))
-            int l2 = 0, n2 = 0;
-            c2_decomp(nlev, l, lb + 1, K - k, &l2, &n2);
-            return c2_tree_mat(*s.tr, E.Dv, E.I.N, s.cinfo, s.lcl, l2, n2);
-         }, v, mo);
-         int mn = C2_INF;
-#pragma unroll
-         for (int r = 0; r < NR; ++r) {
-            const int j = gl + r * G;
-            if (K && j < mo) { s.Brev[(S - l) * mp + j] = v[r]; mn = min(mn, v[r]); }
+   }
+   __syncthreads();
+   for (int z = nlev; z >= 0; --z) {
+      // layers of this phase: odd multiples of 2^z
+      if (warp < HW) {
+         int q0 = (lf + (1 << z) - 1) >> z;        // first multiple of 2^z >= lf
+         q0 |= 1;
+         const int cnt = (q0 << z) <= S ? (((S >> z) - q0) >> 1) + 1 : 0;
+         for (int base = warp * NG; base < cnt; base += HW * NG) {
+            const int t = base + gq;
+            c2_row_step<G, NR, false>(E, s, S, t < cnt, (q0 + 2 * t) << z, z, gl);
          }
-#pragma unroll
-         for (int sft = G / 2; sft > 0; sft >>= 1) mn = min(mn, __shfl_xor_sync(FULL, mn, sft, G));
-         if (K && gl == 0) s.minBrev[S - l] = mn;
+      } else {
+         // l = q 2^z, q odd, l <= lb, l + 2^z <= S
+         const int qmax = min(lb >> z, (S >> z) - 1);
+         const int cnt = qmax >= 1 ? ((qmax - 1) >> 1) + 1 : 0;
+         for (int base = (warp - HW) * NG; base < cnt; base += (C2_WARPS - HW) * NG) {
+            const int t = base + gq;
+            c2_row_step<G, NR, true>(E, s, S, t < cnt, (1 + 2 * t) << z, z, gl);
+         }
       }
+      __syncthreads();
    }
 }
 
@@ -971,7 +993,7 @@ __global__ void __launch_bounds__(C2_THREADS) k_chain2_ls(C2Env E, PathDev P, in
    __shared__ C2Ctl ctl;
    __shared__ RngState g;
    __shared__ C2Tree tree;
-   C2Sm s = c2_carve(smem_c, E.I.C, E.I.mp, E.g_cinfo, E.cinfo_in_smem != 0);
+   C2Sm s = c2_carve_env(smem_c, E);
    s.tr = &tree;
    if (threadIdx.x == 0) {
       c2_tree_init(tree, E);
@@ -1009,7 +1031,7 @@ static __device__ void c2_vns_body(const C2Env &E, const PathDev &tour, const Vn
    const bool lead = !multi || blockIdx.x == 0;
    double *vbuf_all = reinterpret_cast<double *>(smem_c);       // greedy scratch (start of the run only): overlaps the state
    __shared__ C2Tree tree;
-   C2Sm s = c2_carve(smem_c, I.C, I.mp, E.g_cinfo, E.cinfo_in_smem != 0);
+   C2Sm s = c2_carve_env(smem_c, E);
    s.tr = &tree;
    unsigned long long epoch = 0;
    unsigned round_no = 0;

@@ -2,12 +2,12 @@
 #pragma once
 #include "ctx.hpp"
 
-bool c2_fits(const vnsgpu_ctx *ctx, size_t *smem, int *cinfo_in_smem);
+bool c2_fits(const vnsgpu_ctx *ctx, size_t *smem, int *place);
 int c2_blocks(const vnsgpu_ctx *ctx);
-vnsgpu_status c2_launch_ls(vnsgpu_ctx *ctx, int path, int kind, int num_changes, double budget, int skip, size_t smem, int cinfo_in_smem);
+vnsgpu_status c2_launch_ls(vnsgpu_ctx *ctx, int path, int kind, int num_changes, double budget, int skip, size_t smem, int place);
 vnsgpu_status c2_launch_vns(vnsgpu_ctx *ctx, int path, const VnsParamsDev &prm, double *d_ir, double *d_il, double *d_it, size_t smem,
-                            int cinfo_in_smem);
-vnsgpu_status c2_launch_multi(vnsgpu_ctx *ctx, int nruns, void *d_slots, const VnsParamsDev &prm, size_t smem, int cinfo_in_smem);
+                            int place);
+vnsgpu_status c2_launch_multi(vnsgpu_ctx *ctx, int nruns, void *d_slots, const VnsParamsDev &prm, size_t smem, int place);
 size_t c2_run_slot_bytes();
 void c2_run_slot_fill(void *slot, const PathDev &tour, const RngState &rng);
 const VnsResultDev &c2_run_slot_result(const void *slot);

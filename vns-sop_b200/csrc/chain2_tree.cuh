@@ -79,22 +79,27 @@ static __device__ void c2_tree_rebuild(const C2Tree &tr, const int *Dv, int N, c
       if (hi1 <= lo1) { a0 = 0; a1 = -1; }
       if (hi2 <= lo2) { b0 = 0; b1 = -1; }
       if (a1 >= a0 && b1 >= b0 && b0 <= a1 + 1 && a0 <= b1 + 1) { a0 = min(a0, b0); a1 = max(a1, b1); b0 = 0; b1 = -1; }
-      const int na = max(a1 - a0 + 1, 0), nb = max(b1 - b0 + 1, 0);
-      for (int q = warp; q < na + nb; q += nw) {
+      const int na = max(a1 - a0 + 1, 0), nb = max(b1 - b0 + 1, 0), ncount = na + nb;
+      // wpn warps share a node (its elements are dealt out to them) when the level has fewer nodes than warps
+      const int wpn = ncount > 0 ? max(1, nw / ncount) : 1, slots = nw / wpn;
+      for (int q = warp / wpn; q < ncount; q += slots) {
+         if (warp >= slots * wpn) break;
          const int k = q < na ? a0 + q : b0 + (q - na);
          const C2Mat L = c2_tree_mat(tr, Dv, N, cinfo, lcl, l - 1, 2 * k), R = c2_tree_mat(tr, Dv, N, cinfo, lcl, l - 1, 2 * k + 1);
          int *out = tr.nodes + (size_t)(tr.lvl_off[l] + k) * tr.pitch;
          const int ma = L.ma, mk = L.mb, mb = R.mb;
-         for (int e = lane; e < ma * mb; e += 32) {
+         for (int e = (warp % wpn) * 32 + lane; e < ma * mb; e += wpn * 32) {
             const int i = e / mb, j = e - i * mb;
             const int *lp = L.p + i * mk, *rp = R.p + j;
             int a = VNS_INT_INF, b = VNS_INT_INF;
             int t = 0;
-            for (; t + 1 < mk; t += 2) {
-               a = __viaddmin_s32(lp[t], rp[t * mb], a);
-               b = __viaddmin_s32(lp[t + 1], rp[(t + 1) * mb], b);
+            for (; t + 3 < mk; t += 4) {
+               const int l0 = lp[t], l1 = lp[t + 1], l2 = lp[t + 2], l3 = lp[t + 3];
+               const int r0 = rp[t * mb], r1 = rp[(t + 1) * mb], r2 = rp[(t + 2) * mb], r3 = rp[(t + 3) * mb];
+               a = __viaddmin_s32(l0, r0, a); b = __viaddmin_s32(l1, r1, b);
+               a = __viaddmin_s32(l2, r2, a); b = __viaddmin_s32(l3, r3, b);
             }
-            if (t < mk) a = __viaddmin_s32(lp[t], rp[t * mb], a);
+            for (; t < mk; ++t) a = __viaddmin_s32(lp[t], rp[t * mb], a);
             out[e] = min(a, b);
          }
       }

@@ -35,6 +35,11 @@ struct HostGraphKey {
    int skip, packed, mode, sort, use_int, G;
 };
 
+struct PhaseEvent {
+   int phase;
+   cudaEvent_t e0, e1;
+};
+
 struct vnsgpu_ctx {
    int device = 0;
    cudaStream_t own = nullptr, stream = nullptr;
@@ -85,9 +90,13 @@ struct vnsgpu_ctx {
    void *d_cinfo = nullptr;       // int2 {first sample, size} per cluster
    void *d_c2grid = nullptr;      // grid barrier + control words, slots, RNG jump matrices
    int c2_ncta = 0;
+   bool phase_timing = false;     // vnsgpu_set_phase_timing: CUDA events around the phases of the batched evaluation call
+   std::vector<PhaseEvent> phase_events;
    int chain_tree = -1;           // vnsgpu_set_chain_tree: -1 from the instance size, 0 off, 1 on
    int *d_c2tree = nullptr;       // product-tree replicas
    size_t c2_tree_bytes = 0;
+   int *d_c2rows = nullptr;       // F / Brev replicas of instances beyond shared memory
+   size_t c2_rows_bytes = 0;
    size_t c2_slots_off = 0, c2_jump_off = 0;
    // the host-buffer evaluation call as a CUDA graph (eval_batch_host)
    bool use_graph = true, hg_seen = false;
@@ -179,3 +188,24 @@ static inline vnsgpu_status check_path_err(vnsgpu_ctx *ctx, int path)
 
 static inline size_t chain_smem(const vnsgpu_ctx *ctx) { return sizeof(double) * 2 * ctx->I.mp * VNS_CHAIN_WARPS; }
 
+
+// phase timing (measure.cu): PhaseTimer t(ctx, phase, stream) records an event pair around the launches in its scope
+struct PhaseTimer {
+   vnsgpu_ctx *ctx;
+   cudaStream_t st;
+   PhaseEvent pe;
+   bool on;
+   PhaseTimer(vnsgpu_ctx *c, int phase, cudaStream_t s) : ctx(c), st(s), on(c->phase_timing)
+   {
+      if (!on) return;
+      pe.phase = phase;
+      if (cudaEventCreate(&pe.e0) != cudaSuccess || cudaEventCreate(&pe.e1) != cudaSuccess) { on = false; cudaGetLastError(); return; }
+      cudaEventRecord(pe.e0, st);
+   }
+   ~PhaseTimer()
+   {
+      if (!on) return;
+      cudaEventRecord(pe.e1, st);
+      ctx->phase_events.push_back(pe);
+   }
+};

@@ -62,6 +62,9 @@ _SIGS = {
     "vnsgpu_set_chain_form": [vp, C.c_int],
     "vnsgpu_set_chain_blocks": [vp, C.c_int],
     "vnsgpu_set_chain_tree": [vp, C.c_int],
+    "vnsgpu_measure_read_peaks": [vp, dp],
+    "vnsgpu_set_phase_timing": [vp, C.c_int],
+    "vnsgpu_phase_times": [vp, dp, C.POINTER(C.c_int64)],
     "vnsgpu_set_target_reward": [vp, C.c_double],
     "vnsgpu_chain_cycles": [vp, C.POINTER(C.c_int64), C.c_int],
     "vnsgpu_int_path_active": [vp],
@@ -214,6 +217,21 @@ class Engine:
     def set_chain_form(self, form):
         """0: second form (lower bound first, shake in shared memory, integer tables), 1: first form"""
         self._ck(self.lib.vnsgpu_set_chain_form(self.h, int(form)))
+
+    def measure_read_peaks(self):
+        """{'l1': GB/s, 'l2': GB/s, 'hbm': GB/s}: streaming-read bandwidth with the data resident at that level"""
+        g = (C.c_double * 3)()
+        self._ck(self.lib.vnsgpu_measure_read_peaks(self.h, g))
+        return {"l1": g[0], "l2": g[1], "hbm": g[2]}
+
+    def set_phase_timing(self, enable):
+        self._ck(self.lib.vnsgpu_set_phase_timing(self.h, int(enable)))
+
+    def phase_times(self):
+        """{phase: (ms, count)} of the batched evaluation call since the last query"""
+        ms, cnt = (C.c_double * 4)(), (C.c_int64 * 4)()
+        self._ck(self.lib.vnsgpu_phase_times(self.h, ms, cnt))
+        return {k: (ms[i], cnt[i]) for i, k in enumerate(("seg", "vec", "sort", "eval"))}
 
     def set_chain_tree(self, mode):
         """product tree of the second chain form: -1 from the instance size, 0 off, 1 on"""
