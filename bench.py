@@ -79,6 +79,9 @@ def parse_args():
     ap.add_argument("--no-solve-cpu", action="store_true", help="time-to-reward: skip the reference binary runs (long on vm1084)")
     ap.add_argument("--sweep", action="store_true", help="candidate-batch sweep 2^10 .. --batch (x4 steps), device-resident (BASELINE config 5)")
     ap.add_argument("--multi-start", type=int, default=148, help="seeds of the multi-start leg (0 = skip)")
+    ap.add_argument("--also", default="vm1084,synth20k", help="further workloads measured (device-resident leg only) into the same JSON "
+                                                               "line under `workloads` (BASELINE configs 4 and 5); '' = none")
+    ap.add_argument("--min-timed-s", type=float, default=0.5, help="a timed step repeats the call until K steps take at least this long")
     return ap.parse_args()
 
 
@@ -377,6 +380,36 @@ def measured_hbm_peak():
         return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
 
 
+def vec_form_bytes(rows, T, layer_m, cluster_m):
+    """Bytes k_eval_vec has to move for ITS algorithm, per batch: for every candidate the two endpoint vectors
+    (4 B per sample) and - MOVE / EXCHANGE with a non-empty untouched run - ONE block (a table block or a segment product,
+    4 B per entry); the descriptor in and the results out are counted by the caller.  rows: (n, 3) int32 [op, a, b];
+    layer_m[l] = samples of layer l (0 .. T+1); cluster_m[c] = samples of cluster c.  Mirrors decode_cand_vec (vec.cuh)."""
+    op, a, b = rows[:, 0].astype(np.int64), rows[:, 1].astype(np.int64), rows[:, 2].astype(np.int64)
+    lm = np.asarray(layer_m, np.int64)
+    vec = np.zeros(len(rows), np.int64)
+    blk = np.zeros(len(rows), np.int64)
+    addrep = (op == 0) | (op == 1)
+    vec[addrep] = 2 * np.asarray(cluster_m, np.int64)[a[addrep]]
+    mv = op == 3
+    up = mv & (b > a)
+    dn = mv & (b < a)
+    ex = op == 4
+    la = np.zeros(len(rows), np.int64)
+    lb = np.zeros(len(rows), np.int64)
+    i, j = np.minimum(a, b) + 1, np.maximum(a, b) + 1
+    la[up], lb[up] = i[up] + 1, j[up] - 1
+    la[dn], lb[dn] = i[dn], j[dn] - 1
+    pq = np.minimum(a, b) + 1, np.maximum(a, b) + 1
+    la[ex], lb[ex] = pq[0][ex] + 1, pq[1][ex] - 1
+    chain = mv | ex
+    ok = chain & (la >= 0) & (lb <= T + 1) & (la <= T + 1) & (lb >= 0)
+    vec[ok] = lm[la[ok]] + lm[lb[ok]]
+    hasblk = ok & (lb > la)
+    blk[hasblk] = lm[la[hasblk]] * lm[lb[hasblk]]
+    return int(4 * vec.sum()), int(4 * blk.sum()), float(hasblk.mean())
+
+
 def prepare_gpu_state(eng, state=None):
     if state is not None:
         return eng.path(np.ascontiguousarray(state[0], np.int32), int(state[1]))
@@ -422,6 +455,39 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
         return float(t.item())
 
+    env = (rank, world, local, dev, barrier, max_over_ranks, sum_over_ranks)
+    line = bench_workload(args, env)
+    # BASELINE.json asks for configs 4 and 5 at 1/2/4/8 GPUs too: the same device-resident measurement on them, in the
+    # same JSON line (short legs: no host-buffer call, no CPU legs)
+    extras = [w for w in args.also.split(",") if w and w != args.workload]
+    if extras:
+        line["workloads"] = {}
+    for w in extras:
+        sub = argparse.Namespace(**vars(args))
+        sub.workload, sub.no_e2e, sub.no_cpu, sub.no_solve, sub.sweep = w, True, True, True, False
+        sl = bench_workload(sub, env)
+        line["workloads"][w] = {k: sl[k] for k in ("value", "unit", "ms_per_step", "steps", "dtype", "data", "config", "roofline", "gpu_launches", "table_build",
+                                                     "accepted_in_batch", "first_accept") if k in sl}
+    if "workloads" in line and "synth20k" in line["workloads"]:
+        line["roofline_hbm"] = dict(line["workloads"]["synth20k"]["roofline"], workload="synth20k")
+    if rank == 0 and world == 1 and not args.no_solve and args.workload == "krob200" and "vm1084" in extras:
+        line["time_to_reward_vm1084"] = solve_only("vm1084")
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def bench_workload(args, env):
+    """One workload: table build, device-resident throughput (value) with per-phase kernel times, optionally the
+    host-buffer legs (e2e), the CPU baseline and the seeded solves.  Returns the JSON line as a dict."""
+    import ctypes as C
+
+    import torch
+
+    from vns_sop_b200 import engine, sharding
+
+    rank, world, local, dev, barrier, max_over_ranks, sum_over_ranks = env
     sf, pb = load_workload(args.workload)
     if device_only(args.workload):
         args.no_cpu = args.no_solve = True
@@ -500,6 +566,18 @@ def run_b200(args):
     with torch.cuda.stream(stream):
         for _ in range(W):
             step()
+        # a step of 0.3 ms x K = 20 would be a 7 ms timed region: one timed STEP is `inner` back-to-back calls (each a
+        # full pass over the batch), sized from the warm-up so that the K steps take >= --min-timed-s
+        w0, w1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        w0.record(stream)
+        for _ in range(3):
+            step()
+        w1.record(stream)
+        barrier()
+        est_ms = max_over_ranks(w0.elapsed_time(w1)) / 3
+        inner = int(max(1, min(4096, np.ceil(args.min_timed_s * 1e3 / (K * max(est_ms, 1e-3))))))
+        eng.set_phase_timing(True)
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
@@ -508,7 +586,8 @@ def run_b200(args):
         e0.record(stream)
         for a, b in ev:
             a.record(stream)
-            step()
+            for _ in range(inner):
+                step()
             b.record(stream)
         e1.record(stream)
         if sampler:
@@ -518,10 +597,12 @@ def run_b200(args):
         barrier()
         t_host1 = time.perf_counter()
         launches = eng.launches - l0
+        phases = eng.phase_times()
+        eng.set_phase_timing(False)
     total_ms = max_over_ranks(e0.elapsed_time(e1))
-    kern_ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
+    kern_ms = float(np.mean([a.elapsed_time(b) for a, b in ev])) / inner      # one call = one pass over the batch
     clocks = sampler.window(t_host0, t_host1) if sampler else None
-    value = world * n * K / (total_ms * 1e-3)
+    value = world * n * K * inner / (total_ms * 1e-3)
     first_dev = int(d_first.item())
     if first_dev >= 0x7f7f7f7f7f7f7f7f:      # VNSGPU_NO_KEY of the sharded form
         first_dev = -1
@@ -603,15 +684,22 @@ def run_b200(args):
                 sharding.reduce_first_accept(first.value, rank * n, device=dev)
 
         def timed(packed):
+            """K x rep calls (rep sized from the warm-up so that the region takes >= --min-timed-s / 2); returns the time
+            of K calls' worth (= total / rep) so that the formulas below stay per K calls"""
             for _ in range(W):
                 host_step(packed)
             barrier()
+            t0 = time.perf_counter()
+            host_step(packed)
+            barrier()
+            one = max_over_ranks(time.perf_counter() - t0)
+            rep = int(max(1, min(256, np.ceil(0.5 * args.min_timed_s / (K * max(one, 1e-5))))))
             l0 = eng.launches
             t0 = time.perf_counter()
-            for _ in range(K):
+            for _ in range(K * rep):
                 host_step(packed)
             barrier()
-            return max_over_ranks(time.perf_counter() - t0), eng.launches - l0
+            return max_over_ranks(time.perf_counter() - t0) / rep, (eng.launches - l0) // rep
 
         dt16, _ = timed(0)
         dt8, nl8 = timed(1)
@@ -674,17 +762,77 @@ def run_b200(args):
             assert first.value == first_dev, "host and device entry points disagree on the first accepted candidate"
         assert torch.equal(h_len[:4096], d_len[:4096].cpu()), "host and device entry points disagree"
 
-    hbm_regime = eng.table_bytes / 2 > (48 << 20)      # the library's own switch (vec_lat): int32 table beyond 48 MiB
-    vec_mode = bool(int_path and args.vector_cache and pb.m.max() <= 32 and ((16 if pb.m.max() > 16 else 4) * n >= pb.C * pb.C or args.vector_cache == 2))
-    peak, peak_src = measured_hbm_peak()
-    achieved = alg_bytes / (kern_ms * 1e-3) / 1e9
+    mode = eng.eval_mode(n)              # the library's own choice for this batch (form, sort, HBM form)
+    hbm_regime = mode["hbm_form"]
+    vec_mode = mode["form"] == 2
+    G = mode["group_lanes"]
+    NRr = 1 if -(-int(pb.m.max()) // G) <= 1 else (2 if -(-int(pb.m.max()) // G) <= 2 else 4)
+    kernel_name = ("k_eval_vec<%d,%d,%s>" % (G, NRr, "1" if hbm_regime else "0")) if vec_mode else \
+                  ("k_eval_groups<%s,%d,%d,%s>" % ("int" if int_path else "double", G, NRr, "1" if mode["form"] == 1 else "0"))
+    hbm_peak, peak_src = measured_hbm_peak()
+    peaks = eng.measure_read_peaks() if rank == 0 or world == 1 else None
+    if world > 1:
+        t = torch.tensor([peaks["l1"], peaks["l2"], peaks["hbm"]] if peaks else [0.0, 0.0, 0.0], dtype=torch.float64, device=dev)
+        import torch.distributed as dist
+        dist.broadcast(t, 0)
+        peaks = {"l1": float(t[0]), "l2": float(t[1]), "hbm": float(t[2])}
+    eval_ms, eval_cnt = phases["eval"]
+    eval_ms_per_launch = eval_ms / max(eval_cnt, 1)
+    # bytes the dominant kernel has to move for its own algorithm (not the reference chain's)
+    layer_m = pb.m[np.concatenate(([pb.start], np.asarray(vns[:T], np.int64), [pb.goal]))]
+    desc_b, out_b = 16, 17               # device-resident call: vnsgpu_cand in; length + lower bound (f64) + flags out
+    if vec_mode:
+        vb, bb, blk_share = vec_form_bytes(rows, T, layer_m, pb.m)
+        kbytes = n * (desc_b + out_b) + vb + bb
+        breakdown = {"descriptor": desc_b, "results": out_b, "endpoint_vectors": vb / n, "block": bb / n, "candidates_with_a_block": blk_share}
+    else:                                # block by block / segment products: the chain's blocks at the width the kernel reads
+        kbytes = n * (desc_b + out_b) + (alg_bytes - 8 * n)
+        breakdown = {"descriptor": desc_b, "results": out_b, "chain_blocks_and_rows": (alg_bytes - 8 * n) / n}
+    # working set the kernel gathers from: the table copy it reads + segment products + endpoint vectors
+    LS = pb.C + 2
+    ws = int(pb.N) ** 2 * (4 if int_path else 8)
+    if mode["form"] >= 1:
+        ws += 4 * int(layer_m.sum()) ** 2 // 2
+    if vec_mode:
+        ws += 4 * int((2 * LS * pb.C + LS + 4 * (T + 2) * (T + 2)) * pb.m.max())
+    bound = "l1" if ws <= (160 << 10) else ("l2" if ws <= (96 << 20) else "hbm")
+    peak = peaks[bound] if bound != "hbm" else hbm_peak
+    achieved = kbytes / (eval_ms_per_launch * 1e-3) / 1e9 if eval_ms_per_launch > 0 else None
+    roofline = {
+        "kernel": kernel_name, "kernel_ms": eval_ms_per_launch, "launches_timed": int(eval_cnt),
+        "bound": bound, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak if achieved else None,
+        "traffic": ncu_traffic(args.workload, n),
+        "peak_source": ("streaming read with the data resident in %s, measured in this run (vnsgpu_measure_read_peaks)" % bound.upper())
+                       if bound != "hbm" else peak_src,
+        "peaks_measured_gbs": dict(peaks, hbm_copy=hbm_peak),
+        "algorithmic_bytes_per_launch": int(kbytes), "bytes_per_candidate": breakdown,
+        "working_set_bytes": int(ws),
+        "share_of_step": eval_ms / (kern_ms * K * inner) if kern_ms > 0 else None,
+        "phases_ms_per_call": {k: v[0] / (K * inner) for k, v in phases.items()},
+        "cache_level": ncu_cache_level(args.workload, n),
+        "reference_work_rate": {"gbs": alg_bytes_f64 / (kern_ms * 1e-3) / 1e9, "bytes_per_candidate": alg_bytes_f64 / n,
+                                "what": "SURVEY.md 8d's figure: the bytes the REFERENCE's chain would read for these candidates (8 B per entry of "
+                                        "every block + first F row + last B row + result) / the time of one whole call.  The shared segment "
+                                        "products and endpoint vectors let the kernel read far fewer bytes, so this is a work rate, not a "
+                                        "bandwidth, and is not compared with any peak"},
+        "note": "achieved = bytes the dominant kernel must move for its own algorithm (per candidate: descriptor, two endpoint vectors, at most "
+                "one block, results) / its own launch time (CUDA events on the launching stream inside the timed region).  bound = the "
+                "memory level that holds the working set the kernel gathers from; peak = streaming-read bandwidth measured with the data "
+                "resident at that level.  The kernel is a gather of 4-byte entries with one DPX add-min per entry: on cache-resident "
+                "tables it is bound by instruction issue / L1 wavefronts (cache_level, from the committed ncu capture), so frac is low "
+                "by construction there; the HBM-regime block (roofline_hbm, workload synth20k) is the bandwidth claim",
+    }
     line = {
         "metric": "candidate_move_evals_per_sec", "value": value, "unit": "evals/s", "n_gpus": world,
         "steps": K, "warmup": W, "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "i32 (exact on this all-integer table; results bit-identical to the f64 reference)" if int_path else "f64",
-        "data": "synthetic",
+        "data": ("synthetic instance (generated, seeded)" if WORKLOADS[args.workload][1] is None else
+                 "dataset instance shipped with the reference (datasets/, re-encoded under tests/golden/)") +
+                "; candidates drawn with the reference's proposal distribution (seeded)",
+        "ms_per_call": kern_ms,
         "config": {"workload": WORKLOADS[args.workload][0], "clusters": int(pb.C), "samples": int(pb.N),
-                   "candidates_per_step_per_gpu": n, "targets_in_path": int(T),
+                   "candidates_per_step_per_gpu": n * inner, "candidates_per_call_per_gpu": n, "calls_per_step": inner,
+                   "targets_in_path": int(T),
                    "state": state_text(args.workload),
                    "mix": "50% insertRandom proposals (MOVE/ADD), 50% exchangeRandom (EXCHANGE/REPLACE)",
                    "outputs": "length + lower bound + flags per candidate, first accepted index",
@@ -704,21 +852,7 @@ def run_b200(args):
                    "sharding": "candidates split by rank (global batch = n_gpus x per-GPU batch), table and path replicated; "
                                "N > 1 adds one 8-byte all-reduce(MIN) per step for the chosen move"},
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": ncu_traffic(args.workload, n), "cache_level": ncu_cache_level(args.workload, n), "peak_source": peak_src,
-                     "kernel": "k_eval_vec" if vec_mode else "k_eval_groups",
-                     "kernel_ms": kern_ms, "algorithmic_bytes_per_launch": int(alg_bytes),
-                     "algorithmic_bytes_per_candidate": alg_bytes / n,
-                     "algorithmic_bytes_per_candidate_at_8B_per_entry": alg_bytes_f64 / n,
-                     "stream_bytes_per_candidate": 33,
-                     "working_set": ("L1/L2-resident table (%.2f MB): the HBM traffic is the 16 B descriptor + 17 B of "
-                                     "results per candidate, so this fraction is NOT an HBM-bandwidth claim" % (eng.table_bytes / 1e6))
-                                    if not hbm_regime else "HBM-resident table (%.0f MB as doubles): block gathers miss L2" % (eng.table_bytes / 1e6),
-                     "note": "achieved = algorithmic bytes (SURVEY.md 8d: every distance-block entry of the reference's chain "
-                             "once at the width the kernel reads, + first F row + last B row + result) / time of one step "
-                             "(sort + segment products + endpoint vectors + evaluation kernels, CUDA events).  The shared "
-                             "products / vectors make the kernel read FEWER table bytes than this reference-chain figure, so frac can "
-                             "exceed 1: it is a reference-work rate, not a bandwidth; `traffic` is what DRAM really moved.  See DESIGN.md 4-5"},
+        "roofline": roofline,
         "accepted_in_batch": ok_flags, "first_accept": first_dev,
     }
     if table_build:
@@ -729,13 +863,16 @@ def run_b200(args):
         line["cpu_baseline"] = cpu_baseline_leg(args, sf, pb, vns, T, rows, d_len, d_lb, state)
     if rank == 0 and world == 1 and not args.no_solve and state is None:
         line["time_to_reward"] = solve_leg(args, eng, sf, pb)
+    if world > 1 and not args.no_solve and state is None and args.multi_start > 0:
+        # N GPUs: the honest multi-GPU mode of the search on shipped instances is replicas - every rank races
+        # its own 148 seeds to the reference's seed-1 final reward; the job's time to that reward is the fastest rank's
+        line["race_n_gpus"] = race_leg(args, eng, rank, world, max_over_ranks)
     if sampler:
         sampler.stop()
-    if rank == 0:
-        print(json.dumps(line), flush=True)
+    del d_c, d_len, d_lb, d_fl
     eng.close()
-    if world > 1:
-        dist.destroy_process_group()
+    torch.cuda.empty_cache()
+    return line
 
 
 def cpu_baseline_leg(args, sf, pb, vns, T, rows, d_len, d_lb, state=None):
@@ -855,6 +992,51 @@ def solve_leg(args, eng, sf, pb):
             "cpu_first_hit_s": min(t_hit) if t_hit else None,
             "cpu_note": "reference binary, one seed per host core, all started together: the earliest time any run's improvement "
                         "log (results.log SOLUTION_TIME_REWARD_LENGTH_IMPROVEMENTS) shows reward >= target"})
+    return out
+
+
+def race_leg(args, eng, rank, world, max_over_ranks):
+    with open(os.path.join(ROOT, "tests", "golden", "golden.json")) as fh:
+        gold = json.load(fh).get(args.workload, {}).get("solve_seed1")
+    if not gold:
+        return None
+    nruns = args.multi_start
+    p = eng.path()
+    t0 = time.perf_counter()
+    res, win = p.vns_run_batch(list(range(rank * nruns + 1, (rank + 1) * nruns + 1)), target_reward=gold["REWARDS"])
+    wall = time.perf_counter() - t0
+    eng.set_target_reward(0.0)
+    hit = res[win].reward >= gold["REWARDS"]
+    best = -max_over_ranks(-(wall if hit else 1e9))          # min over ranks
+    return {"target_reward": gold["REWARDS"], "seeds_per_gpu": nruns, "n_gpus": world, "seeds": world * nruns,
+            "wall_s_first_gpu_to_target": best, "rank0_wall_s": wall, "rank0_winner_seed": rank * nruns + win + 1,
+            "mode": "replicas: independent seeded chains per GPU, no collective in the search; one all-reduce(MIN) of the wall times"}
+
+
+def solve_only(name, blocks=0):
+    """Seeded (seed 1, stock sop.cfg) device solve of a further instance with its golden record - BASELINE config 4."""
+    from vns_sop_b200 import engine
+    sf, pb = load_workload(name)
+    eng = engine.Engine(0).load_problem(pb)
+    p = eng.path()
+    eng.sync()
+    t0 = time.perf_counter()
+    res, impr = p.vns_run(1)
+    wall = time.perf_counter() - t0
+    with open(os.path.join(ROOT, "tests", "golden", "golden.json")) as fh:
+        gold = json.load(fh).get(name, {}).get("solve_seed1")
+    out = {"workload": WORKLOADS[name][0], "seed": 1, "gpu_wall_s": wall, "gpu_device_ms": res.time_ms,
+           "gpu_time_to_final_reward_s": res.time_last_impr_ms / 1e3, "reward": res.reward, "length": res.length, "num_iters": res.num_iters,
+           "proposals": res.proposals, "evals": res.evals, "accepts": res.accepts, "chain_proposals_per_s": res.proposals / wall}
+    if gold:
+        out["golden"] = {"reward": gold["REWARDS"], "length": gold["LENGTH"], "num_iters": gold["NUM_ITERS"],
+                         "reference_wall_s_recorded": gold.get("reference_wall_s"),
+                         "reference_wall_note": "the compiled reference binary, one core, recorded when tests/golden was generated (not re-run "
+                                                "here: it takes ~18 minutes)",
+                         "same_trajectory": bool(gold["REWARDS"] == res.reward and gold["LENGTH"] == res.length and gold["NUM_ITERS"] == res.num_iters
+                                                 and gold["NUM_ITERS_LAST_IMPR"] == res.num_iters_last_impr
+                                                 and [[r, l] for r, l, _ in impr] == gold["IMPROVEMENTS"])}
+    eng.close()
     return out
 
 

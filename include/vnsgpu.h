@@ -129,10 +129,12 @@ vnsgpu_status vnsgpu_set_u16_table(vnsgpu_ctx *ctx, int enable);
 /* vnsgpu_local_search keeps the whole search state in one SM's shared memory when it fits (clusters <=
  * 510, samples per cluster <= 32); enable = 0 forces the global-memory chain (tests run both). */
 vnsgpu_status vnsgpu_set_smem_chain(vnsgpu_ctx *ctx, int enable);
-/* Form of the shared-memory chain on all-integer tables.  0 (default): the second form - the lower bound of every
+/* Form of the shared-memory chain on all-integer tables.  -1 (default): the first form below 96 clusters, the second from
+ * there on.  0: the second form - the lower bound of every
  * proposal first (one thread each, O(1) from prefix sums along the path), only the survivors are evaluated, up to 256
- * draw pairs per thread block and round, shake + fitDOPtoBudget in shared memory as well.  1: the first form (one
- * sub-warp group per proposal, 64 proposals per round).  Same trajectory either way (tests run both). */
+ * draw pairs per thread block and round, shake + fitDOPtoBudget in shared memory as well, product tree, cooperating
+ * thread blocks, instances beyond shared memory.  1: the first form (one sub-warp group per proposal, 64 proposals per
+ * round).  Same trajectory either way (tests run both). */
 vnsgpu_status vnsgpu_set_chain_form(vnsgpu_ctx *ctx, int form);
 /* Thread blocks that cooperate on ONE trajectory-exact chain (second form; cooperative launch).  Every block holds a
  * replica of the search state and evaluates its own slice of 256 draw pairs of the round's window (it reaches its
@@ -255,6 +257,10 @@ vnsgpu_status vnsgpu_eval_batch_dev_shard(vnsgpu_ctx *ctx, int path, int64_t n, 
  * the path's current state, advancing *rng exactly as the reference's draws would; HOST buffer */
 vnsgpu_status vnsgpu_gen_proposals(vnsgpu_ctx *ctx, int path, int kind, int64_t n, vnsgpu_rng *rng,
                                    vnsgpu_cand *cands);
+/* How vnsgpu_eval_batch_dev would evaluate a batch of n candidates right now: bits 0-1 = form (0 block by block, 1 exact
+ * segment products, 2 endpoint vectors + segment products), bit 4 = the batch is sorted on the device first, bit 5 = the
+ * table is beyond the caches (HBM form of the endpoint-vector kernel), bits 8-15 = lanes per candidate group */
+int vnsgpu_eval_mode(const vnsgpu_ctx *ctx, int64_t n);
 /* algorithmic bytes of a candidate list: w*sum m_src*m_dst + 8*(m_first + m_last) + 8,
  * w = bytes per table entry the active evaluation path reads (8 double, 4 exact-int32) */
 vnsgpu_status vnsgpu_cand_bytes(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *cands, int64_t *bytes);

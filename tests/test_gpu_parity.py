@@ -144,7 +144,7 @@ def _set_chain_mode(e, mode):
 def _reset_chain_mode(e):
     e.set_smem_chain(True)
     e.set_int_path(True)
-    e.set_chain_form(0)
+    e.set_chain_form(-1)
     e.set_chain_blocks(0)
     e.set_chain_tree(-1)
 

@@ -376,6 +376,12 @@ static vnsgpu_status launch_eval(vnsgpu_ctx *ctx, int path, int64_t n, int64_t i
    return VNSGPU_OK;
 }
 
+int vnsgpu_eval_mode(const vnsgpu_ctx *ctx, int64_t n)
+{
+   const int mode = eval_mode(ctx, n);
+   return mode | (eval_sorts(ctx, n, mode) ? 16 : 0) | (vec_lat(ctx) ? 32 : 0) | (ctx->group_lanes << 8);
+}
+
 vnsgpu_status vnsgpu_eval_batch_dev(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *d_cands, double budget, int skip,
                                     double *d_len, double *d_lb, uint8_t *d_flags, long long *d_first_accept, void *stream)
 {

@@ -45,7 +45,11 @@ static void build_jump(int ncta, std::vector<unsigned> &out)
 // placement: bit 0 = cluster table in shared memory, bit 1 = F / Brev rows in shared memory (else per-block global slices)
 bool c2_fits(const vnsgpu_ctx *ctx, size_t *smem, int *place)
 {
-   if (!ctx->use_chain2 || !vnsgpu_int_path_active(ctx) || ctx->I.mp > 32 || !group_kernel_ok(ctx)) return false;
+   // automatic choice: below ~96 clusters a round is a handful of short chains and the first form's leaner round wins
+   // (seeded krob200 solve 4.45 s against 4.89 s); from there on the lower-bound filter, the large window and the product
+   // tree do (vm1084: 458 s -> 35.6 s)
+   const bool want = ctx->chain_form == 0 || (ctx->chain_form < 0 && ctx->I.C >= 96);
+   if (!want || !vnsgpu_int_path_active(ctx) || ctx->I.mp > 32 || !group_kernel_ok(ctx)) return false;
    // static shared memory of the kernels (control block, slot, RNG, the few words of search.cuh's helpers) + margin
    const size_t fixed = sizeof(C2Ctl) + sizeof(C2Slot) + sizeof(RngState) + sizeof(C2Tree) + 2048;
    const size_t greedy = sizeof(double) * 2 * ctx->I.mp * VNS_CHAIN_WARPS;   // the greedy start of vns_run borrows the buffer

@@ -84,7 +84,7 @@ struct vnsgpu_ctx {
    int max_smem = 48 * 1024;      // opt-in shared memory per block
    bool use_smem_chain = true;    // vnsgpu_set_smem_chain
    // second search chain (chain2.cuh): exact-int tables, lower bound first, 1 .. num_sms cooperating thread blocks
-   bool use_chain2 = true;        // vnsgpu_set_chain_form
+   int chain_form = -1;           // vnsgpu_set_chain_form: -1 from the instance size, 0 second form, 1 first form
    int chain_blocks = 0;          // vnsgpu_set_chain_blocks: 0 = from the instance size
    int *d_dmin32 = nullptr;       // cluster-pair minima as int32
    void *d_cinfo = nullptr;       // int2 {first sample, size} per cluster

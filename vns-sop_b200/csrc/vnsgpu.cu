@@ -89,7 +89,7 @@ vnsgpu_status vnsgpu_set_smem_chain(vnsgpu_ctx *ctx, int enable)
 
 vnsgpu_status vnsgpu_set_chain_form(vnsgpu_ctx *ctx, int form)
 {
-   ctx->use_chain2 = form != 1;
+   ctx->chain_form = form < 0 ? -1 : (form != 0);
    return VNSGPU_OK;
 }
 

@@ -100,7 +100,7 @@ _SIGS = {
     "vnsgpu_path_destroy": [vp, C.c_int],
     "vnsgpu_set_vector_cache": [vp, C.c_int],
 }
-EXPORTS = sorted(list(_SIGS) + ["vnsgpu_noalloc_max_cands", "vnsgpu_destroy", "vnsgpu_last_error", "vnsgpu_version", "vnsgpu_launch_count",
+EXPORTS = sorted(list(_SIGS) + ["vnsgpu_noalloc_max_cands", "vnsgpu_eval_mode", "vnsgpu_destroy", "vnsgpu_last_error", "vnsgpu_version", "vnsgpu_launch_count",
                                 "vnsgpu_table_bytes", "vnsgpu_table_kernel_ms", "vnsgpu_rng_seed", "vnsgpu_rng_next"])
 
 
@@ -122,6 +122,7 @@ def load_library(build_if_stale=True):
     lib.vnsgpu_last_error.argtypes, lib.vnsgpu_last_error.restype = [vp], C.c_char_p
     lib.vnsgpu_version.argtypes, lib.vnsgpu_version.restype = [], C.c_char_p
     lib.vnsgpu_launch_count.argtypes, lib.vnsgpu_launch_count.restype = [vp], C.c_int64
+    lib.vnsgpu_eval_mode.argtypes, lib.vnsgpu_eval_mode.restype = [vp, C.c_int64], C.c_int
     lib.vnsgpu_noalloc_max_cands.argtypes, lib.vnsgpu_noalloc_max_cands.restype = [], C.c_int64
     lib.vnsgpu_table_bytes.argtypes, lib.vnsgpu_table_bytes.restype = [vp], C.c_int64
     lib.vnsgpu_table_kernel_ms.argtypes, lib.vnsgpu_table_kernel_ms.restype = [vp], C.c_double
@@ -217,6 +218,11 @@ class Engine:
     def set_chain_form(self, form):
         """0: second form (lower bound first, shake in shared memory, integer tables), 1: first form"""
         self._ck(self.lib.vnsgpu_set_chain_form(self.h, int(form)))
+
+    def eval_mode(self, n):
+        """how a batch of n candidates would be evaluated: {'form': 0|1|2, 'sorted': bool, 'hbm_form': bool, 'group_lanes': G}"""
+        w = self.lib.vnsgpu_eval_mode(self.h, int(n))
+        return {"form": w & 3, "sorted": bool(w & 16), "hbm_form": bool(w & 32), "group_lanes": (w >> 8) & 0xff}
 
     def measure_read_peaks(self):
         """{'l1': GB/s, 'l2': GB/s, 'hbm': GB/s}: streaming-read bandwidth with the data resident at that level"""
