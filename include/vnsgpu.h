@@ -257,6 +257,22 @@ vnsgpu_status vnsgpu_eval_batch_dev_shard(vnsgpu_ctx *ctx, int path, int64_t n, 
  * the path's current state, advancing *rng exactly as the reference's draws would; HOST buffer */
 vnsgpu_status vnsgpu_gen_proposals(vnsgpu_ctx *ctx, int path, int kind, int64_t n, vnsgpu_rng *rng,
                                    vnsgpu_cand *cands);
+/* The same proposals generated ON THE DEVICE, in draw order, into a device buffer: format 0 = vnsgpu_cand[n], 2 =
+ * vnsgpu_pack_cand32 words.  glibc's stream is linear, so every thread block jumps to its own slice of draws (31 x 31
+ * jump matrices) and a scan of the valid-pair counts gives each proposal its index.  d_draws (may be NULL): per proposal
+ * the number of rand() calls consumed up to and including it - vnsgpu_rng_advance(&rng_at_entry, d_draws[k]) is the
+ * generator just after proposal k, what the reference's loop leaves behind when it accepts k.  *rng (host) advances past
+ * proposal n - 1; the call synchronises `stream` (NULL = context stream).  Replaces the draws of insertRandom
+ * (vns_sop_solver.cpp:507-519) and exchangeRandom (:723-730) for a whole window at once. */
+vnsgpu_status vnsgpu_gen_proposals_dev(vnsgpu_ctx *ctx, int path, int kind, int64_t n, vnsgpu_rng *rng, void *d_out, int format,
+                                       uint32_t *d_draws, void *stream);
+/* rand() called ndraws times (jump-ahead: O(log ndraws) 31 x 31 matrix-vector products on the host) */
+void vnsgpu_rng_advance(vnsgpu_rng *rng, uint64_t ndraws);
+/* One round of a host-driven insertRandom / exchangeRandom: n proposals drawn on the device, evaluated, the first accepted
+ * one in draw order returned (*first_accept = its index or -1, *accepted = its descriptor), *rng rewound to just after
+ * its draws (past all n when none is accepted).  132 bytes in, ~30 bytes out, whatever n. */
+vnsgpu_status vnsgpu_propose_eval(vnsgpu_ctx *ctx, int path, int kind, int64_t n, vnsgpu_rng *rng, double budget, int skip,
+                                  int64_t *first_accept, vnsgpu_cand *accepted);
 /* How vnsgpu_eval_batch_dev would evaluate a batch of n candidates right now: bits 0-1 = form (0 block by block, 1 exact
  * segment products, 2 endpoint vectors + segment products), bit 4 = the batch is sorted on the device first, bit 5 = the
  * table is beyond the caches (HBM form of the endpoint-vector kernel), bits 8-15 = lanes per candidate group */
@@ -264,6 +280,27 @@ int vnsgpu_eval_mode(const vnsgpu_ctx *ctx, int64_t n);
 /* algorithmic bytes of a candidate list: w*sum m_src*m_dst + 8*(m_first + m_last) + 8,
  * w = bytes per table entry the active evaluation path reads (8 double, 4 exact-int32) */
 vnsgpu_status vnsgpu_cand_bytes(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *cands, int64_t *bytes);
+
+/* ---- multi-GPU exchange steps: candidates shard over ranks, table and incumbent are replicated; the only
+ *      collectives are the all-reduce(MIN) of the first-accepted key and the broadcast of the incumbent.  One context per
+ *      GPU and rank; the communicator is NCCL's (libnccl.so.2 is bound with dlopen at the first call - VNSGPU_E_NCCL when it
+ *      cannot be loaded or a collective fails).  No reference counterpart: the reference is a single-threaded CPU program. */
+#define VNSGPU_COMM_ID_BYTES 128
+/* rank 0: ncclGetUniqueId; hand the 128 bytes to the other ranks out of band (file, socket, MPI, torch.distributed) */
+vnsgpu_status vnsgpu_comm_unique_id(vnsgpu_ctx *ctx, void *id128);
+/* every rank, collectively: ncclCommInitRank on the context's device */
+vnsgpu_status vnsgpu_comm_init(vnsgpu_ctx *ctx, const void *id128, int rank, int nranks);
+/* use a communicator the caller owns (ncclComm_t as void*); the context never destroys it */
+vnsgpu_status vnsgpu_comm_adopt(vnsgpu_ctx *ctx, void *nccl_comm, int rank, int nranks);
+vnsgpu_status vnsgpu_comm_destroy(vnsgpu_ctx *ctx);
+vnsgpu_status vnsgpu_comm_info(const vnsgpu_ctx *ctx, int *rank, int *nranks);
+/* in place all-reduce(MIN) of the key vnsgpu_eval_batch_dev_shard wrote: the chosen move, identical on every rank and for
+ * any number of ranks; asynchronous on `stream` (NULL = context stream).  Without a communicator (1 GPU): no-op */
+vnsgpu_status vnsgpu_reduce_first_key(vnsgpu_ctx *ctx, long long *d_key, void *stream);
+/* the incumbent: every rank's `path` becomes a copy of root's (targets, VNS vector, shortest / shortest_back rows, minima:
+ * one contiguous device block, one ncclBroadcast) */
+vnsgpu_status vnsgpu_path_broadcast(vnsgpu_ctx *ctx, int path, int root, void *stream);
+vnsgpu_status vnsgpu_bcast_bytes(vnsgpu_ctx *ctx, void *d_buf, int64_t nbytes, int root, void *stream);
 
 /* ---- measurement support (bench.py; SURVEY.md 8d: "report achieved / peak for whichever level holds the working set") ---
  * Streaming-read bandwidth of the whole device with the data resident in L1 (each thread block re-reads its own 64 KB),

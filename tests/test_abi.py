@@ -89,3 +89,15 @@ int main(void) {
         a, b = out[k].split()
         assert int(a) == int(p64[k]) and int(b) == int(p32[k]), (k, out[k], p64[k], p32[k])
     assert out[len(rows)].split() == [str(0x2a37), "3", str(engine.F_BAD), "16"]
+
+
+def test_rng_advance_equals_stepping():
+    """vnsgpu_rng_advance (jump-ahead through powers of the companion matrix of x_i = x_{i-3} + x_{i-31}) against calling
+    rand() that many times; host-only code, no GPU needed."""
+    from vns_sop_b200 import engine
+    for seed, n in ((1, 0), (1, 1), (7, 2), (12345, 31), (3, 512), (99, 100003)):
+        a, b = engine.seeded_rng(seed), engine.seeded_rng(seed)
+        for _ in range(n):
+            engine.rng_next(a)
+        engine.rng_advance(b, n)
+        assert [engine.rng_next(a) for _ in range(40)] == [engine.rng_next(b) for _ in range(40)], (seed, n)

@@ -499,3 +499,59 @@ def test_edge_cases(eng_cache):
     before = engine.rng_next(engine.Rng.from_buffer_copy(rng))
     st = p.exchangeRandom(100, rng)                # T == 0 -> no proposals, RNG untouched
     assert st.proposals == 0 and engine.rng_next(rng) == before
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["krob200", "vm1084"])
+def test_device_side_proposals_equal_the_host_draws(name, eng_cache):
+    """vnsgpu_gen_proposals_dev (every thread block jumps to its slice of the glibc stream) against vnsgpu_gen_proposals
+    (the sequential replay of vns_sop_solver.cpp:507-519, :723-730): same proposals in the same order in both descriptor
+    formats, same generator afterwards, and the per-proposal draw counts rewind to the state the sequential loop has
+    right after that proposal.  vnsgpu_propose_eval = generate + evaluate + first accepted + rewind."""
+    import ctypes as C
+    import torch
+    from vns_sop_b200 import engine
+    e, sf, pb = eng_cache(name)
+    p = e.path()
+    p.greedy_insertion()
+    dev = torch.device("cuda", 0)
+
+    def same_stream(a, b):      # the same generator, whatever the rotation of the 31-word ring
+        a, b = engine.Rng.from_buffer_copy(bytes(a)), engine.Rng.from_buffer_copy(bytes(b))
+        return [engine.rng_next(a) for _ in range(64)] == [engine.rng_next(b) for _ in range(64)]
+
+    for kind in (1, 2):
+        for n in (1000, 300000):
+            r_host, r_dev, r_dev2 = engine.seeded_rng(21 + kind), engine.seeded_rng(21 + kind), engine.seeded_rng(21 + kind)
+            host = p.gen_proposals(kind, n, r_host)
+            d_c = torch.empty(n * 16, dtype=torch.uint8, device=dev)
+            d_dr = torch.empty(n, dtype=torch.int32, device=dev)
+            p.gen_proposals_dev(kind, n, r_dev, d_c.data_ptr(), 0, d_dr.data_ptr())
+            got = d_c.cpu().numpy().view(engine.CAND_DTYPE)
+            for f in ("op", "a", "b", "gain_cluster"):
+                assert (got[f] == host[f]).all(), (kind, n, f)
+            assert same_stream(r_dev, r_host)
+            d_w = torch.empty(n, dtype=torch.int32, device=dev)
+            p.gen_proposals_dev(kind, n, r_dev2, d_w.data_ptr(), 2, None)
+            assert (d_w.cpu().numpy().view(np.uint32) == p.pack_cands32(host)).all()
+            assert same_stream(r_dev2, r_host)
+            draws = d_dr.cpu().numpy().view(np.uint32)
+            assert (np.diff(draws.astype(np.int64)) >= 2).all() and draws[0] >= 2
+            for k in (0, 7, n // 2, n - 1):            # generator right after proposal k
+                a, b = engine.seeded_rng(21 + kind), engine.seeded_rng(21 + kind)
+                p.gen_proposals(kind, k + 1, a)
+                engine.rng_advance(b, int(draws[k]))
+                assert engine.rng_next(a) == engine.rng_next(b) and engine.rng_next(a) == engine.rng_next(b), (kind, n, k)
+        # one round: first accepted proposal of a window + generator rewound to it
+        n = 5000
+        r1, r2 = engine.seeded_rng(77), engine.seeded_rng(77)
+        host = p.gen_proposals(kind, n, engine.seeded_rng(77))
+        _, _, fl, first = p.eval_batch(host)
+        got_first, cand = p.propose_eval(kind, n, r1)
+        assert got_first == first
+        if first >= 0:
+            assert cand == tuple(int(host[f][first]) for f in ("op", "a", "b", "gain_cluster"))
+            p.gen_proposals(kind, first + 1, r2)
+        else:
+            p.gen_proposals(kind, n, r2)
+        assert engine.rng_next(r1) == engine.rng_next(r2)

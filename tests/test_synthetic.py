@@ -72,7 +72,8 @@ def test_synthetic_long_tour_candidates(synth, int_path):
     oln, olb = po.eval_batch(cands)
     e.set_int_path(int_path)
     try:
-        for seg, vec in ((True, True), (True, False), (False, False)):
+        # segment products: 1 = default build, 2 = one-level chains, 3 = two-level (tiles of 32 layers) whatever the size
+        for seg, vec in ((1, True), (3, True), (2, False), (3, False), (1, False), (0, False)):
             e.set_segment_cache(seg)
             e.set_vector_cache(vec)
             ln, lb, fl, first = pg.eval_batch(pg.make_cands(cands))

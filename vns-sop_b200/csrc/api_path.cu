@@ -25,6 +25,7 @@ vnsgpu_status vnsgpu_path_create(vnsgpu_ctx *ctx, int *path)
    size_t total = al16(o_minB + sizeof(double) * rows);
    PathHost ph;
    CK(cudaMalloc(&ph.block, total));
+   ph.bytes = total;
    CK(cudaMemsetAsync(ph.block, 0, total, ctx->stream));
    char *b = (char *)ph.block;
    ph.d.hdr = (int *)(b + o_hdr); ph.d.hd = (double *)(b + o_hd);
@@ -214,12 +215,36 @@ static vnsgpu_status prepare_seg(vnsgpu_ctx *ctx, int path, cudaStream_t st)
    const size_t smem = seg_build_smem(I.rows, I.mp, nst);
    if (smem <= (size_t)ctx->max_smem && I.mp <= 32 && I.N < 65536) {
       const int grid = std::min(I.rows, I.C + 2);
+      // T is only known on the device: the two-level build is chosen from the bound of T (a tour visits every cluster at
+      // most once); on a short tour its extra launches find nothing to do
+      // (below ~256 layers the one-level chains are as fast: vm1084, 219 clusters: 0.12 ms)
+      // and with clusters of ~32 samples both forms are bound by the m^3 add-mins of the products themselves: 64 k-sample DOP
+      // state, T = 600: 0.99 ms one-level, 1.24 ms two-level; 20 k-node state, m = 10, T = 793: 0.78 -> 0.33 ms)
+      const int tile = (ctx->use_seg_tiles && ((I.C + 2 > 8 * SEG_TILE && I.mp <= 16) || ctx->use_seg_tiles_always)) ? SEG_TILE : 0;
       if (nst == 16) {
          if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k_seg_build<16, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-         k_seg_build<16, 4><<<grid, VNS_SEG_THREADS, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta);
+         k_seg_build<16, 4><<<grid, VNS_SEG_THREADS, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta, tile);
       } else {
          if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k_seg_build<8, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-         k_seg_build<8, 1><<<grid, VNS_SEG_THREADS, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta);
+         k_seg_build<8, 1><<<grid, VNS_SEG_THREADS, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta, tile);
+      }
+      LAUNCHED(ctx);
+      if (tile) {
+         const int ntiles = (grid + SEG_TILE - 1) / SEG_TILE + 1;
+         const size_t sm1 = sizeof(int) * (size_t)I.mp * I.mp;
+         k_seg_tiles<<<ntiles, 256, sm1, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta);
+         LAUNCHED(ctx);
+         const unsigned g3 = (unsigned)((grid + 1 + 7) / 8), g4 = (unsigned)(((long long)(grid + 1) * ntiles + 7) / 8);
+#define VNS_SEG_CROSS(GG)                                                                                             \
+   do {                                                                                                               \
+      k_seg_cross<0, GG><<<g3, 256, 0, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta, ntiles);              \
+      LAUNCHED(ctx);                                                                                                  \
+      k_seg_cross<1, GG><<<g4, 256, 0, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta, ntiles);              \
+   } while (0)
+         if (I.mp <= 8) VNS_SEG_CROSS(8);
+         else if (I.mp <= 16) VNS_SEG_CROSS(16);
+         else VNS_SEG_CROSS(32);
+#undef VNS_SEG_CROSS
       }
    } else
       k_seg_build_g<<<I.rows, 128, 0, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta);

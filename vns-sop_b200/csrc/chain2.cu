@@ -6,6 +6,7 @@
 #include "eval.cuh"
 #include "chain2.cuh"
 #include "chain2_host.hpp"
+#include "rngjump.hpp"
 
 static __global__ void __launch_bounds__(256) k_dmin_to_int(int n, const double *__restrict__ dmin, int *__restrict__ out)
 {
@@ -13,33 +14,12 @@ static __global__ void __launch_bounds__(256) k_dmin_to_int(int n, const double 
    if (k < n) out[k] = (int)dmin[k];
 }
 
-// jump[r][j][t]: x_{p + 512 r - 31 + t} = sum_j jump[r][j][t] * x_{p - 31 + j}  (mod 2^32) for the glibc TYPE_3 recurrence
-// x_i = x_{i-31} + x_{i-3}.  Companion matrix M: s'[t] = s[t+1] (t < 30), s'[30] = s[0] + s[28]; jump[r] = M^(512 r).
+// jump[r][j][t]: coefficient of s[j] in state word t after 2 * C2_PAIRS * r draws (rngjump.hpp)
 static void build_jump(int ncta, std::vector<unsigned> &out)
 {
-   typedef std::vector<unsigned> Mat;   // 31 x 31, row-major: out_state[t] = sum_j A[t][j] * s[j]
-   auto mul = [](const Mat &A, const Mat &B) {
-      Mat Cm(31 * 31, 0u);
-      for (int i = 0; i < 31; ++i)
-         for (int k = 0; k < 31; ++k) {
-            const unsigned a = A[i * 31 + k];
-            if (!a) continue;
-            for (int j = 0; j < 31; ++j) Cm[i * 31 + j] += a * B[k * 31 + j];
-         }
-      return Cm;
-   };
-   Mat M(31 * 31, 0u), P(31 * 31, 0u);
-   for (int t = 0; t < 30; ++t) M[t * 31 + t + 1] = 1u;
-   M[30 * 31 + 0] = 1u; M[30 * 31 + 28] = 1u;
-   Mat step = M;                                  // M^(2 * C2_PAIRS) by squaring (2 * C2_PAIRS is a power of two)
-   for (int d = 1; d < 2 * C2_PAIRS; d <<= 1) step = mul(step, step);
-   for (int t = 0; t < 31; ++t) P[t * 31 + t] = 1u;   // identity
-   out.assign((size_t)ncta * 31 * 32, 0u);
-   for (int r = 0; r < ncta; ++r) {
-      for (int t = 0; t < 31; ++t)
-         for (int j = 0; j < 31; ++j) out[((size_t)r * 31 + j) * 32 + t] = P[t * 31 + j];
-      P = mul(step, P);
-   }
+   int lg = 0;
+   while ((1 << lg) < 2 * C2_PAIRS) ++lg;
+   rngjump::powers_for_device(ncta, lg, out);
 }
 
 // placement: bit 0 = cluster table in shared memory, bit 1 = F / Brev rows in shared memory (else per-block global slices)

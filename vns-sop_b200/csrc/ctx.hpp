@@ -20,6 +20,7 @@ static_assert(sizeof(vnsgpu_cand) == 16, "cand layout");
 
 struct PathHost {
    void *block = nullptr;
+   size_t bytes = 0;         // size of the block (one cudaMalloc: header .. minB)
    PathDev d{};
 };
 
@@ -57,6 +58,8 @@ struct vnsgpu_ctx {
    bool use_int = true;      // vnsgpu_set_int_path
    bool sort_batches = true; // evaluate batches in chain-length order (vnsgpu_set_batch_sort)
    bool use_seg = true;      // exact segment products on integer tables (vnsgpu_set_segment_cache)
+   bool use_seg_tiles_always = false;   // enable = 3: the two-level build whatever the size (tests)
+   bool use_seg_tiles = true; // two-level build of the segment products on long tours (enable = 2 of vnsgpu_set_segment_cache: off)
    bool seg_ok = false;      // the int32 buffer has room for them and offsets fit 32 bits
    int *d_segmeta = nullptr;
    int use_vec = 1;          // 0 off, 1 when the batch is large enough, 2 always; endpoint vectors on top of the segment products (vnsgpu_set_vector_cache, vec.cuh)
@@ -90,6 +93,15 @@ struct vnsgpu_ctx {
    void *d_cinfo = nullptr;       // int2 {first sample, size} per cluster
    void *d_c2grid = nullptr;      // grid barrier + control words, slots, RNG jump matrices
    int c2_ncta = 0;
+   // multi-GPU exchange steps (comm.cu): NCCL communicator, created from a unique id or adopted from the caller
+   void *comm = nullptr;
+   bool comm_owned = false;
+   int comm_rank = 0, comm_size = 1;
+   // device-side candidate generation (gen.cu)
+   unsigned *d_genjump = nullptr;
+   size_t genjump_lo_words = 0;
+   void *d_gen = nullptr, *d_gencands = nullptr;
+   size_t gen_bytes = 0, gencands_bytes = 0;
    bool phase_timing = false;     // vnsgpu_set_phase_timing: CUDA events around the phases of the batched evaluation call
    std::vector<PhaseEvent> phase_events;
    int chain_tree = -1;           // vnsgpu_set_chain_tree: -1 from the instance size, 0 off, 1 on

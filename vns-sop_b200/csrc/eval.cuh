@@ -563,13 +563,16 @@ __host__ __device__ inline size_t seg_build_smem(int rows, int mp, int nst)
 
 // U steps per barrier (small clusters: a step is a few hundred cycles of work, the barrier + wait + fetch round costs as
 // much): the U table blocks of a round have landed before its barrier, the rows stay warp-private in between.
+// tile > 0 (two-level build, see k_seg_cross): block a stops at the first layer of the next tile, b <= (a / tile + 1) * tile
 template <int NST, int U>
-__global__ void __launch_bounds__(VNS_SEG_THREADS) k_seg_build(InstDev I, PathDev P, int *Dv, const int *meta)
+__global__ void __launch_bounds__(VNS_SEG_THREADS) k_seg_build(InstDev I, PathDev P, int *Dv, const int *meta, int tile)
 {
    extern __shared__ __align__(16) int smem_i[];
    constexpr int INF = VNS_INT_INF;
-   const int T = P.hdr[HDR_T], S = T + 1, R = I.rows + 3, mp2 = (I.mp * I.mp + 3) & ~3;
+   const int T = P.hdr[HDR_T], Sfull = T + 1, R = I.rows + 3, mp2 = (I.mp * I.mp + 3) & ~3;
    const int a = blockIdx.x;
+   if (a + 2 > Sfull) return;
+   const int S = tile > 0 ? min(Sfull, (a / tile + 1) * tile) : Sfull;     // last layer of this block's chain
    if (a + 2 > S) return;
    unsigned short *l_m = reinterpret_cast<unsigned short *>(smem_i), *l_off = l_m + R;   // per layer l >= a: cluster size, first sample
    int *dblk = smem_i + ((R + 3) & ~3);                      // ring of NST table blocks
@@ -654,4 +657,133 @@ __global__ void __launch_bounds__(VNS_SEG_THREADS) k_seg_build(InstDev I, PathDe
       }
    }
    asm volatile("cp.async.wait_group 0;");
+}
+
+
+// ---- two-level build of the segment products (paths of a hundred layers and more) --------------------------------------
+// k_seg_build's block a runs S - a DEPENDENT products (793 on the 20 k-node state: 722 us for 65 MB, ncu r2i).  With tiles
+// of SEG_TILE layers (s_t = t SEG_TILE) every M(a,b) is at most one product of two products that are themselves wanted:
+//   1. k_seg_build(tile)   M(a,b), b <= s_{t(a)+1}: chains of <= SEG_TILE steps, all a in parallel
+//   2. k_seg_tiles         M(s_t1, s_t2) = M(s_t1, s_{t2-1}) (x) M(s_{t2-1}, s_t2): one chain of <= S / SEG_TILE steps per t1
+//   3. k_seg_cross<0>      M(a, s_t2) = M(a, s_{t(a)+1}) (x) M(s_{t(a)+1}, s_t2), t2 >= t(a) + 2, a not a tile start
+//   4. k_seg_cross<1>      M(a, b)   = M(a, s_{t(b)}) (x) M(s_{t(b)}, b), t(b) > t(a), b not a tile start, b > s_{t(a)+1}
+// Critical path SEG_TILE + S / SEG_TILE + 2 products instead of S; steps 3 and 4 are independent products (one warp per
+// (a, tile), the left operand staged in shared memory).  Exact: integer min-plus products are associative.
+#define SEG_TILE 32
+
+struct SegMeta {
+   const int *cum, *loff;
+   const long long *rowoff;
+   int N;
+   __device__ __forceinline__ int m(int l) const { return __ldg(cum + l + 1) - __ldg(cum + l); }
+   // M(a,b), b > a: the table block when b == a + 1, else the product stored behind the table
+   __device__ __forceinline__ long long off(int a, int b) const
+   {
+      if (b == a + 1) return (long long)__ldg(loff + a) * N + (long long)m(a) * __ldg(loff + b);
+      return __ldg(rowoff + a) + (long long)m(a) * (__ldg(cum + b) - __ldg(cum + a + 2));
+   }
+};
+
+static __device__ __forceinline__ SegMeta seg_meta(const InstDev &I, const int *meta)
+{
+   const int R = I.rows + 3;
+   return SegMeta{meta, meta + 5 * R, reinterpret_cast<const long long *>(meta + 2 * R), I.N};
+}
+
+// One pass of a warp: 32 / G products C_q = A (x) B_q at once (q = lane / G), A (ma x mk) staged in shared memory with a
+// pitch of 32 ints and INF beyond column mk, lane j = lane % G owns column j of B_q in KU registers (one coalesced load per
+// row of B_q) and walks the rows of A with 16-byte broadcast loads: per row KU DPX add-mins and KU / 4 shared loads.
+template <int G, int KU>
+static __device__ __forceinline__ void seg_warp_pass(int *__restrict__ out, const int *__restrict__ As, const int *__restrict__ Bm, bool on,
+                                                     int ma, int mk, int mb, int j)
+{
+   int breg[KU];
+#pragma unroll
+   for (int t = 0; t < KU; ++t) breg[t] = (on && t < mk && j < mb) ? __ldcg(Bm + t * mb + j) : VNS_INT_INF;
+   for (int i = 0; i < ma; ++i) {
+      int x = VNS_INT_INF, y = VNS_INT_INF;
+#pragma unroll
+      for (int t = 0; t < KU; t += 4) {
+         const int4 p = *reinterpret_cast<const int4 *>(As + i * 32 + t);
+         x = __viaddmin_s32(p.x, breg[t], x); y = __viaddmin_s32(p.y, breg[t + 1], y);
+         x = __viaddmin_s32(p.z, breg[t + 2], x); y = __viaddmin_s32(p.w, breg[t + 3], y);
+      }
+      if (on && j < mb) out[i * mb + j] = min(x, y);
+   }
+}
+
+// step 2: block t1 (t1 = 0 .. ntiles - 2): M(s_t1, s_t2) for t2 = t1 + 2 ..  (t2 = t1 + 1 came out of step 1)
+static __global__ void __launch_bounds__(256) k_seg_tiles(InstDev I, PathDev P, int *Dv, const int *meta)
+{
+   extern __shared__ int smem_i[];
+   const int T = P.hdr[HDR_T], S = T + 1;
+   const SegMeta sm = seg_meta(I, meta);
+   const int a = blockIdx.x * SEG_TILE;
+   if (a + 2 * SEG_TILE > S) return;
+   const int ma = sm.m(a);
+   for (int b = a + 2 * SEG_TILE; b <= S; b += SEG_TILE) {
+      const int x = b - SEG_TILE, mk = sm.m(x), mb = sm.m(b);
+      const int *A = Dv + sm.off(a, x), *Bm = Dv + sm.off(x, b);
+      int *out = Dv + sm.off(a, b);
+      for (int e = threadIdx.x; e < ma * mk; e += blockDim.x) smem_i[e] = __ldcg(A + e);     // written by this block one step ago
+      __syncthreads();
+      for (int w = threadIdx.x >> 5; w * 32 < ma * mb; w += blockDim.x >> 5) {
+         const int e = w * 32 + (threadIdx.x & 31);
+         if (e < ma * mb) {
+            const int i = e / mb, j = e - i * mb;
+            int acc = VNS_INT_INF;
+            for (int t = 0; t < mk; ++t) acc = __viaddmin_s32(smem_i[i * mk + t], __ldcg(Bm + t * mb + j), acc);
+            out[e] = acc;
+         }
+      }
+      __threadfence_block();
+      __syncthreads();
+   }
+}
+
+// steps 3 (MODE 0: one warp per a, b over the tile starts beyond the next one) and 4 (MODE 1: one warp per (a, tile tb),
+// b over the tile's layers).  G = lanes per product (>= mp).  Static shared memory: 8 warps x 32 x 32 ints.
+template <int MODE, int G>
+__global__ void __launch_bounds__(256) k_seg_cross(InstDev I, PathDev P, int *Dv, const int *meta, int ntiles_cap)
+{
+   __shared__ __align__(16) int s_A[8][32 * 32];
+   constexpr int NB = 32 / G;
+   const int T = P.hdr[HDR_T], S = T + 1;
+   const SegMeta sm = seg_meta(I, meta);
+   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, q = lane / G, j = lane % G;
+   int *As = s_A[wib];
+   const long long task = (long long)blockIdx.x * (blockDim.x >> 5) + wib;
+   int a, x, b0, b1, bstep;
+   if (MODE == 0) {
+      a = (int)task;
+      if (a > S || a % SEG_TILE == 0) return;                  // tile starts: step 2
+      x = (a / SEG_TILE + 1) * SEG_TILE;
+      b0 = x + SEG_TILE; b1 = S; bstep = SEG_TILE;
+   } else {
+      a = (int)(task / ntiles_cap);
+      const int tb = (int)(task % ntiles_cap);
+      if (a > S || tb <= a / SEG_TILE) return;
+      x = tb * SEG_TILE;
+      b0 = x + 1; b1 = min(S, x + SEG_TILE - 1); bstep = 1;
+   }
+   if (b0 > b1 || x > S || x < a + 1) return;
+   const int ma = sm.m(a), mk = sm.m(x);
+   {
+      const int *A = Dv + sm.off(a, x);
+      for (int e = lane; e < ma * 32; e += 32) {
+         const int i = e >> 5, t = e & 31;
+         As[e] = t < mk ? __ldcg(A + i * mk + t) : VNS_INT_INF;
+      }
+      __syncwarp();
+   }
+   for (int bb = b0; bb <= b1; bb += NB * bstep) {
+      const int b = bb + q * bstep;
+      const bool on = b <= b1;
+      const int mb = on ? sm.m(b) : 0;
+      int *out = Dv + (on ? sm.off(a, b) : 0);
+      const int *Bm = Dv + (on ? sm.off(x, b) : 0);
+      if (mk <= 8) seg_warp_pass<G, 8>(out, As, Bm, on, ma, mk, mb, j);
+      else if (mk <= 16) seg_warp_pass<G, 16>(out, As, Bm, on, ma, mk, mb, j);
+      else seg_warp_pass<G, 32>(out, As, Bm, on, ma, mk, mb, j);
+   }
 }

@@ -52,9 +52,11 @@ void vnsgpu_destroy(vnsgpu_ctx *ctx)
    if (!ctx) return;
    cudaSetDevice(ctx->device);
    cudaStreamSynchronize(ctx->stream);
+   vnsgpu_comm_destroy(ctx);
    free_instance(ctx);
    cudaFree(ctx->d_scratch); cudaFree(ctx->d_rng); cudaFree(ctx->d_stats); cudaFree(ctx->d_first);
    cudaFree(ctx->d_res); cudaFree(ctx->d_info); cudaFree(ctx->d_prof); cudaFree(ctx->d_stop); cudaFree(ctx->d_c2grid); cudaFree(ctx->d_c2tree); cudaFree(ctx->d_c2rows);
+   cudaFree(ctx->d_genjump); cudaFree(ctx->d_gen); cudaFree(ctx->d_gencands);
    if (ctx->s_in) {
       cudaStreamDestroy(ctx->s_in); cudaStreamDestroy(ctx->s_out); cudaEventDestroy(ctx->ev_start); cudaEventDestroy(ctx->ev_out);
       for (int k = 0; k < VNS_PIPE_EVENTS; ++k) { cudaEventDestroy(ctx->ev_in[k]); cudaEventDestroy(ctx->ev_k[k]); }
@@ -108,6 +110,8 @@ vnsgpu_status vnsgpu_set_chain_blocks(vnsgpu_ctx *ctx, int blocks)
 vnsgpu_status vnsgpu_set_segment_cache(vnsgpu_ctx *ctx, int enable)
 {
    ctx->use_seg = enable != 0;
+   ctx->use_seg_tiles = enable != 2;      // 2: products on, but built by the one-level chain kernel (tests compare both)
+   ctx->use_seg_tiles_always = enable == 3;   // 3: two-level build whatever the size
    return VNSGPU_OK;
 }
 

@@ -63,6 +63,16 @@ _SIGS = {
     "vnsgpu_set_chain_blocks": [vp, C.c_int],
     "vnsgpu_set_chain_tree": [vp, C.c_int],
     "vnsgpu_measure_read_peaks": [vp, dp],
+    "vnsgpu_comm_unique_id": [vp, vp],
+    "vnsgpu_comm_init": [vp, vp, C.c_int, C.c_int],
+    "vnsgpu_comm_adopt": [vp, vp, C.c_int, C.c_int],
+    "vnsgpu_comm_destroy": [vp],
+    "vnsgpu_comm_info": [vp, ip, ip],
+    "vnsgpu_reduce_first_key": [vp, vp, vp],
+    "vnsgpu_path_broadcast": [vp, C.c_int, C.c_int, vp],
+    "vnsgpu_bcast_bytes": [vp, vp, C.c_int64, C.c_int, vp],
+    "vnsgpu_gen_proposals_dev": [vp, C.c_int, C.c_int, C.c_int64, C.POINTER(Rng), vp, C.c_int, vp, vp],
+    "vnsgpu_propose_eval": [vp, C.c_int, C.c_int, C.c_int64, C.POINTER(Rng), C.c_double, C.c_int, C.POINTER(C.c_int64), vp],
     "vnsgpu_set_phase_timing": [vp, C.c_int],
     "vnsgpu_phase_times": [vp, dp, C.POINTER(C.c_int64)],
     "vnsgpu_set_target_reward": [vp, C.c_double],
@@ -100,7 +110,7 @@ _SIGS = {
     "vnsgpu_path_destroy": [vp, C.c_int],
     "vnsgpu_set_vector_cache": [vp, C.c_int],
 }
-EXPORTS = sorted(list(_SIGS) + ["vnsgpu_noalloc_max_cands", "vnsgpu_eval_mode", "vnsgpu_destroy", "vnsgpu_last_error", "vnsgpu_version", "vnsgpu_launch_count",
+EXPORTS = sorted(list(_SIGS) + ["vnsgpu_noalloc_max_cands", "vnsgpu_rng_advance", "vnsgpu_eval_mode", "vnsgpu_destroy", "vnsgpu_last_error", "vnsgpu_version", "vnsgpu_launch_count",
                                 "vnsgpu_table_bytes", "vnsgpu_table_kernel_ms", "vnsgpu_rng_seed", "vnsgpu_rng_next"])
 
 
@@ -122,6 +132,7 @@ def load_library(build_if_stale=True):
     lib.vnsgpu_last_error.argtypes, lib.vnsgpu_last_error.restype = [vp], C.c_char_p
     lib.vnsgpu_version.argtypes, lib.vnsgpu_version.restype = [], C.c_char_p
     lib.vnsgpu_launch_count.argtypes, lib.vnsgpu_launch_count.restype = [vp], C.c_int64
+    lib.vnsgpu_rng_advance.argtypes, lib.vnsgpu_rng_advance.restype = [C.POINTER(Rng), C.c_uint64], None
     lib.vnsgpu_eval_mode.argtypes, lib.vnsgpu_eval_mode.restype = [vp, C.c_int64], C.c_int
     lib.vnsgpu_noalloc_max_cands.argtypes, lib.vnsgpu_noalloc_max_cands.restype = [], C.c_int64
     lib.vnsgpu_table_bytes.argtypes, lib.vnsgpu_table_bytes.restype = [vp], C.c_int64
@@ -137,6 +148,11 @@ def seeded_rng(seed):
     g = Rng()
     load_library().vnsgpu_rng_seed(C.byref(g), seed)
     return g
+
+
+def rng_advance(rng, ndraws):
+    """rand() called ndraws times (jump-ahead)"""
+    load_library().vnsgpu_rng_advance(C.byref(rng), int(ndraws))
 
 
 def rng_next(g):
@@ -223,6 +239,21 @@ class Engine:
         """how a batch of n candidates would be evaluated: {'form': 0|1|2, 'sorted': bool, 'hbm_form': bool, 'group_lanes': G}"""
         w = self.lib.vnsgpu_eval_mode(self.h, int(n))
         return {"form": w & 3, "sorted": bool(w & 16), "hbm_form": bool(w & 32), "group_lanes": (w >> 8) & 0xff}
+
+    # ---- multi-GPU exchange steps (NCCL behind the C ABI) -------------------------------------------------------------
+    def comm_unique_id(self):
+        buf = (C.c_char * 128)()
+        self._ck(self.lib.vnsgpu_comm_unique_id(self.h, buf))
+        return bytes(buf)
+
+    def comm_init(self, unique_id, rank, nranks):
+        self._ck(self.lib.vnsgpu_comm_init(self.h, C.c_char_p(unique_id), rank, nranks))
+
+    def comm_destroy(self):
+        self._ck(self.lib.vnsgpu_comm_destroy(self.h))
+
+    def reduce_first_key(self, d_key_ptr, stream=None):
+        self._ck(self.lib.vnsgpu_reduce_first_key(self.h, C.c_void_p(d_key_ptr), C.c_void_p(stream) if stream else None))
 
     def measure_read_peaks(self):
         """{'l1': GB/s, 'l2': GB/s, 'hbm': GB/s}: streaming-read bandwidth with the data resident at that level"""
@@ -508,6 +539,21 @@ class VnsSopPath:
         c = np.zeros(n, CAND_DTYPE)
         self.e._ck(self.lib.vnsgpu_gen_proposals(self.e.h, self.h, kind, n, C.byref(rng), c.ctypes.data))
         return c
+
+    def gen_proposals_dev(self, kind, n, rng, d_out, fmt=0, d_draws=None, stream=None):
+        """n proposals of neighbourhood `kind` generated on the device into d_out (device pointer: vnsgpu_cand[n] for fmt 0,
+        uint32[n] for fmt 2); d_draws: device pointer to uint32[n] or None; rng (host) advances past proposal n - 1"""
+        self.e._ck(self.lib.vnsgpu_gen_proposals_dev(self.e.h, self.h, kind, n, C.byref(rng), C.c_void_p(d_out), fmt,
+                                                     C.c_void_p(d_draws) if d_draws else None, C.c_void_p(stream) if stream else None))
+
+    def propose_eval(self, kind, n, rng, budget=None, skip=1):
+        """one round of a host-driven local search: -> (index of the first accepted proposal or -1, its (op, a, b, gain) or None);
+        rng is left just after the accepted proposal's draws"""
+        first = C.c_int64(-1)
+        c = np.zeros(1, CAND_DTYPE)
+        budget = self.e.pb.budget if budget is None else budget
+        self.e._ck(self.lib.vnsgpu_propose_eval(self.e.h, self.h, kind, n, C.byref(rng), budget, skip, C.byref(first), c.ctypes.data))
+        return first.value, (tuple(int(x) for x in c[0]) if first.value >= 0 else None)
 
     def cand_bytes(self, cands):
         c = self.make_cands(cands)
