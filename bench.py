@@ -549,13 +549,32 @@ def bench_workload(args, env):
     torch.cuda.synchronize()
     sp = C.c_void_p(stream.cuda_stream)
 
+    comm_stream = None
+    if world > 1:
+        # the library's own NCCL communicator (vnsgpu_comm_*): the unique id travels through torch.distributed, the
+        # collectives of the path do not
+        import torch.distributed as dist
+        idt = torch.zeros(128, dtype=torch.uint8, device=dev)
+        if rank == 0:
+            idt.copy_(torch.frombuffer(bytearray(eng.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        eng.comm_init(bytes(idt.cpu().numpy().tobytes()), rank, world)
+        comm_stream = torch.cuda.Stream(device=dev)
+    d_keys = torch.zeros(4, dtype=torch.int64, device=dev)      # ring: the key of step k reduces while step k + 1 evaluates
+    step_no = [0]
+
     def step():
         if world > 1:      # sharded form: the key comes out as a global index, ready for the collective
+            key = d_keys[step_no[0] % 4:]
+            step_no[0] += 1
             st = lib.vnsgpu_eval_batch_dev_shard(eng.h, p.h, n, C.c_void_p(d_c.data_ptr()), pb.budget, 1,
                                                  C.c_void_p(d_len.data_ptr()), C.c_void_p(d_lb.data_ptr()),
-                                                 C.c_void_p(d_fl.data_ptr()), C.c_void_p(d_first.data_ptr()), rank * n, sp)
+                                                 C.c_void_p(d_fl.data_ptr()), C.c_void_p(key.data_ptr()), rank * n, sp)
             eng._ck(st)
-            sharding.reduce_key_(d_first)      # the path's one exchange step: the chosen move (8 bytes, all-reduce MIN)
+            # the path's one exchange step: the chosen move (8 bytes, all-reduce MIN) - on a second stream, so that its
+            # latency (16-28 us, r1y) hides behind the next step's kernels instead of serialising with them
+            comm_stream.wait_stream(stream)
+            eng.reduce_first_key(key.data_ptr(), comm_stream.cuda_stream)
             return
         st = lib.vnsgpu_eval_batch_dev(eng.h, p.h, n, C.c_void_p(d_c.data_ptr()), pb.budget, 1,
                                        C.c_void_p(d_len.data_ptr()), C.c_void_p(d_lb.data_ptr()),
@@ -589,6 +608,8 @@ def bench_workload(args, env):
             for _ in range(inner):
                 step()
             b.record(stream)
+        if comm_stream is not None:
+            stream.wait_stream(comm_stream)      # the last keys' reductions are inside the timed region
         e1.record(stream)
         if sampler:
             sampler.sample_now()          # after the last launch: the device is still working through the queued steps
@@ -603,7 +624,7 @@ def bench_workload(args, env):
     kern_ms = float(np.mean([a.elapsed_time(b) for a, b in ev])) / inner      # one call = one pass over the batch
     clocks = sampler.window(t_host0, t_host1) if sampler else None
     value = world * n * K * inner / (total_ms * 1e-3)
-    first_dev = int(d_first.item())
+    first_dev = int(d_first.item()) if world == 1 else int(d_keys[(step_no[0] - 1) % 4].item())
     if first_dev >= 0x7f7f7f7f7f7f7f7f:      # VNSGPU_NO_KEY of the sharded form
         first_dev = -1
     ok_flags = int(((d_fl & 2) != 0).sum().item())
@@ -625,7 +646,7 @@ def bench_workload(args, env):
                         eng._ck(lib.vnsgpu_eval_batch_dev_shard(eng.h, p.h, b, C.c_void_p(d_c.data_ptr()), pb.budget, 1,
                                                                 C.c_void_p(d_len.data_ptr()), C.c_void_p(d_lb.data_ptr()),
                                                                 C.c_void_p(d_fl.data_ptr()), C.c_void_p(d_first.data_ptr()), rank * b, sp))
-                        sharding.reduce_key_(d_first)
+                        eng.reduce_first_key(d_first.data_ptr(), stream.cuda_stream)
                     else:
                         eng._ck(lib.vnsgpu_eval_batch_dev(eng.h, p.h, b, C.c_void_p(d_c.data_ptr()), pb.budget, 1,
                                                           C.c_void_p(d_len.data_ptr()), C.c_void_p(d_lb.data_ptr()),
@@ -662,6 +683,9 @@ def bench_workload(args, env):
         h_res = torch.empty(n, dtype=torch.int32).pin_memory() if int_path else None
 
         def host_step(packed=1):
+            if packed == 9:
+                propose_step()
+                return
             if packed == 4:     # 4 B descriptors in, only the chosen move (first accepted index) out: what insertRandom /
                                 # exchangeRandom consume (vns_sop_solver.cpp:619-646, :805-832)
                 eng._ck(lib.vnsgpu_eval_batch_packed32(eng.h, p.h, n, C.c_void_p(h_pk32.data_ptr()), pb.budget, 1,
@@ -701,6 +725,22 @@ def bench_workload(args, env):
             barrier()
             return max_over_ranks(time.perf_counter() - t0) / rep, (eng.launches - l0) // rep
 
+        # the call a host-driven search makes per round: proposals drawn ON THE DEVICE from the host's generator state
+        # (vnsgpu_propose_eval: 132 B in), evaluated, first accepted proposal + its descriptor + the rewound generator out
+        rng_p = engine.seeded_rng(4242 + rank)
+        prop_kind = [1]
+
+        def propose_step(_=None):
+            prop_kind[0] = 3 - prop_kind[0]           # alternate insertRandom / exchangeRandom windows (the 50 / 50 mix)
+            f, _c = p.propose_eval(prop_kind[0], n, rng_p)
+            if world > 1:      # the chosen move over all ranks' windows: one 8-byte all-reduce(MIN)
+                d_keys[0] = f + rank * n if f >= 0 else engine.NO_KEY
+                torch.cuda.current_stream().synchronize()
+                eng.reduce_first_key(d_keys.data_ptr(), None)
+                eng.sync()
+                return int(d_keys[0].item())
+            return f
+        host_step_saved = None
         dt16, _ = timed(0)
         dt8, nl8 = timed(1)
         first8 = first.value
@@ -740,6 +780,15 @@ def bench_workload(args, env):
             in_b, out_b = 8, 9
             e2e = dict(sub8, unit="evals/s", with_16B_descriptors=sub16,
                        call="vnsgpu_eval_batch_packed (pinned host buffers: 8 B descriptors in; lengths + flags + first accepted index out)")
+        dtp, nlp = timed(9)
+        e2e["propose_eval"] = {"value": world * n * K / dtp, "unit": "evals/s", "ms_per_step": 1e3 * dtp / K, "call": "vnsgpu_propose_eval",
+                               "h2d_bytes_per_step": world * 132, "d2h_bytes_per_step": world * (8 + 8 + 4 + 16),
+                               "frac_of_value": (world * n * K / dtp) / value,
+                               "what": "per step: n proposals drawn on the device from the host's glibc rand() state (alternating "
+                                       "insertRandom / exchangeRandom windows), evaluated, first accepted index + descriptor + draw "
+                                       "count back; the generator is rewound on the host (vnsgpu_rng_advance).  No candidate or "
+                                       "result arrays cross PCIe"}
+        launches += nlp
         # what the link alone allows: the same buffers copied with nothing else running (explains e2e vs value)
         d_tmp = torch.empty(n * 16, dtype=torch.uint8, device=dev)
         h_tmp = h_c

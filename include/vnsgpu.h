@@ -241,7 +241,10 @@ vnsgpu_status vnsgpu_eval_batch_noalloc(vnsgpu_ctx *ctx, int path, int64_t n, co
                                         int skip, double *len, double *lb, uint8_t *flags, int64_t *first_accept);
 int64_t vnsgpu_noalloc_max_cands(void);
 /* device buffers, asynchronous on `stream` (NULL = context stream); d_first_accept: one int64 that
- * the call resets and fills like first_accept above (-1 = none), or NULL */
+ * the call resets and fills like first_accept above (-1 = none), or NULL.  The segment products, endpoint vectors and
+ * sort scratch a call builds belong to the CONTEXT: at most one evaluation call of a context may be in flight at a time
+ * (a second one on another stream, or one racing vnsgpu_path_copy of the same path, overwrites them) - order such calls
+ * with an event, or use one context per concurrent evaluation. */
 vnsgpu_status vnsgpu_eval_batch_dev(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *d_cands,
                                     double budget, int skip, double *d_len, double *d_lb, uint8_t *d_flags,
                                     long long *d_first_accept, void *stream);

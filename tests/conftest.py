@@ -54,3 +54,19 @@ def random_candidates(rs, vns, T, n):
             if abs(a - b) >= 2:
                 out.append((4, a, b))
     return np.array(out, dtype=np.int32)
+
+
+def real_valued_explicit_krob200():
+    """krob200 as a REAL-VALUED explicit matrix (raw Euclid + seeded U[0,1) noise, asymmetric): the one input on which the
+    floating-point association of the reference's sums can show - the reference parses EXPLICIT
+    weights as doubles (dataset_loader_sop.cpp:254-257), so the same matrix goes through the compiled reference, the C
+    port and the GPU's IEEE double path."""
+    import dataclasses
+    from vns_sop_b200 import instances as ins
+    sf, _ = load_problem("krob200")
+    xy = np.asarray(sf.coords, np.float64)
+    d = np.sqrt(((xy[:, None, :] - xy[None, :, :]) ** 2).sum(-1))
+    W = d + np.random.RandomState(20190147).rand(*d.shape)
+    np.fill_diagonal(W, 0.0)
+    sf2 = dataclasses.replace(sf, coords=None, weights=W, edge_weight_type="EXPLICIT", name="krob200_real")
+    return sf2, ins.build_problem(sf2)

@@ -494,6 +494,20 @@ def test_edge_cases(eng_cache):
         p.addPoint(3, 2)                           # vns_sop_path.cpp:69-72
     with pytest.raises(engine.VnsGpuError):
         p.tryToMove(0, 1)
+    # a descriptor whose gain cluster is out of range is a bad descriptor (it indexes the reward table)
+    q = e.path()
+    q.greedy_insertion()
+    c = q.make_cands(np.array([[0, int(q.vns[-1]), 0]], np.int32))
+    c["gain_cluster"] = pb.C + 5
+    ln, lb, fl, first = q.eval_batch(c)
+    assert fl[0] == engine.F_BAD and np.isnan(ln[0]) and first == -1
+    # tours are capped at one target per cluster (the batched evaluation is sized for that): duplicates are refused
+    # with a status, never a crash
+    r = e.path()
+    with pytest.raises(engine.VnsGpuError) as ei:
+        for k in range(pb.C + 2):
+            r.addPoint(2 + k % 3, 0)
+    assert "E_RANGE" in str(ei.value) and r.getNumTargets() == pb.C
     # local search on states where the reference's guards skip the loop (:498, :711)
     rng = engine.seeded_rng(1)
     before = engine.rng_next(engine.Rng.from_buffer_copy(rng))
@@ -555,3 +569,84 @@ def test_device_side_proposals_equal_the_host_draws(name, eng_cache):
         else:
             p.gen_proposals(kind, n, r2)
         assert engine.rng_next(r1) == engine.rng_next(r2)
+
+
+@pytest.mark.gpu
+def test_real_valued_explicit_matrix_double_path():
+    """The fixture tests/test_oracle_vs_ref.py pins against the compiled reference (real-valued EXPLICIT matrix), on the
+    GPU's IEEE double path: table, bounds, greedy, 20 000 candidates, shake + local search, generator position."""
+    from conftest import real_valued_explicit_krob200
+    from oracle import binding as ob
+    from vns_sop_b200 import engine
+    sf, pb = real_valued_explicit_krob200()
+    e = engine.Engine(0).load_problem(pb)
+    try:
+        assert not e.int_path_active
+        o = ob.Oracle(pb)
+        assert (e.table_dense() == o.dense()).all()
+        lo, hi = e.bounds()
+        olo, ohi = o.bounds()
+        assert (lo == olo).all() and (hi == ohi).all()
+        po, pg = o.path(), e.path()
+        po.greedy()
+        pg.greedy_insertion()
+        assert (pg.vns == po.vns).all() and pg.getPathLength() == po.length()
+        rs = np.random.RandomState(3)
+        cands = random_candidates(rs, po.vns, po.T, 20000)
+        ln, lb, fl, _ = pg.eval_batch(cands)
+        oln, olb = po.eval_batch(cands)
+        assert (ln == oln).all() and (lb == olb).all()
+        go, gg = ob.new_rng(9), engine.seeded_rng(9)
+        for it in range(10):
+            k = 1 + it % 2
+            po.shake(k, go)
+            pg.shake(k, gg)
+            po.local_search(k, 1600, go)
+            pg._ls(k, 1600, gg, None, 1)
+            assert (pg.vns == po.vns).all() and pg.getNumTargets() == po.T
+            assert pg.getPathLength() == po.length() and pg.getReward() == po.reward()
+        assert engine.rng_next(gg) == ob.rng_next(go)
+    finally:
+        e.close()
+
+
+@pytest.mark.gpu
+def test_dop_s16_generated_instance_vs_oracle():
+    """BASELINE config 3: 16 heading samples on the Tsiligirides-2 centres, table from the Dubins kernel; the C port
+    loads that table as the EXPLICIT matrix the reference's DOP files carry.  Greedy, candidates in every evaluation
+    form, a seeded shake + local-search sequence."""
+    import bench
+    from oracle import binding as ob
+    from vns_sop_b200 import engine
+    sf, pb = bench.load_workload("dop_s16")
+    e = engine.Engine(0).load_problem(pb, dubins=(16, sf.dubins_radius, 1))
+    try:
+        bench.fill_dubins_weights(sf, pb, e.table_dense())
+        o = ob.Oracle(pb)
+        assert (e.table_dense() == o.dense()).all() and pb.m.max() == 16
+        po, pg = o.path(), e.path()
+        po.greedy()
+        pg.greedy_insertion()
+        assert (pg.vns == po.vns).all() and pg.getPathLength() == po.length() and pg.getReward() == po.reward()
+        rs = np.random.RandomState(4)
+        cands = random_candidates(rs, po.vns, po.T, 30000)
+        oln, olb = po.eval_batch(cands)
+        for int_path in (True, False):
+            e.set_int_path(int_path)
+            for seg, vec in ((1, 2), (1, 0), (0, 0)):
+                e.set_segment_cache(seg)
+                e.set_vector_cache(vec)
+                ln, lb, fl, _ = pg.eval_batch(cands)
+                assert (ln == oln).all() and (lb == olb).all(), (int_path, seg, vec)
+        e.set_int_path(True); e.set_segment_cache(1); e.set_vector_cache(1)
+        go, gg = ob.new_rng(6), engine.seeded_rng(6)
+        for it in range(6):
+            k = 1 + it % 2
+            po.shake(k, go)
+            pg.shake(k, gg)
+            po.local_search(k, len(po.vns) ** 2, go)
+            pg._ls(k, len(po.vns) ** 2, gg, None, 1)
+            assert (pg.vns == po.vns).all() and pg.getNumTargets() == po.T and pg.getPathLength() == po.length()
+        assert engine.rng_next(gg) == ob.rng_next(go)
+    finally:
+        e.close()

@@ -46,3 +46,35 @@ def test_random_walk_matches_reference(name, tmp_path):
             for x, y in zip(Fo, Fr):
                 assert (x[l, :pb.m[c]] == y[l, :pb.m[c]]).all()
     assert ob.rng_next(g) == r.rand()
+
+
+def test_real_valued_explicit_matrix_matches_reference(tmp_path):
+    """Floating-point association pinned against the REFERENCE, not only against the port: a
+    real-valued EXPLICIT matrix through the compiled reference and through the C port - table, greedy tour, 20 000
+    candidates with their lower bounds, shake + local-search calls, generator position."""
+    from conftest import real_valued_explicit_krob200
+    sf, pb = real_valued_explicit_krob200()
+    f = str(tmp_path / "krob200_real.sop")
+    ins.write_sop(sf, f)
+    r = ob.RefOracle(f)
+    o = ob.Oracle(pb)
+    W = o.dense()
+    assert (W == r.dense()).all() and (W != np.round(W)).any()
+    po, pr = o.path(), r.path()
+    po.greedy()
+    pr.greedy()
+    assert po.T == pr.T and (po.vns == pr.vns).all() and po.length() == pr.length()
+    rs = np.random.RandomState(3)
+    cands = random_candidates(rs, po.vns, po.T, 20000)
+    a, b = po.eval_batch(cands), pr.eval_batch(cands)
+    assert (a[0] == b[0]).all() and (a[1] == b[1]).all()
+    g = ob.new_rng(9)
+    r.seed(9)
+    for it in range(10):
+        k = 1 + it % 2
+        po.shake(k, g)
+        pr.shake(k)
+        po.local_search(k, 1600, g)
+        pr.local_search(k, 1600)
+        assert po.T == pr.T and (po.vns == pr.vns).all() and po.length() == pr.length() and po.reward() == pr.reward()
+    assert ob.rng_next(g) == r.rand()

@@ -14,7 +14,7 @@ NVCC_FLAGS = [
 ]
 # translation units of the library (each compiled on its own core, then linked; no relocatable device code: no kernel
 # calls a device function of another unit)
-UNITS = ["vnsgpu.cu", "api_path.cu", "api_search.cu", "chain2.cu", "comm.cu", "noalloc.cu", "measure.cu", "gen.cu"]
+UNITS = ["vnsgpu.cu", "api_path.cu", "api_search.cu", "chain2.cu", "chain2_k8.cu", "chain2_k16.cu", "comm.cu", "noalloc.cu", "measure.cu", "gen.cu"]
 OBJ = os.path.join(HERE, "build")
 
 
@@ -90,7 +90,7 @@ def build_cli(force=False):
         return CLI
     cxx = os.environ.get("VNSGPU_CXX", "/usr/bin/g++")
     cmd = [cxx, "-O2", "-std=c++17", "-Wall", "-I", os.path.join(HERE, "..", "include"), "-I", HOST,
-           os.path.join(HOST, "sop_vns_b200.cpp"), "-o", CLI, "-L", HERE, "-lvnsgpu", "-Wl,-rpath,$ORIGIN"]
+           os.path.join(HOST, "sop_vns_b200.cpp"), "-o", CLI, "-L", HERE, "-lvnsgpu", "-pthread", "-Wl,-rpath,$ORIGIN"]
     subprocess.check_call(cmd)
     return CLI
 

@@ -94,6 +94,9 @@ vnsgpu_status vnsgpu_path_add_point(vnsgpu_ctx *ctx, int path, int cluster, int 
    const int T = h.hdr[HDR_T];
    if (idx > T || idx < 0) return fail(ctx, VNSGPU_E_RANGE, "addPoint idx exceeds maximum");   // vns_sop_path.cpp:69-72
    if (cluster < 0 || cluster >= ctx->I.C || T + 3 > ctx->I.rows) return fail(ctx, VNSGPU_E_RANGE, "addPoint cluster / capacity");
+   // the batched evaluation (layer maps, endpoint vectors, segment products, search chains) is sized for tours of at most C
+   // targets - what the solver can build (every cluster at most once); the reference's addPoint itself has no such limit
+   if (T + 1 > ctx->I.C) return fail(ctx, VNSGPU_E_RANGE, "addPoint: more targets than clusters");
    k_path_edit<<<1, 256, 0, ctx->stream>>>(ctx->I, ctx->paths[path].d, 0, cluster, idx);
    LAUNCHED(ctx);
    return check_path_err(ctx, path);
@@ -279,7 +282,18 @@ static vnsgpu_status prepare_eval(vnsgpu_ctx *ctx, int path, int mode, cudaStrea
    const int gyu = std::min(Smax, std::max(16, (8 * ctx->num_sms + gxu - 1) / gxu));
    const int gyp = std::min(Smax, std::max(16, (8 * ctx->num_sms + gxp - 1) / gxp));
    PhaseTimer pt(ctx, VNSGPU_PHASE_VEC, st);
-   if (u16) k_vec_uw<unsigned short><<<dim3(gxu, gyu), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D16, ctx->d_segmeta, ctx->d_vec, ctx->d_veclb, LS);
+   // small clusters on a symmetric table: 2 - 4 clusters per warp (k_vec_uw_packed)
+   const int pslot = (I.symmetric && ctx->use_vec_pack) ? (I.mp <= 8 ? 8 : (I.mp <= 10 ? 10 : (I.mp <= 16 ? 16 : 0))) : 0;
+   if (pslot) {
+      const int pk = 32 / pslot, gxk = ((I.C + pk - 1) / pk + wpc - 1) / wpc;
+      const int gyk = std::min(Smax, std::max(16, (8 * ctx->num_sms + gxk - 1) / gxk));
+      const size_t smk = (size_t)pk * slot * wpc;
+#define VNS_VEC_PACKED(TT, SL, TAB)                                                                                   \
+   k_vec_uw_packed<TT, SL><<<dim3(gxk, gyk), thr, smk, st>>>(I, ctx->paths[path].d, TAB, ctx->d_segmeta, ctx->d_vec, ctx->d_veclb, LS)
+      if (u16) { if (pslot == 8) VNS_VEC_PACKED(unsigned short, 8, ctx->d_D16); else if (pslot == 10) VNS_VEC_PACKED(unsigned short, 10, ctx->d_D16); else VNS_VEC_PACKED(unsigned short, 16, ctx->d_D16); }
+      else { if (pslot == 8) VNS_VEC_PACKED(int, 8, ctx->d_D32); else if (pslot == 10) VNS_VEC_PACKED(int, 10, ctx->d_D32); else VNS_VEC_PACKED(int, 16, ctx->d_D32); }
+#undef VNS_VEC_PACKED
+   } else if (u16) k_vec_uw<unsigned short><<<dim3(gxu, gyu), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D16, ctx->d_segmeta, ctx->d_vec, ctx->d_veclb, LS);
    else k_vec_uw<int><<<dim3(gxu, gyu), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta, ctx->d_vec, ctx->d_veclb, LS);
    LAUNCHED(ctx);
    if (u16) k_vec_pairs<unsigned short><<<dim3(gxp, gyp), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D16, ctx->d_segmeta, ctx->d_vec, LS);
@@ -410,6 +424,7 @@ int vnsgpu_eval_mode(const vnsgpu_ctx *ctx, int64_t n)
 vnsgpu_status vnsgpu_eval_batch_dev(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *d_cands, double budget, int skip,
                                     double *d_len, double *d_lb, uint8_t *d_flags, long long *d_first_accept, void *stream)
 {
+   CK(cudaSetDevice(ctx->device));
    if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
    if (n <= 0) return VNSGPU_OK;
    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
@@ -430,6 +445,7 @@ vnsgpu_status vnsgpu_eval_batch_dev_shard(vnsgpu_ctx *ctx, int path, int64_t n, 
                                           double *d_len, double *d_lb, uint8_t *d_flags, long long *d_first_key, int64_t index_base,
                                           void *stream)
 {
+   CK(cudaSetDevice(ctx->device));
    if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
    if (!d_first_key || index_base < 0) return VNSGPU_E_RANGE;
    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;

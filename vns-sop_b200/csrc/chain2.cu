@@ -138,24 +138,15 @@ static int c2_variant(const vnsgpu_ctx *ctx)
    return 5;
 }
 
-template <typename K> static vnsgpu_status c2_launch(vnsgpu_ctx *ctx, K kernel, int nblocks, bool coop, size_t smem, void **args)
-{
-   CK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-   if (coop) CK(cudaLaunchCooperativeKernel((const void *)kernel, dim3(nblocks), dim3(C2_THREADS), args, smem, ctx->stream));
-   else CK(cudaLaunchKernel((const void *)kernel, dim3(nblocks), dim3(C2_THREADS), args, smem, ctx->stream));
-   LAUNCHED(ctx);
-   return VNSGPU_OK;
-}
+// the kernels are instantiated in chain2_k8.cu / chain2_k16.cu (which: 0 k_chain2_ls, 1 k_chain2_vns_run, 2 k_chain2_vns_multi)
+vnsgpu_status c2k_launch_g8(vnsgpu_ctx *ctx, int variant, int which, int nblocks, bool coop, size_t smem, void **args);
+vnsgpu_status c2k_launch_g16(vnsgpu_ctx *ctx, int variant, int which, int nblocks, bool coop, size_t smem, void **args);
 
-#define C2_DISPATCH(KERNEL, nblocks_, coop_)                                                            \
-   switch (c2_variant(ctx)) {                                                                           \
-   case 0: return c2_launch(ctx, KERNEL<8, 1>, nblocks_, coop_, smem, args);                            \
-   case 1: return c2_launch(ctx, KERNEL<8, 2>, nblocks_, coop_, smem, args);                            \
-   case 2: return c2_launch(ctx, KERNEL<8, 4>, nblocks_, coop_, smem, args);                            \
-   case 3: return c2_launch(ctx, KERNEL<16, 1>, nblocks_, coop_, smem, args);                           \
-   case 4: return c2_launch(ctx, KERNEL<16, 2>, nblocks_, coop_, smem, args);                           \
-   default: return c2_launch(ctx, KERNEL<32, 1>, nblocks_, coop_, smem, args);                          \
-   }
+static vnsgpu_status c2_dispatch(vnsgpu_ctx *ctx, int which, int nblocks, bool coop, size_t smem, void **args)
+{
+   const int v = c2_variant(ctx);
+   return v < 3 ? c2k_launch_g8(ctx, v, which, nblocks, coop, smem, args) : c2k_launch_g16(ctx, v, which, nblocks, coop, smem, args);
+}
 
 vnsgpu_status c2_launch_ls(vnsgpu_ctx *ctx, int path, int kind, int num_changes, double budget, int skip, size_t smem, int place)
 {
@@ -168,7 +159,7 @@ vnsgpu_status c2_launch_ls(vnsgpu_ctx *ctx, int path, int kind, int num_changes,
    LsStats *st = ctx->d_stats;
    long long *prof = ctx->d_prof;
    void *args[] = {&E, &P, &kind, &num_changes, &budget, &skip, &rng, &st, &prof};
-   C2_DISPATCH(k_chain2_ls, ncta, ncta > 1)
+   return c2_dispatch(ctx, 0, ncta, ncta > 1, smem, args);
 }
 
 vnsgpu_status c2_launch_vns(vnsgpu_ctx *ctx, int path, const VnsParamsDev &prm_, double *d_ir, double *d_il, double *d_it, size_t smem,
@@ -184,7 +175,7 @@ vnsgpu_status c2_launch_vns(vnsgpu_ctx *ctx, int path, const VnsParamsDev &prm_,
    VnsResultDev *res = ctx->d_res;
    long long *prof = ctx->d_prof;
    void *args[] = {&E, &P, &prm, &rng, &res, &d_ir, &d_il, &d_it, &prof};
-   C2_DISPATCH(k_chain2_vns_run, ncta, ncta > 1)
+   return c2_dispatch(ctx, 1, ncta, ncta > 1, smem, args);
 }
 
 vnsgpu_status c2_launch_multi(vnsgpu_ctx *ctx, int nruns, void *d_slots_, const VnsParamsDev &prm_, size_t smem, int place)
@@ -195,7 +186,7 @@ vnsgpu_status c2_launch_multi(vnsgpu_ctx *ctx, int nruns, void *d_slots_, const 
    C2RunSlot *d_slots = (C2RunSlot *)d_slots_;
    VnsParamsDev prm = prm_;
    void *args[] = {&E, &d_slots, &prm};
-   C2_DISPATCH(k_chain2_vns_multi, nruns, false)
+   return c2_dispatch(ctx, 2, nruns, false, smem, args);
 }
 
 size_t c2_run_slot_bytes() { return sizeof(C2RunSlot); }

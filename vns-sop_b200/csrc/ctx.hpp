@@ -62,6 +62,7 @@ struct vnsgpu_ctx {
    bool use_seg_tiles = true; // two-level build of the segment products on long tours (enable = 2 of vnsgpu_set_segment_cache: off)
    bool seg_ok = false;      // the int32 buffer has room for them and offsets fit 32 bits
    int *d_segmeta = nullptr;
+   bool use_vec_pack = true; // several small clusters per warp in the endpoint-vector build (vnsgpu_set_vector_cache(ctx, 3): off)
    int use_vec = 1;          // 0 off, 1 when the batch is large enough, 2 always; endpoint vectors on top of the segment products (vnsgpu_set_vector_cache, vec.cuh)
    int *d_vec = nullptr, *d_veclb = nullptr;
    int group_lanes = 8;      // lanes per candidate of k_eval_groups, from the mean cluster size

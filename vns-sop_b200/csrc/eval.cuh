@@ -326,6 +326,7 @@ k_eval_groups(InstDev I, const V *__restrict__ Dv, PathDev P, SegCache seg, long
       if (perm && slot < n) kidx = __ldg(perm + slot);
       int4 cd = make_int4(-1, 0, 0, -1);
       if (slot < n) cd = __ldg(reinterpret_cast<const int4 *>(cands) + kidx);
+      if (cd.w >= I.C) cd.x = -1;                 // gain cluster out of range: a bad descriptor like any other bad index
       int K, s0, sK, nolb;                        // K = 0: out of range -> flags BAD
       V fin;
       double between;

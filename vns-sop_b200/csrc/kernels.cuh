@@ -62,7 +62,8 @@ static __global__ void __launch_bounds__(VNS_EVAL_THREADS) k_eval_batch(InstDev 
    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
    unsigned long long best = ULLONG_MAX;   // d_first is preset to all-ones (= -1 as int64: none)
    for (long long k = (((long long)blockIdx.x * blockDim.x) >> 5) + warp; k < n; k += nwarps) {
-      const int4 cd = __ldg(reinterpret_cast<const int4 *>(cands) + k);   // op, a, b, gain_cluster
+      int4 cd = __ldg(reinterpret_cast<const int4 *>(cands) + k);   // op, a, b, gain_cluster
+      if (cd.w >= I.C) cd.x = -1;                 // gain cluster out of range: a bad descriptor like any other bad index
       const CandPlan pl = make_plan(T, cd.x, cd.y, cd.z, I.C);
       double l, bound;
       unsigned f = 0;

@@ -166,6 +166,66 @@ __global__ void __launch_bounds__(256) k_vec_uw(InstDev I, PathDev P, const TT *
    }
 }
 
+// Small clusters on a symmetric table: PK = 32 / SLOT clusters per warp (SLOT = 8, 10 or 16 lanes each, >= mp).  The blocks
+// D(cl, c0 .. c0 + PK - 1) of consecutive clusters are ONE contiguous run of the block-major row band, staged with a single
+// warp_stage; group g = lane / SLOT works on cluster c0 + g, lane j = lane % SLOT on its sample j.  With clusters of 10
+// samples the one-cluster-per-warp form has a third of its lanes busy (20 k-node instance: 0.66 ms for 0.5 GB).
+template <typename TT, int SLOT>
+__global__ void __launch_bounds__(256) k_vec_uw_packed(InstDev I, PathDev P, const TT *__restrict__ Dv, const int *__restrict__ meta,
+                                                       int *__restrict__ vec, int *__restrict__ lbs, int LS)
+{
+   extern __shared__ int smem_i[];
+   constexpr int PK = 32 / SLOT;
+   const int T = P.hdr[HDR_T], S = T + 1, C = I.C, mp = I.mp;
+   const int lane = threadIdx.x & 31, g = lane / SLOT, j = lane - g * SLOT;
+   const int c0 = (int)(((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * PK);
+   if (c0 >= C) return;
+   const LayerMeta lm = layer_meta(I, meta);
+   VecCache vc{vec, lbs, LS};
+   const size_t slot = PK * vec_slot_bytes(mp, sizeof(TT));
+   char *sU = reinterpret_cast<char *>(smem_i) + (threadIdx.x >> 5) * slot;
+   const int c = c0 + g;
+   const bool cok = g < PK && c < C;
+   const int mc = cok ? __ldg(I.m + c) : 0, oc = cok ? __ldg(I.off + c) : 0;
+   const int oc0 = __ldg(I.off + c0), oend = __ldg(I.off + min(c0 + PK, C));       // samples of the warp's clusters: [oc0, oend)
+   for (int l = blockIdx.y; l <= S; l += gridDim.y) {
+      const int cl = lm.cl(l), ml = lm.m(l), ol = lm.off(l);
+      const bool doU = l <= S - 1, doW = l >= 1;
+      const TT *run = warp_stage(sU, Dv + ((long long)ol * I.N + (long long)ml * oc0), ml * (oend - oc0), lane);   // D(cl, c0 ..)
+      const int f = (doU && lane < ml) ? (int)P.F[(size_t)l * mp + lane] : VNS_INT_INF;
+      const int bv = (doW && lane < ml) ? (int)P.B[(size_t)l * mp + lane] : VNS_INT_INF;
+      int lb_ins = 0, lb_rep = 0, lb_rem = 0;
+      if (doW && cok && j == 0) {   // lower-bound sums (integers: order-free)
+         const int a = lm.cl(l - 1), nx = l <= S - 1 ? lm.cl(l + 1) : cl;
+         const int din = (int)I.dmin[(size_t)a * C + c];
+         lb_ins = din + (int)I.dmin[(size_t)c * C + cl];
+         lb_rep = din + (int)I.dmin[(size_t)c * C + nx];
+         lb_rem = (int)I.dmin[(size_t)a * C + nx];
+      }
+      warp_stage_wait();
+      const TT *blk = run + ml * (oc - oc0) + min(j, max(mc, 1) - 1);      // this group's block, this lane's column
+      int u = VNS_INT_INF, wv = VNS_INT_INF;
+      for (int s_ = 0; s_ < ml; ++s_) {           // both products walk the same staged entry (symmetric table)
+         const int d = cok ? (int)blk[s_ * mc] : 0;
+         u = __viaddmin_s32(__shfl_sync(0xffffffffu, f, s_), d, u);
+         wv = __viaddmin_s32(__shfl_sync(0xffffffffu, bv, s_), d, wv);
+      }
+      if (cok && j < mp) {
+         if (doU) {
+            vec[vec_uw(vc, C, mp, 0, c, l) + j] = j < mc ? u : VNS_INT_INF;
+            if (c == 0) vec[vec_fi(vc, C, mp, l) + j] = f;      // c == 0 is group 0: lane == j holds F[l][j]
+         }
+         if (doW) vec[vec_uw(vc, C, mp, 1, c, l) + j] = j < mc ? wv : VNS_INT_INF;
+      }
+      if (doW && cok && j == 0) {
+         lbs[(size_t)c * LS + l] = lb_ins;                                   // insert c before l
+         if (l <= S - 1) lbs[(size_t)(C + c) * LS + l] = lb_rep;             // c replaces l
+         if (c == 0 && l <= S - 1) lbs[(size_t)2 * C * LS + l] = lb_rem;     // l removed
+      }
+      __syncwarp();   // the staged run is overwritten by the next layer
+   }
+}
+
 // one warp per (x, l), x = 1 .. T (path layer, cluster cx; strided over grid.y), l = 1 .. S.  Two table blocks, four products.
 template <typename TT>
 __global__ void __launch_bounds__(256) k_vec_pairs(InstDev I, PathDev P, const TT *__restrict__ Dv, const int *__restrict__ meta,
@@ -342,6 +402,7 @@ k_eval_vec(InstDev I, const int *__restrict__ Dv, PathDev P, SegCache seg, VecCa
          } else
             cd = __ldg(reinterpret_cast<const int4 *>(cands) + kidx);
       }
+      if (cd.w >= C) cd.x = -1;                   // gain cluster out of range: a bad descriptor like any other bad index
       const VecCode vcd = decode_cand_vec(vc, T, C, mp, lcl, [&](int l) { return s_cum[l + 1] - s_cum[l]; },
                                           [&](int c) { return cinfo[c].y; }, [&](int l) { return s_pd[l]; }, cd.x, cd.y, cd.z);
       long long p_rb = 0;

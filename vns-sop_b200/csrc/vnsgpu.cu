@@ -117,6 +117,7 @@ vnsgpu_status vnsgpu_set_segment_cache(vnsgpu_ctx *ctx, int enable)
 
 vnsgpu_status vnsgpu_set_vector_cache(vnsgpu_ctx *ctx, int enable)
 {
+   ctx->use_vec_pack = enable != 3;        // 3: vectors always, one cluster per warp in the build (tests compare both)
    ctx->use_vec = enable < 0 ? 0 : (enable > 2 ? 2 : enable);
    return VNSGPU_OK;
 }

@@ -11,7 +11,9 @@
 // search (the binding INTEGRATION.md describes); both modes follow the reference's seeded trajectory.
 //
 // New keys (not in the reference): --seed=N (srand(N); default: time, like math_common.cpp:9-14),
-// --device=N, --device-loop=0|1, --config-file=path (default ./sop.cfg when present).
+// --device=N, --gpus=N (--batch only: the seeds are spread over devices N0 .. N0+N-1, one host thread and one context per
+// device - replicas, no collective: the honest multi-GPU mode of the search on shipped instances),
+// --device-loop=0|1, --config-file=path (default ./sop.cfg when present).
 // Not provided: the GUI (gui=none is the only accepted value), log4cxx logging, sop-type=op|opn|dop loaders
 // (sop-type=opn throws in the reference itself; its datasets are pre-sampled .sop files), the ILP solver.
 #include <sys/stat.h>
@@ -26,6 +28,7 @@
 #include <iostream>
 #include <map>
 #include <sstream>
+#include <thread>
 
 #include "sop_instance.hpp"
 #include "vnsgpu_path.hpp"
@@ -49,7 +52,7 @@ class Config {
           {"maximal-calculation-time-sec", "168000"}, {"lower-bound-above-budget-then-skip", "1"},
           {"generate-examples-of-operations", "0"}, {"sop-type", "sop"}, {"sop-solver", "vns"},
           {"initial-greedy-solution", "1"}, {"gui", "none"}, {"problem", ""}, {"nowait", "0"},
-          {"seed", ""}, {"device", "0"}, {"device-loop", "1"}, {"config-file", ""}, {"dump-problem", "0"}};
+          {"seed", ""}, {"device", "0"}, {"gpus", "1"}, {"device-loop", "1"}, {"config-file", ""}, {"dump-problem", "0"}};
       for (auto &d : defaults) { order_.push_back(d[0]); v_[d[0]] = d[1]; }
    }
    bool known(const std::string &k) const { return v_.count(k) != 0; }
@@ -343,7 +346,7 @@ int run(int argc, char **argv)
    for (int i = 1; i < argc; ++i) {   // --key=value | --key value | -h
       std::string a(argv[i]);
       if (a == "-h" || a == "--help") {
-         std::cout << "sop_vns_b200 --problem=FILE.sop [--seed=N] [--device=N] [--device-loop=0|1] [--batch=N] [--output=DIR]\n"
+         std::cout << "sop_vns_b200 --problem=FILE.sop [--seed=N] [--device=N] [--gpus=N] [--device-loop=0|1] [--batch=N] [--output=DIR]\n"
                       "             [--num-iterations=N] [--num-iterations-unimproved=N] [--maximal-calculation-time-sec=N]\n"
                       "             [--lower-bound-above-budget-then-skip=0|1] [--initial-greedy-solution=0|1] [--name=S]\n"
                       "             [--config-file=sop.cfg]   (all keys of the reference's sop.cfg are accepted)\n";
@@ -402,30 +405,59 @@ int run(int argc, char **argv)
    if (device_loop) {
       std::vector<uint32_t> seeds(nruns);
       for (int i = 0; i < nruns; ++i) seeds[i] = seed + (uint32_t)(first + i);
-      std::vector<vnsgpu_vns_result> res(nruns);
-      std::vector<int> tours(nruns, -1);
-      vnsgpu_vns_params prm = params_of(cfg, pb, seed);
-      int best = -1;
-      const auto t0 = std::chrono::steady_clock::now();
-      vnsgpu_status st = vnsgpu_vns_run_batch(eng.ctx(), tour.handle(), nruns, seeds.data(), &prm, res.data(), &best, tours.data());
-      if (st == VNSGPU_E_TOO_LARGE) {   // instance beyond the one-block-per-run kernel: run the seeds one by one (any other status is a real failure)
-         for (int i = 0; i < nruns; ++i) recs[i] = iterate_device(eng, cfg, pb, seeds[i], tour);
-      } else {
-         eng.check(st);
+      // one launch per device: runs [lo, hi) on engine e (its own context, table and tour)
+      auto run_on = [&](vnsgpu::Engine &e, vnsgpu::VnsSopPath &t0path, int lo, int hi) {
+         const int cnt = hi - lo;
+         if (cnt <= 0) return;
+         std::vector<vnsgpu_vns_result> res(cnt);
+         std::vector<int> tours(cnt, -1);
+         vnsgpu_vns_params prm = params_of(cfg, pb, seed);
+         int best = -1;
+         const auto t0 = std::chrono::steady_clock::now();
+         vnsgpu_status st = vnsgpu_vns_run_batch(e.ctx(), t0path.handle(), cnt, seeds.data() + lo, &prm, res.data(), &best, tours.data());
+         if (st == VNSGPU_E_TOO_LARGE) {   // instance beyond the one-block-per-run kernel: run the seeds one by one (any other status is a real failure)
+            for (int i = 0; i < cnt; ++i) recs[lo + i] = iterate_device(e, cfg, pb, seeds[lo + i], t0path);
+            return;
+         }
+         e.check(st);
          const long wall = (long)std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::steady_clock::now() - t0).count();
-         for (int i = 0; i < nruns; ++i) {
-            RunRecord &r = recs[i];
+         for (int i = 0; i < cnt; ++i) {
+            RunRecord &r = recs[lo + i];
             r.res = res[i];
-            r.ctime_ms = wall;   // all runs share the launch
+            r.ctime_ms = wall;   // all runs of a device share the launch
             std::vector<int> c, s;
             int T = 0;
-            eng.check(vnsgpu_path_get(eng.ctx(), tours[i], &T, 0, 0, 0, &r.length, 0, &r.reward));
+            e.check(vnsgpu_path_get(e.ctx(), tours[i], &T, 0, 0, 0, &r.length, 0, &r.reward));
             c.resize(T + 2);
             s.resize(T + 2);
-            eng.check(vnsgpu_path_get_solution(eng.ctx(), tours[i], c.data(), s.data(), 0));
+            e.check(vnsgpu_path_get_solution(e.ctx(), tours[i], c.data(), s.data(), 0));
             for (int j = 0; j < T + 2; ++j) r.path.push_back(vnsgpu::IndexSOP{c[j], s[j]});
-            vnsgpu_path_destroy(eng.ctx(), tours[i]);
+            vnsgpu_path_destroy(e.ctx(), tours[i]);
          }
+      };
+      const int gpus = std::max(1, std::min(cfg.num("gpus"), nruns));
+      if (gpus == 1) {
+         run_on(eng, tour, 0, nruns);
+      } else {
+         std::vector<std::thread> th;
+         std::vector<std::string> errs(gpus);
+         for (int g = 0; g < gpus; ++g) {
+            const int lo = (int)((long long)nruns * g / gpus), hi = (int)((long long)nruns * (g + 1) / gpus);
+            th.emplace_back([&, g, lo, hi] {
+               try {
+                  if (g == 0) { run_on(eng, tour, lo, hi); return; }
+                  vnsgpu::Engine e(cfg.num("device") + g);
+                  e.setClusters(pb.m, pb.reward, pb.start, pb.goal);
+                  if (!pb.xy.empty()) e.buildTableEuclid(pb.xy, pb.rule);
+                  else e.setTableDense(pb.W);
+                  vnsgpu::VnsSopPath t(e, pb.initial_vns(), 0);
+                  run_on(e, t, lo, hi);
+               } catch (const std::exception &ex) { errs[g] = ex.what(); }
+            });
+         }
+         for (auto &t : th) t.join();
+         for (int g = 0; g < gpus; ++g)
+            if (!errs[g].empty()) throw std::runtime_error("device " + std::to_string(cfg.num("device") + g) + ": " + errs[g]);
       }
    } else {
       for (int i = 0; i < nruns; ++i) recs[i] = iterate_host_loop(eng, cfg, pb, seed + (uint32_t)(first + i), tour);
