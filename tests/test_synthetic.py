@@ -177,7 +177,8 @@ def test_synthetic_local_search_placements(synth, place, blocks, monkeypatch):
 
 
 @pytest.mark.gpu
-def test_20k_instance_local_search_vs_oracle():
+@pytest.mark.parametrize("staged", [0, 1])
+def test_20k_instance_local_search_vs_oracle(staged, monkeypatch):
     """Config 5 (20 000 nodes / 2000 clusters, 3.2 GB table): one insertRandom and one exchangeRandom call of 30 000
     proposals each on the device (cooperating thread blocks, product tree, rows in global memory) against the C port on
     the same state: same VNS vector, targets, length, reward and RNG position; and 4000 candidates of that state
@@ -185,6 +186,7 @@ def test_20k_instance_local_search_vs_oracle():
     import time
     from oracle import binding as ob
     from vns_sop_b200 import engine, instances as ins, synthetic as sy
+    monkeypatch.setenv("VNSGPU_VEC_STAGED", str(staged))      # 1: the bulk-copy staged evaluation kernel (opt-in), read at vnsgpu_create
     sf = sy.generate()
     pb = ins.build_problem(sf)
     e = engine.Engine(0).load_problem(pb)
@@ -195,9 +197,12 @@ def test_20k_instance_local_search_vs_oracle():
         assert pg.getPathLength() == po.length()
         rs = np.random.RandomState(9)
         cands = random_candidates(rs, vns, T, 4000)
-        ln, lb, fl, first = pg.eval_batch(pg.make_cands(cands))
         oln, olb = po.eval_batch(cands)
-        assert (ln == oln).all() and (lb == olb).all()
+        for vecmode in (1, 2, 3):      # 1: the library's choice at this batch size (segment products); 2: endpoint vectors forced -
+            e.set_vector_cache(vecmode)      # packed vector build + staged evaluation kernel; 3: unpacked vector build
+            ln, lb, fl, first = pg.eval_batch(pg.make_cands(cands))
+            assert (ln == oln).all() and (lb == olb).all(), vecmode
+        e.set_vector_cache(1)
         rg, ro = engine.seeded_rng(3), ob.new_rng(3)
         for k in (1, 2):
             e.sync()

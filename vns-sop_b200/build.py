@@ -48,8 +48,7 @@ def _unit_deps(unit):
 
 
 def build(force=False, verbose=False):
-    if not force and not stale():
-        return LIB
+    # always decided per object (an edit made while an earlier build was still linking is older than the library)
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     os.makedirs(OBJ, exist_ok=True)
     units = [u for u in UNITS if os.path.exists(os.path.join(CSRC, u))]
@@ -58,7 +57,8 @@ def build(force=False, verbose=False):
         o = os.path.join(OBJ, u.replace(".cu", ".o"))
         objs.append(o)
         deps = _unit_deps(u)
-        if not force and os.path.exists(o) and all(os.path.getmtime(d) <= os.path.getmtime(o) for d in deps if os.path.exists(d)):
+        hdr = os.path.join(HERE, "..", "include", "vnsgpu.h")
+        if not force and os.path.exists(o) and all(os.path.getmtime(d) <= os.path.getmtime(o) for d in deps + [hdr] if os.path.exists(d)):
             continue
         cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", "-o", o, os.path.join(CSRC, u)]
         log = open(o + ".log", "w")
@@ -75,7 +75,8 @@ def build(force=False, verbose=False):
             print(open(log.name).read())
     if failed:
         raise RuntimeError("nvcc failed on " + ", ".join(failed))
-    subprocess.check_call([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB] + objs, cwd=CSRC)
+    if procs or not os.path.exists(LIB) or any(os.path.getmtime(o) > os.path.getmtime(LIB) for o in objs):
+        subprocess.check_call([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB] + objs, cwd=CSRC)
     return LIB
 
 

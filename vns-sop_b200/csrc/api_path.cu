@@ -63,6 +63,7 @@ vnsgpu_status vnsgpu_path_copy(vnsgpu_ctx *ctx, int dst, int src)
    if (!path_ok(ctx, dst) || !path_ok(ctx, src)) return VNSGPU_E_STATE;
    k_path_copy<<<1, 256, 0, ctx->stream>>>(ctx->I, ctx->paths[dst].d, ctx->paths[src].d);
    LAUNCHED(ctx);
+   ctx->paths[dst].hdr_ok = false;
    return VNSGPU_OK;
 }
 
@@ -391,8 +392,30 @@ static vnsgpu_status launch_eval(vnsgpu_ctx *ctx, int path, int64_t n, int64_t i
       if (lat) VNS_LAUNCH_VEC_L(GG, RR, true);                                                                        \
       else VNS_LAUNCH_VEC_L(GG, RR, false);                                                                           \
    } while (0)
-         // tables beyond the caches: the same kernel with the NEXT candidate's block and vectors prefetched into L1
+         // tables beyond the caches: the same kernel with the NEXT candidate's block and vectors prefetched into L1 - or,
+         // with clusters of at most 16 samples, the staged form (every lane copies its candidate's block and vectors into
+         // shared memory with cp.async: k_eval_vec_st)
          const bool lat = vec_lat(ctx);
+         if (lat && I.mp <= 16 && ctx->use_vec_staged) {
+            const size_t meta_b = (smem + 15) & ~(size_t)15, per_warp = sizeof(int) * 32 * (size_t)vecst_slot_ints(I.mp);
+            const int wpc = (int)std::min<size_t>(8, ((size_t)ctx->max_smem - 2048 - meta_b) / per_warp);
+            if (wpc >= 2) {
+               const size_t sm_st = meta_b + per_warp * wpc;
+               const int gst = (int)std::max<int64_t>(1, std::min<int64_t>((n + 32 * wpc - 1) / (32 * wpc), ctx->num_sms));
+#define VNS_LAUNCH_ST(GG, RR)                                                                                        \
+   do {                                                                                                              \
+      CK(cudaFuncSetAttribute(k_eval_vec_st<GG, RR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_st));        \
+      k_eval_vec_st<GG, RR><<<gst, 32 * wpc, sm_st, st>>>(I, ctx->d_D32, P, seg, vc, n, idx0, d_cands, d_perm, budget, skip, d_len, d_lb, \
+                                                          d_flags, d_first, fmt, d_leni, (int)(meta_b / 4));          \
+   } while (0)
+               if (G == 8 && NR == 1) VNS_LAUNCH_ST(8, 1);
+               else if (G == 8) VNS_LAUNCH_ST(8, 2);
+               else VNS_LAUNCH_ST(16, 1);
+#undef VNS_LAUNCH_ST
+               LAUNCHED(ctx);
+               return VNSGPU_OK;
+            }
+         }
          if (G == 8 && NR == 1) VNS_LAUNCH_VEC(8, 1);
          else if (G == 8 && NR == 2) VNS_LAUNCH_VEC(8, 2);
          else if (G == 8) VNS_LAUNCH_VEC(8, 4);
@@ -414,6 +437,27 @@ static vnsgpu_status launch_eval(vnsgpu_ctx *ctx, int path, int64_t n, int64_t i
    LAUNCHED(ctx);
    return VNSGPU_OK;
 }
+
+} // extern "C"
+
+bool eval_dev_accepts_packed32(const vnsgpu_ctx *ctx, int64_t n)
+{
+   const int mode = eval_mode(ctx, n);
+   return mode == 2 && !eval_sorts(ctx, n, mode) && ctx->I.C < 16384 && group_kernel_ok(ctx);
+}
+
+vnsgpu_status eval_dev_first(vnsgpu_ctx *ctx, int path, int64_t n, const void *d_cands, int format, double budget, int skip, long long *d_first,
+                             cudaStream_t st)
+{
+   CK(cudaMemsetAsync(d_first, 0xFF, sizeof(long long), st));   // -1 = none
+   const int useseg = eval_mode(ctx, n);
+   vnsgpu_status s = prepare_eval(ctx, path, useseg, st);
+   if (s) return s;
+   return launch_eval(ctx, path, n, 0, reinterpret_cast<const vnsgpu_cand *>(d_cands), budget, skip, nullptr, nullptr, nullptr,
+                      (unsigned long long *)d_first, st, 0, 0, useseg, format == 2 ? 2 : 0, nullptr);
+}
+
+extern "C" {
 
 int vnsgpu_eval_mode(const vnsgpu_ctx *ctx, int64_t n)
 {

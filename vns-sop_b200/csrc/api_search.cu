@@ -231,6 +231,7 @@ vnsgpu_status vnsgpu_vns_run(vnsgpu_ctx *ctx, int path, const vnsgpu_vns_params 
       }
    }
    if (s) { if (work >= 0) vnsgpu_path_destroy(ctx, work); return s; }
+   ctx->paths[path].hdr_ok = false;
    VnsResultDev r;
    CK(cudaMemcpyAsync(&r, ctx->d_res, sizeof(r), cudaMemcpyDeviceToHost, ctx->stream));
    CK(cudaStreamSynchronize(ctx->stream));

@@ -130,6 +130,7 @@ vnsgpu_status vnsgpu_path_broadcast(vnsgpu_ctx *ctx, int path, int root, void *s
    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
    void *b = ctx->paths[path].block;
    NCK(nccl_api().Broadcast(b, b, ctx->paths[path].bytes, ncclChar, root, (ncclComm_t)ctx->comm, st));
+   ctx->paths[path].hdr_ok = false;
    return VNSGPU_OK;
 }
 

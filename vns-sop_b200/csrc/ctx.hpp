@@ -18,7 +18,15 @@ static_assert(sizeof(vnsgpu_cand) == 16, "cand layout");
 
 #define VNS_PIPE_EVENTS 16
 
+// host mirror of the path header (read back after every mutating call)
+struct PathHdr {
+   int hdr[HDR_INTS];
+   double hd[HD_DBLS];
+};
+
 struct PathHost {
+   PathHdr hdr_cache{};      // the header as last read back (every mutating call ends with a read); valid while hdr_ok
+   bool hdr_ok = false;
    void *block = nullptr;
    size_t bytes = 0;         // size of the block (one cudaMalloc: header .. minB)
    PathDev d{};
@@ -62,6 +70,8 @@ struct vnsgpu_ctx {
    bool use_seg_tiles = true; // two-level build of the segment products on long tours (enable = 2 of vnsgpu_set_segment_cache: off)
    bool seg_ok = false;      // the int32 buffer has room for them and offsets fit 32 bits
    int *d_segmeta = nullptr;
+   bool use_vec_staged = false; // staged (bulk-copy) evaluation kernel on tables beyond the caches: opt-in, VNSGPU_VEC_STAGED=1 (slower
+                                // than the prefetch form so far: 1.10 ms against 0.73 ms on the 20 k-node table, profiles/r3d_*)
    bool use_vec_pack = true; // several small clusters per warp in the endpoint-vector build (vnsgpu_set_vector_cache(ctx, 3): off)
    int use_vec = 1;          // 0 off, 1 when the batch is large enough, 2 always; endpoint vectors on top of the segment products (vnsgpu_set_vector_cache, vec.cuh)
    int *d_vec = nullptr, *d_veclb = nullptr;
@@ -100,7 +110,8 @@ struct vnsgpu_ctx {
    int comm_rank = 0, comm_size = 1;
    // device-side candidate generation (gen.cu)
    unsigned *d_genjump = nullptr;
-   size_t genjump_lo_words = 0;
+   size_t genjump_lo_words = 0, genjump_mid_words = 0;
+   void *h_pick = nullptr;        // pinned record vnsgpu_propose_eval reads back
    void *d_gen = nullptr, *d_gencands = nullptr;
    size_t gen_bytes = 0, gencands_bytes = 0;
    bool phase_timing = false;     // vnsgpu_set_phase_timing: CUDA events around the phases of the batched evaluation call
@@ -173,18 +184,14 @@ static inline bool path_ok(vnsgpu_ctx *ctx, int path)
 
 static inline size_t al16(size_t x) { return (x + 15) & ~(size_t)15; }
 
-// host mirror of the path header (read back after every mutating call)
-struct PathHdr {
-   int hdr[HDR_INTS];
-   double hd[HD_DBLS];
-};
-
 static inline vnsgpu_status read_hdr(vnsgpu_ctx *ctx, int path, PathHdr *h)
 {
    const PathDev &d = ctx->paths[path].d;
    // hdr and hd are adjacent at the start of the block
    CK(cudaMemcpyAsync(h, d.hdr, sizeof(PathHdr), cudaMemcpyDeviceToHost, ctx->stream));
    CK(cudaStreamSynchronize(ctx->stream));
+   ctx->paths[path].hdr_cache = *h;
+   ctx->paths[path].hdr_ok = true;
    return VNSGPU_OK;
 }
 
@@ -222,3 +229,9 @@ struct PhaseTimer {
       ctx->phase_events.push_back(pe);
    }
 };
+
+// internal entry points of api_path.cu used by gen.cu: evaluation of device candidates for the first accepted index only;
+// format 0 = vnsgpu_cand, 2 = vnsgpu_pack_cand32 words (only when eval_dev_accepts_packed32 says so)
+bool eval_dev_accepts_packed32(const vnsgpu_ctx *ctx, int64_t n);
+vnsgpu_status eval_dev_first(vnsgpu_ctx *ctx, int path, int64_t n, const void *d_cands, int format, double budget, int skip, long long *d_first,
+                             cudaStream_t st);

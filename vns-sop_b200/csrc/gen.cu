@@ -3,62 +3,71 @@
 // (:723-730: to in [0, T-1], redrawn while |from - to| <= 2) in DRAW ORDER, as device descriptors - the batched evaluation
 // then needs no candidate bytes over PCIe at all.
 //
-// glibc's rand() stream is linear, so slice r of 256 draw pairs starts from the state M^(512 r) s: two 31 x 31
-// matrix-vector products (powers of M^512 and of M^(512 * 64), rngjump.hpp).  Pass 1: every thread block generates its
-// slice (warp 0: 17 x 31 values by shuffle prefix sums), maps the pairs to (from, to), counts the valid ones.  Pass 2:
+// glibc's rand() stream is linear, so warp w's 32 draw pairs start from the state M^(64 w) s: three 31 x 31 matrix-vector
+// products (powers of M^64, M^4096 and M^262144, rngjump.hpp).  Pass 1: every warp generates its 64 draws (3 x 31 values
+// by shuffle prefix sums), maps the pairs to (from, to); a thread block counts its 256 pairs' valid ones.  Pass 2:
 // exclusive scan of the slice counts.  Pass 3: valid pair k of slice r becomes proposal offset[r] + k, written as a
 // vnsgpu_cand (16 B) or a vnsgpu_pack_cand32 word together with the number of rand() calls consumed up to and including
 // it - what rewinds the RNG to "just after the accepted proposal" (rngjump::advance on the host).
 #include "ctx.hpp"
 #include "rngjump.hpp"
 
-#define GEN_PAIRS 256
-#define GEN_LO 64
-#define GEN_HI 1024
+#define GEN_PAIRS 256          // pairs per thread block (one slice of the scan)
+#define GEN_WPAIRS 32          // pairs per warp: every warp jumps to its own 64 draws
+#define GEN_L0 64              // jump tables: M^(64 a), a < 64;  M^(4096 b), b < 64;  M^(262144 c), c < 256  (64 Mi draws)
+#define GEN_L1 64
+#define GEN_L2 256
 
 struct GenJob {
-   const unsigned *lo, *hi;     // jump matrices [r][31][32]
-   unsigned s0[31];             // canonical state at the start of the call
+   const unsigned *j0, *j1, *j2;   // jump matrices [r][31][32]
+   unsigned s0[31];                // canonical state at the start of the call
    int kind, nvns, T;
    long long nslices;
 };
 
+static __device__ __forceinline__ unsigned gen_matvec(const unsigned *__restrict__ m, const unsigned *v, int lane)
+{
+   unsigned acc = 0;
+   if (lane < 31)
+#pragma unroll 8
+      for (int j = 0; j < 31; ++j) acc += __ldg(m + j * 32 + lane) * v[j];
+   return acc;
+}
+
 static __global__ void __launch_bounds__(GEN_PAIRS) k_gen_pairs(GenJob J, unsigned long long *__restrict__ pairs, unsigned *__restrict__ counts)
 {
-   __shared__ unsigned ring[31 + 31 * 17 + 2];
-   __shared__ unsigned s1[32];
+   __shared__ unsigned ring[GEN_PAIRS / 32][31 + 31 * 3 + 3];
+   __shared__ unsigned sv[GEN_PAIRS / 32][2][32];
    __shared__ int wcnt[GEN_PAIRS / 32];
    constexpr unsigned FULL = 0xffffffffu;
    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-   const long long r = blockIdx.x;
-   if (warp == 0) {
-      const unsigned *mh = J.hi + (size_t)(r / GEN_LO) * 31 * 32, *ml = J.lo + (size_t)(r % GEN_LO) * 31 * 32;
-      unsigned acc = 0;
-      if (lane < 31)
-         for (int j = 0; j < 31; ++j) acc += __ldg(mh + j * 32 + lane) * J.s0[j];
-      s1[lane] = acc;
+   const long long ws = (long long)blockIdx.x * (GEN_PAIRS / 32) + warp;       // this warp's slice of 64 draws
+   unsigned *rg = ring[warp];
+   {
+      const unsigned a = gen_matvec(J.j2 + (size_t)(ws / (GEN_L0 * GEN_L1)) * 31 * 32, J.s0, lane);
+      sv[warp][0][lane] = a;
       __syncwarp();
-      acc = 0;
-      if (lane < 31)
-         for (int j = 0; j < 31; ++j) acc += __ldg(ml + j * 32 + lane) * s1[j];
-      if (lane < 31) ring[lane] = acc;
+      const unsigned b = gen_matvec(J.j1 + (size_t)((ws / GEN_L0) % GEN_L1) * 31 * 32, sv[warp][0], lane);
+      sv[warp][1][lane] = b;
       __syncwarp();
-      for (int gen = 31; gen < 31 + 2 * GEN_PAIRS; gen += 31) {     // x_{gen+k} = x_{gen+k-31} + x_{gen+k-3}: scan with stride 3
-         unsigned a = 0;
-         if (lane < 31) a = ring[gen - 31 + lane];
-         if (lane < 3) a += ring[gen - 3 + lane];
+      const unsigned c = gen_matvec(J.j0 + (size_t)(ws % GEN_L0) * 31 * 32, sv[warp][1], lane);
+      if (lane < 31) rg[lane] = c;
+      __syncwarp();
+      for (int gen = 31; gen < 31 + 2 * GEN_WPAIRS; gen += 31) {     // x_{gen+k} = x_{gen+k-31} + x_{gen+k-3}: scan with stride 3
+         unsigned a2 = 0;
+         if (lane < 31) a2 = rg[gen - 31 + lane];
+         if (lane < 3) a2 += rg[gen - 3 + lane];
 #pragma unroll
          for (int d = 3; d < 32; d <<= 1) {
-            const unsigned t = __shfl_up_sync(FULL, a, d);
-            if (lane >= d) a += t;
+            const unsigned t = __shfl_up_sync(FULL, a2, d);
+            if (lane >= d) a2 += t;
          }
-         if (lane < 31) ring[gen + lane] = a;
+         if (lane < 31) rg[gen + lane] = a2;
          __syncwarp();
       }
    }
-   __syncthreads();
    const int p = threadIdx.x;
-   const unsigned r1 = ring[31 + 2 * p] >> 1, r2 = ring[31 + 2 * p + 1] >> 1;
+   const unsigned r1 = rg[31 + 2 * lane] >> 1, r2 = rg[31 + 2 * lane + 1] >> 1;
    const int tohi = J.kind == 1 ? J.T : J.T - 1, gap = J.kind == 1 ? 1 : 2;
    const int from = (int)(((unsigned long long)r1 * (unsigned)J.nvns) >> 31);           // randIntMinMax, math_common.cpp:21-28
    const int to = (int)(((unsigned long long)r2 * (unsigned)(tohi + 1)) >> 31);
@@ -68,8 +77,8 @@ static __global__ void __launch_bounds__(GEN_PAIRS) k_gen_pairs(GenJob J, unsign
    __syncthreads();
    int rank = __popc(bal & ((1u << lane) - 1)), total = 0;
    for (int w = 0; w < GEN_PAIRS / 32; ++w) { if (w < warp) rank += wcnt[w]; total += wcnt[w]; }
-   pairs[r * GEN_PAIRS + p] = valid ? (1ull << 63) | ((unsigned long long)rank << 40) | ((unsigned long long)to << 20) | (unsigned)from : 0ull;
-   if (threadIdx.x == 0) counts[r] = (unsigned)total;
+   pairs[(long long)blockIdx.x * GEN_PAIRS + p] = valid ? (1ull << 63) | ((unsigned long long)rank << 40) | ((unsigned long long)to << 20) | (unsigned)from : 0ull;
+   if (threadIdx.x == 0) counts[blockIdx.x] = (unsigned)total;
 }
 
 // exclusive scan of the slice counts (one block); total[0] = number of valid pairs, total[1] = draws consumed up to and
@@ -120,31 +129,53 @@ static __global__ void __launch_bounds__(GEN_PAIRS) k_gen_emit(int kind, int T, 
 static vnsgpu_status gen_tables(vnsgpu_ctx *ctx)
 {
    if (ctx->d_genjump) return VNSGPU_OK;
-   std::vector<unsigned> lo, hi;
-   rngjump::powers_for_device(GEN_LO, 9, lo);            // steps of 2 * GEN_PAIRS = 2^9 draws
-   rngjump::powers_for_device(GEN_HI, 15, hi);           // steps of 2^9 * GEN_LO = 2^15 draws
-   CK(cudaMalloc(&ctx->d_genjump, sizeof(unsigned) * (lo.size() + hi.size())));
-   CK(cudaMemcpy(ctx->d_genjump, lo.data(), sizeof(unsigned) * lo.size(), cudaMemcpyHostToDevice));
-   CK(cudaMemcpy(ctx->d_genjump + lo.size(), hi.data(), sizeof(unsigned) * hi.size(), cudaMemcpyHostToDevice));
-   ctx->genjump_lo_words = lo.size();
+   std::vector<unsigned> t0, t1, t2;
+   rngjump::powers_for_device(GEN_L0, 6, t0);            // steps of 2 * GEN_WPAIRS = 2^6 draws
+   rngjump::powers_for_device(GEN_L1, 12, t1);           // steps of 2^6 * GEN_L0 = 2^12 draws
+   rngjump::powers_for_device(GEN_L2, 18, t2);           // steps of 2^12 * GEN_L1 = 2^18 draws
+   CK(cudaMalloc(&ctx->d_genjump, sizeof(unsigned) * (t0.size() + t1.size() + t2.size())));
+   CK(cudaMemcpy(ctx->d_genjump, t0.data(), sizeof(unsigned) * t0.size(), cudaMemcpyHostToDevice));
+   CK(cudaMemcpy(ctx->d_genjump + t0.size(), t1.data(), sizeof(unsigned) * t1.size(), cudaMemcpyHostToDevice));
+   CK(cudaMemcpy(ctx->d_genjump + t0.size() + t1.size(), t2.data(), sizeof(unsigned) * t2.size(), cudaMemcpyHostToDevice));
+   ctx->genjump_lo_words = t0.size();
+   ctx->genjump_mid_words = t1.size();
    return VNSGPU_OK;
 }
 
-extern "C" {
+// what one round of a host-driven search reads back: one 64-byte record, one copy, one synchronisation
+struct GenPick {
+   long long first;               // first accepted proposal or -1
+   unsigned long long total_valid, total_draws;
+   unsigned draws_first, pad;
+   int4 cand;
+};
 
-void vnsgpu_rng_advance(vnsgpu_rng *rng, uint64_t ndraws) { rngjump::advance(*reinterpret_cast<RngState *>(rng), ndraws); }
-
-vnsgpu_status vnsgpu_gen_proposals_dev(vnsgpu_ctx *ctx, int path, int kind, int64_t n, vnsgpu_rng *rng, void *d_out, int format,
-                                       uint32_t *d_draws, void *stream)
+static __global__ void k_gen_pick(const long long *d_first, const unsigned long long *total, const unsigned *draws, const void *cands, int format,
+                                  GenPick *out)
 {
-   CK(cudaSetDevice(ctx->device));
-   if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
-   if (kind != 1 && kind != 2) return fail(ctx, VNSGPU_E_RANGE, "kind must be 1 (insert) or 2 (exchange)");
-   if (format != 0 && format != 2) return fail(ctx, VNSGPU_E_RANGE, "format must be 0 (vnsgpu_cand) or 2 (vnsgpu_pack_cand32 words)");
-   if (n <= 0) return VNSGPU_OK;
-   cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+   GenPick g;
+   g.first = *d_first;
+   g.total_valid = total[0]; g.total_draws = total[1];
+   g.draws_first = 0; g.pad = 0; g.cand = make_int4(-1, 0, 0, -1);
+   if (g.first >= 0) {
+      g.draws_first = draws[g.first];
+      if (format == 2) {
+         const unsigned w = reinterpret_cast<const unsigned *>(cands)[g.first];
+         g.cand.x = (int)(w & 7); g.cand.y = (int)((w >> 3) & 0x3fff); g.cand.z = (int)((w >> 17) & 0x3fff); g.cand.w = (w >> 31) ? g.cand.y : -1;
+      } else
+         g.cand = reinterpret_cast<const int4 *>(cands)[g.first];
+   }
+   *out = g;
+}
+
+// launches the three generation kernels on `st`; no synchronisation.  d_total: 2 x u64 (valid pairs, draws up to proposal n - 1)
+static vnsgpu_status gen_launch(vnsgpu_ctx *ctx, int path, int kind, int64_t n, const vnsgpu_rng *rng, void *d_out, int format, uint32_t *d_draws,
+                                cudaStream_t st, unsigned long long **d_total_out)
+{
    PathHdr h;
-   vnsgpu_status s = read_hdr(ctx, path, &h);
+   vnsgpu_status s = VNSGPU_OK;
+   if (ctx->paths[path].hdr_ok) h = ctx->paths[path].hdr_cache;      // no round trip: every mutating call read the header back
+   else s = read_hdr(ctx, path, &h);
    if (s) return s;
    const int T = h.hdr[HDR_T], nvns = h.hdr[HDR_NVNS];
    if (kind == 1 ? nvns < 3 : (nvns < 4 || T < 3)) return fail(ctx, VNSGPU_E_STATE, "neighbourhood is empty for this state");
@@ -161,20 +192,20 @@ vnsgpu_status vnsgpu_gen_proposals_dev(vnsgpu_ctx *ctx, int path, int kind, int6
    if (pv < 0.05) return fail(ctx, VNSGPU_E_STATE, "fewer than 5% of the draw pairs are proposals in this state: use vnsgpu_gen_proposals");
    const double need = (double)n / pv;
    const long long nslices = (long long)((need + 6.0 * std::sqrt(need * (1.0 - pv) / pv) + 2 * GEN_PAIRS) / GEN_PAIRS) + 1;
-   if (nslices > (long long)GEN_LO * GEN_HI) return fail(ctx, VNSGPU_E_RANGE, "more than 16 Mi draw pairs in one call: split the batch");
+   if (nslices * GEN_PAIRS * 2 > (long long)64 * GEN_L0 * GEN_L1 * GEN_L2) return fail(ctx, VNSGPU_E_RANGE, "more than 32 Mi draw pairs in one call: split the batch");
    s = gen_tables(ctx);
    if (s) return s;
-   const size_t bytes = sizeof(unsigned long long) * (size_t)nslices * GEN_PAIRS + sizeof(unsigned long long) * (size_t)nslices + sizeof(unsigned) * (size_t)nslices + 64;
+   const size_t bytes = sizeof(unsigned long long) * (size_t)nslices * GEN_PAIRS + sizeof(unsigned long long) * (size_t)nslices + sizeof(unsigned) * (size_t)nslices + 256;
    if (bytes > ctx->gen_bytes) {
       if (ctx->d_gen) { CK(cudaStreamSynchronize(st)); CK(cudaFree(ctx->d_gen)); }
       ctx->d_gen = nullptr; ctx->gen_bytes = 0;
       CK(cudaMalloc(&ctx->d_gen, bytes));
       ctx->gen_bytes = bytes;
    }
-   unsigned long long *d_total = (unsigned long long *)ctx->d_gen, *d_pairs = d_total + 8, *d_offs = d_pairs + (size_t)nslices * GEN_PAIRS;
+   unsigned long long *d_total = (unsigned long long *)ctx->d_gen, *d_pairs = d_total + 32, *d_offs = d_pairs + (size_t)nslices * GEN_PAIRS;
    unsigned *d_counts = (unsigned *)(d_offs + nslices);
    GenJob J;
-   J.lo = ctx->d_genjump; J.hi = ctx->d_genjump + ctx->genjump_lo_words;
+   J.j0 = ctx->d_genjump; J.j1 = J.j0 + ctx->genjump_lo_words; J.j2 = J.j1 + ctx->genjump_mid_words;
    rngjump::canonical(*reinterpret_cast<const RngState *>(rng), J.s0);
    J.kind = kind; J.nvns = nvns; J.T = T; J.nslices = nslices;
    CK(cudaMemsetAsync(d_total, 0, 64, st));
@@ -184,6 +215,26 @@ vnsgpu_status vnsgpu_gen_proposals_dev(vnsgpu_ctx *ctx, int path, int kind, int6
    LAUNCHED(ctx);
    k_gen_emit<<<(unsigned)nslices, GEN_PAIRS, 0, st>>>(kind, T, n, ctx->paths[path].d.vns, d_pairs, d_offs, d_out, format, d_draws, d_total);
    LAUNCHED(ctx);
+   *d_total_out = d_total;
+   return VNSGPU_OK;
+}
+
+extern "C" {
+
+void vnsgpu_rng_advance(vnsgpu_rng *rng, uint64_t ndraws) { rngjump::advance(*reinterpret_cast<RngState *>(rng), ndraws); }
+
+vnsgpu_status vnsgpu_gen_proposals_dev(vnsgpu_ctx *ctx, int path, int kind, int64_t n, vnsgpu_rng *rng, void *d_out, int format,
+                                       uint32_t *d_draws, void *stream)
+{
+   CK(cudaSetDevice(ctx->device));
+   if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
+   if (kind != 1 && kind != 2) return fail(ctx, VNSGPU_E_RANGE, "kind must be 1 (insert) or 2 (exchange)");
+   if (format != 0 && format != 2) return fail(ctx, VNSGPU_E_RANGE, "format must be 0 (vnsgpu_cand) or 2 (vnsgpu_pack_cand32 words)");
+   if (n <= 0) return VNSGPU_OK;
+   cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+   unsigned long long *d_total = nullptr;
+   vnsgpu_status s = gen_launch(ctx, path, kind, n, rng, d_out, format, d_draws, st, &d_total);
+   if (s) return s;
    unsigned long long tot[2];
    CK(cudaMemcpyAsync(tot, d_total, sizeof(tot), cudaMemcpyDeviceToHost, st));
    CK(cudaStreamSynchronize(st));
@@ -201,37 +252,41 @@ vnsgpu_status vnsgpu_propose_eval(vnsgpu_ctx *ctx, int path, int kind, int64_t n
 {
    CK(cudaSetDevice(ctx->device));
    if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
+   if (kind != 1 && kind != 2) return fail(ctx, VNSGPU_E_RANGE, "kind must be 1 (insert) or 2 (exchange)");
    if (first_accept) *first_accept = -1;
    if (n <= 0) return VNSGPU_OK;
-   const size_t bytes = sizeof(vnsgpu_cand) * (size_t)n + sizeof(unsigned) * (size_t)n + 64;
+   const size_t bytes = sizeof(vnsgpu_cand) * (size_t)n + sizeof(unsigned) * (size_t)n + 256;
    if (bytes > ctx->gencands_bytes) {
       if (ctx->d_gencands) { CK(cudaStreamSynchronize(ctx->stream)); CK(cudaFree(ctx->d_gencands)); }
       ctx->d_gencands = nullptr; ctx->gencands_bytes = 0;
       CK(cudaMalloc(&ctx->d_gencands, bytes));
       ctx->gencands_bytes = bytes;
    }
+   if (!ctx->h_pick) CK(cudaMallocHost(&ctx->h_pick, sizeof(GenPick)));
    long long *d_first = (long long *)ctx->d_gencands;
-   vnsgpu_cand *d_c = (vnsgpu_cand *)((char *)ctx->d_gencands + 64);
-   unsigned *d_draws = (unsigned *)(d_c + n);
-   const vnsgpu_rng rng0 = *rng;
-   vnsgpu_status s = vnsgpu_gen_proposals_dev(ctx, path, kind, n, rng, d_c, 0, d_draws, ctx->stream);
+   GenPick *d_pick = (GenPick *)((char *)ctx->d_gencands + 64);
+   void *d_c = (char *)ctx->d_gencands + 256;
+   unsigned *d_draws = (unsigned *)((char *)d_c + sizeof(vnsgpu_cand) * (size_t)n);
+   cudaStream_t st = ctx->stream;
+   // 4-byte descriptors that the endpoint-vector kernel reads in place, when the batch takes that form
+   const int format = eval_dev_accepts_packed32(ctx, n) ? 2 : 0;
+   unsigned long long *d_total = nullptr;
+   vnsgpu_status s = gen_launch(ctx, path, kind, n, rng, d_c, format, d_draws, st, &d_total);
    if (s) return s;
-   s = vnsgpu_eval_batch_dev(ctx, path, n, d_c, budget, skip, nullptr, nullptr, nullptr, d_first, ctx->stream);
+   s = eval_dev_first(ctx, path, n, d_c, format, budget, skip, d_first, st);
    if (s) return s;
-   long long first = -1;
-   CK(cudaMemcpyAsync(&first, d_first, sizeof(first), cudaMemcpyDeviceToHost, ctx->stream));
-   CK(cudaStreamSynchronize(ctx->stream));
-   if (first >= 0) {
-      unsigned used = 0;
-      vnsgpu_cand c;
-      CK(cudaMemcpyAsync(&used, d_draws + first, sizeof(used), cudaMemcpyDeviceToHost, ctx->stream));
-      CK(cudaMemcpyAsync(&c, d_c + first, sizeof(c), cudaMemcpyDeviceToHost, ctx->stream));
-      CK(cudaStreamSynchronize(ctx->stream));
-      *rng = rng0;
-      vnsgpu_rng_advance(rng, used);
-      if (accepted) *accepted = c;
-   }
-   if (first_accept) *first_accept = first;
+   k_gen_pick<<<1, 1, 0, st>>>(d_first, d_total, d_draws, d_c, format, d_pick);
+   LAUNCHED(ctx);
+   GenPick *hp = (GenPick *)ctx->h_pick;
+   CK(cudaMemcpyAsync(hp, d_pick, sizeof(GenPick), cudaMemcpyDeviceToHost, st));
+   CK(cudaStreamSynchronize(st));
+   if ((int64_t)hp->total_valid < n || hp->total_draws == 0) return fail(ctx, VNSGPU_E_STATE, "vnsgpu_propose_eval: slice estimate fell short (6-sigma event): call again");
+   if (hp->first >= 0) {
+      vnsgpu_rng_advance(rng, hp->draws_first);
+      if (accepted) { accepted->op = hp->cand.x; accepted->a = hp->cand.y; accepted->b = hp->cand.z; accepted->gain_cluster = hp->cand.w; }
+   } else
+      vnsgpu_rng_advance(rng, hp->total_draws);
+   if (first_accept) *first_accept = hp->first;
    return VNSGPU_OK;
 }
 

@@ -541,3 +541,214 @@ k_eval_vec(InstDev I, const int *__restrict__ Dv, PathDev P, SegCache seg, VecCa
    }
    if (d_first && best != ULLONG_MAX) atomicMin(d_first, best);
 }
+
+
+// ---- staged form for tables beyond the caches with small clusters (mp <= 16) ------------------------------------------
+// k_eval_vec<.,.,PF> gathers every candidate's block and vectors with plain loads + L1 prefetches: on the 20 k-node table
+// (blocks of 400 B, vectors of 40 B, 5 GB of table + products + vectors) it is a chain of exposed HBM round trips (ncu
+// r2i: 23 % of the measured copy bandwidth, eligible warps 0.8 / cycle).  Here lane L owns candidate base + L through
+// the memory phase: it issues the copies of ITS block and two vectors as (at most three) bulk copies - cp.async.bulk,
+// completion on the warp's mbarrier - into its own shared-memory slot (start rounded down to the 16-byte line, the data
+// keeps its offset inside the slot), so one warp has 32 candidates' bytes in flight from 3 instructions per lane and 8
+// warps per SM keep ~140 KB outstanding; after one wait the groups evaluate out of shared memory.  Slots start zeroed and only ever receive table / product / vector words (all in [0, INF]), so the
+// unclamped rows of the block product pair INF with numbers that neither wrap nor win.
+__host__ __device__ inline int vecst_slot_ints(int mp)
+{
+   const int v = ((mp * 4 + 15) & ~15) + 16, b = ((mp * mp * 4 + 15) & ~15) + 16;      // bytes: vector, block (+ alignment slack)
+   return (2 * v + b) / 4 + 4;
+}
+
+template <int G, int NR>
+__global__ void __launch_bounds__(VNS_EVAL_THREADS)
+k_eval_vec_st(InstDev I, const int *__restrict__ Dv, PathDev P, SegCache seg, VecCache vc, long long n, long long idx0,
+              const void *__restrict__ cands, const unsigned *__restrict__ perm, double budget, int skipflag,
+              double *__restrict__ len, double *__restrict__ lb, uint8_t *__restrict__ flags, unsigned long long *d_first,
+              int fmt, int *__restrict__ leni, int meta_ints)
+{
+   extern __shared__ __align__(16) int smem_i[];
+   constexpr unsigned FULL = 0xffffffffu;
+   constexpr int INF = VNS_INT_INF;
+   const int T = P.hdr[HDR_T], C = I.C, mp = I.mp;
+   int *lcl = smem_i;
+   int2 *cinfo = reinterpret_cast<int2 *>(smem_i + ((T + 2 + 1) & ~1));
+   for (int l = threadIdx.x; l < T + 2; l += blockDim.x) lcl[l] = layer_cluster(I, P.tg, T, l);
+   for (int c = threadIdx.x; c < C; c += blockDim.x) cinfo[c] = make_int2(I.off[c], I.m[c]);
+   long long *s_rowoff = reinterpret_cast<long long *>(cinfo + C);
+   int *s_cum = reinterpret_cast<int *>(s_rowoff + (T + 2)), *s_pd = s_cum + (T + 3);
+   for (int l = threadIdx.x; l < T + 3; l += blockDim.x) s_cum[l] = seg.cum[l];
+   for (int l = threadIdx.x; l < T + 2; l += blockDim.x) { s_pd[l] = seg.pd[l]; s_rowoff[l] = seg.rowoff[l]; }
+   // staging slots behind the layer maps: [warp][candidate lane][slot]
+   const int slot_ints = vecst_slot_ints(mp);
+   const int vbytes = ((mp * 4 + 15) & ~15) + 16;
+   int *stage_all = smem_i + meta_ints;
+   for (int e = threadIdx.x; e < (int)(blockDim.x >> 5) * 32 * slot_ints; e += blockDim.x) stage_all[e] = 0;
+   // one mbarrier per warp: every lane arrives once per batch with the bytes of its own copies (expect_tx); the bulk copies
+   // complete on it (complete_tx), so the phase ends when all 32 lanes' bytes have landed
+   __shared__ __align__(8) unsigned long long s_bar[VNS_EVAL_THREADS / 32];
+   const unsigned bar = (unsigned)__cvta_generic_to_shared(&s_bar[threadIdx.x >> 5]);
+   if ((threadIdx.x & 31) == 0) asm volatile("mbarrier.init.shared::cta.b64 [%0], 32;" ::"r"(bar));
+   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // the zeroed slots and the barrier, before the async proxy writes
+   __syncthreads();
+   int *wstage = stage_all + (threadIdx.x >> 5) * 32 * slot_ints;
+   unsigned parity = 0;
+
+   constexpr int NG = 32 / G;
+   const int lane = threadIdx.x & 31, gl = lane % G, g = lane / G;
+   const double L = P.hd[HD_LEN];
+   const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+   const long long warp0 = (((long long)blockIdx.x * blockDim.x) >> 5) + (threadIdx.x >> 5);
+   unsigned long long best = ULLONG_MAX;
+
+   for (long long base = warp0 * 32; base < n; base += nwarps * 32) {
+      // ---- phase 1: lane-parallel fetch + decode ------------------------------------------------------------------
+      const long long slot = base + lane;
+      long long kidx = slot;
+      if (perm && slot < n) kidx = __ldg(perm + slot);
+      int4 cd = make_int4(-1, 0, 0, -1);
+      if (slot < n) {
+         if ((fmt & 3) == 2) {
+            const unsigned w = __ldg(reinterpret_cast<const unsigned *>(cands) + kidx);
+            cd.x = (int)(w & 7); cd.y = (int)((w >> 3) & 0x3fff); cd.z = (int)((w >> 17) & 0x3fff); cd.w = (w >> 31) ? cd.y : -1;
+         } else
+            cd = __ldg(reinterpret_cast<const int4 *>(cands) + kidx);
+      }
+      if (cd.w >= C) cd.x = -1;
+      const VecCode vcd = decode_cand_vec(vc, T, C, mp, lcl, [&](int l) { return s_cum[l + 1] - s_cum[l]; },
+                                          [&](int c) { return cinfo[c].y; }, [&](int l) { return s_pd[l]; }, cd.x, cd.y, cd.z);
+      long long p_rb = 0;
+      const int mA = vcd.mA, mB = vcd.mB;
+      const bool blk = vcd.ok && vcd.lb > vcd.la;
+      if (blk) {
+         if (vcd.lb == vcd.la + 1) {
+            const int2 cia = cinfo[lcl[vcd.la]], cib = cinfo[lcl[vcd.lb]];
+            p_rb = (long long)cia.x * I.N + (long long)cia.y * cib.x;
+         } else
+            p_rb = s_rowoff[vcd.la] + (long long)mA * (s_cum[vcd.lb] - s_cum[vcd.la + 2]);
+      }
+      // ---- memory phase: this lane's candidate -> this lane's slot ---------------------------------------------------
+      char *myslot = reinterpret_cast<char *>(wstage + lane * slot_ints);
+      unsigned shifts = 0;
+      {
+         const unsigned d0 = (unsigned)__cvta_generic_to_shared(myslot);
+         // 16-byte aligned enclosing range of [src, src + nints): start rounded down, length rounded up; the data keeps its
+         // offset inside the slot
+         const int *srcA = vc.vec + vcd.offA, *srcB = vc.vec + vcd.offB, *srcM = Dv + p_rb;
+         const unsigned shA = (unsigned)((size_t)srcA & 15), shB = (unsigned)((size_t)srcB & 15), shM = (unsigned)((size_t)srcM & 15);
+         const unsigned nbA = vcd.ok ? ((shA + (unsigned)mA * 4u + 15u) & ~15u) : 0u, nbB = vcd.ok ? ((shB + (unsigned)mB * 4u + 15u) & ~15u) : 0u;
+         const unsigned nbM = blk ? ((shM + (unsigned)(mA * mB) * 4u + 15u) & ~15u) : 0u;
+         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(nbA + nbB + nbM) : "memory");
+         if (nbA) asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                               ::"r"(d0), "l"(reinterpret_cast<const char *>(srcA) - shA), "r"(nbA), "r"(bar) : "memory");
+         if (nbB) asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                               ::"r"(d0 + vbytes), "l"(reinterpret_cast<const char *>(srcB) - shB), "r"(nbB), "r"(bar) : "memory");
+         if (nbM) asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                               ::"r"(d0 + 2 * vbytes), "l"(reinterpret_cast<const char *>(srcM) - shM), "r"(nbM), "r"(bar) : "memory");
+         shifts = shA | (shB << 4) | (shM << 8);
+      }
+      unsigned p_pack;
+      {
+         int tmax = blk ? mA : 1, nvmax = blk ? mB : 1, anyblk = blk;
+#pragma unroll
+         for (int sft = 1; sft < NG; sft <<= 1) {
+            tmax = max(tmax, __shfl_xor_sync(FULL, tmax, sft));
+            nvmax = max(nvmax, __shfl_xor_sync(FULL, nvmax, sft));
+            anyblk |= __shfl_xor_sync(FULL, anyblk, sft);
+         }
+         p_pack = (unsigned)mA | ((unsigned)mB << 6) | ((unsigned)tmax << 12) | ((unsigned)nvmax << 18) | ((unsigned)blk << 24) |
+                  ((unsigned)anyblk << 25);
+      }
+      {
+         unsigned done = 0;
+         while (!done)
+            asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+         parity ^= 1;
+      }
+      int myfin = INF;
+      // ---- phase 2: G iterations, group g evaluates candidate it * NG + g out of shared memory -----------------------------
+#pragma unroll 2
+      for (int it = 0; it < G; ++it) {
+         const int c = it * NG + g;
+         const unsigned pk = __shfl_sync(FULL, p_pack, c), sh = __shfl_sync(FULL, shifts, c);
+         const int mAc = pk & 63, mBc = (pk >> 6) & 63, tmaxAll = (pk >> 12) & 63, nvmax = (pk >> 18) & 63;
+         const bool blkc = (pk >> 24) & 1;
+         const char *cs = reinterpret_cast<const char *>(wstage + c * slot_ints);
+         const int *sA = reinterpret_cast<const int *>(cs + (sh & 15)), *sB = reinterpret_cast<const int *>(cs + vbytes + ((sh >> 4) & 15));
+         const int *sM = reinterpret_cast<const int *>(cs + 2 * vbytes + ((sh >> 8) & 15));
+         int vA[NR], vB[NR];
+#pragma unroll
+         for (int r = 0; r < NR; ++r) {
+            const int j = gl + r * G;
+            vA[r] = j < mAc ? sA[j] : INF;
+            vB[r] = j < mBc ? sB[j] : INF;
+         }
+         if ((pk >> 25) & 1) {                                 // warp-uniform: some group of this iteration has a block
+            const int nvalid = blkc ? mBc : 1;
+            int acc[NR];
+#pragma unroll
+            for (int rd = 0; rd < NR; ++rd) {
+               acc[rd] = INF;
+               if (rd == 0 || nvmax > rd * G) {                 // warp-uniform
+                  const int cb = min(gl + rd * G, nvalid - 1);
+#pragma unroll
+                  for (int rs = 0; rs < NR; ++rs) {
+                     if (rs == 0 || tmaxAll > rs * G) {         // warp-uniform
+                        const int tm = min(tmaxAll - rs * G, G);
+                        const int opnd = vA[rs];
+                        const int *prow = sM + cb + rs * G * nvalid;
+#pragma unroll
+                        for (int t0 = 0; t0 < G; t0 += 8) {
+                           if (t0 == 0 || t0 < tm) {            // warp-uniform
+                              int dd[8];
+#pragma unroll
+                              for (int t = 0; t < 8; ++t) dd[t] = blkc ? prow[nvalid * min(t0 + t, max(mAc - rs * G, 1) - 1)] : 0;
+#pragma unroll
+                              for (int t = 0; t < 8; ++t) acc[rd] = __viaddmin_s32(__shfl_sync(FULL, opnd, min(t0 + t, max(mAc - rs * G, 1) - 1), G), dd[t], acc[rd]);
+                           }
+                        }
+                     }
+                  }
+               }
+            }
+#pragma unroll
+            for (int r = 0; r < NR; ++r) vA[r] = blkc ? (gl + r * G < mBc ? acc[r] : INF) : vA[r];
+         }
+         int fin = INF;
+#pragma unroll
+         for (int r = 0; r < NR; ++r) fin = min(fin, gl + r * G < mBc ? vA[r] + vB[r] : INF);
+#pragma unroll
+         for (int sft = G / 2; sft > 0; sft >>= 1) fin = min(fin, __shfl_xor_sync(FULL, fin, sft, G));
+         const int got = __shfl_sync(FULL, fin, (lane % NG) * G);
+         myfin = (lane / NG == it) ? got : myfin;
+      }
+      __syncwarp();      // the slots are overwritten by the next batch: order this batch's reads before the async proxy's writes
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      // ---- phase 3: lane-parallel epilogue ----------------------------------------------------------------------------------
+      if (slot < n) {
+         double l, bound;
+         unsigned f = 0;
+         if (!vcd.ok) {
+            l = CUDART_NAN; bound = CUDART_NAN; f = VNSGPU_F_BAD;
+         } else {
+            l = (double)myfin;
+            bound = vcd.nolb ? l : P.minF[vcd.s0] + (double)vcd.lbsum + P.minB[vcd.sK];
+            double dR = 0.0, lm = l;
+            if (cd.x == VNSGPU_OP_ADD) {
+               dR = cd.w >= 0 ? __ldg(I.reward + cd.w) : 0.0;      // vns_sop_solver.cpp:581
+               lm = (L - 0.0) + (l - L);                           // :580,:583
+            } else if (cd.x == VNSGPU_OP_REPLACE) {
+               dR = cd.w >= 0 ? 0.0 + (__ldg(I.reward + cd.w) - __ldg(I.reward + lcl[cd.z + 1])) : 0.0;   // :784
+            }
+            if (lm <= budget) f |= VNSGPU_F_FEASIBLE;
+            if (lm <= budget && (dR > 0 || (L - lm) > VNS_MIN_CHANGE_EPS)) f |= VNSGPU_F_ACCEPT;          // :619,:805
+            if (bound > budget && !vcd.nolb) f |= VNSGPU_F_LB_SKIP;                                  // :539,...
+         }
+         if (len) len[kidx] = l;
+         if (leni) leni[kidx] = (fmt & 4) ? (vcd.ok ? (int)((unsigned)myfin | (f << 29)) : -1) : (vcd.ok ? myfin : INT_MIN);
+         if (lb) lb[kidx] = bound;
+         if (flags) flags[kidx] = (uint8_t)f;
+         if ((f & VNSGPU_F_ACCEPT) && !(skipflag && (f & VNSGPU_F_LB_SKIP)) && (unsigned long long)(kidx + idx0) < best)
+            best = (unsigned long long)(kidx + idx0);
+      }
+   }
+   if (d_first && best != ULLONG_MAX) atomicMin(d_first, best);
+}

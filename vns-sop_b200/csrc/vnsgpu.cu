@@ -28,6 +28,7 @@ vnsgpu_status vnsgpu_create(vnsgpu_ctx **out, int device)
    CK(cudaMemset(ctx->d_prof, 0, 4 * sizeof(long long)));
    CK(cudaMalloc(&ctx->d_info, 2 * sizeof(unsigned long long)));
    CK(cudaMalloc(&ctx->d_stop, sizeof(int)));
+   if (const char *e = getenv("VNSGPU_VEC_STAGED")) ctx->use_vec_staged = atoi(e) != 0;     // experiments / tests
    return VNSGPU_OK;
 }
 
@@ -64,6 +65,7 @@ void vnsgpu_destroy(vnsgpu_ctx *ctx)
    if (ctx->own) cudaStreamDestroy(ctx->own);
    if (ctx->hg_exec) cudaGraphExecDestroy(ctx->hg_exec);
    if (ctx->h_first) cudaFreeHost(ctx->h_first);
+   if (ctx->h_pick) cudaFreeHost(ctx->h_pick);
    delete ctx;
 }
 
