@@ -8,7 +8,7 @@ modes = sys.argv[2].split(",") if len(sys.argv) > 2 else ["c2-1", "c2-4", "v1"]
 sf, pb = load_problem(name)
 e = engine.Engine(0).load_problem(pb)
 for mode in modes:
-    e.set_chain_form(1 if mode == "v1" else 0)
+    e.set_chain_form(3 if mode == "c3" else (1 if mode == "v1" else 0))
     e.set_chain_blocks(int(mode.split("-")[1].rstrip("t")) if mode.startswith("c2-") else 1)
     e.set_chain_tree(1 if mode.endswith("t") and mode != "v1" else 0)
     p = e.path(); p.greedy_insertion(); rng = engine.seeded_rng(7)

@@ -127,21 +127,28 @@ def test_greedy_insertion(name, golden, eng_cache):
     assert p.getPathLength() == g["greedy"]["length"] and p.getReward() == g["greedy"]["reward"]
 
 
-CHAIN_MODES = ["smem-int", "smem-int-tree", "smem-int-grid3", "smem-int-grid8-tree", "smem-int-v1", "smem-double", "global"]
+CHAIN_MODES = ["smem-tab", "smem-tab-u16", "smem-int", "smem-int-tree", "smem-int-grid3", "smem-int-grid8-tree", "smem-int-v1", "smem-double", "global"]
 
 
 def _set_chain_mode(e, mode):
     """smem-int: second chain form (lower bound first), one thread block; -gridN: N cooperating thread blocks;
     -tree: with the product tree forced on (default: off below 96 clusters); -v1: first form; smem-double: first form
-    in IEEE double; global: global-memory chain"""
+    in IEEE double; global: global-memory chain; smem-tab: third form (the whole distance table in shared memory, as
+    int32 when that fits, else as uint16), -u16: its uint16 copy forced (instances without one take another form)"""
+    import os
     e.set_smem_chain(mode != "global")
     e.set_int_path(mode != "smem-double")
-    e.set_chain_form(1 if mode == "smem-int-v1" else 0)
+    e.set_chain_form(3 if mode.startswith("smem-tab") else (1 if mode == "smem-int-v1" else 0))
+    os.environ.pop("VNSGPU_CHAIN3_U16", None)
+    if mode == "smem-tab-u16":
+        os.environ["VNSGPU_CHAIN3_U16"] = "1"
     e.set_chain_blocks(int(mode.split("grid")[1].split("-")[0]) if "grid" in mode else 1)
     e.set_chain_tree(1 if "tree" in mode else (0 if mode.startswith("smem-int") else -1))
 
 
 def _reset_chain_mode(e):
+    import os
+    os.environ.pop("VNSGPU_CHAIN3_U16", None)
     e.set_smem_chain(True)
     e.set_int_path(True)
     e.set_chain_form(-1)
@@ -190,8 +197,8 @@ def test_full_vns_run_seed1_follows_reference_trajectory(name, mode, golden, eng
     counts, every improvement (reward, length) and the final tour equal the reference's results.log."""
     e, sf, pb = eng_cache(name)
     s = golden[name]["solve_seed1"]
-    if mode not in ("smem-int", "smem-int-tree", "smem-int-grid3") and name == "krob200":
-        pytest.skip("long run: the second chain form (1 and 3 thread blocks) covers krob200")
+    if mode not in ("smem-tab", "smem-int", "smem-int-tree", "smem-int-grid3") and name == "krob200":
+        pytest.skip("long run: the third and the second chain form (1 and 3 thread blocks) cover krob200")
     _set_chain_mode(e, mode)
     try:
         p = e.path()

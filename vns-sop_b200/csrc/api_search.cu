@@ -43,6 +43,7 @@ static vnsgpu_status launch_local_search(vnsgpu_ctx *ctx, int path, int kind, in
 {
    size_t smem = 0;
    int cis = 0;
+   if (c3_fits(ctx, &smem, &cis)) return c3_launch_ls(ctx, path, kind, num_changes, budget, skip, smem, cis);
    if (ctx->use_smem_chain && c2_fits(ctx, &smem, &cis)) return c2_launch_ls(ctx, path, kind, num_changes, budget, skip, smem, cis);
    if (vnsgpu_int_path_active(ctx) && chain_fits<int>(ctx, &smem))
       return launch_chain_v<int>(ctx, ctx->d_D32, path, kind, num_changes, budget, skip, smem);
@@ -200,9 +201,10 @@ vnsgpu_status vnsgpu_vns_run(vnsgpu_ctx *ctx, int path, const vnsgpu_vns_params 
    if (s) return s;
    size_t smem2 = 0;
    int cis = 0;
-   const bool c2 = ctx->use_smem_chain && c2_fits(ctx, &smem2, &cis);
+   const bool c3 = c3_fits(ctx, &smem2, &cis);
+   const bool c2 = !c3 && ctx->use_smem_chain && c2_fits(ctx, &smem2, &cis);
    int work = -1;
-   if (!c2) {
+   if (!c2 && !c3) {
       s = vnsgpu_path_create(ctx, &work);   // actualVNSGOPPath (vns_sop_solver.cpp:195); the second chain keeps it in shared memory
       if (s) return s;
    }
@@ -215,7 +217,9 @@ vnsgpu_status vnsgpu_vns_run(vnsgpu_ctx *ctx, int path, const vnsgpu_vns_params 
    prm.skip = p->lower_bound_skip; prm.greedy = p->greedy_initial; prm.budget = p->budget;
    prm.max_time_ms = p->max_time_ms; prm.max_improvements = cap;
    prm.target_reward = 0.0; prm.stop_flag = nullptr;
-   if (c2)
+   if (c3)
+      s = c3_launch_vns(ctx, path, prm, d_ir, d_il, d_it, smem2, cis);
+   else if (c2)
       s = c2_launch_vns(ctx, path, prm, d_ir, d_il, d_it, smem2, cis);
    else {
       size_t smem = 0;
@@ -260,7 +264,8 @@ vnsgpu_status vnsgpu_vns_run_batch(vnsgpu_ctx *ctx, int path, int nruns, const u
    if (nruns < 1) return fail(ctx, VNSGPU_E_RANGE, "nruns < 1");
    size_t smem = 0;
    int cis = 0;
-   const bool c2 = ctx->use_smem_chain && c2_fits(ctx, &smem, &cis);
+   const bool c3 = c3_fits(ctx, &smem, &cis);
+   const bool c2 = c3 || (ctx->use_smem_chain && c2_fits(ctx, &smem, &cis));   // c2: the slot layout both forms share
    const size_t extra = chain_smem(ctx) + sizeof(RngState) + 64;
    bool as_int = false;
    if (!c2) {
@@ -312,7 +317,8 @@ vnsgpu_status vnsgpu_vns_run_batch(vnsgpu_ctx *ctx, int path, int nruns, const u
          prm.stop_flag = ctx->d_stop;
       }
       if (!s) {
-         if (c2) s = c2_launch_multi(ctx, nruns, d_slots, prm, smem, cis);
+         if (c3) s = c3_launch_multi(ctx, nruns, d_slots, prm, smem, cis);
+         else if (c2) s = c2_launch_multi(ctx, nruns, d_slots, prm, smem, cis);
          else
             s = as_int ? launch_chain_multi_v<int>(ctx, ctx->d_D32, nruns, (VnsRunSlot *)d_slots, prm, smem + chain_smem(ctx))
                        : launch_chain_multi_v<double>(ctx, ctx->d_D, nruns, (VnsRunSlot *)d_slots, prm, smem + chain_smem(ctx));

@@ -1,0 +1,312 @@
+// Full-neighbourhood modes on top of the batched evaluation: every candidate of a neighbourhood is
+// evaluated by ONE vnsgpu_eval_batch_dev call (endpoint vectors + segment products on integer tables), a device
+// reduction picks the move, a one-block kernel applies it.
+//   * vnsgpu_greedy_batched: greedy_insertion (vns_sop_solver.cpp:1091-1155) - per round the (|VNS| - T) x (T + 1) grid
+//     of tryToAdd, strict minimum of (d - L) / reward among d <= budget, first grid index on ties (:1119).  Same tour as
+//     vnsgpu_greedy and as the reference (trajectory-exact: the reference's loop is already an enumeration).
+//   * vnsgpu_best_move / vnsgpu_apply_move / vnsgpu_best_improvement: the opt-in, NOT trajectory-exact local search -
+//     the whole insert (MOVE / ADD) or exchange (EXCHANGE / REPLACE) neighbourhood in the reference's index order
+//     (from-major), the best improving candidate instead of the first drawn one.
+#include "ctx.hpp"
+#include "path.cuh"
+#include "search.cuh"
+
+struct BestRec {            // device result of the reduction
+   long long idx;           // enumeration index of the chosen candidate, -1: none
+   double a, b;             // greedy: (d - L) / reward, d;  best-improvement: added reward, length after the move
+   int from, to;            // VNS-vector index that moves / target index it goes to
+   int kind, pad;
+};
+
+struct BestKey {
+   double a, b;
+   long long idx;
+};
+
+// total orders (smaller = better).  MODE 0: a ascending, first index.  MODE 1: a (added reward) descending, b (length)
+// ascending, first index
+template <int MODE> __device__ __forceinline__ bool key_better(const BestKey &x, const BestKey &y)
+{
+   if (x.idx < 0) return false;
+   if (y.idx < 0) return true;
+   if (MODE == 0) return x.a < y.a || (x.a == y.a && x.idx < y.idx);
+   return x.a > y.a || (x.a == y.a && (x.b < y.b || (x.b == y.b && x.idx < y.idx)));
+}
+
+// ---- enumeration of a neighbourhood (device descriptors, index order = the reference's loop order) ----------------------
+// kind 0: greedy grid  g = (av - T) * (T + 1) + pos  -> tryToAdd(VNS[av], pos)                      (:1109-1127)
+// kind 1: insert       k = from * (T + 1) + to        -> tryToMove(from, to) / tryToAdd(VNS[from], to)    (:507-519 pairs)
+// kind 2: exchange     k = from * T + to              -> tryToExchange(from, to) / tryToReplace(VNS[from], to)  (:723-730)
+// pairs the reference redraws (|from - to| <= gap) get op = -1: the evaluation flags them VNSGPU_F_BAD, never chosen
+static __global__ void __launch_bounds__(256) k_nbh_cands(PathDev P, int kind, long long n, vnsgpu_cand *__restrict__ out)
+{
+   const int T = P.hdr[HDR_T];
+   const int ncol = kind == 2 ? T : T + 1;
+   for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (long long)gridDim.x * blockDim.x) {
+      const int row = (int)(k / ncol), to = (int)(k - (long long)row * ncol);
+      vnsgpu_cand c;
+      if (kind == 0) {
+         const int cl = P.vns[T + row];
+         c.op = VNSGPU_OP_ADD; c.a = cl; c.b = to; c.gain_cluster = cl;
+      } else {
+         const int from = row, gap = kind == 1 ? 1 : 2;
+         if (abs(from - to) <= gap) { c.op = -1; c.a = 0; c.b = 0; c.gain_cluster = -1; }
+         else if (from < T) { c.op = kind == 1 ? VNSGPU_OP_MOVE : VNSGPU_OP_EXCHANGE; c.a = from; c.b = to; c.gain_cluster = -1; }
+         else {
+            const int cl = P.vns[from];
+            c.op = kind == 1 ? VNSGPU_OP_ADD : VNSGPU_OP_REPLACE; c.a = cl; c.b = to; c.gain_cluster = cl;
+         }
+      }
+      out[k] = c;
+   }
+}
+
+// ---- arg-best over the evaluated neighbourhood ---------------------------------------------------------------------------
+// partial: one BestKey per block; the last block to finish (ticket) reduces the partials and writes *rec
+template <int MODE>
+static __global__ void __launch_bounds__(256) k_best_reduce(InstDev I, PathDev P, int kind, long long n, const vnsgpu_cand *__restrict__ cands,
+                                                            const double *__restrict__ len, const uint8_t *__restrict__ flags, double budget,
+                                                            BestKey *partial, unsigned *ticket, BestRec *rec)
+{
+   __shared__ BestKey sh[256];
+   __shared__ bool last;
+   const int T = P.hdr[HDR_T];
+   const double L = P.hd[HD_LEN];
+   BestKey best{0.0, 0.0, -1};
+   for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (long long)gridDim.x * blockDim.x) {
+      const double d = len[k];
+      BestKey cur{0.0, d, k};
+      bool ok;
+      if (MODE == 0) {
+         const vnsgpu_cand c = cands[k];
+         cur.a = (d - L) / __ldg(I.reward + c.gain_cluster);                   // :1116-1117
+         ok = d <= budget;                                                    // :1119 (NaN fails)
+      } else {
+         const uint8_t f = flags[k];
+         ok = (f & VNSGPU_F_FEASIBLE) && !(f & VNSGPU_F_BAD);
+         if (ok) {
+            const vnsgpu_cand c = cands[k];
+            double dR = 0.0;
+            if (c.op == VNSGPU_OP_ADD) dR = __ldg(I.reward + c.gain_cluster);                                             // :581
+            else if (c.op == VNSGPU_OP_REPLACE) dR = 0.0 + (__ldg(I.reward + c.gain_cluster) - __ldg(I.reward + P.tg[c.b]));   // :784
+            cur.a = dR;
+            // improving in the lexicographic objective (reward, then length): the reference's test (:619,:805-806) also
+            // takes a shorter tour with LESS reward; a best-improvement descent must not
+            ok = dR > 0 || (dR == 0 && (L - d) > VNS_MIN_CHANGE_EPS);
+         }
+      }
+      if (ok && key_better<MODE>(cur, best)) best = cur;
+   }
+   sh[threadIdx.x] = best;
+   __syncthreads();
+   for (int s = 128; s > 0; s >>= 1) {
+      if ((int)threadIdx.x < s && key_better<MODE>(sh[threadIdx.x + s], sh[threadIdx.x])) sh[threadIdx.x] = sh[threadIdx.x + s];
+      __syncthreads();
+   }
+   if (threadIdx.x == 0) {
+      partial[blockIdx.x] = sh[0];
+      __threadfence();
+      last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+   }
+   __syncthreads();
+   if (!last) return;
+   __threadfence();
+   best = BestKey{0.0, 0.0, -1};
+   for (int b = threadIdx.x; b < (int)gridDim.x; b += blockDim.x) {
+      const BestKey q = *(volatile BestKey *)(partial + b);
+      if (key_better<MODE>(q, best)) best = q;
+   }
+   sh[threadIdx.x] = best;
+   __syncthreads();
+   for (int s = 128; s > 0; s >>= 1) {
+      if ((int)threadIdx.x < s && key_better<MODE>(sh[threadIdx.x + s], sh[threadIdx.x])) sh[threadIdx.x] = sh[threadIdx.x + s];
+      __syncthreads();
+   }
+   if (threadIdx.x == 0) {
+      BestRec r;
+      r.idx = sh[0].idx; r.a = sh[0].a; r.b = sh[0].b; r.kind = kind; r.pad = 0; r.from = r.to = -1;
+      if (r.idx >= 0) {
+         const int ncol = kind == 2 ? T : T + 1;
+         const int row = (int)(r.idx / ncol);
+         r.to = (int)(r.idx - (long long)row * ncol);
+         r.from = kind == 0 ? T + row : row;
+      }
+      *rec = r;
+      *ticket = 0;
+   }
+}
+
+// ---- apply the chosen move (one block): the accept branches of insertRandom (:621-646) / exchangeRandom (:807-832), or
+//      greedy_insertion's addPoint + VNS splice (:1133-1146) - all three are "VNS[from] goes to index `to`" -----------------
+static __global__ void __launch_bounds__(VNS_CHAIN_THREADS) k_apply_move(InstDev I, PathDev P, const BestRec *rec, int from_arg, int to_arg, int kind_arg)
+{
+   int from = from_arg, to = to_arg, kind = kind_arg;
+   if (rec) {
+      if (rec->idx < 0) return;
+      from = rec->from; to = rec->to; kind = rec->kind;
+   }
+   int T = P.hdr[HDR_T];
+   const int nvns = P.hdr[HDR_NVNS];
+   __syncthreads();
+   if (kind == 2) cta_apply_exchange(I, P, T, from, to);
+   else T = cta_apply_insert(I, P, T, nvns, from, to);
+   __syncthreads();
+   if (threadIdx.x == 0) { P.hdr[HDR_T] = T; P.hd[HD_REWARD] = path_reward(I, P.tg, T); }
+}
+
+// ---- host side --------------------------------------------------------------------------------------------------------------
+struct BestBufs {
+   vnsgpu_cand *cands;
+   double *len;
+   uint8_t *flags;
+   BestKey *partial;
+   unsigned *ticket;
+   BestRec *rec;
+};
+
+static vnsgpu_status best_bufs(vnsgpu_ctx *ctx, long long n, BestBufs *b)
+{
+   const size_t nb = 2048;
+   const size_t o_len = al16(sizeof(vnsgpu_cand) * (size_t)n), o_fl = o_len + al16(sizeof(double) * (size_t)n),
+                o_part = o_fl + al16((size_t)n), o_tick = o_part + al16(sizeof(BestKey) * nb), o_rec = o_tick + 16,
+                total = o_rec + al16(sizeof(BestRec));
+   if (total > ctx->best_bytes) {
+      if (ctx->d_best) { CK(cudaStreamSynchronize(ctx->stream)); CK(cudaFree(ctx->d_best)); }
+      ctx->d_best = nullptr; ctx->best_bytes = 0;
+      const size_t cap = total + total / 4;
+      CK(cudaMalloc(&ctx->d_best, cap));
+      ctx->best_bytes = cap;
+   }
+   // the offsets depend on n: the ticket must be zero whatever the previous call's layout was
+   char *p = (char *)ctx->d_best;
+   b->cands = (vnsgpu_cand *)p; b->len = (double *)(p + o_len); b->flags = (uint8_t *)(p + o_fl);
+   b->partial = (BestKey *)(p + o_part); b->ticket = (unsigned *)(p + o_tick); b->rec = (BestRec *)(p + o_rec);
+   CK(cudaMemsetAsync(b->ticket, 0, 16, ctx->stream));
+   return VNSGPU_OK;
+}
+
+// evaluate neighbourhood `kind` (0 greedy grid, 1 insert, 2 exchange) of the path's current state and reduce it; the
+// record stays on the device (b->rec) and is copied to *out
+static vnsgpu_status best_step(vnsgpu_ctx *ctx, int path, int kind, double budget, BestBufs *b, BestRec *out, long long *n_out)
+{
+   PathHdr h;
+   vnsgpu_status s = read_hdr(ctx, path, &h);
+   if (s) return s;
+   const int T = h.hdr[HDR_T], nvns = h.hdr[HDR_NVNS];
+   long long n = 0;
+   if (kind == 0) n = (long long)(nvns - T) * (T + 1);
+   else if (kind == 1) n = nvns >= 3 ? (long long)nvns * (T + 1) : 0;                 // guard :498
+   else n = (nvns >= 4 && T > 0) ? (long long)nvns * T : 0;                          // guard :711
+   if (n_out) *n_out = n;
+   out->idx = -1; out->from = out->to = -1; out->a = out->b = 0; out->kind = kind;
+   if (n <= 0) return VNSGPU_OK;
+   s = best_bufs(ctx, n, b);
+   if (s) return s;
+   const PathDev P = ctx->paths[path].d;
+   const int grid = (int)std::min<long long>((n + 255) / 256, 2048);
+   k_nbh_cands<<<grid, 256, 0, ctx->stream>>>(P, kind, n, b->cands);
+   LAUNCHED(ctx);
+   s = vnsgpu_eval_batch_dev(ctx, path, n, b->cands, budget, 0, b->len, nullptr, kind == 0 ? nullptr : b->flags, nullptr, ctx->stream);
+   if (s) return s;
+   if (kind == 0)
+      k_best_reduce<0><<<grid, 256, 0, ctx->stream>>>(ctx->I, P, kind, n, b->cands, b->len, b->flags, budget, b->partial, b->ticket, b->rec);
+   else
+      k_best_reduce<1><<<grid, 256, 0, ctx->stream>>>(ctx->I, P, kind, n, b->cands, b->len, b->flags, budget, b->partial, b->ticket, b->rec);
+   LAUNCHED(ctx);
+   CK(cudaMemcpyAsync(out, b->rec, sizeof(BestRec), cudaMemcpyDeviceToHost, ctx->stream));
+   CK(cudaStreamSynchronize(ctx->stream));
+   return VNSGPU_OK;
+}
+
+static vnsgpu_status apply_rec(vnsgpu_ctx *ctx, int path, const BestRec *d_rec, int from, int to, int kind)
+{
+   k_apply_move<<<1, VNS_CHAIN_THREADS, 0, ctx->stream>>>(ctx->I, ctx->paths[path].d, d_rec, from, to, kind);
+   LAUNCHED(ctx);
+   ctx->paths[path].hdr_ok = false;
+   return VNSGPU_OK;
+}
+
+extern "C" {
+
+vnsgpu_status vnsgpu_greedy_batched(vnsgpu_ctx *ctx, int path, double budget, int *rounds, int64_t *evals)
+{
+   CK(cudaSetDevice(ctx->device));
+   if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
+   int nr = 0;
+   int64_t ne = 0;
+   for (;;) {
+      BestBufs b;
+      BestRec r;
+      long long n = 0;
+      vnsgpu_status s = best_step(ctx, path, 0, budget, &b, &r, &n);
+      if (s) return s;
+      ne += n;
+      if (r.idx < 0) break;                                              // :1129
+      s = apply_rec(ctx, path, b.rec, 0, 0, 0);
+      if (s) return s;
+      ++nr;
+   }
+   if (rounds) *rounds = nr;
+   if (evals) *evals = ne;
+   return check_path_err(ctx, path);
+}
+
+vnsgpu_status vnsgpu_best_move(vnsgpu_ctx *ctx, int path, int kind, double budget, vnsgpu_best_move_t *out)
+{
+   CK(cudaSetDevice(ctx->device));
+   if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
+   if (kind != 1 && kind != 2) return fail(ctx, VNSGPU_E_RANGE, "kind must be 1 (insert) or 2 (exchange)");
+   BestBufs b;
+   BestRec r;
+   long long n = 0;
+   vnsgpu_status s = best_step(ctx, path, kind, budget, &b, &r, &n);
+   if (s) return s;
+   if (out) {
+      out->index = r.idx; out->from = r.from; out->to = r.to; out->kind = kind;
+      out->added_reward = r.a; out->length = r.b; out->n_candidates = n;
+   }
+   return VNSGPU_OK;
+}
+
+vnsgpu_status vnsgpu_apply_move(vnsgpu_ctx *ctx, int path, int kind, int from, int to)
+{
+   CK(cudaSetDevice(ctx->device));
+   if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
+   if (kind != 1 && kind != 2) return fail(ctx, VNSGPU_E_RANGE, "kind must be 1 (insert) or 2 (exchange)");
+   PathHdr h;
+   vnsgpu_status s = read_hdr(ctx, path, &h);
+   if (s) return s;
+   const int T = h.hdr[HDR_T], nvns = h.hdr[HDR_NVNS], gap = kind == 1 ? 1 : 2, tohi = kind == 1 ? T : T - 1;
+   if (from < 0 || from >= nvns || to < 0 || to > tohi || std::abs(from - to) <= gap) return fail(ctx, VNSGPU_E_RANGE, "move outside the neighbourhood");
+   s = apply_rec(ctx, path, nullptr, from, to, kind);
+   if (s) return s;
+   return check_path_err(ctx, path);
+}
+
+vnsgpu_status vnsgpu_best_improvement(vnsgpu_ctx *ctx, int path, double budget, int max_steps, int *steps, int64_t *evals)
+{
+   CK(cudaSetDevice(ctx->device));
+   if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
+   int ns = 0;
+   int64_t ne = 0;
+   int kind = 1, failed = 0;
+   while (failed < 2 && (max_steps <= 0 || ns < max_steps)) {
+      BestBufs b;
+      BestRec r;
+      long long n = 0;
+      vnsgpu_status s = best_step(ctx, path, kind, budget, &b, &r, &n);
+      if (s) return s;
+      ne += n;
+      if (r.idx < 0) { ++failed; kind = 3 - kind; continue; }
+      s = apply_rec(ctx, path, b.rec, 0, 0, 0);
+      if (s) return s;
+      ++ns;
+      failed = 0;
+      kind = 1;                       // variable neighbourhood descent: back to the first neighbourhood after every move
+   }
+   if (steps) *steps = ns;
+   if (evals) *evals = ne;
+   return check_path_err(ctx, path);
+}
+
+} // extern "C"

@@ -28,7 +28,7 @@ bool c2_fits(const vnsgpu_ctx *ctx, size_t *smem, int *place)
    // automatic choice: below ~96 clusters a round is a handful of short chains and the first form's leaner round wins
    // (seeded krob200 solve 4.45 s against 4.89 s); from there on the lower-bound filter, the large window and the product
    // tree do (vm1084: 458 s -> 35.6 s)
-   const bool want = ctx->chain_form == 0 || (ctx->chain_form < 0 && ctx->I.C >= 96);
+   const bool want = ctx->chain_form == 0 || ((ctx->chain_form < 0 || ctx->chain_form == 3) && ctx->I.C >= 96);
    if (!want || !vnsgpu_int_path_active(ctx) || ctx->I.mp > 32 || !group_kernel_ok(ctx)) return false;
    // static shared memory of the kernels (control block, slot, RNG, the few words of search.cuh's helpers) + margin
    const size_t fixed = sizeof(C2Ctl) + sizeof(C2Slot) + sizeof(RngState) + sizeof(C2Tree) + 2048;
@@ -60,19 +60,29 @@ static bool c2_tree_wanted(const vnsgpu_ctx *ctx)
    return ctx->I.C >= 96;
 }
 
+// int32 cluster-pair minima + {first sample, size} per cluster on the device (shared with the third form, chain3.cu)
+vnsgpu_status c2_ensure_tables(vnsgpu_ctx *ctx)
+{
+   const InstDev &I = ctx->I;
+   if (ctx->d_dmin32) return VNSGPU_OK;
+   CK(cudaMalloc(&ctx->d_dmin32, sizeof(int) * (size_t)I.C * I.C));
+   k_dmin_to_int<<<(I.C * I.C + 255) / 256, 256, 0, ctx->stream>>>(I.C * I.C, ctx->d_dmin, ctx->d_dmin32);
+   LAUNCHED(ctx);
+   std::vector<int2> ci(I.C);
+   for (int c = 0; c < I.C; ++c) ci[c] = make_int2(ctx->off[c], ctx->m[c]);
+   CK(cudaMalloc(&ctx->d_cinfo, sizeof(int2) * I.C));
+   CK(cudaMemcpyAsync(ctx->d_cinfo, ci.data(), sizeof(int2) * I.C, cudaMemcpyHostToDevice, ctx->stream));
+   CK(cudaStreamSynchronize(ctx->stream));
+   return VNSGPU_OK;
+}
+
 static vnsgpu_status c2_prepare(vnsgpu_ctx *ctx, int ncta, C2Env *E, int place, int nblocks)
 {
    const int cinfo_in_smem = place & 1;
    const InstDev &I = ctx->I;
-   if (!ctx->d_dmin32) {
-      CK(cudaMalloc(&ctx->d_dmin32, sizeof(int) * (size_t)I.C * I.C));
-      k_dmin_to_int<<<(I.C * I.C + 255) / 256, 256, 0, ctx->stream>>>(I.C * I.C, ctx->d_dmin, ctx->d_dmin32);
-      LAUNCHED(ctx);
-      std::vector<int2> ci(I.C);
-      for (int c = 0; c < I.C; ++c) ci[c] = make_int2(ctx->off[c], ctx->m[c]);
-      CK(cudaMalloc(&ctx->d_cinfo, sizeof(int2) * I.C));
-      CK(cudaMemcpyAsync(ctx->d_cinfo, ci.data(), sizeof(int2) * I.C, cudaMemcpyHostToDevice, ctx->stream));
-      CK(cudaStreamSynchronize(ctx->stream));
+   {
+      vnsgpu_status ts = c2_ensure_tables(ctx);
+      if (ts) return ts;
    }
    if (ncta > 1 && ctx->c2_ncta < ncta) {
       if (ctx->d_c2grid) { CK(cudaStreamSynchronize(ctx->stream)); CK(cudaFree(ctx->d_c2grid)); }

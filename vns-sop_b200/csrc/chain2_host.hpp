@@ -2,6 +2,7 @@
 #pragma once
 #include "ctx.hpp"
 
+vnsgpu_status c2_ensure_tables(vnsgpu_ctx *ctx);
 bool c2_fits(const vnsgpu_ctx *ctx, size_t *smem, int *place);
 int c2_blocks(const vnsgpu_ctx *ctx);
 vnsgpu_status c2_launch_ls(vnsgpu_ctx *ctx, int path, int kind, int num_changes, double budget, int skip, size_t smem, int place);
@@ -11,3 +12,10 @@ vnsgpu_status c2_launch_multi(vnsgpu_ctx *ctx, int nruns, void *d_slots, const V
 size_t c2_run_slot_bytes();
 void c2_run_slot_fill(void *slot, const PathDev &tour, const RngState &rng);
 const VnsResultDev &c2_run_slot_result(const void *slot);
+
+// third form (chain3.cu): the whole distance table in shared memory.  u16: the uint16 copy is the one that fits
+bool c3_fits(const vnsgpu_ctx *ctx, size_t *smem, int *u16);
+vnsgpu_status c3_launch_ls(vnsgpu_ctx *ctx, int path, int kind, int num_changes, double budget, int skip, size_t smem, int u16);
+vnsgpu_status c3_launch_vns(vnsgpu_ctx *ctx, int path, const VnsParamsDev &prm, double *d_ir, double *d_il, double *d_it, size_t smem,
+                            int u16);
+vnsgpu_status c3_launch_multi(vnsgpu_ctx *ctx, int nruns, void *d_slots, const VnsParamsDev &prm, size_t smem, int u16);

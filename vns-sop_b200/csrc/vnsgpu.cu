@@ -93,7 +93,7 @@ vnsgpu_status vnsgpu_set_smem_chain(vnsgpu_ctx *ctx, int enable)
 
 vnsgpu_status vnsgpu_set_chain_form(vnsgpu_ctx *ctx, int form)
 {
-   ctx->chain_form = form < 0 ? -1 : (form != 0);
+   ctx->chain_form = form < 0 ? -1 : (form == 3 ? 3 : (form == 2 ? 0 : (form != 0)));
    return VNSGPU_OK;
 }
 
