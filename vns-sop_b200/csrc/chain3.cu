@@ -13,7 +13,7 @@ bool c3_fits(const vnsgpu_ctx *ctx, size_t *smem, int *u16)
 {
    const bool want = ctx->chain_form == 3 || ctx->chain_form < 0;
    if (!want || !ctx->use_smem_chain || !vnsgpu_int_path_active(ctx) || ctx->I.mp > 32) return false;
-   if ((long long)ctx->I.N * ctx->I.N >= (1ll << 20)) return false;      // block offsets are packed into 20 bits
+   if ((long long)ctx->I.N * ctx->I.N >= (1ll << 19)) return false;      // block offsets are packed into 19 bits
    // static shared memory of the kernels (control block, generator state, the few words of search.cuh's helpers) + margin
    const size_t fixed = sizeof(C3Ctl) + sizeof(RngState) + 2048;
    const size_t greedy = sizeof(double) * 2 * ctx->I.mp * C3_WARPS;       // the greedy start borrows the table's place

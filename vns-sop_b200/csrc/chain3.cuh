@@ -11,7 +11,7 @@
 //     in a round at all;
 //   * every warp derives the round's window by itself - draw pairs from a shared ring of raw rand() values, validity,
 //     the O(1) lower bound, the survivor masks (ballots) - so there is no cross-warp compaction, no thread-0 loop and
-//     no barrier before the evaluation; survivor number (warp, group) is found with __fns on the masks;
+//     no barrier before the evaluation; every warp writes the same survivor list (pair indices in draw order) for its groups to pick from;
 //   * the round's bookkeeping (proposals consumed, generator position, T, L, window size) is replicated in registers
 //     of every thread; shared memory only carries the first accepted pair (one atomicMin cell per pass, four cells in
 //     rotation: no reset barrier);
@@ -25,7 +25,7 @@
 #include "eval.cuh"
 #include "search.cuh"
 
-#define C3_THREADS 256
+#define C3_THREADS 512
 #define C3_WARPS (C3_THREADS / 32)
 #define C3_RING 1024                       // raw generator outputs kept (power of two)
 #define C3_MAXCH 4                         // chunks of 32 draw pairs per round
@@ -38,6 +38,7 @@ struct C3Ctl {
    int bad;                  // a proposal decoded to no chain (impossible by construction)
    int ema;                  // running proposals per accept (window sizing)
    int first[4];             // first accepted pair of a pass (atomicMin), cells in rotation
+   unsigned balv[C3_MAXCH], bals[C3_MAXCH];   // valid / surviving pairs of the round's window, per chunk (every warp writes the same)
    LsStats st;
    long long prof[4];
 };
@@ -50,19 +51,27 @@ template <typename TT> struct C3Sm {
    int *F, *Brev;            // R x mpp
    int *minF, *minBrev, *pd; // R
    int *lcl, *vns, *seg;     // 2R, 2R, alias of Brev (shake scratch)
+   unsigned *ew;             // edge words of the path's layers (re-scans), R + 2
+   int *surv;                // pair index of survivor k of the round's window (every warp writes the same values)
    unsigned *ring;           // C3_RING
+   unsigned *gw;             // per evaluation group: the block words of its chain, gwcap each
+   int gwcap;
    int N, C, mp;
 };
 
 // dynamic shared memory: table | dmin | reward | cinfo | F Brev minF minBrev pd lcl vns | ring
-__host__ __device__ inline size_t c3_tab_bytes(int N, int esz) { return ((size_t)N * N * esz + 15) & ~(size_t)15; }
+// the table is followed by 32 * mp + 32 zero entries: the row loops read whole groups of 4 / 8 / 16 / 32 rows (or row
+// entries) without clamping; rows beyond a block pair an INF sample with whatever follows the block (table entries or
+// this padding: all in [0, 2^29))
+__host__ __device__ inline size_t c3_tab_bytes(int N, int mp, int esz) { return (((size_t)N * N + 32 * (size_t)mp + 32) * esz + 15) & ~(size_t)15; }
 __host__ __device__ inline size_t c3_smem_bytes(int C, int N, int mp, int esz)
 {
    const size_t R = C + 3, mpp = mp < 2 ? 2 : mp;
-   size_t b = c3_tab_bytes(N, esz);
+   size_t b = c3_tab_bytes(N, mp, esz);
    b += ((size_t)C * C * sizeof(int) + 7) & ~(size_t)7;
    b += (size_t)C * sizeof(double) + (size_t)C * sizeof(int2);
-   b += sizeof(int) * (2 * R * mpp + 7 * R) + sizeof(unsigned) * C3_RING;
+   b += sizeof(int) * (2 * R * mpp + 8 * R + 8 + 32 * C3_MAXCH) + sizeof(unsigned) * C3_RING;
+   b += sizeof(unsigned) * (size_t)(C3_THREADS / (mp <= 8 ? 8 : (mp <= 16 ? 16 : 32))) * (R + 5);   // block words of every group's chain
    return b + 16;
 }
 
@@ -72,7 +81,7 @@ template <typename TT> static __device__ __forceinline__ C3Sm<TT> c3_carve(unsig
    C3Sm<TT> s;
    s.N = I.N; s.C = I.C; s.mp = I.mp;
    s.tab = reinterpret_cast<const TT *>(base);
-   base += c3_tab_bytes(I.N, sizeof(TT));
+   base += c3_tab_bytes(I.N, I.mp, sizeof(TT));
    s.dmin = reinterpret_cast<const int *>(base);
    base += ((size_t)I.C * I.C * sizeof(int) + 7) & ~(size_t)7;
    s.reward = reinterpret_cast<const double *>(base);
@@ -87,7 +96,11 @@ template <typename TT> static __device__ __forceinline__ C3Sm<TT> c3_carve(unsig
    s.pd = p; p += R;
    s.lcl = p; p += 2 * R;
    s.vns = p; p += 2 * R;
+   s.surv = p; p += 32 * C3_MAXCH;
+   s.ew = reinterpret_cast<unsigned *>(p) + 2; p += R + 8;      // indices -2 .. R + 5
    s.ring = reinterpret_cast<unsigned *>(p);
+   s.gw = s.ring + C3_RING;
+   s.gwcap = (int)R + 5;
    s.seg = s.Brev;
    return s;
 }
@@ -104,10 +117,15 @@ template <typename TT> static __device__ void c3_load_tables(const C3Env &E, con
 {
    const InstDev &I = E.I;
    {  // table: 16-byte words (both copies are allocated with slack behind the last entry)
-      const size_t n16 = c3_tab_bytes(I.N, sizeof(TT)) / 16;
+      const size_t n16 = ((size_t)I.N * I.N * sizeof(TT) + 15) / 16, all16 = c3_tab_bytes(I.N, I.mp, sizeof(TT)) / 16;
       const int4 *src = reinterpret_cast<const int4 *>(E.tab_g);
       int4 *dst = reinterpret_cast<int4 *>(const_cast<TT *>(s.tab));
       for (size_t k = threadIdx.x; k < n16; k += blockDim.x) dst[k] = __ldg(src + k);
+      for (size_t k = n16 + threadIdx.x; k < all16; k += blockDim.x) dst[k] = make_int4(0, 0, 0, 0);
+      __syncthreads();
+      // the last 16-byte word of the copy may carry bytes from behind the table: make them zeros as well
+      TT *tw = const_cast<TT *>(s.tab);
+      for (size_t k = (size_t)I.N * I.N + threadIdx.x; k < n16 * (16 / sizeof(TT)); k += blockDim.x) tw[k] = 0;
    }
    int *dm = const_cast<int *>(s.dmin);
    for (int k = threadIdx.x; k < I.C * I.C; k += blockDim.x) dm[k] = __ldg(E.dmin_g + k);
@@ -117,120 +135,222 @@ template <typename TT> static __device__ void c3_load_tables(const C3Env &E, con
    __syncthreads();
 }
 
+// ---- min-plus rows, unclamped ------------------------------------------------------------------------------------------------
+// acc = min_t (v[t] + p[t * stride]) over rows 0 .. tmax-1 (tmax warp-uniform, rounded up to 4 or a multiple of 8); v[t]
+// arrives by shuffle (width G); rows beyond the block meet an INF sample.  Per row: LDS, SHFL, VIADDMNMX - no clamp.
+// Kept as LOOPS on purpose: one warp executes every instruction of a round once, so straight-line code runs at the
+// speed of instruction fetch (L0 instruction cache ~6 KB, L1.5 32 KB); the first, fully unrolled version of these
+// kernels took 500 cycles per DP layer.
+template <typename TT, int G>
+static __device__ __forceinline__ int c3_block(const TT *p, int stride, int v, int tmax)
+{
+   constexpr unsigned FULL = 0xffffffffu;
+   int a0 = C3_INF, a1 = C3_INF;
+   if (tmax <= 4) {
+      const int d0 = (int)p[0], d1 = (int)p[stride], d2 = (int)p[2 * stride], d3 = (int)p[3 * stride];
+      const int x0 = __shfl_sync(FULL, v, 0, G), x1 = __shfl_sync(FULL, v, 1, G), x2 = __shfl_sync(FULL, v, 2, G), x3 = __shfl_sync(FULL, v, 3, G);
+      a0 = __viaddmin_s32(x0, d0, a0); a1 = __viaddmin_s32(x1, d1, a1);
+      a0 = __viaddmin_s32(x2, d2, a0); a1 = __viaddmin_s32(x3, d3, a1);
+   } else {
+#pragma unroll 1
+      for (int t0 = 0; t0 < tmax; t0 += 8) {
+         int d[8], x[8];
+#pragma unroll
+         for (int t = 0; t < 8; ++t) d[t] = (int)p[t * stride];
+#pragma unroll
+         for (int t = 0; t < 8; ++t) x[t] = __shfl_sync(FULL, v, t0 + t, G);
+#pragma unroll
+         for (int t = 0; t < 8; t += 2) { a0 = __viaddmin_s32(x[t], d[t], a0); a1 = __viaddmin_s32(x[t + 1], d[t + 1], a1); }
+         p += 8 * stride;
+      }
+   }
+   return min(a0, a1);
+}
+
+// edge (l-1 -> l) of the path as one word: block offset | rows << 20 | columns << 26
+template <typename TT> static __device__ __forceinline__ unsigned c3_edge_word(const C3Sm<TT> &s, int ca, int cb)
+{
+   const int2 cia = s.cinfo[ca], cib = s.cinfo[cb];
+   return (unsigned)(cia.x * s.N + cia.y * cib.x) | ((unsigned)cia.y << 20) | ((unsigned)cib.y << 26);
+}
+
 // ---- DP layers on the shared-memory state, one warp (lane = sample; mp <= 32) -------------------------------------------
 // F[l] = F[l-1] (x) D(c_{l-1}, c_l)   vns_sop_path.cpp:1353-1373 / 1426-1448 / 1488-1511
 template <typename TT> static __device__ __forceinline__ void c3_fwd_layer(const C3Sm<TT> &s, int l, int lane)
 {
    constexpr unsigned FULL = 0xffffffffu;
    const int mp = s.mp;
-   const int2 cia = s.cinfo[s.lcl[l - 1]], cib = s.cinfo[s.lcl[l]];
-   const int v = lane < cia.y ? s.F[(l - 1) * mp + lane] : C3_INF;
-   const TT *blk = s.tab + (cia.x * s.N + cia.y * cib.x) + min(lane, cib.y - 1);
-   int acc = C3_INF;
-   for (int i = 0; i < cia.y; ++i) acc = __viaddmin_s32(__shfl_sync(FULL, v, i), (int)blk[i * cib.y], acc);
-   acc = lane < cib.y ? acc : C3_INF;
-   if (lane < cib.y) s.F[l * mp + lane] = acc;
+   const unsigned w = c3_edge_word(s, s.lcl[l - 1], s.lcl[l]);
+   const int ma = (w >> 20) & 63, mb = w >> 26;
+   const int v = lane < ma ? s.F[(l - 1) * mp + lane] : C3_INF;
+   int acc = c3_block<TT, 32>(s.tab + (w & 0xfffffu) + min(lane, mb - 1), mb, v, ma);
+   acc = lane < mb ? acc : C3_INF;
+   if (lane < mb) s.F[l * mp + lane] = acc;
    const int mn = __reduce_min_sync(FULL, acc);
    if (lane == 0) s.minF[l] = mn;
    __syncwarp();
 }
 
-// forward layers [lf, S] (lf >= 1); the first eight rows of the NEXT layer's block are loaded while the current layer
-// is reduced; per-layer minima in the same pass
+// ---- re-scans: one warp, one dependent chain --------------------------------------------------------------------------------
+// A layer is SHFL (27 cycles) -> VIADDMNMX x 4 (5 each) -> min -> select -> next layer's SHFL: ~65 cycles when nothing else
+// sits on the chain (scripts/micro/op_latency.cu).  One warp issues in order, so every load, shuffle or reduction whose
+// result is consumed right behind it stalls the whole chain for its full latency; the first versions of this loop took
+// 420-500 cycles per layer (scripts/micro/c3_parts.cu).  Hence:
+//   * the edge words (block offset | rows << 20 | columns << 26) of all layers are written to shared memory by the lanes in
+//     parallel before the loop; the loop reads them two layers ahead;
+//   * the first eight rows of the NEXT layer's block are loaded before the current layer is reduced (rows beyond a block
+//     meet INF samples: no clamping); blocks with more than eight rows take a tail loop;
+//   * the per-layer minima (the lower bounds read them) come from a lane-parallel pass behind the loop instead of a
+//     REDUX per layer.
+#define C3_EW_NONE ((1u << 20) | (1u << 26))     // offset 0, 1 x 1: a valid read that nobody uses
+
+//   * the loop works on 32-bit shared-memory addresses held in registers (laundered through an empty asm) and explicit
+//     ld.shared / st.shared in program order: left to itself the compiler re-derives every shared-memory pointer from
+//     S2R / LDC in each iteration (35 instructions and two S2R round trips per layer) and parks each load right in
+//     front of its consumer.
+static __device__ __forceinline__ unsigned c3_saddr(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+static __device__ __forceinline__ unsigned c3_keep(unsigned x) { asm volatile("" : "+r"(x)); return x; }
+static __device__ __forceinline__ int c3_lds(unsigned a)
+{
+   int v;
+   asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(a));
+   return v;
+}
+static __device__ __forceinline__ void c3_sts(unsigned a, int v) { asm volatile("st.shared.s32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+template <typename TT> static __device__ __forceinline__ int c3_ldt(unsigned a);
+template <> __device__ __forceinline__ int c3_ldt<int>(unsigned a) { return c3_lds(a); }
+template <> __device__ __forceinline__ int c3_ldt<unsigned short>(unsigned a)
+{
+   int v;
+   asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(a));
+   return v;
+}
+
+// rows t0 .. t0 + 7 of a block (unclamped) against the shuffled samples: the tail of blocks with more than eight rows
+template <typename TT, int W>
+static __device__ __forceinline__ void c3_rows8(unsigned pa, unsigned strideB, int v, int t0, int &a0, int &a1)
+{
+   constexpr unsigned FULL = 0xffffffffu;
+   int d[8], x[8];
+#pragma unroll
+   for (int t = 0; t < 8; ++t) d[t] = c3_ldt<TT>(pa + (unsigned)(t0 + t) * strideB);
+#pragma unroll
+   for (int t = 0; t < 8; ++t) x[t] = __shfl_sync(FULL, v, t0 + t, W);
+#pragma unroll
+   for (int t = 0; t < 8; t += 2) { a0 = __viaddmin_s32(x[t], d[t], a0); a1 = __viaddmin_s32(x[t + 1], d[t + 1], a1); }
+}
+
 template <typename TT> static __device__ void c3_fwd_scan(const C3Sm<TT> &s, int S, int lf, int lane)
 {
    constexpr unsigned FULL = 0xffffffffu;
+   constexpr int ES = (int)sizeof(TT);
    if (lf > S) return;
-   const int mp = s.mp, N = s.N;
-   const TT *tab = s.tab;
-   int2 cia = s.cinfo[s.lcl[lf - 1]], cib = s.cinfo[s.lcl[lf]];
-   int v = lane < cia.y ? s.F[(lf - 1) * mp + lane] : C3_INF;
+   const int mp = s.mp;
+   for (int l = lf + lane; l <= S; l += 32) s.ew[l] = c3_edge_word(s, s.lcl[l - 1], s.lcl[l]);
+   if (lane < 2) s.ew[S + 1 + lane] = C3_EW_NONE;
+   __syncwarp();
+   lane = (int)c3_keep((unsigned)lane);
+   const unsigned tabA = c3_keep(c3_saddr(s.tab)), mp4 = c3_keep(4u * (unsigned)mp);
+   unsigned ewp = c3_keep(c3_saddr(s.ew + lf)), frow = c3_keep(c3_saddr(s.F + lf * mp + lane));
+   unsigned w = (unsigned)c3_lds(ewp), wn = (unsigned)c3_lds(ewp + 4);
+   ewp += 8;
+   int v = lane < (int)((w >> 20) & 63) ? c3_lds(frow - mp4) : C3_INF;
+   unsigned pa = tabA + ES * ((w & 0xfffffu) + min(lane, (int)(w >> 26) - 1));
    int dd[8];
-   {
-      const TT *blk = tab + (cia.x * N + cia.y * cib.x) + min(lane, cib.y - 1);
 #pragma unroll
-      for (int t = 0; t < 8; ++t) dd[t] = (int)blk[min(t, cia.y - 1) * cib.y];
-   }
+   for (int t = 0; t < 8; ++t) dd[t] = c3_ldt<TT>(pa + t * ES * (w >> 26));
+#pragma unroll 2
    for (int l = lf; l <= S; ++l) {
-      int2 cin = cib;
+      int x[8];
+#pragma unroll
+      for (int t = 0; t < 8; ++t) x[t] = __shfl_sync(FULL, v, t);
+      const unsigned wn2 = (unsigned)c3_lds(ewp);
+      ewp += 4;
+      const unsigned sbn = ES * (wn >> 26);
+      const unsigned pn = tabA + ES * ((wn & 0xfffffu) + min(lane, (int)(wn >> 26) - 1));
       int dn[8];
-      if (l < S) {
-         cin = s.cinfo[s.lcl[l + 1]];
-         const TT *nb = tab + (cib.x * N + cib.y * cin.x) + min(lane, cin.y - 1);
 #pragma unroll
-         for (int t = 0; t < 8; ++t) dn[t] = (int)nb[min(t, cib.y - 1) * cin.y];
-      } else {
+      for (int t = 0; t < 8; ++t) dn[t] = c3_ldt<TT>(pn + t * sbn);
+      int a0 = __viaddmin_s32(x[0], dd[0], C3_INF), a1 = __viaddmin_s32(x[1], dd[1], C3_INF);
 #pragma unroll
-         for (int t = 0; t < 8; ++t) dn[t] = 0;
+      for (int t = 2; t < 8; t += 2) { a0 = __viaddmin_s32(x[t], dd[t], a0); a1 = __viaddmin_s32(x[t + 1], dd[t + 1], a1); }
+      const int ma = (w >> 20) & 63, mb = w >> 26;
+      if (ma > 8) {
+#pragma unroll 1
+         for (int t0 = 8; t0 < ma; t0 += 8) c3_rows8<TT, 32>(pa, ES * mb, v, t0, a0, a1);
       }
-      int a0 = C3_INF, a1 = C3_INF;
-#pragma unroll
-      for (int t = 0; t < 8; t += 2) {
-         a0 = __viaddmin_s32(__shfl_sync(FULL, v, min(t, cia.y - 1)), dd[t], a0);
-         a1 = __viaddmin_s32(__shfl_sync(FULL, v, min(t + 1, cia.y - 1)), dd[t + 1], a1);
-      }
-      if (cia.y > 8) {
-         const TT *blk = tab + (cia.x * N + cia.y * cib.x) + min(lane, cib.y - 1);
-         for (int i = 8; i < cia.y; ++i) a0 = __viaddmin_s32(__shfl_sync(FULL, v, i), (int)blk[i * cib.y], a0);
-      }
-      const int acc = lane < cib.y ? min(a0, a1) : C3_INF;
-      if (lane < cib.y) s.F[l * mp + lane] = acc;
-      const int mn = __reduce_min_sync(FULL, acc);
-      if (lane == 0) s.minF[l] = mn;
+      const int acc = lane < mb ? min(a0, a1) : C3_INF;
+      if (lane < mb) c3_sts(frow, acc);
+      frow += mp4;
       v = acc;
-      cia = cib; cib = cin;
+      w = wn; wn = wn2; pa = pn;
 #pragma unroll
       for (int t = 0; t < 8; ++t) dd[t] = dn[t];
+   }
+   __syncwarp();
+   for (int l = lf + lane; l <= S; l += 32) {
+      const int m = (int)(s.ew[l] >> 26);
+      int mn = C3_INF;
+      for (int j = 0; j < m; ++j) mn = min(mn, s.F[l * mp + j]);
+      s.minF[l] = mn;
    }
    __syncwarp();
 }
 
 // backward layers [lb, 0]: B[l][i] = min_j (B[l+1][j] + D(c_l, c_{l+1})[i][j])   :1380-1399 / 1453-1472 / 1515-1539
-// rows are stored by distance from the goal (slot S - l), so inserting a target never moves a row
+// rows are stored by distance from the goal (slot S - l), so inserting a target never moves a row.  ew[l + 1] = edge l -> l + 1
 template <typename TT> static __device__ void c3_bwd_scan(const C3Sm<TT> &s, int S, int lb, int lane)
 {
    constexpr unsigned FULL = 0xffffffffu;
+   constexpr int ES = (int)sizeof(TT);
    if (lb < 0) return;
-   const int mp = s.mp, N = s.N;
-   const TT *tab = s.tab;
-   int2 cib = s.cinfo[s.lcl[lb + 1]], cia = s.cinfo[s.lcl[lb]];
-   int v = lane < cib.y ? s.Brev[(S - (lb + 1)) * mp + lane] : C3_INF;
+   const int mp = s.mp;
+   for (int l = lb - lane; l >= 0; l -= 32) s.ew[l + 1] = c3_edge_word(s, s.lcl[l], s.lcl[l + 1]);
+   if (lane < 2) s.ew[-lane] = C3_EW_NONE;
+   __syncwarp();
+   lane = (int)c3_keep((unsigned)lane);
+   const unsigned tabA = c3_keep(c3_saddr(s.tab)), mp4 = c3_keep(4u * (unsigned)mp);
+   unsigned ewp = c3_keep(c3_saddr(s.ew + lb + 1)), brow = c3_keep(c3_saddr(s.Brev + (S - lb) * mp + lane));
+   unsigned w = (unsigned)c3_lds(ewp), wn = (unsigned)c3_lds(ewp - 4);
+   ewp -= 8;
+   int v = lane < (int)(w >> 26) ? c3_lds(brow - mp4) : C3_INF;
+   unsigned pa = tabA + ES * ((w & 0xfffffu) + min(lane, (int)((w >> 20) & 63) - 1) * (w >> 26));
    int dd[8];
-   {
-      const TT *blk = tab + (cia.x * N + cia.y * cib.x) + min(lane, cia.y - 1) * cib.y;
 #pragma unroll
-      for (int t = 0; t < 8; ++t) dd[t] = (int)blk[min(t, cib.y - 1)];
-   }
+   for (int t = 0; t < 8; ++t) dd[t] = c3_ldt<TT>(pa + t * ES);
+#pragma unroll 2
    for (int l = lb; l >= 0; --l) {
-      int2 cip = cia;
+      int x[8];
+#pragma unroll
+      for (int t = 0; t < 8; ++t) x[t] = __shfl_sync(FULL, v, t);
+      const unsigned wn2 = (unsigned)c3_lds(ewp);
+      ewp -= 4;
+      const unsigned pn = tabA + ES * ((wn & 0xfffffu) + min(lane, (int)((wn >> 20) & 63) - 1) * (wn >> 26));
       int dn[8];
-      if (l > 0) {
-         cip = s.cinfo[s.lcl[l - 1]];
-         const TT *nb = tab + (cip.x * N + cip.y * cia.x) + min(lane, cip.y - 1) * cia.y;
 #pragma unroll
-         for (int t = 0; t < 8; ++t) dn[t] = (int)nb[min(t, cia.y - 1)];
-      } else {
+      for (int t = 0; t < 8; ++t) dn[t] = c3_ldt<TT>(pn + t * ES);
+      int a0 = __viaddmin_s32(x[0], dd[0], C3_INF), a1 = __viaddmin_s32(x[1], dd[1], C3_INF);
 #pragma unroll
-         for (int t = 0; t < 8; ++t) dn[t] = 0;
+      for (int t = 2; t < 8; t += 2) { a0 = __viaddmin_s32(x[t], dd[t], a0); a1 = __viaddmin_s32(x[t + 1], dd[t + 1], a1); }
+      const int ma = (w >> 20) & 63, mb = w >> 26;
+      if (mb > 8) {
+#pragma unroll 1
+         for (int t0 = 8; t0 < mb; t0 += 8) c3_rows8<TT, 32>(pa, ES, v, t0, a0, a1);
       }
-      int a0 = C3_INF, a1 = C3_INF;
-#pragma unroll
-      for (int t = 0; t < 8; t += 2) {
-         a0 = __viaddmin_s32(__shfl_sync(FULL, v, min(t, cib.y - 1)), dd[t], a0);
-         a1 = __viaddmin_s32(__shfl_sync(FULL, v, min(t + 1, cib.y - 1)), dd[t + 1], a1);
-      }
-      if (cib.y > 8) {
-         const TT *blk = tab + (cia.x * N + cia.y * cib.x) + min(lane, cia.y - 1) * cib.y;
-         for (int j = 8; j < cib.y; ++j) a0 = __viaddmin_s32(__shfl_sync(FULL, v, j), (int)blk[j], a0);
-      }
-      const int acc = lane < cia.y ? min(a0, a1) : C3_INF;
-      if (lane < cia.y) s.Brev[(S - l) * mp + lane] = acc;
-      const int mn = __reduce_min_sync(FULL, acc);
-      if (lane == 0) s.minBrev[S - l] = mn;
+      const int acc = lane < ma ? min(a0, a1) : C3_INF;
+      if (lane < ma) c3_sts(brow, acc);
+      brow += mp4;
       v = acc;
-      cib = cia; cia = cip;
+      w = wn; wn = wn2; pa = pn;
 #pragma unroll
       for (int t = 0; t < 8; ++t) dd[t] = dn[t];
+   }
+   __syncwarp();
+   for (int l = lb - lane; l >= 0; l -= 32) {
+      const int m = (int)((s.ew[l + 1] >> 20) & 63);
+      int mn = C3_INF;
+      for (int j = 0; j < m; ++j) mn = min(mn, s.Brev[(S - l) * mp + j]);
+      s.minBrev[S - l] = mn;
    }
    __syncwarp();
 }
@@ -338,16 +458,19 @@ template <typename TT> static __device__ __forceinline__ int c3_lower_bound(cons
 
 // ---- one proposal by one sub-warp group of G lanes (lane = destination sample; mp <= G) ----------------------------------
 // chain of K table blocks from F[s0] to B[sK] (tryToMove :932-1154, tryToAdd :245-304, tryToExchange :635-797,
-// tryToReplace :456-513; CandCode of eval.cuh).  A warp advances its 32 / G proposals in lock step: per round of G steps
-// every lane first describes one block of its group's chain (offset, shape; the warp-wide row count by xor-shuffles),
-// the step loop then needs two broadcasts, <= G / 4 x (4 LDS + 4 SHFL + 4 VIADDMNMX) and no barrier.  Integers: the
-// reference's two closing associations give the same number.  All 32 lanes must call; K = 0: idle group.
+// tryToReplace :456-513; CandCode of eval.cuh).  A warp advances its 32 / G proposals in lock step.  First every lane
+// describes blocks of its group's chain and writes their words (offset | rows << 20 | columns << 26; bit 19: some group of
+// the warp has more than eight rows in this step) to the group's list in shared memory; the step loop then is the
+// re-scan's loop: SHFL x 8 -> next step's rows -> VIADDMNMX chain.  Integers: the reference's two closing associations
+// give the same number.  Returns v[j] + B[sK][j] of this lane (INF-like beyond the last layer): the caller's acceptance
+// test is monotone in the length, so it tests every lane's value instead of reducing them first.
+// All 32 lanes must call; K = 0: idle group.
 template <typename TT, int G>
-static __device__ __forceinline__ int c3_eval(const C3Sm<TT> &s, int T, const CandCode &cc, int gl)
+static __device__ __forceinline__ int c3_eval(const C3Sm<TT> &s, int T, const CandCode &cc, int gl, unsigned *gw)
 {
    constexpr unsigned FULL = 0xffffffffu;
+   constexpr int ES = (int)sizeof(TT);
    const int S = T + 1, mp = s.mp, N = s.N, K = cc.K;
-   const TT *tab = s.tab;
    int v = C3_INF, bK = C3_INF;
    if (K) {
       const int m0 = s.cinfo[s.lcl[cc.s0]].y, mK = s.cinfo[s.lcl[cc.sK]].y;
@@ -355,48 +478,59 @@ static __device__ __forceinline__ int c3_eval(const C3Sm<TT> &s, int T, const Ca
       bK = gl < mK ? s.Brev[(S - cc.sK) * mp + gl] : C3_INF;
    }
    const int Kmax = __reduce_max_sync(FULL, K);
-   for (int e0 = 0; e0 < Kmax; e0 += G) {
-      unsigned w = (1u << 20) | (1u << 26);     // offset 0, 1 x 1: a valid read that no group uses
-      int tm = 1;
-      {
-         const int k = e0 + gl + 1;
-         if (k <= K) {
-            const int la = cand_layer(cc, k - 1), lb = cand_layer(cc, k);
-            const int2 cia = s.cinfo[la < 0 ? cc.foreign : s.lcl[la]], cib = s.cinfo[lb < 0 ? cc.foreign : s.lcl[lb]];
-            w = (unsigned)(cia.x * N + cia.y * cib.x) | ((unsigned)cia.y << 20) | ((unsigned)cib.y << 26);
-            tm = cia.y;
-         }
-#pragma unroll
-         for (int sft = G; sft < 32; sft <<= 1) tm = max(tm, __shfl_xor_sync(FULL, tm, sft));
+   for (int e0 = 0; e0 < Kmax + 2; e0 += G) {
+      const int k = e0 + gl + 1;
+      unsigned w = C3_EW_NONE;
+      int big = 0;
+      if (k <= K) {
+         const int la = cand_layer(cc, k - 1), lb = cand_layer(cc, k);
+         const int2 cia = s.cinfo[la < 0 ? cc.foreign : s.lcl[la]], cib = s.cinfo[lb < 0 ? cc.foreign : s.lcl[lb]];
+         w = (unsigned)(cia.x * N + cia.y * cib.x) | ((unsigned)cia.y << 20) | ((unsigned)cib.y << 26);
+         big = cia.y > 8;
       }
-      const int kend = min(G, Kmax - e0);
-      for (int kk = 0; kk < kend; ++kk) {
-         const unsigned wk = __shfl_sync(FULL, w, kk, G);
-         const int tmax = __shfl_sync(FULL, tm, kk, G);                 // warp-uniform
-         const int ma = (wk >> 20) & 63, mb = wk >> 26;
-         const TT *blk = tab + (wk & 0xfffffu) + min(gl, mb - 1);
-         int a0 = C3_INF, a1 = C3_INF;
-         for (int t0 = 0; t0 < tmax; t0 += 4) {
-            int d[4], x[4];
+      if (G > 8) {
 #pragma unroll
-            for (int t = 0; t < 4; ++t) {
-               const int r = min(t0 + t, ma - 1);
-               d[t] = (int)blk[r * mb];
-               x[t] = __shfl_sync(FULL, v, r, G);
-            }
-            a0 = __viaddmin_s32(x[0], d[0], a0);
-            a1 = __viaddmin_s32(x[1], d[1], a1);
-            a0 = __viaddmin_s32(x[2], d[2], a0);
-            a1 = __viaddmin_s32(x[3], d[3], a1);
-         }
-         if (e0 + kk + 1 <= K) v = gl < mb ? min(a0, a1) : C3_INF;
+         for (int sft = G; sft < 32; sft <<= 1) big |= __shfl_xor_sync(FULL, big, sft);
+         w |= (unsigned)big << 19;
       }
+      if (k <= Kmax + 2) gw[k] = w;
    }
-   int fin = K ? v + bK : C3_INF;          // lanes beyond the last layer hold INF + INF < 2^31
-   fin = min(fin, C3_INF);
+   __syncwarp();
+   const unsigned tabA = c3_keep(c3_saddr(s.tab));
+   const int glk = (int)c3_keep((unsigned)gl);
+   unsigned gwp = c3_keep(c3_saddr(gw + 1));
+   unsigned w = (unsigned)c3_lds(gwp), wn = (unsigned)c3_lds(gwp + 4);
+   gwp += 8;
+   unsigned pa = tabA + ES * ((w & 0x7ffffu) + min(glk, (int)(w >> 26) - 1));
+   int dd[8];
 #pragma unroll
-   for (int sft = G / 2; sft > 0; sft >>= 1) fin = min(fin, __shfl_xor_sync(FULL, fin, sft, G));
-   return fin;
+   for (int t = 0; t < 8; ++t) dd[t] = c3_ldt<TT>(pa + t * ES * (w >> 26));
+#pragma unroll 2
+   for (int k = 1; k <= Kmax; ++k) {
+      int x[8];
+#pragma unroll
+      for (int t = 0; t < 8; ++t) x[t] = __shfl_sync(FULL, v, t, G);
+      const unsigned wn2 = (unsigned)c3_lds(gwp);
+      gwp += 4;
+      const unsigned sbn = ES * (wn >> 26);
+      const unsigned pn = tabA + ES * ((wn & 0x7ffffu) + min(glk, (int)(wn >> 26) - 1));
+      int dn[8];
+#pragma unroll
+      for (int t = 0; t < 8; ++t) dn[t] = c3_ldt<TT>(pn + t * sbn);
+      int a0 = __viaddmin_s32(x[0], dd[0], C3_INF), a1 = __viaddmin_s32(x[1], dd[1], C3_INF);
+#pragma unroll
+      for (int t = 2; t < 8; t += 2) { a0 = __viaddmin_s32(x[t], dd[t], a0); a1 = __viaddmin_s32(x[t + 1], dd[t + 1], a1); }
+      const int mb = w >> 26;
+      if (G > 8 && ((w >> 19) & 1)) {            // warp-uniform: rows 8 .. G - 1 for everybody (INF samples beyond a block)
+#pragma unroll 1
+         for (int t0 = 8; t0 < G; t0 += 8) c3_rows8<TT, G>(pa, ES * mb, v, t0, a0, a1);
+      }
+      if (k <= K) v = glk < mb ? min(a0, a1) : C3_INF;
+      w = wn; wn = wn2; pa = pn;
+#pragma unroll
+      for (int t = 0; t < 8; ++t) dd[t] = dn[t];
+   }
+   return K ? min(v + bK, C3_INF) : C3_INF;          // lanes beyond the last layer hold INF + INF < 2^31
 }
 
 // insertRandom accept (vns_sop_solver.cpp:621-646): VNS[from] is re-inserted immediately before the element that was at
@@ -410,21 +544,25 @@ template <typename TT> static __device__ int c3_apply(const C3Sm<TT> &s, int kin
    if (kind == 1) {
       const int c = s.vns[from];
       __syncthreads();                    // every thread holds c; nobody still evaluates
+      // tg[tlo .. thi] and vns[vlo .. vhi] move by `delta`, then c lands at index `at`
+      int tlo, thi, vlo, vhi, delta, at;
       if (from < T) {
          if (to > from) {                 // travels up to index to-1; layers from+1 .. to change
-            if (warp == 0) { c3_shift1(tg, from + 1, to - 1, -1, lane); if (lane == 0) tg[to - 1] = c; }
-            if (warp == 1) { c3_shift1(s.vns, from + 1, to - 1, -1, lane); if (lane == 0) s.vns[to - 1] = c; }
+            tlo = vlo = from + 1; thi = vhi = to - 1; delta = -1; at = to - 1;
             lf = from + 1; lb = to;
          } else {                         // travels down to index `to`; layers to+1 .. from+1 change
-            if (warp == 0) { c3_shift1(tg, to, from - 1, +1, lane); if (lane == 0) tg[to] = c; }
-            if (warp == 1) { c3_shift1(s.vns, to, from - 1, +1, lane); if (lane == 0) s.vns[to] = c; }
+            tlo = vlo = to; thi = vhi = from - 1; delta = +1; at = to;
             lf = to + 1; lb = from + 1;
          }
       } else {                            // from outside the path (from >= T >= to): one more target at index `to`
-         if (warp == 0) { c3_shift1(tg, to, T, +1, lane); if (lane == 0) tg[to] = c; }      // includes the goal's entry
-         if (warp == 1) { c3_shift1(s.vns, to, from - 1, +1, lane); if (lane == 0) s.vns[to] = c; }
+         tlo = vlo = to; thi = T; vhi = from - 1; delta = +1; at = to;      // tg's range includes the goal's entry
          T += 1;
          lf = to + 1; lb = to + 1;        // B rows of the old layers to+1 .. S keep their slots
+      }
+      if (warp < 2) {
+         int *arr = warp == 0 ? tg : s.vns;
+         c3_shift1(arr, warp == 0 ? tlo : vlo, warp == 0 ? thi : vhi, delta, lane);
+         if (lane == 0) arr[at] = c;
       }
    } else {
       if (threadIdx.x == 0) {
@@ -456,6 +594,8 @@ static __device__ void c3_local_search(const C3Sm<TT> &s, C3Ctl &ctl, RngState &
    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, gl = lane % G, gq = lane / G;
    const int nvns = ctl.nvns;
    const int gap = kind == 1 ? 1 : 2;
+   // lengths and bounds are integers: x > budget <=> x > floor(budget)
+   const int ibudget = budget >= 2147483647.0 ? 2147483647 : (budget < 0.0 ? -1 : (int)floor(budget));
    __syncthreads();
    if (!(kind == 1 ? (nvns >= 3) : (nvns >= 4 && ctl.T > 0))) return;    // guards :498 and :711 (uniform)
    if (warp == C3_WARPS - 1) {
@@ -476,29 +616,27 @@ static __device__ void c3_local_search(const C3Sm<TT> &s, C3Ctl &ctl, RngState &
       const int target = min(max(2 * ema, 32), 32 * C3_MAXCH);
       int nch = target > 64 ? 4 : (target > 32 ? 2 : 1);
       while (nch > 1 && nch * 32 > remaining) nch >>= 1;
-      unsigned balv[C3_MAXCH], bals[C3_MAXCH];
       int nvalid = 0, nsurv = 0, lastp = -1;
       const int tohi = kind == 1 ? T : T - 1;
-#pragma unroll
-      for (int ch = 0; ch < C3_MAXCH; ++ch) {
-         balv[ch] = 0; bals[ch] = 0;
-         if (ch < nch) {
-            const int p = ch * 32 + lane;
-            const unsigned r1 = s.ring[(pos + 2 * p) & M] >> 1, r2 = s.ring[(pos + 2 * p + 1) & M] >> 1;
-            const int from = (int)(((unsigned long long)r1 * (unsigned)nvns) >> 31);            // :507 / :723
-            const int to = (int)(((unsigned long long)r2 * (unsigned)(tohi + 1)) >> 31);        // :508 / :724
-            bool valid = abs(from - to) > gap;                                                 // :510-519 / :726-730
-            const unsigned bv0 = __ballot_sync(FULL, valid);
-            // the call ends after exactly num_changes proposals: later ones do not exist
-            valid = valid && nvalid + __popc(bv0 & ((1u << lane) - 1)) < remaining;
-            bool surv = valid;
-            if (valid && skipflag) surv = !((double)c3_lower_bound(s, T, kind, from, to) > budget);   // :539,:574,:749,:779
-            const unsigned bv = __ballot_sync(FULL, valid), bs = __ballot_sync(FULL, surv);
-            balv[ch] = bv; bals[ch] = bs;
-            nvalid += __popc(bv); nsurv += __popc(bs);
-            if (bv) lastp = ch * 32 + 31 - __clz(bv);
-         }
+#pragma unroll 1
+      for (int ch = 0; ch < nch; ++ch) {
+         const int p = ch * 32 + lane;
+         const unsigned r1 = s.ring[(pos + 2 * p) & M] >> 1, r2 = s.ring[(pos + 2 * p + 1) & M] >> 1;
+         const int from = (int)(((unsigned long long)r1 * (unsigned)nvns) >> 31);            // :507 / :723
+         const int to = (int)(((unsigned long long)r2 * (unsigned)(tohi + 1)) >> 31);        // :508 / :724
+         bool valid = abs(from - to) > gap;                                                 // :510-519 / :726-730
+         const unsigned bv0 = __ballot_sync(FULL, valid);
+         // the call ends after exactly num_changes proposals: later ones do not exist
+         valid = valid && nvalid + __popc(bv0 & ((1u << lane) - 1)) < remaining;
+         bool surv = valid;
+         if (valid && skipflag) surv = !(c3_lower_bound(s, T, kind, from, to) > ibudget);   // :539,:574,:749,:779
+         const unsigned bv = __ballot_sync(FULL, valid), bs = __ballot_sync(FULL, surv);
+         if (surv) s.surv[nsurv + __popc(bs & ((1u << lane) - 1))] = p;     // every warp writes the same list
+         if (lane == 0) { ctl.balv[ch] = bv; ctl.bals[ch] = bs; }
+         nvalid += __popc(bv); nsurv += __popc(bs);
+         if (bv) lastp = ch * 32 + 31 - __clz(bv);
       }
+      __syncwarp();
       const long long t1 = clock64();
       // ---- 2. survivors in draw order, one group each; stop behind the first pass that accepts ---------------------------
       int fp = C3_NONE;
@@ -508,17 +646,7 @@ static __device__ void c3_local_search(const C3Sm<TT> &s, C3Ctl &ctl, RngState &
          if (base + warp * NG < nsurv) {
             const int sidx = base + warp * NG + gq;
             const bool act = sidx < nsurv;
-            int p = 0;
-            {
-               int rem = sidx;
-               bool done = !act;
-#pragma unroll
-               for (int ch = 0; ch < C3_MAXCH; ++ch) {
-                  const int cnt = __popc(bals[ch]);
-                  if (!done && rem < cnt) { p = ch * 32 + (int)__fns(bals[ch], 0, rem + 1); done = true; }
-                  else if (!done) rem -= cnt;
-               }
-            }
+            const int p = act ? s.surv[sidx] : 0;
             const unsigned r1 = s.ring[(pos + 2 * p) & M] >> 1, r2 = s.ring[(pos + 2 * p + 1) & M] >> 1;
             const int from = (int)(((unsigned long long)r1 * (unsigned)nvns) >> 31);
             const int to = (int)(((unsigned long long)r2 * (unsigned)(tohi + 1)) >> 31);
@@ -530,13 +658,14 @@ static __device__ void c3_local_search(const C3Sm<TT> &s, C3Ctl &ctl, RngState &
                else { op = in ? VNSGPU_OP_EXCHANGE : VNSGPU_OP_REPLACE; a = in ? from : cf; }
             }
             const CandCode cc = decode_cand(T, s.C, op, a, to);
-            const int fin = c3_eval<TT, G>(s, T, cc, gl);
-            if (act && gl == 0) {
+            const int fin = c3_eval<TT, G>(s, T, cc, gl, s.gw + (warp * NG + gq) * s.gwcap);
+            // integers: (L - 0.0) + (len - L) == len (:580,:583); len <= budget <=> len <= floor(budget); L - len > 1e-5 <=> L > len.
+            // The test is monotone in the length: the group's minimum passes iff some lane's value does
+            if (act) {
                double dR = 0.0;
                if (!in) dR = kind == 1 ? s.reward[cf]                                              // :581
                                        : 0.0 + (s.reward[cf] - s.reward[s.vns[to]]);              // :784
-               const double len = (double)fin, Ld = (double)L;    // integers: (L - 0.0) + (len - L) == len  (:580,:583)
-               const bool acc = cc.K > 0 && len <= budget && (dR > 0 || (Ld - len) > VNS_MIN_CHANGE_EPS);   // :619,:805-806
+               const bool acc = cc.K > 0 && fin < C3_INF && fin <= ibudget && (dR > 0 || L > fin);   // :619,:805-806
                if (acc) atomicMin(&ctl.first[cell], p);
                if (cc.K == 0) ctl.bad = 1;
             }
@@ -554,10 +683,10 @@ static __device__ void c3_local_search(const C3Sm<TT> &s, C3Ctl &ctl, RngState &
       int wfrom = 0, wto = 0;
       if (found) {
          used = 0; passed = 0;
-#pragma unroll
-         for (int ch = 0; ch < C3_MAXCH; ++ch) {
-            const unsigned upto = ch < (fp >> 5) ? FULL : (ch == (fp >> 5) ? (2u << (fp & 31)) - 1u : 0u);
-            used += __popc(balv[ch] & upto); passed += __popc(bals[ch] & upto);
+#pragma unroll 1
+         for (int ch = 0; ch <= (fp >> 5); ++ch) {
+            const unsigned upto = ch < (fp >> 5) ? FULL : (2u << (fp & 31)) - 1u;
+            used += __popc(ctl.balv[ch] & upto); passed += __popc(ctl.bals[ch] & upto);
          }
          adv = 2u * (unsigned)(fp + 1);
          const unsigned r1 = s.ring[(pos + 2 * fp) & M] >> 1, r2 = s.ring[(pos + 2 * fp + 1) & M] >> 1;
