@@ -289,6 +289,32 @@ int vnsgpu_eval_mode(const vnsgpu_ctx *ctx, int64_t n);
  * w = bytes per table entry the active evaluation path reads (8 double, 4 exact-int32) */
 vnsgpu_status vnsgpu_cand_bytes(vnsgpu_ctx *ctx, int path, int64_t n, const vnsgpu_cand *cands, int64_t *bytes);
 
+/* ---- full-neighbourhood modes on the batched evaluation --------------------------------------------
+ * greedy_insertion (vns_sop_solver.cpp:1091-1155) with every round's (|VNS| - T) x (T + 1) tryToAdd grid evaluated by ONE
+ * batched call and reduced on the device: strict minimum of (d - L) / reward among d <= budget, first grid index on ties
+ * (:1119).  Same tour as vnsgpu_greedy and the reference.  rounds / evals (may be NULL): insertions made / candidates
+ * evaluated. */
+vnsgpu_status vnsgpu_greedy_batched(vnsgpu_ctx *ctx, int path, double budget, int *rounds, int64_t *evals);
+/* Opt-in local search that is NOT trajectory-exact: the WHOLE insert (kind 1: tryToMove / tryToAdd of every (from, to)
+ * pair insertRandom can draw, :507-519) or exchange (kind 2: tryToExchange / tryToReplace, :723-730) neighbourhood is
+ * evaluated at once and the BEST improving candidate is returned instead of the first drawn one: most added reward,
+ * then shortest tour, then lowest index (from-major).  Improving = feasible and (added reward > 0, or the same reward and
+ * at least 1e-5 shorter); unlike the reference's acceptance test (:619,:805-806) a shorter tour with LESS reward does not
+ * qualify, so a descent terminates.  index = -1: no improving candidate. */
+typedef struct {
+   int64_t index;          /* from * (tohi + 1) + to, tohi = T (insert) or T - 1 (exchange); -1: none */
+   int32_t from, to, kind, pad;
+   double added_reward, length;
+   int64_t n_candidates;
+} vnsgpu_best_move_t;
+vnsgpu_status vnsgpu_best_move(vnsgpu_ctx *ctx, int path, int kind, double budget, vnsgpu_best_move_t *out);
+/* the accept branch of insertRandom (:621-646, kind 1) / exchangeRandom (:807-832, kind 2) for the pair (from, to):
+ * VNS[from] moves in front of index `to` / VNS[from] and VNS[to] swap; F / B re-scanned */
+vnsgpu_status vnsgpu_apply_move(vnsgpu_ctx *ctx, int path, int kind, int from, int to);
+/* variable-neighbourhood descent with the two calls above: best insert move until there is none, then best exchange move,
+ * back to insert after every applied move; ends when neither neighbourhood improves (or after max_steps > 0 moves) */
+vnsgpu_status vnsgpu_best_improvement(vnsgpu_ctx *ctx, int path, double budget, int max_steps, int *steps, int64_t *evals);
+
 /* ---- multi-GPU exchange steps: candidates shard over ranks, table and incumbent are replicated; the only
  *      collectives are the all-reduce(MIN) of the first-accepted key and the broadcast of the incumbent.  One context per
  *      GPU and rank; the communicator is NCCL's (libnccl.so.2 is bound with dlopen at the first call - VNSGPU_E_NCCL when it

@@ -113,7 +113,8 @@ static __global__ void __launch_bounds__(256) k_best_reduce(InstDev I, PathDev P
    __threadfence();
    best = BestKey{0.0, 0.0, -1};
    for (int b = threadIdx.x; b < (int)gridDim.x; b += blockDim.x) {
-      const BestKey q = *(volatile BestKey *)(partial + b);
+      BestKey q;
+      q.a = __ldcg(&partial[b].a); q.b = __ldcg(&partial[b].b); q.idx = __ldcg(&partial[b].idx);
       if (key_better<MODE>(q, best)) best = q;
    }
    sh[threadIdx.x] = best;

@@ -114,6 +114,8 @@ struct vnsgpu_ctx {
    void *h_pick = nullptr;        // pinned record vnsgpu_propose_eval reads back
    void *d_gen = nullptr, *d_gencands = nullptr;
    size_t gen_bytes = 0, gencands_bytes = 0;
+   void *d_best = nullptr;        // full-neighbourhood modes (best.cu): descriptors, lengths, flags, partial keys
+   size_t best_bytes = 0;
    bool phase_timing = false;     // vnsgpu_set_phase_timing: CUDA events around the phases of the batched evaluation call
    std::vector<PhaseEvent> phase_events;
    int chain_tree = -1;           // vnsgpu_set_chain_tree: -1 from the instance size, 0 off, 1 on

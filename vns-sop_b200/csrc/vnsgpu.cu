@@ -57,7 +57,7 @@ void vnsgpu_destroy(vnsgpu_ctx *ctx)
    free_instance(ctx);
    cudaFree(ctx->d_scratch); cudaFree(ctx->d_rng); cudaFree(ctx->d_stats); cudaFree(ctx->d_first);
    cudaFree(ctx->d_res); cudaFree(ctx->d_info); cudaFree(ctx->d_prof); cudaFree(ctx->d_stop); cudaFree(ctx->d_c2grid); cudaFree(ctx->d_c2tree); cudaFree(ctx->d_c2rows);
-   cudaFree(ctx->d_genjump); cudaFree(ctx->d_gen); cudaFree(ctx->d_gencands);
+   cudaFree(ctx->d_genjump); cudaFree(ctx->d_gen); cudaFree(ctx->d_gencands); cudaFree(ctx->d_best);
    if (ctx->s_in) {
       cudaStreamDestroy(ctx->s_in); cudaStreamDestroy(ctx->s_out); cudaEventDestroy(ctx->ev_start); cudaEventDestroy(ctx->ev_out);
       for (int k = 0; k < VNS_PIPE_EVENTS; ++k) { cudaEventDestroy(ctx->ev_in[k]); cudaEventDestroy(ctx->ev_k[k]); }

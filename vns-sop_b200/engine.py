@@ -34,6 +34,12 @@ class LsStats(C.Structure):
     _fields_ = [(n, C.c_int64) for n in ("proposals", "lb_skips", "evals", "accepts", "rounds")]
 
 
+class BestMove(C.Structure):
+    """vnsgpu_best_move_t"""
+    _fields_ = [("index", C.c_int64), ("from_", C.c_int32), ("to", C.c_int32), ("kind", C.c_int32), ("pad", C.c_int32),
+                ("added_reward", C.c_double), ("length", C.c_double), ("n_candidates", C.c_int64)]
+
+
 class VnsParams(C.Structure):
     _fields_ = [("num_iterations", C.c_int32), ("num_iterations_unimproved", C.c_int32),
                 ("lower_bound_skip", C.c_int32), ("greedy_initial", C.c_int32), ("budget", C.c_double),
@@ -105,6 +111,10 @@ _SIGS = {
     "vnsgpu_shake": [vp, C.c_int, C.c_int, C.c_double, C.POINTER(Rng)],
     "vnsgpu_fit_to_budget": [vp, C.c_int, C.c_double],
     "vnsgpu_greedy": [vp, C.c_int, C.c_double],
+    "vnsgpu_greedy_batched": [vp, C.c_int, C.c_double, C.POINTER(C.c_int), C.POINTER(C.c_int64)],
+    "vnsgpu_best_move": [vp, C.c_int, C.c_int, C.c_double, C.POINTER(BestMove)],
+    "vnsgpu_apply_move": [vp, C.c_int, C.c_int, C.c_int, C.c_int],
+    "vnsgpu_best_improvement": [vp, C.c_int, C.c_double, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int64)],
     "vnsgpu_vns_run": [vp, C.c_int, C.POINTER(VnsParams), C.POINTER(VnsResult), dp, dp, dp],
     "vnsgpu_vns_run_batch": [vp, C.c_int, C.c_int, C.POINTER(C.c_uint32), C.POINTER(VnsParams), C.POINTER(VnsResult), ip, ip],
     "vnsgpu_path_destroy": [vp, C.c_int],
@@ -586,6 +596,30 @@ class VnsSopPath:
     def greedy_insertion(self, budget=None):
         budget = self.e.pb.budget if budget is None else budget
         self.e._ck(self.lib.vnsgpu_greedy(self.e.h, self.h, budget))
+
+    def greedy_insertion_batched(self, budget=None):
+        """greedy_insertion with every round's tryToAdd grid as one batched evaluation; returns (rounds, evals)"""
+        budget = self.e.pb.budget if budget is None else budget
+        r, n = C.c_int(0), C.c_int64(0)
+        self.e._ck(self.lib.vnsgpu_greedy_batched(self.e.h, self.h, budget, C.byref(r), C.byref(n)))
+        return r.value, n.value
+
+    def best_move(self, kind, budget=None):
+        """best improving candidate of the whole insert (1) / exchange (2) neighbourhood (not trajectory-exact)"""
+        budget = self.e.pb.budget if budget is None else budget
+        m = BestMove()
+        self.e._ck(self.lib.vnsgpu_best_move(self.e.h, self.h, int(kind), budget, C.byref(m)))
+        return m
+
+    def apply_move(self, kind, from_, to):
+        self.e._ck(self.lib.vnsgpu_apply_move(self.e.h, self.h, int(kind), int(from_), int(to)))
+
+    def best_improvement(self, budget=None, max_steps=0):
+        """variable-neighbourhood descent over whole neighbourhoods; returns (moves applied, candidates evaluated)"""
+        budget = self.e.pb.budget if budget is None else budget
+        st, n = C.c_int(0), C.c_int64(0)
+        self.e._ck(self.lib.vnsgpu_best_improvement(self.e.h, self.h, budget, int(max_steps), C.byref(st), C.byref(n)))
+        return st.value, n.value
 
     def vns_run(self, seed, num_iterations=2000, num_iterations_unimproved=1000, skip=1, greedy=1, budget=None,
                 max_time_ms=0.0, max_improvements=4096):
