@@ -47,6 +47,10 @@ WORKLOADS = {
                 os.path.join(ROOT, "tests", "golden", "dop_s08.npz"), {"dubins_S": 16}),
     # BASELINE.json config 5: generated (vns-sop_b200/synthetic.py), table far beyond L2 - the HBM regime
     "synth20k": ("synthetic scaled SOP: 20000 nodes / 2000 clusters of 10, CEIL_2D (generated, seed 20190147)", None, {"n_points": 20000}),
+    # SURVEY.md 8d's raw-Euclid variant of config 5: a real-valued table, evaluated in IEEE double block by block (no
+    # segment products, no endpoint vectors: floating-point sums do not reassociate)
+    "synth20k_raw": ("synthetic scaled SOP: 20000 nodes / 2000 clusters of 10, unrounded Euclid = real-valued table (generated, seed 20190147)",
+                     None, {"n_points": 20000, "edge_weight_type": "RAW_2D"}),
     "synth2k": ("synthetic scaled SOP: 2000 nodes / 200 clusters of 10, CEIL_2D (generated, seed 20190147)", None, {"n_points": 2000}),
     # BASELINE.json config 5, DOP flavour: 2000 locations x 32 heading samples = 64 064 samples; the 32.8 GB table only ever
     # exists on the device (vnsgpu_build_table_dubins), so this workload has no CPU legs
@@ -79,8 +83,10 @@ def parse_args():
     ap.add_argument("--no-solve-cpu", action="store_true", help="time-to-reward: skip the reference binary runs (long on vm1084)")
     ap.add_argument("--sweep", action="store_true", help="candidate-batch sweep 2^10 .. --batch (x4 steps), device-resident (BASELINE config 5)")
     ap.add_argument("--multi-start", type=int, default=148, help="seeds of the multi-start leg (0 = skip)")
-    ap.add_argument("--also", default="vm1084,synth20k", help="further workloads measured (device-resident leg only) into the same JSON "
+    ap.add_argument("--also", default="vm1084,synth20k,synth20k_raw", help="further workloads measured (device-resident leg only) into the same JSON "
                                                                "line under `workloads` (BASELINE configs 4 and 5); '' = none")
+    ap.add_argument("--no-full-nbh", action="store_true", help="skip the full-neighbourhood leg (batched greedy + best-improvement descent)")
+    ap.add_argument("--descent-steps", type=int, default=200, help="moves of the best-improvement descent in the full-neighbourhood leg")
     ap.add_argument("--min-timed-s", type=float, default=0.5, help="a timed step repeats the call until K steps take at least this long")
     return ap.parse_args()
 
@@ -465,9 +471,11 @@ def run_b200(args):
     for w in extras:
         sub = argparse.Namespace(**vars(args))
         sub.workload, sub.no_e2e, sub.no_cpu, sub.no_solve, sub.sweep = w, True, True, True, False
+        if w.endswith("_raw"):
+            sub.batch = min(args.batch, 1 << 18)     # double path, block by block: ~260 blocks per candidate at T = 793
         sl = bench_workload(sub, env)
         line["workloads"][w] = {k: sl[k] for k in ("value", "unit", "ms_per_step", "steps", "dtype", "data", "config", "roofline", "gpu_launches", "table_build",
-                                                     "accepted_in_batch", "first_accept") if k in sl}
+                                                     "accepted_in_batch", "first_accept", "full_neighbourhood") if k in sl}
     if "workloads" in line and "synth20k" in line["workloads"]:
         line["roofline_hbm"] = dict(line["workloads"]["synth20k"]["roofline"], workload="synth20k")
     if rank == 0 and world == 1 and not args.no_solve and args.workload == "krob200" and "vm1084" in extras:
@@ -912,6 +920,8 @@ def bench_workload(args, env):
         line["cpu_baseline"] = cpu_baseline_leg(args, sf, pb, vns, T, rows, d_len, d_lb, state)
     if rank == 0 and world == 1 and not args.no_solve and state is None:
         line["time_to_reward"] = solve_leg(args, eng, sf, pb)
+    if rank == 0 and world == 1 and int_path and not args.no_full_nbh and not device_only(args.workload):
+        line["full_neighbourhood"] = full_neighbourhood_leg(args, eng, sf, pb, cpu=not args.no_cpu and pb.N <= 5000)
     if world > 1 and not args.no_solve and state is None and args.multi_start > 0:
         # N GPUs: the honest multi-GPU mode of the search on shipped instances is replicas - every rank races
         # its own 148 seeds to the reference's seed-1 final reward; the job's time to that reward is the fastest rank's
@@ -922,6 +932,43 @@ def bench_workload(args, env):
     eng.close()
     torch.cuda.empty_cache()
     return line
+
+
+def full_neighbourhood_leg(args, eng, sf, pb, cpu):
+    """greedy_insertion with every round as one batched evaluation (same tour as the reference's
+    greedy), then the opt-in best-improvement descent over whole neighbourhoods - NOT the reference's trajectory."""
+    import torch
+    p = eng.path()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    rounds, evals = p.greedy_insertion_batched()
+    torch.cuda.synchronize()
+    t1 = time.perf_counter()
+    r0, l0, T0 = p.getReward(), p.getPathLength(), p.getNumTargets()
+    steps, evals2 = p.best_improvement(max_steps=args.descent_steps)
+    torch.cuda.synchronize()
+    t2 = time.perf_counter()
+    out = {"greedy_batched": {"seconds": t1 - t0, "rounds": rounds, "candidates": evals, "evals_per_s": evals / max(t1 - t0, 1e-9),
+                              "targets": T0, "reward": r0, "length": l0, "trajectory_exact": True,
+                              "what": "greedy_insertion (vns_sop_solver.cpp:1091-1155): per round ONE vnsgpu_eval_batch_dev over the "
+                                      "(|VNS| - T) x (T + 1) tryToAdd grid + device arg-min + one-block apply; the tour equals the "
+                                      "reference's greedy tour (tests/test_best.py)"},
+           "best_improvement": {"seconds": t2 - t1, "moves": steps, "max_moves": args.descent_steps, "candidates": evals2,
+                                "evals_per_s": evals2 / max(t2 - t1, 1e-9), "reward": p.getReward(), "length": p.getPathLength(),
+                                "targets": p.getNumTargets(), "trajectory_exact": False,
+                                "what": "opt-in descent: per move the WHOLE insert or exchange neighbourhood evaluated at once, best "
+                                        "improving candidate applied (most added reward, then shortest, then lowest index); a "
+                                        "different search than the reference's first-improvement random sampling"}}
+    if cpu:
+        from oracle import binding as ob
+        o = ob.Oracle(pb)
+        po = o.path()
+        c0 = time.perf_counter()
+        po.greedy()
+        c1 = time.perf_counter()
+        out["greedy_batched"]["cpu_port_seconds_1_core"] = c1 - c0
+        out["greedy_batched"]["same_tour_as_cpu"] = bool(po.T == T0 and po.length() == l0 and po.reward() == r0)
+    return out
 
 
 def cpu_baseline_leg(args, sf, pb, vns, T, rows, d_len, d_lb, state=None):

@@ -17,7 +17,8 @@ from typing import List, Optional
 import numpy as np
 
 RULE_RAW, RULE_ROUND, RULE_CEIL = 0, 1, 2
-_RULES = {"EUC_2D": RULE_ROUND, "CEIL_2D": RULE_CEIL}
+_RULES = {"EUC_2D": RULE_ROUND, "CEIL_2D": RULE_CEIL,
+          "RAW_2D": RULE_RAW}   # not a TSPLIB type: the unrounded Euclid of SOPLoader::getOP / getOPN (sop_loader.cpp:278,360)
 
 
 @dataclasses.dataclass
