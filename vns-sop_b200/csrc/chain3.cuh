@@ -428,32 +428,48 @@ static __device__ __forceinline__ void c3_ring_fill(unsigned *ring, unsigned gen
 // ---- lower bound of a proposal in O(1) (one thread): minF(s0) + dist_between + minB(sK) --------------------------------
 // tryToMoveLowerBound vns_sop_path.cpp:799-930, tryToAddLowerBound :207-243, tryToExchangeLowerBound :573-633,
 // tryToReplaceLowerBound :423-454; integers, so the reference's left-to-right sums equal these prefix differences
+// Branch-free: the lanes of a warp hold different cases (up / down / from outside), and one warp executing the cases one
+// after the other pays every case's chain of dependent loads.  Every case is  minF[s0] + sum of <= 4 cluster-pair minima +
+// (pd[p1] - pd[p0]) + minBrev[S - sK]  with the pairs given as layer indices (-1 = the foreign cluster VNS[from]).
 template <typename TT> static __device__ __forceinline__ int c3_lower_bound(const C3Sm<TT> &s, int T, int kind, int from, int to)
 {
    const int S = T + 1, C = s.C;
    const int *lcl = s.lcl;
-   auto dm = [&](int ca, int cb) { return s.dmin[ca * C + cb]; };
    const bool in = from < T;
+   const int cfor = s.vns[from];
+   const int lo = min(from, to), hi = max(from, to);
+   const bool up = to > from;
+   int s0, sK, p0 = 0, p1 = 0;
+   int a0, b0, a1, b1, a2 = 0, b2 = 0, a3 = 0, b3 = 0;      // pairs (a_k -> b_k); pairs 2 and 3 may be absent
+   bool has2 = false, has3 = false;
    if (kind == 1) {
-      if (in) {
-         const int i = min(from, to) + 1, j = max(from, to) + 1;
-         if (to > from)   // up: i-1, i+1 .. j-1, i, j
-            return s.minF[i - 1] + dm(lcl[i - 1], lcl[i + 1]) + (s.pd[j - 1] - s.pd[i + 1]) + dm(lcl[j - 1], lcl[i]) + dm(lcl[i], lcl[j]) +
-                   s.minBrev[S - j];
-         // down: i-1, j, i .. j-1, j+1
-         return s.minF[i - 1] + dm(lcl[i - 1], lcl[j]) + dm(lcl[j], lcl[i]) + (s.pd[j - 1] - s.pd[i]) + dm(lcl[j - 1], lcl[j + 1]) +
-                s.minBrev[S - (j + 1)];
-      }
-      const int c = s.vns[from];
-      return s.minF[to] + dm(lcl[to], c) + dm(c, lcl[to + 1]) + s.minBrev[S - (to + 1)];
+      const int i = lo + 1, j = hi + 1;
+      // in, up:   i-1, i+1 .. j-1, i, j        in, down: i-1, j, i .. j-1, j+1        out: to, c, to+1
+      s0 = in ? i - 1 : to;
+      sK = in ? (up ? j : j + 1) : to + 1;
+      a0 = s0;                     b0 = in ? (up ? i + 1 : j) : -1;
+      a1 = in ? (up ? j - 1 : j) : -1;  b1 = in ? i : to + 1;
+      a2 = up ? i : j - 1;         b2 = up ? j : j + 1;       has2 = in;
+      p0 = in ? (up ? i + 1 : i) : 0;  p1 = in ? j - 1 : 0;
+   } else {
+      const int i = lo, j = hi + 1;
+      // in: i, j, i+2 .. j-1, i+1, j+1        out: to, c, to+2
+      s0 = in ? i : to;
+      sK = in ? j + 1 : to + 2;
+      a0 = s0;                     b0 = in ? j : -1;
+      a1 = in ? j : -1;            b1 = in ? i + 2 : to + 2;
+      a2 = j - 1;                  b2 = i + 1;                has2 = in;
+      a3 = i + 1;                  b3 = j + 1;                has3 = in;
+      p0 = in ? i + 2 : 0;         p1 = in ? j - 1 : 0;
    }
-   if (in) {   // i, j, i+2 .. j-1, i+1, j+1
-      const int i = min(from, to), j = max(from, to) + 1;
-      return s.minF[i] + dm(lcl[i], lcl[j]) + dm(lcl[j], lcl[i + 2]) + (s.pd[j - 1] - s.pd[i + 2]) + dm(lcl[j - 1], lcl[i + 1]) +
-             dm(lcl[i + 1], lcl[j + 1]) + s.minBrev[S - (j + 1)];
-   }
-   const int c = s.vns[from];
-   return s.minF[to] + dm(lcl[to], c) + dm(c, lcl[to + 2]) + s.minBrev[S - (to + 2)];
+   // layer -> cluster (absent pairs read layer 0: a valid address, their term is dropped)
+   const int ca0 = lcl[a0], cb0 = b0 < 0 ? cfor : lcl[max(b0, 0)];
+   const int ca1 = a1 < 0 ? cfor : lcl[max(a1, 0)], cb1 = lcl[b1];
+   const int ca2 = lcl[has2 ? a2 : 0], cb2 = lcl[has2 ? b2 : 0];
+   const int ca3 = lcl[has3 ? a3 : 0], cb3 = lcl[has3 ? b3 : 0];
+   const int e0 = s.minF[s0], e1 = s.minBrev[S - sK], e2 = s.pd[p1], e3 = s.pd[p0];
+   const int d0 = s.dmin[ca0 * C + cb0], d1 = s.dmin[ca1 * C + cb1], d2 = s.dmin[ca2 * C + cb2], d3 = s.dmin[ca3 * C + cb3];
+   return (e0 + e1) + (e2 - e3) + (d0 + d1) + ((has2 ? d2 : 0) + (has3 ? d3 : 0));
 }
 
 // ---- one proposal by one sub-warp group of G lanes (lane = destination sample; mp <= G) ----------------------------------
