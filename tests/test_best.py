@@ -28,8 +28,16 @@ def eng_cache():
         e.close()
 
 
+@pytest.fixture(params=["rescan", "products"])
+def apply_form(request, monkeypatch):
+    """how an accepted move reaches the DP rows: the one-block sequential re-scan, or every layer in parallel from the segment
+    products of the new state (the default from 256 clusters on)"""
+    monkeypatch.setenv("VNSGPU_APPLY_PRODUCTS", "1" if request.param == "products" else "0")
+    return request.param
+
+
 @pytest.mark.parametrize("name", ALL)
-def test_greedy_batched_builds_the_reference_tour(name, golden, eng_cache):
+def test_greedy_batched_builds_the_reference_tour(name, golden, eng_cache, apply_form):
     """greedy_insertion (vns_sop_solver.cpp:1091-1155) with each round as one batched evaluation + device arg-min"""
     e, sf, pb = eng_cache(name)
     g, a = golden[name], load_arrays(name)
@@ -98,7 +106,7 @@ def apply_on_vector(vns, T, kind, fr, to):
 
 
 @pytest.mark.parametrize("name", SMALL)
-def test_best_move_is_the_brute_force_choice(name, golden, eng_cache):
+def test_best_move_is_the_brute_force_choice(name, golden, eng_cache, apply_form):
     from oracle import binding as ob
     e, sf, pb = eng_cache(name)
     g, a = golden[name], load_arrays(name)
@@ -135,7 +143,7 @@ def test_best_move_is_the_brute_force_choice(name, golden, eng_cache):
 
 
 @pytest.mark.parametrize("name", SMALL)
-def test_best_improvement_descent(name, golden, eng_cache):
+def test_best_improvement_descent(name, golden, eng_cache, apply_form):
     from oracle import binding as ob
     e, sf, pb = eng_cache(name)
     o = ob.Oracle(pb)
@@ -151,13 +159,18 @@ def test_best_improvement_descent(name, golden, eng_cache):
     assert p.best_move(1).index == -1 and p.best_move(2).index == -1
     po = o.path(p.vns, p.getNumTargets())
     assert po.length() == l1 and po.reward() == r1
+    F, B = p.layers()
+    oF, oB = po.layers()[:2]
+    for l in range(p.getNumTargets() + 2):
+        k = pb.m[pb.start if l == 0 else (pb.goal if l == p.getNumTargets() + 1 else p.vns[l - 1])]
+        assert (F[l, :k] == oF[l, :k]).all() and (B[l, :k] == oB[l, :k]).all(), l
     # the descent is deterministic
     q = e.path()
     q.greedy_insertion_batched()
     assert q.best_improvement() == (steps, evals) and (q.vns == p.vns).all()
 
 
-def test_synthetic_2000_nodes_greedy_and_descent():
+def test_synthetic_2000_nodes_greedy_and_descent(apply_form):
     """2000 nodes / 200 clusters: the batched greedy equals the one-block greedy; the descent improves the tour"""
     from vns_sop_b200 import engine, instances as ins, synthetic as sy
     pb = ins.build_problem(sy.generate(2000, 10))

@@ -155,6 +155,49 @@ static __global__ void __launch_bounds__(VNS_CHAIN_THREADS) k_apply_move(InstDev
    if (threadIdx.x == 0) { P.hdr[HDR_T] = T; P.hd[HD_REWARD] = path_reward(I, P.tg, T); }
 }
 
+// the same move as a splice of the VNS vector and the targets only (T, reward, the goal's zero row of B): the rows come
+// from the segment products afterwards (path_rows_from_products) - all layers in parallel instead of the sequential re-scan
+static __global__ void __launch_bounds__(VNS_CHAIN_THREADS) k_splice_move(InstDev I, PathDev P, const BestRec *rec, int from_arg, int to_arg, int kind_arg)
+{
+   __shared__ int s_c;
+   int from = from_arg, to = to_arg, kind = kind_arg;
+   if (rec) {
+      if (rec->idx < 0) return;
+      from = rec->from; to = rec->to; kind = rec->kind;
+   }
+   int T = P.hdr[HDR_T];
+   if (threadIdx.x == 0) s_c = P.vns[from];
+   __syncthreads();
+   const int c = s_c;
+   if (kind == 2) {
+      if (threadIdx.x == 0) {
+         const int ct = P.vns[to];
+         P.vns[to] = c; P.vns[from] = ct;
+         P.tg[to] = c;
+         if (from < T) P.tg[from] = ct;
+      }
+   } else if (from < T) {
+      if (to > from) {
+         cta_shift(P.vns, from + 1, to - 1 - from, -1);
+         cta_shift(P.tg, from + 1, to - 1 - from, -1);
+         if (threadIdx.x == 0) { P.vns[to - 1] = c; P.tg[to - 1] = c; }
+      } else {
+         cta_shift(P.vns, to, from - to, +1);
+         cta_shift(P.tg, to, from - to, +1);
+         if (threadIdx.x == 0) { P.vns[to] = c; P.tg[to] = c; }
+      }
+   } else {
+      cta_shift(P.vns, to, from - to, +1);
+      cta_shift(P.tg, to, T - to, +1);
+      if (threadIdx.x == 0) { P.vns[to] = c; P.tg[to] = c; }
+      T += 1;
+      const int mS = I.m[I.goal];
+      for (int j = threadIdx.x; j < mS; j += blockDim.x) P.B[(size_t)(T + 1) * I.mp + j] = 0.0;   // the goal layer moved up by one
+   }
+   __syncthreads();
+   if (threadIdx.x == 0) { P.hdr[HDR_T] = T; P.hd[HD_REWARD] = path_reward(I, P.tg, T); }
+}
+
 // ---- host side --------------------------------------------------------------------------------------------------------------
 struct BestBufs {
    vnsgpu_cand *cands;
@@ -188,7 +231,7 @@ static vnsgpu_status best_bufs(vnsgpu_ctx *ctx, long long n, BestBufs *b)
 
 // evaluate neighbourhood `kind` (0 greedy grid, 1 insert, 2 exchange) of the path's current state and reduce it; the
 // record stays on the device (b->rec) and is copied to *out
-static vnsgpu_status best_step(vnsgpu_ctx *ctx, int path, int kind, double budget, BestBufs *b, BestRec *out, long long *n_out)
+static vnsgpu_status best_step(vnsgpu_ctx *ctx, int path, int kind, double budget, BestBufs *b, BestRec *out, long long *n_out, bool fresh = false)
 {
    PathHdr h;
    vnsgpu_status s = read_hdr(ctx, path, &h);
@@ -207,7 +250,9 @@ static vnsgpu_status best_step(vnsgpu_ctx *ctx, int path, int kind, double budge
    const int grid = (int)std::min<long long>((n + 255) / 256, 2048);
    k_nbh_cands<<<grid, 256, 0, ctx->stream>>>(P, kind, n, b->cands);
    LAUNCHED(ctx);
+   ctx->seg_fresh_path = fresh ? path : -1;      // the products path_rows_from_products built for this very state
    s = vnsgpu_eval_batch_dev(ctx, path, n, b->cands, budget, 0, b->len, nullptr, kind == 0 ? nullptr : b->flags, nullptr, ctx->stream);
+   ctx->seg_fresh_path = -1;
    if (s) return s;
    if (kind == 0)
       k_best_reduce<0><<<grid, 256, 0, ctx->stream>>>(ctx->I, P, kind, n, b->cands, b->len, b->flags, budget, b->partial, b->ticket, b->rec);
@@ -219,8 +264,26 @@ static vnsgpu_status best_step(vnsgpu_ctx *ctx, int path, int kind, double budge
    return VNSGPU_OK;
 }
 
-static vnsgpu_status apply_rec(vnsgpu_ctx *ctx, int path, const BestRec *d_rec, int from, int to, int kind)
+// true: the move was applied through the products, which are current for the next evaluation of this state
+static bool apply_uses_products(const vnsgpu_ctx *ctx)
 {
+   // the sequential re-scan of one block is T dependent layer steps (~0.5 us each); the products cost a few launches:
+   // worth it from a few hundred layers on
+   if (const char *e = getenv("VNSGPU_APPLY_PRODUCTS")) return path_products_available(ctx) && atoi(e) != 0;   // tests: force either form
+   return path_products_available(ctx) && ctx->I.C >= 256;
+}
+
+static vnsgpu_status apply_rec(vnsgpu_ctx *ctx, int path, const BestRec *d_rec, int from, int to, int kind, bool *fresh)
+{
+   *fresh = false;
+   if (apply_uses_products(ctx)) {
+      k_splice_move<<<1, VNS_CHAIN_THREADS, 0, ctx->stream>>>(ctx->I, ctx->paths[path].d, d_rec, from, to, kind);
+      LAUNCHED(ctx);
+      vnsgpu_status s = path_rows_from_products(ctx, path, ctx->stream);
+      if (s) return s;
+      *fresh = true;
+      return VNSGPU_OK;
+   }
    k_apply_move<<<1, VNS_CHAIN_THREADS, 0, ctx->stream>>>(ctx->I, ctx->paths[path].d, d_rec, from, to, kind);
    LAUNCHED(ctx);
    ctx->paths[path].hdr_ok = false;
@@ -235,15 +298,16 @@ vnsgpu_status vnsgpu_greedy_batched(vnsgpu_ctx *ctx, int path, double budget, in
    if (!path_ok(ctx, path)) return VNSGPU_E_STATE;
    int nr = 0;
    int64_t ne = 0;
+   bool fresh = false;
    for (;;) {
       BestBufs b;
       BestRec r;
       long long n = 0;
-      vnsgpu_status s = best_step(ctx, path, 0, budget, &b, &r, &n);
+      vnsgpu_status s = best_step(ctx, path, 0, budget, &b, &r, &n, fresh);
       if (s) return s;
       ne += n;
       if (r.idx < 0) break;                                              // :1129
-      s = apply_rec(ctx, path, b.rec, 0, 0, 0);
+      s = apply_rec(ctx, path, b.rec, 0, 0, 0, &fresh);
       if (s) return s;
       ++nr;
    }
@@ -279,7 +343,8 @@ vnsgpu_status vnsgpu_apply_move(vnsgpu_ctx *ctx, int path, int kind, int from, i
    if (s) return s;
    const int T = h.hdr[HDR_T], nvns = h.hdr[HDR_NVNS], gap = kind == 1 ? 1 : 2, tohi = kind == 1 ? T : T - 1;
    if (from < 0 || from >= nvns || to < 0 || to > tohi || std::abs(from - to) <= gap) return fail(ctx, VNSGPU_E_RANGE, "move outside the neighbourhood");
-   s = apply_rec(ctx, path, nullptr, from, to, kind);
+   bool fresh = false;
+   s = apply_rec(ctx, path, nullptr, from, to, kind, &fresh);
    if (s) return s;
    return check_path_err(ctx, path);
 }
@@ -291,15 +356,16 @@ vnsgpu_status vnsgpu_best_improvement(vnsgpu_ctx *ctx, int path, double budget, 
    int ns = 0;
    int64_t ne = 0;
    int kind = 1, failed = 0;
+   bool fresh = false;
    while (failed < 2 && (max_steps <= 0 || ns < max_steps)) {
       BestBufs b;
       BestRec r;
       long long n = 0;
-      vnsgpu_status s = best_step(ctx, path, kind, budget, &b, &r, &n);
+      vnsgpu_status s = best_step(ctx, path, kind, budget, &b, &r, &n, fresh);
       if (s) return s;
       ne += n;
-      if (r.idx < 0) { ++failed; kind = 3 - kind; continue; }
-      s = apply_rec(ctx, path, b.rec, 0, 0, 0);
+      if (r.idx < 0) { ++failed; kind = 3 - kind; continue; }      // the state did not change: the products stay current
+      s = apply_rec(ctx, path, b.rec, 0, 0, 0, &fresh);
       if (s) return s;
       ++ns;
       failed = 0;

@@ -114,6 +114,7 @@ struct vnsgpu_ctx {
    void *h_pick = nullptr;        // pinned record vnsgpu_propose_eval reads back
    void *d_gen = nullptr, *d_gencands = nullptr;
    size_t gen_bytes = 0, gencands_bytes = 0;
+   int seg_fresh_path = -1;       // set by best.cu right before an evaluation call: the products of this path's state are current
    void *d_best = nullptr;        // full-neighbourhood modes (best.cu): descriptors, lengths, flags, partial keys
    size_t best_bytes = 0;
    bool phase_timing = false;     // vnsgpu_set_phase_timing: CUDA events around the phases of the batched evaluation call
@@ -232,6 +233,10 @@ struct PhaseTimer {
    }
 };
 
+// internal entry points of api_path.cu used by best.cu: every F / B row of a path from the segment products of its current
+// targets (all layers in parallel; integer tables)
+bool path_products_available(const vnsgpu_ctx *ctx);
+vnsgpu_status path_rows_from_products(vnsgpu_ctx *ctx, int path, cudaStream_t st);
 // internal entry points of api_path.cu used by gen.cu: evaluation of device candidates for the first accepted index only;
 // format 0 = vnsgpu_cand, 2 = vnsgpu_pack_cand32 words (only when eval_dev_accepts_packed32 says so)
 bool eval_dev_accepts_packed32(const vnsgpu_ctx *ctx, int64_t n);
