@@ -129,16 +129,17 @@ vnsgpu_status vnsgpu_set_u16_table(vnsgpu_ctx *ctx, int enable);
 /* vnsgpu_local_search keeps the whole search state in one SM's shared memory when it fits (clusters <=
  * 510, samples per cluster <= 32); enable = 0 forces the global-memory chain (tests run both). */
 vnsgpu_status vnsgpu_set_smem_chain(vnsgpu_ctx *ctx, int enable);
-/* Form of the shared-memory chain on all-integer tables.  -1 (default): the third form when the whole distance table
- * fits one SM's shared memory (N^2 int32 or uint16 entries + the search state below ~220 KB: every shipped OPN / DOP
- * instance up to 12 headings and the ~200-node GTSP instances), else the first form below 96 clusters, the second from
- * there on.  0 (or 2): the second form - the lower bound of every
+/* Form of the shared-memory chain on all-integer tables.  -1 (default): the third form below 96 clusters, or when the whole
+ * distance table fits one SM's shared memory (N^2 int32 or uint16 entries + the search state below ~220 KB: every shipped
+ * OPN / DOP instance up to 12 headings and the ~200-node GTSP instances); the second form from 96 clusters on; the first
+ * form for what is left (cluster sizes beyond 32, real-valued tables).  0 (or 2): the second form - the lower bound of every
  * proposal first (one thread each, O(1) from prefix sums along the path), only the survivors are evaluated, up to 256
  * draw pairs per thread block and round, shake + fitDOPtoBudget in shared memory as well, product tree, cooperating
  * thread blocks, instances beyond shared memory.  1: the first form (one sub-warp group per proposal, 64 proposals per
  * round).  3: the third form - table, cluster-pair minima and state all in shared memory, every warp derives the
  * round's window itself (no compaction barrier), bookkeeping replicated in registers, generator running ahead during
- * the re-scan; falls back to the default choice when the table does not fit.  Same trajectory in every form (tests
+ * the re-scan; below 96 clusters a table that does not fit stays in global memory (read-only path) and the rest is the same;
+ * otherwise falls back to the default choice.  Same trajectory in every form (tests
  * run all of them). */
 vnsgpu_status vnsgpu_set_chain_form(vnsgpu_ctx *ctx, int form);
 /* Thread blocks that cooperate on ONE trajectory-exact chain (second form; cooperative launch).  Every block holds a

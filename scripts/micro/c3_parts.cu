@@ -12,7 +12,7 @@ __global__ void __launch_bounds__(C3_THREADS) k_parts(C3Env E, const int *lcl_g,
 {
    extern __shared__ __align__(16) unsigned char smem_c[];
    typedef int TT;
-   const C3Sm<TT> s = c3_carve<TT>(smem_c, E.I);
+   const C3Sm<TT> s = c3_carve<TT>(smem_c, E.I, E.tab_g);
    c3_load_tables(E, s);
    const int S = T + 1, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
    for (int l = threadIdx.x; l <= S; l += blockDim.x) s.lcl[l] = lcl_g[l];

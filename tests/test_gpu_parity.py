@@ -127,21 +127,22 @@ def test_greedy_insertion(name, golden, eng_cache):
     assert p.getPathLength() == g["greedy"]["length"] and p.getReward() == g["greedy"]["reward"]
 
 
-CHAIN_MODES = ["smem-tab", "smem-tab-u16", "smem-int", "smem-int-tree", "smem-int-grid3", "smem-int-grid8-tree", "smem-int-v1", "smem-double", "global"]
+CHAIN_MODES = ["smem-tab", "smem-tab-u16", "smem-tab-g32", "smem-tab-g16", "smem-int", "smem-int-tree", "smem-int-grid3", "smem-int-grid8-tree", "smem-int-v1", "smem-double", "global"]
 
 
 def _set_chain_mode(e, mode):
     """smem-int: second chain form (lower bound first), one thread block; -gridN: N cooperating thread blocks;
     -tree: with the product tree forced on (default: off below 96 clusters); -v1: first form; smem-double: first form
     in IEEE double; global: global-memory chain; smem-tab: third form (the whole distance table in shared memory, as
-    int32 when that fits, else as uint16), -u16: its uint16 copy forced (instances without one take another form)"""
+    int32 when that fits, else as uint16), -u16: its uint16 copy forced (instances without one take another form), -g32 /
+    -g16: the table read from global memory (int32 / uint16 copy), state in shared memory"""
     import os
     e.set_smem_chain(mode != "global")
     e.set_int_path(mode != "smem-double")
     e.set_chain_form(3 if mode.startswith("smem-tab") else (1 if mode == "smem-int-v1" else 0))
     os.environ.pop("VNSGPU_CHAIN3_U16", None)
-    if mode == "smem-tab-u16":
-        os.environ["VNSGPU_CHAIN3_U16"] = "1"
+    if mode in ("smem-tab-u16", "smem-tab-g32", "smem-tab-g16"):      # variant: bit 0 uint16 copy, bit 1 table read from global memory
+        os.environ["VNSGPU_CHAIN3_U16"] = {"smem-tab-u16": "1", "smem-tab-g32": "2", "smem-tab-g16": "3"}[mode]
     e.set_chain_blocks(int(mode.split("grid")[1].split("-")[0]) if "grid" in mode else 1)
     e.set_chain_tree(1 if "tree" in mode else (0 if mode.startswith("smem-int") else -1))
 

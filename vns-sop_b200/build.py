@@ -14,7 +14,7 @@ NVCC_FLAGS = [
 ]
 # translation units of the library (each compiled on its own core, then linked; no relocatable device code: no kernel
 # calls a device function of another unit)
-UNITS = ["vnsgpu.cu", "api_path.cu", "api_search.cu", "chain2.cu", "chain2_k8.cu", "chain2_k16.cu", "chain3.cu", "best.cu", "comm.cu", "noalloc.cu", "measure.cu", "gen.cu"]
+UNITS = ["vnsgpu.cu", "api_path.cu", "api_search.cu", "chain2.cu", "chain2_k8.cu", "chain2_k16.cu", "chain3.cu", "chain3_g.cu", "best.cu", "comm.cu", "noalloc.cu", "measure.cu", "gen.cu"]
 OBJ = os.path.join(HERE, "build")
 
 

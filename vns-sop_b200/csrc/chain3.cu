@@ -1,15 +1,14 @@
 // Host side + kernel instantiations of the third search chain (chain3.cuh): the whole distance table in one SM's shared
 // memory.  Called from api_search.cu.
-#include "ctx.hpp"
-#include "path.cuh"
-#include "search.cuh"
-#include "eval.cuh"
-#include "chain3.cuh"
+#include "chain3_kernels.inl"
 #include "chain2_host.hpp"
 
-// fits when the int32 table (or its uint16 copy) plus the search state stay below the opt-in shared memory of one
-// block.  chain_form: -1 (default) takes this form whenever it fits; 3 forces it; 0 / 1 / 2 name the other forms.
-bool c3_fits(const vnsgpu_ctx *ctx, size_t *smem, int *u16)
+// variant: bit 0 = the uint16 copy of the table, bit 1 = the table stays in global memory (read-only path).
+// Shared-memory table: when the int32 table (or its uint16 copy) plus the search state stay below the opt-in shared memory of
+// one block.  Global table: instances below 96 clusters whose table does not fit (from 96 clusters on the second form's
+// product tree wins).  chain_form: -1 (default) takes this form whenever one of the two applies; 3 forces it; 0 / 1 / 2 name
+// the other forms.
+bool c3_fits(const vnsgpu_ctx *ctx, size_t *smem, int *variant)
 {
    const bool want = ctx->chain_form == 3 || ctx->chain_form < 0;
    if (!want || !ctx->use_smem_chain || !vnsgpu_int_path_active(ctx) || ctx->I.mp > 32) return false;
@@ -17,18 +16,21 @@ bool c3_fits(const vnsgpu_ctx *ctx, size_t *smem, int *u16)
    // static shared memory of the kernels (control block, generator state, the few words of search.cuh's helpers) + margin
    const size_t fixed = sizeof(C3Ctl) + sizeof(RngState) + 2048;
    const size_t greedy = sizeof(double) * 2 * ctx->I.mp * C3_WARPS;       // the greedy start borrows the table's place
-   const int forced = getenv("VNSGPU_CHAIN3_U16") ? atoi(getenv("VNSGPU_CHAIN3_U16")) : -1;   // tests: force a copy
-   for (int w = 0; w < 2; ++w) {
-      if (forced >= 0 && w != (forced & 1)) continue;
-      if (w == 1 && !(ctx->d_D16 && ctx->use_u16)) continue;
-      const size_t b = std::max(c3_smem_bytes(ctx->I.C, ctx->I.N, ctx->I.mp, w ? 2 : 4), greedy);
-      if (b + fixed <= (size_t)ctx->max_smem) { *smem = b; *u16 = w; return true; }
+   const int forced = getenv("VNSGPU_CHAIN3_U16") ? atoi(getenv("VNSGPU_CHAIN3_U16")) : -1;   // tests: force a variant (0 .. 3)
+   for (int v = 0; v < 4; ++v) {
+      if (forced >= 0 && v != (forced & 3)) continue;
+      const bool u16 = v & 1, tg = (v & 2) != 0;
+      if (u16 && !(ctx->d_D16 && ctx->use_u16)) continue;
+      if (tg && forced < 0 && (ctx->I.C >= 96 || (!u16 && ctx->d_D16 && ctx->use_u16))) continue;   // global: the smaller copy when there is one
+      const size_t b = std::max(c3_smem_bytes(ctx->I.C, ctx->I.N, ctx->I.mp, u16 ? 2 : 4, tg), greedy);
+      if (b + fixed <= (size_t)ctx->max_smem) { *smem = b; *variant = v; return true; }
    }
    return false;
 }
 
-static vnsgpu_status c3_prepare(vnsgpu_ctx *ctx, C3Env *E, int u16)
+static vnsgpu_status c3_prepare(vnsgpu_ctx *ctx, C3Env *E, int variant)
 {
+   const int u16 = variant & 1;
    vnsgpu_status s = c2_ensure_tables(ctx);
    if (s) return s;
    E->I = ctx->I;
@@ -38,34 +40,17 @@ static vnsgpu_status c3_prepare(vnsgpu_ctx *ctx, C3Env *E, int u16)
    return VNSGPU_OK;
 }
 
-template <typename K> static vnsgpu_status c3k_launch(vnsgpu_ctx *ctx, K kernel, int nblocks, size_t smem, void **args)
-{
-   CK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-   CK(cudaLaunchKernel((const void *)kernel, dim3(nblocks), dim3(C3_THREADS), args, smem, ctx->stream));
-   LAUNCHED(ctx);
-   return VNSGPU_OK;
-}
+// kernels with the table in global memory: chain3_g.cu
+vnsgpu_status c3k_pick_global(vnsgpu_ctx *ctx, int u16, int G, int which, int nblocks, size_t smem, void **args);
 
-// which: 0 k_chain3_ls, 1 k_chain3_vns_run, 2 k_chain3_vns_multi
-template <typename TT, int G> static vnsgpu_status c3k_pick(vnsgpu_ctx *ctx, int which, int nblocks, size_t smem, void **args)
-{
-   if (which == 0) return c3k_launch(ctx, k_chain3_ls<TT, G>, nblocks, smem, args);
-   if (which == 1) return c3k_launch(ctx, k_chain3_vns_run<TT, G>, nblocks, smem, args);
-   return c3k_launch(ctx, k_chain3_vns_multi<TT, G>, nblocks, smem, args);
-}
-
-static vnsgpu_status c3_dispatch(vnsgpu_ctx *ctx, int u16, int which, int nblocks, size_t smem, void **args)
+static vnsgpu_status c3_dispatch(vnsgpu_ctx *ctx, int variant, int which, int nblocks, size_t smem, void **args)
 {
    int G = ctx->I.mp <= 8 ? 8 : (ctx->I.mp <= 16 ? 16 : 32);              // one register per lane: the group holds the largest cluster
    if (const char *e = getenv("VNSGPU_CHAIN_G")) { const int g = atoi(e); if ((g == 8 || g == 16 || g == 32) && g >= G) G = g; }
-   if (u16) {
-      if (G == 8) return c3k_pick<unsigned short, 8>(ctx, which, nblocks, smem, args);
-      if (G == 16) return c3k_pick<unsigned short, 16>(ctx, which, nblocks, smem, args);
-      return c3k_pick<unsigned short, 32>(ctx, which, nblocks, smem, args);
-   }
-   if (G == 8) return c3k_pick<int, 8>(ctx, which, nblocks, smem, args);
-   if (G == 16) return c3k_pick<int, 16>(ctx, which, nblocks, smem, args);
-   return c3k_pick<int, 32>(ctx, which, nblocks, smem, args);
+   if (variant == 0) C3_PICK(int);
+   if (variant == 1) C3_PICK(unsigned short);
+   return c3k_pick_global(ctx, variant & 1, G, which, nblocks, smem, args);
+#undef C3_PICK
 }
 
 vnsgpu_status c3_launch_ls(vnsgpu_ctx *ctx, int path, int kind, int num_changes, double budget, int skip, size_t smem, int u16)

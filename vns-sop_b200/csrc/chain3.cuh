@@ -33,6 +33,13 @@
 #define C3_INF VNS_INT_INF
 #define C3_NONE 0x7fffffff
 
+// Where the distance table is read from: TT = int / unsigned short -> a copy in shared memory; C3G<int> / C3G<unsigned short> ->
+// the table in global memory through the read-only path (ld.global.nc: L1 hit latency is that of shared memory; instances
+// whose table does not fit beside the state, e.g. 21 clusters x 16 headings = 226 KB as uint16).  Everything else is the same.
+template <typename E> struct C3G {};
+template <typename TT> struct C3TT { typedef TT elem; typedef unsigned addr; static constexpr bool global = false; };
+template <typename E> struct C3TT<C3G<E>> { typedef E elem; typedef unsigned long long addr; static constexpr bool global = true; };
+
 struct C3Ctl {
    int T, nvns, L, err;
    int bad;                  // a proposal decoded to no chain (impossible by construction)
@@ -44,7 +51,7 @@ struct C3Ctl {
 };
 
 template <typename TT> struct C3Sm {
-   const TT *tab;            // N x N, block-major
+   const typename C3TT<TT>::elem *tab;   // N x N, block-major (shared-memory copy, or the global table)
    const int *dmin;          // C x C cluster-pair minima
    const double *reward;     // C
    const int2 *cinfo;        // C: {first sample, size}
@@ -64,10 +71,10 @@ template <typename TT> struct C3Sm {
 // entries) without clamping; rows beyond a block pair an INF sample with whatever follows the block (table entries or
 // this padding: all in [0, 2^29))
 __host__ __device__ inline size_t c3_tab_bytes(int N, int mp, int esz) { return (((size_t)N * N + 32 * (size_t)mp + 32) * esz + 15) & ~(size_t)15; }
-__host__ __device__ inline size_t c3_smem_bytes(int C, int N, int mp, int esz)
+__host__ __device__ inline size_t c3_smem_bytes(int C, int N, int mp, int esz, bool table_in_global = false)
 {
    const size_t R = C + 3, mpp = mp < 2 ? 2 : mp;
-   size_t b = c3_tab_bytes(N, mp, esz);
+   size_t b = table_in_global ? 0 : c3_tab_bytes(N, mp, esz);
    b += ((size_t)C * C * sizeof(int) + 7) & ~(size_t)7;
    b += (size_t)C * sizeof(double) + (size_t)C * sizeof(int2);
    b += sizeof(int) * (2 * R * mpp + 8 * R + 8 + 32 * C3_MAXCH) + sizeof(unsigned) * C3_RING;
@@ -75,13 +82,18 @@ __host__ __device__ inline size_t c3_smem_bytes(int C, int N, int mp, int esz)
    return b + 16;
 }
 
-template <typename TT> static __device__ __forceinline__ C3Sm<TT> c3_carve(unsigned char *base, const InstDev &I)
+template <typename TT> static __device__ __forceinline__ C3Sm<TT> c3_carve(unsigned char *base, const InstDev &I, const void *tab_g)
 {
+   typedef typename C3TT<TT>::elem EL;
    const size_t R = I.C + 3, mpp = I.mp < 2 ? 2 : I.mp;
    C3Sm<TT> s;
    s.N = I.N; s.C = I.C; s.mp = I.mp;
-   s.tab = reinterpret_cast<const TT *>(base);
-   base += c3_tab_bytes(I.N, I.mp, sizeof(TT));
+   if (C3TT<TT>::global)
+      s.tab = reinterpret_cast<const EL *>(tab_g);
+   else {
+      s.tab = reinterpret_cast<const EL *>(base);
+      base += c3_tab_bytes(I.N, I.mp, sizeof(EL));
+   }
    s.dmin = reinterpret_cast<const int *>(base);
    base += ((size_t)I.C * I.C * sizeof(int) + 7) & ~(size_t)7;
    s.reward = reinterpret_cast<const double *>(base);
@@ -115,17 +127,18 @@ struct C3Env {
 // instance constants -> shared memory (once per kernel); all threads
 template <typename TT> static __device__ void c3_load_tables(const C3Env &E, const C3Sm<TT> &s)
 {
+   typedef typename C3TT<TT>::elem EL;
    const InstDev &I = E.I;
-   {  // table: 16-byte words (both copies are allocated with slack behind the last entry)
-      const size_t n16 = ((size_t)I.N * I.N * sizeof(TT) + 15) / 16, all16 = c3_tab_bytes(I.N, I.mp, sizeof(TT)) / 16;
+   if (!C3TT<TT>::global) {  // table: 16-byte words (both copies are allocated with slack behind the last entry)
+      const size_t n16 = ((size_t)I.N * I.N * sizeof(EL) + 15) / 16, all16 = c3_tab_bytes(I.N, I.mp, sizeof(EL)) / 16;
       const int4 *src = reinterpret_cast<const int4 *>(E.tab_g);
-      int4 *dst = reinterpret_cast<int4 *>(const_cast<TT *>(s.tab));
+      int4 *dst = reinterpret_cast<int4 *>(const_cast<EL *>(s.tab));
       for (size_t k = threadIdx.x; k < n16; k += blockDim.x) dst[k] = __ldg(src + k);
       for (size_t k = n16 + threadIdx.x; k < all16; k += blockDim.x) dst[k] = make_int4(0, 0, 0, 0);
       __syncthreads();
       // the last 16-byte word of the copy may carry bytes from behind the table: make them zeros as well
-      TT *tw = const_cast<TT *>(s.tab);
-      for (size_t k = (size_t)I.N * I.N + threadIdx.x; k < n16 * (16 / sizeof(TT)); k += blockDim.x) tw[k] = 0;
+      EL *tw = const_cast<EL *>(s.tab);
+      for (size_t k = (size_t)I.N * I.N + threadIdx.x; k < n16 * (16 / sizeof(EL)); k += blockDim.x) tw[k] = 0;
    }
    int *dm = const_cast<int *>(s.dmin);
    for (int k = threadIdx.x; k < I.C * I.C; k += blockDim.x) dm[k] = __ldg(E.dmin_g + k);
@@ -183,7 +196,7 @@ template <typename TT> static __device__ __forceinline__ void c3_fwd_layer(const
    const unsigned w = c3_edge_word(s, s.lcl[l - 1], s.lcl[l]);
    const int ma = (w >> 20) & 63, mb = w >> 26;
    const int v = lane < ma ? s.F[(l - 1) * mp + lane] : C3_INF;
-   int acc = c3_block<TT, 32>(s.tab + (w & 0xfffffu) + min(lane, mb - 1), mb, v, ma);
+   int acc = c3_block<typename C3TT<TT>::elem, 32>(s.tab + (w & 0xfffffu) + min(lane, mb - 1), mb, v, ma);
    acc = lane < mb ? acc : C3_INF;
    if (lane < mb) s.F[l * mp + lane] = acc;
    const int mn = __reduce_min_sync(FULL, acc);
@@ -217,7 +230,8 @@ static __device__ __forceinline__ int c3_lds(unsigned a)
    return v;
 }
 static __device__ __forceinline__ void c3_sts(unsigned a, int v) { asm volatile("st.shared.s32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
-template <typename TT> static __device__ __forceinline__ int c3_ldt(unsigned a);
+static __device__ __forceinline__ unsigned long long c3_keep(unsigned long long x) { asm volatile("" : "+l"(x)); return x; }
+template <typename TT> static __device__ __forceinline__ int c3_ldt(typename C3TT<TT>::addr a);
 template <> __device__ __forceinline__ int c3_ldt<int>(unsigned a) { return c3_lds(a); }
 template <> __device__ __forceinline__ int c3_ldt<unsigned short>(unsigned a)
 {
@@ -225,10 +239,28 @@ template <> __device__ __forceinline__ int c3_ldt<unsigned short>(unsigned a)
    asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(a));
    return v;
 }
+template <> __device__ __forceinline__ int c3_ldt<C3G<int>>(unsigned long long a)
+{
+   int v;
+   asm volatile("ld.global.nc.s32 %0, [%1];" : "=r"(v) : "l"(a));
+   return v;
+}
+template <> __device__ __forceinline__ int c3_ldt<C3G<unsigned short>>(unsigned long long a)
+{
+   int v;
+   asm volatile("ld.global.nc.u16 %0, [%1];" : "=r"(v) : "l"(a));
+   return v;
+}
+// address of the table as the loops use it (shared window offset, or the 64-bit global address), held in a register
+template <typename TT> static __device__ __forceinline__ typename C3TT<TT>::addr c3_tab_addr(const void *tab)
+{
+   if (C3TT<TT>::global) return (typename C3TT<TT>::addr)c3_keep((unsigned long long)tab);
+   return (typename C3TT<TT>::addr)c3_keep(c3_saddr(tab));
+}
 
 // rows t0 .. t0 + 7 of a block (unclamped) against the shuffled samples: the tail of blocks with more than eight rows
 template <typename TT, int W>
-static __device__ __forceinline__ void c3_rows8(unsigned pa, unsigned strideB, int v, int t0, int &a0, int &a1)
+static __device__ __forceinline__ void c3_rows8(typename C3TT<TT>::addr pa, unsigned strideB, int v, int t0, int &a0, int &a1)
 {
    constexpr unsigned FULL = 0xffffffffu;
    int d[8], x[8];
@@ -243,19 +275,21 @@ static __device__ __forceinline__ void c3_rows8(unsigned pa, unsigned strideB, i
 template <typename TT> static __device__ void c3_fwd_scan(const C3Sm<TT> &s, int S, int lf, int lane)
 {
    constexpr unsigned FULL = 0xffffffffu;
-   constexpr int ES = (int)sizeof(TT);
+   typedef typename C3TT<TT>::addr AT;
+   constexpr int ES = (int)sizeof(typename C3TT<TT>::elem);
    if (lf > S) return;
    const int mp = s.mp;
    for (int l = lf + lane; l <= S; l += 32) s.ew[l] = c3_edge_word(s, s.lcl[l - 1], s.lcl[l]);
    if (lane < 2) s.ew[S + 1 + lane] = C3_EW_NONE;
    __syncwarp();
    lane = (int)c3_keep((unsigned)lane);
-   const unsigned tabA = c3_keep(c3_saddr(s.tab)), mp4 = c3_keep(4u * (unsigned)mp);
+   const AT tabA = c3_tab_addr<TT>(s.tab);
+   const unsigned mp4 = c3_keep(4u * (unsigned)mp);
    unsigned ewp = c3_keep(c3_saddr(s.ew + lf)), frow = c3_keep(c3_saddr(s.F + lf * mp + lane));
    unsigned w = (unsigned)c3_lds(ewp), wn = (unsigned)c3_lds(ewp + 4);
    ewp += 8;
    int v = lane < (int)((w >> 20) & 63) ? c3_lds(frow - mp4) : C3_INF;
-   unsigned pa = tabA + ES * ((w & 0xfffffu) + min(lane, (int)(w >> 26) - 1));
+   AT pa = tabA + ES * ((w & 0xfffffu) + min(lane, (int)(w >> 26) - 1));
    int dd[8];
 #pragma unroll
    for (int t = 0; t < 8; ++t) dd[t] = c3_ldt<TT>(pa + t * ES * (w >> 26));
@@ -267,7 +301,7 @@ template <typename TT> static __device__ void c3_fwd_scan(const C3Sm<TT> &s, int
       const unsigned wn2 = (unsigned)c3_lds(ewp);
       ewp += 4;
       const unsigned sbn = ES * (wn >> 26);
-      const unsigned pn = tabA + ES * ((wn & 0xfffffu) + min(lane, (int)(wn >> 26) - 1));
+      const AT pn = tabA + ES * ((wn & 0xfffffu) + min(lane, (int)(wn >> 26) - 1));
       int dn[8];
 #pragma unroll
       for (int t = 0; t < 8; ++t) dn[t] = c3_ldt<TT>(pn + t * sbn);
@@ -302,19 +336,21 @@ template <typename TT> static __device__ void c3_fwd_scan(const C3Sm<TT> &s, int
 template <typename TT> static __device__ void c3_bwd_scan(const C3Sm<TT> &s, int S, int lb, int lane)
 {
    constexpr unsigned FULL = 0xffffffffu;
-   constexpr int ES = (int)sizeof(TT);
+   typedef typename C3TT<TT>::addr AT;
+   constexpr int ES = (int)sizeof(typename C3TT<TT>::elem);
    if (lb < 0) return;
    const int mp = s.mp;
    for (int l = lb - lane; l >= 0; l -= 32) s.ew[l + 1] = c3_edge_word(s, s.lcl[l], s.lcl[l + 1]);
    if (lane < 2) s.ew[-lane] = C3_EW_NONE;
    __syncwarp();
    lane = (int)c3_keep((unsigned)lane);
-   const unsigned tabA = c3_keep(c3_saddr(s.tab)), mp4 = c3_keep(4u * (unsigned)mp);
+   const AT tabA = c3_tab_addr<TT>(s.tab);
+   const unsigned mp4 = c3_keep(4u * (unsigned)mp);
    unsigned ewp = c3_keep(c3_saddr(s.ew + lb + 1)), brow = c3_keep(c3_saddr(s.Brev + (S - lb) * mp + lane));
    unsigned w = (unsigned)c3_lds(ewp), wn = (unsigned)c3_lds(ewp - 4);
    ewp -= 8;
    int v = lane < (int)(w >> 26) ? c3_lds(brow - mp4) : C3_INF;
-   unsigned pa = tabA + ES * ((w & 0xfffffu) + min(lane, (int)((w >> 20) & 63) - 1) * (w >> 26));
+   AT pa = tabA + ES * ((w & 0xfffffu) + min(lane, (int)((w >> 20) & 63) - 1) * (w >> 26));
    int dd[8];
 #pragma unroll
    for (int t = 0; t < 8; ++t) dd[t] = c3_ldt<TT>(pa + t * ES);
@@ -325,7 +361,7 @@ template <typename TT> static __device__ void c3_bwd_scan(const C3Sm<TT> &s, int
       for (int t = 0; t < 8; ++t) x[t] = __shfl_sync(FULL, v, t);
       const unsigned wn2 = (unsigned)c3_lds(ewp);
       ewp -= 4;
-      const unsigned pn = tabA + ES * ((wn & 0xfffffu) + min(lane, (int)((wn >> 20) & 63) - 1) * (wn >> 26));
+      const AT pn = tabA + ES * ((wn & 0xfffffu) + min(lane, (int)((wn >> 20) & 63) - 1) * (wn >> 26));
       int dn[8];
 #pragma unroll
       for (int t = 0; t < 8; ++t) dn[t] = c3_ldt<TT>(pn + t * ES);
@@ -485,7 +521,8 @@ template <typename TT, int G>
 static __device__ __forceinline__ int c3_eval(const C3Sm<TT> &s, int T, const CandCode &cc, int gl, unsigned *gw)
 {
    constexpr unsigned FULL = 0xffffffffu;
-   constexpr int ES = (int)sizeof(TT);
+   typedef typename C3TT<TT>::addr AT;
+   constexpr int ES = (int)sizeof(typename C3TT<TT>::elem);
    const int S = T + 1, mp = s.mp, N = s.N, K = cc.K;
    int v = C3_INF, bK = C3_INF;
    if (K) {
@@ -512,12 +549,12 @@ static __device__ __forceinline__ int c3_eval(const C3Sm<TT> &s, int T, const Ca
       if (k <= Kmax + 2) gw[k] = w;
    }
    __syncwarp();
-   const unsigned tabA = c3_keep(c3_saddr(s.tab));
+   const AT tabA = c3_tab_addr<TT>(s.tab);
    const int glk = (int)c3_keep((unsigned)gl);
    unsigned gwp = c3_keep(c3_saddr(gw + 1));
    unsigned w = (unsigned)c3_lds(gwp), wn = (unsigned)c3_lds(gwp + 4);
    gwp += 8;
-   unsigned pa = tabA + ES * ((w & 0x7ffffu) + min(glk, (int)(w >> 26) - 1));
+   AT pa = tabA + ES * ((w & 0x7ffffu) + min(glk, (int)(w >> 26) - 1));
    int dd[8];
 #pragma unroll
    for (int t = 0; t < 8; ++t) dd[t] = c3_ldt<TT>(pa + t * ES * (w >> 26));
@@ -529,7 +566,7 @@ static __device__ __forceinline__ int c3_eval(const C3Sm<TT> &s, int T, const Ca
       const unsigned wn2 = (unsigned)c3_lds(gwp);
       gwp += 4;
       const unsigned sbn = ES * (wn >> 26);
-      const unsigned pn = tabA + ES * ((wn & 0x7ffffu) + min(glk, (int)(wn >> 26) - 1));
+      const AT pn = tabA + ES * ((wn & 0x7ffffu) + min(glk, (int)(wn >> 26) - 1));
       int dn[8];
 #pragma unroll
       for (int t = 0; t < 8; ++t) dn[t] = c3_ldt<TT>(pn + t * sbn);
@@ -923,7 +960,7 @@ __global__ void __launch_bounds__(C3_THREADS) k_chain3_ls(C3Env E, PathDev P, in
    extern __shared__ __align__(16) unsigned char smem_c[];
    __shared__ C3Ctl ctl;
    __shared__ RngState g;
-   const C3Sm<TT> s = c3_carve<TT>(smem_c, E.I);
+   const C3Sm<TT> s = c3_carve<TT>(smem_c, E.I, E.tab_g);
    if (threadIdx.x == 0) {
       g = *rng;
       ctl.st = LsStats{0, 0, 0, 0, 0}; ctl.prof[0] = ctl.prof[1] = ctl.prof[2] = ctl.prof[3] = 0; ctl.ema = 16;
@@ -950,7 +987,7 @@ static __device__ void c3_vns_body(const C3Env &E, const PathDev &tour, const Vn
    __shared__ int s_stop, s_improved;
    const InstDev &I = E.I;
    double *vbuf_all = reinterpret_cast<double *>(smem_c);       // greedy scratch (start of the run only): under the table
-   const C3Sm<TT> s = c3_carve<TT>(smem_c, I);
+   const C3Sm<TT> s = c3_carve<TT>(smem_c, I, E.tab_g);
    if (threadIdx.x == 0) {
       g = *rng; s_stop = 0;
       ctl.st = LsStats{0, 0, 0, 0, 0}; ctl.prof[0] = ctl.prof[1] = ctl.prof[2] = ctl.prof[3] = 0; ctl.err = 0; ctl.bad = 0; ctl.ema = 16;

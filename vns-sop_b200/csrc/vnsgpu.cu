@@ -231,10 +231,12 @@ static vnsgpu_status build_table(vnsgpu_ctx *ctx, TableJob J, bool maybe_int)
          CK(cudaMemsetAsync(ctx->d_D32 + nn, 0, extra, ctx->stream));
    }
    if (ctx->d_D16) { CK(cudaFree(ctx->d_D16)); ctx->d_D16 = nullptr; }
-   if (ctx->d_D32 && cudaMalloc(&ctx->d_D16, sizeof(unsigned short) * (size_t)nn + 64) != cudaSuccess) {   // optimistic as well
+   // + 4 KB of zeros: the third search chain reads whole groups of rows without clamping (chain3.cuh)
+   if (ctx->d_D32 && cudaMalloc(&ctx->d_D16, sizeof(unsigned short) * (size_t)nn + 4096) != cudaSuccess) {   // optimistic as well
       cudaGetLastError();
       ctx->d_D16 = nullptr;
    }
+   if (ctx->d_D16) CK(cudaMemsetAsync(ctx->d_D16 + nn, 0, 4096, ctx->stream));
    J.D16 = ctx->d_D16;
    CK(cudaMemsetAsync(ctx->d_info, 0, 2 * sizeof(unsigned long long), ctx->stream));
    J.D = ctx->d_D; J.Di = ctx->d_D32; J.dmin = ctx->d_dmin; J.dmax = ctx->d_dmax; J.info = ctx->d_info;
