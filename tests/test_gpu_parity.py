@@ -45,8 +45,12 @@ def test_table_and_bounds(name, golden, eng_cache):
     assert (lo == a["dmin"]).all() and (hi == a["dmax"]).all()
 
 
+@pytest.mark.parametrize("rows", ["scan", "products"])
 @pytest.mark.parametrize("name", ALL)
-def test_update_and_queries_on_greedy_path(name, golden, eng_cache):
+def test_update_and_queries_on_greedy_path(name, rows, golden, eng_cache, monkeypatch):
+    """update() + the const queries on the reference's greedy tour; rows = how vnsgpu_path_set fills shortest / shortest_back:
+    the sequential scan, or every layer in parallel from the exact segment products (the default from 128 targets on)"""
+    monkeypatch.setenv("VNSGPU_APPLY_PRODUCTS", "1" if rows == "products" else "0")
     e, sf, pb = eng_cache(name)
     g, a = golden[name], load_arrays(name)
     T = g["greedy"]["T"]

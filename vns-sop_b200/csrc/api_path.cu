@@ -80,8 +80,17 @@ vnsgpu_status vnsgpu_path_set(vnsgpu_ctx *ctx, int path, const int *vns, int nvn
    CK(cudaMemcpyAsync(d.hdr, hdr, sizeof(hdr), cudaMemcpyHostToDevice, ctx->stream));
    if (nvns) CK(cudaMemcpyAsync(d.vns, vns, sizeof(int) * nvns, cudaMemcpyHostToDevice, ctx->stream));
    if (T) CK(cudaMemcpyAsync(d.tg, vns, sizeof(int) * T, cudaMemcpyHostToDevice, ctx->stream));
-   k_path_update<<<1, 64, 0, ctx->stream>>>(ctx->I, d);
-   LAUNCHED(ctx);
+   // update() (vns_sop_path.cpp:1321-1404) walks T layers one after the other; on long tours over an integer table every
+   // layer's rows come from the segment products instead, all layers in parallel (VNSGPU_APPLY_PRODUCTS: tests force either)
+   bool par = path_products_available(ctx) && T >= 128;
+   if (const char *e = getenv("VNSGPU_APPLY_PRODUCTS")) par = path_products_available(ctx) && atoi(e) != 0 && T >= 1;
+   if (par) {
+      vnsgpu_status ps = path_rows_from_products(ctx, path, ctx->stream, true);
+      if (ps) return ps;
+   } else {
+      k_path_update<<<1, 64, 0, ctx->stream>>>(ctx->I, d);
+      LAUNCHED(ctx);
+   }
    return check_path_err(ctx, path);
 }
 
@@ -307,6 +316,16 @@ static __global__ void __launch_bounds__(256) k_rows_from_seg(InstDev I, PathDev
    }
 }
 
+// the rows that do not come from a product: F[0] = 0 (heuristic_types.h:184-187), B[S] = 0, and getReward
+static __global__ void __launch_bounds__(64) k_rows_ends(InstDev I, PathDev P)
+{
+   const int T = P.hdr[HDR_T], S = T + 1;
+   const int m0 = I.m[I.start], mS = I.m[I.goal];
+   for (int j = threadIdx.x; j < m0; j += blockDim.x) P.F[j] = 0.0;
+   for (int j = threadIdx.x; j < mS; j += blockDim.x) P.B[(size_t)S * I.mp + j] = 0.0;
+   if (threadIdx.x == 0) P.hd[HD_REWARD] = path_reward(I, P.tg, T);
+}
+
 // addPoint's consistency check (vns_sop_path.cpp:80-88) behind k_rows_from_seg
 static __global__ void k_rows_check(PathDev P)
 {
@@ -508,9 +527,13 @@ bool path_products_available(const vnsgpu_ctx *ctx)
 // targets (and T, F[0], B[S]) of `path` are in place: products of this state, then all rows from them.  A caller that
 // evaluates a batch on the same state next sets ctx->seg_fresh_path = path right before that call: prepare_eval then
 // keeps these products (the flag lives for that one call)
-vnsgpu_status path_rows_from_products(vnsgpu_ctx *ctx, int path, cudaStream_t st)
+vnsgpu_status path_rows_from_products(vnsgpu_ctx *ctx, int path, cudaStream_t st, bool init_ends)
 {
    if (!path_products_available(ctx)) return fail(ctx, VNSGPU_E_STATE, "segment products not available for this table");
+   if (init_ends) {
+      k_rows_ends<<<1, 64, 0, st>>>(ctx->I, ctx->paths[path].d);
+      LAUNCHED(ctx);
+   }
    vnsgpu_status s = prepare_seg(ctx, path, st);
    if (s) return s;
    const int jobs = 2 * (ctx->I.rows + 2);

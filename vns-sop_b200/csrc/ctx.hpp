@@ -236,7 +236,7 @@ struct PhaseTimer {
 // internal entry points of api_path.cu used by best.cu: every F / B row of a path from the segment products of its current
 // targets (all layers in parallel; integer tables)
 bool path_products_available(const vnsgpu_ctx *ctx);
-vnsgpu_status path_rows_from_products(vnsgpu_ctx *ctx, int path, cudaStream_t st);
+vnsgpu_status path_rows_from_products(vnsgpu_ctx *ctx, int path, cudaStream_t st, bool init_ends = false);
 // internal entry points of api_path.cu used by gen.cu: evaluation of device candidates for the first accepted index only;
 // format 0 = vnsgpu_cand, 2 = vnsgpu_pack_cand32 words (only when eval_dev_accepts_packed32 says so)
 bool eval_dev_accepts_packed32(const vnsgpu_ctx *ctx, int64_t n);
