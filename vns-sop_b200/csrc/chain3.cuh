@@ -1,5 +1,6 @@
-// Trajectory-exact search chain, third form: instances whose WHOLE distance table fits one SM's shared memory
-// (exact int32 tables; the table is held as int32 or, when every entry is below 65535, as uint16).
+// Trajectory-exact search chain, third form: small instances (exact int32 tables).  The whole distance table sits in one
+// SM's shared memory as int32 or, when every entry is below 65535, as uint16; a table that does not fit (below 96 clusters)
+// is read from global memory through the read-only path by the same kernels (C3G<> below).
 //
 // insertRandom (vns_sop_solver.cpp:469-684) and exchangeRandom (:686-864) accept one proposal in 5 .. 15 on the shipped
 // instances, so a round of a trajectory-exact chain is ONE accept: draw -> lower bound -> evaluate a dozen dependent
