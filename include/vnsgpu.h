@@ -312,6 +312,12 @@ vnsgpu_status vnsgpu_best_move(vnsgpu_ctx *ctx, int path, int kind, double budge
 /* the accept branch of insertRandom (:621-646, kind 1) / exchangeRandom (:807-832, kind 2) for the pair (from, to):
  * VNS[from] moves in front of index `to` / VNS[from] and VNS[to] swap; F / B re-scanned */
 vnsgpu_status vnsgpu_apply_move(vnsgpu_ctx *ctx, int path, int kind, int from, int to);
+/* Multi-GPU form of the three calls above and of vnsgpu_greedy_batched: with enable != 0 and a communicator (vnsgpu_comm_*)
+ * every rank evaluates one contiguous range of each neighbourhood's enumeration against its replica of the table and the
+ * path, the ranks' best keys (24 bytes each) are all-gathered and every rank picks - and applies - the same move: the
+ * result is the single-GPU one for any number of ranks.  The calls become collective: every rank makes them in the same
+ * order on paths in the same state.  evals / n_candidates then count this rank's share. */
+vnsgpu_status vnsgpu_set_shard_neighbourhoods(vnsgpu_ctx *ctx, int enable);
 /* variable-neighbourhood descent with the two calls above: best insert move until there is none, then best exchange move,
  * back to insert after every applied move; ends when neither neighbourhood improves (or after max_steps > 0 moves) */
 vnsgpu_status vnsgpu_best_improvement(vnsgpu_ctx *ctx, int path, double budget, int max_steps, int *steps, int64_t *evals);

@@ -64,7 +64,15 @@ e._ck(e.lib.vnsgpu_eval_batch_dev_shard(e.h, p.h, hi - lo, C.c_void_p(d_c.data_p
 e.reduce_first_key(d_key.data_ptr())
 e.sync()
 ln, lb, fl, first = p.eval_batch(cands)                        # the whole batch on this rank alone
-np.savez(os.path.join(tmp, "r%%d.npz" %% rank), T=T, vns=vns, length=p.getPathLength(), key=int(d_key.item()), first=first)
+# full-neighbourhood modes: every neighbourhood split over the two ranks = the single-GPU search
+q1 = e.path(); q1.greedy_insertion_batched(); s1 = q1.best_improvement()
+e.set_shard_neighbourhoods(1)
+q2 = e.path(); r2 = q2.greedy_insertion_batched(); s2 = q2.best_improvement()
+m = q2.best_move(1)
+e.set_shard_neighbourhoods(0)
+np.savez(os.path.join(tmp, "r%%d.npz" %% rank), T=T, vns=vns, length=p.getPathLength(), key=int(d_key.item()), first=first,
+         nb_same=bool((q1.vns == q2.vns).all() and q1.getPathLength() == q2.getPathLength() and q1.getReward() == q2.getReward()),
+         nb_vns=np.array(q2.vns), nb_steps=np.array([s1[0], s2[0]]), nb_evals=np.array([s1[1], s2[1]]), nb_last=m.index)
 e.comm_destroy()
 e.close()
 '''
@@ -81,6 +89,12 @@ def test_comm_broadcast_and_first_key_two_ranks(tmp_path):
     assert int(a["T"]) == int(b["T"]) > 0 and (a["vns"] == b["vns"]).all() and float(a["length"]) == float(b["length"])   # the incumbent arrived
     assert int(a["key"]) == int(b["key"]) == int(a["first"]) == int(b["first"])      # the reduced key = the single-GPU answer
     assert int(a["first"]) >= 0
+    # sharded full-neighbourhood descent: same tour as unsharded on both ranks, the same number of moves, and the two
+    # shards' candidate counts add up to the whole neighbourhoods
+    assert bool(a["nb_same"]) and bool(b["nb_same"]) and (a["nb_vns"] == b["nb_vns"]).all()
+    assert a["nb_steps"][0] == a["nb_steps"][1] == b["nb_steps"][1]
+    assert int(a["nb_evals"][1]) + int(b["nb_evals"][1]) == int(a["nb_evals"][0])
+    assert int(a["nb_last"]) == int(b["nb_last"]) == -1
 
 
 @needs2

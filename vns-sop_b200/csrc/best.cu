@@ -38,11 +38,13 @@ template <int MODE> __device__ __forceinline__ bool key_better(const BestKey &x,
 // kind 1: insert       k = from * (T + 1) + to        -> tryToMove(from, to) / tryToAdd(VNS[from], to)    (:507-519 pairs)
 // kind 2: exchange     k = from * T + to              -> tryToExchange(from, to) / tryToReplace(VNS[from], to)  (:723-730)
 // pairs the reference redraws (|from - to| <= gap) get op = -1: the evaluation flags them VNSGPU_F_BAD, never chosen
-static __global__ void __launch_bounds__(256) k_nbh_cands(PathDev P, int kind, long long n, vnsgpu_cand *__restrict__ out)
+static __global__ void __launch_bounds__(256) k_nbh_cands(PathDev P, int kind, long long k0, long long n, vnsgpu_cand *__restrict__ out)
 {
    const int T = P.hdr[HDR_T];
    const int ncol = kind == 2 ? T : T + 1;
-   for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (long long)gridDim.x * blockDim.x) {
+   // this rank's shard: enumeration indices k0 .. k0 + n - 1
+   for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < n; q += (long long)gridDim.x * blockDim.x) {
+      const long long k = k0 + q;
       const int row = (int)(k / ncol), to = (int)(k - (long long)row * ncol);
       vnsgpu_cand c;
       if (kind == 0) {
@@ -57,7 +59,7 @@ static __global__ void __launch_bounds__(256) k_nbh_cands(PathDev P, int kind, l
             c.op = kind == 1 ? VNSGPU_OP_ADD : VNSGPU_OP_REPLACE; c.a = cl; c.b = to; c.gain_cluster = cl;
          }
       }
-      out[k] = c;
+      out[q] = c;
    }
 }
 
@@ -66,16 +68,15 @@ static __global__ void __launch_bounds__(256) k_nbh_cands(PathDev P, int kind, l
 template <int MODE>
 static __global__ void __launch_bounds__(256) k_best_reduce(InstDev I, PathDev P, int kind, long long n, const vnsgpu_cand *__restrict__ cands,
                                                             const double *__restrict__ len, const uint8_t *__restrict__ flags, double budget,
-                                                            BestKey *partial, unsigned *ticket, BestRec *rec)
+                                                            BestKey *partial, unsigned *ticket, BestKey *key_out, long long k0)
 {
    __shared__ BestKey sh[256];
    __shared__ bool last;
-   const int T = P.hdr[HDR_T];
    const double L = P.hd[HD_LEN];
    BestKey best{0.0, 0.0, -1};
    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (long long)gridDim.x * blockDim.x) {
       const double d = len[k];
-      BestKey cur{0.0, d, k};
+      BestKey cur{0.0, d, k0 + k};      // global enumeration index
       bool ok;
       if (MODE == 0) {
          const vnsgpu_cand c = cands[k];
@@ -124,17 +125,28 @@ static __global__ void __launch_bounds__(256) k_best_reduce(InstDev I, PathDev P
       __syncthreads();
    }
    if (threadIdx.x == 0) {
-      BestRec r;
-      r.idx = sh[0].idx; r.a = sh[0].a; r.b = sh[0].b; r.kind = kind; r.pad = 0; r.from = r.to = -1;
-      if (r.idx >= 0) {
-         const int ncol = kind == 2 ? T : T + 1;
-         const int row = (int)(r.idx / ncol);
-         r.to = (int)(r.idx - (long long)row * ncol);
-         r.from = kind == 0 ? T + row : row;
-      }
-      *rec = r;
+      *key_out = sh[0];
       *ticket = 0;
    }
+}
+
+// the best of nkeys keys (one per rank of a sharded neighbourhood, in rank order - the same array on every rank, so every
+// rank picks the same move) as the record the apply kernels read
+template <int MODE> static __global__ void k_best_pick(PathDev P, int kind, const BestKey *__restrict__ keys, int nkeys, BestRec *rec)
+{
+   const int T = P.hdr[HDR_T];
+   BestKey best{0.0, 0.0, -1};
+   for (int r = 0; r < nkeys; ++r)
+      if (key_better<MODE>(keys[r], best)) best = keys[r];
+   BestRec o;
+   o.idx = best.idx; o.a = best.a; o.b = best.b; o.kind = kind; o.pad = 0; o.from = o.to = -1;
+   if (o.idx >= 0) {
+      const int ncol = kind == 2 ? T : T + 1;
+      const int row = (int)(o.idx / ncol);
+      o.to = (int)(o.idx - (long long)row * ncol);
+      o.from = kind == 0 ? T + row : row;
+   }
+   *rec = o;
 }
 
 // ---- apply the chosen move (one block): the accept branches of insertRandom (:621-646) / exchangeRandom (:807-832), or
@@ -206,6 +218,7 @@ struct BestBufs {
    BestKey *partial;
    unsigned *ticket;
    BestRec *rec;
+   BestKey *mykey, *keys;    // this rank's best, and every rank's (all-gather)
 };
 
 static vnsgpu_status best_bufs(vnsgpu_ctx *ctx, long long n, BestBufs *b)
@@ -213,7 +226,8 @@ static vnsgpu_status best_bufs(vnsgpu_ctx *ctx, long long n, BestBufs *b)
    const size_t nb = 2048;
    const size_t o_len = al16(sizeof(vnsgpu_cand) * (size_t)n), o_fl = o_len + al16(sizeof(double) * (size_t)n),
                 o_part = o_fl + al16((size_t)n), o_tick = o_part + al16(sizeof(BestKey) * nb), o_rec = o_tick + 16,
-                total = o_rec + al16(sizeof(BestRec));
+                o_my = o_rec + al16(sizeof(BestRec)), o_keys = o_my + al16(sizeof(BestKey)),
+                total = o_keys + al16(sizeof(BestKey) * (size_t)std::max(1, ctx->comm_size));
    if (total > ctx->best_bytes) {
       if (ctx->d_best) { CK(cudaStreamSynchronize(ctx->stream)); CK(cudaFree(ctx->d_best)); }
       ctx->d_best = nullptr; ctx->best_bytes = 0;
@@ -225,6 +239,7 @@ static vnsgpu_status best_bufs(vnsgpu_ctx *ctx, long long n, BestBufs *b)
    char *p = (char *)ctx->d_best;
    b->cands = (vnsgpu_cand *)p; b->len = (double *)(p + o_len); b->flags = (uint8_t *)(p + o_fl);
    b->partial = (BestKey *)(p + o_part); b->ticket = (unsigned *)(p + o_tick); b->rec = (BestRec *)(p + o_rec);
+   b->mykey = (BestKey *)(p + o_my); b->keys = (BestKey *)(p + o_keys);
    CK(cudaMemsetAsync(b->ticket, 0, 16, ctx->stream));
    return VNSGPU_OK;
 }
@@ -241,23 +256,37 @@ static vnsgpu_status best_step(vnsgpu_ctx *ctx, int path, int kind, double budge
    if (kind == 0) n = (long long)(nvns - T) * (T + 1);
    else if (kind == 1) n = nvns >= 3 ? (long long)nvns * (T + 1) : 0;                 // guard :498
    else n = (nvns >= 4 && T > 0) ? (long long)nvns * T : 0;                          // guard :711
-   if (n_out) *n_out = n;
+   // with vnsgpu_set_shard_neighbourhoods and a communicator every rank evaluates one contiguous range of the enumeration
+   // (table and path are replicated) and the ranks' best keys are all-gathered: one collective of 24 bytes per rank
+   const bool shard = ctx->shard_nbh && ctx->comm && ctx->comm_size > 1;
+   const int R = shard ? ctx->comm_size : 1, r = shard ? ctx->comm_rank : 0;
+   const long long k0 = n * r / R, nl = n * (r + 1) / R - k0;
+   if (n_out) *n_out = nl;
    out->idx = -1; out->from = out->to = -1; out->a = out->b = 0; out->kind = kind;
    if (n <= 0) return VNSGPU_OK;
-   s = best_bufs(ctx, n, b);
+   s = best_bufs(ctx, std::max<long long>(nl, 1), b);
    if (s) return s;
    const PathDev P = ctx->paths[path].d;
-   const int grid = (int)std::min<long long>((n + 255) / 256, 2048);
-   k_nbh_cands<<<grid, 256, 0, ctx->stream>>>(P, kind, n, b->cands);
-   LAUNCHED(ctx);
-   ctx->seg_fresh_path = fresh ? path : -1;      // the products path_rows_from_products built for this very state
-   s = vnsgpu_eval_batch_dev(ctx, path, n, b->cands, budget, 0, b->len, nullptr, kind == 0 ? nullptr : b->flags, nullptr, ctx->stream);
-   ctx->seg_fresh_path = -1;
-   if (s) return s;
+   const int grid = (int)std::max<long long>(1, std::min<long long>((nl + 255) / 256, 2048));
+   if (nl > 0) {
+      k_nbh_cands<<<grid, 256, 0, ctx->stream>>>(P, kind, k0, nl, b->cands);
+      LAUNCHED(ctx);
+      ctx->seg_fresh_path = fresh ? path : -1;      // the products path_rows_from_products built for this very state
+      s = vnsgpu_eval_batch_dev(ctx, path, nl, b->cands, budget, 0, b->len, nullptr, kind == 0 ? nullptr : b->flags, nullptr, ctx->stream);
+      ctx->seg_fresh_path = -1;
+      if (s) return s;
+   }
    if (kind == 0)
-      k_best_reduce<0><<<grid, 256, 0, ctx->stream>>>(ctx->I, P, kind, n, b->cands, b->len, b->flags, budget, b->partial, b->ticket, b->rec);
+      k_best_reduce<0><<<grid, 256, 0, ctx->stream>>>(ctx->I, P, kind, nl, b->cands, b->len, b->flags, budget, b->partial, b->ticket, b->mykey, k0);
    else
-      k_best_reduce<1><<<grid, 256, 0, ctx->stream>>>(ctx->I, P, kind, n, b->cands, b->len, b->flags, budget, b->partial, b->ticket, b->rec);
+      k_best_reduce<1><<<grid, 256, 0, ctx->stream>>>(ctx->I, P, kind, nl, b->cands, b->len, b->flags, budget, b->partial, b->ticket, b->mykey, k0);
+   LAUNCHED(ctx);
+   if (shard) {
+      s = comm_allgather_bytes(ctx, b->mykey, b->keys, sizeof(BestKey), ctx->stream);
+      if (s) return s;
+   }
+   if (kind == 0) k_best_pick<0><<<1, 1, 0, ctx->stream>>>(P, kind, shard ? b->keys : b->mykey, R, b->rec);
+   else k_best_pick<1><<<1, 1, 0, ctx->stream>>>(P, kind, shard ? b->keys : b->mykey, R, b->rec);
    LAUNCHED(ctx);
    CK(cudaMemcpyAsync(out, b->rec, sizeof(BestRec), cudaMemcpyDeviceToHost, ctx->stream));
    CK(cudaStreamSynchronize(ctx->stream));
@@ -291,6 +320,12 @@ static vnsgpu_status apply_rec(vnsgpu_ctx *ctx, int path, const BestRec *d_rec, 
 }
 
 extern "C" {
+
+vnsgpu_status vnsgpu_set_shard_neighbourhoods(vnsgpu_ctx *ctx, int enable)
+{
+   ctx->shard_nbh = enable != 0;
+   return VNSGPU_OK;
+}
 
 vnsgpu_status vnsgpu_greedy_batched(vnsgpu_ctx *ctx, int path, double budget, int *rounds, int64_t *evals)
 {

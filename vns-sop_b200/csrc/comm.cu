@@ -21,6 +21,7 @@ struct NcclApi {
    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
    ncclResult_t (*AllReduce)(const void *, void *, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
    ncclResult_t (*Broadcast)(const void *, void *, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+   ncclResult_t (*AllGather)(const void *, void *, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
    const char *(*GetErrorString)(ncclResult_t) = nullptr;
    std::string err;
 };
@@ -41,6 +42,7 @@ static NcclApi &nccl_api()
    api.CommDestroy = (decltype(api.CommDestroy))sym("ncclCommDestroy");
    api.AllReduce = (decltype(api.AllReduce))sym("ncclAllReduce");
    api.Broadcast = (decltype(api.Broadcast))sym("ncclBroadcast");
+   api.AllGather = (decltype(api.AllGather))sym("ncclAllGather");
    api.GetErrorString = (decltype(api.GetErrorString))sym("ncclGetErrorString");
    return api;
 }
@@ -56,6 +58,18 @@ static vnsgpu_status nccl_fail(vnsgpu_ctx *ctx, const char *what, ncclResult_t r
       ncclResult_t r__ = (call);                                     \
       if (r__ != ncclSuccess) return nccl_fail(ctx, #call, r__);     \
    } while (0)
+
+// every rank's `bytes` bytes at d_send, in rank order, into d_recv of every rank (best.cu: the ranks' best keys of a sharded
+// neighbourhood); a context without communicator copies its own block
+vnsgpu_status comm_allgather_bytes(vnsgpu_ctx *ctx, const void *d_send, void *d_recv, size_t bytes, cudaStream_t st)
+{
+   if (!ctx->comm) {
+      CK(cudaMemcpyAsync(d_recv, d_send, bytes, cudaMemcpyDeviceToDevice, st));
+      return VNSGPU_OK;
+   }
+   NCK(nccl_api().AllGather(d_send, d_recv, bytes, ncclChar, (ncclComm_t)ctx->comm, st));
+   return VNSGPU_OK;
+}
 
 extern "C" {
 

@@ -115,6 +115,7 @@ struct vnsgpu_ctx {
    void *d_gen = nullptr, *d_gencands = nullptr;
    size_t gen_bytes = 0, gencands_bytes = 0;
    int seg_fresh_path = -1;       // set by best.cu right before an evaluation call: the products of this path's state are current
+   bool shard_nbh = false;        // vnsgpu_set_shard_neighbourhoods: full-neighbourhood modes split every neighbourhood over the communicator's ranks
    void *d_best = nullptr;        // full-neighbourhood modes (best.cu): descriptors, lengths, flags, partial keys
    size_t best_bytes = 0;
    bool phase_timing = false;     // vnsgpu_set_phase_timing: CUDA events around the phases of the batched evaluation call
@@ -233,6 +234,8 @@ struct PhaseTimer {
    }
 };
 
+// comm.cu: all-gather of a few bytes per rank (best.cu)
+vnsgpu_status comm_allgather_bytes(vnsgpu_ctx *ctx, const void *d_send, void *d_recv, size_t bytes, cudaStream_t st);
 // internal entry points of api_path.cu used by best.cu: every F / B row of a path from the segment products of its current
 // targets (all layers in parallel; integer tables)
 bool path_products_available(const vnsgpu_ctx *ctx);

@@ -112,6 +112,7 @@ _SIGS = {
     "vnsgpu_fit_to_budget": [vp, C.c_int, C.c_double],
     "vnsgpu_greedy": [vp, C.c_int, C.c_double],
     "vnsgpu_greedy_batched": [vp, C.c_int, C.c_double, C.POINTER(C.c_int), C.POINTER(C.c_int64)],
+    "vnsgpu_set_shard_neighbourhoods": [vp, C.c_int],
     "vnsgpu_best_move": [vp, C.c_int, C.c_int, C.c_double, C.POINTER(BestMove)],
     "vnsgpu_apply_move": [vp, C.c_int, C.c_int, C.c_int, C.c_int],
     "vnsgpu_best_improvement": [vp, C.c_int, C.c_double, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int64)],
@@ -240,6 +241,10 @@ class Engine:
 
     def set_smem_chain(self, enable):
         self._ck(self.lib.vnsgpu_set_smem_chain(self.h, int(enable)))
+
+    def set_shard_neighbourhoods(self, enable):
+        """full-neighbourhood modes split every neighbourhood over the communicator's ranks (collective calls)"""
+        self._ck(self.lib.vnsgpu_set_shard_neighbourhoods(self.h, int(enable)))
 
     def set_chain_form(self, form):
         """0: second form (lower bound first, shake in shared memory, integer tables), 1: first form"""
