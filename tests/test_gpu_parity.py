@@ -177,6 +177,38 @@ def test_shake_and_local_search_sequence(name, mode, golden, eng_cache):
         _reset_chain_mode(e)
 
 
+@pytest.mark.parametrize("mode", ["smem-tab", "smem-tab-g16", "smem-int", "smem-int-v1"])
+@pytest.mark.parametrize("name", ["berlin52", "opn_s08", "dop_s12", "krob200"])
+def test_local_search_edge_cases_vs_oracle(name, mode, golden, eng_cache):
+    """insertRandom / exchangeRandom calls the golden sequence does not reach, against the C port on the same state and
+    generator: calls of 1 .. 100 proposals (the window's cut at the end of a call), the lower-bound skip off, a budget nothing
+    fits, a budget everything fits, an empty tour.  States, counters and generator positions must agree after every call."""
+    from oracle import binding as ob
+    from vns_sop_b200 import engine
+    e, sf, pb = eng_cache(name)
+    g, a = golden[name], load_arrays(name)
+    o = ob.Oracle(pb)
+    _set_chain_mode(e, mode)
+    try:
+        for start in ("greedy", "empty"):
+            vns = np.array(a["greedy_vns"])
+            T = g["greedy"]["T"] if start == "greedy" else 0
+            pg, po = e.path(vns, T), o.path(vns, T)
+            rg, ro = engine.seeded_rng(11), ob.new_rng(11)
+            cases = [(1, 1, None, 1), (2, 1, None, 1), (1, 5, None, 1), (2, 33, None, 0), (1, 100, None, 0), (2, 64, None, 1),
+                     (1, 40, 1.0, 1), (2, 40, 1.0, 0), (1, 70, 1e12, 1), (2, 70, 1e12, 1), (1, 31, pb.budget * 0.5, 1), (2, 32, pb.budget * 0.5, 0)]
+            for i, (kind, iters, budget, skip) in enumerate(cases):
+                sg = pg._ls(kind, iters, rg, budget, skip)
+                so = po.local_search(kind, iters, ro, budget, skip)
+                assert pg.getNumTargets() == po.T and (pg.vns == po.vns).all(), (start, i)
+                assert pg.getPathLength() == po.length() and pg.getReward() == po.reward(), (start, i)
+                assert (sg.proposals, sg.accepts) == (so.proposals, so.accepts), (start, i)
+                assert sg.lb_skips == so.lb_skips and sg.evals == so.evals, (start, i)
+            assert engine.rng_next(rg) == ob.rng_next(ro), start
+    finally:
+        _reset_chain_mode(e)
+
+
 def _run_sequence(e, pb, g, a):
     from vns_sop_b200 import engine
     p = e.path(a["greedy_vns"], g["greedy"]["T"])
