@@ -480,6 +480,15 @@ def run_b200(args):
         line["roofline_hbm"] = dict(line["workloads"]["synth20k"]["roofline"], workload="synth20k")
     if rank == 0 and world == 1 and not args.no_solve and args.workload == "krob200" and "vm1084" in extras:
         line["time_to_reward_vm1084"] = solve_only("vm1084")
+    if rank == 0 and world == 1 and not args.no_solve and args.workload == "krob200" and args.also:
+        # BASELINE.json config 3 (DOP, 16 heading samples, table from the Dubins kernel): seeded solve against the reference
+        # binary on the same table, 148 seeds in one launch against one reference process per core
+        sub = argparse.Namespace(**vars(args))
+        sub.workload, sub.no_e2e, sub.no_cpu, sub.no_solve, sub.sweep, sub.no_full_nbh = "dop_s16", True, True, False, False, True
+        sub.steps, sub.warmup = min(args.steps, 5), min(args.warmup, 3)
+        sl = bench_workload(sub, env)
+        line["time_to_reward_dop_s16"] = dict(sl.get("time_to_reward", {}), workload=sl["config"]["workload"], evals_per_s=sl["value"],
+                                              table_build=sl.get("table_build"))
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
