@@ -83,6 +83,7 @@ def parse_args():
     ap.add_argument("--no-solve-cpu", action="store_true", help="time-to-reward: skip the reference binary runs (long on vm1084)")
     ap.add_argument("--sweep", action="store_true", help="candidate-batch sweep 2^10 .. --batch (x4 steps), device-resident (BASELINE config 5)")
     ap.add_argument("--multi-start", type=int, default=148, help="seeds of the multi-start leg (0 = skip)")
+    ap.add_argument("--multi-start-dense", type=int, default=592, help="seeds of the dense multi-start launch (four per SM; 0 = skip)")
     ap.add_argument("--also", default="vm1084,synth20k,synth20k_raw", help="further workloads measured (device-resident leg only) into the same JSON "
                                                                "line under `workloads` (BASELINE configs 4 and 5); '' = none")
     ap.add_argument("--no-full-nbh", action="store_true", help="skip the full-neighbourhood leg (batched greedy + best-improvement descent)")
@@ -1052,6 +1053,17 @@ def solve_leg(args, eng, sf, pb):
     out["multi_start"] = {"gpu_runs": nruns, "gpu_wall_s": gpu_multi, "gpu_runs_per_s": nruns / gpu_multi,
                           "best_reward": res_b[best].reward, "best_length": res_b[best].length, "best_seed": best + 1,
                           "seed1_same_as_single_run": res_b[0].reward == res.reward and res_b[0].length == res.length}
+    # dense: four seeds per SM in one launch (third chain form: thread blocks of 128 threads, the table shared through L1
+    # when the state is small enough for several blocks per SM)
+    if args.multi_start_dense > nruns:
+        pd_ = eng.path()
+        t0 = time.perf_counter()
+        res_d, best_d = pd_.vns_run_batch(list(range(1, args.multi_start_dense + 1)))
+        gpu_dense = time.perf_counter() - t0
+        out["multi_start"]["dense"] = {"gpu_runs": args.multi_start_dense, "gpu_wall_s": gpu_dense, "gpu_runs_per_s": args.multi_start_dense / gpu_dense,
+                                       "best_reward": res_d[best_d].reward, "best_length": res_d[best_d].length, "best_seed": best_d + 1,
+                                       "first_runs_same_as_above": all(res_d[k].reward == res_b[k].reward and res_d[k].length == res_b[k].length
+                                                                       for k in range(nruns))}
     # race: the same launch with the reference's seed-1 final reward as target - it ends as soon as ANY seed's tour
     # reaches it ("wall time to the reference's reward" with one seed per SM); every run stays a prefix of its
     # seeded reference trajectory

@@ -264,7 +264,7 @@ vnsgpu_status vnsgpu_vns_run_batch(vnsgpu_ctx *ctx, int path, int nruns, const u
    if (nruns < 1) return fail(ctx, VNSGPU_E_RANGE, "nruns < 1");
    size_t smem = 0;
    int cis = 0;
-   const bool c3 = c3_fits(ctx, &smem, &cis);
+   const bool c3 = c3_fits(ctx, &smem, &cis, nruns > ctx->num_sms);
    const bool c2 = c3 || (ctx->use_smem_chain && c2_fits(ctx, &smem, &cis));   // c2: the slot layout both forms share
    const size_t extra = chain_smem(ctx) + sizeof(RngState) + 64;
    bool as_int = false;

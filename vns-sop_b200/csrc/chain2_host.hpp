@@ -15,7 +15,7 @@ const VnsResultDev &c2_run_slot_result(const void *slot);
 
 // third form (chain3.cu): the whole search state (and the distance table when it fits) in shared memory.  u16 = variant:
 // bit 0 the uint16 copy of the table, bit 1 the table stays in global memory
-bool c3_fits(const vnsgpu_ctx *ctx, size_t *smem, int *u16);
+bool c3_fits(const vnsgpu_ctx *ctx, size_t *smem, int *u16, bool dense = false);
 vnsgpu_status c3_launch_ls(vnsgpu_ctx *ctx, int path, int kind, int num_changes, double budget, int skip, size_t smem, int u16);
 vnsgpu_status c3_launch_vns(vnsgpu_ctx *ctx, int path, const VnsParamsDev &prm, double *d_ir, double *d_il, double *d_it, size_t smem,
                             int u16);

@@ -8,7 +8,7 @@
 // one block.  Global table: instances below 96 clusters whose table does not fit (from 96 clusters on the second form's
 // product tree wins).  chain_form: -1 (default) takes this form whenever one of the two applies; 3 forces it; 0 / 1 / 2 name
 // the other forms.
-bool c3_fits(const vnsgpu_ctx *ctx, size_t *smem, int *variant)
+bool c3_fits(const vnsgpu_ctx *ctx, size_t *smem, int *variant, bool dense)
 {
    const bool want = ctx->chain_form == 3 || ctx->chain_form < 0;
    if (!want || !ctx->use_smem_chain || !vnsgpu_int_path_active(ctx) || ctx->I.mp > 32) return false;
@@ -17,12 +17,16 @@ bool c3_fits(const vnsgpu_ctx *ctx, size_t *smem, int *variant)
    const size_t fixed = sizeof(C3Ctl) + sizeof(RngState) + 2048;
    const size_t greedy = sizeof(double) * 2 * ctx->I.mp * C3_WARPS;       // the greedy start borrows the table's place
    const int forced = getenv("VNSGPU_CHAIN3_U16") ? atoi(getenv("VNSGPU_CHAIN3_U16")) : -1;   // tests: force a variant (0 .. 3)
-   for (int v = 0; v < 4; ++v) {
+   // dense (more seeded runs than SMs in one launch): the table stays in global memory when the state is small enough for
+   // several thread blocks per SM - they share the table in L1 instead of holding a copy each
+   for (int k = 0; k < 4; ++k) {
+      const int v = dense ? (k + 2) & 3 : k;
       if (forced >= 0 && v != (forced & 3)) continue;
       const bool u16 = v & 1, tg = (v & 2) != 0;
       if (u16 && !(ctx->d_D16 && ctx->use_u16)) continue;
       if (tg && forced < 0 && (ctx->I.C >= 96 || (!u16 && ctx->d_D16 && ctx->use_u16))) continue;   // global: the smaller copy when there is one
       const size_t b = std::max(c3_smem_bytes(ctx->I.C, ctx->I.N, ctx->I.mp, u16 ? 2 : 4, tg), greedy);
+      if (dense && tg && 2 * (b + fixed) > (size_t)ctx->max_smem) continue;                          // not even two blocks per SM: no point
       if (b + fixed <= (size_t)ctx->max_smem) { *smem = b; *variant = v; return true; }
    }
    return false;
