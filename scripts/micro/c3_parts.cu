@@ -30,7 +30,7 @@ __global__ void __launch_bounds__(C3_THREADS) k_parts(C3Env E, const int *lcl_g,
       c3_pd_scan(s, S, lane);
    }
    __syncthreads();
-   long long t_f = 0, t_b = 0, t_e = 0, t_w = 0, t_p = 0;
+   long long t_f = 0, t_b = 0, t_e = 0, t_w = 0, t_p = 0, t_e5 = 0, t_e2 = 0, t_d = 0;
    int acc = 0;
    for (int rep = 0; rep < nrep; ++rep) {
       __syncthreads();
@@ -47,6 +47,22 @@ __global__ void __launch_bounds__(C3_THREADS) k_parts(C3Env E, const int *lcl_g,
          acc += c3_eval<TT, 16>(s, T, cc, lane % 16, s.gw + (lane / 16) * s.gwcap);
          t1 = clock64();
          t_e += t1 - t0;
+         {  // shorter chains: tryToExchange(3, 6) -> K = 5, tryToAdd(cluster 5, 4) -> K = 2
+            const CandCode c5 = decode_cand(T, s.C, VNSGPU_OP_EXCHANGE, 3, 6);
+            t0 = clock64();
+            acc += c3_eval<TT, 16>(s, T, c5, lane % 16, s.gw + (lane / 16) * s.gwcap);
+            t1 = clock64();
+            t_e5 += t1 - t0;
+            const CandCode c2 = decode_cand(T, s.C, VNSGPU_OP_ADD, 5, 4);
+            t0 = clock64();
+            acc += c3_eval<TT, 16>(s, T, c2, lane % 16, s.gw + (lane / 16) * s.gwcap);
+            t1 = clock64();
+            t_e2 += t1 - t0;
+            t0 = clock64();
+            const CandCode c9 = decode_cand(T, s.C, VNSGPU_OP_MOVE, 3 + (lane & 1), 9);
+            acc += c9.K;
+            t_d += clock64() - t0;
+         }
          // lower bounds of 32 proposals
          const int from = (lane * 7 + rep) % T, to = (from + 3 + lane % 5) % T;
          t0 = clock64();
@@ -62,7 +78,7 @@ __global__ void __launch_bounds__(C3_THREADS) k_parts(C3Env E, const int *lcl_g,
       }
       __syncthreads();
    }
-   if (threadIdx.x == 0) { cyc[0] = t_f; cyc[1] = t_b; cyc[2] = t_e; cyc[3] = t_w; cyc[4] = t_p; sink[0] = acc; }
+   if (threadIdx.x == 0) { cyc[0] = t_f; cyc[1] = t_b; cyc[2] = t_e; cyc[3] = t_w; cyc[4] = t_p; cyc[5] = t_e5; cyc[6] = t_e2; cyc[7] = t_d; sink[0] = acc; }
 }
 
 int main()
@@ -91,12 +107,13 @@ int main()
    cudaFuncSetAttribute(k_parts, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
    const int nrep = 200;
    for (int it = 0; it < 2; ++it) { k_parts<<<1, C3_THREADS, smem>>>(E, d_lcl, T, d_cyc, d_sink, nrep); cudaDeviceSynchronize(); }
-   long long h[5];
+   long long h[8];
    cudaMemcpy(h, d_cyc, sizeof(h), cudaMemcpyDeviceToHost);
    printf("N = %d, T = %d (%s)\n", N, T, cudaGetErrorString(cudaGetLastError()));
    printf("forward re-scan   %8.1f cycles / layer  (%d layers)\n", (double)h[0] / nrep / (T + 1), T + 1);
    printf("backward re-scan  %8.1f cycles / layer\n", (double)h[1] / nrep / (T + 1));
    printf("evaluation        %8.1f cycles / call, K = 12 block steps\n", (double)h[2] / nrep);
+   printf("evaluation        %8.1f cycles / call, K = 5;  %8.1f cycles / call, K = 2;  decode_cand %6.1f cycles\n", (double)h[5] / nrep, (double)h[6] / nrep, (double)h[7] / nrep);
    printf("lower bound + ballot %5.1f cycles / 32 proposals\n", (double)h[3] / nrep);
    printf("prefix sums       %8.1f cycles / call\n", (double)h[4] / nrep);
    return 0;
