@@ -955,6 +955,7 @@ def full_neighbourhood_leg(args, eng, sf, pb, cpu):
     torch.cuda.synchronize()
     t1 = time.perf_counter()
     r0, l0, T0 = p.getReward(), p.getPathLength(), p.getNumTargets()
+    greedy_vns = np.array(p.vns)
     steps, evals2 = p.best_improvement(max_steps=args.descent_steps)
     torch.cuda.synchronize()
     t2 = time.perf_counter()
@@ -969,6 +970,18 @@ def full_neighbourhood_leg(args, eng, sf, pb, cpu):
                                 "what": "opt-in descent: per move the WHOLE insert or exchange neighbourhood evaluated at once, best "
                                         "improving candidate applied (most added reward, then shortest, then lowest index); a "
                                         "different search than the reference's first-improvement random sampling"}}
+    # the trajectory-exact chain (seed 1, stock settings) from the same greedy tour for the time the descent took: what the
+    # reference's own search reaches in that time on this device
+    pc = eng.path(greedy_vns, T0)
+    torch.cuda.synchronize()
+    c0 = time.perf_counter()
+    res, impr = pc.vns_run(1, greedy=0, max_time_ms=1e3 * (t2 - t1))
+    c1 = time.perf_counter()
+    out["best_improvement"]["exact_chain_same_time"] = {"seconds": c1 - c0, "time_limit_s": t2 - t1, "reward": res.reward, "length": res.length,
+                                                        "vns_steps": res.num_iters, "proposals": res.proposals, "accepts": res.accepts,
+                                                        "what": "vnsgpu_vns_run (seed 1, the reference's trajectory) started from the same greedy tour "
+                                                                "with maximal-calculation-time = the descent's time; the limit is checked once per VNS "
+                                                                "step (vns_sop_solver.cpp:189-193), so the run overshoots by up to one local-search call"}
     if cpu:
         from oracle import binding as ob
         o = ob.Oracle(pb)
