@@ -203,6 +203,28 @@ class VnsSopPath {
    void pathExchange(double budget, vnsgpu_rng &rng) { e_->check(vnsgpu_shake(e_->ctx(), h_, 2, budget, &rng)); }   // :1001-1089
    void fitDOPtoBudget(double budget) { e_->check(vnsgpu_fit_to_budget(e_->ctx(), h_, budget)); }                   // :364-385
    void greedy_insertion(double budget) { e_->check(vnsgpu_greedy(e_->ctx(), h_, budget)); }                        // :1091-1155
+   // the same greedy with every round's tryToAdd grid as one batched evaluation (the choice beyond a few hundred clusters)
+   int greedy_insertion_batched(double budget)
+   {
+      int rounds = 0;
+      e_->check(vnsgpu_greedy_batched(e_->ctx(), h_, budget, &rounds, nullptr));
+      return rounds;
+   }
+   // opt-in, not the reference's trajectory: best improving candidate of the whole insert (1) / exchange (2) neighbourhood,
+   // its application, and the descent over both neighbourhoods (returns the number of moves applied)
+   vnsgpu_best_move_t bestMove(int kind, double budget)
+   {
+      vnsgpu_best_move_t m;
+      e_->check(vnsgpu_best_move(e_->ctx(), h_, kind, budget, &m));
+      return m;
+   }
+   void applyMove(int kind, int from, int to) { e_->check(vnsgpu_apply_move(e_->ctx(), h_, kind, from, to)); }
+   int bestImprovement(double budget, int max_steps = 0)
+   {
+      int steps = 0;
+      e_->check(vnsgpu_best_improvement(e_->ctx(), h_, budget, max_steps, &steps, nullptr));
+      return steps;
+   }
 
  private:
    Engine *e_;
