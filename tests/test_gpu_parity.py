@@ -298,6 +298,22 @@ def test_multi_start_race_stops_at_target_reward(golden, eng_cache):
             assert (r.reward, r.length, r.num_iters) == (full[sd][0].reward, full[sd][0].length, full[sd][0].num_iters)
 
 
+@pytest.mark.parametrize("gx", [1, 3])
+@pytest.mark.parametrize("name", ["krob200", "dop_s12", "vm1084"])
+def test_endpoint_vectors_do_not_depend_on_the_grid(name, gx, golden, eng_cache, monkeypatch):
+    """k_vec_pairs strides over the layers with the warps of grid.x, which the host sizes from the header as it last read it:
+    a grid far below the layers (symmetric and asymmetric tables) gives the oracle's lengths"""
+    from oracle import binding as ob
+    e, sf, pb = eng_cache(name)
+    g, a = golden[name], load_arrays(name)
+    monkeypatch.setenv("VNSGPU_VEC_PAIRS_GX", str(gx))
+    po, pg = ob.Oracle(pb).path(a["greedy_vns"], g["greedy"]["T"]), e.path(a["greedy_vns"], g["greedy"]["T"])
+    cands = random_candidates(np.random.RandomState(11), po.vns, po.T, 300007 if name == "vm1084" else 60013)
+    ln, lb, fl, first = pg.eval_batch(cands)
+    oln, olb = po.eval_batch(cands)
+    assert (ln == oln).all() and (lb == olb).all()
+
+
 @pytest.mark.parametrize("int_path", [True, False])
 @pytest.mark.parametrize("name", ALL)
 def test_eval_batch_both_arithmetic_paths_vs_oracle(name, int_path, golden, eng_cache):

@@ -356,19 +356,34 @@ static vnsgpu_status prepare_eval(vnsgpu_ctx *ctx, int path, int mode, cudaStrea
    const int thr = 2 * slot * 8 <= 40 * 1024 ? 256 : 128;      // 2 staged blocks per warp: <= 40 KB per CTA
    const int wpc = thr / 32;
    const size_t smem = 2 * slot * wpc;
-   // grid.y = layer lanes (the kernels stride over the layers): enough CTAs to fill the device on small instances,
-   // few enough that none is empty on large ones
-   const int gxu = (I.C + wpc - 1) / wpc, gxp = (Smax + 1 + wpc - 1) / wpc;
-   const int gyu = std::min(Smax, std::max(16, (8 * ctx->num_sms + gxu - 1) / gxu));
-   const int gyp = std::min(Smax, std::max(16, (8 * ctx->num_sms + gxp - 1) / gxp));
+   // grid.y = layer lanes (the kernels stride over the layers): about eight waves of resident blocks.  The warps' work is
+   // uneven (cluster sizes, cache hits), so the block scheduler's dynamic assignment is worth more than a grid that is
+   // resident at once: measured on the 20 k-node / 64 k-sample states, 1 wave 0.557 / 1.98 ms, the old 1.35 waves 0.483 /
+   // 1.67 ms, 4 waves 0.477 / 1.60 ms, 8 waves 0.464 / 1.56 ms, 16 waves the same (profiles/r4y_waves.txt).
+   // k_vec_pairs' grid.x covers the layers: from the header as last read back when there is one and the launch is not being
+   // captured into a graph (a graph is replayed on later states), else from the bound - the surplus warps return at once
+   cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+   if (cudaStreamIsCapturing(st, &cap) != cudaSuccess) { cudaGetLastError(); cap = cudaStreamCaptureStatusActive; }
+   const PathHost &ph = ctx->paths[path];
+   const int Sknown = (ph.hdr_ok && cap == cudaStreamCaptureStatusNone) ? std::min(Smax, ph.hdr_cache.hdr[HDR_T] + 1) : Smax;
+   auto layer_lanes = [&](auto kern, size_t sm, int gx) {
+      int nb = 0;
+      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, thr, sm) != cudaSuccess || nb < 1) { cudaGetLastError(); nb = 1; }
+      return std::max(1, std::min(Smax, 8 * nb * ctx->num_sms / gx));
+   };
+   const int force_gxp = getenv("VNSGPU_VEC_PAIRS_GX") ? atoi(getenv("VNSGPU_VEC_PAIRS_GX")) : 0;   // tests: a grid.x below the layers
+   const int gxu = (I.C + wpc - 1) / wpc, gxp = force_gxp > 0 ? force_gxp : (Sknown + 1 + wpc - 1) / wpc;
+   const int gyu = u16 ? layer_lanes(k_vec_uw<unsigned short>, smem, gxu) : layer_lanes(k_vec_uw<int>, smem, gxu);
+   const int gyp = u16 ? layer_lanes(k_vec_pairs<unsigned short>, smem, gxp) : layer_lanes(k_vec_pairs<int>, smem, gxp);
    PhaseTimer pt(ctx, VNSGPU_PHASE_VEC, st);
    // small clusters on a symmetric table: 2 - 4 clusters per warp (k_vec_uw_packed)
    const int pslot = (I.symmetric && ctx->use_vec_pack) ? (I.mp <= 8 ? 8 : (I.mp <= 10 ? 10 : (I.mp <= 16 ? 16 : 0))) : 0;
    if (pslot) {
       const int pk = 32 / pslot, gxk = ((I.C + pk - 1) / pk + wpc - 1) / wpc;
-      const int gyk = std::min(Smax, std::max(16, (8 * ctx->num_sms + gxk - 1) / gxk));
       const size_t smk = (size_t)pk * slot * wpc;
+      int gyk = 1;
 #define VNS_VEC_PACKED(TT, SL, TAB)                                                                                   \
+   gyk = layer_lanes(k_vec_uw_packed<TT, SL>, smk, gxk),                                                                 \
    k_vec_uw_packed<TT, SL><<<dim3(gxk, gyk), thr, smk, st>>>(I, ctx->paths[path].d, TAB, ctx->d_segmeta, ctx->d_vec, ctx->d_veclb, LS)
       if (u16) { if (pslot == 8) VNS_VEC_PACKED(unsigned short, 8, ctx->d_D16); else if (pslot == 10) VNS_VEC_PACKED(unsigned short, 10, ctx->d_D16); else VNS_VEC_PACKED(unsigned short, 16, ctx->d_D16); }
       else { if (pslot == 8) VNS_VEC_PACKED(int, 8, ctx->d_D32); else if (pslot == 10) VNS_VEC_PACKED(int, 10, ctx->d_D32); else VNS_VEC_PACKED(int, 16, ctx->d_D32); }

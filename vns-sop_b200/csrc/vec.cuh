@@ -226,7 +226,8 @@ __global__ void __launch_bounds__(256) k_vec_uw_packed(InstDev I, PathDev P, con
    }
 }
 
-// one warp per (x, l), x = 1 .. T (path layer, cluster cx; strided over grid.y), l = 1 .. S.  Two table blocks, four products.
+// one warp per (x, l), x = 1 .. T (path layer, cluster cx; strided over grid.y), l = 1 .. S (strided over the warps of grid.x:
+// the host sizes grid.x from T as it last read it, the result does not depend on it).  Two table blocks, four products.
 template <typename TT>
 __global__ void __launch_bounds__(256) k_vec_pairs(InstDev I, PathDev P, const TT *__restrict__ Dv, const int *__restrict__ meta,
                                                    int *__restrict__ vec, int LS)
@@ -234,32 +235,54 @@ __global__ void __launch_bounds__(256) k_vec_pairs(InstDev I, PathDev P, const T
    extern __shared__ int smem_i[];
    const int T = P.hdr[HDR_T], S = T + 1, C = I.C, mp = I.mp;
    const int lane = threadIdx.x & 31;
-   const int wl = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
-   if (wl > S) return;
+   const int wl0 = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), nwx = (int)((gridDim.x * blockDim.x) >> 5);
    const LayerMeta lm = layer_meta(I, meta);
    VecCache vc{vec, nullptr, LS};
    const size_t slot = vec_slot_bytes(mp, sizeof(TT));
    char *s1 = reinterpret_cast<char *>(smem_i) + (threadIdx.x >> 5) * 2 * slot, *s2 = s1 + slot;
+   for (int wl = wl0; wl <= S; wl += nwx) {
    if (I.symmetric) {
       // one block D(cx, lcl[l]) per warp, l = 0 .. S: it is also D(lcl[l], cx) transposed, so all four products are
       // forward steps through it:  InsF(x,l), RepF(x,l-1) from U;  InsB(x,l+1), RepB(x,l+1) from W
       const int l = wl;
       const int ml = lm.m(l), ofl = lm.off(l);
-      for (int x = blockIdx.y + 1; x <= T; x += gridDim.y) {
-         const int cx = lm.cl(x), mx = lm.m(x), ox = lm.off(x);
-         const TT *b1 = warp_stage(s1, Dv + ((long long)ox * I.N + (long long)mx * ofl), mx * ml, lane);
-         auto ld = [&](int k, int ll, bool on) { return (on && lane < mx) ? __ldg(vec + vec_uw(vc, C, mp, k, cx, min(max(ll, 0), S)) + lane) : VNS_INT_INF; };
-         const int u1 = ld(0, l - 1, l >= 1), u2 = ld(0, l - 2, l >= 2), w1 = ld(1, l + 1, l <= S - 1), w2 = ld(1, l + 2, l <= S - 2);
-         warp_stage_wait();
+      // double-buffered over x: the block and the four vectors of the NEXT x are in flight (cp.async into the warp's second
+      // slot, plain loads into registers) while the current x is reduced - a warp's iterations were one exposed HBM round
+      // trip each (16 % of the HBM peak on the 20 k-node state)
+      struct XIn { int cx, mx; const TT *b; int u1, u2, w1, w2; };
+      auto issue = [&](int x, char *slot) {
+         XIn q;
+         q.cx = lm.cl(x); q.mx = lm.m(x);
+         const int ox = lm.off(x);
+         q.b = warp_stage(slot, Dv + ((long long)ox * I.N + (long long)q.mx * ofl), q.mx * ml, lane);
+         asm volatile("cp.async.commit_group;");
+         auto ld = [&](int k, int ll, bool on) { return (on && lane < q.mx) ? __ldg(vec + vec_uw(vc, C, mp, k, q.cx, min(max(ll, 0), S)) + lane) : VNS_INT_INF; };
+         q.u1 = ld(0, l - 1, l >= 1); q.u2 = ld(0, l - 2, l >= 2); q.w1 = ld(1, l + 1, l <= S - 1); q.w2 = ld(1, l + 2, l <= S - 2);
+         return q;
+      };
+      int x = blockIdx.y + 1, par = 0;
+      if (x > T) return;      // no x for this grid.y lane, whatever the layer
+      XIn cur = issue(x, s1);
+      for (; x <= T; x += gridDim.y) {
+         const int xn = x + gridDim.y;
+         XIn nxt = cur;
+         if (xn <= T) {
+            nxt = issue(xn, par ? s1 : s2);
+            asm volatile("cp.async.wait_group 1;");
+         } else
+            asm volatile("cp.async.wait_group 0;");
+         __syncwarp();
+         const TT *b1 = cur.b;
+         const int mx = cur.mx;
          int a1 = VNS_INT_INF, a2 = VNS_INT_INF, a3 = VNS_INT_INF, a4 = VNS_INT_INF;
          const int j = min(lane, ml - 1);
 #pragma unroll 2
          for (int s = 0; s < mx; ++s) {
             const int d = (int)b1[s * ml + j];
-            a1 = __viaddmin_s32(__shfl_sync(0xffffffffu, u1, s), d, a1);
-            a2 = __viaddmin_s32(__shfl_sync(0xffffffffu, u2, s), d, a2);
-            a3 = __viaddmin_s32(__shfl_sync(0xffffffffu, w1, s), d, a3);
-            a4 = __viaddmin_s32(__shfl_sync(0xffffffffu, w2, s), d, a4);
+            a1 = __viaddmin_s32(__shfl_sync(0xffffffffu, cur.u1, s), d, a1);
+            a2 = __viaddmin_s32(__shfl_sync(0xffffffffu, cur.u2, s), d, a2);
+            a3 = __viaddmin_s32(__shfl_sync(0xffffffffu, cur.w1, s), d, a3);
+            a4 = __viaddmin_s32(__shfl_sync(0xffffffffu, cur.w2, s), d, a4);
          }
          if (lane < mp) {
             const bool in = lane < ml;
@@ -268,12 +291,14 @@ __global__ void __launch_bounds__(256) k_vec_pairs(InstDev I, PathDev P, const T
             if (l <= S - 1) vec[vec_pair(vc, C, mp, 1, x, l + 1) + lane] = in ? a3 : VNS_INT_INF;
             if (l <= S - 2) vec[vec_pair(vc, C, mp, 3, x, l + 1) + lane] = in ? a4 : VNS_INT_INF;
          }
-         __syncwarp();   // the staged block is overwritten by the next x
+         __syncwarp();   // this x's slot is the target of the staging two iterations on
+         cur = nxt;
+         par ^= 1;
       }
-      return;
+      continue;
    }
    const int l = wl + 1;
-   if (l > S) return;
+   if (l > S) break;
    const int ml = lm.m(l), ma = lm.m(l - 1), ofl = lm.off(l), ofa = lm.off(l - 1);
    for (int x = blockIdx.y + 1; x <= T; x += gridDim.y) {
       const int cx = lm.cl(x), mx = lm.m(x), ox = lm.off(x);
@@ -289,6 +314,7 @@ __global__ void __launch_bounds__(256) k_vec_pairs(InstDev I, PathDev P, const T
       put(vec_pair(vc, C, mp, 1, x, l), vec_bwd(b2, ma, mx, w1, lane));                       // InsB(x,l)   from W(cx,l)
       if (l <= S - 1) put(vec_pair(vc, C, mp, 3, x, l), vec_bwd(b2, ma, mx, w2, lane));       // RepB(x,l)   from W(cx,l+1)
       __syncwarp();   // the staged blocks are overwritten by the next x
+   }
    }
 }
 
