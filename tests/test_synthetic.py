@@ -73,7 +73,7 @@ def test_synthetic_long_tour_candidates(synth, int_path):
     e.set_int_path(int_path)
     try:
         # segment products: 1 = default build, 2 = one-level chains, 3 = two-level (tiles of 32 layers) whatever the size
-        for seg, vec in ((1, True), (3, True), (1, 3), (2, False), (3, False), (1, False), (0, False)):      # vec 3: unpacked vector build
+        for seg, vec in ((1, True), (3, True), (1, 3), (3, 3), (2, False), (3, False), (1, False), (0, False)):      # vec 3: unpacked vector build, 16 lanes per product in the cross products
             e.set_segment_cache(seg)
             e.set_vector_cache(vec)
             ln, lb, fl, first = pg.eval_batch(pg.make_cands(cands))

@@ -244,7 +244,7 @@ static vnsgpu_status prepare_seg(vnsgpu_ctx *ctx, int path, cudaStream_t st)
       LAUNCHED(ctx);
       if (tile) {
          const int ntiles = (grid + SEG_TILE - 1) / SEG_TILE + 1;
-         const size_t sm1 = sizeof(int) * (size_t)I.mp * I.mp;
+         const size_t sm1 = sizeof(int) * (size_t)(2 + SEG_TILES_RING) * I.mp * I.mp;      // mp <= 16 here: 8 KB
          k_seg_tiles<<<ntiles, 256, sm1, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta);
          LAUNCHED(ctx);
          const unsigned g3 = (unsigned)((grid + 1 + 7) / 8), g4 = (unsigned)(((long long)(grid + 1) * ntiles + 7) / 8);
@@ -255,6 +255,7 @@ static vnsgpu_status prepare_seg(vnsgpu_ctx *ctx, int path, cudaStream_t st)
       k_seg_cross<1, GG><<<g4, 256, 0, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta, ntiles);              \
    } while (0)
          if (I.mp <= 8) VNS_SEG_CROSS(8);
+         else if (I.mp <= 10 && ctx->use_vec_pack) VNS_SEG_CROSS(10);
          else if (I.mp <= 16) VNS_SEG_CROSS(16);
          else VNS_SEG_CROSS(32);
 #undef VNS_SEG_CROSS
