@@ -307,11 +307,17 @@ def test_endpoint_vectors_do_not_depend_on_the_grid(name, gx, golden, eng_cache,
     e, sf, pb = eng_cache(name)
     g, a = golden[name], load_arrays(name)
     monkeypatch.setenv("VNSGPU_VEC_PAIRS_GX", str(gx))
+    monkeypatch.setenv("VNSGPU_SEG_CROSS_GRID", str(gx))      # the same for the cross products of the two-level segment build
     po, pg = ob.Oracle(pb).path(a["greedy_vns"], g["greedy"]["T"]), e.path(a["greedy_vns"], g["greedy"]["T"])
     cands = random_candidates(np.random.RandomState(11), po.vns, po.T, 300007 if name == "vm1084" else 60013)
-    ln, lb, fl, first = pg.eval_batch(cands)
     oln, olb = po.eval_batch(cands)
-    assert (ln == oln).all() and (lb == olb).all()
+    try:
+        for seg in (1, 3):                                    # 3: two-level build whatever the size
+            e.set_segment_cache(seg)
+            ln, lb, fl, first = pg.eval_batch(cands)
+            assert (ln == oln).all() and (lb == olb).all(), seg
+    finally:
+        e.set_segment_cache(True)
 
 
 @pytest.mark.parametrize("int_path", [True, False])

@@ -216,6 +216,16 @@ static int eval_mode(const vnsgpu_ctx *ctx, int64_t n)
    return 1;
 }
 
+// T + 2 as the host last read it - when it did and the launch is not being captured into a graph (a graph is replayed on
+// later states) - else `bound`.  Only for grids of kernels whose result does not depend on the grid.
+static int known_layers(vnsgpu_ctx *ctx, int path, cudaStream_t st, int bound)
+{
+   cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+   if (cudaStreamIsCapturing(st, &cap) != cudaSuccess) { cudaGetLastError(); return bound; }
+   const PathHost &ph = ctx->paths[path];
+   return (ph.hdr_ok && cap == cudaStreamCaptureStatusNone) ? std::min(bound, ph.hdr_cache.hdr[HDR_T] + 2) : bound;
+}
+
 static vnsgpu_status prepare_seg(vnsgpu_ctx *ctx, int path, cudaStream_t st)
 {
    const InstDev &I = ctx->I;
@@ -247,17 +257,23 @@ static vnsgpu_status prepare_seg(vnsgpu_ctx *ctx, int path, cudaStream_t st)
          const size_t sm1 = sizeof(int) * (size_t)(2 + SEG_TILES_RING) * I.mp * I.mp;      // mp <= 16 here: 8 KB
          k_seg_tiles<<<ntiles, 256, sm1, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta);
          LAUNCHED(ctx);
-         const unsigned g3 = (unsigned)((grid + 1 + 7) / 8), g4 = (unsigned)(((long long)(grid + 1) * ntiles + 7) / 8);
-#define VNS_SEG_CROSS(GG)                                                                                             \
+         // the cross products stride over their tasks: grids from the header as last read (see prepare_eval), else the bound
+         const int lk = known_layers(ctx, path, st, grid);
+         const int force_g = getenv("VNSGPU_SEG_CROSS_GRID") ? atoi(getenv("VNSGPU_SEG_CROSS_GRID")) : 0;     // tests: a grid below the tasks
+         const unsigned g3 = force_g > 0 ? force_g : (unsigned)((lk + 1 + 7) / 8);
+         const long long ntk = (lk + SEG_TILE - 1) / SEG_TILE + 1;                                            // >= the kernel's nt
+         const unsigned g4 = force_g > 0 ? force_g : (unsigned)std::max(1ll, (SEG_TILE / 2 * ntk * (ntk - 1) + 7) / 8);
+#define VNS_SEG_CROSS(GG, KU)                                                                                         \
    do {                                                                                                               \
-      k_seg_cross<0, GG><<<g3, 256, 0, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta, ntiles);              \
+      k_seg_cross<0, GG, KU><<<g3, 256, 0, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta);                  \
       LAUNCHED(ctx);                                                                                                  \
-      k_seg_cross<1, GG><<<g4, 256, 0, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta, ntiles);              \
+      k_seg_cross<1, GG, KU><<<g4, 256, 0, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta);                  \
    } while (0)
-         if (I.mp <= 8) VNS_SEG_CROSS(8);
-         else if (I.mp <= 10 && ctx->use_vec_pack) VNS_SEG_CROSS(10);
-         else if (I.mp <= 16) VNS_SEG_CROSS(16);
-         else VNS_SEG_CROSS(32);
+         if (I.mp <= 8) VNS_SEG_CROSS(8, 8);
+         else if (I.mp <= 10 && ctx->use_vec_pack) VNS_SEG_CROSS(10, 12);
+         else if (I.mp <= 12) VNS_SEG_CROSS(16, 12);
+         else if (I.mp <= 16) VNS_SEG_CROSS(16, 16);
+         else VNS_SEG_CROSS(32, 32);
 #undef VNS_SEG_CROSS
       }
    } else
@@ -363,10 +379,7 @@ static vnsgpu_status prepare_eval(vnsgpu_ctx *ctx, int path, int mode, cudaStrea
    // 1.67 ms, 4 waves 0.477 / 1.60 ms, 8 waves 0.464 / 1.56 ms, 16 waves the same (profiles/r4y_waves.txt).
    // k_vec_pairs' grid.x covers the layers: from the header as last read back when there is one and the launch is not being
    // captured into a graph (a graph is replayed on later states), else from the bound - the surplus warps return at once
-   cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
-   if (cudaStreamIsCapturing(st, &cap) != cudaSuccess) { cudaGetLastError(); cap = cudaStreamCaptureStatusActive; }
-   const PathHost &ph = ctx->paths[path];
-   const int Sknown = (ph.hdr_ok && cap == cudaStreamCaptureStatusNone) ? std::min(Smax, ph.hdr_cache.hdr[HDR_T] + 1) : Smax;
+   const int Sknown = known_layers(ctx, path, st, Smax + 1) - 1;
    auto layer_lanes = [&](auto kern, size_t sm, int gx) {
       int nb = 0;
       if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, thr, sm) != cudaSuccess || nb < 1) { cudaGetLastError(); nb = 1; }

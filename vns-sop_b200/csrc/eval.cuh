@@ -724,25 +724,54 @@ static __device__ __forceinline__ SegMeta seg_meta(const InstDev &I, const int *
    return SegMeta{meta, meta + 5 * R, reinterpret_cast<const long long *>(meta + 2 * R), I.N};
 }
 
-// One pass of a warp: 32 / G products C_q = A (x) B_q at once (q = lane / G), A (ma x mk) staged in shared memory with a
-// pitch of 32 ints and INF beyond column mk, lane j = lane % G owns column j of B_q in KU registers (one coalesced load per
-// row of B_q) and walks the rows of A with 16-byte broadcast loads: per row KU DPX add-mins and KU / 4 shared loads.
+// A warp's passes over b = b0, b0 + bstep .. b1: 32 / G products C_q = A (x) B_q at once (q = lane / G), A (ma x mk) staged in
+// shared memory with a pitch of 32 ints and INF beyond column mk, lane j = lane % G owns column j of B_q in KU registers (one
+// coalesced load per row of B_q) and walks the rows of A with 16-byte broadcast loads: per row KU DPX add-mins and KU / 4
+// shared loads.  The NEXT pass's columns are loaded before the current pass is reduced (the passes were one exposed L2 round
+// trip each).
 template <int G, int KU>
-static __device__ __forceinline__ void seg_warp_pass(int *__restrict__ out, const int *__restrict__ As, const int *__restrict__ Bm, bool on,
-                                                     int ma, int mk, int mb, int j)
+static __device__ __forceinline__ void seg_warp_passes(int *__restrict__ Dv, const SegMeta &sm, const int *__restrict__ As, int a, int x,
+                                                       int b0, int b1, int bstep, int ma, int mk, int q, int j)
 {
-   int breg[KU];
+   constexpr int NB = 32 / G;
+   struct Pass { bool on; int mb; long long out; };
+   int breg[KU], nreg[KU];
+   auto fetch = [&](int bb, int *r) {
+      Pass p;
+      const int b = bb + q * bstep;
+      p.on = b <= b1 && q < NB;                        // G = 10: lanes 30, 31 idle
+      p.mb = p.on ? sm.m(b) : 0;
+      p.out = p.on ? sm.off(a, b) : 0;
+      const int *Bm = Dv + (p.on ? sm.off(x, b) : 0);
 #pragma unroll
-   for (int t = 0; t < KU; ++t) breg[t] = (on && t < mk && j < mb) ? __ldcg(Bm + t * mb + j) : VNS_INT_INF;
-   for (int i = 0; i < ma; ++i) {
-      int x = VNS_INT_INF, y = VNS_INT_INF;
+      for (int t = 0; t < KU; ++t) r[t] = (p.on && t < mk && j < p.mb) ? __ldcg(Bm + t * p.mb + j) : VNS_INT_INF;
+      return p;
+   };
+   Pass cur = fetch(b0, breg);
+   for (int bb = b0; bb <= b1; bb += NB * bstep) {
+      const int bn = bb + NB * bstep;
+      Pass nxt = cur;
+      if (bn <= b1) nxt = fetch(bn, nreg);
+      // the row loop is the kernel (ncu r5f: 54 instructions per row, 12 of them add-mins): pointers stepped instead of
+      // indexed, the store predicated in place instead of a divergent region
+      int *op = Dv + cur.out + j;
+      const int4 *ap = reinterpret_cast<const int4 *>(As);
+      const int st_ok = cur.on && j < cur.mb;
+      for (int i = 0; i < ma; ++i, op += cur.mb, ap += 8) {
+         int u = VNS_INT_INF, v = VNS_INT_INF;
 #pragma unroll
-      for (int t = 0; t < KU; t += 4) {
-         const int4 p = *reinterpret_cast<const int4 *>(As + i * 32 + t);
-         x = __viaddmin_s32(p.x, breg[t], x); y = __viaddmin_s32(p.y, breg[t + 1], y);
-         x = __viaddmin_s32(p.z, breg[t + 2], x); y = __viaddmin_s32(p.w, breg[t + 3], y);
+         for (int t = 0; t < KU; t += 4) {
+            const int4 p = ap[t / 4];
+            u = __viaddmin_s32(p.x, breg[t], u); v = __viaddmin_s32(p.y, breg[t + 1], v);
+            u = __viaddmin_s32(p.z, breg[t + 2], u); v = __viaddmin_s32(p.w, breg[t + 3], v);
+         }
+         asm volatile("{ .reg .pred p; setp.ne.s32 p, %2, 0; @p st.global.b32 [%0], %1; }" ::"l"(op), "r"(min(u, v)), "r"(st_ok) : "memory");
       }
-      if (on && j < mb) out[i * mb + j] = min(x, y);
+      if (bn <= b1) {
+#pragma unroll
+         for (int t = 0; t < KU; ++t) breg[t] = nreg[t];
+      }
+      cur = nxt;
    }
 }
 
@@ -800,49 +829,49 @@ static __global__ void __launch_bounds__(256) k_seg_tiles(InstDev I, PathDev P, 
 
 // steps 3 (MODE 0: one warp per a, b over the tile starts beyond the next one) and 4 (MODE 1: one warp per (a, tile tb),
 // b over the tile's layers).  G = lanes per product (>= mp; 10 = three products per warp for clusters of 9 or 10 samples, where
-// 16 lanes per product and 16 register rows left 61 % of the add-mins on padding).  Static shared memory: 8 warps x 32 x 32 ints.
-template <int MODE, int G>
-__global__ void __launch_bounds__(256) k_seg_cross(InstDev I, PathDev P, int *Dv, const int *meta, int ntiles_cap)
+// 16 lanes per product and 16 register rows left 61 % of the add-mins on padding), KU = register rows (>= mp, chosen by the host:
+// one size per kernel keeps the double-buffered columns at 2 KU registers).  Static shared memory: 8 warps x 32 x 32 ints.
+template <int MODE, int G, int KU>
+__global__ void __launch_bounds__(256) k_seg_cross(InstDev I, PathDev P, int *Dv, const int *meta)
 {
    __shared__ __align__(16) int s_A[8][32 * 32];
-   constexpr int NB = 32 / G;
    const int T = P.hdr[HDR_T], S = T + 1;
    const SegMeta sm = seg_meta(I, meta);
    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, q = lane / G, j = lane % G;
    int *As = s_A[wib];
-   const long long task = (long long)blockIdx.x * (blockDim.x >> 5) + wib;
-   int a, x, b0, b1, bstep;
-   if (MODE == 0) {
-      a = (int)task;
-      if (a > S || a % SEG_TILE == 0) return;                  // tile starts: step 2
-      x = (a / SEG_TILE + 1) * SEG_TILE;
-      b0 = x + SEG_TILE; b1 = S; bstep = SEG_TILE;
-   } else {
-      a = (int)(task / ntiles_cap);
-      const int tb = (int)(task % ntiles_cap);
-      if (a > S || tb <= a / SEG_TILE) return;
-      x = tb * SEG_TILE;
-      b0 = x + 1; b1 = min(S, x + SEG_TILE - 1); bstep = 1;
-   }
-   if (b0 > b1 || x > S || x < a + 1) return;
-   const int ma = sm.m(a), mk = sm.m(x);
-   {
-      const int *A = Dv + sm.off(a, x);
-      for (int e = lane; e < ma * 32; e += 32) {
-         const int i = e >> 5, t = e & 31;
-         As[e] = t < mk ? __ldcg(A + i * mk + t) : VNS_INT_INF;
+   // the warps stride over the tasks: the host sizes the grid from T as it last read it, the result does not depend on it
+   const int nt = (S - 1) / SEG_TILE + 1;                        // tiles with a layer b that is not a tile start
+   // MODE 1: only the pairs (a, tb) with tb beyond a's tile are enumerated - tile row ta holds SEG_TILE (nt - 1 - ta) of them -
+   // so every warp of a block has work (a rectangular enumeration left half of the resident warps idle)
+   const long long ntasks = MODE == 0 ? S + 1 : (long long)(SEG_TILE / 2) * nt * (nt - 1), nwarps = (long long)gridDim.x * (blockDim.x >> 5);
+   for (long long task = (long long)blockIdx.x * (blockDim.x >> 5) + wib; task < ntasks; task += nwarps) {
+      int a, x, b0, b1, bstep;
+      if (MODE == 0) {
+         a = (int)task;
+         if (a % SEG_TILE == 0) continue;                        // tile starts: step 2
+         x = (a / SEG_TILE + 1) * SEG_TILE;
+         b0 = x + SEG_TILE; b1 = S; bstep = SEG_TILE;
+      } else {
+         int ta = 0;
+         long long base = 0;
+         while (base + (long long)SEG_TILE * (nt - 1 - ta) <= task) { base += (long long)SEG_TILE * (nt - 1 - ta); ++ta; }
+         const int r = nt - 1 - ta, idx = (int)(task - base);
+         a = ta * SEG_TILE + idx / r;
+         const int tb = ta + 1 + idx % r;
+         x = tb * SEG_TILE;
+         b0 = x + 1; b1 = min(S, x + SEG_TILE - 1); bstep = 1;
       }
-      __syncwarp();
-   }
-   for (int bb = b0; bb <= b1; bb += NB * bstep) {
-      const int b = bb + q * bstep;
-      const bool on = b <= b1 && q < NB;               // G = 10: lanes 30, 31 idle
-      const int mb = on ? sm.m(b) : 0;
-      int *out = Dv + (on ? sm.off(a, b) : 0);
-      const int *Bm = Dv + (on ? sm.off(x, b) : 0);
-      if (mk <= 8) seg_warp_pass<G, 8>(out, As, Bm, on, ma, mk, mb, j);
-      else if (mk <= 12) seg_warp_pass<G, 12>(out, As, Bm, on, ma, mk, mb, j);
-      else if (mk <= 16) seg_warp_pass<G, 16>(out, As, Bm, on, ma, mk, mb, j);
-      else seg_warp_pass<G, 32>(out, As, Bm, on, ma, mk, mb, j);
+      if (b0 > b1 || x > S || x < a + 1) continue;
+      const int ma = sm.m(a), mk = sm.m(x);
+      __syncwarp();                                              // the task before is done with the staged operand
+      {
+         const int *A = Dv + sm.off(a, x);
+         for (int e = lane; e < ma * 32; e += 32) {
+            const int i = e >> 5, t = e & 31;
+            As[e] = t < mk ? __ldcg(A + i * mk + t) : VNS_INT_INF;
+         }
+         __syncwarp();
+      }
+      seg_warp_passes<G, KU>(Dv, sm, As, a, x, b0, b1, bstep, ma, mk, q, j);
    }
 }
