@@ -5,6 +5,7 @@
 #include "eval.cuh"
 #include "vec.cuh"
 #include "kernels.cuh"
+#include "chain2_host.hpp"
 
 extern "C" {
 
@@ -361,7 +362,7 @@ static vnsgpu_status prepare_eval(vnsgpu_ctx *ctx, int path, int mode, cudaStrea
    const int LS = I.C + 2;
    if (!ctx->d_vec) {
       CK(cudaMalloc(&ctx->d_vec, sizeof(int) * vec_ints(I.C, LS, I.mp)));
-      CK(cudaMalloc(&ctx->d_veclb, sizeof(int) * vec_lb_ints(I.C, LS)));
+      CK(cudaMalloc(&ctx->d_veclb, sizeof(int) * (vec_lb_ints(I.C, LS) + (size_t)2 * LS * I.mp)));   // + F and B rows as int32
       CK(cudaMemsetAsync(ctx->d_vec, 0, sizeof(int) * vec_ints(I.C, LS, I.mp), st));
       CK(cudaMemsetAsync(ctx->d_veclb, 0, sizeof(int) * vec_lb_ints(I.C, LS), st));
    }
@@ -388,8 +389,14 @@ static vnsgpu_status prepare_eval(vnsgpu_ctx *ctx, int path, int mode, cudaStrea
    const int force_gxp = getenv("VNSGPU_VEC_PAIRS_GX") ? atoi(getenv("VNSGPU_VEC_PAIRS_GX")) : 0;   // tests: a grid.x below the layers
    const int gxu = (I.C + wpc - 1) / wpc, gxp = force_gxp > 0 ? force_gxp : (Sknown + 1 + wpc - 1) / wpc;
    const int gyu = u16 ? layer_lanes(k_vec_uw<unsigned short>, smem, gxu) : layer_lanes(k_vec_uw<int>, smem, gxu);
-   const int gyp = u16 ? layer_lanes(k_vec_pairs<unsigned short>, smem, gxp) : layer_lanes(k_vec_pairs<int>, smem, gxp);
+   const size_t smem_p = 2 * vec_pairs_slot_bytes(I.mp, u16 ? sizeof(unsigned short) : sizeof(int)) * wpc;     // blocks + their four vectors
+   const int gyp = u16 ? layer_lanes(k_vec_pairs<unsigned short>, smem_p, gxp) : layer_lanes(k_vec_pairs<int>, smem_p, gxp);
+   // cluster-pair minima as int32 (shared with the chain forms; the call synchronises ctx->stream when it builds them)
+   if (!ctx->d_dmin32) { vnsgpu_status ds = c2_ensure_tables(ctx); if (ds) return ds; }
+   int *fbi = ctx->d_veclb + vec_lb_ints(I.C, LS);
    PhaseTimer pt(ctx, VNSGPU_PHASE_VEC, st);
+   k_rows_to_int<<<std::min(64, (Smax + 2) * I.mp / 256 + 1), 256, 0, st>>>(I, ctx->paths[path].d, fbi, LS);
+   LAUNCHED(ctx);
    // small clusters on a symmetric table: 2 - 4 clusters per warp (k_vec_uw_packed)
    const int pslot = (I.symmetric && ctx->use_vec_pack) ? (I.mp <= 8 ? 8 : (I.mp <= 10 ? 10 : (I.mp <= 16 ? 16 : 0))) : 0;
    if (pslot) {
@@ -398,15 +405,15 @@ static vnsgpu_status prepare_eval(vnsgpu_ctx *ctx, int path, int mode, cudaStrea
       int gyk = 1;
 #define VNS_VEC_PACKED(TT, SL, TAB)                                                                                   \
    gyk = layer_lanes(k_vec_uw_packed<TT, SL>, smk, gxk),                                                                 \
-   k_vec_uw_packed<TT, SL><<<dim3(gxk, gyk), thr, smk, st>>>(I, ctx->paths[path].d, TAB, ctx->d_segmeta, ctx->d_vec, ctx->d_veclb, LS)
+   k_vec_uw_packed<TT, SL><<<dim3(gxk, gyk), thr, smk, st>>>(I, ctx->paths[path].d, TAB, ctx->d_segmeta, ctx->d_vec, ctx->d_veclb, LS, fbi, ctx->d_dmin32)
       if (u16) { if (pslot == 8) VNS_VEC_PACKED(unsigned short, 8, ctx->d_D16); else if (pslot == 10) VNS_VEC_PACKED(unsigned short, 10, ctx->d_D16); else VNS_VEC_PACKED(unsigned short, 16, ctx->d_D16); }
       else { if (pslot == 8) VNS_VEC_PACKED(int, 8, ctx->d_D32); else if (pslot == 10) VNS_VEC_PACKED(int, 10, ctx->d_D32); else VNS_VEC_PACKED(int, 16, ctx->d_D32); }
 #undef VNS_VEC_PACKED
-   } else if (u16) k_vec_uw<unsigned short><<<dim3(gxu, gyu), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D16, ctx->d_segmeta, ctx->d_vec, ctx->d_veclb, LS);
-   else k_vec_uw<int><<<dim3(gxu, gyu), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta, ctx->d_vec, ctx->d_veclb, LS);
+   } else if (u16) k_vec_uw<unsigned short><<<dim3(gxu, gyu), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D16, ctx->d_segmeta, ctx->d_vec, ctx->d_veclb, LS, fbi, ctx->d_dmin32);
+   else k_vec_uw<int><<<dim3(gxu, gyu), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta, ctx->d_vec, ctx->d_veclb, LS, fbi, ctx->d_dmin32);
    LAUNCHED(ctx);
-   if (u16) k_vec_pairs<unsigned short><<<dim3(gxp, gyp), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D16, ctx->d_segmeta, ctx->d_vec, LS);
-   else k_vec_pairs<int><<<dim3(gxp, gyp), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta, ctx->d_vec, LS);
+   if (u16) k_vec_pairs<unsigned short><<<dim3(gxp, gyp), thr, smem_p, st>>>(I, ctx->paths[path].d, ctx->d_D16, ctx->d_segmeta, ctx->d_vec, LS);
+   else k_vec_pairs<int><<<dim3(gxp, gyp), thr, smem_p, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta, ctx->d_vec, LS);
    LAUNCHED(ctx);
    return VNSGPU_OK;
 }

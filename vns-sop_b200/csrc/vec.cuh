@@ -56,6 +56,9 @@ __device__ __forceinline__ unsigned vec_pair(const VecCache &vc, int C, int mp, 
 // TT = int (int32 table) or unsigned short (uint16 table: half the bytes).  Slot size: vec_slot_bytes.
 __host__ __device__ inline size_t vec_slot_bytes(int mp, size_t elem) { return (((size_t)mp * mp * elem + 15) & ~(size_t)15) + 32; }
 
+// k_vec_pairs: a staged block + the four endpoint vectors it is multiplied with (pitch: mp rounded up to 4 ints)
+__host__ __device__ inline size_t vec_pairs_slot_bytes(int mp, size_t elem) { return vec_slot_bytes(mp, elem) + (size_t)16 * ((mp + 3) & ~3); }
+
 template <typename TT>
 __device__ __forceinline__ const TT *warp_stage(char *slot, const TT *__restrict__ src, int n, int lane)
 {
@@ -113,11 +116,23 @@ __device__ __forceinline__ LayerMeta layer_meta(const InstDev &I, const int *met
    return LayerMeta{meta, meta + 4 * R, meta + 5 * R};
 }
 
+// F and B rows as int32 (fbi: F rows, then B rows from LS * mp on): the build kernels read every row once per cluster, and a
+// double -> int conversion costs them an FP64-pipe instruction each time (the hottest stall of k_vec_uw_packed in ncu r5h)
+static __global__ void __launch_bounds__(256) k_rows_to_int(InstDev I, PathDev P, int *__restrict__ fbi, int LS)
+{
+   const int n = (P.hdr[HDR_T] + 2) * I.mp;
+   for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) {
+      fbi[e] = (int)P.F[e];
+      fbi[LS * I.mp + e] = (int)P.B[e];
+   }
+}
+
 // one warp per (l, c), l strided over grid.y: consecutive warps read consecutive blocks of row band lcl[l] (U) and write
 // consecutive vectors.  Needs mp <= 32.  Dynamic shared memory: 2 slots (vec_slot_bytes) per warp.
 template <typename TT>
 __global__ void __launch_bounds__(256) k_vec_uw(InstDev I, PathDev P, const TT *__restrict__ Dv, const int *__restrict__ meta,
-                                                int *__restrict__ vec, int *__restrict__ lbs, int LS)
+                                                int *__restrict__ vec, int *__restrict__ lbs, int LS, const int *__restrict__ fbi,
+                                                const int *__restrict__ dmin)
 {
    extern __shared__ int smem_i[];
    const int T = P.hdr[HDR_T], S = T + 1, C = I.C, mp = I.mp;
@@ -137,15 +152,15 @@ __global__ void __launch_bounds__(256) k_vec_uw(InstDev I, PathDev P, const TT *
       const TT *bU = nullptr, *bW = nullptr;
       if (doU || sym) bU = warp_stage(sU, Dv + ((long long)ol * I.N + (long long)ml * oc), ml * mc, lane);     // D(cl, c)
       if (doW && !sym) bW = warp_stage(sW, Dv + ((long long)oc * I.N + (long long)mc * ol), mc * ml, lane);    // D(c, cl)
-      const int f = (doU && lane < ml) ? (int)P.F[(size_t)l * mp + lane] : VNS_INT_INF;
-      const int bv = (doW && lane < ml) ? (int)P.B[(size_t)l * mp + lane] : VNS_INT_INF;
+      const int f = (doU && lane < ml) ? __ldg(fbi + l * mp + lane) : VNS_INT_INF;
+      const int bv = (doW && lane < ml) ? __ldg(fbi + (LS + l) * mp + lane) : VNS_INT_INF;
       int lb_ins = 0, lb_rep = 0, lb_rem = 0;
       if (doW && lane == 0) {   // lower-bound sums (integers: order-free)
          const int a = lm.cl(l - 1), nx = l <= S - 1 ? lm.cl(l + 1) : cl;
-         const int din = (int)I.dmin[(size_t)a * C + c];
-         lb_ins = din + (int)I.dmin[(size_t)c * C + cl];
-         lb_rep = din + (int)I.dmin[(size_t)c * C + nx];
-         lb_rem = (int)I.dmin[(size_t)a * C + nx];
+         const int din = __ldg(dmin + (size_t)a * C + c);
+         lb_ins = din + __ldg(dmin + (size_t)c * C + cl);
+         lb_rep = din + __ldg(dmin + (size_t)c * C + nx);
+         lb_rem = __ldg(dmin + (size_t)a * C + nx);
       }
       warp_stage_wait();
       if (doU) {   // U(c,l) = F[l] (x) D(cl, c)
@@ -172,7 +187,8 @@ __global__ void __launch_bounds__(256) k_vec_uw(InstDev I, PathDev P, const TT *
 // samples the one-cluster-per-warp form has a third of its lanes busy (20 k-node instance: 0.66 ms for 0.5 GB).
 template <typename TT, int SLOT>
 __global__ void __launch_bounds__(256) k_vec_uw_packed(InstDev I, PathDev P, const TT *__restrict__ Dv, const int *__restrict__ meta,
-                                                       int *__restrict__ vec, int *__restrict__ lbs, int LS)
+                                                       int *__restrict__ vec, int *__restrict__ lbs, int LS, const int *__restrict__ fbi,
+                                                       const int *__restrict__ dmin)
 {
    extern __shared__ int smem_i[];
    constexpr int PK = 32 / SLOT;
@@ -192,23 +208,35 @@ __global__ void __launch_bounds__(256) k_vec_uw_packed(InstDev I, PathDev P, con
       const int cl = lm.cl(l), ml = lm.m(l), ol = lm.off(l);
       const bool doU = l <= S - 1, doW = l >= 1;
       const TT *run = warp_stage(sU, Dv + ((long long)ol * I.N + (long long)ml * oc0), ml * (oend - oc0), lane);   // D(cl, c0 ..)
-      const int f = (doU && lane < ml) ? (int)P.F[(size_t)l * mp + lane] : VNS_INT_INF;
-      const int bv = (doW && lane < ml) ? (int)P.B[(size_t)l * mp + lane] : VNS_INT_INF;
+      const int f = (doU && lane < ml) ? __ldg(fbi + l * mp + lane) : VNS_INT_INF;
+      const int bv = (doW && lane < ml) ? __ldg(fbi + (LS + l) * mp + lane) : VNS_INT_INF;
       int lb_ins = 0, lb_rep = 0, lb_rem = 0;
       if (doW && cok && j == 0) {   // lower-bound sums (integers: order-free)
          const int a = lm.cl(l - 1), nx = l <= S - 1 ? lm.cl(l + 1) : cl;
-         const int din = (int)I.dmin[(size_t)a * C + c];
-         lb_ins = din + (int)I.dmin[(size_t)c * C + cl];
-         lb_rep = din + (int)I.dmin[(size_t)c * C + nx];
-         lb_rem = (int)I.dmin[(size_t)a * C + nx];
+         const int din = __ldg(dmin + (size_t)a * C + c);
+         lb_ins = din + __ldg(dmin + (size_t)c * C + cl);
+         lb_rep = din + __ldg(dmin + (size_t)c * C + nx);
+         lb_rem = __ldg(dmin + (size_t)a * C + nx);
       }
       warp_stage_wait();
-      const TT *blk = run + ml * (oc - oc0) + min(j, max(mc, 1) - 1);      // this group's block, this lane's column
+      // this group's block, this lane's column; idle groups walk the start of the run (their results are not stored)
+      const TT *blk = cok ? run + ml * (oc - oc0) + min(j, max(mc, 1) - 1) : run;
       int u = VNS_INT_INF, wv = VNS_INT_INF;
-      for (int s_ = 0; s_ < ml; ++s_) {           // both products walk the same staged entry (symmetric table)
-         const int d = cok ? (int)blk[s_ * mc] : 0;
-         u = __viaddmin_s32(__shfl_sync(0xffffffffu, f, s_), d, u);
-         wv = __viaddmin_s32(__shfl_sync(0xffffffffu, bv, s_), d, wv);
+      // both products walk the same staged entry (symmetric table).  The kernel is issue-bound (ncu r5h: 376 instructions per
+      // (warp, layer), 20 of them add-mins): a layer of SLOT samples - the common case - runs a fixed, unrolled trip count
+      if (ml == SLOT) {
+#pragma unroll
+         for (int s_ = 0; s_ < SLOT; ++s_, blk += mc) {
+            const int d = (int)*blk;
+            u = __viaddmin_s32(__shfl_sync(0xffffffffu, f, s_), d, u);
+            wv = __viaddmin_s32(__shfl_sync(0xffffffffu, bv, s_), d, wv);
+         }
+      } else {
+         for (int s_ = 0; s_ < ml; ++s_, blk += mc) {
+            const int d = (int)*blk;
+            u = __viaddmin_s32(__shfl_sync(0xffffffffu, f, s_), d, u);
+            wv = __viaddmin_s32(__shfl_sync(0xffffffffu, bv, s_), d, wv);
+         }
       }
       if (cok && j < mp) {
          if (doU) {
@@ -238,7 +266,7 @@ __global__ void __launch_bounds__(256) k_vec_pairs(InstDev I, PathDev P, const T
    const int wl0 = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), nwx = (int)((gridDim.x * blockDim.x) >> 5);
    const LayerMeta lm = layer_meta(I, meta);
    VecCache vc{vec, nullptr, LS};
-   const size_t slot = vec_slot_bytes(mp, sizeof(TT));
+   const size_t slot = vec_pairs_slot_bytes(mp, sizeof(TT)), voff = vec_slot_bytes(mp, sizeof(TT));
    char *s1 = reinterpret_cast<char *>(smem_i) + (threadIdx.x >> 5) * 2 * slot, *s2 = s1 + slot;
    for (int wl = wl0; wl <= S; wl += nwx) {
    if (I.symmetric) {
@@ -248,48 +276,78 @@ __global__ void __launch_bounds__(256) k_vec_pairs(InstDev I, PathDev P, const T
       const int ml = lm.m(l), ofl = lm.off(l);
       // double-buffered over x: the block and the four vectors of the NEXT x are in flight (cp.async into the warp's second
       // slot, plain loads into registers) while the current x is reduced - a warp's iterations were one exposed HBM round
-      // trip each (16 % of the HBM peak on the 20 k-node state)
-      struct XIn { int cx, mx; const TT *b; int u1, u2, w1, w2; };
-      auto issue = [&](int x, char *slot) {
+      // trip each (16 % of the HBM peak on the 20 k-node state).  After that the kernel was issue-bound (ncu r5h: 367
+      // instructions per (x, l), 40 of them add-mins): the parts of the indices that do not depend on x are computed once per
+      // layer, the product walks two block rows per trip with a stepped pointer.
+      const unsigned xstr = (unsigned)LS * (unsigned)mp, fstr = (unsigned)LS * xstr, pbase = (unsigned)(2 * LS * C + LS) * (unsigned)mp;
+      const bool on1 = l >= 1, on2 = l >= 2, on3 = l <= S - 1, on4 = l <= S - 2;
+      // vec_uw(k, cx, ll) = ((k LS + ll) C + cx) mp;   vec_pair(fam, x, ll) = pbase + fam fstr + x xstr + ll mp
+      const unsigned ld1 = (unsigned)(max(l - 1, 0) * C) * mp + lane, ld2 = (unsigned)(max(l - 2, 0) * C) * mp + lane;
+      const unsigned ld3 = (unsigned)((LS + min(l + 1, S)) * C) * mp + lane, ld4 = (unsigned)((LS + min(l + 2, S)) * C) * mp + lane;
+      const unsigned st1 = pbase + (unsigned)l * mp + lane, st2 = pbase + 2 * fstr + (unsigned)max(l - 1, 0) * mp + lane;
+      const unsigned st3 = pbase + fstr + (unsigned)(l + 1) * mp + lane, st4 = pbase + 3 * fstr + (unsigned)(l + 1) * mp + lane;
+      // the four vectors go to shared memory with the block (4-byte cp.async per lane) and are read back four entries at a
+      // time as broadcast loads: the shuffles that handed them round (4 per block row) had the kernel on the shared-memory /
+      // shuffle pipe (ncu r5h: LSU pipe 60 %, short-scoreboard stalls 3.4 warps per issue)
+      const int VP = (mp + 3) & ~3;
+      struct XIn { int mx; const TT *b; const int *v; };
+      auto issue = [&](int x, char *slot_) {
          XIn q;
-         q.cx = lm.cl(x); q.mx = lm.m(x);
-         const int ox = lm.off(x);
-         q.b = warp_stage(slot, Dv + ((long long)ox * I.N + (long long)q.mx * ofl), q.mx * ml, lane);
-         asm volatile("cp.async.commit_group;");
-         auto ld = [&](int k, int ll, bool on) { return (on && lane < q.mx) ? __ldg(vec + vec_uw(vc, C, mp, k, q.cx, min(max(ll, 0), S)) + lane) : VNS_INT_INF; };
-         q.u1 = ld(0, l - 1, l >= 1); q.u2 = ld(0, l - 2, l >= 2); q.w1 = ld(1, l + 1, l <= S - 1); q.w2 = ld(1, l + 2, l <= S - 2);
+         const int cx = lm.cl(x), ox = lm.off(x);
+         q.mx = lm.m(x);
+         q.b = warp_stage(slot_, Dv + ((long long)ox * I.N + (long long)q.mx * ofl), q.mx * ml, lane);
+         q.v = reinterpret_cast<const int *>(slot_ + voff);
+         if (lane < q.mx) {
+            const unsigned cb = (unsigned)cx * mp, d0 = (unsigned)__cvta_generic_to_shared(slot_ + voff) + 4 * lane;
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d0), "l"(vec + ld1 + cb) : "memory");
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d0 + 4 * VP), "l"(vec + ld2 + cb) : "memory");
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d0 + 8 * VP), "l"(vec + ld3 + cb) : "memory");
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d0 + 12 * VP), "l"(vec + ld4 + cb) : "memory");
+         }
+         asm volatile("cp.async.commit_group;" ::: "memory");
          return q;
       };
       int x = blockIdx.y + 1, par = 0;
       if (x > T) return;      // no x for this grid.y lane, whatever the layer
+      const int j = min(lane, ml - 1);
+      const bool st_on = lane < mp, in_l = lane < ml;
       XIn cur = issue(x, s1);
       for (; x <= T; x += gridDim.y) {
          const int xn = x + gridDim.y;
          XIn nxt = cur;
          if (xn <= T) {
             nxt = issue(xn, par ? s1 : s2);
-            asm volatile("cp.async.wait_group 1;");
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
          } else
-            asm volatile("cp.async.wait_group 0;");
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
          __syncwarp();
-         const TT *b1 = cur.b;
+         const TT *bp = cur.b + j;
+         const int *v = cur.v;
          const int mx = cur.mx;
+         // vectors whose layer does not exist (on1 .. on4 false) are read all the same - from the row next to it - and their
+         // results are not stored
          int a1 = VNS_INT_INF, a2 = VNS_INT_INF, a3 = VNS_INT_INF, a4 = VNS_INT_INF;
-         const int j = min(lane, ml - 1);
-#pragma unroll 2
-         for (int s = 0; s < mx; ++s) {
-            const int d = (int)b1[s * ml + j];
-            a1 = __viaddmin_s32(__shfl_sync(0xffffffffu, cur.u1, s), d, a1);
-            a2 = __viaddmin_s32(__shfl_sync(0xffffffffu, cur.u2, s), d, a2);
-            a3 = __viaddmin_s32(__shfl_sync(0xffffffffu, cur.w1, s), d, a3);
-            a4 = __viaddmin_s32(__shfl_sync(0xffffffffu, cur.w2, s), d, a4);
+         int s = 0;
+         for (; s + 3 < mx; s += 4, bp += 4 * ml) {
+            const int4 U1 = *reinterpret_cast<const int4 *>(v + s), U2 = *reinterpret_cast<const int4 *>(v + VP + s);
+            const int4 W1 = *reinterpret_cast<const int4 *>(v + 2 * VP + s), W2 = *reinterpret_cast<const int4 *>(v + 3 * VP + s);
+            const int d0 = (int)bp[0], d1 = (int)bp[ml], d2 = (int)bp[2 * ml], d3 = (int)bp[3 * ml];
+            a1 = __viaddmin_s32(U1.x, d0, a1); a2 = __viaddmin_s32(U2.x, d0, a2); a3 = __viaddmin_s32(W1.x, d0, a3); a4 = __viaddmin_s32(W2.x, d0, a4);
+            a1 = __viaddmin_s32(U1.y, d1, a1); a2 = __viaddmin_s32(U2.y, d1, a2); a3 = __viaddmin_s32(W1.y, d1, a3); a4 = __viaddmin_s32(W2.y, d1, a4);
+            a1 = __viaddmin_s32(U1.z, d2, a1); a2 = __viaddmin_s32(U2.z, d2, a2); a3 = __viaddmin_s32(W1.z, d2, a3); a4 = __viaddmin_s32(W2.z, d2, a4);
+            a1 = __viaddmin_s32(U1.w, d3, a1); a2 = __viaddmin_s32(U2.w, d3, a2); a3 = __viaddmin_s32(W1.w, d3, a3); a4 = __viaddmin_s32(W2.w, d3, a4);
          }
-         if (lane < mp) {
-            const bool in = lane < ml;
-            if (l >= 1) vec[vec_pair(vc, C, mp, 0, x, l) + lane] = in ? a1 : VNS_INT_INF;
-            if (l >= 2) vec[vec_pair(vc, C, mp, 2, x, l - 1) + lane] = in ? a2 : VNS_INT_INF;
-            if (l <= S - 1) vec[vec_pair(vc, C, mp, 1, x, l + 1) + lane] = in ? a3 : VNS_INT_INF;
-            if (l <= S - 2) vec[vec_pair(vc, C, mp, 3, x, l + 1) + lane] = in ? a4 : VNS_INT_INF;
+         for (; s < mx; ++s, bp += ml) {
+            const int d0 = (int)bp[0];
+            a1 = __viaddmin_s32(v[s], d0, a1); a2 = __viaddmin_s32(v[VP + s], d0, a2);
+            a3 = __viaddmin_s32(v[2 * VP + s], d0, a3); a4 = __viaddmin_s32(v[3 * VP + s], d0, a4);
+         }
+         if (st_on) {
+            const unsigned xb = (unsigned)x * xstr;
+            if (on1) vec[st1 + xb] = in_l ? a1 : VNS_INT_INF;
+            if (on2) vec[st2 + xb] = in_l ? a2 : VNS_INT_INF;
+            if (on3) vec[st3 + xb] = in_l ? a3 : VNS_INT_INF;
+            if (on4) vec[st4 + xb] = in_l ? a4 : VNS_INT_INF;
          }
          __syncwarp();   // this x's slot is the target of the staging two iterations on
          cur = nxt;
