@@ -393,10 +393,14 @@ static vnsgpu_status prepare_eval(vnsgpu_ctx *ctx, int path, int mode, cudaStrea
    const int gyp = u16 ? layer_lanes(k_vec_pairs<unsigned short>, smem_p, gxp) : layer_lanes(k_vec_pairs<int>, smem_p, gxp);
    // cluster-pair minima as int32 (shared with the chain forms; the call synchronises ctx->stream when it builds them)
    if (!ctx->d_dmin32) { vnsgpu_status ds = c2_ensure_tables(ctx); if (ds) return ds; }
-   int *fbi = ctx->d_veclb + vec_lb_ints(I.C, LS);
+   // F / B rows as int32 for the build kernels: from 512 clusters on (below that the conversions inside the kernels cost
+   // less than one more launch: krob200's vec phase 14.4 us without, 17.0 us with it)
+   int *fbi = I.C >= 512 ? ctx->d_veclb + vec_lb_ints(I.C, LS) : nullptr;
    PhaseTimer pt(ctx, VNSGPU_PHASE_VEC, st);
-   k_rows_to_int<<<std::min(64, (Smax + 2) * I.mp / 256 + 1), 256, 0, st>>>(I, ctx->paths[path].d, fbi, LS);
-   LAUNCHED(ctx);
+   if (fbi) {
+      k_rows_to_int<<<std::min(64, (Smax + 2) * I.mp / 256 + 1), 256, 0, st>>>(I, ctx->paths[path].d, fbi, LS);
+      LAUNCHED(ctx);
+   }
    // small clusters on a symmetric table: 2 - 4 clusters per warp (k_vec_uw_packed)
    const int pslot = (I.symmetric && ctx->use_vec_pack) ? (I.mp <= 8 ? 8 : (I.mp <= 10 ? 10 : (I.mp <= 16 ? 16 : 0))) : 0;
    if (pslot) {

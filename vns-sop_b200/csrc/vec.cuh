@@ -152,8 +152,9 @@ __global__ void __launch_bounds__(256) k_vec_uw(InstDev I, PathDev P, const TT *
       const TT *bU = nullptr, *bW = nullptr;
       if (doU || sym) bU = warp_stage(sU, Dv + ((long long)ol * I.N + (long long)ml * oc), ml * mc, lane);     // D(cl, c)
       if (doW && !sym) bW = warp_stage(sW, Dv + ((long long)oc * I.N + (long long)mc * ol), mc * ml, lane);    // D(c, cl)
-      const int f = (doU && lane < ml) ? __ldg(fbi + l * mp + lane) : VNS_INT_INF;
-      const int bv = (doW && lane < ml) ? __ldg(fbi + (LS + l) * mp + lane) : VNS_INT_INF;
+      // fbi: the rows as int32 (k_rows_to_int, large instances), else converted here
+      const int f = (doU && lane < ml) ? (fbi ? __ldg(fbi + l * mp + lane) : (int)P.F[(size_t)l * mp + lane]) : VNS_INT_INF;
+      const int bv = (doW && lane < ml) ? (fbi ? __ldg(fbi + (LS + l) * mp + lane) : (int)P.B[(size_t)l * mp + lane]) : VNS_INT_INF;
       int lb_ins = 0, lb_rep = 0, lb_rem = 0;
       if (doW && lane == 0) {   // lower-bound sums (integers: order-free)
          const int a = lm.cl(l - 1), nx = l <= S - 1 ? lm.cl(l + 1) : cl;
@@ -208,8 +209,9 @@ __global__ void __launch_bounds__(256) k_vec_uw_packed(InstDev I, PathDev P, con
       const int cl = lm.cl(l), ml = lm.m(l), ol = lm.off(l);
       const bool doU = l <= S - 1, doW = l >= 1;
       const TT *run = warp_stage(sU, Dv + ((long long)ol * I.N + (long long)ml * oc0), ml * (oend - oc0), lane);   // D(cl, c0 ..)
-      const int f = (doU && lane < ml) ? __ldg(fbi + l * mp + lane) : VNS_INT_INF;
-      const int bv = (doW && lane < ml) ? __ldg(fbi + (LS + l) * mp + lane) : VNS_INT_INF;
+      // fbi: the rows as int32 (k_rows_to_int, large instances), else converted here
+      const int f = (doU && lane < ml) ? (fbi ? __ldg(fbi + l * mp + lane) : (int)P.F[(size_t)l * mp + lane]) : VNS_INT_INF;
+      const int bv = (doW && lane < ml) ? (fbi ? __ldg(fbi + (LS + l) * mp + lane) : (int)P.B[(size_t)l * mp + lane]) : VNS_INT_INF;
       int lb_ins = 0, lb_rep = 0, lb_rem = 0;
       if (doW && cok && j == 0) {   // lower-bound sums (integers: order-free)
          const int a = lm.cl(l - 1), nx = l <= S - 1 ? lm.cl(l + 1) : cl;
