@@ -133,6 +133,12 @@ def test_20k_instance_properties():
                 outs[(int_path, seg)] = p.eval_batch(p.make_cands(cands))
         e.set_int_path(True)
         e.set_segment_cache(True)
+        # the endpoint-vector form (this batch is below its break-even at 2000 clusters: forced), whose per-state build takes
+        # its large-instance branches here: int32 row copies, lower-bound sums in a kernel of their own, two-level segment build
+        for vec in (2, 3):
+            e.set_vector_cache(vec)
+            outs[("vec", vec)] = p.eval_batch(p.make_cands(cands))
+        e.set_vector_cache(True)
         ln, lb, fl, first = outs[(True, True)]
         for k, (l2, b2, f2, first2) in outs.items():
             assert (l2 == ln).all() and (b2 == lb).all() and (f2 == fl).all() and first2 == first, k

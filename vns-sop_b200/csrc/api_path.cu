@@ -400,6 +400,8 @@ static vnsgpu_status prepare_eval(vnsgpu_ctx *ctx, int path, int mode, cudaStrea
    if (fbi) {
       k_rows_to_int<<<std::min(64, (Smax + 2) * I.mp / 256 + 1), 256, 0, st>>>(I, ctx->paths[path].d, fbi, LS);
       LAUNCHED(ctx);
+      k_vec_lbs<<<8 * ctx->num_sms, 256, 0, st>>>(I, ctx->paths[path].d, ctx->d_segmeta, ctx->d_dmin32, ctx->d_veclb, LS);
+      LAUNCHED(ctx);
    }
    // small clusters on a symmetric table: 2 - 4 clusters per warp (k_vec_uw_packed)
    const int pslot = (I.symmetric && ctx->use_vec_pack) ? (I.mp <= 8 ? 8 : (I.mp <= 10 ? 10 : (I.mp <= 16 ? 16 : 0))) : 0;

@@ -127,6 +127,25 @@ static __global__ void __launch_bounds__(256) k_rows_to_int(InstDev I, PathDev P
    }
 }
 
+// The lower-bound sums of k_vec_uw / k_vec_uw_packed as a kernel of their own, one thread per (cluster c, layer l), l fastest:
+// inside the build kernels a whole warp issued the three gathers and their 64-bit indices for one lane in ten (ncu r5k: 14 %
+// of k_vec_uw_packed's instructions).  Large instances only (the build kernels skip the sums when they get int32 rows).
+static __global__ void __launch_bounds__(256) k_vec_lbs(InstDev I, PathDev P, const int *__restrict__ meta, const int *__restrict__ dmin,
+                                                        int *__restrict__ lbs, int LS)
+{
+   const int T = P.hdr[HDR_T], S = T + 1, C = I.C;
+   const LayerMeta lm = layer_meta(I, meta);
+   const long long n = (long long)C * S;
+   for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (long long)gridDim.x * blockDim.x) {
+      const int c = (int)(e / S), l = (int)(e - (long long)c * S) + 1;            // l = 1 .. S
+      const int a = lm.cl(l - 1), cl = lm.cl(l), nx = l <= S - 1 ? lm.cl(l + 1) : cl;
+      const int din = __ldg(dmin + (size_t)a * C + c);
+      lbs[(size_t)c * LS + l] = din + __ldg(dmin + (size_t)c * C + cl);                               // insert c before l
+      if (l <= S - 1) lbs[(size_t)(C + c) * LS + l] = din + __ldg(dmin + (size_t)c * C + nx);         // c replaces l
+      if (c == 0 && l <= S - 1) lbs[(size_t)2 * C * LS + l] = __ldg(dmin + (size_t)a * C + nx);       // l removed
+   }
+}
+
 // one warp per (l, c), l strided over grid.y: consecutive warps read consecutive blocks of row band lcl[l] (U) and write
 // consecutive vectors.  Needs mp <= 32.  Dynamic shared memory: 2 slots (vec_slot_bytes) per warp.
 template <typename TT>
@@ -156,7 +175,7 @@ __global__ void __launch_bounds__(256) k_vec_uw(InstDev I, PathDev P, const TT *
       const int f = (doU && lane < ml) ? (fbi ? __ldg(fbi + l * mp + lane) : (int)P.F[(size_t)l * mp + lane]) : VNS_INT_INF;
       const int bv = (doW && lane < ml) ? (fbi ? __ldg(fbi + (LS + l) * mp + lane) : (int)P.B[(size_t)l * mp + lane]) : VNS_INT_INF;
       int lb_ins = 0, lb_rep = 0, lb_rem = 0;
-      if (doW && lane == 0) {   // lower-bound sums (integers: order-free)
+      if (doW && lane == 0 && !fbi) {   // lower-bound sums (integers: order-free); large instances: k_vec_lbs
          const int a = lm.cl(l - 1), nx = l <= S - 1 ? lm.cl(l + 1) : cl;
          const int din = __ldg(dmin + (size_t)a * C + c);
          lb_ins = din + __ldg(dmin + (size_t)c * C + cl);
@@ -172,7 +191,7 @@ __global__ void __launch_bounds__(256) k_vec_uw(InstDev I, PathDev P, const TT *
       if (doW) {   // W(c,l) = D(c, cl) (x) B[l]
          const int wv = sym ? vec_fwd(bU, ml, mc, bv, lane) : vec_bwd(bW, mc, ml, bv, lane);
          if (lane < mp) vec[vec_uw(vc, C, mp, 1, c, l) + lane] = wv;
-         if (lane == 0) {
+         if (lane == 0 && !fbi) {
             lbs[(size_t)c * LS + l] = lb_ins;                                   // insert c before l
             if (l <= S - 1) lbs[(size_t)(C + c) * LS + l] = lb_rep;             // c replaces l
             if (c == 0 && l <= S - 1) lbs[(size_t)2 * C * LS + l] = lb_rem;     // l removed
@@ -213,7 +232,7 @@ __global__ void __launch_bounds__(256) k_vec_uw_packed(InstDev I, PathDev P, con
       const int f = (doU && lane < ml) ? (fbi ? __ldg(fbi + l * mp + lane) : (int)P.F[(size_t)l * mp + lane]) : VNS_INT_INF;
       const int bv = (doW && lane < ml) ? (fbi ? __ldg(fbi + (LS + l) * mp + lane) : (int)P.B[(size_t)l * mp + lane]) : VNS_INT_INF;
       int lb_ins = 0, lb_rep = 0, lb_rem = 0;
-      if (doW && cok && j == 0) {   // lower-bound sums (integers: order-free)
+      if (doW && cok && j == 0 && !fbi) {   // lower-bound sums (integers: order-free); large instances: k_vec_lbs
          const int a = lm.cl(l - 1), nx = l <= S - 1 ? lm.cl(l + 1) : cl;
          const int din = __ldg(dmin + (size_t)a * C + c);
          lb_ins = din + __ldg(dmin + (size_t)c * C + cl);
@@ -247,7 +266,7 @@ __global__ void __launch_bounds__(256) k_vec_uw_packed(InstDev I, PathDev P, con
          }
          if (doW) vec[vec_uw(vc, C, mp, 1, c, l) + j] = j < mc ? wv : VNS_INT_INF;
       }
-      if (doW && cok && j == 0) {
+      if (doW && cok && j == 0 && !fbi) {
          lbs[(size_t)c * LS + l] = lb_ins;                                   // insert c before l
          if (l <= S - 1) lbs[(size_t)(C + c) * LS + l] = lb_rep;             // c replaces l
          if (c == 0 && l <= S - 1) lbs[(size_t)2 * C * LS + l] = lb_rem;     // l removed
