@@ -105,6 +105,42 @@ def test_synthetic_shake_and_local_search(synth):
 
 
 @pytest.mark.gpu
+def test_synthetic_600_clusters_large_instance_builds_vs_oracle():
+    """6000 nodes / 600 clusters, T = 237: the smallest instance on which the per-state builds take their large-instance
+    branches (from 512 clusters on: int32 row copies, lower-bound sums in k_vec_lbs; more than 256 layers' worth of clusters:
+    two-level segment build with the 10-lane cross products) and the oracle still answers in seconds."""
+    from oracle import binding as ob
+    from vns_sop_b200 import engine, instances as ins, synthetic as sy
+    pb = ins.build_problem(sy.generate(6000, 10))
+    assert pb.C >= 512
+    e = engine.Engine(0).load_problem(pb)
+    try:
+        vns, T = sy.centroid_tour_state(pb)
+        po, pg = ob.Oracle(pb).path(vns, T), e.path(vns, T)
+        assert pg.getPathLength() == po.length() and pg.getReward() == po.reward()
+        cands = random_candidates(np.random.RandomState(7), vns, T, 120000)      # 4 n >= C^2: the endpoint-vector form engages
+        oln, olb = po.eval_batch(cands)
+        for seg, vec in ((1, True), (1, 3), (2, True), (3, 3), (1, False)):
+            e.set_segment_cache(seg)
+            e.set_vector_cache(vec)
+            ln, lb, fl, first = pg.eval_batch(pg.make_cands(cands))
+            assert (ln == oln).all() and (lb == olb).all(), (seg, vec)
+        # a state change between two batches: the builds follow the path
+        e.set_segment_cache(True)
+        e.set_vector_cache(True)
+        rg, ro = engine.seeded_rng(3), ob.new_rng(3)
+        pg.shake(1, rg)
+        po.shake(1, ro)
+        assert (pg.vns == po.vns).all() and pg.getNumTargets() == po.T
+        cands = random_candidates(np.random.RandomState(8), po.vns, po.T, 120000)
+        oln, olb = po.eval_batch(cands)
+        ln, lb, fl, first = pg.eval_batch(pg.make_cands(cands))
+        assert (ln == oln).all() and (lb == olb).all()
+    finally:
+        e.close()
+
+
+@pytest.mark.gpu
 def test_20k_instance_properties():
     """The bench workload itself (3.2 GB table, HBM regime): no oracle at this size inside the test budget, so
     size-independent properties - the table's block-major gather equals direct evaluation on sampled entries,
