@@ -136,6 +136,17 @@ def test_synthetic_600_clusters_large_instance_builds_vs_oracle():
         oln, olb = po.eval_batch(cands)
         ln, lb, fl, first = pg.eval_batch(pg.make_cands(cands))
         assert (ln == oln).all() and (lb == olb).all()
+        # greedy_insertion as batched rounds: from 512 clusters on its tryToAdd-only batches take the endpoint-vector form
+        # without pair vectors; same tour as the one-block greedy (the reference's loop), with and without the vectors
+        p1, p2, p3 = e.path(), e.path(), e.path()
+        p1.greedy_insertion()
+        rounds, evals = p2.greedy_insertion_batched()
+        assert rounds == p1.getNumTargets() == p2.getNumTargets() and (p1.vns == p2.vns).all()
+        assert p1.getPathLength() == p2.getPathLength() and p1.getReward() == p2.getReward()
+        e.set_vector_cache(0)
+        p3.greedy_insertion_batched()
+        e.set_vector_cache(True)
+        assert (p3.vns == p1.vns).all() and p3.getPathLength() == p1.getPathLength()
     finally:
         e.close()
 

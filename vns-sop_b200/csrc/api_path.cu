@@ -217,6 +217,20 @@ static int eval_mode(const vnsgpu_ctx *ctx, int64_t n)
    return 1;
 }
 
+// A batch of tryToAdd candidates only (the greedy grid of best.cu) on a large instance: endpoint vectors whatever the batch
+// size - ADD is a dot-min of U and W, so the build stops after k_vec_uw (no pair vectors) and nothing is sorted
+static int eval_mode_hinted(vnsgpu_ctx *ctx, int64_t n)
+{
+   const bool add_only = ctx->batch_add_only;
+   ctx->batch_add_only = false;
+   int mode = eval_mode(ctx, n);
+   const int64_t C = ctx->I.C;
+   ctx->vec_skip_pairs = add_only && C >= 512 && seg_wanted(ctx, n) && ctx->use_vec && ctx->I.mp <= 32 &&
+                         vec_ints((int)C, (int)C + 2, ctx->I.mp) < (1ull << 31);
+   if (ctx->vec_skip_pairs) mode = 2;
+   return mode;
+}
+
 // T + 2 as the host last read it - when it did and the launch is not being captured into a graph (a graph is replayed on
 // later states) - else `bound`.  Only for grids of kernels whose result does not depend on the grid.
 static int known_layers(vnsgpu_ctx *ctx, int path, cudaStream_t st, int bound)
@@ -418,6 +432,7 @@ static vnsgpu_status prepare_eval(vnsgpu_ctx *ctx, int path, int mode, cudaStrea
    } else if (u16) k_vec_uw<unsigned short><<<dim3(gxu, gyu), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D16, ctx->d_segmeta, ctx->d_vec, ctx->d_veclb, LS, fbi, ctx->d_dmin32);
    else k_vec_uw<int><<<dim3(gxu, gyu), thr, smem, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta, ctx->d_vec, ctx->d_veclb, LS, fbi, ctx->d_dmin32);
    LAUNCHED(ctx);
+   if (ctx->vec_skip_pairs) return VNSGPU_OK;      // tryToAdd candidates only: U and W are all they read
    if (u16) k_vec_pairs<unsigned short><<<dim3(gxp, gyp), thr, smem_p, st>>>(I, ctx->paths[path].d, ctx->d_D16, ctx->d_segmeta, ctx->d_vec, LS);
    else k_vec_pairs<int><<<dim3(gxp, gyp), thr, smem_p, st>>>(I, ctx->paths[path].d, ctx->d_D32, ctx->d_segmeta, ctx->d_vec, LS);
    LAUNCHED(ctx);
@@ -436,7 +451,7 @@ static bool vec_lat(const vnsgpu_ctx *ctx) { return (size_t)ctx->I.N * ctx->I.N 
 static bool eval_sorts(const vnsgpu_ctx *ctx, int64_t n, int useseg)
 {
    const bool light = useseg == 2 && !vec_lat(ctx) && ctx->I.mp <= 2 * ctx->group_lanes;
-   return group_kernel_ok(ctx) && ctx->sort_batches && n >= VNS_SORT_MIN && n < (1ll << 32) && !light;
+   return group_kernel_ok(ctx) && ctx->sort_batches && n >= VNS_SORT_MIN && n < (1ll << 32) && !light && !ctx->vec_skip_pairs;
 }
 
 // fmt / d_leni: only with useseg == 2 and !eval_sorts(): d_cands are vnsgpu_pack_cand32 words read in place (fmt 2),
@@ -620,13 +635,11 @@ vnsgpu_status vnsgpu_eval_batch_dev(vnsgpu_ctx *ctx, int path, int64_t n, const 
    if (n <= 0) return VNSGPU_OK;
    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
    if (d_first_accept) CK(cudaMemsetAsync(d_first_accept, 0xFF, sizeof(long long), st));   // -1 = none
-   const int useseg = eval_mode(ctx, n);
-   {
-      vnsgpu_status s = prepare_eval(ctx, path, useseg, st);
-      if (s) return s;
-   }
-   return launch_eval(ctx, path, n, 0, d_cands, budget, skip, d_len, d_lb, d_flags, (unsigned long long *)d_first_accept, st, 0, 0,
-                      useseg);
+   const int useseg = eval_mode_hinted(ctx, n);
+   vnsgpu_status s = prepare_eval(ctx, path, useseg, st);
+   if (!s) s = launch_eval(ctx, path, n, 0, d_cands, budget, skip, d_len, d_lb, d_flags, (unsigned long long *)d_first_accept, st, 0, 0, useseg);
+   ctx->vec_skip_pairs = false;
+   return s;
 }
 
 // One rank's shard of a batch that several GPUs evaluate: the key of the first accepted candidate comes

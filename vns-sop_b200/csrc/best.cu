@@ -272,8 +272,10 @@ static vnsgpu_status best_step(vnsgpu_ctx *ctx, int path, int kind, double budge
       k_nbh_cands<<<grid, 256, 0, ctx->stream>>>(P, kind, k0, nl, b->cands);
       LAUNCHED(ctx);
       ctx->seg_fresh_path = fresh ? path : -1;      // the products path_rows_from_products built for this very state
+      ctx->batch_add_only = kind == 0;              // the greedy grid: tryToAdd only
       s = vnsgpu_eval_batch_dev(ctx, path, nl, b->cands, budget, 0, b->len, nullptr, kind == 0 ? nullptr : b->flags, nullptr, ctx->stream);
       ctx->seg_fresh_path = -1;
+      ctx->batch_add_only = false;
       if (s) return s;
    }
    if (kind == 0)

@@ -114,6 +114,8 @@ struct vnsgpu_ctx {
    void *h_pick = nullptr;        // pinned record vnsgpu_propose_eval reads back
    void *d_gen = nullptr, *d_gencands = nullptr;
    size_t gen_bytes = 0, gencands_bytes = 0;
+   bool batch_add_only = false;   // set by best.cu right before an evaluation call: the batch holds tryToAdd candidates only
+   bool vec_skip_pairs = false;   // while such a batch is evaluated in endpoint-vector form: no pair vectors, no sort
    int seg_fresh_path = -1;       // set by best.cu right before an evaluation call: the products of this path's state are current
    bool shard_nbh = false;        // vnsgpu_set_shard_neighbourhoods: full-neighbourhood modes split every neighbourhood over the communicator's ranks
    void *d_best = nullptr;        // full-neighbourhood modes (best.cu): descriptors, lengths, flags, partial keys
