@@ -1,0 +1,2 @@
+mkdir -p gpurun_out
+timeout 600 python scripts/time_greedy_sharded.py synth20k 2 > gpurun_out/r7a_sharded_synth20k_n2.log 2>&1; tail -6 gpurun_out/r7a_sharded_synth20k_n2.log

@@ -16,6 +16,9 @@ if len(sys.argv) > 3:          # worker: WORKLOAD NGPUS RANK TMP
     while not os.path.exists(idf):
         time.sleep(0.05)
     e.comm_init(open(idf, "rb").read(), rank, world)
+    # the communicator's first collective sets its channels up (a few hundred ms): not part of either timing
+    e.set_shard_neighbourhoods(1)
+    w = e.path(); w.greedy_insertion_batched(); w.best_move(1); e.sync()
     for shard in (0, 1):
         e.set_shard_neighbourhoods(shard)
         p = e.path(); e.sync()
